@@ -1,0 +1,235 @@
+/*
+ * gut_b200.h -- C ABI of the B200-native 3DGUT rasteriser (libgut_b200.so).
+ *
+ * This is the drop-in boundary for the reference's native layer: every entry
+ * point replaces one piece of the pybind11 module `lib3dgut_cc`
+ * (reference: threedgut_tracer/bindings.cpp:79-113, class SplatRaster in
+ * threedgut_tracer/include/3dgut/splatRaster.h:47-89).  Plain C types only:
+ * raw device pointers, sizes and a cudaStream_t passed as void*.  No torch,
+ * no pybind, no C++ types cross this line.
+ *
+ * Conventions
+ *  - every function returns 0 on success or a GutStatus error code; the text
+ *    of the last error of a handle is available from gut_last_error().
+ *    (The reference logs and swallows errors, splatRaster.cpp:225-237; the
+ *    host wrapper here raises instead.)
+ *  - all pointers named d_* are DEVICE pointers valid on the handle's device,
+ *    16-byte aligned, fp32 unless stated, borrowed for the duration of the
+ *    call (the work is enqueued on `stream`; the caller keeps them alive
+ *    until the stream reaches that point, as PyTorch's caching allocator
+ *    does for tensors used on the current stream).
+ *  - a handle is NOT thread safe, like the reference's SplatRaster
+ *    (mutable m_parameters / m_forwardContext).
+ *  - gut_backward consumes the forward context of the immediately preceding
+ *    gut_forward on the same handle and stream
+ *    (reference: gutRenderer.cu:413-417).
+ */
+#ifndef GUT_B200_H
+#define GUT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GUT_ABI_VERSION 1
+
+typedef enum GutStatus {
+    GUT_OK                = 0,
+    GUT_ERR_BAD_INPUT     = 1, /* null pointer, bad size, unsupported config     */
+    GUT_ERR_CUDA          = 2, /* a CUDA runtime call failed (see last_error)     */
+    GUT_ERR_NO_FORWARD    = 3, /* backward without a matching forward context     */
+    GUT_ERR_OUT_OF_MEMORY = 4,
+    GUT_ERR_UNSUPPORTED   = 5
+} GutStatus;
+
+/* reference: CameraModelParameters::ShutterType, cameraModels.h:39-45 (same order) */
+typedef enum GutShutterType {
+    GUT_SHUTTER_ROLLING_TOP_TO_BOTTOM = 0,
+    GUT_SHUTTER_ROLLING_LEFT_TO_RIGHT = 1,
+    GUT_SHUTTER_ROLLING_BOTTOM_TO_TOP = 2,
+    GUT_SHUTTER_ROLLING_RIGHT_TO_LEFT = 3,
+    GUT_SHUTTER_GLOBAL                = 4
+} GutShutterType;
+
+/* reference: CameraModelParameters::ModelType, cameraModels.h:47-52 */
+typedef enum GutCameraModel {
+    GUT_CAMERA_OPENCV_PINHOLE = 0,
+    GUT_CAMERA_OPENCV_FISHEYE = 1
+} GutCameraModel;
+
+/*
+ * The compile-time -D defines of the reference (threedgut_tracer/setup_3dgut.py:47-70,
+ * consumed in include/3dgut/threedgut.cuh:31-83) become one runtime struct;
+ * kernels are template-specialised on the fields that shape register use
+ * (kernel_degree, k_buffer_size) and read the rest as launch constants.
+ * Defaults = configs/render/3dgut.yaml + configs/render/3dgrt.yaml.
+ */
+typedef struct GutConfig {
+    int32_t abi_version;                 /* must be GUT_ABI_VERSION                              */
+    int32_t kernel_degree;               /* particle_kernel_degree: 0,1,2,3,4,5,8  (default 2)    */
+    float   min_kernel_response;         /* particle_kernel_min_response            (0.0113)      */
+    float   min_alpha;                   /* particle_kernel_min_alpha               (1/255)       */
+    float   max_alpha;                   /* particle_kernel_max_alpha               (0.99)        */
+    float   min_transmittance;           /* min_transmittance                       (1e-4)        */
+    int32_t sph_max_degree;              /* particle_radiance_sph_degree -> (d+1)^2 coeffs (3)    */
+    int32_t enable_hitcounts;            /* enable_hitcounts                        (1)           */
+    int32_t rect_bounding;               /* splat.rect_bounding                     (1)           */
+    int32_t tight_opacity_bounding;      /* splat.tight_opacity_bounding            (1)           */
+    int32_t tile_based_culling;          /* splat.tile_based_culling                (1)           */
+    int32_t n_rolling_shutter_iterations;/* splat.n_rolling_shutter_iterations      (5)           */
+    float   ut_alpha, ut_beta, ut_kappa; /* splat.ut_*                              (1, 2, 0)     */
+    float   ut_in_image_margin_factor;   /* splat.ut_in_image_margin_factor         (0.1)         */
+    int32_t ut_require_all_sigma_points_valid; /* must be 0 (threedgut.cuh:73)                    */
+    int32_t k_buffer_size;               /* splat.k_buffer_size: 0 = unsorted       (0)           */
+    int32_t global_z_order;              /* splat.global_z_order                    (1)           */
+    int32_t enable_kernel_timings;       /* render.enable_kernel_timings            (0)           */
+} GutConfig;
+
+/* Fill *cfg with the reference defaults listed above. */
+void gut_default_config(GutConfig* cfg);
+
+/*
+ * Camera intrinsics + the two shutter poses of one view.
+ * reference: CameraModelParameters (cameraModels.h:22-58) built by
+ * fromOpenCV{Pinhole,Fisheye}CameraModelParameters (bindings.cpp:33-77) and
+ * TSensorState (sensors.h:37-42).  Poses are WORLD->SENSOR, stored
+ * [tx,ty,tz,qx,qy,qz,qw] (sensors.h:33).
+ */
+typedef struct GutCamera {
+    int32_t model;               /* GutCameraModel                                   */
+    int32_t shutter;             /* GutShutterType                                   */
+    float   principal_point[2];
+    float   focal_length[2];
+    float   radial_coeffs[6];    /* pinhole k1..k6 ; fisheye uses [0..3]             */
+    float   tangential_coeffs[2];/* pinhole only                                     */
+    float   thin_prism_coeffs[4];/* pinhole only                                     */
+    float   max_angle;           /* fisheye only                                     */
+    float   start_pose[7];
+    float   end_pose[7];
+    int64_t start_timestamp_us;  /* carried for API fidelity; kernels never read it  */
+    int64_t end_timestamp_us;
+} GutCamera;
+
+/*
+ * Optional stage outputs for the bit-exact parity tests.  Any
+ * pointer may be NULL.  Sizes: per-particle arrays N; sorted arrays
+ * `capacity_intersections` entries (the call fails with GUT_ERR_BAD_INPUT if
+ * the frame produced more).  All device pointers.
+ */
+typedef struct GutStageOutputs {
+    uint32_t* d_tiles_count;        /* [N]   K1: tiles touched per particle          */
+    float*    d_proj_position;      /* [N,2] K1                                      */
+    float*    d_proj_conic_opacity; /* [N,4] K1                                      */
+    float*    d_proj_extent;        /* [N,2] K1                                      */
+    float*    d_global_depth;       /* [N]   K1                                      */
+    float*    d_features;           /* [N,3] K1: SH->RGB + 0.5, unclamped            */
+    uint64_t* d_sorted_keys;        /* [M]   (tile<<32)|depth bits, sorted           */
+    uint32_t* d_sorted_particle_idx;/* [M]   particle index per sorted key           */
+    uint32_t* d_tile_ranges;        /* [T,2] first / one-past-last sorted index      */
+    uint64_t  capacity_intersections;
+    uint64_t  num_intersections;    /* OUT: M of this frame                          */
+} GutStageOutputs;
+
+typedef struct GutHandle GutHandle;
+
+/* reference: SplatRaster::SplatRaster(json) splatRaster.cpp:153-168 */
+int gut_create(const GutConfig* cfg, int device, GutHandle** out);
+/* reference: SplatRaster::~SplatRaster + ~GutRenderForwardContext gutRenderer.cu:106-127 */
+void gut_destroy(GutHandle* h);
+
+/*
+ * Forward render of one view.  reference: SplatRaster::trace
+ * (splatRaster.cpp:173-244) -> GUTRenderer::renderForward (gutRenderer.cu:241-398).
+ *
+ *   d_particle_density [N,12] = {pos3, density, quat wxyz, scale3, pad}   (gaussianParticles.cuh:20-26)
+ *   d_particle_radiance[N,(sph_max_degree+1)^2,3] SH coefficients
+ *   d_ray_origin, d_ray_direction [H,W,3] sensor-space rays
+ * outputs (the function initialises them: rgba=0, dist=1e6, hits=0, visibility=0,
+ * as torch::zeros/ones do at splatRaster.cpp:196-199):
+ *   d_ray_radiance_density [H,W,4], d_ray_hit_distance [H,W], d_ray_hit_count [H,W],
+ *   d_particle_visibility [N] (1.0f where the projected conic is valid; the
+ *   reference stores int 1 in float storage)
+ */
+int gut_forward(GutHandle* h, void* stream, const GutCamera* camera,
+                uint32_t num_particles, int32_t sph_degree_active,
+                const float* d_particle_density, const float* d_particle_radiance,
+                uint32_t width, uint32_t height,
+                const float* d_ray_origin, const float* d_ray_direction,
+                float* d_ray_radiance_density, float* d_ray_hit_distance,
+                float* d_ray_hit_count, float* d_particle_visibility,
+                GutStageOutputs* stage_outputs /* may be NULL */);
+
+/*
+ * Backward of the immediately preceding gut_forward.  reference:
+ * SplatRaster::traceBwd (splatRaster.cpp:246-332) -> GUTRenderer::renderBackward
+ * (gutRenderer.cu:400-497).
+ *   d_particle_density_grad  [N,12]  (column 11, the padding, stays 0)
+ *   d_particle_radiance_grad [N,(sph_max_degree+1)^2,3]
+ * accumulate == 0: the buffers are overwritten (reference semantics: fresh zeros);
+ * accumulate != 0: gradients are ADDED to the buffers' current content (used to sum
+ *   the views of one rank before the data-parallel allreduce).
+ */
+int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
+                 uint32_t num_particles, int32_t sph_degree_active,
+                 const float* d_particle_density, const float* d_particle_radiance,
+                 uint32_t width, uint32_t height,
+                 const float* d_ray_origin, const float* d_ray_direction,
+                 const float* d_ray_radiance_density, const float* d_ray_radiance_density_grad,
+                 const float* d_ray_hit_distance, const float* d_ray_hit_distance_grad,
+                 float* d_particle_density_grad, float* d_particle_radiance_grad,
+                 int32_t accumulate);
+
+/*
+ * Same two calls with HOST buffers: inputs are copied host->device and results
+ * device->host inside the call on `stream` (the end-to-end path bench.py times).
+ * Particle parameters stay device resident (they are the model, not a per-view
+ * input).  Pointers named h_* are host pointers, ideally pinned.
+ */
+int gut_forward_host(GutHandle* h, void* stream, const GutCamera* camera,
+                     uint32_t num_particles, int32_t sph_degree_active,
+                     const float* d_particle_density, const float* d_particle_radiance,
+                     uint32_t width, uint32_t height,
+                     const float* h_ray_origin, const float* h_ray_direction,
+                     float* h_ray_radiance_density, float* h_ray_hit_distance,
+                     float* h_ray_hit_count, float* d_particle_visibility);
+
+int gut_backward_host(GutHandle* h, void* stream, const GutCamera* camera,
+                      uint32_t num_particles, int32_t sph_degree_active,
+                      const float* d_particle_density, const float* d_particle_radiance,
+                      uint32_t width, uint32_t height,
+                      const float* h_ray_radiance_density_grad, const float* h_ray_hit_distance_grad,
+                      float* d_particle_density_grad, float* d_particle_radiance_grad,
+                      int32_t accumulate);
+
+/* reference: SplatRaster::collectTimes splatRaster.cpp:334-364 -- mean ms of the
+ * forward/backward calls since the last collection; -1 when none was timed. */
+int gut_timings(GutHandle* h, float* forward_render_ms, float* backward_render_ms);
+
+/*
+ * Per-stage mean device times (ms) since the last call, in the order of
+ * gut_stage_name(i), i < gut_num_stages().  Stage names follow the reference's
+ * DeviceLaunchesLogger tags (gutRenderer.cu:256-378).
+ */
+int         gut_num_stages(void);
+const char* gut_stage_name(int i);
+int         gut_stage_timings(GutHandle* h, float* ms_out /* [gut_num_stages()] */);
+
+/* Statistics of the last forward (what defines the work). */
+typedef struct GutFrameStats {
+    uint64_t num_intersections;     /* M                                    */
+    uint32_t num_tiles;             /* T                                    */
+    uint32_t max_tile_list_length;
+    uint64_t kernel_launches;       /* kernels launched by this handle so far */
+} GutFrameStats;
+int gut_frame_stats(GutHandle* h, GutFrameStats* out);
+
+const char* gut_last_error(GutHandle* h);
+int         gut_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GUT_B200_H */
