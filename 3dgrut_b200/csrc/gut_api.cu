@@ -1,0 +1,516 @@
+// gut_api.cu -- the C ABI of libgut_b200 (include/gut_b200.h): handle, workspace, stage sequencing.
+//
+// Replaces the reference's SplatRaster (threedgut_tracer/src/splatRaster.cpp) and GUTRenderer host code
+// (threedgut_tracer/src/gutRenderer.cu:99-497).  No torch, no pybind: raw device pointers and a stream.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <deque>
+#include <string>
+#include <vector>
+
+#include "gut_internal.h"
+
+namespace {
+
+enum Stage { ST_PROJECT = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RENDER, ST_BWD_RENDER, ST_BWD_PROJECT, ST_COUNT };
+const char* kStageNames[ST_COUNT] = {"render::project", "render::prepare-expand", "render::expand", "render::sort",
+                                     "render::render",  "render-backward::render", "render-backward::project"};
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+    int tag = 0;
+};
+
+}  // namespace
+
+struct GutHandle {
+    GutConfig cfg;
+    int device = 0;
+    std::string error;
+    uint64_t launches = 0;
+
+    // per-particle workspace (K1 outputs) -- grow only, like GutRenderForwardContext (gutRenderer.cu:166-203)
+    DevBuf tiles_count, proj_pos, conic, extent, depth, features, feature_grad;
+    // per-tile
+    DevBuf tile_hist, tile_start, tile_cursor, stats;
+    // per-intersection
+    DevBuf entries, scratch, sorted_idx, records, quats;
+    // host-buffer mode (gut_*_host)
+    DevBuf h_ray_ori, h_ray_dir, h_rgba, h_dist, h_hits, h_rgba_grad, h_dist_grad;
+    uint32_t* pinned_stats = nullptr;  // [2] = {M, max tile list}
+
+    // forward context consumed by backward
+    bool fwd_valid = false;
+    cudaStream_t fwd_stream = nullptr;
+    uint32_t fwd_N = 0, fwd_W = 0, fwd_H = 0;
+    uint64_t fwd_M = 0;
+    uint32_t fwd_max_list = 0;
+    GutFrame fwd_frame = {};
+
+    // timers (SplatRaster::CudaTimer, splatRaster.cpp:108-151): keep the last 256
+    std::deque<EventPair> timers;        // tag 0 = forward_render, 1 = backward_render
+    std::deque<EventPair> stage_timers;  // tag = Stage
+    float last_fwd_ms = -1.0f, last_bwd_ms = -1.0f;
+    float last_stage_ms[ST_COUNT];
+};
+
+namespace {
+
+int fail(GutHandle* h, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->error = buf;
+    return code;
+}
+
+#define GUT_CUDA(h, call)                                                                                    \
+    do {                                                                                                     \
+        cudaError_t e_ = (call);                                                                             \
+        if (e_ != cudaSuccess)                                                                               \
+            return fail(h, e_ == cudaErrorMemoryAllocation ? GUT_ERR_OUT_OF_MEMORY : GUT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, \
+                        cudaGetErrorString(e_), __FILE__, __LINE__);                                         \
+    } while (0)
+
+cudaError_t ensure(DevBuf& b, size_t bytes, cudaStream_t s, float slack = 1.0f) {
+    if (bytes <= b.cap && b.p) return cudaSuccess;
+    if (b.p) {
+        cudaError_t e = cudaFreeAsync(b.p, s);
+        if (e != cudaSuccess) return e;
+        b.p = nullptr; b.cap = 0;
+    }
+    size_t want = (size_t)((double)bytes * slack);
+    want = (want + 255) & ~(size_t)255;
+    if (want == 0) want = 256;
+    cudaError_t e = cudaMallocAsync(&b.p, want, s);
+    if (e != cudaSuccess) { b.p = nullptr; return e; }
+    b.cap = want;
+    return cudaSuccess;
+}
+
+void release(DevBuf& b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.cap = 0;
+}
+
+// ---- host pose algebra (reference: include/3dgut/sensors/sensors.h:44-73, tcnn quaternion helpers vec.h:1066-1183) ----
+struct HQuat { float w, x, y, z; };
+
+void quat_cols(HQuat q, float3& c0, float3& c1, float3& c2) { quat_to_columns(q.w, q.x, q.y, q.z, c0, c1, c2); }
+
+HQuat quat_from_cols(float3 c0, float3 c1, float3 c2) {
+    // m[i][j] = column i, row j
+    const float m00 = c0.x, m01 = c0.y, m02 = c0.z, m10 = c1.x, m11 = c1.y, m12 = c1.z, m20 = c2.x, m21 = c2.y, m22 = c2.z;
+    HQuat q;
+    const float tr = m00 + m11 + m22;
+    if (tr > 0.0f) {
+        const float S = sqrtf(tr + 1.0f) * 2.0f;
+        q.w = 0.25f * S; q.x = (m12 - m21) / S; q.y = (m20 - m02) / S; q.z = (m01 - m10) / S;
+    } else if (m00 > m11 && m00 > m22) {
+        const float S = sqrtf(1.0f + m00 - m11 - m22) * 2.0f;
+        q.w = (m12 - m21) / S; q.x = 0.25f * S; q.y = (m10 + m01) / S; q.z = (m20 + m02) / S;
+    } else if (m11 > m22) {
+        const float S = sqrtf(1.0f + m11 - m00 - m22) * 2.0f;
+        q.w = (m20 - m02) / S; q.x = (m10 + m01) / S; q.y = 0.25f * S; q.z = (m21 + m12) / S;
+    } else {
+        const float S = sqrtf(1.0f + m22 - m00 - m11) * 2.0f;
+        q.w = (m01 - m10) / S; q.x = (m20 + m02) / S; q.y = (m21 + m12) / S; q.z = 0.25f * S;
+    }
+    return q;
+}
+
+HQuat host_slerp(HQuat a, HQuat b, float t) {
+    float c = (a.w * b.w + a.x * b.x) + (a.y * b.y + a.z * b.z);
+    if (c < 0.0f) { b.w = -b.w; b.x = -b.x; b.y = -b.y; b.z = -b.z; c = -c; }
+    HQuat r;
+    if (c > 1.0f - 1.1920928955078125e-07f) {
+        const float u = 1.0f - t;
+        r.w = a.w * u + b.w * t; r.x = a.x * u + b.x * t; r.y = a.y * u + b.y * t; r.z = a.z * u + b.z * t;
+    } else {
+        const float ang = acosf(c);
+        const float s0 = sinf((1.0f - t) * ang), s1 = sinf(t * ang), sd = sinf(ang);
+        r.w = (s0 * a.w + s1 * b.w) / sd; r.x = (s0 * a.x + s1 * b.x) / sd;
+        r.y = (s0 * a.y + s1 * b.y) / sd; r.z = (s0 * a.z + s1 * b.z) / sd;
+    }
+    return r;
+}
+
+GutFrame make_frame(const GutConfig& cfg, const GutCamera& cam, uint32_t W, uint32_t H) {
+    GutFrame f;
+    f.width = W; f.height = H;
+    f.grid_x = (W + GUT_TILE - 1) / GUT_TILE;
+    f.grid_y = (H + GUT_TILE - 1) / GUT_TILE;
+    f.num_tiles = f.grid_x * f.grid_y;
+    // mid-shutter pose: lerp translation, slerp rotation at 0.5 (gutRenderer.cu:266)
+    const float* p0 = cam.start_pose; const float* p1 = cam.end_pose;
+    const HQuat qm = host_slerp(HQuat{p0[6], p0[3], p0[4], p0[5]}, HQuat{p1[6], p1[3], p1[4], p1[5]}, 0.5f);
+    const float3 tm = f3(p0[0] * (1.0f - 0.5f) + p1[0] * 0.5f, p0[1] * (1.0f - 0.5f) + p1[1] * 0.5f, p0[2] * (1.0f - 0.5f) + p1[2] * 0.5f);
+    quat_cols(qm, f.view.c[0], f.view.c[1], f.view.c[2]);
+    f.view.c[3] = tm;
+    // inverse pose: transpose -> quaternion -> matrix round trip, exactly as sensorPoseInverse + sensorPoseToMat do
+    const float3 r0 = f.view.c[0], r1 = f.view.c[1], r2 = f.view.c[2];
+    const float3 i0 = f3(r0.x, r1.x, r2.x), i1 = f3(r0.y, r1.y, r2.y), i2 = f3(r0.z, r1.z, r2.z);
+    const HQuat qi = quat_from_cols(i0, i1, i2);
+    const float3 ti = rotate_cols(-1.0f * i0, -1.0f * i1, -1.0f * i2, tm);
+    quat_cols(qi, f.c2w.c[0], f.c2w.c[1], f.c2w.c[2]);
+    f.c2w.c[3] = ti;
+    f.cam_centre = ti;
+    f.ut_delta = (float)sqrt((double)cfg.ut_alpha * (double)cfg.ut_alpha * (3.0 + (double)cfg.ut_kappa));
+    return f;
+}
+
+bool degree_supported(int d) { return d == 0 || d == 1 || d == 2 || d == 3 || d == 4 || d == 5 || d == 8; }
+
+void start_timer(std::deque<EventPair>& q, int tag, cudaStream_t s) {
+    EventPair ep;
+    ep.tag = tag;
+    if (cudaEventCreate(&ep.a) != cudaSuccess || cudaEventCreate(&ep.b) != cudaSuccess) return;
+    cudaEventRecord(ep.a, s);
+    q.push_back(ep);
+    while (q.size() > 256) {
+        cudaEventDestroy(q.front().a); cudaEventDestroy(q.front().b);
+        q.pop_front();
+    }
+}
+void stop_timer(std::deque<EventPair>& q, cudaStream_t s) {
+    if (!q.empty()) cudaEventRecord(q.back().b, s);
+}
+
+struct StageTimer {  // RAII: times one stage when kernel timings are enabled
+    GutHandle* h; cudaStream_t s; bool on;
+    StageTimer(GutHandle* h_, int tag, cudaStream_t s_) : h(h_), s(s_), on(h_->cfg.enable_kernel_timings != 0) {
+        if (on) start_timer(h->stage_timers, tag, s);
+    }
+    ~StageTimer() { if (on) stop_timer(h->stage_timers, s); }
+};
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int check_common(GutHandle* h, const GutCamera* camera, uint32_t N, int sph_degree, uint32_t W, uint32_t H) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!camera) return fail(h, GUT_ERR_BAD_INPUT, "camera is NULL");
+    if (camera->model != GUT_CAMERA_OPENCV_PINHOLE && camera->model != GUT_CAMERA_OPENCV_FISHEYE)
+        return fail(h, GUT_ERR_BAD_INPUT, "unknown camera model %d", camera->model);
+    if (camera->shutter < 0 || camera->shutter > GUT_SHUTTER_GLOBAL) return fail(h, GUT_ERR_BAD_INPUT, "unknown shutter type %d", camera->shutter);
+    if (W == 0 || H == 0) return fail(h, GUT_ERR_BAD_INPUT, "empty image %ux%u", W, H);
+    if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "active SH degree %d outside [0,%d]", sph_degree, h->cfg.sph_max_degree);
+    if ((uint64_t)N * 12ull > 0xffffffffull * 4ull) return fail(h, GUT_ERR_BAD_INPUT, "too many particles");
+    return GUT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void gut_default_config(GutConfig* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->abi_version = GUT_ABI_VERSION;
+    cfg->kernel_degree = 2;
+    cfg->min_kernel_response = 0.0113f;
+    cfg->min_alpha = (float)(1.0 / 255.0);
+    cfg->max_alpha = 0.99f;
+    cfg->min_transmittance = 0.0001f;
+    cfg->sph_max_degree = 3;
+    cfg->enable_hitcounts = 1;
+    cfg->rect_bounding = 1;
+    cfg->tight_opacity_bounding = 1;
+    cfg->tile_based_culling = 1;
+    cfg->n_rolling_shutter_iterations = 5;
+    cfg->ut_alpha = 1.0f; cfg->ut_beta = 2.0f; cfg->ut_kappa = 0.0f;
+    cfg->ut_in_image_margin_factor = 0.1f;
+    cfg->ut_require_all_sigma_points_valid = 0;
+    cfg->k_buffer_size = 0;
+    cfg->global_z_order = 1;
+    cfg->enable_kernel_timings = 0;
+}
+
+int gut_abi_version(void) { return GUT_ABI_VERSION; }
+size_t gut_sizeof_config(void) { return sizeof(GutConfig); }
+size_t gut_sizeof_camera(void) { return sizeof(GutCamera); }
+size_t gut_sizeof_stage_outputs(void) { return sizeof(GutStageOutputs); }
+size_t gut_sizeof_frame_stats(void) { return sizeof(GutFrameStats); }
+
+int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
+    if (!cfg || !out) return GUT_ERR_BAD_INPUT;
+    *out = nullptr;
+    if (cfg->abi_version != GUT_ABI_VERSION) return GUT_ERR_BAD_INPUT;
+    if (!degree_supported(cfg->kernel_degree)) return GUT_ERR_UNSUPPORTED;
+    if (cfg->sph_max_degree < 0 || cfg->sph_max_degree > 3) return GUT_ERR_UNSUPPORTED;
+    if (cfg->ut_require_all_sigma_points_valid) return GUT_ERR_UNSUPPORTED;  // static_assert in threedgut.cuh:73
+    if (cfg->k_buffer_size != 0) return GUT_ERR_UNSUPPORTED;                 // sorted (K>0) path: SURVEY 8f rank 2, not built yet
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return GUT_ERR_CUDA;
+    GutHandle* h = new GutHandle();
+    h->cfg = *cfg;
+    h->device = device;
+    for (int i = 0; i < ST_COUNT; ++i) h->last_stage_ms[i] = -1.0f;
+    DeviceGuard g(device);
+    if (cudaMallocHost(&h->pinned_stats, 2 * sizeof(uint32_t)) != cudaSuccess) { delete h; return GUT_ERR_CUDA; }
+    *out = h;
+    return GUT_OK;
+}
+
+void gut_destroy(GutHandle* h) {
+    if (!h) return;
+    DeviceGuard g(h->device);
+    cudaDeviceSynchronize();
+    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->feature_grad, &h->tile_hist,
+                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->records, &h->quats,
+                     &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
+    for (DevBuf* b : all) release(*b);
+    if (h->pinned_stats) cudaFreeHost(h->pinned_stats);
+    for (auto& t : h->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    for (auto& t : h->stage_timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    delete h;
+}
+
+const char* gut_last_error(GutHandle* h) { return h ? h->error.c_str() : "null handle"; }
+
+int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, float* d_rgba,
+                float* d_dist, float* d_hits, float* d_visibility, GutStageOutputs* so) {
+    int rc = check_common(h, camera, N, sph_degree, W, H);
+    if (rc != GUT_OK) return rc;
+    if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_dist || !d_hits) return fail(h, GUT_ERR_BAD_INPUT, "null ray/output pointer");
+    if (N > 0 && (!d_density || !d_radiance || !d_visibility)) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    h->fwd_valid = false;
+    if (h->cfg.enable_kernel_timings) start_timer(h->timers, 0, s);
+
+    const GutFrame fr = make_frame(h->cfg, *camera, W, H);
+    const uint32_t T = fr.num_tiles;
+    const size_t n1 = N ? N : 1;
+    GUT_CUDA(h, ensure(h->tiles_count, n1 * 4, s));
+    GUT_CUDA(h, ensure(h->proj_pos, n1 * 8, s));
+    GUT_CUDA(h, ensure(h->conic, n1 * 16, s));
+    GUT_CUDA(h, ensure(h->extent, n1 * 8, s));
+    GUT_CUDA(h, ensure(h->depth, n1 * 4, s));
+    GUT_CUDA(h, ensure(h->features, n1 * 16, s));
+    GUT_CUDA(h, ensure(h->tile_hist, (size_t)T * 4, s));
+    GUT_CUDA(h, ensure(h->tile_start, ((size_t)T + 1) * 4, s));
+    GUT_CUDA(h, ensure(h->tile_cursor, (size_t)T * 4, s));
+    GUT_CUDA(h, ensure(h->stats, 16, s));
+
+    GutProjBuffers pb;
+    pb.tiles_count = (uint32_t*)h->tiles_count.p; pb.proj_pos = (float2*)h->proj_pos.p; pb.conic_opacity = (float4*)h->conic.p;
+    pb.extent = (float2*)h->extent.p; pb.depth = (float*)h->depth.p; pb.features = (float4*)h->features.p;
+
+    {
+        StageTimer t(h, ST_PROJECT, s);
+        GUT_CUDA(h, cudaMemsetAsync(h->tile_hist.p, 0, (size_t)T * 4, s));
+        GUT_CUDA(h, gut_launch_project(h->cfg, *camera, fr, N, sph_degree, d_density, d_radiance, pb, d_visibility, (uint32_t*)h->tile_hist.p, s));
+        h->launches += N ? 1 : 0;
+    }
+    {
+        StageTimer t(h, ST_SCAN, s);
+        GUT_CUDA(h, gut_launch_tile_scan(T, (const uint32_t*)h->tile_hist.p, (uint32_t*)h->tile_start.p, (uint32_t*)h->tile_cursor.p,
+                                         (uint32_t*)h->stats.p, s));
+        h->launches += 1;
+        // the one device->host dependency of the frame: M sizes the per-intersection buffers (reference: gutRenderer.cu:313-321)
+        GUT_CUDA(h, cudaMemcpyAsync(h->pinned_stats, h->stats.p, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    }
+    GUT_CUDA(h, cudaStreamSynchronize(s));
+    const uint64_t M = h->pinned_stats[0];
+    const uint32_t max_list = h->pinned_stats[1];
+
+    h->fwd_stream = s; h->fwd_N = N; h->fwd_W = W; h->fwd_H = H; h->fwd_M = M; h->fwd_max_list = max_list; h->fwd_frame = fr;
+
+    if (M == 0) {
+        // nothing intersects the image: outputs keep their initial values (reference early return, gutRenderer.cu:323-325)
+        GUT_CUDA(h, gut_launch_fill_outputs(W * H, d_rgba, d_dist, d_hits, s));
+        h->launches += 1;
+    } else {
+        GUT_CUDA(h, ensure(h->entries, M * 8, s, 1.25f));
+        GUT_CUDA(h, ensure(h->sorted_idx, M * 4, s, 1.25f));
+        GUT_CUDA(h, ensure(h->records, M * sizeof(GutRecord), s, 1.25f));
+        GUT_CUDA(h, ensure(h->quats, M * 16, s, 1.25f));
+        if (max_list > 4096) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
+        {
+            StageTimer t(h, ST_EMIT, s);
+            GUT_CUDA(h, gut_launch_emit(h->cfg, fr, N, pb, (const uint32_t*)h->tile_start.p, (uint32_t*)h->tile_cursor.p, (uint2*)h->entries.p, s));
+            h->launches += 1;
+        }
+        {
+            StageTimer t(h, ST_SORT, s);
+            GUT_CUDA(h, gut_launch_tile_sort(fr, N, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p, d_density,
+                                             (const float4*)h->features.p, (uint32_t*)h->sorted_idx.p, (GutRecord*)h->records.p,
+                                             (float4*)h->quats.p, s));
+            h->launches += 1;
+        }
+        {
+            StageTimer t(h, ST_RENDER, s);
+            GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p, d_ray_ori, d_ray_dir,
+                                          d_rgba, d_dist, d_hits, s));
+            h->launches += 1;
+        }
+    }
+    h->fwd_valid = true;
+    if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
+
+    if (so) {
+        so->num_intersections = M;
+        if (so->d_tiles_count) GUT_CUDA(h, cudaMemcpyAsync(so->d_tiles_count, pb.tiles_count, (size_t)N * 4, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_position) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_position, pb.proj_pos, (size_t)N * 8, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_conic_opacity) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_conic_opacity, pb.conic_opacity, (size_t)N * 16, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_extent) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_extent, pb.extent, (size_t)N * 8, cudaMemcpyDeviceToDevice, s));
+        if (so->d_global_depth) GUT_CUDA(h, cudaMemcpyAsync(so->d_global_depth, pb.depth, (size_t)N * 4, cudaMemcpyDeviceToDevice, s));
+        if (so->d_features) { GUT_CUDA(h, gut_launch_copy_features3(N, pb.features, (float*)so->d_features, s)); h->launches += N ? 1 : 0; }
+        if (so->d_sorted_keys || so->d_sorted_particle_idx || so->d_tile_ranges) {
+            if ((so->d_sorted_keys || so->d_sorted_particle_idx) && M > so->capacity_intersections)
+                return fail(h, GUT_ERR_BAD_INPUT, "stage outputs hold %llu intersections, frame produced %llu",
+                            (unsigned long long)so->capacity_intersections, (unsigned long long)M);
+            if (M > 0) {
+                if (so->d_sorted_particle_idx) GUT_CUDA(h, cudaMemcpyAsync(so->d_sorted_particle_idx, h->sorted_idx.p, M * 4, cudaMemcpyDeviceToDevice, s));
+                GUT_CUDA(h, gut_launch_export_keys(fr, (const uint32_t*)h->tile_start.p, (const uint32_t*)h->sorted_idx.p, pb.depth,
+                                                   (uint64_t*)so->d_sorted_keys, (uint32_t*)so->d_tile_ranges, s));
+                h->launches += 1;
+            } else if (so->d_tile_ranges) {
+                GUT_CUDA(h, cudaMemsetAsync(so->d_tile_ranges, 0, (size_t)T * 8, s));
+            }
+        }
+    }
+    return GUT_OK;
+}
+
+int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                 const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
+                 const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad, float* d_radiance_grad,
+                 int32_t accumulate) {
+    int rc = check_common(h, camera, N, sph_degree, W, H);
+    if (rc != GUT_OK) return rc;
+    (void)d_radiance;
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!h->fwd_valid || h->fwd_stream != s)
+        return fail(h, GUT_ERR_NO_FORWARD, "cannot render backward: no forward context on this stream (reference: gutRenderer.cu:413-417)");
+    if (h->fwd_N != N || h->fwd_W != W || h->fwd_H != H) return fail(h, GUT_ERR_NO_FORWARD, "backward shapes differ from the preceding forward");
+    if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_rgba_grad || !d_dist || !d_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null ray/gradient pointer");
+    if (N > 0 && (!d_density || !d_density_grad || !d_radiance_grad)) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    if (N == 0) return GUT_OK;
+    DeviceGuard guard(h->device);
+    if (h->cfg.enable_kernel_timings) start_timer(h->timers, 1, s);
+    const GutFrame& fr = h->fwd_frame;
+
+    GUT_CUDA(h, ensure(h->feature_grad, (size_t)N * 16, s));
+    GUT_CUDA(h, cudaMemsetAsync(h->feature_grad.p, 0, (size_t)N * 16, s));
+    if (!accumulate) GUT_CUDA(h, cudaMemsetAsync(d_density_grad, 0, (size_t)N * 48, s));
+    if (h->fwd_M > 0) {
+        StageTimer t(h, ST_BWD_RENDER, s);
+        GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p,
+                                               (const float4*)h->quats.p, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
+                                               d_density_grad, (float4*)h->feature_grad.p, s));
+        h->launches += 1;
+    }
+    {
+        StageTimer t(h, ST_BWD_PROJECT, s);
+        GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
+                                                (const float4*)h->features.p, (const float4*)h->feature_grad.p, d_radiance_grad, accumulate, s));
+        h->launches += 1;
+    }
+    if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
+    return GUT_OK;
+}
+
+int gut_forward_host(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                     const float* d_radiance, uint32_t W, uint32_t H, const float* h_ray_ori, const float* h_ray_dir, float* h_rgba,
+                     float* h_dist, float* h_hits, float* d_visibility) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!h_ray_ori || !h_ray_dir || !h_rgba || !h_dist || !h_hits) return fail(h, GUT_ERR_BAD_INPUT, "null host pointer");
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    const size_t P = (size_t)W * H;
+    GUT_CUDA(h, ensure(h->h_ray_ori, P * 12, s)); GUT_CUDA(h, ensure(h->h_ray_dir, P * 12, s));
+    GUT_CUDA(h, ensure(h->h_rgba, P * 16, s)); GUT_CUDA(h, ensure(h->h_dist, P * 4, s)); GUT_CUDA(h, ensure(h->h_hits, P * 4, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h->h_ray_ori.p, h_ray_ori, P * 12, cudaMemcpyHostToDevice, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h->h_ray_dir.p, h_ray_dir, P * 12, cudaMemcpyHostToDevice, s));
+    int rc = gut_forward(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, (const float*)h->h_ray_ori.p,
+                         (const float*)h->h_ray_dir.p, (float*)h->h_rgba.p, (float*)h->h_dist.p, (float*)h->h_hits.p, d_visibility, nullptr);
+    if (rc != GUT_OK) return rc;
+    GUT_CUDA(h, cudaMemcpyAsync(h_rgba, h->h_rgba.p, P * 16, cudaMemcpyDeviceToHost, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h_dist, h->h_dist.p, P * 4, cudaMemcpyDeviceToHost, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h_hits, h->h_hits.p, P * 4, cudaMemcpyDeviceToHost, s));
+    return GUT_OK;
+}
+
+int gut_backward_host(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                      const float* d_radiance, uint32_t W, uint32_t H, const float* h_rgba_grad, const float* h_dist_grad,
+                      float* d_density_grad, float* d_radiance_grad, int32_t accumulate) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!h_rgba_grad || !h_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null host pointer");
+    if (!h->fwd_valid || !h->h_rgba.p || h->fwd_W != W || h->fwd_H != H)
+        return fail(h, GUT_ERR_NO_FORWARD, "gut_backward_host needs a preceding gut_forward_host of the same view");
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    const size_t P = (size_t)W * H;
+    GUT_CUDA(h, ensure(h->h_rgba_grad, P * 16, s)); GUT_CUDA(h, ensure(h->h_dist_grad, P * 4, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h->h_rgba_grad.p, h_rgba_grad, P * 16, cudaMemcpyHostToDevice, s));
+    GUT_CUDA(h, cudaMemcpyAsync(h->h_dist_grad.p, h_dist_grad, P * 4, cudaMemcpyHostToDevice, s));
+    return gut_backward(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, (const float*)h->h_ray_ori.p,
+                        (const float*)h->h_ray_dir.p, (const float*)h->h_rgba.p, (const float*)h->h_rgba_grad.p, (const float*)h->h_dist.p,
+                        (const float*)h->h_dist_grad.p, d_density_grad, d_radiance_grad, accumulate);
+}
+
+static void collect(std::deque<EventPair>& q, float* sums, int* counts, int ntags) {
+    for (auto& t : q) {
+        float ms = 0.0f;
+        if (cudaEventSynchronize(t.b) == cudaSuccess && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess && t.tag < ntags) {
+            sums[t.tag] += ms; counts[t.tag] += 1;
+        }
+        cudaEventDestroy(t.a); cudaEventDestroy(t.b);
+    }
+    q.clear();
+}
+
+int gut_timings(GutHandle* h, float* fwd_ms, float* bwd_ms) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    DeviceGuard guard(h->device);
+    float sums[2] = {0, 0}; int counts[2] = {0, 0};
+    collect(h->timers, sums, counts, 2);
+    if (counts[0]) h->last_fwd_ms = sums[0] / counts[0];
+    if (counts[1]) h->last_bwd_ms = sums[1] / counts[1];
+    if (fwd_ms) *fwd_ms = h->last_fwd_ms;
+    if (bwd_ms) *bwd_ms = h->last_bwd_ms;
+    return GUT_OK;
+}
+
+int gut_num_stages(void) { return ST_COUNT; }
+const char* gut_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+
+int gut_stage_timings(GutHandle* h, float* ms_out) {
+    if (!h || !ms_out) return GUT_ERR_BAD_INPUT;
+    DeviceGuard guard(h->device);
+    float sums[ST_COUNT]; int counts[ST_COUNT];
+    for (int i = 0; i < ST_COUNT; ++i) { sums[i] = 0; counts[i] = 0; }
+    collect(h->stage_timers, sums, counts, ST_COUNT);
+    for (int i = 0; i < ST_COUNT; ++i) {
+        if (counts[i]) h->last_stage_ms[i] = sums[i] / counts[i];
+        ms_out[i] = h->last_stage_ms[i];
+    }
+    return GUT_OK;
+}
+
+int gut_frame_stats(GutHandle* h, GutFrameStats* out) {
+    if (!h || !out) return GUT_ERR_BAD_INPUT;
+    out->num_intersections = h->fwd_M;
+    out->num_tiles = h->fwd_frame.num_tiles;
+    out->max_tile_list_length = h->fwd_max_list;
+    out->kernel_launches = h->launches;
+    return GUT_OK;
+}
+
+}  // extern "C"

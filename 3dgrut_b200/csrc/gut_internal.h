@@ -1,0 +1,80 @@
+// gut_internal.h -- structures shared by the translation units of libgut_b200 (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gut_b200.h"
+#include "gut_math.cuh"
+
+// Per-frame constants computed on the host once per call
+// (reference: GUTRenderer::renderForward, src/gutRenderer.cu:259-267,282-285,385).
+struct GutFrame {
+    uint32_t width, height;
+    uint32_t grid_x, grid_y;    // tiles
+    uint32_t num_tiles;
+    GutMat4x3 view;             // world -> sensor at the mid-shutter pose (depth ordering, z cull)
+    GutMat4x3 c2w;              // sensor -> world at the mid-shutter pose (ray set-up)
+    float3 cam_centre;          // sensor position in world space (SH view direction)
+    float ut_delta;             // sqrt(alpha^2 (3 + kappa)), narrowed from double (setup_3dgut.py:45)
+};
+
+// One sorted (tile, particle) intersection, expanded for the compositing kernels ("record stream").
+// 80 B = 5 x float4, written in sorted order by the tile-sort kernel so a batch is one contiguous
+// cp.async.bulk copy.  ms = diag(1/scale) * R^T : the map from world offsets to the particle's
+// canonical (unit-Gaussian) frame; rows ms0..ms2.
+struct __align__(16) GutRecord {
+    float ms0x, ms0y, ms0z, px;     // row 0 of ms | position.x
+    float ms1x, ms1y, ms1z, py;     // row 1       | position.y
+    float ms2x, ms2y, ms2z, pz;     // row 2       | position.z
+    float sx, sy, sz, density;      // scale       | density
+    float fr, fg, fb;               // max(feature, 0)
+    uint32_t idx;                   // particle index
+};
+static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
+
+// Device buffers of the per-particle projection stage (K1 outputs).
+struct GutProjBuffers {
+    uint32_t* tiles_count;   // [N]
+    float2* proj_pos;        // [N]
+    float4* conic_opacity;   // [N]
+    float2* extent;          // [N]
+    float* depth;            // [N]
+    float4* features;        // [N] xyz = SH radiance + 0.5 (unclamped), w unused
+};
+
+// ---- launchers implemented in the .cu files (all enqueue on `stream`, return cudaGetLastError()) ----
+cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const GutFrame& frame, uint32_t N, int sph_degree,
+                               const float* density12, const float* sph, GutProjBuffers out, float* visibility,
+                               uint32_t* tile_hist, cudaStream_t stream);
+
+cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
+                                        const float* density12, const uint32_t* tiles_count, const float4* features,
+                                        const float4* feature_grad, float* sph_grad, int accumulate, cudaStream_t stream);
+
+// exclusive scan of tile_hist[T] -> tile_start[T+1]; also zeroes tile_cursor[T], writes stats[0]=M, stats[1]=max list
+cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
+                                 uint32_t* stats, cudaStream_t stream);
+
+cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_t N, GutProjBuffers proj,
+                            const uint32_t* tile_start, uint32_t* tile_cursor, uint2* entries, cudaStream_t stream);
+
+// per-tile sort of (depth, idx) + expansion into the record stream; scratch = alt buffer for oversize tiles
+cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32_t* tile_start, uint2* entries, uint2* scratch,
+                                 const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
+                                 float4* quats, cudaStream_t stream);
+
+// debug/parity: rebuild the reference-shaped sorted key array and tile ranges
+cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_start, const uint32_t* sorted_idx, const float* depth,
+                                   uint64_t* sorted_keys, uint32_t* ranges, cudaStream_t stream);
+
+cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
+                              const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
+                              cudaStream_t stream);
+
+cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
+                                       const GutRecord* records, const float4* quats, const float* ray_ori, const float* ray_dir,
+                                       const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
+                                       float* density_grad, float4* feature_grad, cudaStream_t stream);
+
+cudaError_t gut_launch_fill_outputs(uint32_t num_pixels, float* rgba, float* dist, float* hits, cudaStream_t stream);
+cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream);

@@ -1,0 +1,368 @@
+// gut_project.cu -- K1 (per-particle unscented-transform projection + SH colour + tile counting) and
+// K6 (SH backward).  Built with --fmad=false (see gut_math.cuh): integer results of this stage are
+// bit-reproducible against the CPU oracle.
+//
+// reference: GUTProjector::eval / unscentedParticleProjection / computeProjectedExtentConicOpacity
+//            (threedgut_tracer/include/3dgut/kernels/cuda/renderers/gutProjector.cuh:81-322),
+//            projectPoint* (include/3dgut/kernels/cuda/sensors/cameraProjections.cuh:22-185),
+//            radianceFromSpH / radianceFromSpHBwd (include/3dgut/kernels/cuda/models/gaussianParticles.cuh:64-187),
+//            GUTProjector::evalBackward (gutProjector.cuh:390-430).
+#include <float.h>
+
+#include "gut_internal.h"
+
+namespace {
+
+struct Quat { float w, x, y, z; };
+
+GUT_D Quat pose_quat(const float* p) { return Quat{p[6], p[3], p[4], p[5]}; }
+GUT_D float3 pose_t(const float* p) { return f3(p[0], p[1], p[2]); }
+GUT_D float mixf(float a, float b, float c) { return a * (1.0f - c) + b * c; }
+
+// tcnn::slerp semantics (thirdparty/tiny-cuda-nn/include/tiny-cuda-nn/vec.h:1133-1153): shortest arc, lerp when nearly parallel,
+// result NOT renormalised.
+GUT_D Quat slerp(Quat a, Quat b, float t) {
+    float c = (a.w * b.w + a.x * b.x) + (a.y * b.y + a.z * b.z);
+    if (c < 0.0f) { b.w = -b.w; b.x = -b.x; b.y = -b.y; b.z = -b.z; c = -c; }
+    Quat r;
+    if (c > 1.0f - FLT_EPSILON) {
+        const float u = 1.0f - t;
+        r.w = a.w * u + b.w * t; r.x = a.x * u + b.x * t; r.y = a.y * u + b.y * t; r.z = a.z * u + b.z * t;
+    } else {
+        const float ang = acosf(c);
+        const float s0 = sinf((1.0f - t) * ang), s1 = sinf(t * ang), sd = sinf(ang);
+        r.w = (s0 * a.w + s1 * b.w) / sd; r.x = (s0 * a.x + s1 * b.x) / sd;
+        r.y = (s0 * a.y + s1 * b.y) / sd; r.z = (s0 * a.z + s1 * b.z) / sd;
+    }
+    return r;
+}
+
+GUT_D float3 to_sensor(Quat q, float3 t, float3 p) {
+    float3 c0, c1, c2;
+    quat_to_columns(q.w, q.x, q.y, q.z, c0, c1, c2);
+    return rotate_cols(c0, c1, c2, p) + t;
+}
+
+GUT_D bool within_resolution(float rx, float ry, float tol, float2 p) {
+    const float mx = rx * tol, my = ry * tol;
+    return (p.x > -mx) && (p.y > -my) && (p.x < rx + mx) && (p.y < ry + my);
+}
+
+// OpenCV pinhole with rational radial, tangential and thin-prism terms (cameraProjections.cuh:57-103)
+GUT_D bool project_pinhole(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out) {
+    if (pos.z <= 0.0f) { out = make_float2(0.0f, 0.0f); return false; }
+    const float ux = pos.x / pos.z, uy = pos.y / pos.z;
+    const float sx = ux * ux, sy = uy * uy;
+    const float r2 = sx + sy;
+    const float a1 = 2.0f * ux * uy, a2 = r2 + 2.0f * sx, a3 = r2 + 2.0f * sy;
+    const float* k = cam.radial_coeffs; const float* p = cam.tangential_coeffs; const float* s = cam.thin_prism_coeffs;
+    const float num = 1.0f + r2 * (k[0] + r2 * (k[1] + r2 * k[2]));
+    const float den = 1.0f + r2 * (k[3] + r2 * (k[4] + r2 * k[5]));
+    const float icd = num / den;
+    const float dx = p[0] * a1 + p[1] * a2 + r2 * (s[0] + r2 * s[1]);
+    const float dy = p[0] * a3 + p[1] * a1 + r2 * (s[2] + r2 * s[3]);
+    const bool radial_ok = (icd > 0.8f) && (icd < 1.2f);
+    if (radial_ok) {
+        out.x = (icd * ux + dx) * cam.focal_length[0] + cam.principal_point[0];
+        out.y = (icd * uy + dy) * cam.focal_length[1] + cam.principal_point[1];
+    } else {
+        const float f = sqrtf(fw * fw + fh * fh) / sqrtf(r2);
+        out.x = f * ux + cam.principal_point[0];
+        out.y = f * uy + cam.principal_point[1];
+    }
+    return radial_ok && within_resolution(fw, fh, tol, out);
+}
+
+// OpenCV fisheye (equidistant + 4-term polynomial), angle clamped at max_angle (cameraProjections.cuh:105-128)
+GUT_D bool project_fisheye(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out) {
+    const float rho = fmaxf(sqrtf(pos.x * pos.x + pos.y * pos.y), FLT_EPSILON);
+    const float theta = fminf(atan2f(rho, pos.z), cam.max_angle);
+    const float t2 = theta * theta;
+    const float* c = cam.radial_coeffs;
+    float y = c[3];
+    y = t2 * y + c[2];
+    y = t2 * y + c[1];
+    y = t2 * y + c[0];
+    const float delta = (theta * (y * t2 + 1.0f)) / rho;
+    out.x = cam.focal_length[0] * pos.x * delta + cam.principal_point[0];
+    out.y = cam.focal_length[1] * pos.y * delta + cam.principal_point[1];
+    return (theta < cam.max_angle) && within_resolution(fw, fh, tol, out);
+}
+
+GUT_D bool project_point(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out) {
+    if (cam.model == GUT_CAMERA_OPENCV_PINHOLE) return project_pinhole(cam, fw, fh, pos, tol, out);
+    if (cam.model == GUT_CAMERA_OPENCV_FISHEYE) return project_fisheye(cam, fw, fh, pos, tol, out);
+    out = make_float2(0.0f, 0.0f);
+    return false;
+}
+
+GUT_D float shutter_time(const GutCamera& cam, float fw, float fh, float2 p) {
+    switch (cam.shutter) {
+    case GUT_SHUTTER_ROLLING_TOP_TO_BOTTOM: return floorf(p.y) / (fh - 1.0f);
+    case GUT_SHUTTER_ROLLING_LEFT_TO_RIGHT: return floorf(p.x) / (fw - 1.0f);
+    case GUT_SHUTTER_ROLLING_BOTTOM_TO_TOP: return (fh - ceilf(p.y)) / (fh - 1.0f);
+    case GUT_SHUTTER_ROLLING_RIGHT_TO_LEFT: return (fw - ceilf(p.x)) / (fw - 1.0f);
+    default: return 0.5f;
+    }
+}
+
+// Project with the start pose; under a rolling shutter refine the capture time of the point by fixed-point
+// iteration on its own image row/column (cameraProjections.cuh:146-185).
+GUT_D bool project_with_shutter(const GutCamera& cam, float fw, float fh, int n_iter, float3 pos, float tol, float2& out) {
+    const Quat q0 = pose_quat(cam.start_pose);
+    const float3 t0 = pose_t(cam.start_pose);
+    bool ok = project_point(cam, fw, fh, to_sensor(q0, t0, pos), tol, out);
+    if (cam.shutter == GUT_SHUTTER_GLOBAL) return ok;
+    const Quat q1 = pose_quat(cam.end_pose);
+    const float3 t1 = pose_t(cam.end_pose);
+    if (!ok) {
+        ok = project_point(cam, fw, fh, to_sensor(q1, t1, pos), tol, out);
+        if (!ok) return false;
+    }
+    for (int i = 0; i < n_iter; ++i) {
+        const float a = shutter_time(cam, fw, fh, out);
+        const float3 t = f3(mixf(t0.x, t1.x, a), mixf(t0.y, t1.y, a), mixf(t0.z, t1.z, a));
+        ok = project_point(cam, fw, fh, to_sensor(slerp(q0, q1, a), t, pos), tol, out);
+    }
+    return ok;
+}
+
+GUT_D float view_depth(const GutMat4x3& v, float3 p) { return p.x * v.c[0].z + p.y * v.c[1].z + p.z * v.c[2].z + v.c[3].z; }
+
+// Dilated conic, mip-splatting opacity, culling bound and screen extent (gutProjector.cuh:81-116).
+GUT_D bool conic_extent(const GutConfig& cfg, float3 cov, float opacity, float2& extent, float4& co, float& max_power) {
+    const float dil = 0.3f;
+    const float dx = cov.x + dil, dy = cov.y, dz = cov.z + dil;
+    const float ddet = dx * dz - dy * dy;
+    if (ddet == 0.0f) return false;
+    co.x = dz / ddet; co.y = -dy / ddet; co.z = dx / ddet;
+    const float det = cov.x * cov.z - cov.y * cov.y;
+    co.w = opacity * sqrtf(fmaxf(0.000025f, det / ddet));
+    if (co.w < cfg.min_alpha) return false;
+    max_power = gut_logf(co.w / cfg.min_alpha);
+    const float ef = cfg.tight_opacity_bounding ? fminf(3.33f, sqrtf(2.0f * max_power)) : 3.33f;
+    const float mid = 0.5f * (dx + dz);
+    const float lambda = mid + sqrtf(fmaxf(0.01f, mid * mid - ddet));
+    const float radius = ef * sqrtf(lambda);
+    if (cfg.rect_bounding) {
+        extent.x = fminf(ef * sqrtf(dx), radius);
+        extent.y = fminf(ef * sqrtf(dz), radius);
+    } else {
+        extent.x = radius; extent.y = radius;
+    }
+    return radius > 0.0f;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K1.  One thread per particle.  The 48-byte parameter record is fetched as three 128-bit loads.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCamera cam, GutFrame fr, uint32_t N, int sph_degree,
+                                                          const float4* __restrict__ density12, const float* __restrict__ sph,
+                                                          GutProjBuffers out, float* __restrict__ visibility,
+                                                          uint32_t* __restrict__ tile_hist) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos.xyz, density
+    const float4 r1 = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
+    const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale.xyz, pad
+    const float3 pos = f3(r0.x, r0.y, r0.z);
+    const float opacity = r0.w;
+    const float fw = (float)fr.width, fh = (float)fr.height;
+
+    // UT weights (threedgut.cuh:62-71, gutProjector.cuh:150,163,201)
+    const float D = 3.0f;
+    const float lambda = cfg.ut_alpha * cfg.ut_alpha * (D + cfg.ut_kappa) - D;
+    const float w0_mean = lambda / (D + lambda);
+    const float wi = 1.0f / (2.0f * (D + lambda));
+    const float w0_cov = lambda / (D + lambda) + (1.0f - cfg.ut_alpha * cfg.ut_alpha + cfg.ut_beta);
+    const float tol = cfg.ut_in_image_margin_factor;
+    const int n_iter = cfg.n_rolling_shutter_iterations;
+
+    bool valid_proj = false;
+    float2 centre = make_float2(0.0f, 0.0f);
+    float3 cov = f3(0.0f, 0.0f, 0.0f);
+    float3 sensor_ray = f3(0.0f, 0.0f, 0.0f);
+    if (opacity >= cfg.min_alpha && !(view_depth(fr.view, pos) < 0.2f)) {
+        float3 c[3];
+        quat_to_columns(r1.x, r1.y, r1.z, r1.w, c[0], c[1], c[2]);
+        const float sc[3] = {r2.x, r2.y, r2.z};
+        sensor_ray = pos - fr.cam_centre;
+        float2 sp[7];
+        int nvalid = project_with_shutter(cam, fw, fh, n_iter, pos, tol, sp[0]) ? 1 : 0;
+        centre.x = sp[0].x * w0_mean; centre.y = sp[0].y * w0_mean;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float3 d = (fr.ut_delta * sc[a]) * c[a];
+            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos + d, tol, sp[a + 1]) ? 1 : 0;
+            centre.x += wi * sp[a + 1].x; centre.y += wi * sp[a + 1].y;
+            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos - d, tol, sp[a + 4]) ? 1 : 0;
+            centre.x += wi * sp[a + 4].x; centre.y += wi * sp[a + 4].y;
+        }
+        const bool reject = cfg.ut_require_all_sigma_points_valid ? (nvalid < 7) : (nvalid == 0);
+        if (!reject) {
+            float cx = sp[0].x - centre.x, cy = sp[0].y - centre.y;
+            cov = f3(w0_cov * (cx * cx), w0_cov * (cx * cy), w0_cov * (cy * cy));
+#pragma unroll
+            for (int k = 1; k < 7; ++k) {
+                cx = sp[k].x - centre.x; cy = sp[k].y - centre.y;
+                cov.x += wi * (cx * cx); cov.y += wi * (cx * cy); cov.z += wi * (cy * cy);
+            }
+            valid_proj = true;
+        }
+    }
+
+    float2 extent = make_float2(0.0f, 0.0f);
+    float4 co = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float max_power = 0.0f;
+    const bool valid_conic = valid_proj && conic_extent(cfg, cov, opacity, extent, co, max_power);
+    // reference stores int 1 into float storage (gutProjector.cuh:275); 1.0f has the same truthiness and survives FTZ
+    visibility[i] = valid_conic ? 1.0f : 0.0f;
+
+    uint32_t ntiles = 0;
+    if (valid_conic) {
+        const GutTileBox bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, extent);
+        for (uint32_t y = bb.y0; y < bb.y1; ++y)
+            for (uint32_t x = bb.x0; x < bb.x1; ++x) {
+                if (!cfg.tile_based_culling || gut_tile_min_power((float)x, (float)y, co, centre) < max_power) {
+                    ntiles++;
+                    atomicAdd(&tile_hist[y * fr.grid_x + x], 1u);  // RED: per-tile list length for the bucket scan
+                }
+            }
+    }
+    out.tiles_count[i] = ntiles;
+    if (ntiles == 0) {
+        out.proj_pos[i] = make_float2(0.0f, 0.0f);
+        out.conic_opacity[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        out.extent[i] = make_float2(0.0f, 0.0f);
+        out.depth[i] = 0.0f;
+        out.features[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        return;
+    }
+
+    // SH colour seen from the sensor centre, +0.5, unclamped (gutProjector.cuh:304-310, gaussianParticles.cuh:64-96)
+    const float dist = sqrtf(dot(sensor_ray, sensor_ray));
+    const float3 dir = f3(sensor_ray.x / dist, sensor_ray.y / dist, sensor_ray.z / dist);
+    float b[16];
+    gut_sh_basis(sph_degree, dir, b);
+    const int ncoef_all = (cfg.sph_max_degree + 1) * (cfg.sph_max_degree + 1);
+    const int nact = (sph_degree + 1) * (sph_degree + 1);
+    const float* cf = sph + (size_t)i * ncoef_all * 3;
+    float3 rad;
+    if (ncoef_all == 16) {  // 192 B per particle: twelve 128-bit loads
+        const float4* cf4 = reinterpret_cast<const float4*>(cf);
+        float v[48];
+#pragma unroll
+        for (int q = 0; q < 12; ++q) {
+            const float4 t = (q * 4 < nact * 3) ? __ldg(cf4 + q) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+        }
+        rad = f3(b[0] * v[0], b[0] * v[1], b[0] * v[2]);
+#pragma unroll
+        for (int k = 1; k < 16; ++k)
+            if (k < nact) { rad.x = rad.x + b[k] * v[3 * k]; rad.y = rad.y + b[k] * v[3 * k + 1]; rad.z = rad.z + b[k] * v[3 * k + 2]; }
+    } else {
+        rad = f3(b[0] * cf[0], b[0] * cf[1], b[0] * cf[2]);
+        for (int k = 1; k < nact; ++k) { rad.x = rad.x + b[k] * cf[3 * k]; rad.y = rad.y + b[k] * cf[3 * k + 1]; rad.z = rad.z + b[k] * cf[3 * k + 2]; }
+    }
+    out.features[i] = make_float4(rad.x + 0.5f, rad.y + 0.5f, rad.z + 0.5f, 0.0f);
+    out.proj_pos[i] = centre;
+    out.conic_opacity[i] = co;
+    out.extent[i] = extent;
+    out.depth[i] = cfg.global_z_order ? view_depth(fr.view, pos) : dist;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K6.  dL/dSH = basis(dir) x (dL/dfeature masked by feature > 0).  One thread per particle; particles the
+// frame did not touch get zeros (accumulate == 0) so no separate memset pass over [N,48] is needed.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gut_project_backward_kernel(GutConfig cfg, GutFrame fr, uint32_t N, int sph_degree,
+                                                                   const float4* __restrict__ density12,
+                                                                   const uint32_t* __restrict__ tiles_count,
+                                                                   const float4* __restrict__ features,
+                                                                   const float4* __restrict__ feature_grad,
+                                                                   float* __restrict__ sph_grad, int accumulate) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int ncoef_all = (cfg.sph_max_degree + 1) * (cfg.sph_max_degree + 1);
+    const int nact = (sph_degree + 1) * (sph_degree + 1);
+    float* out = sph_grad + (size_t)i * ncoef_all * 3;
+    const bool touched = tiles_count[i] != 0;
+    if (!touched) {
+        if (!accumulate) {
+            if (ncoef_all == 16) {
+                float4* o4 = reinterpret_cast<float4*>(out);
+#pragma unroll
+                for (int q = 0; q < 12; ++q) o4[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            } else {
+                for (int k = 0; k < ncoef_all * 3; ++k) out[k] = 0.0f;
+            }
+        }
+        return;
+    }
+    const float4 r0 = __ldg(density12 + 3 * (size_t)i);
+    const float3 v = f3(r0.x, r0.y, r0.z) - fr.cam_centre;
+    const float len = sqrtf(dot(v, v));
+    const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(v.x / len, v.y / len, v.z / len);
+    float b[16];
+    gut_sh_basis(sph_degree, dir, b);
+    const float4 ft = features[i];
+    float4 g = feature_grad[i];
+    g.x *= (ft.x > 0.0f ? 1.0f : 0.0f); g.y *= (ft.y > 0.0f ? 1.0f : 0.0f); g.z *= (ft.z > 0.0f ? 1.0f : 0.0f);
+    if (ncoef_all == 16) {
+        float vals[48];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const float bk = (k < nact) ? b[k] : 0.0f;
+            vals[3 * k] = bk * g.x; vals[3 * k + 1] = bk * g.y; vals[3 * k + 2] = bk * g.z;
+        }
+        float4* o4 = reinterpret_cast<float4*>(out);
+#pragma unroll
+        for (int q = 0; q < 12; ++q) {
+            float4 t = make_float4(vals[4 * q], vals[4 * q + 1], vals[4 * q + 2], vals[4 * q + 3]);
+            if (accumulate) { const float4 o = o4[q]; t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w; }
+            o4[q] = t;
+        }
+    } else {
+        for (int k = 0; k < ncoef_all; ++k) {
+            const float bk = (k < nact) ? b[k] : 0.0f;
+            for (int ch = 0; ch < 3; ++ch) {
+                const float gv = bk * (ch == 0 ? g.x : (ch == 1 ? g.y : g.z));
+                out[3 * k + ch] = accumulate ? out[3 * k + ch] + gv : gv;
+            }
+        }
+    }
+}
+
+__global__ void gut_copy_features3_kernel(uint32_t N, const float4* __restrict__ f4, float* __restrict__ f3out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float4 v = f4[i];
+    f3out[3 * (size_t)i] = v.x; f3out[3 * (size_t)i + 1] = v.y; f3out[3 * (size_t)i + 2] = v.z;
+}
+
+}  // namespace
+
+cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const GutFrame& frame, uint32_t N, int sph_degree,
+                               const float* density12, const float* sph, GutProjBuffers out, float* visibility,
+                               uint32_t* tile_hist, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_project_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, cam, frame, N, sph_degree,
+                                                             reinterpret_cast<const float4*>(density12), sph, out, visibility, tile_hist);
+    return cudaGetLastError();
+}
+
+cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
+                                        const float* density12, const uint32_t* tiles_count, const float4* features,
+                                        const float4* feature_grad, float* sph_grad, int accumulate, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_project_backward_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, frame, N, sph_degree,
+                                                                      reinterpret_cast<const float4*>(density12), tiles_count,
+                                                                      features, feature_grad, sph_grad, accumulate);
+    return cudaGetLastError();
+}
+
+cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_copy_features3_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, features4, features3);
+    return cudaGetLastError();
+}

@@ -1,0 +1,294 @@
+"""ctypes binding of libgut_b200.so and the ``SplatRaster`` object the Tracer drives.
+
+Mirrors the reference's pybind11 class ``lib3dgut_cc.SplatRaster``
+(threedgut_tracer/bindings.cpp:79-86, threedgut_tracer/src/splatRaster.cpp): same
+method names (``trace``, ``trace_bwd``, ``collect_times``), same argument meaning,
+torch tensors in and out -- but underneath it only passes raw device pointers and
+the current CUDA stream through the C ABI of ``include/gut_b200.h``.
+
+There is no CPU fallback: if the library is missing or was not built for the
+device, loading raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import torch
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgut_b200.so")
+_lib = None
+
+
+class GutError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"libgut_b200: {abi.GutStatus(code).name}: {message}")
+        self.code = code
+
+
+def build_library(force=False):
+    """Compile the CUDA library in-tree for sm_100a (``make -C csrc``)."""
+    src_dir = os.path.join(_HERE, "csrc")
+    args = ["make", "-C", src_dir, "-s"]
+    if force:
+        subprocess.check_call(["make", "-C", src_dir, "-s", "clean"])
+    subprocess.check_call(args)
+    return LIB_PATH
+
+
+def load_library():
+    """dlopen the C-ABI library and declare its prototypes.  Raises if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C 3dgrut_b200/csrc`).  There is no CPU fallback for the 3DGUT rasteriser."
+        )
+    lib = C.CDLL(LIB_PATH)
+    vp, u32, i32, fp = C.c_void_p, C.c_uint32, C.c_int32, C.c_void_p
+    lib.gut_abi_version.restype = C.c_int
+    lib.gut_default_config.argtypes = [C.POINTER(abi.GutConfig)]
+    lib.gut_default_config.restype = None
+    lib.gut_create.argtypes = [C.POINTER(abi.GutConfig), C.c_int, C.POINTER(vp)]
+    lib.gut_create.restype = C.c_int
+    lib.gut_destroy.argtypes = [vp]
+    lib.gut_destroy.restype = None
+    lib.gut_forward.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp,
+                                C.POINTER(abi.GutStageOutputs)]
+    lib.gut_forward.restype = C.c_int
+    lib.gut_backward.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, fp, i32]
+    lib.gut_backward.restype = C.c_int
+    lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
+    lib.gut_forward_host.restype = C.c_int
+    lib.gut_backward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, i32]
+    lib.gut_backward_host.restype = C.c_int
+    lib.gut_timings.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.gut_timings.restype = C.c_int
+    lib.gut_num_stages.restype = C.c_int
+    lib.gut_stage_name.argtypes = [C.c_int]
+    lib.gut_stage_name.restype = C.c_char_p
+    lib.gut_stage_timings.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.gut_stage_timings.restype = C.c_int
+    lib.gut_frame_stats.argtypes = [vp, C.POINTER(abi.GutFrameStats)]
+    lib.gut_frame_stats.restype = C.c_int
+    lib.gut_last_error.argtypes = [vp]
+    lib.gut_last_error.restype = C.c_char_p
+    for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats"):
+        getattr(lib, name).restype = C.c_size_t
+    if lib.gut_abi_version() != abi.GUT_ABI_VERSION:
+        raise ImportError(f"libgut_b200 ABI {lib.gut_abi_version()} != python mirror {abi.GUT_ABI_VERSION}")
+    if lib.gut_sizeof_config() != C.sizeof(abi.GutConfig) or lib.gut_sizeof_camera() != C.sizeof(abi.GutCamera):
+        raise ImportError("libgut_b200 struct layout differs from 3dgrut_b200/abi.py")
+    _lib = lib
+    return lib
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _check_cuda_f32(name, t, device):
+    if not t.is_cuda or t.dtype != torch.float32:
+        raise GutError(abi.GutStatus.BAD_INPUT, f"{name} must be a float32 CUDA tensor (got {t.dtype} on {t.device})")
+    if t.device != device:
+        raise GutError(abi.GutStatus.BAD_INPUT, f"{name} is on {t.device}, expected {device}")
+    return t.contiguous()
+
+
+class SplatRaster:
+    """One rasteriser instance = one native handle + its grow-only device workspace.
+
+    reference: class SplatRaster (include/3dgut/splatRaster.h:27-90).
+    """
+
+    def __init__(self, config: abi.GutConfig, device=None):
+        self.lib = load_library()
+        if not torch.cuda.is_available():
+            raise RuntimeError("3dgrut_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        major, _minor = torch.cuda.get_device_capability(self.device)
+        if major != 10:
+            raise RuntimeError(f"libgut_b200 is built for sm_100a only; device capability is {major}.{_minor}")
+        self.config = config
+        h = C.c_void_p()
+        rc = self.lib.gut_create(C.byref(config), self.device.index, C.byref(h))
+        if rc != 0:
+            raise GutError(rc, "gut_create failed (unsupported configuration?)")
+        self._h = h
+        self.n_coeffs = (config.sph_max_degree + 1) ** 2
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                self.lib.gut_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    def _raise(self, rc):
+        raise GutError(rc, self.lib.gut_last_error(self._h).decode())
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---- reference-shaped entry points ------------------------------------------------------------------
+    def trace(self, frame_number, num_active_features, particle_density, particle_radiance, ray_origin, ray_direction,
+              ray_timestamp, sensor: abi.GutCamera, start_timestamp=0, end_timestamp=1, start_pose=None, end_pose=None,
+              stage_outputs=False):
+        """reference: SplatRaster::trace (splatRaster.cpp:173-244).
+
+        ``sensor`` already carries the two poses (set by camera.camera_from_batch); ``start_pose``/``end_pose``
+        override them when given, for callers that follow the reference argument list literally.
+        ``ray_timestamp`` is accepted and ignored, like the reference's kernels ignore it.
+        Returns (rayRadianceDensity [H,W,4], rayHitDistance [H,W,1], rayHitCount [H,W,1], particleVisibility [N,1])
+        and, when ``stage_outputs`` is set, a dict of the intermediate stage tensors as a fifth element.
+        """
+        del frame_number, ray_timestamp
+        dev = self.device
+        if start_pose is not None:
+            abi.set_poses(sensor, [float(v) for v in start_pose], [float(v) for v in (end_pose if end_pose is not None else start_pose)],
+                          (start_timestamp, end_timestamp))
+        dens = _check_cuda_f32("particle_density", particle_density, dev)
+        rad = _check_cuda_f32("particle_radiance", particle_radiance, dev)
+        ro = _check_cuda_f32("ray_origin", ray_origin, dev)
+        rd = _check_cuda_f32("ray_direction", ray_direction, dev)
+        if ro.dim() != 4 or ro.shape[0] != 1 or ro.shape[3] != 3 or rd.shape != ro.shape:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"rays must be [1,H,W,3], got {tuple(ro.shape)} / {tuple(rd.shape)}")
+        n = dens.shape[0]
+        if dens.dim() != 2 or dens.shape[1] != 12:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"particle_density must be [N,12], got {tuple(dens.shape)}")
+        if rad.shape[0] != n or rad.numel() != n * self.n_coeffs * 3:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"particle_radiance must be [N,{self.n_coeffs * 3}], got {tuple(rad.shape)}")
+        height, width = ro.shape[1], ro.shape[2]
+        # the library initialises all four outputs itself (no torch.zeros fill kernels)
+        rgba = torch.empty((height, width, 4), dtype=torch.float32, device=dev)
+        dist = torch.empty((height, width, 1), dtype=torch.float32, device=dev)
+        hits = torch.empty((height, width, 1), dtype=torch.float32, device=dev)
+        vis = torch.empty((n, 1), dtype=torch.float32, device=dev)
+        so = None
+        stage = None
+        if stage_outputs:
+            so, stage = self._alloc_stage_outputs(n, width, height)
+        rc = self.lib.gut_forward(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
+                                  width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(dist), _ptr(hits), _ptr(vis),
+                                  C.byref(so) if so is not None else None)
+        if rc != 0 and stage_outputs and "stage outputs hold" in self.lib.gut_last_error(self._h).decode():
+            # grow the debug buffers to the frame's M and run again
+            so, stage = self._alloc_stage_outputs(n, width, height, capacity=int(so.num_intersections))
+            rc = self.lib.gut_forward(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
+                                      width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(dist), _ptr(hits), _ptr(vis), C.byref(so))
+        if rc != 0:
+            self._raise(rc)
+        if stage_outputs:
+            m = int(so.num_intersections)
+            stage["num_intersections"] = m
+            stage["sorted_keys"] = stage["sorted_keys"][:m]
+            stage["sorted_particle_idx"] = stage["sorted_particle_idx"][:m]
+            return rgba, dist, hits, vis, stage
+        return rgba, dist, hits, vis
+
+    def _alloc_stage_outputs(self, n, width, height, capacity=None):
+        dev = self.device
+        tiles = ((width + 15) // 16) * ((height + 15) // 16)
+        cap = capacity if capacity is not None else max(1, 16 * n)
+        st = {
+            "tiles_count": torch.zeros(n, dtype=torch.int32, device=dev),
+            "proj_position": torch.zeros((n, 2), dtype=torch.float32, device=dev),
+            "proj_conic_opacity": torch.zeros((n, 4), dtype=torch.float32, device=dev),
+            "proj_extent": torch.zeros((n, 2), dtype=torch.float32, device=dev),
+            "global_depth": torch.zeros(n, dtype=torch.float32, device=dev),
+            "features": torch.zeros((n, 3), dtype=torch.float32, device=dev),
+            "sorted_keys": torch.zeros(cap, dtype=torch.int64, device=dev),
+            "sorted_particle_idx": torch.zeros(cap, dtype=torch.int32, device=dev),
+            "tile_ranges": torch.zeros((tiles, 2), dtype=torch.int32, device=dev),
+        }
+        so = abi.GutStageOutputs(
+            d_tiles_count=st["tiles_count"].data_ptr(), d_proj_position=st["proj_position"].data_ptr(),
+            d_proj_conic_opacity=st["proj_conic_opacity"].data_ptr(), d_proj_extent=st["proj_extent"].data_ptr(),
+            d_global_depth=st["global_depth"].data_ptr(), d_features=st["features"].data_ptr(),
+            d_sorted_keys=st["sorted_keys"].data_ptr(), d_sorted_particle_idx=st["sorted_particle_idx"].data_ptr(),
+            d_tile_ranges=st["tile_ranges"].data_ptr(), capacity_intersections=cap, num_intersections=0,
+        )
+        return so, st
+
+    def trace_bwd(self, frame_number, num_active_features, particle_density, particle_radiance, ray_origin, ray_direction,
+                  ray_timestamp, sensor: abi.GutCamera, start_timestamp, end_timestamp, start_pose, end_pose,
+                  ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad,
+                  out_density_grad=None, out_radiance_grad=None, accumulate=False):
+        """reference: SplatRaster::traceBwd (splatRaster.cpp:246-332).
+
+        ``out_*`` + ``accumulate`` are this build's extension: gradients are added into caller-owned buffers
+        (sum over the views of a rank before the data-parallel allreduce).
+        """
+        del frame_number, ray_timestamp, start_timestamp, end_timestamp, start_pose, end_pose
+        dev = self.device
+        dens = _check_cuda_f32("particle_density", particle_density, dev)
+        rad = _check_cuda_f32("particle_radiance", particle_radiance, dev)
+        ro = _check_cuda_f32("ray_origin", ray_origin, dev)
+        rd = _check_cuda_f32("ray_direction", ray_direction, dev)
+        rgba = _check_cuda_f32("ray_radiance_density", ray_radiance_density, dev)
+        rgba_g = _check_cuda_f32("ray_radiance_density_grad", ray_radiance_density_grad, dev)
+        dist = _check_cuda_f32("ray_hit_distance", ray_hit_distance, dev)
+        dist_g = _check_cuda_f32("ray_hit_distance_grad", ray_hit_distance_grad, dev)
+        n = dens.shape[0]
+        height, width = ro.shape[1], ro.shape[2]
+        if rgba_g.numel() != height * width * 4 or dist_g.numel() != height * width:
+            raise GutError(abi.GutStatus.BAD_INPUT, "gradient shapes do not match the view")
+        if out_density_grad is None:
+            out_density_grad = torch.empty((n, 12), dtype=torch.float32, device=dev)
+            out_radiance_grad = torch.empty((n, self.n_coeffs * 3), dtype=torch.float32, device=dev)
+            accumulate = False
+        rc = self.lib.gut_backward(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
+                                   width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
+                                   _ptr(out_density_grad), _ptr(out_radiance_grad), 1 if accumulate else 0)
+        if rc != 0:
+            self._raise(rc)
+        return out_density_grad, out_radiance_grad
+
+    def collect_times(self):
+        """reference: SplatRaster::collectTimes (splatRaster.cpp:334-364) -> {tag: mean ms}."""
+        f, b = C.c_float(-1.0), C.c_float(-1.0)
+        self.lib.gut_timings(self._h, C.byref(f), C.byref(b))
+        out = {}
+        if f.value >= 0:
+            out["forward_render"] = f.value
+        if b.value >= 0:
+            out["backward_render"] = b.value
+        return out
+
+    def stage_times(self):
+        n = self.lib.gut_num_stages()
+        arr = (C.c_float * n)()
+        self.lib.gut_stage_timings(self._h, arr)
+        return {self.lib.gut_stage_name(i).decode(): arr[i] for i in range(n) if arr[i] >= 0}
+
+    def frame_stats(self):
+        st = abi.GutFrameStats()
+        self.lib.gut_frame_stats(self._h, C.byref(st))
+        return {"num_intersections": st.num_intersections, "num_tiles": st.num_tiles,
+                "max_tile_list_length": st.max_tile_list_length, "kernel_launches": st.kernel_launches}
+
+    # ---- host-buffer entry points (end-to-end path) --------------------------------------------------------
+    def trace_host(self, num_active_features, particle_density, particle_radiance, h_ray_origin, h_ray_direction, sensor,
+                   h_rgba, h_dist, h_hits, visibility):
+        n = particle_density.shape[0]
+        height, width = h_ray_origin.shape[1], h_ray_origin.shape[2]
+        rc = self.lib.gut_forward_host(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(particle_density),
+                                       _ptr(particle_radiance), width, height, _ptr(h_ray_origin), _ptr(h_ray_direction),
+                                       _ptr(h_rgba), _ptr(h_dist), _ptr(h_hits), _ptr(visibility))
+        if rc != 0:
+            self._raise(rc)
+
+    def trace_bwd_host(self, num_active_features, particle_density, particle_radiance, width, height, sensor, h_rgba_grad,
+                       h_dist_grad, out_density_grad, out_radiance_grad, accumulate=False):
+        n = particle_density.shape[0]
+        rc = self.lib.gut_backward_host(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(particle_density),
+                                        _ptr(particle_radiance), width, height, _ptr(h_rgba_grad), _ptr(h_dist_grad),
+                                        _ptr(out_density_grad), _ptr(out_radiance_grad), 1 if accumulate else 0)
+        if rc != 0:
+            self._raise(rc)

@@ -1,0 +1,140 @@
+"""``Tracer`` -- the renderer plugin the 3DGRUT model drives, backed by libgut_b200.
+
+Drop-in for ``threedgut_tracer.Tracer`` (reference: threedgut_tracer/tracer.py:158-431):
+
+    Tracer(conf)                                   # conf.render.* as in configs/render/3dgut.yaml
+    Tracer.build_acc(gaussians, rebuild=True)      # no-op for 3DGUT
+    Tracer.render(gaussians, gpu_batch, train=False, frame_id=0) -> dict
+    Tracer.timings                                 # {"forward_render": ms, "backward_render": ms}
+
+called from ``MixtureOfGaussians`` (threedgrut/model/model.py:184-185, 596, 609) and
+``Trainer3DGRUT`` (threedgrut/trainer.py:786-789).  ``gaussians`` is duck-typed:
+``num_gaussians``, ``n_active_features``, ``positions``, ``get_rotation()``,
+``get_scale()``, ``get_density()``, ``get_features()``, ``background(...)``.
+"""
+import torch
+
+from . import abi
+from .camera import camera_from_batch
+from .native import SplatRaster
+
+
+def _get(conf, path, default=None):
+    """Read ``a.b.c`` from an OmegaConf DictConfig, a plain dict, or an attribute namespace."""
+    cur = conf
+    for key in path.split("."):
+        if cur is None:
+            return default
+        if isinstance(cur, dict):
+            cur = cur.get(key, None)
+        else:
+            try:
+                cur = getattr(cur, key)
+            except (AttributeError, KeyError):
+                try:
+                    cur = cur[key]
+                except Exception:
+                    return default
+    return default if cur is None else cur
+
+
+def config_from_conf(conf) -> abi.GutConfig:
+    """``conf.render.*`` -> GutConfig.  The reference turns the same keys into -D defines
+    (threedgut_tracer/setup_3dgut.py:47-70); missing keys take the reference defaults."""
+    d = abi.default_config()
+    r = "render."
+    d.kernel_degree = int(_get(conf, r + "particle_kernel_degree", d.kernel_degree))
+    d.min_kernel_response = float(_get(conf, r + "particle_kernel_min_response", d.min_kernel_response))
+    d.min_alpha = float(_get(conf, r + "particle_kernel_min_alpha", d.min_alpha))
+    d.max_alpha = float(_get(conf, r + "particle_kernel_max_alpha", d.max_alpha))
+    d.min_transmittance = float(_get(conf, r + "min_transmittance", d.min_transmittance))
+    d.sph_max_degree = int(_get(conf, r + "particle_radiance_sph_degree", d.sph_max_degree))
+    d.enable_hitcounts = int(bool(_get(conf, r + "enable_hitcounts", bool(d.enable_hitcounts))))
+    d.enable_kernel_timings = int(bool(_get(conf, r + "enable_kernel_timings", bool(d.enable_kernel_timings))))
+    s = r + "splat."
+    d.rect_bounding = int(bool(_get(conf, s + "rect_bounding", True)))
+    d.tight_opacity_bounding = int(bool(_get(conf, s + "tight_opacity_bounding", True)))
+    d.tile_based_culling = int(bool(_get(conf, s + "tile_based_culling", True)))
+    d.n_rolling_shutter_iterations = int(_get(conf, s + "n_rolling_shutter_iterations", d.n_rolling_shutter_iterations))
+    d.ut_alpha = float(_get(conf, s + "ut_alpha", d.ut_alpha))
+    d.ut_beta = float(_get(conf, s + "ut_beta", d.ut_beta))
+    d.ut_kappa = float(_get(conf, s + "ut_kappa", d.ut_kappa))
+    d.ut_in_image_margin_factor = float(_get(conf, s + "ut_in_image_margin_factor", d.ut_in_image_margin_factor))
+    d.ut_require_all_sigma_points_valid = int(bool(_get(conf, s + "ut_require_all_sigma_points_valid", False)))
+    d.k_buffer_size = int(_get(conf, s + "k_buffer_size", d.k_buffer_size))
+    d.global_z_order = int(bool(_get(conf, s + "global_z_order", True)))
+    return d
+
+
+class Tracer:
+    class _Autograd(torch.autograd.Function):
+        """reference: Tracer._Autograd (tracer.py:159-286)."""
+
+        @staticmethod
+        def forward(ctx, tracer_wrapper, frame_id, n_active_features, ray_ori, ray_dir, mog_pos, mog_rot, mog_scl, mog_dns, mog_sph,
+                    sensor):
+            # [pos, density, rot, scale, 0] -> [N,12]  (tracer.py:176-178)
+            particle_density = torch.cat([mog_pos, mog_dns, mog_rot, mog_scl, torch.zeros_like(mog_dns)], dim=1).contiguous()
+            particle_radiance = mog_sph.contiguous()
+            rgba, dist, hits, vis = tracer_wrapper.trace(frame_id, n_active_features, particle_density, particle_radiance,
+                                                         ray_ori, ray_dir, None, sensor)
+            ctx.save_for_backward(ray_ori, ray_dir, rgba, dist, particle_density, particle_radiance)
+            ctx.frame_id = frame_id
+            ctx.n_active_features = n_active_features
+            ctx.sensor = sensor
+            ctx.tracer_wrapper = tracer_wrapper
+            ctx.mark_non_differentiable(hits, vis)
+            return rgba, dist, hits, vis
+
+        @staticmethod
+        def backward(ctx, rgba_grad, dist_grad, _hits_grad_unused, _vis_grad_unused):
+            ray_ori, ray_dir, rgba, dist, particle_density, particle_radiance = ctx.saved_tensors
+            if rgba_grad is None:
+                rgba_grad = torch.zeros_like(rgba)
+            if dist_grad is None:
+                dist_grad = torch.zeros_like(dist)
+            density_grad, radiance_grad = ctx.tracer_wrapper.trace_bwd(
+                ctx.frame_id, ctx.n_active_features, particle_density, particle_radiance, ray_ori, ray_dir, None, ctx.sensor,
+                0, 1, None, None, rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous())
+            pos_g, dns_g, rot_g, scl_g, _pad = torch.split(density_grad, [3, 1, 4, 3, 1], dim=1)
+            return (None, None, None, None, None, pos_g.contiguous(), rot_g.contiguous(), scl_g.contiguous(), dns_g.contiguous(),
+                    radiance_grad, None)
+
+    def __init__(self, conf):
+        self.device = "cuda"
+        self.conf = conf
+        torch.zeros(1, device=self.device)  # force CUDA context creation, as the reference does (tracer.py:292)
+        self.tracer_wrapper = SplatRaster(config_from_conf(conf))
+
+    @property
+    def timings(self):
+        return self.tracer_wrapper.collect_times()
+
+    def build_acc(self, gaussians, rebuild=True):
+        pass  # 3DGUT has no acceleration structure (tracer.py:301-302)
+
+    def render(self, gaussians, gpu_batch, train=False, frame_id=0):
+        rays_o = gpu_batch.rays_ori
+        rays_d = gpu_batch.rays_dir
+        sensor = camera_from_batch(gpu_batch)
+        num_gaussians = gaussians.num_gaussians
+        with torch.cuda.nvtx.range(f"model.forward({num_gaussians} gaussians)"):
+            pred_rgba, pred_dist, hits_count, mog_visibility = Tracer._Autograd.apply(
+                self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),
+                gaussians.positions.contiguous(), gaussians.get_rotation().contiguous(), gaussians.get_scale().contiguous(),
+                gaussians.get_density().contiguous(), gaussians.get_features().contiguous(), sensor)
+            pred_rgb = pred_rgba[..., :3].unsqueeze(0).contiguous()
+            pred_opacity = pred_rgba[..., 3:].unsqueeze(0).contiguous()
+            pred_dist = pred_dist.unsqueeze(0).contiguous()
+            hits_count = hits_count.unsqueeze(0).contiguous()
+            pred_rgb, pred_opacity = gaussians.background(gpu_batch.T_to_world.contiguous(), rays_d, pred_rgb, pred_opacity, train)
+            timings = self.tracer_wrapper.collect_times()
+        return {
+            "pred_rgb": pred_rgb,
+            "pred_opacity": pred_opacity,
+            "pred_dist": pred_dist,
+            "pred_normals": torch.nn.functional.normalize(torch.ones_like(pred_rgb), dim=3),
+            "hits_count": hits_count,
+            "frame_time_ms": timings["forward_render"] if "forward_render" in timings else 0.0,
+            "mog_visibility": mog_visibility,
+        }

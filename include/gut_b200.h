@@ -36,6 +36,12 @@ extern "C" {
 
 #define GUT_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define GUT_API __attribute__((visibility("default")))
+#else
+#define GUT_API
+#endif
+
 typedef enum GutStatus {
     GUT_OK                = 0,
     GUT_ERR_BAD_INPUT     = 1, /* null pointer, bad size, unsupported config     */
@@ -89,7 +95,7 @@ typedef struct GutConfig {
 } GutConfig;
 
 /* Fill *cfg with the reference defaults listed above. */
-void gut_default_config(GutConfig* cfg);
+GUT_API void gut_default_config(GutConfig* cfg);
 
 /*
  * Camera intrinsics + the two shutter poses of one view.
@@ -136,9 +142,9 @@ typedef struct GutStageOutputs {
 typedef struct GutHandle GutHandle;
 
 /* reference: SplatRaster::SplatRaster(json) splatRaster.cpp:153-168 */
-int gut_create(const GutConfig* cfg, int device, GutHandle** out);
+GUT_API int gut_create(const GutConfig* cfg, int device, GutHandle** out);
 /* reference: SplatRaster::~SplatRaster + ~GutRenderForwardContext gutRenderer.cu:106-127 */
-void gut_destroy(GutHandle* h);
+GUT_API void gut_destroy(GutHandle* h);
 
 /*
  * Forward render of one view.  reference: SplatRaster::trace
@@ -153,7 +159,7 @@ void gut_destroy(GutHandle* h);
  *   d_particle_visibility [N] (1.0f where the projected conic is valid; the
  *   reference stores int 1 in float storage)
  */
-int gut_forward(GutHandle* h, void* stream, const GutCamera* camera,
+GUT_API int gut_forward(GutHandle* h, void* stream, const GutCamera* camera,
                 uint32_t num_particles, int32_t sph_degree_active,
                 const float* d_particle_density, const float* d_particle_radiance,
                 uint32_t width, uint32_t height,
@@ -172,7 +178,7 @@ int gut_forward(GutHandle* h, void* stream, const GutCamera* camera,
  * accumulate != 0: gradients are ADDED to the buffers' current content (used to sum
  *   the views of one rank before the data-parallel allreduce).
  */
-int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
+GUT_API int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
                  uint32_t num_particles, int32_t sph_degree_active,
                  const float* d_particle_density, const float* d_particle_radiance,
                  uint32_t width, uint32_t height,
@@ -188,7 +194,7 @@ int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
  * Particle parameters stay device resident (they are the model, not a per-view
  * input).  Pointers named h_* are host pointers, ideally pinned.
  */
-int gut_forward_host(GutHandle* h, void* stream, const GutCamera* camera,
+GUT_API int gut_forward_host(GutHandle* h, void* stream, const GutCamera* camera,
                      uint32_t num_particles, int32_t sph_degree_active,
                      const float* d_particle_density, const float* d_particle_radiance,
                      uint32_t width, uint32_t height,
@@ -196,7 +202,7 @@ int gut_forward_host(GutHandle* h, void* stream, const GutCamera* camera,
                      float* h_ray_radiance_density, float* h_ray_hit_distance,
                      float* h_ray_hit_count, float* d_particle_visibility);
 
-int gut_backward_host(GutHandle* h, void* stream, const GutCamera* camera,
+GUT_API int gut_backward_host(GutHandle* h, void* stream, const GutCamera* camera,
                       uint32_t num_particles, int32_t sph_degree_active,
                       const float* d_particle_density, const float* d_particle_radiance,
                       uint32_t width, uint32_t height,
@@ -206,16 +212,16 @@ int gut_backward_host(GutHandle* h, void* stream, const GutCamera* camera,
 
 /* reference: SplatRaster::collectTimes splatRaster.cpp:334-364 -- mean ms of the
  * forward/backward calls since the last collection; -1 when none was timed. */
-int gut_timings(GutHandle* h, float* forward_render_ms, float* backward_render_ms);
+GUT_API int gut_timings(GutHandle* h, float* forward_render_ms, float* backward_render_ms);
 
 /*
  * Per-stage mean device times (ms) since the last call, in the order of
  * gut_stage_name(i), i < gut_num_stages().  Stage names follow the reference's
  * DeviceLaunchesLogger tags (gutRenderer.cu:256-378).
  */
-int         gut_num_stages(void);
-const char* gut_stage_name(int i);
-int         gut_stage_timings(GutHandle* h, float* ms_out /* [gut_num_stages()] */);
+GUT_API int         gut_num_stages(void);
+GUT_API const char* gut_stage_name(int i);
+GUT_API int         gut_stage_timings(GutHandle* h, float* ms_out /* [gut_num_stages()] */);
 
 /* Statistics of the last forward (what defines the work). */
 typedef struct GutFrameStats {
@@ -224,10 +230,15 @@ typedef struct GutFrameStats {
     uint32_t max_tile_list_length;
     uint64_t kernel_launches;       /* kernels launched by this handle so far */
 } GutFrameStats;
-int gut_frame_stats(GutHandle* h, GutFrameStats* out);
+GUT_API int gut_frame_stats(GutHandle* h, GutFrameStats* out);
 
-const char* gut_last_error(GutHandle* h);
-int         gut_abi_version(void);
+GUT_API const char* gut_last_error(GutHandle* h);
+GUT_API int         gut_abi_version(void);
+/* struct sizes as compiled into the library, so a foreign-language binding can verify its mirror of the structs */
+GUT_API size_t      gut_sizeof_config(void);
+GUT_API size_t      gut_sizeof_camera(void);
+GUT_API size_t      gut_sizeof_stage_outputs(void);
+GUT_API size_t      gut_sizeof_frame_stats(void);
 
 #ifdef __cplusplus
 }

@@ -357,7 +357,7 @@ static tile_bbox tile_space_bbox(uint32_t gx, uint32_t gy, v2 pos, v2 ext) {
     return b;
 }
 
-static inline float saturatef(float x) { return x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x); } /* __saturatef; NaN -> 0 */
+static inline float saturatef(float x) { return (x != x) ? 0.0f : (x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x)); } /* __saturatef: NaN -> 0 */
 
 /* tileMinParticlePowerResponse, gutProjector.cuh:49-78 (evaluation order kept; every * and + rounds separately) */
 static float tile_min_power(float tx_, float ty_, v4 co, v2 mean) {
@@ -761,7 +761,10 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                                   const float* density12, const float* features /* [N,3] unclamped */,
                                   const float* ray_ori, const float* ray_dir,
                                   const uint32_t* tile_ranges, const uint32_t* sorted_idx,
-                                  float* rgba, float* dist, float* hits, uint64_t* tests_out) {
+                                  float* rgba, float* dist, float* hits, uint64_t* tests_out,
+                                  float* margin /* optional [H,W]: smallest relative distance of any accept/kill decision of the
+                                                   ray to its threshold -- pixels with a tiny margin may legitimately differ between two
+                                                   fp32 implementations by one whole hit; the parity tests treat them separately */) {
     (void)N;
     const frame_consts f = make_frame(cam, W, H);
     const int K = cfg->k_buffer_size;
@@ -776,6 +779,7 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                 ray_t ray = init_ray(&f, ray_ori, ray_dir, idx);
                 if (!ray.valid) continue;
                 float T = 1.0f, D = 0.0f; v3 C = {0.0f, 0.0f, 0.0f}; uint32_t n = 0; int alive = 1;
+                float mrg = FLT_MAX;
                 hit_t kb[MAX_K]; int nk = 0;
                 for (int k = 0; k < K; ++k) { kb[k].idx = -1; kb[k].t = -1.0f; kb[k].alpha = 0.0f; }
 #define PROCESS_HIT(HT)                                                                                         \
@@ -789,6 +793,7 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
             C.x += fmaxf(ft_[0], 0.0f) * w_; C.y += fmaxf(ft_[1], 0.0f) * w_; C.z += fmaxf(ft_[2], 0.0f) * w_; \
             n++;                                                                                               \
         }                                                                                                      \
+        mrg = fminf(mrg, fabsf(T - cfg->min_transmittance) / cfg->min_transmittance);                          \
         if (T < cfg->min_transmittance) alive = 0;                                                             \
     } while (0)
                 for (uint32_t s = r0; alive && s < r1; ++s) {
@@ -797,7 +802,10 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                     const raw_particle* p = (const raw_particle*)(density12 + 12 * (size_t)pi);
                     v3 rt[3]; particle_rotT(p, rt);
                     canon_t c; tests++;
-                    if (!particle_hit(cfg, p, rt, ray.o, ray.d, &c)) continue;
+                    const int accepted = particle_hit(cfg, p, rt, ray.o, ray.d, &c);
+                    mrg = fminf(mrg, fabsf(c.resp - cfg->min_kernel_response) / cfg->min_kernel_response);
+                    mrg = fminf(mrg, fabsf(c.resp * p->density - cfg->min_alpha) / cfg->min_alpha);
+                    if (!accepted) continue;
                     hit_t h = {(int)pi, canon_distance(p, &c), c.alpha};
                     if (!(h.t > ray.tmin && h.t < ray.tmax)) continue;
                     if (K == 0) { PROCESS_HIT(&h); continue; }
@@ -811,6 +819,7 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                 rgba[4 * idx] = C.x; rgba[4 * idx + 1] = C.y; rgba[4 * idx + 2] = C.z; rgba[4 * idx + 3] = 1.0f - T;
                 dist[idx] = D;
                 if (cfg->enable_hitcounts) hits[idx] = (float)n;
+                if (margin) margin[idx] = mrg;
             }
     }
     if (tests_out) *tests_out = tests;

@@ -110,10 +110,11 @@ def render(cfg, cam, density12, features, ray_ori, ray_dir, W, H, tile_ranges, s
     dist = np.full((H, W), 1e6, np.float32)
     hits = np.zeros((H, W), np.float32)
     tests = C.c_uint64(0)
+    margin = np.full((H, W), np.inf, np.float32)
     lib().gut_oracle_render(C.byref(cfg), C.byref(cam), C.c_uint32(density12.shape[0]), C.c_uint32(W), C.c_uint32(H),
                             _p(density12), _p(features), _p(ray_ori), _p(ray_dir), _p(tile_ranges), _p(sorted_values),
-                            _p(rgba), _p(dist), _p(hits), C.byref(tests))
-    return {"rgba": rgba, "dist": dist, "hits": hits, "tests": tests.value}
+                            _p(rgba), _p(dist), _p(hits), C.byref(tests), _p(margin))
+    return {"rgba": rgba, "dist": dist, "hits": hits, "tests": tests.value, "margin": margin}
 
 
 def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree):
@@ -122,7 +123,7 @@ def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree):
     bins = bin_and_sort(cfg, W, H, proj)
     if bins["M"] == 0:  # early return, gutRenderer.cu:323-325
         out = {"rgba": np.zeros((H, W, 4), np.float32), "dist": np.full((H, W), 1e6, np.float32),
-               "hits": np.zeros((H, W), np.float32), "tests": 0}
+               "hits": np.zeros((H, W), np.float32), "tests": 0, "margin": np.full((H, W), np.inf, np.float32)}
     else:
         out = render(cfg, cam, density12, proj["features"], ray_ori, ray_dir, W, H, bins["tile_ranges"], bins["sorted_values"])
     out.update(proj=proj, bins=bins, visibility=proj["visibility"])

@@ -1,0 +1,158 @@
+"""GPU parity: libgut_b200 (through the Tracer / SplatRaster API and the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star): tile lists / sorted keys / ranges bit-exact; RGB/alpha/depth <= 1e-4 max-abs;
+particle gradients <= 1e-3 relative L2.  Pixels whose accept/kill decisions sit within BORDERLINE_MARGIN of a
+threshold in the oracle are compared separately (two fp32 implementations may legitimately take different
+branches there and differ by one whole hit); their fraction is bounded.
+"""
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+from tests.helpers import (SyntheticGaussians, abi, camera_of, cfg_from_conf, compare_images, make_batch, make_conf,
+                           oracle_reference, rel_l2, syn)
+
+pytestmark = pytest.mark.gpu
+
+TOL_IMG = 1e-4
+TOL_GRAD = 1e-3
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return importlib.import_module("3dgrut_b200")
+
+
+def _raster(pkg, **over):
+    native = importlib.import_module("3dgrut_b200.native")
+    return native.SplatRaster(cfg_from_conf(make_conf(**over)))
+
+
+def _run_forward(raster, scene, view, sph_degree, stage=True):
+    dev = "cuda"
+    d12 = syn.pack_density(scene).to(dev)
+    sph = scene["features"].to(dev)
+    cam = camera_of(view)
+    out = raster.trace(0, sph_degree, d12, sph, view["rays_ori"].to(dev), view["rays_dir"].to(dev), None, cam, stage_outputs=stage)
+    torch.cuda.synchronize()
+    return out, (d12, sph, cam)
+
+
+CASES = [
+    # name, N, W, H, sph_degree, kind, seed
+    ("c1_oracle_config", 10000, 128, 128, 0, "init", 1001),
+    ("sh3_ragged_image", 6000, 150, 70, 3, "init", 5),
+    ("dense_anisotropic", 3000, 96, 96, 2, "dense", 9),
+]
+
+
+@pytest.mark.parametrize("name,n,w,h,deg,kind,seed", CASES)
+def test_forward_stages_and_image(pkg, name, n, w, h, deg, kind, seed):
+    scene = syn.make_scene(n, 3, seed=seed, kind=kind)
+    view = syn.make_view(w, h)
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg)
+    raster = _raster(pkg)
+    (rgba, dist, hits, vis, st), _ = _run_forward(raster, scene, view, deg)
+
+    # K1: integer result exact, floats to 1e-5 relative (pinhole / global shutter is bit-reproducible)
+    tc = st["tiles_count"].cpu().numpy().astype(np.uint32)
+    assert np.array_equal(tc, ref["proj"]["tiles_count"]), f"{name}: tiles_count differs on {(tc != ref['proj']['tiles_count']).sum()} particles"
+    m = tc > 0
+    for key_gpu, key_ref in (("proj_position", "proj_pos"), ("proj_conic_opacity", "conic_opacity"), ("proj_extent", "extent"),
+                             ("global_depth", "depth"), ("features", "features")):
+        a = st[key_gpu].cpu().numpy()[m]; b = ref["proj"][key_ref][m]
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6, err_msg=f"{name}: {key_gpu}")
+    assert np.array_equal(vis.cpu().numpy().reshape(-1)[m] > 0, ref["visibility"][m] > 0)
+
+    # binning: bit-exact
+    bins = ref["bins"]
+    assert st["num_intersections"] == bins["M"]
+    assert np.array_equal(st["sorted_keys"].cpu().numpy().view(np.uint64), bins["sorted_keys"])
+    assert np.array_equal(st["sorted_particle_idx"].cpu().numpy().view(np.uint32), bins["sorted_values"])
+    assert np.array_equal(st["tile_ranges"].cpu().numpy().view(np.uint32), bins["tile_ranges"])
+
+    # image
+    stats = compare_images(rgba.cpu().numpy(), ref["rgba"], ref["borderline"])
+    assert stats["max_abs_clean"] <= TOL_IMG, (name, stats)
+    assert stats["borderline_fraction"] < 0.02, (name, stats)
+    assert stats["max_abs_borderline"] < 2e-2, (name, stats)
+    clean = ~ref["borderline"]
+    d_err = np.abs(dist.cpu().numpy().reshape(h, w) - ref["dist"])[clean]
+    assert d_err.max() <= TOL_IMG * max(1.0, float(np.abs(ref["dist"]).max())), (name, d_err.max())
+    assert np.array_equal(hits.cpu().numpy().reshape(h, w)[clean], ref["hits"][clean])
+
+
+@pytest.mark.parametrize("name,n,w,h,deg,kind,seed", CASES)
+def test_backward_gradients(pkg, name, n, w, h, deg, kind, seed):
+    scene = syn.make_scene(n, 3, seed=seed, kind=kind)
+    view = syn.make_view(w, h)
+    rng = np.random.default_rng(seed)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg, rgba_grad=rgba_grad, dist_grad=dist_grad)
+    raster = _raster(pkg)
+    (rgba, dist, hits, vis), (d12, sph, cam) = _run_forward(raster, scene, view, deg, stage=False)
+    g12, gsph = raster.trace_bwd(0, deg, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba, torch.from_numpy(rgba_grad).cuda(), dist, torch.from_numpy(dist_grad).cuda().reshape(h, w, 1))
+    torch.cuda.synchronize()
+    g12 = g12.cpu().numpy(); gsph = gsph.cpu().numpy()
+    assert np.all(g12[:, 11] == 0)
+    for lo, hi, what in ((0, 3, "position"), (3, 4, "density"), (4, 8, "rotation"), (8, 11, "scale")):
+        e = rel_l2(g12[:, lo:hi], ref["density_grad"][:, lo:hi])
+        assert e <= TOL_GRAD, (name, what, e)
+    e = rel_l2(gsph, ref["radiance_grad"])
+    assert e <= TOL_GRAD, (name, "sph", e)
+
+
+def test_tracer_autograd_matches_native(pkg):
+    """The Tracer.render autograd path returns the same gradients as the raw trace/trace_bwd calls."""
+    n, w, h, deg = 3000, 64, 48, 3
+    scene = syn.make_scene(n, 3, seed=3)
+    view = syn.make_view(w, h)
+    tracer = pkg.Tracer(make_conf())
+    g = SyntheticGaussians(scene, "cuda", n_active_features=deg, requires_grad=True)
+    out = tracer.render(g, make_batch(view, "cuda"), train=True)
+    assert out["pred_rgb"].shape == (1, h, w, 3) and out["pred_opacity"].shape == (1, h, w, 1)
+    assert out["pred_dist"].shape == (1, h, w, 1) and out["hits_count"].shape == (1, h, w, 1)
+    assert out["mog_visibility"].shape == (n, 1)
+    rng = np.random.default_rng(0)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    rg = torch.from_numpy(rgba_grad).cuda()
+    loss = (out["pred_rgb"][0] * rg[..., :3]).sum() + (out["pred_opacity"][0] * rg[..., 3:]).sum() + \
+        (out["pred_dist"][0, ..., 0] * torch.from_numpy(dist_grad).cuda()).sum()
+    loss.backward()
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg, rgba_grad=rgba_grad, dist_grad=dist_grad)
+    assert rel_l2(g.positions.grad.cpu().numpy(), ref["density_grad"][:, 0:3]) <= TOL_GRAD
+    assert rel_l2(g._density.grad.cpu().numpy(), ref["density_grad"][:, 3:4]) <= TOL_GRAD
+    assert rel_l2(g._rotation.grad.cpu().numpy(), ref["density_grad"][:, 4:8]) <= TOL_GRAD
+    assert rel_l2(g._scale.grad.cpu().numpy(), ref["density_grad"][:, 8:11]) <= TOL_GRAD
+    assert rel_l2(g._features.grad.cpu().numpy(), ref["radiance_grad"]) <= TOL_GRAD
+
+
+def test_empty_and_error_paths(pkg):
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = _raster(pkg)
+    w, h = 40, 24
+    view = syn.make_view(w, h)
+    cam = camera_of(view)
+    # all particles behind the camera -> M == 0 -> outputs keep their initial values (gutRenderer.cu:323-325)
+    scene = syn.make_scene(100, 3, seed=1)
+    scene["positions"] = scene["positions"] * 0.01 + torch.tensor([20.0, 0.0, 0.0])
+    d12 = syn.pack_density(scene).cuda(); sph = scene["features"].cuda()
+    rgba, dist, hits, vis = raster.trace(0, 3, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam)
+    torch.cuda.synchronize()
+    assert raster.frame_stats()["num_intersections"] == 0
+    assert float(rgba.abs().max()) == 0.0 and float(dist.min()) == 1e6 and float(hits.max()) == 0.0
+    g12, gsph = raster.trace_bwd(0, 3, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba, torch.ones_like(rgba), dist, torch.ones_like(dist))
+    assert float(g12.abs().max()) == 0.0 and float(gsph.abs().max()) == 0.0
+    # backward without forward on a fresh handle raises (the reference only logs, gutRenderer.cu:413-417)
+    fresh = _raster(pkg)
+    with pytest.raises(native.GutError):
+        fresh.trace_bwd(0, 3, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                        rgba, torch.ones_like(rgba), dist, torch.ones_like(dist))
+    with pytest.raises(native.GutError):
+        raster.trace(0, 3, d12[:, :11].contiguous(), sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam)
