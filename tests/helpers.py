@@ -17,7 +17,7 @@ camera = importlib.import_module("3dgrut_b200.camera")
 protocols = importlib.import_module("3dgrut_b200.protocols")
 
 # relative distance to an accept/kill threshold below which one fp32 implementation may take the other branch
-BORDERLINE_MARGIN = 2e-4
+BORDERLINE_MARGIN = 2e-5
 
 
 def make_conf(**render_overrides):
