@@ -356,7 +356,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         {
             StageTimer t(h, ST_RENDER, s);
             GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p, d_ray_ori, d_ray_dir,
-                                          d_rgba, d_dist, d_hits, s));
+                                          d_rgba, d_dist, d_hits, nullptr, s));
             h->launches += 1;
         }
     }
@@ -501,6 +501,24 @@ int gut_stage_timings(GutHandle* h, float* ms_out) {
         if (counts[i]) h->last_stage_ms[i] = sums[i] / counts[i];
         ms_out[i] = h->last_stage_ms[i];
     }
+    return GUT_OK;
+}
+
+int gut_measure_work(GutHandle* h, void* stream_, const float* d_ray_ori, const float* d_ray_dir, uint64_t* tests, uint64_t* hits) {
+    if (!h || !tests || !hits) return GUT_ERR_BAD_INPUT;
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!h->fwd_valid || h->fwd_stream != s) return fail(h, GUT_ERR_NO_FORWARD, "gut_measure_work needs a preceding forward on this stream");
+    *tests = 0; *hits = 0;
+    if (h->fwd_M == 0) return GUT_OK;
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, ensure(h->stats, 16, s));
+    GUT_CUDA(h, cudaMemsetAsync(h->stats.p, 0, 16, s));
+    GUT_CUDA(h, gut_launch_render(h->cfg, h->fwd_frame, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p, d_ray_ori, d_ray_dir,
+                                  nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, s));
+    unsigned long long host[2] = {0, 0};
+    GUT_CUDA(h, cudaMemcpyAsync(host, h->stats.p, 16, cudaMemcpyDeviceToHost, s));
+    GUT_CUDA(h, cudaStreamSynchronize(s));
+    *tests = host[0]; *hits = host[1];
     return GUT_OK;
 }
 

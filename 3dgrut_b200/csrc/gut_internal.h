@@ -69,7 +69,7 @@ cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_s
 
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              cudaStream_t stream);
+                              unsigned long long* counters /* non-null: count tests/hits instead of rendering */, cudaStream_t stream);
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
                                        const GutRecord* records, const float4* quats, const float* ray_ori, const float* ray_dir,

@@ -142,12 +142,14 @@ GUT_D bool particle_test(const GutConfig& cfg, const float4 A, const float4 B, c
 // ---------------------------------------------------------------------------------------------------
 // K4 forward
 // ---------------------------------------------------------------------------------------------------
-template <int DEG>
+// COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
+// tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
+template <int DEG, bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                     const GutRecord* __restrict__ records,
                                                                     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                     float4* __restrict__ rgba, float* __restrict__ dist,
-                                                                    float* __restrict__ hits) {
+                                                                    float* __restrict__ hits, unsigned long long* __restrict__ counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr uint32_t STAGE_BYTES = BATCH * sizeof(GutRecord);
     __shared__ __align__(8) uint64_t full_bar[2];
@@ -179,7 +181,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
     }
 
     float T = 1.0f, D = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
-    uint32_t nhits = 0;
+    uint32_t nhits = 0, ntests = 0;
     uint32_t b = 0;
     for (; b < nb; ++b) {
         const uint32_t cnt = min((uint32_t)BATCH, n - b * BATCH);
@@ -196,6 +198,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
             if ((j & 15u) == 0u && !__any_sync(0xffffffffu, alive)) break;
             const float4 A = rec[5 * j], B = rec[5 * j + 1], Cm = rec[5 * j + 2], S = rec[5 * j + 3];
             Canon k;
+            if (COUNT && alive) ntests++;
             if (particle_test<DEG>(cfg, A, B, Cm, S, ray.o, ray.d, k) && alive) {
                 // accepted: hit distance = |scale * grd * dot(grd, -gro)|   (canonicalRayDistance, gaussianParticles.slang:165-171)
                 const float il = rsqrtf(k.l2);
@@ -217,6 +220,13 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
     }
     // the tile saturated early while the next batch was already in flight: let the copy land before the CTA retires
     if (b + 1 < nb) mbar_wait(&full_bar[(b + 1) & 1], ((b + 1) >> 1) & 1);
+    if (COUNT) {
+        unsigned long long t = ntests, hh = nhits;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&counters[0], t); atomicAdd(&counters[1], hh); }
+        return;
+    }
     if (inside && ray.valid) {
         rgba[pix] = make_float4(cr, cg, cb, 1.0f - T);
         dist[pix] = D;
@@ -449,12 +459,21 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
 
 template <int DEG>
 cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
-                              const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits, cudaStream_t stream) {
+                              const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
+                              unsigned long long* counters, cudaStream_t stream) {
     const size_t smem = 2 * BATCH * sizeof(GutRecord);
-    cudaError_t e = cudaFuncSetAttribute(gut_render_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    gut_render_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, records, ray_ori, ray_dir,
-                                                                            reinterpret_cast<float4*>(rgba), dist, hits);
+    cudaError_t e;
+    if (counters) {
+        e = cudaFuncSetAttribute(gut_render_kernel<DEG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        gut_render_kernel<DEG, true><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, records, ray_ori, ray_dir,
+                                                                                      nullptr, nullptr, nullptr, counters);
+    } else {
+        e = cudaFuncSetAttribute(gut_render_kernel<DEG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        gut_render_kernel<DEG, false><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, records, ray_ori, ray_dir,
+                                                                                       reinterpret_cast<float4*>(rgba), dist, hits, nullptr);
+    }
     return cudaGetLastError();
 }
 
@@ -488,8 +507,8 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
 
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              cudaStream_t stream) {
-#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, records, ray_ori, ray_dir, rgba, dist, hits, stream)
+                              unsigned long long* counters, cudaStream_t stream) {
+#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, records, ray_ori, ray_dir, rgba, dist, hits, counters, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_FWD)
 #undef CALL_FWD
 }

@@ -75,6 +75,8 @@ def load_library():
     lib.gut_stage_timings.restype = C.c_int
     lib.gut_frame_stats.argtypes = [vp, C.POINTER(abi.GutFrameStats)]
     lib.gut_frame_stats.restype = C.c_int
+    lib.gut_measure_work.argtypes = [vp, vp, fp, fp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.gut_measure_work.restype = C.c_int
     lib.gut_last_error.argtypes = [vp]
     lib.gut_last_error.restype = C.c_char_p
     for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats"):
@@ -272,6 +274,15 @@ class SplatRaster:
         self.lib.gut_frame_stats(self._h, C.byref(st))
         return {"num_intersections": st.num_intersections, "num_tiles": st.num_tiles,
                 "max_tile_list_length": st.max_tile_list_length, "kernel_launches": st.kernel_launches}
+
+    def measure_work(self, ray_origin, ray_direction):
+        """(tests, hits) of the last forward's compositing walk -- roofline accounting only."""
+        t, hh = C.c_uint64(0), C.c_uint64(0)
+        rc = self.lib.gut_measure_work(self._h, self._stream(), _ptr(ray_origin.contiguous()), _ptr(ray_direction.contiguous()),
+                                       C.byref(t), C.byref(hh))
+        if rc != 0:
+            self._raise(rc)
+        return t.value, hh.value
 
     # ---- host-buffer entry points (end-to-end path) --------------------------------------------------------
     def trace_host(self, num_active_features, particle_density, particle_radiance, h_ray_origin, h_ray_direction, sensor,

@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py -- 3DGUT fwd+bwd throughput (Mpix/s) of the B200-native rasteriser.
+
+Workload (BASELINE.json metric "3DGUT fwd+bwd Mpix/s at 3M Gaussians, 1/2/4/8 B200", configs[2]):
+one training step = forward + backward of a batch of 8 synthetic 1237x822 pinhole views over a replicated
+set of 3M random-init Gaussians (SH degree 3), the views sharded over the N ranks, per-Gaussian gradients
+summed with one NCCL allreduce.  Total work per step is fixed, so scaling is "strong".
+
+    python bench.py --gpus 1 --steps K --warmup W            # this implementation
+    python bench.py --impl reference ...                     # CPU oracle port on the host cores (the reference has no CPU path)
+
+Prints ONE JSON line on rank 0 (see the task contract for the keys).
+"""
+import argparse
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "3dgut_fwd_bwd_mpix_per_s"
+UNIT = "Mpix/s"
+W_IMG, H_IMG = 1237, 822
+N_VIEWS = 8
+SPH_DEGREE = 3
+# algorithmic work per unit (restated in DESIGN.md)
+FLOP_FWD_TEST, FLOP_FWD_HIT = 71.0, 32.0
+FLOP_BWD_TEST, FLOP_BWD_HIT = 100.0, 250.0
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--particles", type=int, default=3_000_000, help="override only for smoke runs; the metric is quoted at 3M")
+    p.add_argument("--views", type=int, default=N_VIEWS)
+    p.add_argument("--width", type=int, default=W_IMG)
+    p.add_argument("--height", type=int, default=H_IMG)
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-sample-tiles", type=int, default=24)
+    return p.parse_args()
+
+
+def workload_config(args, world):
+    return {
+        "workload": f"3DGUT training step: {args.particles} random-init Gaussians (S-init), SH deg {SPH_DEGREE}, batch of {args.views} "
+                    f"pinhole views {args.width}x{args.height}, k_buffer_size=0, views sharded over {world} GPU(s), "
+                    f"NCCL allreduce of [N,12]+[N,48] fp32 gradients",
+        "particles": args.particles, "views_per_step": args.views, "width": args.width, "height": args.height,
+        "sph_degree": SPH_DEGREE, "parallelism": f"view-sharded dp{world}, particles replicated",
+        "l2_policy": "inputs larger than L2 (particle parameters + record stream > 126 MB per view)",
+    }
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.sm_max = None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.sm_max = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            }
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.05)
+        except Exception as e:  # NVML unavailable: report that instead of failing the bench
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU oracle arm (cpu_baseline of our line, and the whole --impl reference line)
+# ------------------------------------------------------------------------------------------------------
+def cpu_oracle_sample(args, n_tiles_sample, repeats=1):
+    """fwd+bwd of ONE view of the workload with the C oracle on all host cores, compositing restricted to a
+    sample of tiles (projection, binning and SH backward run over the whole frame).  Returns Mpix/s extrapolated
+    as sample_pixels / (t_composite_sample + t_whole_frame_stages * sample_pixels / frame_pixels)."""
+    from oracle import gut_oracle as O
+    from tests.helpers import abi, camera_of, syn
+
+    import ctypes as C
+
+    cfg = abi.default_config()
+    w, h, n = args.width, args.height, args.particles
+    scene = syn.make_scene(n, 3, seed=1003)
+    view = syn.make_view(w, h, k=0, n_views=args.views)
+    cam = camera_of(view)
+    d12 = syn.pack_density(scene).numpy()
+    sph = scene["features"].numpy()
+    ro, rd = view["rays_ori"].numpy(), view["rays_dir"].numpy()
+    gx, gy = (w + 15) // 16, (h + 15) // 16
+    rng = np.random.default_rng(0)
+    tiles = np.sort(rng.choice(gx * gy, size=min(n_tiles_sample, gx * gy), replace=False)).astype(np.uint32)
+    tx, ty = tiles % gx, tiles // gx
+    sample_pixels = int(((np.minimum((tx + 1) * 16, w) - tx * 16) * (np.minimum((ty + 1) * 16, h) - ty * 16)).sum())
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        proj = O.project(cfg, cam, d12, sph, w, h, SPH_DEGREE)
+        bins = O.bin_and_sort(cfg, w, h, proj)
+        t1 = time.perf_counter()
+        out = O.render(cfg, cam, d12, proj["features"], ro, rd, w, h, bins["tile_ranges"], bins["sorted_values"], tile_list=tiles)
+        out.update(proj=proj, bins=bins)
+        t2 = time.perf_counter()
+        O.backward(cfg, cam, d12, sph, ro, rd, w, h, SPH_DEGREE, out, rgba_grad, dist_grad, tile_list=tiles)
+        t3 = time.perf_counter()
+        whole, comp = (t1 - t0), (t3 - t1)
+        frac = sample_pixels / float(w * h)
+        est = sample_pixels / (comp + whole * frac) / 1e6
+        rec = {"mpix_s": est, "t_whole_frame_stages_s": whole, "t_composite_sample_s": comp, "tests": out["tests"], "M": bins["M"]}
+        if best is None or rec["mpix_s"] > best["mpix_s"]:
+            best = rec
+    cores = os.cpu_count() or 1
+    best["cores"] = cores
+    best["sample"] = (f"one {w}x{h} view of the workload: projection+binning+SH-backward over all {n} particles, compositing fwd+bwd on "
+                      f"{len(tiles)} random tiles ({sample_pixels} px) with OpenMP on {cores} host threads; extrapolated per pixel")
+    return best
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    vals = []
+    last = None
+    for _ in range(max(1, args.warmup // 3)):
+        cpu_oracle_sample(args, max(4, args.cpu_sample_tiles // 4))
+    t_begin = time.perf_counter()
+    for _ in range(args.steps):
+        last = cpu_oracle_sample(args, args.cpu_sample_tiles)
+        vals.append(last["mpix_s"])
+    total = time.perf_counter() - t_begin
+    v = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference ships no CPU implementation of this path (SURVEY.md 8c); this arm times the C oracle port of it",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from tests.helpers import SyntheticGaussians, abi, camera_of, make_batch, make_conf, syn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    native = importlib.import_module("3dgrut_b200.native")
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    pkg = importlib.import_module("3dgrut_b200")
+
+    n, w, h = args.particles, args.width, args.height
+    P = w * h
+    scene = syn.make_scene(n, 3, seed=1003)
+    d12 = syn.pack_density(scene).to(dev)
+    sph = scene["features"].to(dev)
+    my_view_ids = gdist.shard_views(args.views, rank, world)
+    host_views = {k: syn.make_view(w, h, k=k, n_views=args.views) for k in my_view_ids}
+    views, upstream, host_up = [], [], []
+    for k in my_view_ids:
+        hv = host_views[k]
+        views.append({"rays_ori": hv["rays_ori"].to(dev), "rays_dir": hv["rays_dir"].to(dev), "camera": camera_of(hv)})
+        g = torch.Generator().manual_seed(2000 + k)
+        rg = torch.rand((h, w, 4), generator=g) * 2 - 1
+        dg = (torch.rand((h, w, 1), generator=g) * 2 - 1) * 0.01
+        host_up.append((rg.pin_memory(), dg.pin_memory()))
+        upstream.append((rg.to(dev), dg.to(dev)))
+
+    cfg = abi.default_config(enable_kernel_timings=1)
+    raster = native.SplatRaster(cfg, device=dev)
+    exchange = gdist.GradientExchange(n, sph.shape[1], dev, world=world)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step():
+        return gdist.training_step(raster, exchange, views, SPH_DEGREE, d12, sph, upstream)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    raster.stage_times()  # drop warm-up timings
+    launches0 = raster.frame_stats()["kernel_launches"]
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    launches = raster.frame_stats()["kernel_launches"] - launches0
+    stage_ms = raster.stage_times()
+    stats = raster.frame_stats()
+    value = args.views * P * args.steps / (ms_total * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (rank 0's views) ----------------------------------------------
+    tests = hits = 0
+    m_sum = 0
+    for v in views:
+        raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
+        t_, h_ = raster.measure_work(v["rays_ori"], v["rays_dir"])
+        tests += t_; hits += h_
+        m_sum += raster.frame_stats()["num_intersections"]
+    nv = max(1, len(views))
+    tests_v, hits_v, m_v = tests / nv, hits / nv, m_sum / nv
+    clk = clocks["sm_mhz"] or 1965.0
+    fp32_peak = 148 * 128 * 2 * clk * 1e6 / 1e12
+    hbm_peak = 6555.2
+    try:
+        hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    vis_frac = 1.0
+    stages = []
+
+    def add_stage(tag, bound, work, unit_scale, peak, unit, what):
+        ms = stage_ms.get(tag)
+        if ms is None or ms <= 0:
+            return
+        ach = work / (ms * 1e-3) / unit_scale
+        stages.append({"stage": tag, "bound": bound, "ms_per_launch": ms, "achieved": ach, "peak": peak, "unit": unit,
+                       "frac": ach / peak, "algorithmic_work": what})
+
+    add_stage("render::project", "hbm", n * (48 + 56 + 192 * vis_frac), 1e9, hbm_peak, "GB/s", "48+56+192 B/particle")
+    add_stage("render::expand", "hbm", n * 44 + m_v * 8, 1e9, hbm_peak, "GB/s", "44 B/particle + 8 B/intersection")
+    add_stage("render::sort", "hbm", m_v * (8 + 4 + 96 + 60), 1e9, hbm_peak, "GB/s",
+              "8 B bucket read + 4 B index + 96 B record write + 60 B parameter gather per intersection")
+    add_stage("render::render", "fp32", tests_v * FLOP_FWD_TEST + hits_v * FLOP_FWD_HIT, 1e12, fp32_peak, "TFLOP/s",
+              "71 FLOP/test + 32 FLOP/hit")
+    add_stage("render-backward::render", "fp32", tests_v * FLOP_BWD_TEST + hits_v * FLOP_BWD_HIT, 1e12, fp32_peak, "TFLOP/s",
+              "100 FLOP/test + 250 FLOP/hit")
+    add_stage("render-backward::project", "hbm", n * (36 + 192), 1e9, hbm_peak, "GB/s", "36+192 B/particle")
+    dominant = max(stages, key=lambda s: s["ms_per_launch"]) if stages else None
+    roofline = None
+    if dominant:
+        roofline = {"kernel": dominant["stage"], "bound": dominant["bound"], "achieved": dominant["achieved"], "peak": dominant["peak"],
+                    "unit": dominant["unit"], "frac": dominant["frac"], "traffic": None, "ms_per_launch": dominant["ms_per_launch"],
+                    "peak_source": (f"derived: 148 SM x 128 lanes x 2 x {clk:.0f} MHz sampled under load (FP32 is not in MEASURED_PEAKS.json)"
+                                    if dominant["bound"] == "fp32" else peak_src),
+                    "note": "compositing is FP32-issue bound, not HBM or tensor bound (no stage is a dense contraction); "
+                            "HBM-bound stages are listed in roofline_stages"}
+
+    # ---- end to end through the public Tracer API with host inputs --------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        tracer = pkg.Tracer(make_conf())
+        gauss = SyntheticGaussians(scene, dev, n_active_features=SPH_DEGREE, requires_grad=True)
+        pinned = []
+        for k in my_view_ids:
+            hv = host_views[k]
+            pinned.append({kk: (vv.pin_memory() if hasattr(vv, "pin_memory") else vv) for kk, vv in hv.items()})
+        out_host = torch.empty((h, w, 4), dtype=torch.float32).pin_memory()
+        h2d = d2h = 0
+
+        def e2e_step():
+            nonlocal h2d, d2h
+            h2d = d2h = 0
+            for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
+                p.grad = None
+            checksum = None
+            for pv, (rg_h, dg_h) in zip(pinned, host_up):
+                dv = dict(pv)
+                for kk in ("rays_ori", "rays_dir", "T_to_world"):
+                    dv[kk] = pv[kk].to(dev, non_blocking=True)
+                    h2d += pv[kk].numel() * 4
+                rg = rg_h.to(dev, non_blocking=True); dg = dg_h.to(dev, non_blocking=True)
+                h2d += (rg_h.numel() + dg_h.numel()) * 4
+                o = tracer.render(gauss, make_batch(dv, dev), train=True)
+                loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
+                loss.backward()
+                out_host[..., :3].copy_(o["pred_rgb"][0], non_blocking=True)
+                out_host[..., 3:].copy_(o["pred_opacity"][0], non_blocking=True)
+                d2h += out_host.numel() * 4
+                checksum = loss.detach() if checksum is None else checksum + loss.detach()
+            if world > 1:
+                for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
+                    dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
+            if checksum is not None:
+                float(checksum.item())  # device->host read of the step's scalar result
+                d2h += 4
+
+        for _ in range(min(args.warmup, 3)):
+            e2e_step()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        k_e2e = args.steps
+        for _ in range(k_e2e):
+            e2e_step()
+        f1.record()
+        barrier()
+        ms = f0.elapsed_time(f1)
+        tt = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = {"value": args.views * P * k_e2e / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h),
+               "path": "Tracer.render + autograd backward per view; rays, pose and upstream gradients copied from pinned host memory, "
+                       "rendered RGBA and the scalar loss read back every step; particles stay device resident (they are the model)"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            c = cpu_oracle_sample(args, args.cpu_sample_tiles)
+            cpu_baseline = {"value": c["mpix_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"]}
+        except Exception as e:
+            cpu_baseline = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e!r}"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
+            "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
+                              "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P},
+            "stage_ms": stage_ms,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -232,6 +232,14 @@ typedef struct GutFrameStats {
 } GutFrameStats;
 GUT_API int gut_frame_stats(GutHandle* h, GutFrameStats* out);
 
+/*
+ * Instrumented re-run of the compositing walk of the last forward (same rays): returns the number of
+ * ray x particle tests and of accepted hits.  These are the units the FP32 roofline of K4/K5 is
+ * expressed in; not part of the render path, never called inside a timed region.
+ */
+GUT_API int gut_measure_work(GutHandle* h, void* stream, const float* d_ray_origin, const float* d_ray_direction,
+                             uint64_t* num_tests, uint64_t* num_hits);
+
 GUT_API const char* gut_last_error(GutHandle* h);
 GUT_API int         gut_abi_version(void);
 /* struct sizes as compiled into the library, so a foreign-language binding can verify its mirror of the structs */

@@ -762,6 +762,8 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                                   const float* ray_ori, const float* ray_dir,
                                   const uint32_t* tile_ranges, const uint32_t* sorted_idx,
                                   float* rgba, float* dist, float* hits, uint64_t* tests_out,
+                                  const uint32_t* tile_list /* optional: render only these tiles (bounded CPU-baseline sample) */,
+                                  uint32_t n_tile_list,
                                   float* margin /* optional [H,W]: smallest relative distance of any accept/kill decision of the
                                                    ray to its threshold -- pixels with a tiny margin may legitimately differ between two
                                                    fp32 implementations by one whole hit; the parity tests treat them separately */) {
@@ -769,8 +771,10 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
     const frame_consts f = make_frame(cam, W, H);
     const int K = cfg->k_buffer_size;
     uint64_t tests = 0;
+    const int64_t n_work = tile_list ? (int64_t)n_tile_list : (int64_t)f.gx * f.gy;
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : tests)
-    for (int64_t tile = 0; tile < (int64_t)f.gx * f.gy; ++tile) {
+    for (int64_t work = 0; work < n_work; ++work) {
+        const int64_t tile = tile_list ? (int64_t)tile_list[work] : work;
         const uint32_t tx = (uint32_t)(tile % f.gx), ty = (uint32_t)(tile / f.gx);
         const uint32_t r0 = tile_ranges[2 * tile], r1 = tile_ranges[2 * tile + 1];
         for (uint32_t py = ty * TILE; py < ty * TILE + TILE && py < H; ++py)
@@ -867,12 +871,15 @@ ORACLE_API void gut_oracle_render_bwd(const GutConfig* cfg, const GutCamera* cam
                                       const float* ray_ori, const float* ray_dir,
                                       const uint32_t* tile_ranges, const uint32_t* sorted_idx,
                                       const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
-                                      double* density_grad /* [N,12] += */, double* feature_grad /* [N,3] += */) {
+                                      double* density_grad /* [N,12] += */, double* feature_grad /* [N,3] += */,
+                                      const uint32_t* tile_list, uint32_t n_tile_list) {
     (void)N;
     const frame_consts f = make_frame(cam, W, H);
     const float minT = cfg->min_transmittance;
+    const int64_t n_work = tile_list ? (int64_t)n_tile_list : (int64_t)f.gx * f.gy;
 #pragma omp parallel for schedule(dynamic, 1)
-    for (int64_t tile = 0; tile < (int64_t)f.gx * f.gy; ++tile) {
+    for (int64_t work = 0; work < n_work; ++work) {
+        const int64_t tile = tile_list ? (int64_t)tile_list[work] : work;
         const uint32_t tx = (uint32_t)(tile % f.gx), ty = (uint32_t)(tile / f.gx);
         const uint32_t r0 = tile_ranges[2 * tile], r1 = tile_ranges[2 * tile + 1];
         for (uint32_t py = ty * TILE; py < ty * TILE + TILE && py < H; ++py)

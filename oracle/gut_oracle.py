@@ -103,7 +103,14 @@ def bin_and_sort(cfg, W, H, proj):
             "sorted_values": svals, "tile_ranges": ranges}
 
 
-def render(cfg, cam, density12, features, ray_ori, ray_dir, W, H, tile_ranges, sorted_values):
+def _tiles(tile_list):
+    if tile_list is None:
+        return C.c_void_p(0), C.c_uint32(0), None
+    tl = np.ascontiguousarray(tile_list, dtype=np.uint32)
+    return _p(tl), C.c_uint32(tl.shape[0]), tl
+
+
+def render(cfg, cam, density12, features, ray_ori, ray_dir, W, H, tile_ranges, sorted_values, tile_list=None):
     density12 = _f32(density12); features = _f32(features)
     ray_ori = _f32(ray_ori).reshape(-1, 3); ray_dir = _f32(ray_dir).reshape(-1, 3)
     rgba = np.zeros((H, W, 4), np.float32)
@@ -111,13 +118,14 @@ def render(cfg, cam, density12, features, ray_ori, ray_dir, W, H, tile_ranges, s
     hits = np.zeros((H, W), np.float32)
     tests = C.c_uint64(0)
     margin = np.full((H, W), np.inf, np.float32)
+    tl_p, tl_n, _keep = _tiles(tile_list)
     lib().gut_oracle_render(C.byref(cfg), C.byref(cam), C.c_uint32(density12.shape[0]), C.c_uint32(W), C.c_uint32(H),
                             _p(density12), _p(features), _p(ray_ori), _p(ray_dir), _p(tile_ranges), _p(sorted_values),
-                            _p(rgba), _p(dist), _p(hits), C.byref(tests), _p(margin))
+                            _p(rgba), _p(dist), _p(hits), C.byref(tests), tl_p, tl_n, _p(margin))
     return {"rgba": rgba, "dist": dist, "hits": hits, "tests": tests.value, "margin": margin}
 
 
-def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree):
+def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, tile_list=None):
     """Whole forward (K1..K4) as GUTRenderer::renderForward sequences it (src/gutRenderer.cu:241-398)."""
     proj = project(cfg, cam, density12, sph, W, H, sph_degree)
     bins = bin_and_sort(cfg, W, H, proj)
@@ -125,12 +133,13 @@ def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree):
         out = {"rgba": np.zeros((H, W, 4), np.float32), "dist": np.full((H, W), 1e6, np.float32),
                "hits": np.zeros((H, W), np.float32), "tests": 0, "margin": np.full((H, W), np.inf, np.float32)}
     else:
-        out = render(cfg, cam, density12, proj["features"], ray_ori, ray_dir, W, H, bins["tile_ranges"], bins["sorted_values"])
+        out = render(cfg, cam, density12, proj["features"], ray_ori, ray_dir, W, H, bins["tile_ranges"], bins["sorted_values"],
+                     tile_list=tile_list)
     out.update(proj=proj, bins=bins, visibility=proj["visibility"])
     return out
 
 
-def backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, fwd, rgba_grad, dist_grad):
+def backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, fwd, rgba_grad, dist_grad, tile_list=None):
     """K5 + K6 (src/gutRenderer.cu:400-497) for k_buffer_size == 0. Returns ([N,12], [N,ncoef*3]) float32."""
     assert cfg.k_buffer_size == 0, "oracle backward implements the K=0 path (gutKBufferRenderer.cuh:294-386)"
     density12 = _f32(density12); sph = _f32(sph)
@@ -143,10 +152,11 @@ def backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, fwd, 
     ray_ori = _f32(ray_ori).reshape(-1, 3); ray_dir = _f32(ray_dir).reshape(-1, 3)
     rgba_grad = _f32(rgba_grad); dist_grad = _f32(dist_grad)
     proj, bins = fwd["proj"], fwd["bins"]
+    tl_p, tl_n, _keep = _tiles(tile_list)
     lib().gut_oracle_render_bwd(C.byref(cfg), C.byref(cam), C.c_uint32(N), C.c_uint32(W), C.c_uint32(H), _p(density12),
                                 _p(proj["features"]), _p(ray_ori), _p(ray_dir), _p(bins["tile_ranges"]),
                                 _p(bins["sorted_values"]), _p(fwd["rgba"]), _p(rgba_grad), _p(fwd["dist"]), _p(dist_grad),
-                                _p(dg), _p(fg))
+                                _p(dg), _p(fg), tl_p, tl_n)
     fg32 = fg.astype(np.float32)
     lib().gut_oracle_project_bwd(C.byref(cfg), C.byref(cam), C.c_uint32(N), C.c_int(sph_degree), C.c_uint32(W), C.c_uint32(H),
                                  _p(density12), _p(proj["tiles_count"]), _p(proj["features"]), _p(fg32), _p(sg))
