@@ -1,0 +1,52 @@
+#!/usr/bin/env python
+"""Turn the artefacts of scripts/profile.sh into the committed summaries under profiles/.
+usage: scripts/ncu_summarise.py <tag>      (reads gpurun_out/launches_<tag>.csv and gpurun_out/prof_<tag>.ncu-rep)"""
+import collections, csv, io, os, subprocess, sys
+
+tag = sys.argv[1]
+out_dir = "profiles"
+os.makedirs(out_dir, exist_ok=True)
+
+# ---- launch list -> per-kernel totals and shares ------------------------------------------------------
+lines = [l for l in open(f"gpurun_out/launches_{tag}.csv") if l.startswith('"')]
+agg = collections.OrderedDict()
+for x in csv.DictReader(io.StringIO("".join(lines))):
+    v = float(x["Metric Value"].replace(",", ""))
+    u = x["Metric Unit"]
+    v = v / 1e3 if u == "ns" else (v * 1e3 if u == "ms" else v)
+    k = x["Kernel Name"].split("(")[0]
+    a = agg.setdefault(k, [0, 0.0])
+    a[0] += 1; a[1] += v
+tot = sum(v[1] for v in agg.values())
+with open(f"{out_dir}/launches_{tag}.md", "w") as f:
+    f.write(f"# ncu launch list, {tag}\n\n`ncu --metrics gpu__time_duration.sum --clock-control none` over `python bench.py --steps 2 --warmup 3 "
+            "--no-e2e --no-cpu-baseline` (cold-cache, serialised: compare shares).\n\n| kernel | launches | total us | avg us | share |\n|---|---|---|---|---|\n")
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        f.write(f"| `{k}` | {v[0]} | {v[1]:.1f} | {v[1]/v[0]:.1f} | {v[1]/tot:.3f} |\n")
+
+# ---- full capture -> selected raw metrics per kernel ---------------------------------------------------
+rep = f"gpurun_out/prof_{tag}.ncu-rep"
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units = rows[0], rows[1]
+want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "smsp__issue_active.avg.pct", "smsp__inst_executed.sum", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sector_hit_rate.pct", "launch__registers_per_thread",
+        "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "launch__grid_size", "launch__block_size",
+        "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
+        "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
+with open(f"{out_dir}/ncu_full_{tag}.md", "w") as f:
+    f.write(f"# ncu --set full, {tag}\n\n`ncu --set full --clock-control none --import-source on -k regex:gut_` over one view of "
+            "`python bench.py --steps 1 --warmup 3 --views 1 --no-e2e --no-cpu-baseline` (3M Gaussians, 1237x822).\n")
+    for r in rows[2:]:
+        name = r[hdr.index("Kernel Name")].split("(")[0]
+        f.write(f"\n## `{name}`\n\n| metric | value | unit |\n|---|---|---|\n")
+        for w in want:
+            if w in hdr:
+                i = hdr.index(w)
+                f.write(f"| {w} | {r[i]} | {units[i]} |\n")
+print("wrote", f"{out_dir}/launches_{tag}.md", f"{out_dir}/ncu_full_{tag}.md")
