@@ -1,0 +1,94 @@
+"""World-size-2 CPU test (gloo) of the view-sharded data-parallel plumbing (3dgrut_b200/dist.py):
+views are split round-robin, each rank accumulates the gradients of its views in place, one sum-allreduce closes the
+step -- the result must equal the single-process sum over all views.  The rasteriser itself is replaced by a
+deterministic stand-in with the SplatRaster.trace / trace_bwd signature (no GPU here)."""
+import importlib
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+gdist = importlib.import_module("3dgrut_b200.dist")
+
+N, NSPH, NVIEWS, H, W = 257, 48, 5, 6, 7
+
+
+class FakeRaster:
+    """Stand-in with the SplatRaster call signature: gradients are a fixed linear function of the view's upstream gradient."""
+
+    def trace(self, frame, deg, density, radiance, ray_o, ray_d, ray_t, camera):
+        rgba = ray_o.sum() * torch.ones((H, W, 4)); d = torch.ones((H, W, 1))
+        return rgba, d, torch.zeros((H, W, 1)), torch.zeros((density.shape[0], 1))
+
+    def trace_bwd(self, frame, deg, density, radiance, ray_o, ray_d, ray_t, camera, ts0, ts1, p0, p1, rgba, rgba_grad, d, d_grad,
+                  out_density_grad=None, out_radiance_grad=None, accumulate=False):
+        g1 = rgba_grad.sum() * density + d_grad.sum()
+        g2 = rgba_grad.mean() * radiance
+        if accumulate:
+            out_density_grad += g1; out_radiance_grad += g2
+        else:
+            out_density_grad.copy_(g1); out_radiance_grad.copy_(g2)
+        return out_density_grad, out_radiance_grad
+
+
+def _data():
+    g = torch.Generator().manual_seed(0)
+    density = torch.randn((N, 12), generator=g); radiance = torch.randn((N, NSPH), generator=g)
+    views = [{"rays_ori": torch.full((1, H, W, 3), float(k)), "rays_dir": torch.ones((1, H, W, 3)), "camera": None} for k in range(NVIEWS)]
+    ups = [(torch.randn((H, W, 4), generator=g), torch.randn((H, W, 1), generator=g)) for _ in range(NVIEWS)]
+    return density, radiance, views, ups
+
+
+def _step(rank, world):
+    density, radiance, views, ups = _data()
+    ids = gdist.shard_views(NVIEWS, rank, world)
+    ex = gdist.GradientExchange(N, NSPH, "cpu", world=world)
+    gdist.training_step(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids])
+    return ex.density_grad.clone(), ex.radiance_grad.clone()
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g1, g2 = _step(rank, world)
+        q.put((rank, g1.numpy(), g2.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_views_partition():
+    for world in (1, 2, 3, 4, 8):
+        got = sorted(v for r in range(world) for v in gdist.shard_views(8, r, world))
+        assert got == list(range(8))
+        sizes = [len(gdist.shard_views(8, r, world)) for r in range(world)]
+        assert max(sizes) - min(sizes) <= 1
+
+
+@pytest.mark.timeout(120)
+def test_two_rank_step_equals_single_process():
+    ref1, ref2 = _step(0, 1)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs: p.start()
+    res = [q.get(timeout=90) for _ in procs]
+    for p in procs: p.join(30)
+    assert all(p.exitcode == 0 for p in procs)
+    for _, g1, g2 in res:   # every rank holds the full sum after the allreduce
+        torch.testing.assert_close(torch.from_numpy(g1), ref1, rtol=1e-5, atol=1e-4)
+        torch.testing.assert_close(torch.from_numpy(g2), ref2, rtol=1e-5, atol=1e-5)
+
+
+def test_rank_without_views_contributes_zero():
+    # more ranks than views: the empty rank's buffers must be zeroed before the allreduce
+    density, radiance, views, ups = _data()
+    ex = gdist.GradientExchange(N, NSPH, "cpu", world=1)
+    ex.density_grad.fill_(3.0); ex.radiance_grad.fill_(4.0)
+    gdist.training_step(FakeRaster(), ex, [], 3, density, radiance, [])
+    assert float(ex.density_grad.abs().max()) == 0.0 and float(ex.radiance_grad.abs().max()) == 0.0
