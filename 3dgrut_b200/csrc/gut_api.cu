@@ -42,7 +42,7 @@ struct GutHandle {
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
-    DevBuf entries, scratch, sorted_idx, records, quats;
+    DevBuf entries, scratch, sorted_idx, records, records_bwd;
     // host-buffer mode (gut_*_host)
     DevBuf h_ray_ori, h_ray_dir, h_rgba, h_dist, h_hits, h_rgba_grad, h_dist_grad;
     uint32_t* pinned_stats = nullptr;  // [2] = {M, max tile list}
@@ -270,7 +270,7 @@ void gut_destroy(GutHandle* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->feature_grad, &h->tile_hist,
-                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->records, &h->quats,
+                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->records, &h->records_bwd,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
     if (h->pinned_stats) cudaFreeHost(h->pinned_stats);
@@ -339,7 +339,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         GUT_CUDA(h, ensure(h->entries, M * 8, s, 1.25f));
         GUT_CUDA(h, ensure(h->sorted_idx, M * 4, s, 1.25f));
         GUT_CUDA(h, ensure(h->records, M * sizeof(GutRecord), s, 1.25f));
-        GUT_CUDA(h, ensure(h->quats, M * 16, s, 1.25f));
+        GUT_CUDA(h, ensure(h->records_bwd, M * sizeof(GutRecordBwd), s, 1.25f));
         if (max_list > 4096) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
         {
             StageTimer t(h, ST_EMIT, s);
@@ -350,7 +350,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
             StageTimer t(h, ST_SORT, s);
             GUT_CUDA(h, gut_launch_tile_sort(fr, N, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p, d_density,
                                              (const float4*)h->features.p, (uint32_t*)h->sorted_idx.p, (GutRecord*)h->records.p,
-                                             (float4*)h->quats.p, s));
+                                             (GutRecordBwd*)h->records_bwd.p, s));
             h->launches += 1;
         }
         {
@@ -412,7 +412,7 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
     if (h->fwd_M > 0) {
         StageTimer t(h, ST_BWD_RENDER, s);
         GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p,
-                                               (const float4*)h->quats.p, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
+                                               (const GutRecordBwd*)h->records_bwd.p, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
                                                d_density_grad, (float4*)h->feature_grad.p, s));
         h->launches += 1;
     }

@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(SORT_THREADS) gut_tile_sort_kernel(GutFrame fr
                                                                      const float4* __restrict__ density12,
                                                                      const float4* __restrict__ features,
                                                                      uint32_t* __restrict__ sorted_idx, GutRecord* __restrict__ records,
-                                                                     float4* __restrict__ quats) {
+                                                                     GutRecordBwd* __restrict__ records_bwd) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf_a = reinterpret_cast<uint64_t*>(smem_raw);
     uint64_t* buf_b = buf_a + SORT_SMEM_CAP;
@@ -218,13 +218,18 @@ __global__ void __launch_bounds__(SORT_THREADS) gut_tile_sort_kernel(GutFrame fr
         float3 c0, c1, c2;
         quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);  // columns of R == rows of R^T
         const float ix = 1.0f / r2.x, iy = 1.0f / r2.y, iz = 1.0f / r2.z;
+        const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;  // rows of ms = diag(1/s) R^T
+        const float3 v = fr.cam_centre - f3(r0.x, r0.y, r0.z);  // frame origin - position
         float4* out = reinterpret_cast<float4*>(records + b0 + i);
-        out[0] = make_float4(c0.x * ix, c0.y * ix, c0.z * ix, r0.x);
-        out[1] = make_float4(c1.x * iy, c1.y * iy, c1.z * iy, r0.y);
-        out[2] = make_float4(c2.x * iz, c2.y * iz, c2.z * iz, r0.z);
+        out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
+        out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
+        out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
         out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
         out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p));
-        quats[b0 + i] = q;
+        float4* outb = reinterpret_cast<float4*>(records_bwd + b0 + i);
+        outb[0] = q;
+        outb[1] = make_float4(ix, iy, iz, 0.0f);
+        outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
     }
 }
 
@@ -268,7 +273,7 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32_t* tile_start, uint2* entries, uint2* scratch,
                                  const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
-                                 float4* quats, cudaStream_t stream) {
+                                 GutRecordBwd* records_bwd, cudaStream_t stream) {
     const size_t smem = 2 * SORT_SMEM_CAP * sizeof(uint64_t);
     static bool configured = false;
     if (!configured) {
@@ -278,7 +283,7 @@ cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32
     }
     gut_tile_sort_kernel<<<frame.num_tiles, SORT_THREADS, smem, stream>>>(frame, N, tile_start, entries, scratch,
                                                                          reinterpret_cast<const float4*>(density12), features,
-                                                                         sorted_idx, records, quats);
+                                                                         sorted_idx, records, records_bwd);
     return cudaGetLastError();
 }
 

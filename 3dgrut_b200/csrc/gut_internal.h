@@ -20,17 +20,27 @@ struct GutFrame {
 
 // One sorted (tile, particle) intersection, expanded for the compositing kernels ("record stream").
 // 80 B = 5 x float4, written in sorted order by the tile-sort kernel so a batch is one contiguous
-// cp.async.bulk copy.  ms = diag(1/scale) * R^T : the map from world offsets to the particle's
-// canonical (unit-Gaussian) frame; rows ms0..ms2.
+// cp.async.bulk copy.  ms = diag(1/scale) * R^T maps world offsets to the particle's canonical
+// (unit-Gaussian) frame; go = ms * (frame origin - position) is the canonical ray origin of every ray that
+// starts at the frame origin (GutFrame::cam_centre) -- all of them for pinhole / fisheye ray bundles --
+// so a ray/particle test needs ONE mat-vec (the direction), not two.
 struct __align__(16) GutRecord {
-    float ms0x, ms0y, ms0z, px;     // row 0 of ms | position.x
-    float ms1x, ms1y, ms1z, py;     // row 1       | position.y
-    float ms2x, ms2y, ms2z, pz;     // row 2       | position.z
+    float ms0x, ms0y, ms0z, gox;    // row 0 of ms | go.x
+    float ms1x, ms1y, ms1z, goy;    // row 1       | go.y
+    float ms2x, ms2y, ms2z, goz;    // row 2       | go.z
     float sx, sy, sz, density;      // scale       | density
     float fr, fg, fb;               // max(feature, 0)
     uint32_t idx;                   // particle index
 };
 static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
+
+// Backward-only side stream, same order as the records (48 B = 3 x float4).
+struct __align__(16) GutRecordBwd {
+    float qw, qx, qy, qz;           // quaternion (w,x,y,z)
+    float isx, isy, isz, pad0;      // 1 / scale
+    float px, py, pz, pad1;         // position
+};
+static_assert(sizeof(GutRecordBwd) == 48, "backward record must be 3 float4");
 
 // Device buffers of the per-particle projection stage (K1 outputs).
 struct GutProjBuffers {
@@ -61,7 +71,7 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 // per-tile sort of (depth, idx) + expansion into the record stream; scratch = alt buffer for oversize tiles
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32_t* tile_start, uint2* entries, uint2* scratch,
                                  const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
-                                 float4* quats, cudaStream_t stream);
+                                 GutRecordBwd* records_bwd, cudaStream_t stream);
 
 // debug/parity: rebuild the reference-shaped sorted key array and tile ranges
 cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_start, const uint32_t* sorted_idx, const float* depth,
@@ -72,7 +82,7 @@ cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const
                               unsigned long long* counters /* non-null: count tests/hits instead of rendering */, cudaStream_t stream);
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
-                                       const GutRecord* records, const float4* quats, const float* ray_ori, const float* ray_dir,
+                                       const GutRecord* records, const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
                                        float* density_grad, float4* feature_grad, cudaStream_t stream);
 

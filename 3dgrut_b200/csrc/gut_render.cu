@@ -6,14 +6,20 @@
 //   hit math gaussianParticle.hit / integrateHit (kernels/slang/models/gaussianParticles.slang:96-254),
 //   per-hit gradient processHitBwd (kernels/cuda/models/gaussianParticles.cuh:480-738).
 //
-// B200 design (DESIGN.md "K4/K5"):
+// B200 design (DESIGN.md "K4/K5").  Both kernels are bound by instruction issue (ncu: sm__throughput > 80 %, DRAM
+// < 2 %), so the design minimises SASS instructions per ray x particle test:
 //  * one CTA per 16x16 tile, 8 warps, each warp owns a compact 8x4 pixel block (more lanes hit the same
 //    particle than with the reference's 16x2 rows -> better SIMT efficiency in the divergent hit branch);
 //  * the tile's particles arrive as a contiguous 80-byte record stream written in sorted order by the
 //    tile-sort kernel, so a batch is ONE cp.async.bulk (TMA bulk copy, UBLKCP) into shared memory, completed
 //    on an mbarrier and double buffered against compute; no per-thread gathers, no quaternion->matrix math here;
-//  * records carry ms = diag(1/s) R^T so a ray/particle test is 2 mat-vecs, a cross product, one MUFU.RCP and one
-//    MUFU.EX2; normalisation (MUFU.RSQ) and the hit distance are computed only for accepted hits;
+//  * records carry ms = diag(1/s) R^T and go = ms (frame origin - position).  When every ray of the tile starts
+//    at the frame origin (true for pinhole and fisheye bundles; checked per CTA, bitwise) the canonical ray origin
+//    is go itself and a test is ONE mat-vec, a cross product, one MUFU.RCP and one MUFU.EX2; otherwise go is
+//    corrected by ms (ray origin - frame origin).  Normalisation and the hit distance are computed for accepted
+//    hits only, from the unnormalised direction: t = |u.go| sqrt(|s*u|^2) / |u|^2;
+//  * the translation unit is built with -use_fast_math like the reference (setup_3dgut.py:83): FTZ, MUFU
+//    division / sqrt / exp2;
 //  * backward: lanes that hit compute the 14 per-particle gradient values; the warp sums them with a 16-shuffle
 //    transpose-reduce (not 14 x 5 butterflies) and issues ONE red.global.add.f32 instruction per (warp, particle)
 //    -- and nothing at all when no lane of the warp hit (the reference reduces and does 14 atomics regardless,
@@ -76,6 +82,20 @@ GUT_D float kernel_response_grad(float g, float resp, float resp_grad) {
     return -0.5f * resp * resp_grad;
 }
 
+
+// ---- single-instruction MUFU wrappers (flush-to-zero, approximate: what -use_fast_math gives the reference) ----
+GUT_D float mufu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+GUT_D float mufu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+GUT_D float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+GUT_D float mufu_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+// response of the default degree-2 kernel as one FMUL + one MUFU.EX2: exp(-g/2) = 2^(-g log2(e) / 2)
+template <int DEG>
+GUT_D float response_of(float g2) {
+    if (DEG == 2) return mufu_ex2(g2 * -0.72134752044448170368f);
+    return kernel_response<DEG>(g2);
+}
+
 struct Ray {
     float3 o, d;
     float tmin, tmax;
@@ -120,28 +140,84 @@ GUT_D void thread_pixel(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_
     py = ty * GUT_TILE + (w >> 1) * 4 + (l >> 3);
 }
 
-// canonical-frame test shared by forward and backward
+// The records of a batch are walked four at a time; the tail of a tile's last batch is padded in shared memory with
+// records that can never be accepted (density 0), so the inner loop has no remainder handling.
+constexpr uint32_t WALK_UNROLL = 4;
+constexpr uint32_t ALIVE_CHECK = 16;  // records between two warp-wide "is any ray still alive" votes
+
+GUT_D void pad_batch_tail(float4* rec, uint32_t cnt) {
+    const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
+    const uint32_t i = cnt * 5 + threadIdx.x;
+    if (i < cnt_pad * 5) rec[i] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);  // rows (1,1,1), go = 0, scale 1, density 0
+}
+
+// canonical-frame test shared by forward and backward.  u = ms d (unnormalised canonical direction), go = canonical origin.
 struct Canon {
-    float3 gro, grdu, c;  // canonical ray origin, unnormalised canonical direction, grdu x gro
-    float l2, g2, resp, alpha;
+    float3 go, u, c;   // c = u x go
+    float l2, il2, g2, resp, araw;
 };
-template <int DEG>
-GUT_D bool particle_test(const GutConfig& cfg, const float4 A, const float4 B, const float4 Cm, const float4 S, float3 o, float3 d,
-                         Canon& k) {
-    const float3 v = f3(o.x - A.w, o.y - B.w, o.z - Cm.w);
-    k.gro = f3(A.x * v.x + A.y * v.y + A.z * v.z, B.x * v.x + B.y * v.y + B.z * v.z, Cm.x * v.x + Cm.y * v.y + Cm.z * v.z);
-    k.grdu = f3(A.x * d.x + A.y * d.y + A.z * d.z, B.x * d.x + B.y * d.y + B.z * d.z, Cm.x * d.x + Cm.y * d.y + Cm.z * d.z);
-    k.l2 = dot(k.grdu, k.grdu);
-    k.c = cross(k.grdu, k.gro);
-    k.g2 = __fdividef(dot(k.c, k.c), k.l2);  // |normalize(grdu) x gro|^2
-    k.resp = kernel_response<DEG>(k.g2);
-    k.alpha = fminf(cfg.max_alpha, k.resp * S.w);
-    return (k.resp > cfg.min_kernel_response) && (k.alpha > cfg.min_alpha);
+template <int DEG, bool UNIFORM>
+GUT_D bool particle_test(const GutConfig& cfg, const float4 A, const float4 B, const float4 Cm, const float density, const float3 d,
+                         const float3 dlt, Canon& k) {
+    k.go = f3(A.w, B.w, Cm.w);
+    if (!UNIFORM) {  // the ray does not start at the frame origin: go += ms (ray origin - frame origin)
+        k.go.x += A.x * dlt.x + A.y * dlt.y + A.z * dlt.z;
+        k.go.y += B.x * dlt.x + B.y * dlt.y + B.z * dlt.z;
+        k.go.z += Cm.x * dlt.x + Cm.y * dlt.y + Cm.z * dlt.z;
+    }
+    k.u = f3(A.x * d.x + A.y * d.y + A.z * d.z, B.x * d.x + B.y * d.y + B.z * d.z, Cm.x * d.x + Cm.y * d.y + Cm.z * d.z);
+    k.l2 = dot(k.u, k.u);
+    k.c = cross(k.u, k.go);
+    k.il2 = mufu_rcp(k.l2);
+    k.g2 = dot(k.c, k.c) * k.il2;  // |normalize(u) x go|^2
+    k.resp = response_of<DEG>(k.g2);
+    k.araw = k.resp * density;
+    // alpha = min(max_alpha, araw) > min_alpha  <=>  araw > min_alpha  (max_alpha > min_alpha is checked at gut_create)
+    return (k.resp > cfg.min_kernel_response) && (k.araw > cfg.min_alpha);
 }
 
 // ---------------------------------------------------------------------------------------------------
 // K4 forward
 // ---------------------------------------------------------------------------------------------------
+struct FwdState {
+    float T, D, cr, cg, cb;
+    uint32_t nhits, ntests;
+    bool alive;
+};
+
+template <int DEG, bool UNIFORM, bool COUNT>
+GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const Ray& ray, const float3 dlt, FwdState& st) {
+    const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
+    for (uint32_t j0 = 0; j0 < cnt_pad; j0 += ALIVE_CHECK) {
+        if (!__any_sync(0xffffffffu, st.alive)) break;
+        const uint32_t je = min(cnt_pad, j0 + ALIVE_CHECK);
+        for (uint32_t j = j0; j < je; j += WALK_UNROLL) {
+#pragma unroll
+            for (uint32_t q = 0; q < WALK_UNROLL; ++q) {
+                const float4* r = rec + 5 * (j + q);
+                const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
+                Canon k;
+                const bool accept = particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray.d, dlt, k);
+                if (COUNT && st.alive && (j + q) < cnt) st.ntests++;
+                if (accept && st.alive) {
+                    // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
+                    const float3 su = f3(S.x * k.u.x, S.y * k.u.y, S.z * k.u.z);
+                    const float t = fabsf(dot(k.u, k.go)) * k.il2 * mufu_sqrt(dot(su, su));
+                    if (t > ray.tmin && t < ray.tmax) {
+                        const float alpha = fminf(cfg.max_alpha, k.araw);
+                        const float4 F = r[4];
+                        const float w = alpha * st.T;
+                        st.D = fmaf(t, w, st.D);
+                        st.T *= (1.0f - alpha);
+                        if (w > 0.0f) { st.cr = fmaf(F.x, w, st.cr); st.cg = fmaf(F.y, w, st.cg); st.cb = fmaf(F.z, w, st.cb); st.nhits++; }
+                        if (st.T < cfg.min_transmittance) st.alive = false;
+                    }
+                }
+            }
+        }
+    }
+}
+
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
@@ -160,9 +236,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
     const bool inside = px < fr.width && py < fr.height;
     const uint32_t pix = inside ? px + fr.width * py : 0u;
     Ray ray;
-    ray.valid = false;
+    ray.valid = false; ray.o = fr.cam_centre; ray.d = f3(0.f, 0.f, 1.f); ray.tmin = 0.f; ray.tmax = 0.f;
     if (inside) ray = make_ray(fr, ray_ori, ray_dir, pix);
-    bool alive = inside && ray.valid;
+    const float3 dlt = ray.o - fr.cam_centre;
+    const bool at_origin = (dlt.x == 0.0f) && (dlt.y == 0.0f) && (dlt.z == 0.0f);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     const uint32_t n = b1 - b0;
@@ -173,15 +250,16 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
         mbar_init(&full_bar[1], 1);
         fence_mbar_init();
     }
-    __syncthreads();
+    const bool uniform = __syncthreads_and(at_origin || !inside) != 0;  // also publishes the barrier initialisation
     if (threadIdx.x == 0 && nb > 0) {
         const uint32_t cnt = min((uint32_t)BATCH, n);
         mbar_expect_tx(&full_bar[0], cnt * (uint32_t)sizeof(GutRecord));
         bulk_g2s(smem_raw, records + b0, cnt * (uint32_t)sizeof(GutRecord), &full_bar[0]);
     }
 
-    float T = 1.0f, D = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
-    uint32_t nhits = 0, ntests = 0;
+    FwdState st;
+    st.T = 1.0f; st.D = 0.0f; st.cr = st.cg = st.cb = 0.0f; st.nhits = 0; st.ntests = 0;
+    st.alive = inside && ray.valid;
     uint32_t b = 0;
     for (; b < nb; ++b) {
         const uint32_t cnt = min((uint32_t)BATCH, n - b * BATCH);
@@ -193,44 +271,28 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
                      &full_bar[(b + 1) & 1]);
         }
         mbar_wait(&full_bar[b & 1], (b >> 1) & 1);
-        const float4* rec = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES);
-        for (uint32_t j = 0; j < cnt; ++j) {
-            if ((j & 15u) == 0u && !__any_sync(0xffffffffu, alive)) break;
-            const float4 A = rec[5 * j], B = rec[5 * j + 1], Cm = rec[5 * j + 2], S = rec[5 * j + 3];
-            Canon k;
-            if (COUNT && alive) ntests++;
-            if (particle_test<DEG>(cfg, A, B, Cm, S, ray.o, ray.d, k) && alive) {
-                // accepted: hit distance = |scale * grd * dot(grd, -gro)|   (canonicalRayDistance, gaussianParticles.slang:165-171)
-                const float il = rsqrtf(k.l2);
-                const float3 grd = k.grdu * il;
-                const float dp = dot(grd, k.gro);
-                const float3 sg = f3(S.x * grd.x, S.y * grd.y, S.z * grd.z);
-                const float t = fabsf(dp) * sqrtf(dot(sg, sg));
-                if (t > ray.tmin && t < ray.tmax) {
-                    const float4 F = rec[5 * j + 4];
-                    const float w = k.alpha * T;
-                    D += t * w;
-                    T *= (1.0f - k.alpha);
-                    if (w > 0.0f) { cr += F.x * w; cg += F.y * w; cb += F.z * w; nhits++; }
-                    if (T < cfg.min_transmittance) alive = false;
-                }
-            }
+        float4* rec = reinterpret_cast<float4*>(smem_raw + (b & 1) * STAGE_BYTES);
+        if (cnt & (WALK_UNROLL - 1)) {  // only the last batch of a tile can be ragged (CTA-uniform condition)
+            pad_batch_tail(rec, cnt);
+            __syncthreads();
         }
-        if (__syncthreads_and(!alive)) break;
+        if (uniform) forward_walk<DEG, true, COUNT>(cfg, rec, cnt, ray, dlt, st);
+        else forward_walk<DEG, false, COUNT>(cfg, rec, cnt, ray, dlt, st);
+        if (__syncthreads_and(!st.alive)) break;
     }
     // the tile saturated early while the next batch was already in flight: let the copy land before the CTA retires
     if (b + 1 < nb) mbar_wait(&full_bar[(b + 1) & 1], ((b + 1) >> 1) & 1);
     if (COUNT) {
-        unsigned long long t = ntests, hh = nhits;
+        unsigned long long t = st.ntests, hh = st.nhits;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
         if ((threadIdx.x & 31) == 0) { atomicAdd(&counters[0], t); atomicAdd(&counters[1], hh); }
         return;
     }
     if (inside && ray.valid) {
-        rgba[pix] = make_float4(cr, cg, cb, 1.0f - T);
-        dist[pix] = D;
-        if (cfg.enable_hitcounts) hits[pix] = (float)nhits;
+        rgba[pix] = make_float4(st.cr, st.cg, st.cb, 1.0f - st.T);
+        dist[pix] = st.D;
+        if (cfg.enable_hitcounts) hits[pix] = (float)st.nhits;
     } else if (inside) {
         rgba[pix] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         dist[pix] = 1e06f;
@@ -284,15 +346,131 @@ GUT_D float warp_transpose_reduce16(float (&v)[16], uint32_t lane) {
     return v[0];
 }
 
+struct BwdRay {
+    float T_f, D_f, dA, dD;   // final transmittance / distance of the forward pass, upstream gradients
+    float3 C_f, dC;
+    float T, D;               // running state of the re-walk
+    float3 C;
+    bool alive;
+};
+
+template <int DEG, bool UNIFORM>
+GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt, const Ray& ray,
+                         const float3 dlt, BwdRay& st, uint32_t lane, float* __restrict__ density_grad, float4* __restrict__ feature_grad) {
+    const float minT = cfg.min_transmittance;
+    for (uint32_t j = 0; j < cnt; ++j) {
+        if ((j & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive)) break;
+        const float4* r = rec + 5 * j;
+        const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
+        Canon k;
+        const bool hit = particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray.d, dlt, k) && st.alive;  // no tMinMax test here
+        if (!__any_sync(0xffffffffu, hit)) continue;
+
+        float v[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) v[q] = 0.0f;
+        const float4 F = r[4];
+        if (hit) {
+            const float4 Q = recb[3 * j], IS = recb[3 * j + 1], P = recb[3 * j + 2];
+            const float3 s = f3(S.x, S.y, S.z);
+            const float3 go = k.go;
+            const float il = mufu_rsq(k.l2);           // 1 / |u|
+            const float3 grd = k.u * il;               // normalised canonical direction
+            const float dgo = dot(grd, go);
+            const float3 grdd = grd * (-dgo);
+            const float3 grds = s * grdd;
+            const float gsq = dot(grds, grds);
+            const float gdist = mufu_sqrt(gsq);
+            const float alpha = fminf(cfg.max_alpha, k.araw);
+            const float T = st.T;
+            const float w = alpha * T;
+            const float om = 1.0f - alpha;
+            const float nextT = om * T;
+            const float invT = nextT <= minT ? 0.0f : mufu_rcp(nextT);
+
+            // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's element-wise ones)
+            st.D = fmaf(w, gdist, st.D);
+            const float resD = fmaxf((st.D_f - st.D) * invT, 0.0f);
+            const float aHit = (gdist - resD) * T * st.dD;
+            const float hs = gsq > 0.0f ? w * st.dD * mufu_rcp(gdist) : 0.0f;
+            const float3 G = grds * hs;
+            const float3 sG = s * G;
+            const float3 sclHit = grdd * G;
+            const float3 grdHit = f3(-(grd.x * go.x + dgo) * sG.x, -(grd.y * go.y + dgo) * sG.y, -(grd.z * go.z + dgo) * sG.z);
+            const float3 groHit = f3(-grd.x * grd.x * sG.x, -grd.y * grd.y * sG.y, -grd.z * grd.z * sG.z);
+
+            // opacity and colour terms (:569-633)
+            const float resT = alpha < 0.999999f ? st.T_f * mufu_rcp(om) : T;
+            const float aDns = resT * st.dA;
+            st.C = f3(fmaf(w, F.x, st.C.x), fmaf(w, F.y, st.C.y), fmaf(w, F.z, st.C.z));
+            const float3 resC = f3(fmaxf((st.C_f.x - st.C.x) * invT, 0.0f), fmaxf((st.C_f.y - st.C.y) * invT, 0.0f),
+                                   fmaxf((st.C_f.z - st.C.z) * invT, 0.0f));
+            const float Ssum = aHit + aDns + T * ((F.x - resC.x) * st.dC.x + (F.y - resC.y) * st.dC.y + (F.z - resC.z) * st.dC.z);
+            const float dDens = k.resp * Ssum;
+            const float respG = S.w * Ssum;
+            const float g2G = kernel_response_grad<DEG>(k.g2, k.resp, respG);
+
+            // g2 = |grd x go|^2 : adjoint of the cross product (:671-689); grd x go = c / |u|
+            const float3 gcG = k.c * (2.0f * g2G * il);
+            const float3 grdG = cross(go, gcG);
+            const float3 groG = cross(gcG, grd);
+            const float3 groTot = groG + groHit;
+
+            const float3 gis = f3(IS.x, IS.y, IS.z);
+            // go = gposcr / s : d/ds = -go/s ; d/dgposcr = 1/s
+            const float3 gposcrG = gis * groTot;
+            const float3 sclGro = f3(-go.x * gposcrG.x, -go.y * gposcrG.y, -go.z * gposcrG.z);
+            // R gposcrG with rows of R^T = ms_i * s_i  ==>  sum_i groTot_i * ms_i
+            const float3 gposcG = f3(groTot.x * A.x + groTot.y * B.x + groTot.z * Cm.x, groTot.x * A.y + groTot.y * B.y + groTot.z * Cm.y,
+                                     groTot.x * A.z + groTot.y * B.z + groTot.z * Cm.z);
+            // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): (X - grd (grd . X)) / |u|
+            const float3 X = grdG + grdHit;
+            const float gx = dot(grd, X);
+            const float3 grduG = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
+            // u = rayDirR / s
+            const float3 rayDirRG = gis * grduG;
+            const float3 sclDir = f3(-k.u.x * rayDirRG.x, -k.u.y * rayDirRG.y, -k.u.z * rayDirRG.z);
+
+            // dL/dR^T = gposcrG (x) (o - pos) + rayDirRG (x) d, contracted with dR^T/dq (matmul_bw_quat, mathUtils.cuh:468-533)
+            const float3 vv = f3(ray.o.x - P.x, ray.o.y - P.y, ray.o.z - P.z);
+            const float3 dd = ray.d;
+            const float d00 = gposcrG.x * vv.x + rayDirRG.x * dd.x, d01 = gposcrG.x * vv.y + rayDirRG.x * dd.y, d02 = gposcrG.x * vv.z + rayDirRG.x * dd.z;
+            const float d10 = gposcrG.y * vv.x + rayDirRG.y * dd.x, d11 = gposcrG.y * vv.y + rayDirRG.y * dd.y, d12 = gposcrG.y * vv.z + rayDirRG.y * dd.z;
+            const float d20 = gposcrG.z * vv.x + rayDirRG.z * dd.x, d21 = gposcrG.z * vv.y + rayDirRG.z * dd.y, d22 = gposcrG.z * vv.z + rayDirRG.z * dd.z;
+            const float qr = Q.x, qx = Q.y, qy = Q.z, qz = Q.w;
+            const float s01 = d01 + d10, a01 = d01 - d10, s02 = d02 + d20, a20 = d20 - d02, s12 = d12 + d21, a12 = d12 - d21;
+
+            v[0] = -gposcG.x; v[1] = -gposcG.y; v[2] = -gposcG.z;
+            v[3] = dDens;
+            v[4] = 2.0f * (qz * a01 + qy * a20 + qx * a12);
+            v[5] = 2.0f * (qy * s01 + qz * s02 + qr * a12 - 2.0f * qx * (d11 + d22));
+            v[6] = 2.0f * (qx * s01 + qz * s12 + qr * a20 - 2.0f * qy * (d00 + d22));
+            v[7] = 2.0f * (qx * s02 + qy * s12 + qr * a01 - 2.0f * qz * (d00 + d11));
+            v[8] = sclHit.x + sclGro.x + sclDir.x; v[9] = sclHit.y + sclGro.y + sclDir.y; v[10] = sclHit.z + sclGro.z + sclDir.z;
+            v[11] = w * st.dC.x; v[12] = w * st.dC.y; v[13] = w * st.dC.z;
+
+            st.T = nextT;
+            if (nextT < minT) st.alive = false;
+        }
+        const float total = warp_transpose_reduce16(v, lane);
+        const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
+        if ((lane & 1u) == 0u && slot < 14u) {
+            const uint32_t p = __float_as_uint(F.w);
+            float* dst = slot < 11u ? density_grad + 12 * (size_t)p + slot : reinterpret_cast<float*>(feature_grad + p) + (slot - 11u);
+            atomicAdd(dst, total);
+        }
+    }
+}
+
 template <int DEG>
 __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, const GutRecord* __restrict__ records,
-    const float4* __restrict__ quats, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
+    const GutRecordBwd* __restrict__ records_bwd, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ density_grad, float4* __restrict__ feature_grad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr uint32_t REC_BYTES = BATCH * sizeof(GutRecord), Q_BYTES = BATCH * sizeof(float4);
-    constexpr uint32_t STAGE_BYTES = REC_BYTES + Q_BYTES;  // [records | quaternions] per stage
+    constexpr uint32_t REC_BYTES = BATCH * sizeof(GutRecord), RECB_BYTES = BATCH * sizeof(GutRecordBwd);
+    constexpr uint32_t STAGE_BYTES = REC_BYTES + RECB_BYTES;  // [records | backward records] per stage
     __shared__ __align__(8) uint64_t full_bar[2];
 
     const uint32_t tile = blockIdx.x;
@@ -302,22 +480,25 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
     const bool inside = px < fr.width && py < fr.height;
     const uint32_t pix = inside ? px + fr.width * py : 0u;
     Ray ray;
-    ray.valid = false;
-    ray.o = f3(0.f, 0.f, 0.f); ray.d = f3(0.f, 0.f, 1.f);
+    ray.valid = false; ray.o = fr.cam_centre; ray.d = f3(0.f, 0.f, 1.f); ray.tmin = 0.f; ray.tmax = 0.f;
     if (inside) ray = make_ray(fr, ray_ori, ray_dir, pix);
-    bool alive = inside && ray.valid;
+    const float3 dlt = ray.o - fr.cam_centre;
+    const bool at_origin = (dlt.x == 0.0f) && (dlt.y == 0.0f) && (dlt.z == 0.0f);
 
     // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
-    float T_f = 1.0f, D_f = 0.0f, dA = 0.0f, dD = 0.0f;
-    float3 C_f = f3(0.f, 0.f, 0.f), dC = f3(0.f, 0.f, 0.f);
-    if (alive) {
+    BwdRay st;
+    st.alive = inside && ray.valid;
+    st.T_f = 1.0f; st.D_f = 0.0f; st.dA = 0.0f; st.dD = 0.0f;
+    st.C_f = f3(0.f, 0.f, 0.f); st.dC = f3(0.f, 0.f, 0.f);
+    st.T = 1.0f; st.D = 0.0f; st.C = f3(0.f, 0.f, 0.f);
+    if (st.alive) {
         const float4 fd = __ldg(rgba + pix), gd = __ldg(rgba_grad + pix);
-        T_f = 1.0f - fd.w;          // transmittanceBackward
-        dA = gd.w;                  // transmittanceGradient = -dA; used as residualTrm * -(-dA)
-        D_f = __ldg(dist + pix);
-        dD = __ldg(dist_grad + pix);
-        C_f = f3(fd.x, fd.y, fd.z);
-        dC = f3(gd.x, gd.y, gd.z);
+        st.T_f = 1.0f - fd.w;      // transmittanceBackward
+        st.dA = gd.w;              // transmittanceGradient = -dA; used as residualTrm * -(-dA)
+        st.D_f = __ldg(dist + pix);
+        st.dD = __ldg(dist_grad + pix);
+        st.C_f = f3(fd.x, fd.y, fd.z);
+        st.dC = f3(gd.x, gd.y, gd.z);
     }
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
@@ -329,20 +510,16 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
         mbar_init(&full_bar[1], 1);
         fence_mbar_init();
     }
-    __syncthreads();
+    const bool uniform = __syncthreads_and(at_origin || !inside) != 0;
     auto issue = [&](uint32_t bi) {
         const uint32_t c = min((uint32_t)BATCH, n - bi * BATCH);
         uint64_t* bar = &full_bar[bi & 1];
-        mbar_expect_tx(bar, c * (uint32_t)(sizeof(GutRecord) + sizeof(float4)));
+        mbar_expect_tx(bar, c * (uint32_t)(sizeof(GutRecord) + sizeof(GutRecordBwd)));
         unsigned char* base = smem_raw + (bi & 1) * STAGE_BYTES;
         bulk_g2s(base, records + b0 + (size_t)bi * BATCH, c * (uint32_t)sizeof(GutRecord), bar);
-        bulk_g2s(base + REC_BYTES, quats + b0 + (size_t)bi * BATCH, c * (uint32_t)sizeof(float4), bar);
+        bulk_g2s(base + REC_BYTES, records_bwd + b0 + (size_t)bi * BATCH, c * (uint32_t)sizeof(GutRecordBwd), bar);
     };
     if (threadIdx.x == 0 && nb > 0) issue(0);
-
-    float T = 1.0f, D = 0.0f;
-    float3 C = f3(0.f, 0.f, 0.f);
-    const float minT = cfg.min_transmittance;
 
     uint32_t b = 0;
     for (; b < nb; ++b) {
@@ -350,109 +527,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
         if (threadIdx.x == 0 && b + 1 < nb) issue(b + 1);
         mbar_wait(&full_bar[b & 1], (b >> 1) & 1);
         const float4* rec = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES);
-        const float4* qrec = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES + REC_BYTES);
-        for (uint32_t j = 0; j < cnt; ++j) {
-            if ((j & 15u) == 0u && !__any_sync(0xffffffffu, alive)) break;
-            const float4 A = rec[5 * j], B = rec[5 * j + 1], Cm = rec[5 * j + 2], S = rec[5 * j + 3];
-            Canon k;
-            const bool hit = particle_test<DEG>(cfg, A, B, Cm, S, ray.o, ray.d, k) && alive;  // no tMinMax test here
-            if (!__any_sync(0xffffffffu, hit)) continue;
-
-            float v[16];
-#pragma unroll
-            for (int q = 0; q < 16; ++q) v[q] = 0.0f;
-            const float4 F = rec[5 * j + 4];
-            if (hit) {
-                const float4 Q = qrec[j];  // w,x,y,z
-                const float3 s = f3(S.x, S.y, S.z);
-                const float3 gro = k.gro;
-                const float il = rsqrtf(k.l2);
-                const float3 grd = k.grdu * il;
-                const float dgo = dot(grd, gro);
-                const float3 grdd = grd * (-dgo);
-                const float3 grds = s * grdd;
-                const float gsq = dot(grds, grds);
-                const float gdist = sqrtf(gsq);
-                const float alpha = k.alpha;
-                const float w = alpha * T;
-                const float nextT = (1.0f - alpha) * T;
-
-                D += w * gdist;
-                const float resD = fmaxf(nextT <= minT ? 0.0f : __fdividef(D_f - D, nextT), 0.0f);
-                const float aHit = (gdist - resD) * T * dD;
-                const float hs = gsq > 0.0f ? __fdividef(w, gdist) * dD : 0.0f;
-                const float3 grdsG = grds * hs;
-                const float3 sclHit = grdd * grdsG;
-                const float3 grdHit = f3(-s.x * (grd.x * gro.x + dgo) * grdsG.x, -s.y * (grd.y * gro.y + dgo) * grdsG.y,
-                                         -s.z * (grd.z * gro.z + dgo) * grdsG.z);
-                const float3 groHit = f3(-s.x * grd.x * grd.x * grdsG.x, -s.y * grd.y * grd.y * grdsG.y, -s.z * grd.z * grd.z * grdsG.z);
-
-                const float resT = alpha < 0.999999f ? __fdividef(T_f, 1.0f - alpha) : T;
-                const float aDns = resT * dA;
-
-                C = f3(C.x + w * F.x, C.y + w * F.y, C.z + w * F.z);
-                float3 resC = f3(0.f, 0.f, 0.f);
-                if (!(nextT <= minT)) {
-                    const float inv = __fdividef(1.0f, nextT);
-                    resC = f3(fmaxf((C_f.x - C.x) * inv, 0.0f), fmaxf((C_f.y - C.y) * inv, 0.0f), fmaxf((C_f.z - C.z) * inv, 0.0f));
-                }
-                const float Ssum = aHit + aDns + T * ((F.x - resC.x) * dC.x + (F.y - resC.y) * dC.y + (F.z - resC.z) * dC.z);
-                const float dDens = k.resp * Ssum;
-                const float respG = S.w * Ssum;
-                const float g2G = kernel_response_grad<DEG>(k.g2, k.resp, respG);
-
-                // g2 = |grd x gro|^2 : adjoint of the cross product (gaussianParticles.cuh:671-689)
-                const float3 gc = k.c * il;
-                const float3 gcG = gc * (2.0f * g2G);
-                const float3 grdG = f3(gcG.z * gro.y - gcG.y * gro.z, gcG.x * gro.z - gcG.z * gro.x, gcG.y * gro.x - gcG.x * gro.y);
-                const float3 groG = f3(gcG.y * grd.z - gcG.z * grd.y, gcG.z * grd.x - gcG.x * grd.z, gcG.x * grd.y - gcG.y * grd.x);
-                const float3 groTot = groG + groHit;
-
-                const float3 gis = f3(__fdividef(1.0f, s.x), __fdividef(1.0f, s.y), __fdividef(1.0f, s.z));
-                // gro = gposcr / s : d/ds = -gposcr/s^2 = -gro/s ; d/dgposcr = 1/s
-                const float3 sclGro = f3(-gro.x * gis.x * groTot.x, -gro.y * gis.y * groTot.y, -gro.z * gis.z * groTot.z);
-                const float3 gposcrG = gis * groTot;
-                // R (gposcrG) with rows of R^T = ms_i * s_i  ==> sum_i groTot_i * ms_i
-                const float3 gposcG = f3(groTot.x * A.x + groTot.y * B.x + groTot.z * Cm.x, groTot.x * A.y + groTot.y * B.y + groTot.z * Cm.y,
-                                         groTot.x * A.z + groTot.y * B.z + groTot.z * Cm.z);
-                // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): il * (X - grd (grd . X))
-                const float3 X = grdG + grdHit;
-                const float gx = dot(grd, X);
-                const float3 grduG = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
-                // grdu = rayDirR / s
-                const float3 sclDir = f3(-k.grdu.x * gis.x * grduG.x, -k.grdu.y * gis.y * grduG.y, -k.grdu.z * gis.z * grduG.z);
-                const float3 rayDirRG = gis * grduG;
-
-                // dL/dR^T = gposcrG (x) (o - pos) + rayDirRG (x) d, contracted with dR^T/dq (matmul_bw_quat, mathUtils.cuh:468-533)
-                const float3 vv = f3(ray.o.x - A.w, ray.o.y - B.w, ray.o.z - Cm.w);
-                const float3 dd = ray.d;
-                const float d00 = gposcrG.x * vv.x + rayDirRG.x * dd.x, d01 = gposcrG.x * vv.y + rayDirRG.x * dd.y, d02 = gposcrG.x * vv.z + rayDirRG.x * dd.z;
-                const float d10 = gposcrG.y * vv.x + rayDirRG.y * dd.x, d11 = gposcrG.y * vv.y + rayDirRG.y * dd.y, d12 = gposcrG.y * vv.z + rayDirRG.y * dd.z;
-                const float d20 = gposcrG.z * vv.x + rayDirRG.z * dd.x, d21 = gposcrG.z * vv.y + rayDirRG.z * dd.y, d22 = gposcrG.z * vv.z + rayDirRG.z * dd.z;
-                const float qr = Q.x, qx = Q.y, qy = Q.z, qz = Q.w;
-                const float s01 = d01 + d10, a01 = d01 - d10, s02 = d02 + d20, a20 = d20 - d02, s12 = d12 + d21, a12 = d12 - d21;
-
-                v[0] = -gposcG.x; v[1] = -gposcG.y; v[2] = -gposcG.z;
-                v[3] = dDens;
-                v[4] = 2.0f * (qz * a01 + qy * a20 + qx * a12);
-                v[5] = 2.0f * (qy * s01 + qz * s02 + qr * a12 - 2.0f * qx * (d11 + d22));
-                v[6] = 2.0f * (qx * s01 + qz * s12 + qr * a20 - 2.0f * qy * (d00 + d22));
-                v[7] = 2.0f * (qx * s02 + qy * s12 + qr * a01 - 2.0f * qz * (d00 + d11));
-                v[8] = sclHit.x + sclGro.x + sclDir.x; v[9] = sclHit.y + sclGro.y + sclDir.y; v[10] = sclHit.z + sclGro.z + sclDir.z;
-                v[11] = w * dC.x; v[12] = w * dC.y; v[13] = w * dC.z;
-
-                T = nextT;
-                if (T < minT) alive = false;
-            }
-            const float total = warp_transpose_reduce16(v, lane);
-            const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
-            if ((lane & 1u) == 0u && slot < 14u) {
-                const uint32_t p = __float_as_uint(F.w);
-                float* dst = slot < 11u ? density_grad + 12 * (size_t)p + slot : reinterpret_cast<float*>(feature_grad + p) + (slot - 11u);
-                atomicAdd(dst, total);
-            }
-        }
-        if (__syncthreads_and(!alive)) break;
+        const float4* recb = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES + REC_BYTES);
+        if (uniform) backward_walk<DEG, true>(cfg, rec, recb, cnt, ray, dlt, st, lane, density_grad, feature_grad);
+        else backward_walk<DEG, false>(cfg, rec, recb, cnt, ray, dlt, st, lane, density_grad, feature_grad);
+        if (__syncthreads_and(!st.alive)) break;
     }
     if (b + 1 < nb) mbar_wait(&full_bar[(b + 1) & 1], ((b + 1) >> 1) & 1);
 }
@@ -479,14 +557,14 @@ cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const
 
 template <int DEG>
 cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
-                                  const float4* quats, const float* ray_ori, const float* ray_dir, const float* rgba,
+                                  const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir, const float* rgba,
                                   const float* rgba_grad, const float* dist, const float* dist_grad, float* density_grad,
                                   float4* feature_grad, cudaStream_t stream) {
-    const size_t smem = 2 * BATCH * (sizeof(GutRecord) + sizeof(float4));
+    const size_t smem = 2 * BATCH * (sizeof(GutRecord) + sizeof(GutRecordBwd));
     cudaError_t e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     gut_render_backward_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(
-        cfg, frame, tile_start, records, quats, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+        cfg, frame, tile_start, records, records_bwd, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
         reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, density_grad, feature_grad);
     return cudaGetLastError();
 }
@@ -514,11 +592,11 @@ cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const
 }
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
-                                       const GutRecord* records, const float4* quats, const float* ray_ori, const float* ray_dir,
+                                       const GutRecord* records, const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
                                        float* density_grad, float4* feature_grad, cudaStream_t stream) {
 #define CALL_BWD(D) \
-    launch_render_bwd_deg<D>(cfg, frame, tile_start, records, quats, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, density_grad, feature_grad, stream)
+    launch_render_bwd_deg<D>(cfg, frame, tile_start, records, records_bwd, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, density_grad, feature_grad, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_BWD)
 #undef CALL_BWD
 }
