@@ -340,7 +340,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         GUT_CUDA(h, ensure(h->sorted_idx, M * 4, s, 1.25f));
         GUT_CUDA(h, ensure(h->records, M * sizeof(GutRecord), s, 1.25f));
         GUT_CUDA(h, ensure(h->records_bwd, M * sizeof(GutRecordBwd), s, 1.25f));
-        if (max_list > 4096) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
+        if (max_list > 12288) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
         {
             StageTimer t(h, ST_EMIT, s);
             GUT_CUDA(h, gut_launch_emit(h->cfg, fr, N, pb, (const uint32_t*)h->tile_start.p, (uint32_t*)h->tile_cursor.p, (uint2*)h->entries.p, s));
@@ -348,10 +348,10 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         }
         {
             StageTimer t(h, ST_SORT, s);
-            GUT_CUDA(h, gut_launch_tile_sort(fr, N, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p, d_density,
+            GUT_CUDA(h, gut_launch_tile_sort(fr, N, max_list, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p, d_density,
                                              (const float4*)h->features.p, (uint32_t*)h->sorted_idx.p, (GutRecord*)h->records.p,
                                              (GutRecordBwd*)h->records_bwd.p, s));
-            h->launches += 1;
+            h->launches += max_list > 4096 ? 2 : 1;
         }
         {
             StageTimer t(h, ST_RENDER, s);

@@ -83,153 +83,229 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
     const float4 co = proj.conic_opacity[i];
     const float max_power = gut_logf(co.w / cfg.min_alpha);
     const GutTileBox bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, ext);
-    for (uint32_t y = bb.y0; y < bb.y1; ++y)
-        for (uint32_t x = bb.x0; x < bb.x1; ++x) {
-            if (!cfg.tile_based_culling || gut_tile_min_power((float)x, (float)y, co, centre) < max_power) {
-                const uint32_t t = y * fr.grid_x + x;
-                const uint32_t slot = atomicAdd(&tile_cursor[t], 1u);
-                const uint32_t b0 = tile_start[t], b1 = tile_start[t + 1];
-                if (b0 + slot < b1) entries[b0 + slot] = make_uint2(depth_bits, i);
+    // The bucket slot comes back from an L2 atomic (~1 us under contention).  Walking the box EMIT_ILP tiles at a time
+    // keeps that many independent atomics in flight per thread instead of one dependent round trip per tile.
+    constexpr int EMIT_ILP = 4;
+    const uint32_t bw = bb.x1 - bb.x0;
+    const uint32_t total = bw * (bb.y1 - bb.y0);
+    uint32_t x = bb.x0, y = bb.y0;
+    for (uint32_t base = 0; base < total; base += EMIT_ILP) {
+        uint32_t t[EMIT_ILP], slot[EMIT_ILP];
+        bool ok[EMIT_ILP];
+#pragma unroll
+        for (int k = 0; k < EMIT_ILP; ++k) {
+            ok[k] = (base + k) < total;
+            t[k] = y * fr.grid_x + x;
+            if (ok[k] && cfg.tile_based_culling) ok[k] = gut_tile_min_power((float)x, (float)y, co, centre) < max_power;
+            if (++x == bb.x1) { x = bb.x0; ++y; }
+        }
+#pragma unroll
+        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k]], 1u) : 0u;
+#pragma unroll
+        for (int k = 0; k < EMIT_ILP; ++k) {
+            if (ok[k]) {
+                const uint32_t b0 = tile_start[t[k]], b1 = tile_start[t[k] + 1];
+                if (b0 + slot[k] < b1) entries[b0 + slot[k]] = make_uint2(depth_bits, i);
             }
         }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
 // Per-tile sort + record expansion.
+//
+// One CTA per tile.  The bucket (depth bits, particle) is sorted on the DEPTH bits only, with stable 8-bit LSD
+// radix passes over just the bit range that varies inside the bucket (3-4 passes for typical depth ranges);
+// runs of bit-identical depths (rare) are then put in ascending particle order, which is the order the
+// reference's stable sort leaves them in (emission order).  Pass structure: every warp owns a contiguous
+// segment of the bucket, counts its digits into warp-private counters, one scan over (digit, warp) gives each
+// warp its output cursors, and the warp scatters its segment 32 keys at a time ranking equal digits with
+// match.any -- three CTA barriers per pass, no per-round barriers.
+// The epilogue gathers the parameters of the sorted particles, builds the 80 B + 48 B records in shared memory
+// and writes them with bulk async copies (TMA, shared -> global), so HBM sees only full, contiguous lines.
 // ---------------------------------------------------------------------------------------------------
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr uint32_t SORT_SMEM_CAP = 4096;  // entries per buffer kept in shared memory (2 x 32 KB)
+constexpr uint32_t SORT_RADIX_BITS = 8;
+constexpr uint32_t SORT_BINS = 1u << SORT_RADIX_BITS;
+constexpr uint32_t SORT_CHUNK = 256;  // records staged per bulk store (256 x 128 B = 32 KB)
 
+GUT_D uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+GUT_D void bulk_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_addr(ssrc)), "r"(bytes) : "memory");
+}
+GUT_D void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+GUT_D void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+GUT_D void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <int WARPS>
 struct SortShared {
-    uint32_t hist[256];
-    uint32_t base[256];
-    uint32_t warp_cnt[SORT_WARPS][256];
-    uint32_t or_lo, or_hi, and_lo, and_hi;
+    uint32_t warp_cnt[WARPS][SORT_BINS];  // per-warp digit counts, then per-warp output cursors
+    uint32_t wsum[32];
+    uint32_t or_bits, and_bits, ties;
 };
 
-// One stable 8-bit counting pass over n keys, src -> dst (generic pointers: shared or global memory).
-// Returns false (and leaves dst untouched) when the digit is constant over the bucket.
-__device__ bool radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, SortShared& sh) {
+// One stable counting pass on `bits` key bits starting at `shift`.  src/dst may be shared or global memory.
+template <int THREADS>
+__device__ void radix_pass(const uint32_t* src_k, const uint32_t* src_v, uint32_t* dst_k, uint32_t* dst_v, uint32_t n, uint32_t shift,
+                           uint32_t mask, SortShared<THREADS / 32>& sh) {
+    constexpr int WARPS = THREADS / 32;
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    sh.hist[tid] = 0;
+    for (uint32_t i = tid; i < WARPS * SORT_BINS; i += THREADS) (&sh.warp_cnt[0][0])[i] = 0;
     __syncthreads();
-    for (uint32_t i = tid; i < n; i += SORT_THREADS) atomicAdd(&sh.hist[(uint32_t)(src[i] >> shift) & 255u], 1u);
+    const uint32_t seg = (((n + WARPS - 1) / WARPS) + 31u) & ~31u;   // keys per warp, multiple of 32
+    const uint32_t s0 = min(n, wid * seg), s1 = min(n, s0 + seg);
+    for (uint32_t i = s0 + lane; i < s1; i += 32) atomicAdd(&sh.warp_cnt[wid][(src_k[i] >> shift) & mask], 1u);
     __syncthreads();
-    // exclusive scan of 256 bins by warp 0..7 cooperatively (each thread owns one bin)
-    const uint32_t h = sh.hist[tid];
-    const int uniform = __syncthreads_or(h == n);
-    if (uniform) return false;
-    uint32_t incl = h;
+    // cursors: cnt[w][d] <- sum_{d' < d} total(d') + sum_{w' < w} cnt[w'][d]
+    for (uint32_t d0 = 0; d0 < SORT_BINS; d0 += THREADS) {   // one iteration when THREADS >= SORT_BINS
+        const uint32_t d = d0 + tid;
+        uint32_t c[WARPS], tot = 0;
+        if (d < SORT_BINS) {
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (uint32_t)o) incl += v;
+            for (int w = 0; w < WARPS; ++w) { c[w] = sh.warp_cnt[w][d]; tot += c[w]; }
+        }
+        uint32_t incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += v;
+        }
+        if (lane == 31) sh.wsum[wid] = incl;
+        __syncthreads();
+        uint32_t off = 0;
+        for (uint32_t w = 0; w < wid; ++w) off += sh.wsum[w];
+        uint32_t run = off + incl - tot;
+        if (d < SORT_BINS) {
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) { sh.warp_cnt[w][d] = run; run += c[w]; }
+        }
+        __syncthreads();
     }
-    __shared__ uint32_t wsum[SORT_WARPS];
-    if (lane == 31) wsum[wid] = incl;
-    __syncthreads();
-    uint32_t off = 0;
-    for (uint32_t w = 0; w < wid; ++w) off += wsum[w];
-    sh.base[tid] = off + incl - h;
-    for (int w = 0; w < SORT_WARPS; ++w) sh.warp_cnt[w][tid] = 0;
-    __syncthreads();
-
-    // stable scatter, SORT_THREADS keys per round, rounds in order
-    for (uint32_t r0 = 0; r0 < n; r0 += SORT_THREADS) {
-        const uint32_t i = r0 + tid;
-        const bool act = i < n;
-        uint64_t key = 0;
-        uint32_t d = 0xffffffffu;
-        if (act) { key = src[i]; d = (uint32_t)(key >> shift) & 255u; }
-        // rank among the lanes of this warp that hold the same digit (lower lanes first)
+    // stable scatter of the warp's own segment, 32 keys at a time
+    for (uint32_t i0 = s0; i0 < s1; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool act = i < s1;
+        uint32_t key = 0, val = 0, d = 0xffffffffu;
+        if (act) { key = src_k[i]; val = src_v[i]; d = (key >> shift) & mask; }
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-        if (act && rank == 0) sh.warp_cnt[wid][d] = __popc(peers);
-        __syncthreads();
+        uint32_t pos = 0;
+        if (act) pos = sh.warp_cnt[wid][d] + rank;
+        __syncwarp();
         if (act) {
-            uint32_t before = 0;
-            for (uint32_t w = 0; w < wid; ++w) before += sh.warp_cnt[w][d];
-            dst[sh.base[d] + before + rank] = key;
+            dst_k[pos] = key; dst_v[pos] = val;
+            if (rank == 0) sh.warp_cnt[wid][d] += __popc(peers);
         }
-        __syncthreads();
-        // advance the bases by this round's totals and clear the per-warp counters
-        {
-            uint32_t tot = 0;
-#pragma unroll
-            for (int w = 0; w < SORT_WARPS; ++w) { tot += sh.warp_cnt[w][tid]; sh.warp_cnt[w][tid] = 0; }
-            sh.base[tid] += tot;
-        }
-        __syncthreads();
+        __syncwarp();
     }
-    return true;
+    __syncthreads();
 }
 
-__global__ void __launch_bounds__(SORT_THREADS) gut_tile_sort_kernel(GutFrame fr, uint32_t N, const uint32_t* __restrict__ tile_start,
-                                                                     uint2* __restrict__ entries, uint2* __restrict__ scratch,
-                                                                     const float4* __restrict__ density12,
-                                                                     const float4* __restrict__ features,
-                                                                     uint32_t* __restrict__ sorted_idx, GutRecord* __restrict__ records,
-                                                                     GutRecordBwd* __restrict__ records_bwd) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* buf_a = reinterpret_cast<uint64_t*>(smem_raw);
-    uint64_t* buf_b = buf_a + SORT_SMEM_CAP;
-    __shared__ SortShared sh;
+template <int THREADS, uint32_t CAP>
+__global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uint32_t N, const uint32_t* __restrict__ tile_start,
+                                                                uint2* __restrict__ entries, uint2* __restrict__ scratch,
+                                                                uint32_t n_min, uint32_t n_max,
+                                                                const float4* __restrict__ density12,
+                                                                const float4* __restrict__ features,
+                                                                uint32_t* __restrict__ sorted_idx, GutRecord* __restrict__ records,
+                                                                GutRecordBwd* __restrict__ records_bwd) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ SortShared<THREADS / 32> sh;
 
     const uint32_t tile = blockIdx.x;
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     const uint32_t n = b1 - b0;
-    if (n == 0) return;
-    const uint32_t tid = threadIdx.x;
+    if (n == 0 || n < n_min || n > n_max) return;   // this launch handles buckets of n_min..n_max entries
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
 
-    // keys are (depth_bits << 32) | particle; the bucket in global memory is uint2{depth_bits, particle} = little-endian
-    // {lo = depth, hi = particle}, so swap halves while loading.
-    const bool in_smem = n <= SORT_SMEM_CAP;
-    uint64_t* src = in_smem ? buf_a : reinterpret_cast<uint64_t*>(entries + b0);
-    uint64_t* dst = in_smem ? buf_b : reinterpret_cast<uint64_t*>(scratch + b0);
-    if (tid == 0) { sh.or_lo = 0; sh.or_hi = 0; sh.and_lo = 0xffffffffu; sh.and_hi = 0xffffffffu; }
+    // shared-memory layout: [key A | val A | key B | val B], CAP entries each; buckets above CAP sort in global memory
+    // (keys and values de-interleaved in place over `entries` / `scratch`, which hold 2 x n words each).
+    const bool in_smem = n <= CAP;
+    uint32_t* ka = in_smem ? reinterpret_cast<uint32_t*>(smem_raw) : reinterpret_cast<uint32_t*>(scratch + b0);
+    uint32_t* va = ka + (in_smem ? CAP : n);
+    uint32_t* kb = in_smem ? va + CAP : reinterpret_cast<uint32_t*>(entries + b0);
+    uint32_t* vb = kb + (in_smem ? CAP : n);
+
+    if (tid == 0) { sh.or_bits = 0; sh.and_bits = 0xffffffffu; sh.ties = 0; }
     __syncthreads();
     {
-        uint32_t olo = 0, ohi = 0, alo = 0xffffffffu, ahi = 0xffffffffu;
-        for (uint32_t i = tid; i < n; i += SORT_THREADS) {
+        uint32_t o = 0, a = 0xffffffffu;
+        for (uint32_t i = tid; i < n; i += THREADS) {
             const uint2 e = entries[b0 + i];
-            const uint64_t key = ((uint64_t)e.x << 32) | e.y;
-            src[i] = key;  // in the global case this rewrites the bucket in key order
-            olo |= e.y; alo &= e.y; ohi |= e.x; ahi &= e.x;
+            ka[i] = e.x; va[i] = e.y;
+            o |= e.x; a &= e.x;
         }
-        atomicOr(&sh.or_lo, olo); atomicOr(&sh.or_hi, ohi); atomicAnd(&sh.and_lo, alo); atomicAnd(&sh.and_hi, ahi);
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) { o |= __shfl_xor_sync(0xffffffffu, o, s); a &= __shfl_xor_sync(0xffffffffu, a, s); }
+        if (lane == 0) { atomicOr(&sh.or_bits, o); atomicAnd(&sh.and_bits, a); }
     }
     __syncthreads();
-    const uint64_t varying = (((uint64_t)(sh.or_hi ^ sh.and_hi)) << 32) | (uint64_t)(sh.or_lo ^ sh.and_lo);
-    for (int shift = 0; shift < 64; shift += 8) {
-        if (((varying >> shift) & 255ull) == 0) continue;  // digit identical for every key of the bucket
-        if (radix_pass(src, dst, n, shift, sh)) { uint64_t* t = src; src = dst; dst = t; }
-        __syncthreads();
+    const uint32_t varying = sh.or_bits ^ sh.and_bits;
+    if (varying) {
+        const uint32_t lo = __ffs(varying) - 1u, hi = 32u - __clz(varying);   // bits [lo, hi) differ somewhere in the bucket
+        const uint32_t npass = (hi - lo + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+        for (uint32_t p = 0; p < npass; ++p) {
+            const uint32_t shift = lo + p * SORT_RADIX_BITS;
+            const uint32_t bits = min(SORT_RADIX_BITS, hi - shift);
+            radix_pass<THREADS>(ka, va, kb, vb, n, shift, (1u << bits) - 1u, sh);
+            uint32_t* t = ka; ka = kb; kb = t;
+            t = va; va = vb; vb = t;
+        }
     }
+    // runs of identical depth: ascending particle index (what the reference's stable sort leaves, gutRenderer.cu:356-365)
+    for (uint32_t i = tid; i + 1 < n; i += THREADS) {
+        const uint32_t k = ka[i];
+        if (k == ka[i + 1] && (i == 0 || ka[i - 1] != k)) {     // first element of a run of equal keys
+            uint32_t e = i + 2;
+            while (e < n && ka[e] == k) ++e;
+            for (uint32_t a = i + 1; a < e; ++a) {              // insertion sort, runs are tiny
+                const uint32_t v = va[a];
+                uint32_t b = a;
+                while (b > i && va[b - 1] > v) { va[b] = va[b - 1]; --b; }
+                va[b] = v;
+            }
+        }
+    }
+    __syncthreads();
 
-    // ---- epilogue: sorted particle list + record stream (contiguous per tile) ----
-    for (uint32_t i = tid; i < n; i += SORT_THREADS) {
-        const uint32_t p = (uint32_t)(src[i] & 0xffffffffull);
-        sorted_idx[b0 + i] = p;
-        const float4 r0 = __ldg(density12 + 3 * (size_t)p);
-        const float4 q = __ldg(density12 + 3 * (size_t)p + 1);
-        const float4 r2 = __ldg(density12 + 3 * (size_t)p + 2);
-        const float4 ft = __ldg(features + p);
-        float3 c0, c1, c2;
-        quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);  // columns of R == rows of R^T
-        const float ix = 1.0f / r2.x, iy = 1.0f / r2.y, iz = 1.0f / r2.z;
-        const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;  // rows of ms = diag(1/s) R^T
-        const float3 v = fr.cam_centre - f3(r0.x, r0.y, r0.z);  // frame origin - position
-        float4* out = reinterpret_cast<float4*>(records + b0 + i);
-        out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
-        out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
-        out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
-        out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
-        out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p));
-        float4* outb = reinterpret_cast<float4*>(records_bwd + b0 + i);
-        outb[0] = q;
-        outb[1] = make_float4(ix, iy, iz, 0.0f);
-        outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
+    // ---- epilogue: sorted particle list + record streams (contiguous per tile) ----
+    // staging area: the buffer pair the sort no longer needs (or all of shared memory on the global path)
+    unsigned char* stage = in_smem ? reinterpret_cast<unsigned char*>(kb) : smem_raw;   // kb starts the free [key|val] pair
+    float4* st_rec = reinterpret_cast<float4*>(stage);
+    float4* st_bwd = reinterpret_cast<float4*>(stage + SORT_CHUNK * sizeof(GutRecord));
+    for (uint32_t c0 = 0; c0 < n; c0 += SORT_CHUNK) {
+        const uint32_t cnt = min(SORT_CHUNK, n - c0);
+        for (uint32_t i = tid; i < cnt; i += THREADS) {
+            const uint32_t p = va[c0 + i];
+            sorted_idx[b0 + c0 + i] = p;
+            const float4 r0 = __ldg(density12 + 3 * (size_t)p);
+            const float4 q = __ldg(density12 + 3 * (size_t)p + 1);
+            const float4 r2 = __ldg(density12 + 3 * (size_t)p + 2);
+            const float4 ft = __ldg(features + p);
+            float3 c0v, c1v, c2v;
+            quat_to_columns(q.x, q.y, q.z, q.w, c0v, c1v, c2v);  // columns of R == rows of R^T
+            const float ix = 1.0f / r2.x, iy = 1.0f / r2.y, iz = 1.0f / r2.z;
+            const float3 m0 = c0v * ix, m1 = c1v * iy, m2 = c2v * iz;  // rows of ms = diag(1/s) R^T
+            const float3 v = fr.cam_centre - f3(r0.x, r0.y, r0.z);     // frame origin - position
+            float4* out = st_rec + 5 * i;
+            out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
+            out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
+            out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
+            out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
+            out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p));
+            float4* outb = st_bwd + 3 * i;
+            outb[0] = q;
+            outb[1] = make_float4(ix, iy, iz, 0.0f);
+            outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
+        }
+        fence_async_smem();   // generic-proxy writes above -> visible to the async proxy that reads them below
+        __syncthreads();
+        if (tid == 0) {
+            bulk_s2g(records + b0 + c0, st_rec, cnt * (uint32_t)sizeof(GutRecord));
+            bulk_s2g(records_bwd + b0 + c0, st_bwd, cnt * (uint32_t)sizeof(GutRecordBwd));
+            bulk_commit();
+            bulk_wait_read();   // the staging area may be overwritten (or the CTA may exit) once the copies have read it
+        }
+        __syncthreads();
     }
 }
 
@@ -271,19 +347,27 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
     return cudaGetLastError();
 }
 
-cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32_t* tile_start, uint2* entries, uint2* scratch,
-                                 const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
-                                 GutRecordBwd* records_bwd, cudaStream_t stream) {
-    const size_t smem = 2 * SORT_SMEM_CAP * sizeof(uint64_t);
+cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries,
+                                 uint2* scratch, const float* density12, const float4* features, uint32_t* sorted_idx,
+                                 GutRecord* records, GutRecordBwd* records_bwd, cudaStream_t stream) {
+    // small buckets: 256 threads, 4096-entry shared buffers (64 KB -> 3 CTAs per SM);
+    // large buckets: 512 threads, 12288-entry buffers (192 KB, one CTA per SM); above that the passes run over global memory.
+    constexpr uint32_t CAP_S = 4096, CAP_L = 12288;
+    const size_t smem_s = 4 * CAP_S * sizeof(uint32_t), smem_l = 4 * CAP_L * sizeof(uint32_t);
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gut_tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(gut_tile_sort_kernel<256, CAP_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(gut_tile_sort_kernel<512, CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    gut_tile_sort_kernel<<<frame.num_tiles, SORT_THREADS, smem, stream>>>(frame, N, tile_start, entries, scratch,
-                                                                         reinterpret_cast<const float4*>(density12), features,
-                                                                         sorted_idx, records, records_bwd);
+    const float4* d12 = reinterpret_cast<const float4*>(density12);
+    gut_tile_sort_kernel<256, CAP_S><<<frame.num_tiles, 256, smem_s, stream>>>(frame, N, tile_start, entries, scratch, 1u, CAP_S, d12, features,
+                                                                              sorted_idx, records, records_bwd);
+    if (max_list > CAP_S)
+        gut_tile_sort_kernel<512, CAP_L><<<frame.num_tiles, 512, smem_l, stream>>>(frame, N, tile_start, entries, scratch, CAP_S + 1u, 0xffffffffu,
+                                                                                  d12, features, sorted_idx, records, records_bwd);
     return cudaGetLastError();
 }
 

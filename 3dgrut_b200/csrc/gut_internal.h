@@ -69,7 +69,7 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
                             const uint32_t* tile_start, uint32_t* tile_cursor, uint2* entries, cudaStream_t stream);
 
 // per-tile sort of (depth, idx) + expansion into the record stream; scratch = alt buffer for oversize tiles
-cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, const uint32_t* tile_start, uint2* entries, uint2* scratch,
+cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries, uint2* scratch,
                                  const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
                                  GutRecordBwd* records_bwd, cudaStream_t stream);
 
