@@ -42,7 +42,7 @@ struct GutHandle {
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
-    DevBuf entries, scratch, sorted_idx, records, records_bwd;
+    DevBuf entries, scratch, sorted_idx;
     // host-buffer mode (gut_*_host)
     DevBuf h_ray_ori, h_ray_dir, h_rgba, h_dist, h_hits, h_rgba_grad, h_dist_grad;
     uint32_t* pinned_stats = nullptr;  // [2] = {M, max tile list}
@@ -54,6 +54,7 @@ struct GutHandle {
     uint64_t fwd_M = 0;
     uint32_t fwd_max_list = 0;
     GutFrame fwd_frame = {};
+    const float* fwd_density = nullptr;  // particle parameters of the last forward (borrowed; used by gut_measure_work)
 
     // timers (SplatRaster::CudaTimer, splatRaster.cpp:108-151): keep the last 256
     std::deque<EventPair> timers;        // tag 0 = forward_render, 1 = backward_render
@@ -270,7 +271,7 @@ void gut_destroy(GutHandle* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->feature_grad, &h->tile_hist,
-                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->records, &h->records_bwd,
+                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
     if (h->pinned_stats) cudaFreeHost(h->pinned_stats);
@@ -329,7 +330,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     const uint64_t M = h->pinned_stats[0];
     const uint32_t max_list = h->pinned_stats[1];
 
-    h->fwd_stream = s; h->fwd_N = N; h->fwd_W = W; h->fwd_H = H; h->fwd_M = M; h->fwd_max_list = max_list; h->fwd_frame = fr;
+    h->fwd_stream = s; h->fwd_N = N; h->fwd_W = W; h->fwd_H = H; h->fwd_M = M; h->fwd_max_list = max_list; h->fwd_frame = fr; h->fwd_density = d_density;
 
     if (M == 0) {
         // nothing intersects the image: outputs keep their initial values (reference early return, gutRenderer.cu:323-325)
@@ -338,8 +339,6 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     } else {
         GUT_CUDA(h, ensure(h->entries, M * 8, s, 1.25f));
         GUT_CUDA(h, ensure(h->sorted_idx, M * 4, s, 1.25f));
-        GUT_CUDA(h, ensure(h->records, M * sizeof(GutRecord), s, 1.25f));
-        GUT_CUDA(h, ensure(h->records_bwd, M * sizeof(GutRecordBwd), s, 1.25f));
         if (max_list > 12288) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
         {
             StageTimer t(h, ST_EMIT, s);
@@ -348,14 +347,14 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         }
         {
             StageTimer t(h, ST_SORT, s);
-            GUT_CUDA(h, gut_launch_tile_sort(fr, N, max_list, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p, d_density,
-                                             (const float4*)h->features.p, (uint32_t*)h->sorted_idx.p, (GutRecord*)h->records.p,
-                                             (GutRecordBwd*)h->records_bwd.p, s));
+            GUT_CUDA(h, gut_launch_tile_sort(fr, N, max_list, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p,
+                                             (uint32_t*)h->sorted_idx.p, s));
             h->launches += max_list > 4096 ? 2 : 1;
         }
         {
             StageTimer t(h, ST_RENDER, s);
-            GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p, d_ray_ori, d_ray_dir,
+            const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)d_density, (const float4*)h->features.p};
+            GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
                                           d_rgba, d_dist, d_hits, nullptr, s));
             h->launches += 1;
         }
@@ -411,8 +410,8 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
     if (!accumulate) GUT_CUDA(h, cudaMemsetAsync(d_density_grad, 0, (size_t)N * 48, s));
     if (h->fwd_M > 0) {
         StageTimer t(h, ST_BWD_RENDER, s);
-        GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p,
-                                               (const GutRecordBwd*)h->records_bwd.p, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
+        const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)d_density, (const float4*)h->features.p};
+        GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
                                                d_density_grad, (float4*)h->feature_grad.p, s));
         h->launches += 1;
     }
@@ -513,7 +512,8 @@ int gut_measure_work(GutHandle* h, void* stream_, const float* d_ray_ori, const 
     DeviceGuard guard(h->device);
     GUT_CUDA(h, ensure(h->stats, 16, s));
     GUT_CUDA(h, cudaMemsetAsync(h->stats.p, 0, 16, s));
-    GUT_CUDA(h, gut_launch_render(h->cfg, h->fwd_frame, (const uint32_t*)h->tile_start.p, (const GutRecord*)h->records.p, d_ray_ori, d_ray_dir,
+    const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)h->fwd_density, (const float4*)h->features.p};
+    GUT_CUDA(h, gut_launch_render(h->cfg, h->fwd_frame, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
                                   nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, s));
     unsigned long long host[2] = {0, 0};
     GUT_CUDA(h, cudaMemcpyAsync(host, h->stats.p, 16, cudaMemcpyDeviceToHost, s));

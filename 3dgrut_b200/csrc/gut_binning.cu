@@ -121,21 +121,11 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
 // segment of the bucket, counts its digits into warp-private counters, one scan over (digit, warp) gives each
 // warp its output cursors, and the warp scatters its segment 32 keys at a time ranking equal digits with
 // match.any -- three CTA barriers per pass, no per-round barriers.
-// The epilogue gathers the parameters of the sorted particles, builds the 80 B + 48 B records in shared memory
-// and writes them with bulk async copies (TMA, shared -> global), so HBM sees only full, contiguous lines.
+// The output is the sorted particle list only (4 B per intersection); the compositing kernels gather and expand
+// the particle parameters themselves, one batch ahead of their walk, where that latency hides behind FP32 work.
 // ---------------------------------------------------------------------------------------------------
 constexpr uint32_t SORT_RADIX_BITS = 8;
 constexpr uint32_t SORT_BINS = 1u << SORT_RADIX_BITS;
-constexpr uint32_t SORT_CHUNK = 256;  // records staged per bulk store (256 x 128 B = 32 KB)
-
-GUT_D uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-GUT_D void bulk_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_addr(ssrc)), "r"(bytes) : "memory");
-}
-GUT_D void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-GUT_D void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-GUT_D void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
 template <int WARPS>
 struct SortShared {
     uint32_t warp_cnt[WARPS][SORT_BINS];  // per-warp digit counts, then per-warp output cursors
@@ -204,10 +194,7 @@ template <int THREADS, uint32_t CAP>
 __global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uint32_t N, const uint32_t* __restrict__ tile_start,
                                                                 uint2* __restrict__ entries, uint2* __restrict__ scratch,
                                                                 uint32_t n_min, uint32_t n_max,
-                                                                const float4* __restrict__ density12,
-                                                                const float4* __restrict__ features,
-                                                                uint32_t* __restrict__ sorted_idx, GutRecord* __restrict__ records,
-                                                                GutRecordBwd* __restrict__ records_bwd) {
+                                                                uint32_t* __restrict__ sorted_idx) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ SortShared<THREADS / 32> sh;
 
@@ -267,46 +254,8 @@ __global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uin
     }
     __syncthreads();
 
-    // ---- epilogue: sorted particle list + record streams (contiguous per tile) ----
-    // staging area: the buffer pair the sort no longer needs (or all of shared memory on the global path)
-    unsigned char* stage = in_smem ? reinterpret_cast<unsigned char*>(kb) : smem_raw;   // kb starts the free [key|val] pair
-    float4* st_rec = reinterpret_cast<float4*>(stage);
-    float4* st_bwd = reinterpret_cast<float4*>(stage + SORT_CHUNK * sizeof(GutRecord));
-    for (uint32_t c0 = 0; c0 < n; c0 += SORT_CHUNK) {
-        const uint32_t cnt = min(SORT_CHUNK, n - c0);
-        for (uint32_t i = tid; i < cnt; i += THREADS) {
-            const uint32_t p = va[c0 + i];
-            sorted_idx[b0 + c0 + i] = p;
-            const float4 r0 = __ldg(density12 + 3 * (size_t)p);
-            const float4 q = __ldg(density12 + 3 * (size_t)p + 1);
-            const float4 r2 = __ldg(density12 + 3 * (size_t)p + 2);
-            const float4 ft = __ldg(features + p);
-            float3 c0v, c1v, c2v;
-            quat_to_columns(q.x, q.y, q.z, q.w, c0v, c1v, c2v);  // columns of R == rows of R^T
-            const float ix = 1.0f / r2.x, iy = 1.0f / r2.y, iz = 1.0f / r2.z;
-            const float3 m0 = c0v * ix, m1 = c1v * iy, m2 = c2v * iz;  // rows of ms = diag(1/s) R^T
-            const float3 v = fr.cam_centre - f3(r0.x, r0.y, r0.z);     // frame origin - position
-            float4* out = st_rec + 5 * i;
-            out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
-            out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
-            out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
-            out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
-            out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p));
-            float4* outb = st_bwd + 3 * i;
-            outb[0] = q;
-            outb[1] = make_float4(ix, iy, iz, 0.0f);
-            outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
-        }
-        fence_async_smem();   // generic-proxy writes above -> visible to the async proxy that reads them below
-        __syncthreads();
-        if (tid == 0) {
-            bulk_s2g(records + b0 + c0, st_rec, cnt * (uint32_t)sizeof(GutRecord));
-            bulk_s2g(records_bwd + b0 + c0, st_bwd, cnt * (uint32_t)sizeof(GutRecordBwd));
-            bulk_commit();
-            bulk_wait_read();   // the staging area may be overwritten (or the CTA may exit) once the copies have read it
-        }
-        __syncthreads();
-    }
+    // sorted particle list of the tile (the compositing kernels gather the parameters themselves)
+    for (uint32_t i = tid; i < n; i += THREADS) sorted_idx[b0 + i] = va[i];
 }
 
 // reference-shaped debug outputs: sorted u64 keys (tile<<32 | depth bits) and uvec2 tile ranges ((0,0) for empty tiles,
@@ -348,8 +297,7 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 }
 
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries,
-                                 uint2* scratch, const float* density12, const float4* features, uint32_t* sorted_idx,
-                                 GutRecord* records, GutRecordBwd* records_bwd, cudaStream_t stream) {
+                                 uint2* scratch, uint32_t* sorted_idx, cudaStream_t stream) {
     // small buckets: 256 threads, 4096-entry shared buffers (64 KB -> 3 CTAs per SM);
     // large buckets: 512 threads, 12288-entry buffers (192 KB, one CTA per SM); above that the passes run over global memory.
     constexpr uint32_t CAP_S = 4096, CAP_L = 12288;
@@ -362,12 +310,10 @@ cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const float4* d12 = reinterpret_cast<const float4*>(density12);
-    gut_tile_sort_kernel<256, CAP_S><<<frame.num_tiles, 256, smem_s, stream>>>(frame, N, tile_start, entries, scratch, 1u, CAP_S, d12, features,
-                                                                              sorted_idx, records, records_bwd);
+    gut_tile_sort_kernel<256, CAP_S><<<frame.num_tiles, 256, smem_s, stream>>>(frame, N, tile_start, entries, scratch, 1u, CAP_S, sorted_idx);
     if (max_list > CAP_S)
         gut_tile_sort_kernel<512, CAP_L><<<frame.num_tiles, 512, smem_l, stream>>>(frame, N, tile_start, entries, scratch, CAP_S + 1u, 0xffffffffu,
-                                                                                  d12, features, sorted_idx, records, records_bwd);
+                                                                                  sorted_idx);
     return cudaGetLastError();
 }
 

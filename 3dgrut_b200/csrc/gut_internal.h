@@ -18,12 +18,14 @@ struct GutFrame {
     float ut_delta;             // sqrt(alpha^2 (3 + kappa)), narrowed from double (setup_3dgut.py:45)
 };
 
-// One sorted (tile, particle) intersection, expanded for the compositing kernels ("record stream").
-// 80 B = 5 x float4, written in sorted order by the tile-sort kernel so a batch is one contiguous
-// cp.async.bulk copy.  ms = diag(1/scale) * R^T maps world offsets to the particle's canonical
-// (unit-Gaussian) frame; go = ms * (frame origin - position) is the canonical ray origin of every ray that
-// starts at the frame origin (GutFrame::cam_centre) -- all of them for pinhole / fisheye ray bundles --
-// so a ray/particle test needs ONE mat-vec (the direction), not two.
+// What the compositing kernels stage per sorted (tile, particle) intersection.  The sorted particle list of a tile
+// (u32 indices, contiguous) arrives in shared memory by TMA bulk copy; the particle parameters it points to are
+// gathered with 16-byte cp.async copies one batch ahead of the walk and expanded in shared memory into:
+//   GutRecord (80 B = 5 x float4): ms = diag(1/scale) * R^T maps world offsets to the particle's canonical
+//     (unit-Gaussian) frame; go = ms * (frame origin - position) is the canonical ray origin of every ray that
+//     starts at the frame origin (GutFrame::cam_centre) -- all of them for pinhole / fisheye ray bundles -- so a
+//     ray/particle test needs ONE mat-vec (the direction), not two;
+//   GutRecordBwd (48 B, backward only): quaternion, 1/scale, position.
 struct __align__(16) GutRecord {
     float ms0x, ms0y, ms0z, gox;    // row 0 of ms | go.x
     float ms1x, ms1y, ms1z, goy;    // row 1       | go.y
@@ -33,14 +35,19 @@ struct __align__(16) GutRecord {
     uint32_t idx;                   // particle index
 };
 static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
-
-// Backward-only side stream, same order as the records (48 B = 3 x float4).
 struct __align__(16) GutRecordBwd {
     float qw, qx, qy, qz;           // quaternion (w,x,y,z)
     float isx, isy, isz, pad0;      // 1 / scale
     float px, py, pz, pad1;         // position
 };
 static_assert(sizeof(GutRecordBwd) == 48, "backward record must be 3 float4");
+
+// Global-memory sources of the per-intersection data.
+struct GutParticleSource {
+    const uint32_t* sorted_idx;   // [M]  particle index per sorted intersection, tiles contiguous (tile_start)
+    const float4* density12;      // [N,3] {pos, density | quat wxyz | scale, pad}
+    const float4* features;       // [N]  SH radiance + 0.5 (unclamped) from K1
+};
 
 // Device buffers of the per-particle projection stage (K1 outputs).
 struct GutProjBuffers {
@@ -68,21 +75,20 @@ cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t
 cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_t N, GutProjBuffers proj,
                             const uint32_t* tile_start, uint32_t* tile_cursor, uint2* entries, cudaStream_t stream);
 
-// per-tile sort of (depth, idx) + expansion into the record stream; scratch = alt buffer for oversize tiles
+// per-tile sort of the (depth, idx) buckets -> sorted particle list; scratch = alt buffer for oversize tiles
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries, uint2* scratch,
-                                 const float* density12, const float4* features, uint32_t* sorted_idx, GutRecord* records,
-                                 GutRecordBwd* records_bwd, cudaStream_t stream);
+                                 uint32_t* sorted_idx, cudaStream_t stream);
 
 // debug/parity: rebuild the reference-shaped sorted key array and tile ranges
 cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_start, const uint32_t* sorted_idx, const float* depth,
                                    uint64_t* sorted_keys, uint32_t* ranges, cudaStream_t stream);
 
-cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
+cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters /* non-null: count tests/hits instead of rendering */, cudaStream_t stream);
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
-                                       const GutRecord* records, const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir,
+                                       GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
                                        float* density_grad, float4* feature_grad, cudaStream_t stream);
 

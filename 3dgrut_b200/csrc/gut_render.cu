@@ -10,9 +10,13 @@
 // < 2 %), so the design minimises SASS instructions per ray x particle test:
 //  * one CTA per 16x16 tile, 8 warps, each warp owns a compact 8x4 pixel block (more lanes hit the same
 //    particle than with the reference's 16x2 rows -> better SIMT efficiency in the divergent hit branch);
-//  * the tile's particles arrive as a contiguous 80-byte record stream written in sorted order by the
-//    tile-sort kernel, so a batch is ONE cp.async.bulk (TMA bulk copy, UBLKCP) into shared memory, completed
-//    on an mbarrier and double buffered against compute; no per-thread gathers, no quaternion->matrix math here;
+//  * staging runs one batch (256 particles) ahead of the walk and costs the walk nothing: the batch's slice of the
+//    sorted particle list is contiguous and arrives by cp.async.bulk (TMA bulk copy, UBLKCP) on an mbarrier; every
+//    thread then gathers ONE particle's parameters (3 x 16 B + its K1 colour) with cp.async (LDGSTS, no registers
+//    held across the walk) and, when the batch is due, expands them once into an 80-byte shared-memory record that
+//    all 256 rays of the tile read by broadcast -- quaternion->matrix math happens once per (tile, particle), not
+//    per ray.  DRAM sits at ~2 % during compositing, so the gathers are free; writing the records to HBM from the
+//    sort kernel instead (tried first) cost 1 ms per view;
 //  * records carry ms = diag(1/s) R^T and go = ms (frame origin - position).  When every ray of the tile starts
 //    at the frame origin (true for pinhole and fisheye bundles; checked per CTA, bitwise) the canonical ray origin
 //    is go itself and a test is ONE mat-vec, a cross product, one MUFU.RCP and one MUFU.EX2; otherwise go is
@@ -29,7 +33,7 @@
 namespace {
 
 constexpr int RENDER_THREADS = 256;
-constexpr int BATCH = 256;  // records per shared-memory stage (20 KB)
+constexpr int BATCH = 256;  // particles per staged batch = one per thread
 
 // ---- mbarrier / bulk-copy PTX -------------------------------------------------------------------------
 GUT_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -218,17 +222,118 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
     }
 }
 
+// ---- batch staging shared by K4 and K5 --------------------------------------------------------------------
+GUT_D void cp_async16(void* sdst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(sdst)), "l"(gsrc) : "memory");
+}
+GUT_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+GUT_D void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+constexpr uint32_t IDX_STAGE_WORDS = BATCH + 4;   // a batch's slice of the sorted list, widened to 16-byte alignment
+
+template <bool BWD>
+struct StageLayout {
+    static constexpr uint32_t REC = BATCH * sizeof(GutRecord);
+    static constexpr uint32_t RECB = BWD ? BATCH * sizeof(GutRecordBwd) : 0;
+    static constexpr uint32_t RAW = BATCH * 4 * sizeof(float4);
+    static constexpr uint32_t IDX = 2 * IDX_STAGE_WORDS * sizeof(uint32_t);
+    static constexpr uint32_t TOTAL = REC + RECB + RAW + IDX;
+};
+
+// Per-CTA staging pipeline (see the header comment).  Batch bi of the tile is: idx slice by TMA (issued two batches
+// ahead by thread 0), raw parameter gather by cp.async (issued one batch ahead by every thread), expansion into
+// rec/recb right before the walk.
+template <bool BWD>
+struct TileStager {
+    float4* rec; float4* recb; float4* raw; uint32_t* idx; uint64_t* bar;
+    GutParticleSource src;
+    uint32_t b0, n, nb;
+    float3 origin;
+    uint32_t p_next;   // particle this thread gathers for the batch in flight
+
+    GUT_D void init(unsigned char* smem, uint64_t* bars, const GutParticleSource& s, uint32_t b0_, uint32_t n_, float3 origin_) {
+        rec = reinterpret_cast<float4*>(smem);
+        recb = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC);
+        raw = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB);
+        idx = reinterpret_cast<uint32_t*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB + StageLayout<BWD>::RAW);
+        bar = bars; src = s; b0 = b0_; n = n_; nb = (n_ + BATCH - 1) / BATCH; origin = origin_; p_next = 0;
+    }
+    GUT_D uint32_t count(uint32_t bi) const { return min((uint32_t)BATCH, n - bi * BATCH); }
+    // thread 0: bulk-copy the 16-byte aligned superset of sorted_idx[b0 + bi*BATCH, +count)
+    GUT_D void issue_idx(uint32_t bi) {
+        const uint32_t g = b0 + bi * BATCH, a = g & ~3u;
+        const uint32_t bytes = (((g - a) + count(bi)) * 4u + 15u) & ~15u;
+        mbar_expect_tx(&bar[bi & 1], bytes);
+        bulk_g2s(idx + (bi & 1) * IDX_STAGE_WORDS, src.sorted_idx + a, bytes, &bar[bi & 1]);
+    }
+    // every thread: gather the parameters of its particle of batch bi into the raw planes
+    GUT_D void issue_gather(uint32_t bi) {
+        mbar_wait(&bar[bi & 1], (bi >> 1) & 1);
+        const uint32_t t = threadIdx.x;
+        if (t < count(bi)) {
+            const uint32_t p = idx[(bi & 1) * IDX_STAGE_WORDS + ((b0 + bi * BATCH) & 3u) + t];
+            p_next = p;
+            cp_async16(raw + t, src.density12 + 3 * (size_t)p);
+            cp_async16(raw + BATCH + t, src.density12 + 3 * (size_t)p + 1);
+            cp_async16(raw + 2 * BATCH + t, src.density12 + 3 * (size_t)p + 2);
+            cp_async16(raw + 3 * BATCH + t, src.features + p);
+        }
+        cp_async_commit();
+    }
+    // every thread: its gathered particle -> record (the walk of the previous batch must be over: rec is single buffered)
+    GUT_D void expand(uint32_t bi) {
+        cp_async_wait_all();
+        const uint32_t t = threadIdx.x, cnt = count(bi);
+        if (t < cnt) {
+            const float4 r0 = raw[t], q = raw[BATCH + t], r2 = raw[2 * BATCH + t], ft = raw[3 * BATCH + t];
+            float3 c0, c1, c2;
+            quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
+            const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
+            const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
+            const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
+            float4* out = rec + 5 * t;
+            out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
+            out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
+            out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
+            out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
+            out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next));
+            if (BWD) {
+                float4* outb = recb + 3 * t;
+                outb[0] = q;
+                outb[1] = make_float4(ix, iy, iz, 0.0f);
+                outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
+            }
+        }
+        pad_batch_tail(rec, cnt);
+    }
+    // prologue: idx slices of batches 0 and 1, gather of batch 0 (call after the barriers are initialised and published)
+    GUT_D void start() {
+        if (nb == 0) return;
+        if (threadIdx.x == 0) { issue_idx(0); if (nb > 1) issue_idx(1); }
+        issue_gather(0);
+    }
+    // after the CTA barrier that publishes rec of batch bi: put batch bi+1 (gather) and bi+2 (idx slice) in flight
+    GUT_D void advance(uint32_t bi) {
+        if (bi + 1 < nb) issue_gather(bi + 1);
+        if (threadIdx.x == 0 && bi + 2 < nb) issue_idx(bi + 2);   // stage bi&1 was last read by issue_gather(bi), one barrier ago
+    }
+    // early exit after batch bi: let everything in flight land before the CTA retires
+    GUT_D void drain(uint32_t bi) {
+        cp_async_wait_all();
+        if (bi + 2 < nb) mbar_wait(&bar[bi & 1], ((bi + 2) >> 1) & 1);
+    }
+};
+
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
 __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
-                                                                    const GutRecord* __restrict__ records,
+                                                                    GutParticleSource src,
                                                                     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                     float4* __restrict__ rgba, float* __restrict__ dist,
                                                                     float* __restrict__ hits, unsigned long long* __restrict__ counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr uint32_t STAGE_BYTES = BATCH * sizeof(GutRecord);
-    __shared__ __align__(8) uint64_t full_bar[2];
+    __shared__ __align__(8) uint64_t idx_bar[2];
 
     const uint32_t tile = blockIdx.x;
     uint32_t px, py;
@@ -242,46 +347,28 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
     const bool at_origin = (dlt.x == 0.0f) && (dlt.y == 0.0f) && (dlt.z == 0.0f);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
-    const uint32_t n = b1 - b0;
-    const uint32_t nb = (n + BATCH - 1) / BATCH;
+    TileStager<false> stg;
+    stg.init(smem_raw, idx_bar, src, b0, b1 - b0, fr.cam_centre);
 
     if (threadIdx.x == 0) {
-        mbar_init(&full_bar[0], 1);
-        mbar_init(&full_bar[1], 1);
+        mbar_init(&idx_bar[0], 1);
+        mbar_init(&idx_bar[1], 1);
         fence_mbar_init();
     }
     const bool uniform = __syncthreads_and(at_origin || !inside) != 0;  // also publishes the barrier initialisation
-    if (threadIdx.x == 0 && nb > 0) {
-        const uint32_t cnt = min((uint32_t)BATCH, n);
-        mbar_expect_tx(&full_bar[0], cnt * (uint32_t)sizeof(GutRecord));
-        bulk_g2s(smem_raw, records + b0, cnt * (uint32_t)sizeof(GutRecord), &full_bar[0]);
-    }
+    stg.start();
 
     FwdState st;
     st.T = 1.0f; st.D = 0.0f; st.cr = st.cg = st.cb = 0.0f; st.nhits = 0; st.ntests = 0;
     st.alive = inside && ray.valid;
-    uint32_t b = 0;
-    for (; b < nb; ++b) {
-        const uint32_t cnt = min((uint32_t)BATCH, n - b * BATCH);
-        if (threadIdx.x == 0 && b + 1 < nb) {
-            // stage (b+1)&1 was last read in iteration b-1, which ended with a CTA barrier
-            const uint32_t c2 = min((uint32_t)BATCH, n - (b + 1) * BATCH);
-            mbar_expect_tx(&full_bar[(b + 1) & 1], c2 * (uint32_t)sizeof(GutRecord));
-            bulk_g2s(smem_raw + ((b + 1) & 1) * STAGE_BYTES, records + b0 + (size_t)(b + 1) * BATCH, c2 * (uint32_t)sizeof(GutRecord),
-                     &full_bar[(b + 1) & 1]);
-        }
-        mbar_wait(&full_bar[b & 1], (b >> 1) & 1);
-        float4* rec = reinterpret_cast<float4*>(smem_raw + (b & 1) * STAGE_BYTES);
-        if (cnt & (WALK_UNROLL - 1)) {  // only the last batch of a tile can be ragged (CTA-uniform condition)
-            pad_batch_tail(rec, cnt);
-            __syncthreads();
-        }
-        if (uniform) forward_walk<DEG, true, COUNT>(cfg, rec, cnt, ray, dlt, st);
-        else forward_walk<DEG, false, COUNT>(cfg, rec, cnt, ray, dlt, st);
-        if (__syncthreads_and(!st.alive)) break;
+    for (uint32_t b = 0; b < stg.nb; ++b) {
+        stg.expand(b);
+        __syncthreads();
+        stg.advance(b);
+        if (uniform) forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, dlt, st);
+        else forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, dlt, st);
+        if (__syncthreads_and(!st.alive)) { stg.drain(b); break; }   // the tile saturated early
     }
-    // the tile saturated early while the next batch was already in flight: let the copy land before the CTA retires
-    if (b + 1 < nb) mbar_wait(&full_bar[(b + 1) & 1], ((b + 1) >> 1) & 1);
     if (COUNT) {
         unsigned long long t = st.ntests, hh = st.nhits;
 #pragma unroll
@@ -464,14 +551,12 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 
 template <int DEG>
 __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
-    GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, const GutRecord* __restrict__ records,
-    const GutRecordBwd* __restrict__ records_bwd, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
+    GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
+    const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ density_grad, float4* __restrict__ feature_grad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr uint32_t REC_BYTES = BATCH * sizeof(GutRecord), RECB_BYTES = BATCH * sizeof(GutRecordBwd);
-    constexpr uint32_t STAGE_BYTES = REC_BYTES + RECB_BYTES;  // [records | backward records] per stage
-    __shared__ __align__(8) uint64_t full_bar[2];
+    __shared__ __align__(8) uint64_t idx_bar[2];
 
     const uint32_t tile = blockIdx.x;
     const uint32_t lane = threadIdx.x & 31;
@@ -502,69 +587,57 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
     }
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
-    const uint32_t n = b1 - b0;
-    const uint32_t nb = (n + BATCH - 1) / BATCH;
+    TileStager<true> stg;
+    stg.init(smem_raw, idx_bar, src, b0, b1 - b0, fr.cam_centre);
 
     if (threadIdx.x == 0) {
-        mbar_init(&full_bar[0], 1);
-        mbar_init(&full_bar[1], 1);
+        mbar_init(&idx_bar[0], 1);
+        mbar_init(&idx_bar[1], 1);
         fence_mbar_init();
     }
     const bool uniform = __syncthreads_and(at_origin || !inside) != 0;
-    auto issue = [&](uint32_t bi) {
-        const uint32_t c = min((uint32_t)BATCH, n - bi * BATCH);
-        uint64_t* bar = &full_bar[bi & 1];
-        mbar_expect_tx(bar, c * (uint32_t)(sizeof(GutRecord) + sizeof(GutRecordBwd)));
-        unsigned char* base = smem_raw + (bi & 1) * STAGE_BYTES;
-        bulk_g2s(base, records + b0 + (size_t)bi * BATCH, c * (uint32_t)sizeof(GutRecord), bar);
-        bulk_g2s(base + REC_BYTES, records_bwd + b0 + (size_t)bi * BATCH, c * (uint32_t)sizeof(GutRecordBwd), bar);
-    };
-    if (threadIdx.x == 0 && nb > 0) issue(0);
+    stg.start();
 
-    uint32_t b = 0;
-    for (; b < nb; ++b) {
-        const uint32_t cnt = min((uint32_t)BATCH, n - b * BATCH);
-        if (threadIdx.x == 0 && b + 1 < nb) issue(b + 1);
-        mbar_wait(&full_bar[b & 1], (b >> 1) & 1);
-        const float4* rec = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES);
-        const float4* recb = reinterpret_cast<const float4*>(smem_raw + (b & 1) * STAGE_BYTES + REC_BYTES);
-        if (uniform) backward_walk<DEG, true>(cfg, rec, recb, cnt, ray, dlt, st, lane, density_grad, feature_grad);
-        else backward_walk<DEG, false>(cfg, rec, recb, cnt, ray, dlt, st, lane, density_grad, feature_grad);
-        if (__syncthreads_and(!st.alive)) break;
+    for (uint32_t b = 0; b < stg.nb; ++b) {
+        stg.expand(b);
+        __syncthreads();
+        stg.advance(b);
+        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, density_grad, feature_grad);
+        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, density_grad, feature_grad);
+        if (__syncthreads_and(!st.alive)) { stg.drain(b); break; }
     }
-    if (b + 1 < nb) mbar_wait(&full_bar[(b + 1) & 1], ((b + 1) >> 1) & 1);
 }
 
 template <int DEG>
-cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
+cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters, cudaStream_t stream) {
-    const size_t smem = 2 * BATCH * sizeof(GutRecord);
+    const size_t smem = StageLayout<false>::TOTAL;
     cudaError_t e;
     if (counters) {
         e = cudaFuncSetAttribute(gut_render_kernel<DEG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        gut_render_kernel<DEG, true><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, records, ray_ori, ray_dir,
+        gut_render_kernel<DEG, true><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
                                                                                       nullptr, nullptr, nullptr, counters);
     } else {
         e = cudaFuncSetAttribute(gut_render_kernel<DEG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        gut_render_kernel<DEG, false><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, records, ray_ori, ray_dir,
+        gut_render_kernel<DEG, false><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
                                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr);
     }
     return cudaGetLastError();
 }
 
 template <int DEG>
-cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
-                                  const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir, const float* rgba,
+cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
+                                  const float* ray_ori, const float* ray_dir, const float* rgba,
                                   const float* rgba_grad, const float* dist, const float* dist_grad, float* density_grad,
                                   float4* feature_grad, cudaStream_t stream) {
-    const size_t smem = 2 * BATCH * (sizeof(GutRecord) + sizeof(GutRecordBwd));
+    const size_t smem = StageLayout<true>::TOTAL;
     cudaError_t e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     gut_render_backward_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(
-        cfg, frame, tile_start, records, records_bwd, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+        cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
         reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, density_grad, feature_grad);
     return cudaGetLastError();
 }
@@ -583,20 +656,20 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
     default: return cudaErrorInvalidValue;             \
     }
 
-cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, const GutRecord* records,
+cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters, cudaStream_t stream) {
-#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, records, ray_ori, ray_dir, rgba, dist, hits, counters, stream)
+#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, counters, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_FWD)
 #undef CALL_FWD
 }
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
-                                       const GutRecord* records, const GutRecordBwd* records_bwd, const float* ray_ori, const float* ray_dir,
+                                       GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
                                        float* density_grad, float4* feature_grad, cudaStream_t stream) {
 #define CALL_BWD(D) \
-    launch_render_bwd_deg<D>(cfg, frame, tile_start, records, records_bwd, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, density_grad, feature_grad, stream)
+    launch_render_bwd_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, density_grad, feature_grad, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_BWD)
 #undef CALL_BWD
 }
