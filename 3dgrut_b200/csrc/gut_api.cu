@@ -38,7 +38,7 @@ struct GutHandle {
     uint64_t launches = 0;
 
     // per-particle workspace (K1 outputs) -- grow only, like GutRenderForwardContext (gutRenderer.cu:166-203)
-    DevBuf tiles_count, proj_pos, conic, extent, depth, features, feature_grad;
+    DevBuf tiles_count, proj_pos, conic, extent, depth, features, raw_grad;
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
@@ -270,7 +270,7 @@ void gut_destroy(GutHandle* h) {
     if (!h) return;
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
-    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->feature_grad, &h->tile_hist,
+    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->raw_grad, &h->tile_hist,
                      &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
@@ -405,20 +405,22 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
     if (h->cfg.enable_kernel_timings) start_timer(h->timers, 1, s);
     const GutFrame& fr = h->fwd_frame;
 
-    GUT_CUDA(h, ensure(h->feature_grad, (size_t)N * 16, s));
-    GUT_CUDA(h, cudaMemsetAsync(h->feature_grad.p, 0, (size_t)N * 16, s));
-    if (!accumulate) GUT_CUDA(h, cudaMemsetAsync(d_density_grad, 0, (size_t)N * 48, s));
+    // per-particle accumulators of K5 ([N,16] floats): zeroed when (re)allocated, reset by K6 after every use
+    if ((size_t)N * 64 > h->raw_grad.cap || !h->raw_grad.p) {
+        GUT_CUDA(h, ensure(h->raw_grad, (size_t)N * 64, s));
+        GUT_CUDA(h, cudaMemsetAsync(h->raw_grad.p, 0, h->raw_grad.cap, s));
+    }
     if (h->fwd_M > 0) {
         StageTimer t(h, ST_BWD_RENDER, s);
         const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)d_density, (const float4*)h->features.p};
         GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
-                                               d_density_grad, (float4*)h->feature_grad.p, s));
+                                               (float*)h->raw_grad.p, s));
         h->launches += 1;
     }
     {
         StageTimer t(h, ST_BWD_PROJECT, s);
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
-                                                (const float4*)h->features.p, (const float4*)h->feature_grad.p, d_radiance_grad, accumulate, s));
+                                                (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad, accumulate, s));
         h->launches += 1;
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);

@@ -66,7 +66,7 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        const float4* feature_grad, float* sph_grad, int accumulate, cudaStream_t stream);
+                                        float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream);
 
 // exclusive scan of tile_hist[T] -> tile_start[T+1]; also zeroes tile_cursor[T], writes stats[0]=M, stats[1]=max list
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
@@ -90,7 +90,7 @@ cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
                                        GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
-                                       float* density_grad, float4* feature_grad, cudaStream_t stream);
+                                       float* raw_grad /* [N,16] accumulators, see gut_render.cu backward_walk */, cudaStream_t stream);
 
 cudaError_t gut_launch_fill_outputs(uint32_t num_pixels, float* rgba, float* dist, float* hits, cudaStream_t stream);
 cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream);

@@ -272,41 +272,93 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K6.  dL/dSH = basis(dir) x (dL/dfeature masked by feature > 0).  One thread per particle; particles the
-// frame did not touch get zeros (accumulate == 0) so no separate memset pass over [N,48] is needed.
+// K6.  Per particle: (i) turn the ray-summed canonical-frame accumulators of K5 (layout: gut_render.cu, backward_walk)
+// into the [N,12] parameter gradient -- the per-particle tail of processHitBwd (gaussianParticles.cuh:690-738:
+// matmul_bw_vec, matmul_bw_quat, the 1/s factors), done once per particle instead of once per ray; (ii) dL/dSH =
+// basis(dir) x (dL/dfeature masked by feature > 0)  (gutProjector.cuh:390-430, gaussianParticles.cuh:120-187).
+// Particles the frame did not touch get zeros (accumulate == 0), so no memset pass over [N,12] / [N,48] is needed; the
+// accumulators of touched particles are reset to zero here for the next backward.
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) gut_project_backward_kernel(GutConfig cfg, GutFrame fr, uint32_t N, int sph_degree,
                                                                    const float4* __restrict__ density12,
                                                                    const uint32_t* __restrict__ tiles_count,
                                                                    const float4* __restrict__ features,
-                                                                   const float4* __restrict__ feature_grad,
+                                                                   float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
                                                                    float* __restrict__ sph_grad, int accumulate) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     const int ncoef_all = (cfg.sph_max_degree + 1) * (cfg.sph_max_degree + 1);
     const int nact = (sph_degree + 1) * (sph_degree + 1);
     float* out = sph_grad + (size_t)i * ncoef_all * 3;
+    float4* dg = density_grad + 3 * (size_t)i;
     const bool touched = tiles_count[i] != 0;
     if (!touched) {
         if (!accumulate) {
+            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            dg[0] = z; dg[1] = z; dg[2] = z;
             if (ncoef_all == 16) {
                 float4* o4 = reinterpret_cast<float4*>(out);
 #pragma unroll
-                for (int q = 0; q < 12; ++q) o4[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                for (int q = 0; q < 12; ++q) o4[q] = z;
             } else {
                 for (int k = 0; k < ncoef_all * 3; ++k) out[k] = 0.0f;
             }
         }
         return;
     }
-    const float4 r0 = __ldg(density12 + 3 * (size_t)i);
+    const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos, density
+    const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
+    const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
+    float4* rg = raw_grad + 4 * (size_t)i;
+    const float4 g0 = rg[0], g1 = rg[1], g2 = rg[2], g3 = rg[3];
+    {
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        rg[0] = z; rg[1] = z; rg[2] = z; rg[3] = z;
+    }
+    // ---- (i) parameter gradient ----
+    {
+        const float3 A = f3(g0.x, g0.y, g0.z);
+        const float d_density = g0.w;
+        const float3 tau = f3(g1.x, g1.y, g1.z);
+        const float tr_dir = g1.w;
+        const float3 Z = f3(g2.x, g2.y, g2.z);
+        const float W = g3.z;
+        const float3 is = f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z);
+        float3 c0, c1, c2;
+        quat_to_columns(qv.x, qv.y, qv.z, qv.w, c0, c1, c2);
+        const float3 As = A * is;
+        // dL/dpos = -R (A / s)
+        const float3 gpos = f3(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
+                               -(c0.z * As.x + c1.z * As.y + c2.z * As.z));
+        const float3 gscl = f3(-Z.x * is.x, -Z.y * is.y, -Z.z * is.z);
+        // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = sum Z + W ; trace = tr_dir + sum_i A_i v_i / s_i
+        const float3 vf = fr.cam_centre - f3(r0.x, r0.y, r0.z);
+        const float rho = 2.0f * ((Z.x + Z.y + Z.z + W) - (tr_dir + As.x * vf.x + As.y * vf.y + As.z * vf.z));
+        // tangential part: body-frame torque -> 2 q (x) (0, tau)
+        const float3 rv = f3(qv.y, qv.z, qv.w);
+        const float3 rxt = cross(rv, tau);
+        const float gw = rho * qv.x - 2.0f * dot(rv, tau);
+        const float3 gr = f3(rho * rv.x + 2.0f * (qv.x * tau.x + rxt.x), rho * rv.y + 2.0f * (qv.x * tau.y + rxt.y),
+                             rho * rv.z + 2.0f * (qv.x * tau.z + rxt.z));
+        float4 o0 = make_float4(gpos.x, gpos.y, gpos.z, d_density);
+        float4 o1 = make_float4(gw, gr.x, gr.y, gr.z);
+        float4 o2 = make_float4(gscl.x, gscl.y, gscl.z, 0.0f);
+        if (accumulate) {
+            const float4 p0 = dg[0], p1 = dg[1], p2 = dg[2];
+            o0.x += p0.x; o0.y += p0.y; o0.z += p0.z; o0.w += p0.w;
+            o1.x += p1.x; o1.y += p1.y; o1.z += p1.z; o1.w += p1.w;
+            o2.x += p2.x; o2.y += p2.y; o2.z += p2.z;
+        }
+        dg[0] = o0; dg[1] = o1; dg[2] = o2;
+    }
+    // ---- (ii) SH gradient ----
     const float3 v = f3(r0.x, r0.y, r0.z) - fr.cam_centre;
     const float len = sqrtf(dot(v, v));
     const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(v.x / len, v.y / len, v.z / len);
     float b[16];
     gut_sh_basis(sph_degree, dir, b);
     const float4 ft = features[i];
-    float4 g = feature_grad[i];
+    float3 g = f3(g2.w, g3.x, g3.y);
     g.x *= (ft.x > 0.0f ? 1.0f : 0.0f); g.y *= (ft.y > 0.0f ? 1.0f : 0.0f); g.z *= (ft.z > 0.0f ? 1.0f : 0.0f);
     if (ncoef_all == 16) {
         float vals[48];
@@ -353,11 +405,12 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        const float4* feature_grad, float* sph_grad, int accumulate, cudaStream_t stream) {
+                                        float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     gut_project_backward_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, frame, N, sph_degree,
                                                                       reinterpret_cast<const float4*>(density12), tiles_count,
-                                                                      features, feature_grad, sph_grad, accumulate);
+                                                                      features, reinterpret_cast<float4*>(raw_grad),
+                                                                      reinterpret_cast<float4*>(density_grad), sph_grad, accumulate);
     return cudaGetLastError();
 }
 

@@ -297,11 +297,11 @@ struct TileStager {
             out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
             out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
             out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next));
-            if (BWD) {
+            if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
                 float4* outb = recb + 3 * t;
-                outb[0] = q;
-                outb[1] = make_float4(ix, iy, iz, 0.0f);
-                outb[2] = make_float4(r0.x, r0.y, r0.z, 0.0f);
+                outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
+                outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
+                outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
             }
         }
         pad_batch_tail(rec, cnt);
@@ -441,9 +441,21 @@ struct BwdRay {
     bool alive;
 };
 
+// Per accepted hit a lane produces 15 values that are LINEAR in the ray, so they can be summed over rays first (warp
+// transpose-reduce, then one RED per value into the per-particle accumulator `raw`, 16 floats per particle) and
+// turned into parameter gradients once per particle by K6 (gut_project.cu, finish_density_gradient):
+//   [0..2]  A   = dL/d go            (canonical ray origin)        -> dL/dpos   = -ms^T A
+//   [3]     dL/d density
+//   [4..6]  tau = body-frame torque                                 -> dL/dquat  = rho q + 2 q (x) (0, tau)
+//   [7]     tr  = sum_i (dL/dR^T)_ii, direction part                -> rho (radial part of dL/dquat, R(q) is a polynomial)
+//   [8..10] Z_i = go_i A_i + u_i B_i - s_i * (hit-distance term)    -> dL/dscale_i = -Z_i / s_i
+//   [11..13] dL/d colour
+//   [14]    W   = sum_i s_i * (hit-distance scale term)             -> rho
+// with B = dL/d u.  This is the chain rule of processHitBwd (gaussianParticles.cuh:635-738) with the per-ray
+// quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.
 template <int DEG, bool UNIFORM>
 GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt, const Ray& ray,
-                         const float3 dlt, BwdRay& st, uint32_t lane, float* __restrict__ density_grad, float4* __restrict__ feature_grad) {
+                         const float3 dlt, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
     const float minT = cfg.min_transmittance;
     for (uint32_t j = 0; j < cnt; ++j) {
         if ((j & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive)) break;
@@ -458,16 +470,18 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
         for (int q = 0; q < 16; ++q) v[q] = 0.0f;
         const float4 F = r[4];
         if (hit) {
-            const float4 Q = recb[3 * j], IS = recb[3 * j + 1], P = recb[3 * j + 2];
-            const float3 s = f3(S.x, S.y, S.z);
-            const float3 go = k.go;
+            const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
+            const float isz = recb[3 * j + 2].x;
+            const float3 go = k.go, u = k.u;
             const float il = mufu_rsq(k.l2);           // 1 / |u|
-            const float3 grd = k.u * il;               // normalised canonical direction
+            const float3 grd = u * il;                 // normalised canonical direction
             const float dgo = dot(grd, go);
-            const float3 grdd = grd * (-dgo);
-            const float3 grds = s * grdd;
-            const float gsq = dot(grds, grds);
-            const float gdist = mufu_sqrt(gsq);
+            // hit distance gdist = |s * grd * dot(grd, -go)| = |dgo| * |sg|, sg = s * grd
+            const float3 sg = f3(S.x * grd.x, S.y * grd.y, S.z * grd.z);
+            const float3 sg2 = sg * sg;
+            const float sum2 = sg2.x + sg2.y + sg2.z;
+            const float gsq = dgo * dgo * sum2;
+            const float gdist = fabsf(dgo) * mufu_sqrt(sum2);
             const float alpha = fminf(cfg.max_alpha, k.araw);
             const float T = st.T;
             const float w = alpha * T;
@@ -475,16 +489,16 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             const float nextT = om * T;
             const float invT = nextT <= minT ? 0.0f : mufu_rcp(nextT);
 
-            // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's element-wise ones)
+            // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's
+            // element-wise ones).  grds = -dgo sg;  dL/dgrds = grds hs = kap sg  with  kap = -dgo hs
             st.D = fmaf(w, gdist, st.D);
             const float resD = fmaxf((st.D_f - st.D) * invT, 0.0f);
             const float aHit = (gdist - resD) * T * st.dD;
             const float hs = gsq > 0.0f ? w * st.dD * mufu_rcp(gdist) : 0.0f;
-            const float3 G = grds * hs;
-            const float3 sG = s * G;
-            const float3 sclHit = grdd * G;
-            const float3 grdHit = f3(-(grd.x * go.x + dgo) * sG.x, -(grd.y * go.y + dgo) * sG.y, -(grd.z * go.z + dgo) * sG.z);
-            const float3 groHit = f3(-grd.x * grd.x * sG.x, -grd.y * grd.y * sG.y, -grd.z * grd.z * sG.z);
+            const float kap = -dgo * hs;
+            const float kd = kap * dgo;                // s_i * sclHit_i = -kd * sg2_i
+            // grdHit_i = -kap (sg2_i go_i + dgo s_i sg_i) ; groHit_i = -kap sg2_i grd_i
+            const float3 tH = f3(fmaf(sg2.x, go.x, dgo * S.x * sg.x), fmaf(sg2.y, go.y, dgo * S.y * sg.y), fmaf(sg2.z, go.z, dgo * S.z * sg.z));
 
             // opacity and colour terms (:569-633)
             const float resT = alpha < 0.999999f ? st.T_f * mufu_rcp(om) : T;
@@ -501,51 +515,34 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             const float3 gcG = k.c * (2.0f * g2G * il);
             const float3 grdG = cross(go, gcG);
             const float3 groG = cross(gcG, grd);
-            const float3 groTot = groG + groHit;
-
-            const float3 gis = f3(IS.x, IS.y, IS.z);
-            // go = gposcr / s : d/ds = -go/s ; d/dgposcr = 1/s
-            const float3 gposcrG = gis * groTot;
-            const float3 sclGro = f3(-go.x * gposcrG.x, -go.y * gposcrG.y, -go.z * gposcrG.z);
-            // R gposcrG with rows of R^T = ms_i * s_i  ==>  sum_i groTot_i * ms_i
-            const float3 gposcG = f3(groTot.x * A.x + groTot.y * B.x + groTot.z * Cm.x, groTot.x * A.y + groTot.y * B.y + groTot.z * Cm.y,
-                                     groTot.x * A.z + groTot.y * B.z + groTot.z * Cm.z);
-            // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): (X - grd (grd . X)) / |u|
-            const float3 X = grdG + grdHit;
+            // A = dL/dgo (total), X = dL/dgrd (total)
+            const float3 Ag = f3(fmaf(-kap, sg2.x * grd.x, groG.x), fmaf(-kap, sg2.y * grd.y, groG.y), fmaf(-kap, sg2.z * grd.z, groG.z));
+            const float3 X = f3(fmaf(-kap, tH.x, grdG.x), fmaf(-kap, tH.y, grdG.y), fmaf(-kap, tH.z, grdG.z));
+            // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): B = dL/du = (X - grd (grd . X)) / |u|
             const float gx = dot(grd, X);
-            const float3 grduG = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
-            // u = rayDirR / s
-            const float3 rayDirRG = gis * grduG;
-            const float3 sclDir = f3(-k.u.x * rayDirRG.x, -k.u.y * rayDirRG.y, -k.u.z * rayDirRG.z);
+            const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
 
-            // dL/dR^T = gposcrG (x) (o - pos) + rayDirRG (x) d, contracted with dR^T/dq (matmul_bw_quat, mathUtils.cuh:468-533)
-            const float3 vv = f3(ray.o.x - P.x, ray.o.y - P.y, ray.o.z - P.z);
-            const float3 dd = ray.d;
-            const float d00 = gposcrG.x * vv.x + rayDirRG.x * dd.x, d01 = gposcrG.x * vv.y + rayDirRG.x * dd.y, d02 = gposcrG.x * vv.z + rayDirRG.x * dd.z;
-            const float d10 = gposcrG.y * vv.x + rayDirRG.y * dd.x, d11 = gposcrG.y * vv.y + rayDirRG.y * dd.y, d12 = gposcrG.y * vv.z + rayDirRG.y * dd.z;
-            const float d20 = gposcrG.z * vv.x + rayDirRG.z * dd.x, d21 = gposcrG.z * vv.y + rayDirRG.z * dd.y, d22 = gposcrG.z * vv.z + rayDirRG.z * dd.z;
-            const float qr = Q.x, qx = Q.y, qy = Q.z, qz = Q.w;
-            const float s01 = d01 + d10, a01 = d01 - d10, s02 = d02 + d20, a20 = d20 - d02, s12 = d12 + d21, a12 = d12 - d21;
-
-            v[0] = -gposcG.x; v[1] = -gposcG.y; v[2] = -gposcG.z;
+            // P_ij = go_i A_j + u_i B_j : diagonal -> scale, off-diagonal -> body-frame torque
+            v[0] = Ag.x; v[1] = Ag.y; v[2] = Ag.z;
             v[3] = dDens;
-            v[4] = 2.0f * (qz * a01 + qy * a20 + qx * a12);
-            v[5] = 2.0f * (qy * s01 + qz * s02 + qr * a12 - 2.0f * qx * (d11 + d22));
-            v[6] = 2.0f * (qx * s01 + qz * s12 + qr * a20 - 2.0f * qy * (d00 + d22));
-            v[7] = 2.0f * (qx * s02 + qy * s12 + qr * a01 - 2.0f * qz * (d00 + d11));
-            v[8] = sclHit.x + sclGro.x + sclDir.x; v[9] = sclHit.y + sclGro.y + sclDir.y; v[10] = sclHit.z + sclGro.z + sclDir.z;
+            v[4] = R0.y * fmaf(go.z, Ag.y, u.z * Bg.y) - R0.x * fmaf(go.y, Ag.z, u.y * Bg.z);   // rho_zy P_zy - rho_yz P_yz
+            v[5] = R0.z * fmaf(go.x, Ag.z, u.x * Bg.z) - R0.w * fmaf(go.z, Ag.x, u.z * Bg.x);   // rho_xz P_xz - rho_zx P_zx
+            v[6] = R1.x * fmaf(go.y, Ag.x, u.y * Bg.x) - R1.y * fmaf(go.x, Ag.y, u.x * Bg.y);   // rho_yx P_yx - rho_xy P_xy
+            float tr = R1.z * Bg.x * ray.d.x + R1.w * Bg.y * ray.d.y + isz * Bg.z * ray.d.z;
+            if (!UNIFORM) tr += R1.z * Ag.x * dlt.x + R1.w * Ag.y * dlt.y + isz * Ag.z * dlt.z;
+            v[7] = tr;
+            v[8] = fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x));
+            v[9] = fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y));
+            v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));
             v[11] = w * st.dC.x; v[12] = w * st.dC.y; v[13] = w * st.dC.z;
+            v[14] = -kd * sum2;
 
             st.T = nextT;
             if (nextT < minT) st.alive = false;
         }
         const float total = warp_transpose_reduce16(v, lane);
         const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
-        if ((lane & 1u) == 0u && slot < 14u) {
-            const uint32_t p = __float_as_uint(F.w);
-            float* dst = slot < 11u ? density_grad + 12 * (size_t)p + slot : reinterpret_cast<float*>(feature_grad + p) + (slot - 11u);
-            atomicAdd(dst, total);
-        }
+        if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
     }
 }
 
@@ -554,7 +551,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
-    const float* __restrict__ dist_grad, float* __restrict__ density_grad, float4* __restrict__ feature_grad) {
+    const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t idx_bar[2];
 
@@ -602,8 +599,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
         stg.expand(b);
         __syncthreads();
         stg.advance(b);
-        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, density_grad, feature_grad);
-        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, density_grad, feature_grad);
+        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, raw_grad);
+        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, raw_grad);
         if (__syncthreads_and(!st.alive)) { stg.drain(b); break; }
     }
 }
@@ -631,14 +628,14 @@ cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const
 template <int DEG>
 cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                                   const float* ray_ori, const float* ray_dir, const float* rgba,
-                                  const float* rgba_grad, const float* dist, const float* dist_grad, float* density_grad,
-                                  float4* feature_grad, cudaStream_t stream) {
+                                  const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
+                                  cudaStream_t stream) {
     const size_t smem = StageLayout<true>::TOTAL;
     cudaError_t e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     gut_render_backward_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(
         cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
-        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, density_grad, feature_grad);
+        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad);
     return cudaGetLastError();
 }
 
@@ -667,9 +664,9 @@ cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
                                        GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
-                                       float* density_grad, float4* feature_grad, cudaStream_t stream) {
+                                       float* raw_grad, cudaStream_t stream) {
 #define CALL_BWD(D) \
-    launch_render_bwd_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, density_grad, feature_grad, stream)
+    launch_render_bwd_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, raw_grad, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_BWD)
 #undef CALL_BWD
 }
