@@ -279,46 +279,48 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
 // Particles the frame did not touch get zeros (accumulate == 0), so no memset pass over [N,12] / [N,48] is needed; the
 // accumulators of touched particles are reset to zero here for the next backward.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) gut_project_backward_kernel(GutConfig cfg, GutFrame fr, uint32_t N, int sph_degree,
-                                                                   const float4* __restrict__ density12,
-                                                                   const uint32_t* __restrict__ tiles_count,
-                                                                   const float4* __restrict__ features,
-                                                                   float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
-                                                                   float* __restrict__ sph_grad, int accumulate) {
+constexpr int K6_THREADS = 128;
+constexpr int K6_WARPS = K6_THREADS / 32;
+
+// Phase A: one thread per particle computes the [N,12] gradient row and the masked colour gradient + SH basis.
+// Phase B: each warp writes its 32 rows of [N,12] (3 float4 per row) and [N,48] (12 float4 per row) as contiguous,
+// fully coalesced 128-bit accesses (12 independent loads in flight per lane when accumulating) instead of every
+// thread walking its own 192-byte row.
+__global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutConfig cfg, GutFrame fr, uint32_t N, int sph_degree,
+                                                                          const float4* __restrict__ density12,
+                                                                          const uint32_t* __restrict__ tiles_count,
+                                                                          const float4* __restrict__ features,
+                                                                          float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
+                                                                          float* __restrict__ sph_grad, int accumulate) {
+    __shared__ float4 s_dg[K6_WARPS][32 * 3];      // parameter-gradient rows of the warp
+    __shared__ float s_basis[K6_WARPS][32][17];    // SH basis per row (+1 pad: conflict-free column reads)
+    __shared__ float4 s_g[K6_WARPS][32];           // masked colour gradient per row, w = 1 if the row was touched
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
+    const uint32_t warp_base = i - lane;           // first particle of this warp
     const int ncoef_all = (cfg.sph_max_degree + 1) * (cfg.sph_max_degree + 1);
     const int nact = (sph_degree + 1) * (sph_degree + 1);
-    float* out = sph_grad + (size_t)i * ncoef_all * 3;
-    float4* dg = density_grad + 3 * (size_t)i;
-    const bool touched = tiles_count[i] != 0;
-    if (!touched) {
-        if (!accumulate) {
-            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            dg[0] = z; dg[1] = z; dg[2] = z;
-            if (ncoef_all == 16) {
-                float4* o4 = reinterpret_cast<float4*>(out);
+
+    bool touched = false;
+    float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
+    float3 g = f3(0.f, 0.f, 0.f);
+    float b[16];
 #pragma unroll
-                for (int q = 0; q < 12; ++q) o4[q] = z;
-            } else {
-                for (int k = 0; k < ncoef_all * 3; ++k) out[k] = 0.0f;
-            }
+    for (int k = 0; k < 16; ++k) b[k] = 0.0f;
+    if (i < N) touched = tiles_count[i] != 0;
+    if (touched) {
+        const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos, density
+        const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
+        const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
+        const float4 ft = __ldg(features + i);
+        float4* rg = raw_grad + 4 * (size_t)i;
+        const float4 g0 = rg[0], g1 = rg[1], g2 = rg[2], g3 = rg[3];
+        {
+            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            rg[0] = z; rg[1] = z; rg[2] = z; rg[3] = z;
         }
-        return;
-    }
-    const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos, density
-    const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
-    const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
-    float4* rg = raw_grad + 4 * (size_t)i;
-    const float4 g0 = rg[0], g1 = rg[1], g2 = rg[2], g3 = rg[3];
-    {
-        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        rg[0] = z; rg[1] = z; rg[2] = z; rg[3] = z;
-    }
-    // ---- (i) parameter gradient ----
-    {
+        // ---- (i) parameter gradient ----
         const float3 A = f3(g0.x, g0.y, g0.z);
-        const float d_density = g0.w;
         const float3 tau = f3(g1.x, g1.y, g1.z);
         const float tr_dir = g1.w;
         const float3 Z = f3(g2.x, g2.y, g2.z);
@@ -328,60 +330,88 @@ __global__ void __launch_bounds__(256) gut_project_backward_kernel(GutConfig cfg
         quat_to_columns(qv.x, qv.y, qv.z, qv.w, c0, c1, c2);
         const float3 As = A * is;
         // dL/dpos = -R (A / s)
-        const float3 gpos = f3(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
-                               -(c0.z * As.x + c1.z * As.y + c2.z * As.z));
-        const float3 gscl = f3(-Z.x * is.x, -Z.y * is.y, -Z.z * is.z);
+        o0 = make_float4(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
+                         -(c0.z * As.x + c1.z * As.y + c2.z * As.z), g0.w);
+        o2 = make_float4(-Z.x * is.x, -Z.y * is.y, -Z.z * is.z, 0.0f);
         // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = sum Z + W ; trace = tr_dir + sum_i A_i v_i / s_i
         const float3 vf = fr.cam_centre - f3(r0.x, r0.y, r0.z);
         const float rho = 2.0f * ((Z.x + Z.y + Z.z + W) - (tr_dir + As.x * vf.x + As.y * vf.y + As.z * vf.z));
         // tangential part: body-frame torque -> 2 q (x) (0, tau)
         const float3 rv = f3(qv.y, qv.z, qv.w);
         const float3 rxt = cross(rv, tau);
-        const float gw = rho * qv.x - 2.0f * dot(rv, tau);
-        const float3 gr = f3(rho * rv.x + 2.0f * (qv.x * tau.x + rxt.x), rho * rv.y + 2.0f * (qv.x * tau.y + rxt.y),
-                             rho * rv.z + 2.0f * (qv.x * tau.z + rxt.z));
-        float4 o0 = make_float4(gpos.x, gpos.y, gpos.z, d_density);
-        float4 o1 = make_float4(gw, gr.x, gr.y, gr.z);
-        float4 o2 = make_float4(gscl.x, gscl.y, gscl.z, 0.0f);
-        if (accumulate) {
-            const float4 p0 = dg[0], p1 = dg[1], p2 = dg[2];
-            o0.x += p0.x; o0.y += p0.y; o0.z += p0.z; o0.w += p0.w;
-            o1.x += p1.x; o1.y += p1.y; o1.z += p1.z; o1.w += p1.w;
-            o2.x += p2.x; o2.y += p2.y; o2.z += p2.z;
-        }
-        dg[0] = o0; dg[1] = o1; dg[2] = o2;
+        o1 = make_float4(rho * qv.x - 2.0f * dot(rv, tau), rho * rv.x + 2.0f * (qv.x * tau.x + rxt.x),
+                         rho * rv.y + 2.0f * (qv.x * tau.y + rxt.y), rho * rv.z + 2.0f * (qv.x * tau.z + rxt.z));
+        // ---- (ii) SH: masked colour gradient and basis of the view direction ----
+        const float3 v = f3(r0.x, r0.y, r0.z) - fr.cam_centre;
+        const float len = sqrtf(dot(v, v));
+        const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(v.x / len, v.y / len, v.z / len);
+        gut_sh_basis(sph_degree, dir, b);
+        g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
     }
-    // ---- (ii) SH gradient ----
-    const float3 v = f3(r0.x, r0.y, r0.z) - fr.cam_centre;
-    const float len = sqrtf(dot(v, v));
-    const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(v.x / len, v.y / len, v.z / len);
-    float b[16];
-    gut_sh_basis(sph_degree, dir, b);
-    const float4 ft = features[i];
-    float3 g = f3(g2.w, g3.x, g3.y);
-    g.x *= (ft.x > 0.0f ? 1.0f : 0.0f); g.y *= (ft.y > 0.0f ? 1.0f : 0.0f); g.z *= (ft.z > 0.0f ? 1.0f : 0.0f);
-    if (ncoef_all == 16) {
-        float vals[48];
+    s_dg[wid][3 * lane] = o0; s_dg[wid][3 * lane + 1] = o1; s_dg[wid][3 * lane + 2] = o2;
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const float bk = (k < nact) ? b[k] : 0.0f;
-            vals[3 * k] = bk * g.x; vals[3 * k + 1] = bk * g.y; vals[3 * k + 2] = bk * g.z;
-        }
-        float4* o4 = reinterpret_cast<float4*>(out);
+    for (int k = 0; k < 16; ++k) s_basis[wid][lane][k] = (k < nact) ? b[k] : 0.0f;
+    s_g[wid][lane] = make_float4(g.x, g.y, g.z, touched ? 1.0f : 0.0f);
+    __syncwarp();
+
+    const uint32_t rows = warp_base < N ? min(32u, N - warp_base) : 0u;
+    // [N,12]: 3 float4 per row, rows*3 contiguous float4
+    {
+        float4* dst = density_grad + 3 * (size_t)warp_base;
 #pragma unroll
-        for (int q = 0; q < 12; ++q) {
-            float4 t = make_float4(vals[4 * q], vals[4 * q + 1], vals[4 * q + 2], vals[4 * q + 3]);
-            if (accumulate) { const float4 o = o4[q]; t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w; }
-            o4[q] = t;
-        }
-    } else {
-        for (int k = 0; k < ncoef_all; ++k) {
-            const float bk = (k < nact) ? b[k] : 0.0f;
-            for (int ch = 0; ch < 3; ++ch) {
-                const float gv = bk * (ch == 0 ? g.x : (ch == 1 ? g.y : g.z));
-                out[3 * k + ch] = accumulate ? out[3 * k + ch] + gv : gv;
+        for (int it = 0; it < 3; ++it) {
+            const uint32_t f = it * 32 + lane;
+            const uint32_t row = f / 3;
+            if (row < rows) {
+                const bool t_row = s_g[wid][row].w != 0.0f;
+                float4 val = s_dg[wid][f];
+                if (accumulate) {
+                    if (t_row) { const float4 p = dst[f]; val.x += p.x; val.y += p.y; val.z += p.z; val.w += p.w; dst[f] = val; }
+                } else {
+                    dst[f] = val;
+                }
             }
         }
+    }
+    // [N,48]
+    if (ncoef_all == 16) {
+        float4* dst = reinterpret_cast<float4*>(sph_grad) + 12 * (size_t)warp_base;
+        float4 prev[12];
+#pragma unroll
+        for (int it = 0; it < 12; ++it) {   // all loads first: 12 independent coalesced requests per lane
+            const uint32_t f = it * 32 + lane;
+            const uint32_t row = f / 12;
+            prev[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (accumulate && row < rows && s_g[wid][row].w != 0.0f) prev[it] = dst[f];
+        }
+#pragma unroll
+        for (int it = 0; it < 12; ++it) {
+            const uint32_t f = it * 32 + lane;
+            const uint32_t row = f / 12, e0 = (f % 12) * 4;   // elements e0..e0+3 of the row: coefficient e/3, channel e%3
+            if (row < rows) {
+                const float4 gg = s_g[wid][row];
+                if (!accumulate || gg.w != 0.0f) {
+                    float val[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t e = e0 + q, kk = e / 3, ch = e - 3 * kk;
+                        const float bk = s_basis[wid][row][kk];
+                        val[q] = bk * (ch == 0 ? gg.x : (ch == 1 ? gg.y : gg.z));
+                    }
+                    dst[f] = make_float4(val[0] + prev[it].x, val[1] + prev[it].y, val[2] + prev[it].z, val[3] + prev[it].w);
+                }
+            }
+        }
+    } else if (i < N) {   // generic coefficient count: per-thread rows
+        float* out = sph_grad + (size_t)i * ncoef_all * 3;
+        if (touched || !accumulate)
+            for (int k = 0; k < ncoef_all; ++k) {
+                const float bk = (k < nact) ? b[k] : 0.0f;
+                for (int ch = 0; ch < 3; ++ch) {
+                    const float gv = bk * (ch == 0 ? g.x : (ch == 1 ? g.y : g.z));
+                    out[3 * k + ch] = accumulate ? out[3 * k + ch] + gv : gv;
+                }
+            }
     }
 }
 
@@ -407,7 +437,7 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    gut_project_backward_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, frame, N, sph_degree,
+    gut_project_backward_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree,
                                                                       reinterpret_cast<const float4*>(density12), tiles_count,
                                                                       features, reinterpret_cast<float4*>(raw_grad),
                                                                       reinterpret_cast<float4*>(density_grad), sph_grad, accumulate);
