@@ -47,6 +47,7 @@ def parse_args():
     p.add_argument("--height", type=int, default=H_IMG)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-aux", action="store_true", help="skip the auxiliary forward-only 1080p measurement")
     p.add_argument("--cpu-sample-tiles", type=int, default=24)
     return p.parse_args()
 
@@ -297,13 +298,14 @@ def run_ours(args):
 
     add_stage("render::project", "hbm", n * (48 + 56 + 192 * vis_frac), 1e9, hbm_peak, "GB/s", "48+56+192 B/particle")
     add_stage("render::expand", "hbm", n * 44 + m_v * 8, 1e9, hbm_peak, "GB/s", "44 B/particle + 8 B/intersection")
-    add_stage("render::sort", "hbm", m_v * (8 + 4 + 96 + 60), 1e9, hbm_peak, "GB/s",
-              "8 B bucket read + 4 B index + 96 B record write + 60 B parameter gather per intersection")
+    add_stage("render::sort", "hbm", m_v * (8 + 4), 1e9, hbm_peak, "GB/s",
+              "8 B bucket read + 4 B sorted-list write per intersection (the passes run in shared memory)")
     add_stage("render::render", "fp32", tests_v * FLOP_FWD_TEST + hits_v * FLOP_FWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "71 FLOP/test + 32 FLOP/hit")
     add_stage("render-backward::render", "fp32", tests_v * FLOP_BWD_TEST + hits_v * FLOP_BWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "100 FLOP/test + 250 FLOP/hit")
-    add_stage("render-backward::project", "hbm", n * (36 + 192), 1e9, hbm_peak, "GB/s", "36+192 B/particle")
+    add_stage("render-backward::project", "hbm", n * (48 + 16 + 64 + 48 + 192), 1e9, hbm_peak, "GB/s",
+              "48 B params + 16 B colour + 64 B accumulators in, 48 + 192 B gradients out per particle (accumulation re-reads not counted)")
     dominant = max(stages, key=lambda s: s["ms_per_launch"]) if stages else None
     roofline = None
     if dominant:
@@ -325,6 +327,32 @@ def run_ours(args):
             pinned.append({kk: (vv.pin_memory() if hasattr(vv, "pin_memory") else vv) for kk, vv in hv.items()})
         out_host = torch.empty((h, w, 4), dtype=torch.float32).pin_memory()
         h2d = d2h = 0
+        # Inputs of view k+1 are copied host->device on a copy stream while view k computes (two device buffer sets);
+        # the rendered RGBA goes back as ONE contiguous device->host copy per view.  All copies are inside the timed region.
+        copy_stream = torch.cuda.Stream(device=dev)
+        nbuf = 2
+        dev_in = [{"rays_ori": torch.empty((1, h, w, 3), device=dev), "rays_dir": torch.empty((1, h, w, 3), device=dev),
+                   "T_to_world": torch.empty((1, 4, 4), device=dev), "rg": torch.empty((h, w, 4), device=dev),
+                   "dg": torch.empty((h, w, 1), device=dev)} for _ in range(nbuf)]
+        rgba_dev = [torch.empty((h, w, 4), device=dev) for _ in range(nbuf)]
+        free_ev = [None] * nbuf   # recorded on the compute stream when a buffer set may be overwritten
+
+        def stage(vi):
+            nonlocal h2d
+            bi = vi % nbuf
+            pv, (rg_h, dg_h) = pinned[vi], host_up[vi]
+            with torch.cuda.stream(copy_stream):
+                if free_ev[bi] is not None:
+                    copy_stream.wait_event(free_ev[bi])
+                for kk in ("rays_ori", "rays_dir", "T_to_world"):
+                    dev_in[bi][kk].copy_(pv[kk], non_blocking=True)
+                    h2d += pv[kk].numel() * 4
+                dev_in[bi]["rg"].copy_(rg_h, non_blocking=True)
+                dev_in[bi]["dg"].copy_(dg_h, non_blocking=True)
+                h2d += (rg_h.numel() + dg_h.numel()) * 4
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            return ev
 
         def e2e_step():
             nonlocal h2d, d2h
@@ -332,23 +360,33 @@ def run_ours(args):
             for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
                 p.grad = None
             checksum = None
-            for pv, (rg_h, dg_h) in zip(pinned, host_up):
-                dv = dict(pv)
+            cur = torch.cuda.current_stream()
+            ready = stage(0) if pinned else None
+            for vi in range(len(pinned)):
+                bi = vi % nbuf
+                cur.wait_event(ready)
+                if vi + 1 < len(pinned):
+                    ready = stage(vi + 1)
+                dv = dict(pinned[vi])
                 for kk in ("rays_ori", "rays_dir", "T_to_world"):
-                    dv[kk] = pv[kk].to(dev, non_blocking=True)
-                    h2d += pv[kk].numel() * 4
-                rg = rg_h.to(dev, non_blocking=True); dg = dg_h.to(dev, non_blocking=True)
-                h2d += (rg_h.numel() + dg_h.numel()) * 4
+                    dv[kk] = dev_in[bi][kk]
+                rg, dg = dev_in[bi]["rg"], dev_in[bi]["dg"]
                 o = tracer.render(gauss, make_batch(dv, dev), train=True)
                 loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
                 loss.backward()
-                out_host[..., :3].copy_(o["pred_rgb"][0], non_blocking=True)
-                out_host[..., 3:].copy_(o["pred_opacity"][0], non_blocking=True)
+                torch.cat([o["pred_rgb"][0].detach(), o["pred_opacity"][0].detach()], dim=-1, out=rgba_dev[bi])
+                done = torch.cuda.Event()
+                done.record(cur)
+                free_ev[bi] = done
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(done)
+                    out_host.copy_(rgba_dev[bi], non_blocking=True)
                 d2h += out_host.numel() * 4
                 checksum = loss.detach() if checksum is None else checksum + loss.detach()
             if world > 1:
                 for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
                     dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
+            cur.wait_stream(copy_stream)
             if checksum is not None:
                 float(checksum.item())  # device->host read of the step's scalar result
                 d2h += 4
@@ -369,8 +407,28 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.views * P * k_e2e / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h),
-               "path": "Tracer.render + autograd backward per view; rays, pose and upstream gradients copied from pinned host memory, "
-                       "rendered RGBA and the scalar loss read back every step; particles stay device resident (they are the model)"}
+               "path": "Tracer.render + autograd backward per view; rays, pose and upstream gradients copied from pinned host memory "
+                       "(copy stream, one view ahead), rendered RGBA of every view and the scalar loss read back every step; particles stay "
+                       "device resident (they are the model)"}
+
+    # ---- auxiliary: forward-only frame time at 1920x1080 (second half of BASELINE.json's metric; reference convention:
+    # CUDA events around the forward only, splatRaster.cpp:208-241 / threedgrut/render.py:241-251) -------------------
+    fwd_1080p = None
+    if rank == 0 and not args.no_aux:
+        hv = syn.make_view(1920, 1080, k=0, n_views=args.views)
+        ro, rd, cam = hv["rays_ori"].to(dev), hv["rays_dir"].to(dev), camera_of(hv)
+        for _ in range(3):
+            raster.trace(0, SPH_DEGREE, d12, sph, ro, rd, None, cam)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        a0.record()
+        for _ in range(reps):
+            raster.trace(0, SPH_DEGREE, d12, sph, ro, rd, None, cam)
+        a1.record()
+        torch.cuda.synchronize()
+        ms = a0.elapsed_time(a1) / reps
+        fwd_1080p = {"fps": 1e3 / ms, "ms_per_frame": ms, "particles": n, "intersections_M": raster.frame_stats()["num_intersections"]}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -388,7 +446,7 @@ def run_ours(args):
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P},
-            "stage_ms": stage_ms,
+            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
