@@ -303,9 +303,9 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     GUT_CUDA(h, ensure(h->extent, n1 * 8, s));
     GUT_CUDA(h, ensure(h->depth, n1 * 4, s));
     GUT_CUDA(h, ensure(h->features, n1 * 16, s));
-    GUT_CUDA(h, ensure(h->tile_hist, (size_t)T * 4, s));
+    GUT_CUDA(h, ensure(h->tile_hist, (size_t)T * GUT_TILE_SUB * 4, s));
     GUT_CUDA(h, ensure(h->tile_start, ((size_t)T + 1) * 4, s));
-    GUT_CUDA(h, ensure(h->tile_cursor, (size_t)T * 4, s));
+    GUT_CUDA(h, ensure(h->tile_cursor, (size_t)T * GUT_TILE_SUB * 4, s));
     GUT_CUDA(h, ensure(h->stats, 16, s));
 
     GutProjBuffers pb;
@@ -314,7 +314,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
 
     {
         StageTimer t(h, ST_PROJECT, s);
-        GUT_CUDA(h, cudaMemsetAsync(h->tile_hist.p, 0, (size_t)T * 4, s));
+        GUT_CUDA(h, cudaMemsetAsync(h->tile_hist.p, 0, (size_t)T * GUT_TILE_SUB * 4, s));
         GUT_CUDA(h, gut_launch_project(h->cfg, *camera, fr, N, sph_degree, d_density, d_radiance, pb, d_visibility, (uint32_t*)h->tile_hist.p, s));
         h->launches += N ? 1 : 0;
     }
@@ -342,7 +342,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         if (max_list > 12288) GUT_CUDA(h, ensure(h->scratch, M * 8, s, 1.25f));
         {
             StageTimer t(h, ST_EMIT, s);
-            GUT_CUDA(h, gut_launch_emit(h->cfg, fr, N, pb, (const uint32_t*)h->tile_start.p, (uint32_t*)h->tile_cursor.p, (uint2*)h->entries.p, s));
+            GUT_CUDA(h, gut_launch_emit(h->cfg, fr, N, pb, (uint32_t*)h->tile_cursor.p, (uint2*)h->entries.p, (uint32_t)M, s));
             h->launches += 1;
         }
         {

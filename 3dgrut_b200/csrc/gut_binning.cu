@@ -20,11 +20,14 @@ namespace {
 constexpr int SCAN_THREADS = 1024;
 
 // ---------------------------------------------------------------------------------------------------
-// Exclusive scan of the tile histogram (T is a few thousand: one CTA, chunks of 1024 with a carry).
+// Exclusive scan of the tile histogram (T is a few thousand: one CTA, chunks of 1024 tiles with a carry).
+// hist holds GUT_TILE_SUB sub-counts per tile; start[t] = first slot of tile t's bucket, cursor[t*SUB+k] = first
+// slot of sub-bucket k (absolute positions: the emit pass appends with one atomicAdd and no further look-up).
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T, const uint32_t* __restrict__ hist,
                                                                     uint32_t* __restrict__ start, uint32_t* __restrict__ cursor,
                                                                     uint32_t* __restrict__ stats) {
+    static_assert(GUT_TILE_SUB == 8, "the scan reads a tile's sub-counts as two uint4");
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
     __shared__ uint32_t max_s;
@@ -34,7 +37,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
     uint32_t local_max = 0;
     for (uint32_t base = 0; base < T; base += SCAN_THREADS) {
         const uint32_t i = base + tid;
-        const uint32_t v = i < T ? hist[i] : 0u;
+        uint32_t c[GUT_TILE_SUB];
+#pragma unroll
+        for (int k = 0; k < GUT_TILE_SUB; ++k) c[k] = 0;
+        if (i < T) {
+            const uint4 a = reinterpret_cast<const uint4*>(hist)[2 * (size_t)i], b4 = reinterpret_cast<const uint4*>(hist)[2 * (size_t)i + 1];
+            c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b4.x; c[5] = b4.y; c[6] = b4.z; c[7] = b4.w;
+        }
+        uint32_t v = 0;
+#pragma unroll
+        for (int k = 0; k < GUT_TILE_SUB; ++k) v += c[k];
         local_max = max(local_max, v);
         uint32_t incl = v;
 #pragma unroll
@@ -56,7 +68,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
         __syncthreads();
         const uint32_t carry = carry_s;
         const uint32_t excl = carry + (wid ? warp_sums[wid - 1] : 0u) + incl - v;
-        if (i < T) { start[i] = excl; cursor[i] = 0u; }
+        if (i < T) {
+            start[i] = excl;
+            uint32_t run = excl;
+            uint32_t o[GUT_TILE_SUB];
+#pragma unroll
+            for (int k = 0; k < GUT_TILE_SUB; ++k) { o[k] = run; run += c[k]; }
+            reinterpret_cast<uint4*>(cursor)[2 * (size_t)i] = make_uint4(o[0], o[1], o[2], o[3]);
+            reinterpret_cast<uint4*>(cursor)[2 * (size_t)i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
         __syncthreads();
         if (tid == SCAN_THREADS - 1) carry_s = carry + warp_sums[31];
         __syncthreads();
@@ -71,8 +91,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
 // (depth bits, particle) to each surviving tile's bucket.  reference: GUTProjector::expand, gutProjector.cuh:324-388.
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame fr, uint32_t N, GutProjBuffers proj,
-                                                       const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ tile_cursor,
-                                                       uint2* __restrict__ entries) {
+                                                       uint32_t* __restrict__ tile_cursor, uint2* __restrict__ entries, uint32_t capacity) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     if (proj.tiles_count[i] == 0) return;
@@ -100,13 +119,10 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
             if (++x == bb.x1) { x = bb.x0; ++y; }
         }
 #pragma unroll
-        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k]], 1u) : 0u;
+        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + (i & (GUT_TILE_SUB - 1))], 1u) : 0u;
 #pragma unroll
         for (int k = 0; k < EMIT_ILP; ++k) {
-            if (ok[k]) {
-                const uint32_t b0 = tile_start[t[k]], b1 = tile_start[t[k] + 1];
-                if (b0 + slot[k] < b1) entries[b0 + slot[k]] = make_uint2(depth_bits, i);
-            }
+            if (ok[k] && slot[k] < capacity) entries[slot[k]] = make_uint2(depth_bits, i);
         }
     }
 }
@@ -290,9 +306,9 @@ cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t
 }
 
 cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_t N, GutProjBuffers proj,
-                            const uint32_t* tile_start, uint32_t* tile_cursor, uint2* entries, cudaStream_t stream) {
+                            uint32_t* tile_cursor, uint2* entries, uint32_t capacity, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    gut_emit_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, frame, N, proj, tile_start, tile_cursor, entries);
+    gut_emit_kernel<<<(N + 255) / 256, 256, 0, stream>>>(cfg, frame, N, proj, tile_cursor, entries, capacity);
     return cudaGetLastError();
 }
 

@@ -68,12 +68,12 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream);
 
-// exclusive scan of tile_hist[T] -> tile_start[T+1]; also zeroes tile_cursor[T], writes stats[0]=M, stats[1]=max list
+// exclusive scan of tile_hist[T*SUB] -> tile_start[T+1] and absolute sub-bucket cursors tile_cursor[T*SUB]; stats[0]=M, stats[1]=max list
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
                                  uint32_t* stats, cudaStream_t stream);
 
 cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_t N, GutProjBuffers proj,
-                            const uint32_t* tile_start, uint32_t* tile_cursor, uint2* entries, cudaStream_t stream);
+                            uint32_t* tile_cursor, uint2* entries, uint32_t capacity, cudaStream_t stream);
 
 // per-tile sort of the (depth, idx) buckets -> sorted particle list; scratch = alt buffer for oversize tiles
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries, uint2* scratch,

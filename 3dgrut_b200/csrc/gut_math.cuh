@@ -13,6 +13,9 @@
 
 #define GUT_TILE 16  // reference: GUTParameters::Tiling::BlockX/BlockY (renderer/gutRendererParameters.h:22-23)
 #define GUT_INVALID_PARTICLE 0xFFFFFFFFu
+// Every tile's bucket counter / cursor is split into GUT_TILE_SUB sub-counters selected by the low bits of the particle
+// index: the returning L2 atomics of the emit pass then spread over 8x more addresses (same-address atomics serialise).
+#define GUT_TILE_SUB 8
 
 #define GUT_HD __host__ __device__ __forceinline__
 #define GUT_D __device__ __forceinline__

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
             for (uint32_t x = bb.x0; x < bb.x1; ++x) {
                 if (!cfg.tile_based_culling || gut_tile_min_power((float)x, (float)y, co, centre) < max_power) {
                     ntiles++;
-                    atomicAdd(&tile_hist[y * fr.grid_x + x], 1u);  // RED: per-tile list length for the bucket scan
+                    atomicAdd(&tile_hist[(y * fr.grid_x + x) * GUT_TILE_SUB + (i & (GUT_TILE_SUB - 1))], 1u);  // RED: per-tile (sub-)list length for the bucket scan
                 }
             }
     }
