@@ -93,13 +93,6 @@ GUT_D float mufu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"
 GUT_D float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 GUT_D float mufu_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
-// response of the default degree-2 kernel as one FMUL + one MUFU.EX2: exp(-g/2) = 2^(-g log2(e) / 2)
-template <int DEG>
-GUT_D float response_of(float g2) {
-    if (DEG == 2) return mufu_ex2(g2 * -0.72134752044448170368f);
-    return kernel_response<DEG>(g2);
-}
-
 struct Ray {
     float3 o, d;
     float tmin, tmax;
@@ -149,35 +142,95 @@ GUT_D void thread_pixel(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_
 constexpr uint32_t WALK_UNROLL = 4;
 constexpr uint32_t ALIVE_CHECK = 16;  // records between two warp-wide "is any ray still alive" votes
 
-GUT_D void pad_batch_tail(float4* rec, uint32_t cnt) {
-    const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
-    const uint32_t i = cnt * 5 + threadIdx.x;
-    if (i < cnt_pad * 5) rec[i] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);  // rows (1,1,1), go = 0, scale 1, density 0
+// ---- packed FP32 (sm_100a FFMA2 / FMUL2: two fp32 lanes per instruction, one issue slot) --------------------
+// Both compositing kernels are issue bound, and a packed instruction does the work of two scalar ones for the same
+// issue slot (scripts/microbench/ffma2.cu: 4 FFMA2 + 8 IADD take 0.75x the time of 8 FFMA + 8 IADD).  The test
+// therefore runs on TWO particles at once: records are stored pair-interleaved so that one LDS.128 yields two packed
+// operands, and the ray direction enters as a scalar broadcast operand (ptxas folds mov.b64 {x,x} into R.F32).
+typedef unsigned long long u64;
+GUT_D u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+GUT_D void upk2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+GUT_D float half_of(u64 v, int h) { float lo, hi; upk2(v, lo, hi); return h ? hi : lo; }
+GUT_D u64 bc2(float x) { return pk2(x, x); }
+GUT_D u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+GUT_D u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// pure sign flip (neg.f32 without .ftz), so that ptxas folds it into the consumer's operand modifier
+GUT_D u64 neg2(u64 a) {
+    float lo, hi, nl, nh;
+    upk2(a, lo, hi);
+    asm("neg.f32 %0, %1;" : "=f"(nl) : "f"(lo));
+    asm("neg.f32 %0, %1;" : "=f"(nh) : "f"(hi));
+    return pk2(nl, nh);
 }
 
-// canonical-frame test shared by forward and backward.  u = ms d (unnormalised canonical direction), go = canonical origin.
+// Pair-interleaved record: particles (2i, 2i+1) of a batch share 10 quads (160 B).  A vector X = (x, y, z, w) of the
+// two particles is stored as (x0, x1, y0, y1) (z0, z1, w0, w1); quads 0-1 = row 0 of ms + go.x, 2-3 = row 1 + go.y,
+// 4-5 = row 2 + go.z, 6-7 = scale + density, 8 / 9 = clamped colour + particle index of particle 0 / 1.
+constexpr uint32_t PAIR_QUADS = 10;
+GUT_D void store_pair_vec(float* pair, uint32_t v, uint32_t h, float x, float y, float z, float w) {
+    float* q = pair + 8 * v + h;
+    q[0] = x; q[2] = y; q[4] = z; q[6] = w;
+}
+
+// canonical-frame test shared by forward and backward, two particles at a time.  u = ms d (unnormalised canonical
+// direction), go = canonical origin, c = u x go.
+struct PairCanon {
+    u64 gox, goy, goz, ux, uy, uz, cx, cy, cz, l2, il2, g2, resp, araw;
+};
 struct Canon {
-    float3 go, u, c;   // c = u x go
+    float3 go, u, c;
     float l2, il2, g2, resp, araw;
 };
+GUT_D Canon canon_half(const PairCanon& k, int h) {
+    Canon c;
+    c.go = f3(half_of(k.gox, h), half_of(k.goy, h), half_of(k.goz, h));
+    c.u = f3(half_of(k.ux, h), half_of(k.uy, h), half_of(k.uz, h));
+    c.c = f3(half_of(k.cx, h), half_of(k.cy, h), half_of(k.cz, h));
+    c.l2 = half_of(k.l2, h); c.il2 = half_of(k.il2, h); c.g2 = half_of(k.g2, h);
+    c.resp = half_of(k.resp, h); c.araw = half_of(k.araw, h);
+    return c;
+}
 template <int DEG, bool UNIFORM>
-GUT_D bool particle_test(const GutConfig& cfg, const float4 A, const float4 B, const float4 Cm, const float density, const float3 d,
-                         const float3 dlt, Canon& k) {
-    k.go = f3(A.w, B.w, Cm.w);
+GUT_D void pair_test(const GutConfig& cfg, const ulonglong2* __restrict__ r, const float3 d, const float3 dlt, PairCanon& k,
+                     bool& accept0, bool& accept1) {
+    const ulonglong2 a0 = r[0], a1 = r[1], b0 = r[2], b1 = r[3], c0 = r[4], c1 = r[5];
+    const u64 dens = r[7].y;
+    const u64 dx = bc2(d.x), dy = bc2(d.y), dz = bc2(d.z);
+    k.gox = a1.y; k.goy = b1.y; k.goz = c1.y;
     if (!UNIFORM) {  // the ray does not start at the frame origin: go += ms (ray origin - frame origin)
-        k.go.x += A.x * dlt.x + A.y * dlt.y + A.z * dlt.z;
-        k.go.y += B.x * dlt.x + B.y * dlt.y + B.z * dlt.z;
-        k.go.z += Cm.x * dlt.x + Cm.y * dlt.y + Cm.z * dlt.z;
+        const u64 ex = bc2(dlt.x), ey = bc2(dlt.y), ez = bc2(dlt.z);
+        k.gox = fma2(a1.x, ez, fma2(a0.y, ey, fma2(a0.x, ex, k.gox)));
+        k.goy = fma2(b1.x, ez, fma2(b0.y, ey, fma2(b0.x, ex, k.goy)));
+        k.goz = fma2(c1.x, ez, fma2(c0.y, ey, fma2(c0.x, ex, k.goz)));
     }
-    k.u = f3(A.x * d.x + A.y * d.y + A.z * d.z, B.x * d.x + B.y * d.y + B.z * d.z, Cm.x * d.x + Cm.y * d.y + Cm.z * d.z);
-    k.l2 = dot(k.u, k.u);
-    k.c = cross(k.u, k.go);
-    k.il2 = mufu_rcp(k.l2);
-    k.g2 = dot(k.c, k.c) * k.il2;  // |normalize(u) x go|^2
-    k.resp = response_of<DEG>(k.g2);
-    k.araw = k.resp * density;
+    k.ux = fma2(a1.x, dz, fma2(a0.y, dy, mul2(a0.x, dx)));
+    k.uy = fma2(b1.x, dz, fma2(b0.y, dy, mul2(b0.x, dx)));
+    k.uz = fma2(c1.x, dz, fma2(c0.y, dy, mul2(c0.x, dx)));
+    k.l2 = fma2(k.uz, k.uz, fma2(k.uy, k.uy, mul2(k.ux, k.ux)));
+    k.cx = fma2(k.uy, k.goz, neg2(mul2(k.uz, k.goy)));
+    k.cy = fma2(k.uz, k.gox, neg2(mul2(k.ux, k.goz)));
+    k.cz = fma2(k.ux, k.goy, neg2(mul2(k.uy, k.gox)));
+    float l0, l1;
+    upk2(k.l2, l0, l1);
+    k.il2 = pk2(mufu_rcp(l0), mufu_rcp(l1));
+    k.g2 = mul2(fma2(k.cz, k.cz, fma2(k.cy, k.cy, mul2(k.cx, k.cx))), k.il2);  // |normalize(u) x go|^2
+    float r0, r1;
+    if (DEG == 2) {
+        float e0, e1;
+        upk2(mul2(k.g2, bc2(-0.72134752044448170368f)), e0, e1);
+        r0 = mufu_ex2(e0); r1 = mufu_ex2(e1);
+    } else {
+        float g0, g1;
+        upk2(k.g2, g0, g1);
+        r0 = kernel_response<DEG>(g0); r1 = kernel_response<DEG>(g1);
+    }
+    k.resp = pk2(r0, r1);
+    k.araw = mul2(k.resp, dens);
+    float w0, w1;
+    upk2(k.araw, w0, w1);
     // alpha = min(max_alpha, araw) > min_alpha  <=>  araw > min_alpha  (max_alpha > min_alpha is checked at gut_create)
-    return (k.resp > cfg.min_kernel_response) && (k.araw > cfg.min_alpha);
+    accept0 = (r0 > cfg.min_kernel_response) && (w0 > cfg.min_alpha);
+    accept1 = (r1 > cfg.min_kernel_response) && (w1 > cfg.min_alpha);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -197,24 +250,29 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
         const uint32_t je = min(cnt_pad, j0 + ALIVE_CHECK);
         for (uint32_t j = j0; j < je; j += WALK_UNROLL) {
 #pragma unroll
-            for (uint32_t q = 0; q < WALK_UNROLL; ++q) {
-                const float4* r = rec + 5 * (j + q);
-                const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
-                Canon k;
-                const bool accept = particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray.d, dlt, k);
-                if (COUNT && st.alive && (j + q) < cnt) st.ntests++;
-                if (accept && st.alive) {
-                    // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
-                    const float3 su = f3(S.x * k.u.x, S.y * k.u.y, S.z * k.u.z);
-                    const float t = fabsf(dot(k.u, k.go)) * k.il2 * mufu_sqrt(dot(su, su));
-                    if (t > ray.tmin && t < ray.tmax) {
-                        const float alpha = fminf(cfg.max_alpha, k.araw);
-                        const float4 F = r[4];
-                        const float w = alpha * st.T;
-                        st.D = fmaf(t, w, st.D);
-                        st.T *= (1.0f - alpha);
-                        if (w > 0.0f) { st.cr = fmaf(F.x, w, st.cr); st.cg = fmaf(F.y, w, st.cg); st.cb = fmaf(F.z, w, st.cb); st.nhits++; }
-                        if (st.T < cfg.min_transmittance) st.alive = false;
+            for (uint32_t q = 0; q < WALK_UNROLL; q += 2) {
+                const float4* r = rec + PAIR_QUADS * ((j + q) >> 1);
+                PairCanon pk;
+                bool acc[2];
+                pair_test<DEG, UNIFORM>(cfg, reinterpret_cast<const ulonglong2*>(r), ray.d, dlt, pk, acc[0], acc[1]);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (COUNT && st.alive && (j + q + h) < cnt) st.ntests++;
+                    if (acc[h] && st.alive) {
+                        // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
+                        const Canon k = canon_half(pk, h);
+                        const float4 Sxy = r[6], Szd = r[7];
+                        const float3 su = f3((h ? Sxy.y : Sxy.x) * k.u.x, (h ? Sxy.w : Sxy.z) * k.u.y, (h ? Szd.y : Szd.x) * k.u.z);
+                        const float t = fabsf(dot(k.u, k.go)) * k.il2 * mufu_sqrt(dot(su, su));
+                        if (t > ray.tmin && t < ray.tmax) {
+                            const float alpha = fminf(cfg.max_alpha, k.araw);
+                            const float4 F = r[8 + h];
+                            const float w = alpha * st.T;
+                            st.D = fmaf(t, w, st.D);
+                            st.T *= (1.0f - alpha);
+                            if (w > 0.0f) { st.cr = fmaf(F.x, w, st.cr); st.cg = fmaf(F.y, w, st.cg); st.cb = fmaf(F.z, w, st.cb); st.nhits++; }
+                            if (st.T < cfg.min_transmittance) st.alive = false;
+                        }
                     }
                 }
             }
@@ -280,10 +338,15 @@ struct TileStager {
         }
         cp_async_commit();
     }
-    // every thread: its gathered particle -> record (the walk of the previous batch must be over: rec is single buffered)
+    // every thread: its gathered particle -> its half of a pair-interleaved record (the walk of the previous batch must
+    // be over: rec is single buffered).  Threads past the end of the list pad it to a multiple of WALK_UNROLL with
+    // records that can never be accepted (density 0).
     GUT_D void expand(uint32_t bi) {
         cp_async_wait_all();
         const uint32_t t = threadIdx.x, cnt = count(bi);
+        const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
+        float* pair = reinterpret_cast<float*>(rec + PAIR_QUADS * (t >> 1));
+        const uint32_t h = t & 1u;
         if (t < cnt) {
             const float4 r0 = raw[t], q = raw[BATCH + t], r2 = raw[2 * BATCH + t], ft = raw[3 * BATCH + t];
             float3 c0, c1, c2;
@@ -291,20 +354,24 @@ struct TileStager {
             const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
             const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
             const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
-            float4* out = rec + 5 * t;
-            out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
-            out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
-            out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
-            out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
-            out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next));
+            store_pair_vec(pair, 0, h, m0.x, m0.y, m0.z, dot(m0, v));
+            store_pair_vec(pair, 1, h, m1.x, m1.y, m1.z, dot(m1, v));
+            store_pair_vec(pair, 2, h, m2.x, m2.y, m2.z, dot(m2, v));
+            store_pair_vec(pair, 3, h, r2.x, r2.y, r2.z, r0.w);
+            rec[PAIR_QUADS * (t >> 1) + 8 + h] =
+                make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next));
             if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
                 float4* outb = recb + 3 * t;
                 outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
                 outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
                 outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
             }
+        } else if (t < cnt_pad) {
+            store_pair_vec(pair, 0, h, 1.0f, 1.0f, 1.0f, 0.0f);
+            store_pair_vec(pair, 1, h, 1.0f, 1.0f, 1.0f, 0.0f);
+            store_pair_vec(pair, 2, h, 1.0f, 1.0f, 1.0f, 0.0f);
+            store_pair_vec(pair, 3, h, 1.0f, 1.0f, 1.0f, 0.0f);
         }
-        pad_batch_tail(rec, cnt);
     }
     // prologue: idx slices of batches 0 and 1, gather of batch 0 (call after the barriers are initialised and published)
     GUT_D void start() {
@@ -457,18 +524,26 @@ template <int DEG, bool UNIFORM>
 GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt, const Ray& ray,
                          const float3 dlt, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
     const float minT = cfg.min_transmittance;
-    for (uint32_t j = 0; j < cnt; ++j) {
-        if ((j & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive)) break;
-        const float4* r = rec + 5 * j;
-        const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
-        Canon k;
-        const bool hit = particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray.d, dlt, k) && st.alive;  // no tMinMax test here
+    const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);   // pad records are never accepted
+    for (uint32_t jp = 0; jp < cnt_pad; jp += 2) {
+        if ((jp & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive)) break;
+        const float4* r = rec + PAIR_QUADS * (jp >> 1);
+        PairCanon pk;
+        bool acc[2];
+        pair_test<DEG, UNIFORM>(cfg, reinterpret_cast<const ulonglong2*>(r), ray.d, dlt, pk, acc[0], acc[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+        const bool hit = acc[h] && st.alive;  // no tMinMax test here
         if (!__any_sync(0xffffffffu, hit)) continue;
+        const uint32_t j = jp + h;
+        const Canon k = canon_half(pk, h);
+        const float4 Sxy = r[6], Szd = r[7];
+        const float4 S = make_float4(h ? Sxy.y : Sxy.x, h ? Sxy.w : Sxy.z, h ? Szd.y : Szd.x, h ? Szd.w : Szd.z);
 
         float v[16];
 #pragma unroll
         for (int q = 0; q < 16; ++q) v[q] = 0.0f;
-        const float4 F = r[4];
+        const float4 F = r[8 + h];
         if (hit) {
             const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
             const float isz = recb[3 * j + 2].x;
@@ -543,11 +618,12 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
         const float total = warp_transpose_reduce16(v, lane);
         const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
         if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
+        }
     }
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(RENDER_THREADS) gut_render_backward_kernel(
+__global__ void __launch_bounds__(RENDER_THREADS, 3) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
