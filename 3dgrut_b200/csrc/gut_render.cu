@@ -32,8 +32,8 @@
 
 namespace {
 
-constexpr int RENDER_THREADS = 256;
-constexpr int BATCH = 256;  // particles per staged batch = one per thread
+constexpr int RENDER_THREADS = 128;   // 4 warps per 16x16 tile: every lane carries TWO rays in packed fp32 registers
+constexpr int BATCH = 256;            // particles per staged batch = two per thread
 
 // ---- mbarrier / bulk-copy PTX -------------------------------------------------------------------------
 GUT_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -129,12 +129,77 @@ GUT_D Ray make_ray(const GutFrame& fr, const float* __restrict__ ray_ori, const 
     return r;
 }
 
-// pixel owned by this thread: warp w -> 8x4 block (w&1, w>>1), lane -> (lane&7, lane>>3)
-GUT_D void thread_pixel(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_t& py) {
+// ---- packed FP32 (sm_100a FFMA2 / FMUL2 / FADD2: two fp32 lanes per instruction, one issue slot) -----------
+// Both compositing kernels are issue bound, and a packed instruction does the work of two scalar ones for the same
+// issue slot (scripts/microbench/ffma2.cu: 4 FFMA2 + 8 IADD take 0.75x the time of 8 FFMA + 8 IADD).  Every lane
+// therefore carries TWO rays (vertically adjacent pixels): all per-ray quantities are F2 pairs, per-particle
+// quantities enter as scalar broadcast operands (ptxas folds mov.b64 {x,x} into the R.F32 operand form) and the
+// whole test, the state update and the per-hit gradient math run once for both rays.
+typedef unsigned long long u64;
+struct F2 { u64 v; };
+GUT_D F2 mk2(float lo, float hi) { F2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi)); return r; }
+GUT_D F2 bc(float x) { return mk2(x, x); }
+GUT_D float lo(F2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a.v)); return l; }
+GUT_D float hi(F2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a.v)); return h; }
+GUT_D F2 fma(F2 a, F2 b, F2 c) { F2 r; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+GUT_D F2 operator*(F2 a, F2 b) { F2 r; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+GUT_D F2 operator+(F2 a, F2 b) { F2 r; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+GUT_D F2 operator-(F2 a, F2 b) { F2 r; asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+// pure sign flip (neg.f32 without .ftz), so that ptxas folds it into the consumer's operand modifier
+GUT_D F2 operator-(F2 a) {
+    float nl, nh;
+    asm("neg.f32 %0, %1;" : "=f"(nl) : "f"(lo(a)));
+    asm("neg.f32 %0, %1;" : "=f"(nh) : "f"(hi(a)));
+    return mk2(nl, nh);
+}
+struct F2x3 { F2 x, y, z; };
+GUT_D F2x3 bc3(float3 a) { F2x3 r; r.x = bc(a.x); r.y = bc(a.y); r.z = bc(a.z); return r; }
+GUT_D F2 dot(const F2x3& a, const F2x3& b) { return fma(a.z, b.z, fma(a.y, b.y, a.x * b.x)); }
+GUT_D F2x3 cross(const F2x3& a, const F2x3& b) {
+    F2x3 r;
+    r.x = fma(a.y, b.z, -(a.z * b.y));
+    r.y = fma(a.z, b.x, -(a.x * b.z));
+    r.z = fma(a.x, b.y, -(a.y * b.x));
+    return r;
+}
+GUT_D F2x3 operator*(const F2x3& a, F2 s) { F2x3 r; r.x = a.x * s; r.y = a.y * s; r.z = a.z * s; return r; }
+
+// pixels owned by this thread: warp w -> 8x8 block (w&1, w>>1), lane -> column lane&7, rows 2*(lane>>3) and +1
+GUT_D void thread_pixels(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_t& py) {
     const uint32_t tx = tile % fr.grid_x, ty = tile / fr.grid_x;
     const uint32_t w = threadIdx.x >> 5, l = threadIdx.x & 31;
     px = tx * GUT_TILE + (w & 1) * 8 + (l & 7);
-    py = ty * GUT_TILE + (w >> 1) * 4 + (l >> 3);
+    py = ty * GUT_TILE + (w >> 1) * 8 + (l >> 3) * 2;
+}
+
+// the two rays of a lane, packed
+struct RayPair {
+    F2x3 d, dlt;          // world direction; ray origin - frame origin
+    float tmin[2], tmax[2];
+    bool inside[2], valid[2];
+    uint32_t pix[2];
+};
+GUT_D RayPair make_ray_pair(const GutFrame& fr, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir, uint32_t tile,
+                            bool& at_origin) {
+    uint32_t px, py;
+    thread_pixels(fr, tile, px, py);
+    RayPair rp;
+    float3 d[2], e[2];
+    at_origin = true;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        rp.inside[h] = px < fr.width && (py + h) < fr.height;
+        rp.pix[h] = rp.inside[h] ? px + fr.width * (py + h) : 0u;
+        Ray r;
+        r.valid = false; r.o = fr.cam_centre; r.d = f3(0.f, 0.f, 1.f); r.tmin = 0.f; r.tmax = 0.f;
+        if (rp.inside[h]) r = make_ray(fr, ray_ori, ray_dir, rp.pix[h]);
+        d[h] = r.d; e[h] = r.o - fr.cam_centre;
+        rp.tmin[h] = r.tmin; rp.tmax[h] = r.tmax; rp.valid[h] = r.valid;
+        at_origin = at_origin && (!rp.inside[h] || ((e[h].x == 0.0f) && (e[h].y == 0.0f) && (e[h].z == 0.0f)));
+    }
+    rp.d.x = mk2(d[0].x, d[1].x); rp.d.y = mk2(d[0].y, d[1].y); rp.d.z = mk2(d[0].z, d[1].z);
+    rp.dlt.x = mk2(e[0].x, e[1].x); rp.dlt.y = mk2(e[0].y, e[1].y); rp.dlt.z = mk2(e[0].z, e[1].z);
+    return rp;
 }
 
 // The records of a batch are walked four at a time; the tail of a tile's last batch is padded in shared memory with
@@ -142,138 +207,87 @@ GUT_D void thread_pixel(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_
 constexpr uint32_t WALK_UNROLL = 4;
 constexpr uint32_t ALIVE_CHECK = 16;  // records between two warp-wide "is any ray still alive" votes
 
-// ---- packed FP32 (sm_100a FFMA2 / FMUL2: two fp32 lanes per instruction, one issue slot) --------------------
-// Both compositing kernels are issue bound, and a packed instruction does the work of two scalar ones for the same
-// issue slot (scripts/microbench/ffma2.cu: 4 FFMA2 + 8 IADD take 0.75x the time of 8 FFMA + 8 IADD).  The test
-// therefore runs on TWO particles at once: records are stored pair-interleaved so that one LDS.128 yields two packed
-// operands, and the ray direction enters as a scalar broadcast operand (ptxas folds mov.b64 {x,x} into R.F32).
-typedef unsigned long long u64;
-GUT_D u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-GUT_D void upk2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-GUT_D float half_of(u64 v, int h) { float lo, hi; upk2(v, lo, hi); return h ? hi : lo; }
-GUT_D u64 bc2(float x) { return pk2(x, x); }
-GUT_D u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
-GUT_D u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-// pure sign flip (neg.f32 without .ftz), so that ptxas folds it into the consumer's operand modifier
-GUT_D u64 neg2(u64 a) {
-    float lo, hi, nl, nh;
-    upk2(a, lo, hi);
-    asm("neg.f32 %0, %1;" : "=f"(nl) : "f"(lo));
-    asm("neg.f32 %0, %1;" : "=f"(nh) : "f"(hi));
-    return pk2(nl, nh);
-}
-
-// Pair-interleaved record: particles (2i, 2i+1) of a batch share 10 quads (160 B).  A vector X = (x, y, z, w) of the
-// two particles is stored as (x0, x1, y0, y1) (z0, z1, w0, w1); quads 0-1 = row 0 of ms + go.x, 2-3 = row 1 + go.y,
-// 4-5 = row 2 + go.z, 6-7 = scale + density, 8 / 9 = clamped colour + particle index of particle 0 / 1.
-constexpr uint32_t PAIR_QUADS = 10;
-GUT_D void store_pair_vec(float* pair, uint32_t v, uint32_t h, float x, float y, float z, float w) {
-    float* q = pair + 8 * v + h;
-    q[0] = x; q[2] = y; q[4] = z; q[6] = w;
-}
-
-// canonical-frame test shared by forward and backward, two particles at a time.  u = ms d (unnormalised canonical
+// canonical-frame test shared by forward and backward, for the two rays of a lane.  u = ms d (unnormalised canonical
 // direction), go = canonical origin, c = u x go.
-struct PairCanon {
-    u64 gox, goy, goz, ux, uy, uz, cx, cy, cz, l2, il2, g2, resp, araw;
+struct Canon2 {
+    F2x3 go, u, c;
+    F2 l2, il2, g2, resp, araw;
 };
-struct Canon {
-    float3 go, u, c;
-    float l2, il2, g2, resp, araw;
-};
-GUT_D Canon canon_half(const PairCanon& k, int h) {
-    Canon c;
-    c.go = f3(half_of(k.gox, h), half_of(k.goy, h), half_of(k.goz, h));
-    c.u = f3(half_of(k.ux, h), half_of(k.uy, h), half_of(k.uz, h));
-    c.c = f3(half_of(k.cx, h), half_of(k.cy, h), half_of(k.cz, h));
-    c.l2 = half_of(k.l2, h); c.il2 = half_of(k.il2, h); c.g2 = half_of(k.g2, h);
-    c.resp = half_of(k.resp, h); c.araw = half_of(k.araw, h);
-    return c;
-}
 template <int DEG, bool UNIFORM>
-GUT_D void pair_test(const GutConfig& cfg, const ulonglong2* __restrict__ r, const float3 d, const float3 dlt, PairCanon& k,
-                     bool& accept0, bool& accept1) {
-    const ulonglong2 a0 = r[0], a1 = r[1], b0 = r[2], b1 = r[3], c0 = r[4], c1 = r[5];
-    const u64 dens = r[7].y;
-    const u64 dx = bc2(d.x), dy = bc2(d.y), dz = bc2(d.z);
-    k.gox = a1.y; k.goy = b1.y; k.goz = c1.y;
-    if (!UNIFORM) {  // the ray does not start at the frame origin: go += ms (ray origin - frame origin)
-        const u64 ex = bc2(dlt.x), ey = bc2(dlt.y), ez = bc2(dlt.z);
-        k.gox = fma2(a1.x, ez, fma2(a0.y, ey, fma2(a0.x, ex, k.gox)));
-        k.goy = fma2(b1.x, ez, fma2(b0.y, ey, fma2(b0.x, ex, k.goy)));
-        k.goz = fma2(c1.x, ez, fma2(c0.y, ey, fma2(c0.x, ex, k.goz)));
+GUT_D void particle_test(const GutConfig& cfg, const float4 A, const float4 B, const float4 Cm, const float density, const RayPair& ray,
+                         Canon2& k, bool& accept0, bool& accept1) {
+    k.go.x = bc(A.w); k.go.y = bc(B.w); k.go.z = bc(Cm.w);
+    if (!UNIFORM) {  // the rays do not start at the frame origin: go += ms (ray origin - frame origin)
+        k.go.x = fma(bc(A.z), ray.dlt.z, fma(bc(A.y), ray.dlt.y, fma(bc(A.x), ray.dlt.x, k.go.x)));
+        k.go.y = fma(bc(B.z), ray.dlt.z, fma(bc(B.y), ray.dlt.y, fma(bc(B.x), ray.dlt.x, k.go.y)));
+        k.go.z = fma(bc(Cm.z), ray.dlt.z, fma(bc(Cm.y), ray.dlt.y, fma(bc(Cm.x), ray.dlt.x, k.go.z)));
     }
-    k.ux = fma2(a1.x, dz, fma2(a0.y, dy, mul2(a0.x, dx)));
-    k.uy = fma2(b1.x, dz, fma2(b0.y, dy, mul2(b0.x, dx)));
-    k.uz = fma2(c1.x, dz, fma2(c0.y, dy, mul2(c0.x, dx)));
-    k.l2 = fma2(k.uz, k.uz, fma2(k.uy, k.uy, mul2(k.ux, k.ux)));
-    k.cx = fma2(k.uy, k.goz, neg2(mul2(k.uz, k.goy)));
-    k.cy = fma2(k.uz, k.gox, neg2(mul2(k.ux, k.goz)));
-    k.cz = fma2(k.ux, k.goy, neg2(mul2(k.uy, k.gox)));
-    float l0, l1;
-    upk2(k.l2, l0, l1);
-    k.il2 = pk2(mufu_rcp(l0), mufu_rcp(l1));
-    k.g2 = mul2(fma2(k.cz, k.cz, fma2(k.cy, k.cy, mul2(k.cx, k.cx))), k.il2);  // |normalize(u) x go|^2
+    k.u.x = fma(bc(A.z), ray.d.z, fma(bc(A.y), ray.d.y, bc(A.x) * ray.d.x));
+    k.u.y = fma(bc(B.z), ray.d.z, fma(bc(B.y), ray.d.y, bc(B.x) * ray.d.x));
+    k.u.z = fma(bc(Cm.z), ray.d.z, fma(bc(Cm.y), ray.d.y, bc(Cm.x) * ray.d.x));
+    k.l2 = dot(k.u, k.u);
+    k.c = cross(k.u, k.go);
+    k.il2 = mk2(mufu_rcp(lo(k.l2)), mufu_rcp(hi(k.l2)));
+    k.g2 = dot(k.c, k.c) * k.il2;  // |normalize(u) x go|^2
     float r0, r1;
-    if (DEG == 2) {
-        float e0, e1;
-        upk2(mul2(k.g2, bc2(-0.72134752044448170368f)), e0, e1);
-        r0 = mufu_ex2(e0); r1 = mufu_ex2(e1);
+    if (DEG == 2) {   // exp(-g/2) = 2^(-g log2(e) / 2): one packed FMUL + one MUFU.EX2 per ray
+        const F2 e = k.g2 * bc(-0.72134752044448170368f);
+        r0 = mufu_ex2(lo(e)); r1 = mufu_ex2(hi(e));
     } else {
-        float g0, g1;
-        upk2(k.g2, g0, g1);
-        r0 = kernel_response<DEG>(g0); r1 = kernel_response<DEG>(g1);
+        r0 = kernel_response<DEG>(lo(k.g2)); r1 = kernel_response<DEG>(hi(k.g2));
     }
-    k.resp = pk2(r0, r1);
-    k.araw = mul2(k.resp, dens);
-    float w0, w1;
-    upk2(k.araw, w0, w1);
+    k.resp = mk2(r0, r1);
+    k.araw = k.resp * bc(density);
     // alpha = min(max_alpha, araw) > min_alpha  <=>  araw > min_alpha  (max_alpha > min_alpha is checked at gut_create)
-    accept0 = (r0 > cfg.min_kernel_response) && (w0 > cfg.min_alpha);
-    accept1 = (r1 > cfg.min_kernel_response) && (w1 > cfg.min_alpha);
+    accept0 = (r0 > cfg.min_kernel_response) && (lo(k.araw) > cfg.min_alpha);
+    accept1 = (r1 > cfg.min_kernel_response) && (hi(k.araw) > cfg.min_alpha);
 }
 
 // ---------------------------------------------------------------------------------------------------
 // K4 forward
 // ---------------------------------------------------------------------------------------------------
 struct FwdState {
-    float T, D, cr, cg, cb;
-    uint32_t nhits, ntests;
-    bool alive;
+    F2 T, D, cr, cg, cb;
+    uint32_t nhits[2], ntests[2];
+    bool alive[2];
 };
 
 template <int DEG, bool UNIFORM, bool COUNT>
-GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const Ray& ray, const float3 dlt, FwdState& st) {
+GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const RayPair& ray, FwdState& st) {
     const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
     for (uint32_t j0 = 0; j0 < cnt_pad; j0 += ALIVE_CHECK) {
-        if (!__any_sync(0xffffffffu, st.alive)) break;
+        if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
         const uint32_t je = min(cnt_pad, j0 + ALIVE_CHECK);
         for (uint32_t j = j0; j < je; j += WALK_UNROLL) {
 #pragma unroll
-            for (uint32_t q = 0; q < WALK_UNROLL; q += 2) {
-                const float4* r = rec + PAIR_QUADS * ((j + q) >> 1);
-                PairCanon pk;
-                bool acc[2];
-                pair_test<DEG, UNIFORM>(cfg, reinterpret_cast<const ulonglong2*>(r), ray.d, dlt, pk, acc[0], acc[1]);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (COUNT && st.alive && (j + q + h) < cnt) st.ntests++;
-                    if (acc[h] && st.alive) {
-                        // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
-                        const Canon k = canon_half(pk, h);
-                        const float4 Sxy = r[6], Szd = r[7];
-                        const float3 su = f3((h ? Sxy.y : Sxy.x) * k.u.x, (h ? Sxy.w : Sxy.z) * k.u.y, (h ? Szd.y : Szd.x) * k.u.z);
-                        const float t = fabsf(dot(k.u, k.go)) * k.il2 * mufu_sqrt(dot(su, su));
-                        if (t > ray.tmin && t < ray.tmax) {
-                            const float alpha = fminf(cfg.max_alpha, k.araw);
-                            const float4 F = r[8 + h];
-                            const float w = alpha * st.T;
-                            st.D = fmaf(t, w, st.D);
-                            st.T *= (1.0f - alpha);
-                            if (w > 0.0f) { st.cr = fmaf(F.x, w, st.cr); st.cg = fmaf(F.y, w, st.cg); st.cb = fmaf(F.z, w, st.cb); st.nhits++; }
-                            if (st.T < cfg.min_transmittance) st.alive = false;
-                        }
-                    }
+            for (uint32_t q = 0; q < WALK_UNROLL; ++q) {
+                const float4* r = rec + 5 * (j + q);
+                const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
+                Canon2 k;
+                bool acc0, acc1;
+                particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
+                if (COUNT && (j + q) < cnt) { st.ntests[0] += st.alive[0]; st.ntests[1] += st.alive[1]; }
+                const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];
+                if (h0 || h1) {
+                    // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
+                    F2x3 su;
+                    su.x = bc(S.x) * k.u.x; su.y = bc(S.y) * k.u.y; su.z = bc(S.z) * k.u.z;
+                    const F2 ss = dot(su, su), ug = dot(k.u, k.go);
+                    const float t0 = fabsf(lo(ug)) * lo(k.il2) * mufu_sqrt(lo(ss));
+                    const float t1 = fabsf(hi(ug)) * hi(k.il2) * mufu_sqrt(hi(ss));
+                    const bool in0 = h0 && t0 > ray.tmin[0] && t0 < ray.tmax[0];
+                    const bool in1 = h1 && t1 > ray.tmin[1] && t1 < ray.tmax[1];
+                    // a ray that does not take the hit composites alpha = 0: its state is left unchanged
+                    const F2 alpha = mk2(in0 ? fminf(cfg.max_alpha, lo(k.araw)) : 0.0f, in1 ? fminf(cfg.max_alpha, hi(k.araw)) : 0.0f);
+                    const float4 F = r[4];
+                    const F2 w = alpha * st.T;
+                    st.D = fma(mk2(in0 ? t0 : 0.0f, in1 ? t1 : 0.0f), w, st.D);
+                    st.T = st.T * (bc(1.0f) - alpha);
+                    st.cr = fma(bc(F.x), w, st.cr); st.cg = fma(bc(F.y), w, st.cg); st.cb = fma(bc(F.z), w, st.cb);
+                    if (lo(w) > 0.0f) st.nhits[0]++;
+                    if (hi(w) > 0.0f) st.nhits[1]++;
+                    if (lo(st.T) < cfg.min_transmittance) st.alive[0] = false;
+                    if (hi(st.T) < cfg.min_transmittance) st.alive[1] = false;
                 }
             }
         }
@@ -288,6 +302,7 @@ GUT_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory
 GUT_D void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 constexpr uint32_t IDX_STAGE_WORDS = BATCH + 4;   // a batch's slice of the sorted list, widened to 16-byte alignment
+constexpr uint32_t PER_THREAD = BATCH / RENDER_THREADS;   // particles each thread gathers and expands per batch
 
 template <bool BWD>
 struct StageLayout {
@@ -307,14 +322,16 @@ struct TileStager {
     GutParticleSource src;
     uint32_t b0, n, nb;
     float3 origin;
-    uint32_t p_next;   // particle this thread gathers for the batch in flight
+    uint32_t p_next[PER_THREAD];   // particles this thread gathers for the batch in flight
 
     GUT_D void init(unsigned char* smem, uint64_t* bars, const GutParticleSource& s, uint32_t b0_, uint32_t n_, float3 origin_) {
         rec = reinterpret_cast<float4*>(smem);
         recb = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC);
         raw = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB);
         idx = reinterpret_cast<uint32_t*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB + StageLayout<BWD>::RAW);
-        bar = bars; src = s; b0 = b0_; n = n_; nb = (n_ + BATCH - 1) / BATCH; origin = origin_; p_next = 0;
+        bar = bars; src = s; b0 = b0_; n = n_; nb = (n_ + BATCH - 1) / BATCH; origin = origin_;
+#pragma unroll
+        for (uint32_t i = 0; i < PER_THREAD; ++i) p_next[i] = 0;
     }
     GUT_D uint32_t count(uint32_t bi) const { return min((uint32_t)BATCH, n - bi * BATCH); }
     // thread 0: bulk-copy the 16-byte aligned superset of sorted_idx[b0 + bi*BATCH, +count)
@@ -324,53 +341,59 @@ struct TileStager {
         mbar_expect_tx(&bar[bi & 1], bytes);
         bulk_g2s(idx + (bi & 1) * IDX_STAGE_WORDS, src.sorted_idx + a, bytes, &bar[bi & 1]);
     }
-    // every thread: gather the parameters of its particle of batch bi into the raw planes
+    // every thread: gather the parameters of its particles of batch bi into the raw planes
     GUT_D void issue_gather(uint32_t bi) {
         mbar_wait(&bar[bi & 1], (bi >> 1) & 1);
-        const uint32_t t = threadIdx.x;
-        if (t < count(bi)) {
-            const uint32_t p = idx[(bi & 1) * IDX_STAGE_WORDS + ((b0 + bi * BATCH) & 3u) + t];
-            p_next = p;
-            cp_async16(raw + t, src.density12 + 3 * (size_t)p);
-            cp_async16(raw + BATCH + t, src.density12 + 3 * (size_t)p + 1);
-            cp_async16(raw + 2 * BATCH + t, src.density12 + 3 * (size_t)p + 2);
-            cp_async16(raw + 3 * BATCH + t, src.features + p);
+#pragma unroll
+        for (uint32_t i = 0; i < PER_THREAD; ++i) {
+            const uint32_t t = threadIdx.x + i * RENDER_THREADS;
+            if (t < count(bi)) {
+                const uint32_t p = idx[(bi & 1) * IDX_STAGE_WORDS + ((b0 + bi * BATCH) & 3u) + t];
+                p_next[i] = p;
+                cp_async16(raw + t, src.density12 + 3 * (size_t)p);
+                cp_async16(raw + BATCH + t, src.density12 + 3 * (size_t)p + 1);
+                cp_async16(raw + 2 * BATCH + t, src.density12 + 3 * (size_t)p + 2);
+                cp_async16(raw + 3 * BATCH + t, src.features + p);
+            }
         }
         cp_async_commit();
     }
-    // every thread: its gathered particle -> its half of a pair-interleaved record (the walk of the previous batch must
-    // be over: rec is single buffered).  Threads past the end of the list pad it to a multiple of WALK_UNROLL with
-    // records that can never be accepted (density 0).
+    // every thread: its gathered particles -> records (the walk of the previous batch must be over: rec is single
+    // buffered).  Threads past the end of the list pad it to a multiple of WALK_UNROLL with records that can never be
+    // accepted: identity frame (so that u = d is never zero), density 0.
     GUT_D void expand(uint32_t bi) {
         cp_async_wait_all();
-        const uint32_t t = threadIdx.x, cnt = count(bi);
+        const uint32_t cnt = count(bi);
         const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
-        float* pair = reinterpret_cast<float*>(rec + PAIR_QUADS * (t >> 1));
-        const uint32_t h = t & 1u;
-        if (t < cnt) {
-            const float4 r0 = raw[t], q = raw[BATCH + t], r2 = raw[2 * BATCH + t], ft = raw[3 * BATCH + t];
-            float3 c0, c1, c2;
-            quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
-            const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
-            const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
-            const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
-            store_pair_vec(pair, 0, h, m0.x, m0.y, m0.z, dot(m0, v));
-            store_pair_vec(pair, 1, h, m1.x, m1.y, m1.z, dot(m1, v));
-            store_pair_vec(pair, 2, h, m2.x, m2.y, m2.z, dot(m2, v));
-            store_pair_vec(pair, 3, h, r2.x, r2.y, r2.z, r0.w);
-            rec[PAIR_QUADS * (t >> 1) + 8 + h] =
-                make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next));
-            if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
-                float4* outb = recb + 3 * t;
-                outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
-                outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
-                outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+        for (uint32_t i = 0; i < PER_THREAD; ++i) {
+            const uint32_t t = threadIdx.x + i * RENDER_THREADS;
+            float4* out = rec + 5 * t;
+            if (t < cnt) {
+                const float4 r0 = raw[t], q = raw[BATCH + t], r2 = raw[2 * BATCH + t], ft = raw[3 * BATCH + t];
+                float3 c0, c1, c2;
+                quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
+                const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
+                const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
+                const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
+                out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
+                out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
+                out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
+                out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
+                out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next[i]));
+                if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
+                    float4* outb = recb + 3 * t;
+                    outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
+                    outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
+                    outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
+                }
+            } else if (t < cnt_pad) {
+                out[0] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
+                out[1] = make_float4(0.0f, 1.0f, 0.0f, 0.0f);
+                out[2] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+                out[3] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+                out[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             }
-        } else if (t < cnt_pad) {
-            store_pair_vec(pair, 0, h, 1.0f, 1.0f, 1.0f, 0.0f);
-            store_pair_vec(pair, 1, h, 1.0f, 1.0f, 1.0f, 0.0f);
-            store_pair_vec(pair, 2, h, 1.0f, 1.0f, 1.0f, 0.0f);
-            store_pair_vec(pair, 3, h, 1.0f, 1.0f, 1.0f, 0.0f);
         }
     }
     // prologue: idx slices of batches 0 and 1, gather of batch 0 (call after the barriers are initialised and published)
@@ -403,15 +426,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
     __shared__ __align__(8) uint64_t idx_bar[2];
 
     const uint32_t tile = blockIdx.x;
-    uint32_t px, py;
-    thread_pixel(fr, tile, px, py);
-    const bool inside = px < fr.width && py < fr.height;
-    const uint32_t pix = inside ? px + fr.width * py : 0u;
-    Ray ray;
-    ray.valid = false; ray.o = fr.cam_centre; ray.d = f3(0.f, 0.f, 1.f); ray.tmin = 0.f; ray.tmax = 0.f;
-    if (inside) ray = make_ray(fr, ray_ori, ray_dir, pix);
-    const float3 dlt = ray.o - fr.cam_centre;
-    const bool at_origin = (dlt.x == 0.0f) && (dlt.y == 0.0f) && (dlt.z == 0.0f);
+    bool at_origin;
+    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, at_origin);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     TileStager<false> stg;
@@ -422,38 +438,43 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cf
         mbar_init(&idx_bar[1], 1);
         fence_mbar_init();
     }
-    const bool uniform = __syncthreads_and(at_origin || !inside) != 0;  // also publishes the barrier initialisation
+    const bool uniform = __syncthreads_and(at_origin) != 0;  // also publishes the barrier initialisation
     stg.start();
 
     FwdState st;
-    st.T = 1.0f; st.D = 0.0f; st.cr = st.cg = st.cb = 0.0f; st.nhits = 0; st.ntests = 0;
-    st.alive = inside && ray.valid;
+    st.T = bc(1.0f); st.D = bc(0.0f); st.cr = st.cg = st.cb = bc(0.0f);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) { st.nhits[h] = 0; st.ntests[h] = 0; st.alive[h] = ray.inside[h] && ray.valid[h]; }
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.expand(b);
         __syncthreads();
         stg.advance(b);
-        if (uniform) forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, dlt, st);
-        else forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, dlt, st);
-        if (__syncthreads_and(!st.alive)) { stg.drain(b); break; }   // the tile saturated early
+        if (uniform) forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
+        else forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
+        if (__syncthreads_and(!st.alive[0] && !st.alive[1])) { stg.drain(b); break; }   // the tile saturated early
     }
     if (COUNT) {
-        unsigned long long t = st.ntests, hh = st.nhits;
+        unsigned long long t = st.ntests[0] + st.ntests[1], hh = st.nhits[0] + st.nhits[1];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
         if ((threadIdx.x & 31) == 0) { atomicAdd(&counters[0], t); atomicAdd(&counters[1], hh); }
         return;
     }
-    if (inside && ray.valid) {
-        rgba[pix] = make_float4(st.cr, st.cg, st.cb, 1.0f - st.T);
-        dist[pix] = st.D;
-        if (cfg.enable_hitcounts) hits[pix] = (float)st.nhits;
-    } else if (inside) {
-        rgba[pix] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        dist[pix] = 1e06f;
-        hits[pix] = 0.0f;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t pix = ray.pix[h];
+        if (ray.inside[h] && ray.valid[h]) {
+            rgba[pix] = make_float4(h ? hi(st.cr) : lo(st.cr), h ? hi(st.cg) : lo(st.cg), h ? hi(st.cb) : lo(st.cb),
+                                    1.0f - (h ? hi(st.T) : lo(st.T)));
+            dist[pix] = h ? hi(st.D) : lo(st.D);
+            if (cfg.enable_hitcounts) hits[pix] = (float)st.nhits[h];
+        } else if (ray.inside[h]) {
+            rgba[pix] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            dist[pix] = 1e06f;
+            hits[pix] = 0.0f;
+        }
     }
 }
-
 
 // ---------------------------------------------------------------------------------------------------
 // K5 backward (k_buffer_size == 0)
@@ -501,16 +522,18 @@ GUT_D float warp_transpose_reduce16(float (&v)[16], uint32_t lane) {
 }
 
 struct BwdRay {
-    float T_f, D_f, dA, dD;   // final transmittance / distance of the forward pass, upstream gradients
-    float3 C_f, dC;
-    float T, D;               // running state of the re-walk
-    float3 C;
-    bool alive;
+    F2 T_f, D_f, dA, dD;     // final transmittance / distance of the forward pass, upstream gradients
+    F2x3 C_f, dC;
+    F2 T, D;                 // running state of the re-walk
+    F2x3 C;
+    bool alive[2];
 };
 
-// Per accepted hit a lane produces 15 values that are LINEAR in the ray, so they can be summed over rays first (warp
-// transpose-reduce, then one RED per value into the per-particle accumulator `raw`, 16 floats per particle) and
-// turned into parameter gradients once per particle by K6 (gut_project.cu, finish_density_gradient):
+GUT_D float sum2(F2 a) { return lo(a) + hi(a); }
+
+// Per accepted hit a ray produces 15 values that are LINEAR in the ray, so they can be summed over rays first (the two
+// rays of the lane, then the warp transpose-reduce, then one RED per value into the per-particle accumulator `raw`,
+// 16 floats per particle) and turned into parameter gradients once per particle by K6 (gut_project.cu):
 //   [0..2]  A   = dL/d go            (canonical ray origin)        -> dL/dpos   = -ms^T A
 //   [3]     dL/d density
 //   [4..6]  tau = body-frame torque                                 -> dL/dquat  = rho q + 2 q (x) (0, tau)
@@ -520,110 +543,122 @@ struct BwdRay {
 //   [14]    W   = sum_i s_i * (hit-distance scale term)             -> rho
 // with B = dL/d u.  This is the chain rule of processHitBwd (gaussianParticles.cuh:635-738) with the per-ray
 // quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.
+// A ray of the lane that does not take the hit runs the same packed instructions with alpha = 0 and a zeroed
+// upstream sum: every one of its 15 values is then exactly 0 and its state is unchanged.
 template <int DEG, bool UNIFORM>
-GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt, const Ray& ray,
-                         const float3 dlt, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
+GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt,
+                         const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
     const float minT = cfg.min_transmittance;
-    const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);   // pad records are never accepted
-    for (uint32_t jp = 0; jp < cnt_pad; jp += 2) {
-        if ((jp & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive)) break;
-        const float4* r = rec + PAIR_QUADS * (jp >> 1);
-        PairCanon pk;
-        bool acc[2];
-        pair_test<DEG, UNIFORM>(cfg, reinterpret_cast<const ulonglong2*>(r), ray.d, dlt, pk, acc[0], acc[1]);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-        const bool hit = acc[h] && st.alive;  // no tMinMax test here
-        if (!__any_sync(0xffffffffu, hit)) continue;
-        const uint32_t j = jp + h;
-        const Canon k = canon_half(pk, h);
-        const float4 Sxy = r[6], Szd = r[7];
-        const float4 S = make_float4(h ? Sxy.y : Sxy.x, h ? Sxy.w : Sxy.z, h ? Szd.y : Szd.x, h ? Szd.w : Szd.z);
+    const F2 one = bc(1.0f);
+    for (uint32_t j = 0; j < cnt; ++j) {
+        if ((j & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
+        const float4* r = rec + 5 * j;
+        const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
+        Canon2 k;
+        bool acc0, acc1;
+        particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
+        const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];  // no tMinMax test here
+        if (!__any_sync(0xffffffffu, h0 || h1)) continue;
 
         float v[16];
 #pragma unroll
         for (int q = 0; q < 16; ++q) v[q] = 0.0f;
-        const float4 F = r[8 + h];
-        if (hit) {
+        const float4 F = r[4];
+        if (h0 || h1) {
             const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
             const float isz = recb[3 * j + 2].x;
-            const float3 go = k.go, u = k.u;
-            const float il = mufu_rsq(k.l2);           // 1 / |u|
-            const float3 grd = u * il;                 // normalised canonical direction
-            const float dgo = dot(grd, go);
+            const F2x3& go = k.go;
+            const F2x3& u = k.u;
+            const F2 il = mk2(mufu_rsq(h0 ? lo(k.l2) : 1.0f), mufu_rsq(h1 ? hi(k.l2) : 1.0f));   // 1 / |u|
+            const F2x3 grd = u * il;                   // normalised canonical direction
+            const F2 dgo = dot(grd, go);
             // hit distance gdist = |s * grd * dot(grd, -go)| = |dgo| * |sg|, sg = s * grd
-            const float3 sg = f3(S.x * grd.x, S.y * grd.y, S.z * grd.z);
-            const float3 sg2 = sg * sg;
-            const float sum2 = sg2.x + sg2.y + sg2.z;
-            const float gsq = dgo * dgo * sum2;
-            const float gdist = fabsf(dgo) * mufu_sqrt(sum2);
-            const float alpha = fminf(cfg.max_alpha, k.araw);
-            const float T = st.T;
-            const float w = alpha * T;
-            const float om = 1.0f - alpha;
-            const float nextT = om * T;
-            const float invT = nextT <= minT ? 0.0f : mufu_rcp(nextT);
+            F2x3 sg, sg2;
+            sg.x = bc(S.x) * grd.x; sg.y = bc(S.y) * grd.y; sg.z = bc(S.z) * grd.z;
+            sg2.x = sg.x * sg.x; sg2.y = sg.y * sg.y; sg2.z = sg.z * sg.z;
+            const F2 ssum = sg2.x + sg2.y + sg2.z;
+            const F2 gsq = dgo * dgo * ssum;
+            const F2 gdist = mk2(h0 ? fabsf(lo(dgo)) * mufu_sqrt(lo(ssum)) : 0.0f, h1 ? fabsf(hi(dgo)) * mufu_sqrt(hi(ssum)) : 0.0f);
+            const F2 alpha = mk2(h0 ? fminf(cfg.max_alpha, lo(k.araw)) : 0.0f, h1 ? fminf(cfg.max_alpha, hi(k.araw)) : 0.0f);
+            const F2 T = st.T;
+            const F2 w = alpha * T;
+            const F2 om = one - alpha;
+            const F2 nextT = om * T;
+            const F2 invT = mk2(lo(nextT) <= minT ? 0.0f : mufu_rcp(lo(nextT)), hi(nextT) <= minT ? 0.0f : mufu_rcp(hi(nextT)));
 
             // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's
             // element-wise ones).  grds = -dgo sg;  dL/dgrds = grds hs = kap sg  with  kap = -dgo hs
-            st.D = fmaf(w, gdist, st.D);
-            const float resD = fmaxf((st.D_f - st.D) * invT, 0.0f);
-            const float aHit = (gdist - resD) * T * st.dD;
-            const float hs = gsq > 0.0f ? w * st.dD * mufu_rcp(gdist) : 0.0f;
-            const float kap = -dgo * hs;
-            const float kd = kap * dgo;                // s_i * sclHit_i = -kd * sg2_i
+            st.D = fma(w, gdist, st.D);
+            const F2 rD = (st.D_f - st.D) * invT;
+            const F2 resD = mk2(fmaxf(lo(rD), 0.0f), fmaxf(hi(rD), 0.0f));
+            const F2 aHit = (gdist - resD) * T * st.dD;
+            const F2 wd = w * st.dD;
+            const F2 hs = mk2(h0 && lo(gsq) > 0.0f ? lo(wd) * mufu_rcp(lo(gdist)) : 0.0f, h1 && hi(gsq) > 0.0f ? hi(wd) * mufu_rcp(hi(gdist)) : 0.0f);
+            const F2 nkap = dgo * hs;                  // -kap
+            const F2 kd = -(nkap * dgo);               // s_i * sclHit_i = -kd * sg2_i
             // grdHit_i = -kap (sg2_i go_i + dgo s_i sg_i) ; groHit_i = -kap sg2_i grd_i
-            const float3 tH = f3(fmaf(sg2.x, go.x, dgo * S.x * sg.x), fmaf(sg2.y, go.y, dgo * S.y * sg.y), fmaf(sg2.z, go.z, dgo * S.z * sg.z));
+            F2x3 tH;
+            tH.x = fma(sg2.x, go.x, dgo * bc(S.x) * sg.x);
+            tH.y = fma(sg2.y, go.y, dgo * bc(S.y) * sg.y);
+            tH.z = fma(sg2.z, go.z, dgo * bc(S.z) * sg.z);
 
             // opacity and colour terms (:569-633)
-            const float resT = alpha < 0.999999f ? st.T_f * mufu_rcp(om) : T;
-            const float aDns = resT * st.dA;
-            st.C = f3(fmaf(w, F.x, st.C.x), fmaf(w, F.y, st.C.y), fmaf(w, F.z, st.C.z));
-            const float3 resC = f3(fmaxf((st.C_f.x - st.C.x) * invT, 0.0f), fmaxf((st.C_f.y - st.C.y) * invT, 0.0f),
-                                   fmaxf((st.C_f.z - st.C.z) * invT, 0.0f));
-            const float Ssum = aHit + aDns + T * ((F.x - resC.x) * st.dC.x + (F.y - resC.y) * st.dC.y + (F.z - resC.z) * st.dC.z);
-            const float dDens = k.resp * Ssum;
-            const float respG = S.w * Ssum;
-            const float g2G = kernel_response_grad<DEG>(k.g2, k.resp, respG);
+            const F2 resT = mk2(lo(alpha) < 0.999999f ? lo(st.T_f) * mufu_rcp(lo(om)) : lo(T),
+                                hi(alpha) < 0.999999f ? hi(st.T_f) * mufu_rcp(hi(om)) : hi(T));
+            const F2 aDns = resT * st.dA;
+            st.C.x = fma(w, bc(F.x), st.C.x); st.C.y = fma(w, bc(F.y), st.C.y); st.C.z = fma(w, bc(F.z), st.C.z);
+            const F2 rx = (st.C_f.x - st.C.x) * invT, ry = (st.C_f.y - st.C.y) * invT, rz = (st.C_f.z - st.C.z) * invT;
+            const F2 resCx = mk2(fmaxf(lo(rx), 0.0f), fmaxf(hi(rx), 0.0f));
+            const F2 resCy = mk2(fmaxf(lo(ry), 0.0f), fmaxf(hi(ry), 0.0f));
+            const F2 resCz = mk2(fmaxf(lo(rz), 0.0f), fmaxf(hi(rz), 0.0f));
+            const F2 cs = fma(bc(F.z) - resCz, st.dC.z, fma(bc(F.y) - resCy, st.dC.y, (bc(F.x) - resCx) * st.dC.x));
+            const F2 Sall = fma(T, cs, aHit + aDns);
+            const F2 Ssum = mk2(h0 ? lo(Sall) : 0.0f, h1 ? hi(Sall) : 0.0f);
+            const F2 dDens = k.resp * Ssum;
+            const F2 respG = bc(S.w) * Ssum;
+            F2 g2G;
+            if (DEG == 2) g2G = bc(-0.5f) * k.resp * respG;
+            else g2G = mk2(kernel_response_grad<DEG>(lo(k.g2), lo(k.resp), lo(respG)), kernel_response_grad<DEG>(hi(k.g2), hi(k.resp), hi(respG)));
 
             // g2 = |grd x go|^2 : adjoint of the cross product (:671-689); grd x go = c / |u|
-            const float3 gcG = k.c * (2.0f * g2G * il);
-            const float3 grdG = cross(go, gcG);
-            const float3 groG = cross(gcG, grd);
+            const F2x3 gcG = k.c * (bc(2.0f) * g2G * il);
+            const F2x3 grdG = cross(go, gcG);
+            const F2x3 groG = cross(gcG, grd);
             // A = dL/dgo (total), X = dL/dgrd (total)
-            const float3 Ag = f3(fmaf(-kap, sg2.x * grd.x, groG.x), fmaf(-kap, sg2.y * grd.y, groG.y), fmaf(-kap, sg2.z * grd.z, groG.z));
-            const float3 X = f3(fmaf(-kap, tH.x, grdG.x), fmaf(-kap, tH.y, grdG.y), fmaf(-kap, tH.z, grdG.z));
+            F2x3 Ag, X, Bg;
+            Ag.x = fma(nkap, sg2.x * grd.x, groG.x); Ag.y = fma(nkap, sg2.y * grd.y, groG.y); Ag.z = fma(nkap, sg2.z * grd.z, groG.z);
+            X.x = fma(nkap, tH.x, grdG.x); X.y = fma(nkap, tH.y, grdG.y); X.z = fma(nkap, tH.z, grdG.z);
             // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): B = dL/du = (X - grd (grd . X)) / |u|
-            const float gx = dot(grd, X);
-            const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
+            const F2 gx = dot(grd, X);
+            Bg.x = il * fma(-grd.x, gx, X.x); Bg.y = il * fma(-grd.y, gx, X.y); Bg.z = il * fma(-grd.z, gx, X.z);
 
             // P_ij = go_i A_j + u_i B_j : diagonal -> scale, off-diagonal -> body-frame torque
-            v[0] = Ag.x; v[1] = Ag.y; v[2] = Ag.z;
-            v[3] = dDens;
-            v[4] = R0.y * fmaf(go.z, Ag.y, u.z * Bg.y) - R0.x * fmaf(go.y, Ag.z, u.y * Bg.z);   // rho_zy P_zy - rho_yz P_yz
-            v[5] = R0.z * fmaf(go.x, Ag.z, u.x * Bg.z) - R0.w * fmaf(go.z, Ag.x, u.z * Bg.x);   // rho_xz P_xz - rho_zx P_zx
-            v[6] = R1.x * fmaf(go.y, Ag.x, u.y * Bg.x) - R1.y * fmaf(go.x, Ag.y, u.x * Bg.y);   // rho_yx P_yx - rho_xy P_xy
-            float tr = R1.z * Bg.x * ray.d.x + R1.w * Bg.y * ray.d.y + isz * Bg.z * ray.d.z;
-            if (!UNIFORM) tr += R1.z * Ag.x * dlt.x + R1.w * Ag.y * dlt.y + isz * Ag.z * dlt.z;
-            v[7] = tr;
-            v[8] = fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x));
-            v[9] = fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y));
-            v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));
-            v[11] = w * st.dC.x; v[12] = w * st.dC.y; v[13] = w * st.dC.z;
-            v[14] = -kd * sum2;
+            v[0] = sum2(Ag.x); v[1] = sum2(Ag.y); v[2] = sum2(Ag.z);
+            v[3] = sum2(dDens);
+            v[4] = sum2(fma(bc(R0.y), fma(go.z, Ag.y, u.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, u.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
+            v[5] = sum2(fma(bc(R0.z), fma(go.x, Ag.z, u.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, u.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
+            v[6] = sum2(fma(bc(R1.x), fma(go.y, Ag.x, u.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, u.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
+            F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x)));
+            if (!UNIFORM) tr = fma(bc(isz), Ag.z * ray.dlt.z, fma(bc(R1.w), Ag.y * ray.dlt.y, fma(bc(R1.z), Ag.x * ray.dlt.x, tr)));
+            v[7] = sum2(tr);
+            v[8] = sum2(fma(go.x, Ag.x, fma(u.x, Bg.x, kd * sg2.x)));
+            v[9] = sum2(fma(go.y, Ag.y, fma(u.y, Bg.y, kd * sg2.y)));
+            v[10] = sum2(fma(go.z, Ag.z, fma(u.z, Bg.z, kd * sg2.z)));
+            v[11] = sum2(w * st.dC.x); v[12] = sum2(w * st.dC.y); v[13] = sum2(w * st.dC.z);
+            v[14] = -sum2(kd * ssum);
 
             st.T = nextT;
-            if (nextT < minT) st.alive = false;
+            if (lo(nextT) < minT) st.alive[0] = false;
+            if (hi(nextT) < minT) st.alive[1] = false;
         }
         const float total = warp_transpose_reduce16(v, lane);
         const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
         if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
-        }
     }
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(RENDER_THREADS, 3) gut_render_backward_kernel(
+__global__ void __launch_bounds__(RENDER_THREADS, 4) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
@@ -633,31 +668,32 @@ __global__ void __launch_bounds__(RENDER_THREADS, 3) gut_render_backward_kernel(
 
     const uint32_t tile = blockIdx.x;
     const uint32_t lane = threadIdx.x & 31;
-    uint32_t px, py;
-    thread_pixel(fr, tile, px, py);
-    const bool inside = px < fr.width && py < fr.height;
-    const uint32_t pix = inside ? px + fr.width * py : 0u;
-    Ray ray;
-    ray.valid = false; ray.o = fr.cam_centre; ray.d = f3(0.f, 0.f, 1.f); ray.tmin = 0.f; ray.tmax = 0.f;
-    if (inside) ray = make_ray(fr, ray_ori, ray_dir, pix);
-    const float3 dlt = ray.o - fr.cam_centre;
-    const bool at_origin = (dlt.x == 0.0f) && (dlt.y == 0.0f) && (dlt.z == 0.0f);
+    bool at_origin;
+    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, at_origin);
 
     // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
     BwdRay st;
-    st.alive = inside && ray.valid;
-    st.T_f = 1.0f; st.D_f = 0.0f; st.dA = 0.0f; st.dD = 0.0f;
-    st.C_f = f3(0.f, 0.f, 0.f); st.dC = f3(0.f, 0.f, 0.f);
-    st.T = 1.0f; st.D = 0.0f; st.C = f3(0.f, 0.f, 0.f);
-    if (st.alive) {
-        const float4 fd = __ldg(rgba + pix), gd = __ldg(rgba_grad + pix);
-        st.T_f = 1.0f - fd.w;      // transmittanceBackward
-        st.dA = gd.w;              // transmittanceGradient = -dA; used as residualTrm * -(-dA)
-        st.D_f = __ldg(dist + pix);
-        st.dD = __ldg(dist_grad + pix);
-        st.C_f = f3(fd.x, fd.y, fd.z);
-        st.dC = f3(gd.x, gd.y, gd.z);
+    float Tf[2], Df[2], dA[2], dD[2];
+    float3 Cf[2], dC[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        st.alive[h] = ray.inside[h] && ray.valid[h];
+        Tf[h] = 1.0f; Df[h] = 0.0f; dA[h] = 0.0f; dD[h] = 0.0f;
+        Cf[h] = f3(0.f, 0.f, 0.f); dC[h] = f3(0.f, 0.f, 0.f);
+        if (st.alive[h]) {
+            const float4 fd = __ldg(rgba + ray.pix[h]), gd = __ldg(rgba_grad + ray.pix[h]);
+            Tf[h] = 1.0f - fd.w;       // transmittanceBackward
+            dA[h] = gd.w;              // transmittanceGradient = -dA; used as residualTrm * -(-dA)
+            Df[h] = __ldg(dist + ray.pix[h]);
+            dD[h] = __ldg(dist_grad + ray.pix[h]);
+            Cf[h] = f3(fd.x, fd.y, fd.z);
+            dC[h] = f3(gd.x, gd.y, gd.z);
+        }
     }
+    st.T_f = mk2(Tf[0], Tf[1]); st.D_f = mk2(Df[0], Df[1]); st.dA = mk2(dA[0], dA[1]); st.dD = mk2(dD[0], dD[1]);
+    st.C_f.x = mk2(Cf[0].x, Cf[1].x); st.C_f.y = mk2(Cf[0].y, Cf[1].y); st.C_f.z = mk2(Cf[0].z, Cf[1].z);
+    st.dC.x = mk2(dC[0].x, dC[1].x); st.dC.y = mk2(dC[0].y, dC[1].y); st.dC.z = mk2(dC[0].z, dC[1].z);
+    st.T = bc(1.0f); st.D = bc(0.0f); st.C = bc3(f3(0.f, 0.f, 0.f));
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     TileStager<true> stg;
@@ -668,16 +704,16 @@ __global__ void __launch_bounds__(RENDER_THREADS, 3) gut_render_backward_kernel(
         mbar_init(&idx_bar[1], 1);
         fence_mbar_init();
     }
-    const bool uniform = __syncthreads_and(at_origin || !inside) != 0;
+    const bool uniform = __syncthreads_and(at_origin) != 0;
     stg.start();
 
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.expand(b);
         __syncthreads();
         stg.advance(b);
-        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, raw_grad);
-        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, dlt, st, lane, raw_grad);
-        if (__syncthreads_and(!st.alive)) { stg.drain(b); break; }
+        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
+        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
+        if (__syncthreads_and(!st.alive[0] && !st.alive[1])) { stg.drain(b); break; }
     }
 }
 
@@ -708,6 +744,8 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
                                   cudaStream_t stream) {
     const size_t smem = StageLayout<true>::TOTAL;
     cudaError_t e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     gut_render_backward_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(
         cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
