@@ -260,34 +260,43 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
         const uint32_t je = min(cnt_pad, j0 + ALIVE_CHECK);
         for (uint32_t j = j0; j < je; j += WALK_UNROLL) {
 #pragma unroll
-            for (uint32_t q = 0; q < WALK_UNROLL; ++q) {
+            for (uint32_t q = 0; q < WALK_UNROLL; q += 2) {
+                // two independent tests in flight (the walk is latency bound at 4-5 warps per scheduler), then their hits in order
                 const float4* r = rec + 5 * (j + q);
-                const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
-                Canon2 k;
-                bool acc0, acc1;
-                particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
-                if (COUNT && (j + q) < cnt) { st.ntests[0] += st.alive[0]; st.ntests[1] += st.alive[1]; }
-                const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];
-                if (h0 || h1) {
-                    // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
-                    F2x3 su;
-                    su.x = bc(S.x) * k.u.x; su.y = bc(S.y) * k.u.y; su.z = bc(S.z) * k.u.z;
-                    const F2 ss = dot(su, su), ug = dot(k.u, k.go);
-                    const float t0 = fabsf(lo(ug)) * lo(k.il2) * mufu_sqrt(lo(ss));
-                    const float t1 = fabsf(hi(ug)) * hi(k.il2) * mufu_sqrt(hi(ss));
-                    const bool in0 = h0 && t0 > ray.tmin[0] && t0 < ray.tmax[0];
-                    const bool in1 = h1 && t1 > ray.tmin[1] && t1 < ray.tmax[1];
-                    // a ray that does not take the hit composites alpha = 0: its state is left unchanged
-                    const F2 alpha = mk2(in0 ? fminf(cfg.max_alpha, lo(k.araw)) : 0.0f, in1 ? fminf(cfg.max_alpha, hi(k.araw)) : 0.0f);
-                    const float4 F = r[4];
-                    const F2 w = alpha * st.T;
-                    st.D = fma(mk2(in0 ? t0 : 0.0f, in1 ? t1 : 0.0f), w, st.D);
-                    st.T = st.T * (bc(1.0f) - alpha);
-                    st.cr = fma(bc(F.x), w, st.cr); st.cg = fma(bc(F.y), w, st.cg); st.cb = fma(bc(F.z), w, st.cb);
-                    if (lo(w) > 0.0f) st.nhits[0]++;
-                    if (hi(w) > 0.0f) st.nhits[1]++;
-                    if (lo(st.T) < cfg.min_transmittance) st.alive[0] = false;
-                    if (hi(st.T) < cfg.min_transmittance) st.alive[1] = false;
+                Canon2 k[2];
+                bool acc[2][2];
+                float4 S[2];
+#pragma unroll
+                for (int p = 0; p < 2; ++p) {
+                    const float4 A = r[5 * p], B = r[5 * p + 1], Cm = r[5 * p + 2];
+                    S[p] = r[5 * p + 3];
+                    particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S[p].w, ray, k[p], acc[p][0], acc[p][1]);
+                }
+#pragma unroll
+                for (int p = 0; p < 2; ++p) {
+                    if (COUNT && (j + q + p) < cnt) { st.ntests[0] += st.alive[0]; st.ntests[1] += st.alive[1]; }
+                    const bool h0 = acc[p][0] && st.alive[0], h1 = acc[p][1] && st.alive[1];
+                    if (h0 || h1) {
+                        // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
+                        F2x3 su;
+                        su.x = bc(S[p].x) * k[p].u.x; su.y = bc(S[p].y) * k[p].u.y; su.z = bc(S[p].z) * k[p].u.z;
+                        const F2 ss = dot(su, su), ug = dot(k[p].u, k[p].go);
+                        const float t0 = fabsf(lo(ug)) * lo(k[p].il2) * mufu_sqrt(lo(ss));
+                        const float t1 = fabsf(hi(ug)) * hi(k[p].il2) * mufu_sqrt(hi(ss));
+                        const bool in0 = h0 && t0 > ray.tmin[0] && t0 < ray.tmax[0];
+                        const bool in1 = h1 && t1 > ray.tmin[1] && t1 < ray.tmax[1];
+                        // a ray that does not take the hit composites alpha = 0: its state is left unchanged
+                        const F2 alpha = mk2(in0 ? fminf(cfg.max_alpha, lo(k[p].araw)) : 0.0f, in1 ? fminf(cfg.max_alpha, hi(k[p].araw)) : 0.0f);
+                        const float4 F = r[5 * p + 4];
+                        const F2 w = alpha * st.T;
+                        st.D = fma(mk2(in0 ? t0 : 0.0f, in1 ? t1 : 0.0f), w, st.D);
+                        st.T = st.T * (bc(1.0f) - alpha);
+                        st.cr = fma(bc(F.x), w, st.cr); st.cg = fma(bc(F.y), w, st.cg); st.cb = fma(bc(F.z), w, st.cb);
+                        if (lo(w) > 0.0f) st.nhits[0]++;
+                        if (hi(w) > 0.0f) st.nhits[1]++;
+                        if (lo(st.T) < cfg.min_transmittance) st.alive[0] = false;
+                        if (hi(st.T) < cfg.min_transmittance) st.alive[1] = false;
+                    }
                 }
             }
         }
@@ -417,7 +426,7 @@ struct TileStager {
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+__global__ void __launch_bounds__(RENDER_THREADS, 5) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                     GutParticleSource src,
                                                                     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                     float4* __restrict__ rgba, float* __restrict__ dist,
