@@ -489,56 +489,46 @@ __global__ void __launch_bounds__(RENDER_THREADS, 5) gut_render_kernel(GutConfig
 // K5 backward (k_buffer_size == 0)
 // ---------------------------------------------------------------------------------------------------
 
-// Sum 16 per-lane values over the warp with 16 shuffles: each stage exchanges the half of the values the
-// partner lane will own.  On return lane l holds in v[0] the warp total of value
-// ((l>>4)&1)*8 + ((l>>3)&1)*4 + ((l>>2)&1)*2 + ((l>>1)&1); lanes l and l^1 hold the same value.
-GUT_D float warp_transpose_reduce16(float (&v)[16], uint32_t lane) {
+// Sum 16 values x 2 rays per lane over the warp.  Stage 0 adds the two rays of a lane and leaves value k in the low
+// and value k+8 in the high half of 8 packed registers; stages 1-3 (lane xor 16, 8, 4) exchange the packed half of
+// the values the partner lane will own (selects and shuffles per 32-bit half, adds packed); stage 4 (xor 2) splits
+// the last packed register; stage 5 (xor 1) finishes.  16 shuffles in all.  On return lane l holds the warp total of
+// value reduce_slot(l); lanes l and l^1 hold the same value.
+GUT_D uint32_t reduce_slot(uint32_t lane) { return ((lane >> 2) & 7u) | ((lane & 2u) << 2); }
+GUT_D F2 sel2(bool c, F2 a, F2 b) { F2 r; r.v = c ? a.v : b.v; return r; }
+GUT_D F2 shfl2(F2 a, int m) { F2 r; r.v = __shfl_xor_sync(0xffffffffu, a.v, m); return r; }
+GUT_D float warp_transpose_reduce(const F2 (&V)[16], uint32_t lane) {
+    F2 W[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) W[k] = mk2(lo(V[k]) + hi(V[k]), lo(V[k + 8]) + hi(V[k + 8]));
     {
         const bool up = lane & 16;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float send = up ? v[k] : v[k + 8];
-            const float keep = up ? v[k + 8] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-        }
+        for (int k = 0; k < 4; ++k) W[k] = sel2(up, W[k + 4], W[k]) + shfl2(sel2(up, W[k], W[k + 4]), 16);
     }
     {
         const bool up = lane & 8;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float send = up ? v[k] : v[k + 4];
-            const float keep = up ? v[k + 4] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-        }
+        for (int k = 0; k < 2; ++k) W[k] = sel2(up, W[k + 2], W[k]) + shfl2(sel2(up, W[k], W[k + 2]), 8);
     }
     {
         const bool up = lane & 4;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const float send = up ? v[k] : v[k + 2];
-            const float keep = up ? v[k + 2] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-        }
+        W[0] = sel2(up, W[1], W[0]) + shfl2(sel2(up, W[0], W[1]), 4);
     }
-    {
-        const bool up = lane & 2;
-        const float send = up ? v[0] : v[1];
-        const float keep = up ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-    return v[0];
+    const bool up = lane & 2;
+    float x = (up ? hi(W[0]) : lo(W[0])) + __shfl_xor_sync(0xffffffffu, up ? lo(W[0]) : hi(W[0]), 2);
+    x += __shfl_xor_sync(0xffffffffu, x, 1);
+    return x;
 }
 
 struct BwdRay {
-    F2 T_f, D_f, dA, dD;     // final transmittance / distance of the forward pass, upstream gradients
-    F2x3 C_f, dC;
-    F2 T, D;                 // running state of the re-walk
-    F2x3 C;
+    F2 T_f, dA, dD;          // final transmittance of the forward pass, upstream gradients
+    F2x3 dC;
+    F2 T;                    // running transmittance of the re-walk
+    F2 Drem;                 // forward distance / colour still to be composited behind the current hit
+    F2x3 Crem;
     bool alive[2];
 };
-
-GUT_D float sum2(F2 a) { return lo(a) + hi(a); }
 
 // Per accepted hit a ray produces 15 values that are LINEAR in the ray, so they can be summed over rays first (the two
 // rays of the lane, then the warp transpose-reduce, then one RED per value into the per-particle accumulator `raw`,
@@ -559,8 +549,10 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
                          const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
     const float minT = cfg.min_transmittance;
     const F2 one = bc(1.0f);
-    for (uint32_t j = 0; j < cnt; ++j) {
-        if ((j & (ALIVE_CHECK - 1)) == 0u && !__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
+    for (uint32_t j0 = 0; j0 < cnt; j0 += ALIVE_CHECK) {
+      if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
+      const uint32_t je = min(cnt, j0 + ALIVE_CHECK);
+      for (uint32_t j = j0; j < je; ++j) {
         const float4* r = rec + 5 * j;
         const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
         Canon2 k;
@@ -569,11 +561,10 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
         const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];  // no tMinMax test here
         if (!__any_sync(0xffffffffu, h0 || h1)) continue;
 
-        float v[16];
-#pragma unroll
-        for (int q = 0; q < 16; ++q) v[q] = 0.0f;
+        // every lane runs the hit math (rays that do not take the hit are masked, see above): no lane-level branch
+        F2 v[16];
         const float4 F = r[4];
-        if (h0 || h1) {
+        {
             const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
             const float isz = recb[3 * j + 2].x;
             const F2x3& go = k.go;
@@ -597,8 +588,8 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 
             // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's
             // element-wise ones).  grds = -dgo sg;  dL/dgrds = grds hs = kap sg  with  kap = -dgo hs
-            st.D = fma(w, gdist, st.D);
-            const F2 rD = (st.D_f - st.D) * invT;
+            st.Drem = fma(-w, gdist, st.Drem);
+            const F2 rD = st.Drem * invT;
             const F2 resD = mk2(fmaxf(lo(rD), 0.0f), fmaxf(hi(rD), 0.0f));
             const F2 aHit = (gdist - resD) * T * st.dD;
             const F2 wd = w * st.dD;
@@ -615,8 +606,8 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             const F2 resT = mk2(lo(alpha) < 0.999999f ? lo(st.T_f) * mufu_rcp(lo(om)) : lo(T),
                                 hi(alpha) < 0.999999f ? hi(st.T_f) * mufu_rcp(hi(om)) : hi(T));
             const F2 aDns = resT * st.dA;
-            st.C.x = fma(w, bc(F.x), st.C.x); st.C.y = fma(w, bc(F.y), st.C.y); st.C.z = fma(w, bc(F.z), st.C.z);
-            const F2 rx = (st.C_f.x - st.C.x) * invT, ry = (st.C_f.y - st.C.y) * invT, rz = (st.C_f.z - st.C.z) * invT;
+            st.Crem.x = fma(-w, bc(F.x), st.Crem.x); st.Crem.y = fma(-w, bc(F.y), st.Crem.y); st.Crem.z = fma(-w, bc(F.z), st.Crem.z);
+            const F2 rx = st.Crem.x * invT, ry = st.Crem.y * invT, rz = st.Crem.z * invT;
             const F2 resCx = mk2(fmaxf(lo(rx), 0.0f), fmaxf(hi(rx), 0.0f));
             const F2 resCy = mk2(fmaxf(lo(ry), 0.0f), fmaxf(hi(ry), 0.0f));
             const F2 resCz = mk2(fmaxf(lo(rz), 0.0f), fmaxf(hi(rz), 0.0f));
@@ -642,27 +633,29 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             Bg.x = il * fma(-grd.x, gx, X.x); Bg.y = il * fma(-grd.y, gx, X.y); Bg.z = il * fma(-grd.z, gx, X.z);
 
             // P_ij = go_i A_j + u_i B_j : diagonal -> scale, off-diagonal -> body-frame torque
-            v[0] = sum2(Ag.x); v[1] = sum2(Ag.y); v[2] = sum2(Ag.z);
-            v[3] = sum2(dDens);
-            v[4] = sum2(fma(bc(R0.y), fma(go.z, Ag.y, u.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, u.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
-            v[5] = sum2(fma(bc(R0.z), fma(go.x, Ag.z, u.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, u.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
-            v[6] = sum2(fma(bc(R1.x), fma(go.y, Ag.x, u.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, u.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
+            v[0] = (Ag.x); v[1] = (Ag.y); v[2] = (Ag.z);
+            v[3] = (dDens);
+            v[4] = (fma(bc(R0.y), fma(go.z, Ag.y, u.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, u.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
+            v[5] = (fma(bc(R0.z), fma(go.x, Ag.z, u.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, u.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
+            v[6] = (fma(bc(R1.x), fma(go.y, Ag.x, u.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, u.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
             F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x)));
             if (!UNIFORM) tr = fma(bc(isz), Ag.z * ray.dlt.z, fma(bc(R1.w), Ag.y * ray.dlt.y, fma(bc(R1.z), Ag.x * ray.dlt.x, tr)));
-            v[7] = sum2(tr);
-            v[8] = sum2(fma(go.x, Ag.x, fma(u.x, Bg.x, kd * sg2.x)));
-            v[9] = sum2(fma(go.y, Ag.y, fma(u.y, Bg.y, kd * sg2.y)));
-            v[10] = sum2(fma(go.z, Ag.z, fma(u.z, Bg.z, kd * sg2.z)));
-            v[11] = sum2(w * st.dC.x); v[12] = sum2(w * st.dC.y); v[13] = sum2(w * st.dC.z);
-            v[14] = -sum2(kd * ssum);
+            v[7] = (tr);
+            v[8] = (fma(go.x, Ag.x, fma(u.x, Bg.x, kd * sg2.x)));
+            v[9] = (fma(go.y, Ag.y, fma(u.y, Bg.y, kd * sg2.y)));
+            v[10] = (fma(go.z, Ag.z, fma(u.z, Bg.z, kd * sg2.z)));
+            v[11] = (w * st.dC.x); v[12] = (w * st.dC.y); v[13] = (w * st.dC.z);
+            v[14] = -(kd * ssum);
+            v[15] = bc(0.0f);
 
             st.T = nextT;
             if (lo(nextT) < minT) st.alive[0] = false;
             if (hi(nextT) < minT) st.alive[1] = false;
         }
-        const float total = warp_transpose_reduce16(v, lane);
-        const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
+        const float total = warp_transpose_reduce(v, lane);
+        const uint32_t slot = reduce_slot(lane);
         if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
+      }
     }
 }
 
@@ -699,10 +692,10 @@ __global__ void __launch_bounds__(RENDER_THREADS, 4) gut_render_backward_kernel(
             dC[h] = f3(gd.x, gd.y, gd.z);
         }
     }
-    st.T_f = mk2(Tf[0], Tf[1]); st.D_f = mk2(Df[0], Df[1]); st.dA = mk2(dA[0], dA[1]); st.dD = mk2(dD[0], dD[1]);
-    st.C_f.x = mk2(Cf[0].x, Cf[1].x); st.C_f.y = mk2(Cf[0].y, Cf[1].y); st.C_f.z = mk2(Cf[0].z, Cf[1].z);
+    st.T_f = mk2(Tf[0], Tf[1]); st.Drem = mk2(Df[0], Df[1]); st.dA = mk2(dA[0], dA[1]); st.dD = mk2(dD[0], dD[1]);
+    st.Crem.x = mk2(Cf[0].x, Cf[1].x); st.Crem.y = mk2(Cf[0].y, Cf[1].y); st.Crem.z = mk2(Cf[0].z, Cf[1].z);
     st.dC.x = mk2(dC[0].x, dC[1].x); st.dC.y = mk2(dC[0].y, dC[1].y); st.dC.z = mk2(dC[0].z, dC[1].z);
-    st.T = bc(1.0f); st.D = bc(0.0f); st.C = bc3(f3(0.f, 0.f, 0.f));
+    st.T = bc(1.0f);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     TileStager<true> stg;
