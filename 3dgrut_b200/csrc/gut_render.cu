@@ -32,8 +32,9 @@
 
 namespace {
 
-constexpr int RENDER_THREADS = 128;   // 4 warps per 16x16 tile: every lane carries TWO rays in packed fp32 registers
-constexpr int BATCH = 256;            // particles per staged batch = two per thread
+constexpr int RENDER_THREADS = 32;    // one warp per CTA = one 8x8 pixel block; every lane carries TWO rays in packed fp32 registers
+constexpr int BLOCKS_PER_TILE = 4;    // 8x8 blocks of a 16x16 tile
+constexpr int BATCH = 32;             // particles per staged batch = one per lane
 
 // ---- mbarrier / bulk-copy PTX -------------------------------------------------------------------------
 GUT_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -165,9 +166,9 @@ GUT_D F2x3 cross(const F2x3& a, const F2x3& b) {
 GUT_D F2x3 operator*(const F2x3& a, F2 s) { F2x3 r; r.x = a.x * s; r.y = a.y * s; r.z = a.z * s; return r; }
 
 // pixels owned by this thread: warp w -> 8x8 block (w&1, w>>1), lane -> column lane&7, rows 2*(lane>>3) and +1
-GUT_D void thread_pixels(const GutFrame& fr, uint32_t tile, uint32_t& px, uint32_t& py) {
+GUT_D void thread_pixels(const GutFrame& fr, uint32_t tile, uint32_t w, uint32_t& px, uint32_t& py) {
     const uint32_t tx = tile % fr.grid_x, ty = tile / fr.grid_x;
-    const uint32_t w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    const uint32_t l = threadIdx.x & 31;
     px = tx * GUT_TILE + (w & 1) * 8 + (l & 7);
     py = ty * GUT_TILE + (w >> 1) * 8 + (l >> 3) * 2;
 }
@@ -180,9 +181,9 @@ struct RayPair {
     uint32_t pix[2];
 };
 GUT_D RayPair make_ray_pair(const GutFrame& fr, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir, uint32_t tile,
-                            bool& at_origin) {
+                            uint32_t block, bool& at_origin) {
     uint32_t px, py;
-    thread_pixels(fr, tile, px, py);
+    thread_pixels(fr, tile, block, px, py);
     RayPair rp;
     float3 d[2], e[2];
     at_origin = true;
@@ -303,165 +304,128 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
     }
 }
 
-// ---- batch staging shared by K4 and K5 --------------------------------------------------------------------
+// ---- warp-private batch staging shared by K4 and K5 -----------------------------------------------------
 GUT_D void cp_async16(void* sdst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(sdst)), "l"(gsrc) : "memory");
 }
 GUT_D void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 GUT_D void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-constexpr uint32_t IDX_STAGE_WORDS = BATCH + 4;   // a batch's slice of the sorted list, widened to 16-byte alignment
-constexpr uint32_t PER_THREAD = BATCH / RENDER_THREADS;   // particles each thread gathers and expands per batch
-
 template <bool BWD>
 struct StageLayout {
     static constexpr uint32_t REC = BATCH * sizeof(GutRecord);
     static constexpr uint32_t RECB = BWD ? BATCH * sizeof(GutRecordBwd) : 0;
     static constexpr uint32_t RAW = BATCH * 4 * sizeof(float4);
-    static constexpr uint32_t IDX = 2 * IDX_STAGE_WORDS * sizeof(uint32_t);
-    static constexpr uint32_t TOTAL = REC + RECB + RAW + IDX;
+    static constexpr uint32_t TOTAL = REC + RECB + RAW;
 };
 
-// Per-CTA staging pipeline (see the header comment).  Batch bi of the tile is: idx slice by TMA (issued two batches
-// ahead by thread 0), raw parameter gather by cp.async (issued one batch ahead by every thread), expansion into
-// rec/recb right before the walk.
+// Staging pipeline of ONE warp (= one CTA, see the header comment).  A batch is 32 consecutive entries of the tile's
+// sorted list, one per lane.  Batch bi: the lane's list entry is a coalesced load two batches ahead (kept in a
+// register), its parameters are gathered by cp.async one batch ahead into `raw`, and right before the walk the lane
+// expands them into its record.  All ordering is warp-local: __syncwarp and cp.async.wait_group, no CTA barrier.
 template <bool BWD>
-struct TileStager {
-    float4* rec; float4* recb; float4* raw; uint32_t* idx; uint64_t* bar;
+struct WarpStager {
+    float4* rec; float4* recb; float4* raw;
     GutParticleSource src;
-    uint32_t b0, n, nb;
+    uint32_t b0, n, nb, lane;
     float3 origin;
-    uint32_t p_next[PER_THREAD];   // particles this thread gathers for the batch in flight
+    uint32_t p_cur, p_next, p_after;   // this lane's particle of batch bi, bi+1, bi+2
 
-    GUT_D void init(unsigned char* smem, uint64_t* bars, const GutParticleSource& s, uint32_t b0_, uint32_t n_, float3 origin_) {
-        rec = reinterpret_cast<float4*>(smem);
-        recb = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC);
-        raw = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB);
-        idx = reinterpret_cast<uint32_t*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB + StageLayout<BWD>::RAW);
-        bar = bars; src = s; b0 = b0_; n = n_; nb = (n_ + BATCH - 1) / BATCH; origin = origin_;
-#pragma unroll
-        for (uint32_t i = 0; i < PER_THREAD; ++i) p_next[i] = 0;
-    }
     GUT_D uint32_t count(uint32_t bi) const { return min((uint32_t)BATCH, n - bi * BATCH); }
-    // thread 0: bulk-copy the 16-byte aligned superset of sorted_idx[b0 + bi*BATCH, +count)
-    GUT_D void issue_idx(uint32_t bi) {
-        const uint32_t g = b0 + bi * BATCH, a = g & ~3u;
-        const uint32_t bytes = (((g - a) + count(bi)) * 4u + 15u) & ~15u;
-        mbar_expect_tx(&bar[bi & 1], bytes);
-        bulk_g2s(idx + (bi & 1) * IDX_STAGE_WORDS, src.sorted_idx + a, bytes, &bar[bi & 1]);
+    GUT_D uint32_t load_idx(uint32_t bi) const {
+        return (bi < nb && lane < count(bi)) ? __ldg(src.sorted_idx + b0 + bi * BATCH + lane) : 0u;
     }
-    // every thread: gather the parameters of its particles of batch bi into the raw planes
-    GUT_D void issue_gather(uint32_t bi) {
-        mbar_wait(&bar[bi & 1], (bi >> 1) & 1);
-#pragma unroll
-        for (uint32_t i = 0; i < PER_THREAD; ++i) {
-            const uint32_t t = threadIdx.x + i * RENDER_THREADS;
-            if (t < count(bi)) {
-                const uint32_t p = idx[(bi & 1) * IDX_STAGE_WORDS + ((b0 + bi * BATCH) & 3u) + t];
-                p_next[i] = p;
-                cp_async16(raw + t, src.density12 + 3 * (size_t)p);
-                cp_async16(raw + BATCH + t, src.density12 + 3 * (size_t)p + 1);
-                cp_async16(raw + 2 * BATCH + t, src.density12 + 3 * (size_t)p + 2);
-                cp_async16(raw + 3 * BATCH + t, src.features + p);
-            }
+    GUT_D void issue_gather(uint32_t bi, uint32_t p) {
+        if (bi < nb && lane < count(bi)) {
+            cp_async16(raw + lane, src.density12 + 3 * (size_t)p);
+            cp_async16(raw + BATCH + lane, src.density12 + 3 * (size_t)p + 1);
+            cp_async16(raw + 2 * BATCH + lane, src.density12 + 3 * (size_t)p + 2);
+            cp_async16(raw + 3 * BATCH + lane, src.features + p);
         }
         cp_async_commit();
     }
-    // every thread: its gathered particles -> records (the walk of the previous batch must be over: rec is single
-    // buffered).  Threads past the end of the list pad it to a multiple of WALK_UNROLL with records that can never be
-    // accepted: identity frame (so that u = d is never zero), density 0.
-    GUT_D void expand(uint32_t bi) {
+    GUT_D void init(unsigned char* smem, const GutParticleSource& s, uint32_t b0_, uint32_t n_, float3 origin_) {
+        rec = reinterpret_cast<float4*>(smem);
+        recb = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC);
+        raw = reinterpret_cast<float4*>(smem + StageLayout<BWD>::REC + StageLayout<BWD>::RECB);
+        src = s; b0 = b0_; n = n_; nb = (n_ + BATCH - 1) / BATCH; origin = origin_; lane = threadIdx.x;
+        p_cur = load_idx(0); p_next = load_idx(1); p_after = 0;
+        issue_gather(0, p_cur);
+    }
+    // gathered parameters of batch bi -> records; then put batch bi+1 (gather) and bi+2 (list entry) in flight.
+    // Lanes past the end of the list pad it to a multiple of WALK_UNROLL with records that can never be accepted:
+    // identity frame (so that u = d is never zero), density 0.
+    GUT_D void stage(uint32_t bi) {
         cp_async_wait_all();
+        __syncwarp();   // the walk of batch bi-1 is over in every lane: rec may be overwritten
         const uint32_t cnt = count(bi);
         const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
-#pragma unroll
-        for (uint32_t i = 0; i < PER_THREAD; ++i) {
-            const uint32_t t = threadIdx.x + i * RENDER_THREADS;
-            float4* out = rec + 5 * t;
-            if (t < cnt) {
-                const float4 r0 = raw[t], q = raw[BATCH + t], r2 = raw[2 * BATCH + t], ft = raw[3 * BATCH + t];
-                float3 c0, c1, c2;
-                quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
-                const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
-                const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
-                const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
-                out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
-                out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
-                out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
-                out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
-                out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_next[i]));
-                if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
-                    float4* outb = recb + 3 * t;
-                    outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
-                    outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
-                    outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
-                }
-            } else if (t < cnt_pad) {
-                out[0] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
-                out[1] = make_float4(0.0f, 1.0f, 0.0f, 0.0f);
-                out[2] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
-                out[3] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-                out[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float4* out = rec + 5 * lane;
+        if (lane < cnt) {
+            const float4 r0 = raw[lane], q = raw[BATCH + lane], r2 = raw[2 * BATCH + lane], ft = raw[3 * BATCH + lane];
+            float3 c0, c1, c2;
+            quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
+            const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
+            const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
+            const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
+            out[0] = make_float4(m0.x, m0.y, m0.z, dot(m0, v));
+            out[1] = make_float4(m1.x, m1.y, m1.z, dot(m1, v));
+            out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
+            out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
+            out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_cur));
+            if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
+                float4* outb = recb + 3 * lane;
+                outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
+                outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
+                outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
             }
+        } else if (lane < cnt_pad) {
+            out[0] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
+            out[1] = make_float4(0.0f, 1.0f, 0.0f, 0.0f);
+            out[2] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+            out[3] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+            out[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         }
+        __syncwarp();   // raw is consumed, rec is published
+        issue_gather(bi + 1, p_next);
+        p_after = load_idx(bi + 2);
     }
-    // prologue: idx slices of batches 0 and 1, gather of batch 0 (call after the barriers are initialised and published)
-    GUT_D void start() {
-        if (nb == 0) return;
-        if (threadIdx.x == 0) { issue_idx(0); if (nb > 1) issue_idx(1); }
-        issue_gather(0);
-    }
-    // after the CTA barrier that publishes rec of batch bi: put batch bi+1 (gather) and bi+2 (idx slice) in flight
-    GUT_D void advance(uint32_t bi) {
-        if (bi + 1 < nb) issue_gather(bi + 1);
-        if (threadIdx.x == 0 && bi + 2 < nb) issue_idx(bi + 2);   // stage bi&1 was last read by issue_gather(bi), one barrier ago
-    }
-    // early exit after batch bi: let everything in flight land before the CTA retires
-    GUT_D void drain(uint32_t bi) {
-        cp_async_wait_all();
-        if (bi + 2 < nb) mbar_wait(&bar[bi & 1], ((bi + 2) >> 1) & 1);
-    }
+    GUT_D void rotate() { p_cur = p_next; p_next = p_after; }
+    // before the warp retires: nothing may still be landing in its shared memory
+    GUT_D void drain() { cp_async_wait_all(); }
 };
 
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS, 5) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
-                                                                    GutParticleSource src,
-                                                                    const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
-                                                                    float4* __restrict__ rgba, float* __restrict__ dist,
-                                                                    float* __restrict__ hits, unsigned long long* __restrict__ counters) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t idx_bar[2];
+__global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+                                                                     GutParticleSource src,
+                                                                     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
+                                                                     float4* __restrict__ rgba, float* __restrict__ dist,
+                                                                     float* __restrict__ hits, unsigned long long* __restrict__ counters) {
+    __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
 
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
     bool at_origin;
-    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, at_origin);
+    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, block, at_origin);
+    const bool uniform = __all_sync(0xffffffffu, at_origin);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
-    TileStager<false> stg;
-    stg.init(smem_raw, idx_bar, src, b0, b1 - b0, fr.cam_centre);
-
-    if (threadIdx.x == 0) {
-        mbar_init(&idx_bar[0], 1);
-        mbar_init(&idx_bar[1], 1);
-        fence_mbar_init();
-    }
-    const bool uniform = __syncthreads_and(at_origin) != 0;  // also publishes the barrier initialisation
-    stg.start();
+    WarpStager<false> stg;
+    stg.init(smem_raw, src, b0, b1 - b0, fr.cam_centre);
 
     FwdState st;
     st.T = bc(1.0f); st.D = bc(0.0f); st.cr = st.cg = st.cb = bc(0.0f);
 #pragma unroll
     for (int h = 0; h < 2; ++h) { st.nhits[h] = 0; st.ntests[h] = 0; st.alive[h] = ray.inside[h] && ray.valid[h]; }
     for (uint32_t b = 0; b < stg.nb; ++b) {
-        stg.expand(b);
-        __syncthreads();
-        stg.advance(b);
+        stg.stage(b);
         if (uniform) forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
         else forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
-        if (__syncthreads_and(!st.alive[0] && !st.alive[1])) { stg.drain(b); break; }   // the tile saturated early
+        if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;   // the block saturated early
+        stg.rotate();
     }
+    stg.drain();
     if (COUNT) {
         unsigned long long t = st.ntests[0] + st.ntests[1], hh = st.nhits[0] + st.nhits[1];
 #pragma unroll
@@ -660,18 +624,18 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(RENDER_THREADS, 4) gut_render_backward_kernel(
+__global__ void __launch_bounds__(RENDER_THREADS, 16) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t idx_bar[2];
+    __shared__ __align__(16) unsigned char smem_raw[StageLayout<true>::TOTAL];
 
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
     const uint32_t lane = threadIdx.x & 31;
     bool at_origin;
-    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, at_origin);
+    const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, block, at_origin);
+    const bool uniform = __all_sync(0xffffffffu, at_origin);
 
     // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
     BwdRay st;
@@ -698,44 +662,30 @@ __global__ void __launch_bounds__(RENDER_THREADS, 4) gut_render_backward_kernel(
     st.T = bc(1.0f);
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
-    TileStager<true> stg;
-    stg.init(smem_raw, idx_bar, src, b0, b1 - b0, fr.cam_centre);
-
-    if (threadIdx.x == 0) {
-        mbar_init(&idx_bar[0], 1);
-        mbar_init(&idx_bar[1], 1);
-        fence_mbar_init();
-    }
-    const bool uniform = __syncthreads_and(at_origin) != 0;
-    stg.start();
+    WarpStager<true> stg;
+    stg.init(smem_raw, src, b0, b1 - b0, fr.cam_centre);
 
     for (uint32_t b = 0; b < stg.nb; ++b) {
-        stg.expand(b);
-        __syncthreads();
-        stg.advance(b);
+        stg.stage(b);
         if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
         else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
-        if (__syncthreads_and(!st.alive[0] && !st.alive[1])) { stg.drain(b); break; }
+        if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
+        stg.rotate();
     }
+    stg.drain();
 }
 
 template <int DEG>
 cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters, cudaStream_t stream) {
-    const size_t smem = StageLayout<false>::TOTAL;
-    cudaError_t e;
-    if (counters) {
-        e = cudaFuncSetAttribute(gut_render_kernel<DEG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        gut_render_kernel<DEG, true><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
-                                                                                      nullptr, nullptr, nullptr, counters);
-    } else {
-        e = cudaFuncSetAttribute(gut_render_kernel<DEG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        gut_render_kernel<DEG, false><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
-                                                                                       reinterpret_cast<float4*>(rgba), dist, hits, nullptr);
-    }
+    const uint32_t grid = frame.num_tiles * BLOCKS_PER_TILE;
+    if (counters)
+        gut_render_kernel<DEG, true><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
+                                                                       nullptr, counters);
+    else
+        gut_render_kernel<DEG, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
+                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr);
     return cudaGetLastError();
 }
 
@@ -744,12 +694,7 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
                                   const float* ray_ori, const float* ray_dir, const float* rgba,
                                   const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
                                   cudaStream_t stream) {
-    const size_t smem = StageLayout<true>::TOTAL;
-    cudaError_t e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(gut_render_backward_kernel<DEG>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if (e != cudaSuccess) return e;
-    gut_render_backward_kernel<DEG><<<frame.num_tiles, RENDER_THREADS, smem, stream>>>(
+    gut_render_backward_kernel<DEG><<<frame.num_tiles * BLOCKS_PER_TILE, RENDER_THREADS, 0, stream>>>(
         cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
         reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad);
     return cudaGetLastError();
