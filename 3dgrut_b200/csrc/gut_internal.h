@@ -19,13 +19,13 @@ struct GutFrame {
 };
 
 // What the compositing kernels stage per sorted (tile, particle) intersection.  The sorted particle list of a tile
-// (u32 indices, contiguous) arrives in shared memory by TMA bulk copy; the particle parameters it points to are
+// (u32 indices, contiguous) is read with coalesced loads two batches ahead; the particle parameters it points to are
 // gathered with 16-byte cp.async copies one batch ahead of the walk and expanded in shared memory into:
 //   GutRecord (80 B = 5 x float4): ms = diag(1/scale) * R^T maps world offsets to the particle's canonical
 //     (unit-Gaussian) frame; go = ms * (frame origin - position) is the canonical ray origin of every ray that
 //     starts at the frame origin (GutFrame::cam_centre) -- all of them for pinhole / fisheye ray bundles -- so a
 //     ray/particle test needs ONE mat-vec (the direction), not two;
-//   GutRecordBwd (48 B, backward only): quaternion, 1/scale, position.
+//   GutRecordBwd (48 B, backward only): the six scale ratios s_i / s_j of the body-frame torque and 1 / scale.
 struct __align__(16) GutRecord {
     float ms0x, ms0y, ms0z, gox;    // row 0 of ms | go.x
     float ms1x, ms1y, ms1z, goy;    // row 1       | go.y
@@ -36,9 +36,9 @@ struct __align__(16) GutRecord {
 };
 static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
 struct __align__(16) GutRecordBwd {
-    float qw, qx, qy, qz;           // quaternion (w,x,y,z)
-    float isx, isy, isz, pad0;      // 1 / scale
-    float px, py, pz, pad1;         // position
+    float r_yz, r_zy, r_xz, r_zx;   // s_y/s_z, s_z/s_y, s_x/s_z, s_z/s_x
+    float r_yx, r_xy, isx, isy;     // s_y/s_x, s_x/s_y, 1/s_x, 1/s_y
+    float isz, pad0, pad1, pad2;    // 1/s_z
 };
 static_assert(sizeof(GutRecordBwd) == 48, "backward record must be 3 float4");
 

@@ -6,27 +6,30 @@
 //   hit math gaussianParticle.hit / integrateHit (kernels/slang/models/gaussianParticles.slang:96-254),
 //   per-hit gradient processHitBwd (kernels/cuda/models/gaussianParticles.cuh:480-738).
 //
-// B200 design (DESIGN.md "K4/K5").  Both kernels are bound by instruction issue (ncu: sm__throughput > 80 %, DRAM
-// < 2 %), so the design minimises SASS instructions per ray x particle test:
-//  * one CTA per 16x16 tile, 8 warps, each warp owns a compact 8x4 pixel block (more lanes hit the same
-//    particle than with the reference's 16x2 rows -> better SIMT efficiency in the divergent hit branch);
-//  * staging runs one batch (256 particles) ahead of the walk and costs the walk nothing: the batch's slice of the
-//    sorted particle list is contiguous and arrives by cp.async.bulk (TMA bulk copy, UBLKCP) on an mbarrier; every
-//    thread then gathers ONE particle's parameters (3 x 16 B + its K1 colour) with cp.async (LDGSTS, no registers
-//    held across the walk) and, when the batch is due, expands them once into an 80-byte shared-memory record that
-//    all 256 rays of the tile read by broadcast -- quaternion->matrix math happens once per (tile, particle), not
-//    per ray.  DRAM sits at ~2 % during compositing, so the gathers are free; writing the records to HBM from the
-//    sort kernel instead (tried first) cost 1 ms per view;
-//  * records carry ms = diag(1/s) R^T and go = ms (frame origin - position).  When every ray of the tile starts
-//    at the frame origin (true for pinhole and fisheye bundles; checked per CTA, bitwise) the canonical ray origin
+// B200 design (DESIGN.md "K4/K5").  Both kernels are bound by FP32 instruction issue / the FMA pipe (ncu: DRAM < 2 %),
+// so the design minimises issue slots per ray x particle test and keeps the FMA pipe fed:
+//  * one WARP per CTA, owning an 8x8 pixel block (four blocks per 16x16 tile share the tile's sorted list).  A warp
+//    stages, walks and retires on its own: no CTA barrier, no waiting for the slowest warp of a tile, registers and
+//    shared memory are released the moment a block saturates;
+//  * every lane carries TWO rays (vertically adjacent pixels) in packed fp32 registers.  sm_100a issues FFMA2 / FMUL2 /
+//    FADD2 (fma.rn.f32x2 ...) in one slot for two fp32 lanes; per-particle record values enter as scalar broadcast
+//    operands.  The test, the compositing update and the whole per-hit gradient math run once for both rays; a ray
+//    that does not take the hit is masked (alpha = 0), not branched around;
+//  * staging runs one batch (32 particles, one per lane) ahead of the walk: the lane's entry of the tile's sorted list
+//    is a coalesced load two batches ahead, its parameters (3 x 16 B + its K1 colour) are gathered by cp.async (LDGSTS,
+//    no registers held across the walk) and expanded once into an 80-byte shared-memory record that all 64 rays of
+//    the block read by broadcast -- quaternion->matrix math happens once per (block, particle), not per ray.  DRAM
+//    sits at ~2 % during compositing, so the gathers are free;
+//  * records carry ms = diag(1/s) R^T and go = ms (frame origin - position).  When every ray of the block starts
+//    at the frame origin (true for pinhole and fisheye bundles; checked per warp, bitwise) the canonical ray origin
 //    is go itself and a test is ONE mat-vec, a cross product, one MUFU.RCP and one MUFU.EX2; otherwise go is
 //    corrected by ms (ray origin - frame origin).  Normalisation and the hit distance are computed for accepted
 //    hits only, from the unnormalised direction: t = |u.go| sqrt(|s*u|^2) / |u|^2;
 //  * the translation unit is built with -use_fast_math like the reference (setup_3dgut.py:83): FTZ, MUFU
 //    division / sqrt / exp2;
-//  * backward: lanes that hit compute the 14 per-particle gradient values; the warp sums them with a 16-shuffle
-//    transpose-reduce (not 14 x 5 butterflies) and issues ONE red.global.add.f32 instruction per (warp, particle)
-//    -- and nothing at all when no lane of the warp hit (the reference reduces and does 14 atomics regardless,
+//  * backward: the 15 per-particle gradient values of the block's 64 rays are summed with a packed 16-shuffle
+//    transpose-reduce (not 14 x 5 butterflies) and ONE red.global.add.f32 instruction per (warp, particle) -- and
+//    nothing at all when no ray of the block hit (the reference reduces and does 14 atomics regardless,
 //    shRadiativeGaussianParticles.cuh:409-482 called outside the isAlive branch at gutKBufferRenderer.cuh:379-383).
 #include "gut_internal.h"
 
@@ -36,33 +39,7 @@ constexpr int RENDER_THREADS = 32;    // one warp per CTA = one 8x8 pixel block;
 constexpr int BLOCKS_PER_TILE = 4;    // 8x8 blocks of a 16x16 tile
 constexpr int BATCH = 32;             // particles per staged batch = one per lane
 
-// ---- mbarrier / bulk-copy PTX -------------------------------------------------------------------------
 GUT_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-GUT_D void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-GUT_D void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-GUT_D void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-GUT_D void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-GUT_D void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
 
 // ---- generalized-Gaussian kernel response and its derivative wrt the squared canonical distance ---------
 // reference: canonicalRayMaxKernelResponse (gaussianParticles.slang:119-163), particleResponseGrd (gaussianParticles.cuh:219-261)

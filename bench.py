@@ -59,8 +59,19 @@ def workload_config(args, world):
                     f"NCCL allreduce of [N,12]+[N,48] fp32 gradients",
         "particles": args.particles, "views_per_step": args.views, "width": args.width, "height": args.height,
         "sph_degree": SPH_DEGREE, "parallelism": f"view-sharded dp{world}, particles replicated",
-        "l2_policy": "inputs larger than L2 (particle parameters + record stream > 126 MB per view)",
+        "l2_policy": "inputs larger than L2: every view streams the particle parameters and SH (3M x 240 B = 720 MB), the [N,16] gradient "
+                     "accumulators (192 MB) and the [N,12]+[N,48] gradients (720 MB) against a 126 MB L2",
     }
+
+
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the committed `ncu --set full` capture
+    (profiles/traffic.json, written by scripts/ncu_summarise.py); None when no capture is committed."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t["stages"][stage]["dram_bytes_per_launch"]
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -310,7 +321,8 @@ def run_ours(args):
     roofline = None
     if dominant:
         roofline = {"kernel": dominant["stage"], "bound": dominant["bound"], "achieved": dominant["achieved"], "peak": dominant["peak"],
-                    "unit": dominant["unit"], "frac": dominant["frac"], "traffic": None, "ms_per_launch": dominant["ms_per_launch"],
+                    "unit": dominant["unit"], "frac": dominant["frac"], "traffic": ncu_traffic(dominant["stage"]),
+                    "ms_per_launch": dominant["ms_per_launch"],
                     "peak_source": (f"derived: 148 SM x 128 lanes x 2 x {clk:.0f} MHz sampled under load (FP32 is not in MEASURED_PEAKS.json)"
                                     if dominant["bound"] == "fp32" else peak_src),
                     "note": "compositing is FP32-issue bound, not HBM or tensor bound (no stage is a dense contraction); "
