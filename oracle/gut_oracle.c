@@ -993,6 +993,161 @@ ORACLE_API void gut_oracle_render_bwd(const GutConfig* cfg, const GutCamera* cam
 }
 
 /* ------------------------------------------------------------------------------------------
+ * K5 (K > 0): renderBackward -> evalKBuffer<Backward>  gutKBufferRenderer.cuh:217-292 with the backward branch of
+ *   processHitParticle :116-152.  The hits leave the k-buffer in the forward's order; each one is "un-blended" from the
+ *   ray's final colour / distance / transmittance (back-to-front formulation walked front to back):
+ *     particleFeaturesIntegrateBwd          kernels/slang/models/shRadiativeParticles.slang:179-207
+ *       (bwd_diff of integrateRadiance<true> = lerp, :83-99; NB it is handed the UNclamped particle feature,
+ *        gutKBufferRenderer.cuh:131-136, while the forward composited max(feature, 0), :162)
+ *     particleDensityProcessHitBwdToBuffer  kernels/slang/models/gaussianParticles.slang:394-451
+ *       (bwd_diff of processHitFromBuffer<true> :254-283 = hit :188-222 + integrateHit<true> :224-252): Slang autodiff,
+ *        i.e. the TRUE derivative of alpha = min(MaxAlpha, response * density) (no gradient when clamped) and of the hit
+ *        distance |scale * grd * dot(grd, -gro)| -- unlike the hand-written K = 0 backward above.
+ *   Gradients are added with one atomic per value per hit (gaussianParticles.slang:61-75); fp64 accumulation here.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct { float Tb, Tg, Db, Dg; v3 Fb, Fg; } bwd_state;
+
+static void kbuffer_hit_bwd(const GutConfig* cfg, const float* density12, const float* features, const ray_t* ray, const hit_t* h,
+                            bwd_state* st, double* density_grad, double* feature_grad) {
+    const size_t pi = (size_t)h->idx;
+    const float alpha = h->alpha, t = h->t;
+    float alpha_grad = 0.0f;
+    v3 fgrad = V3(0.0f, 0.0f, 0.0f);
+    if (alpha > 0.0f) { /* particleFeaturesIntegrateBwd */
+        const v3 feat = V3(features[3 * pi], features[3 * pi + 1], features[3 * pi + 2]);
+        const float w = 1.0f / (1.0f - alpha);
+        st->Fb = scl3(w, sub3(st->Fb, scl3(alpha, feat)));
+        /* d lerp(I, f, a): da = dI . (f - I), df = dI a, dI_in = dI (1 - a) */
+        alpha_grad = st->Fg.x * (feat.x - st->Fb.x) + st->Fg.y * (feat.y - st->Fb.y) + st->Fg.z * (feat.z - st->Fb.z);
+        fgrad = scl3(alpha, st->Fg);
+        st->Fg = scl3(1.0f - alpha, st->Fg);
+    }
+    double* fg = feature_grad + 3 * pi;
+#pragma omp atomic
+    fg[0] += (double)fgrad.x;
+#pragma omp atomic
+    fg[1] += (double)fgrad.y;
+#pragma omp atomic
+    fg[2] += (double)fgrad.z;
+    if (!(alpha > 0.0f)) return;
+
+    /* particleDensityProcessHitBwdToBuffer */
+    const float w = 1.0f / (1.0f - alpha);
+    st->Tb *= w;
+    st->Db = (st->Db - t * alpha) * w;
+    const raw_particle* p = (const raw_particle*)(density12 + 12 * pi);
+    v3 rt[3]; particle_rotT(p, rt);
+    canon_t c;
+    if (!particle_hit(cfg, p, rt, ray->o, ray->d, &c)) return; /* processHitFromBuffer re-evaluates hit(): same result as the forward */
+    const float depth = canon_distance(p, &c);
+    /* integrateHit<true>: D_out = lerp(D_in, depth, alpha), T_out = T_in (1 - alpha), returns alpha */
+    const float d_alpha = alpha_grad + st->Dg * (depth - st->Db) - st->Tg * st->Tb;
+    const float d_depth = st->Dg * c.alpha;
+    st->Dg *= (1.0f - c.alpha);
+    st->Tg *= (1.0f - c.alpha);
+    /* hit(): alpha = min(MaxAlpha, resp * density) -- no gradient when the clamp is active */
+    const float araw = c.resp * p->density;
+    const int unclamped = !(cfg->max_alpha < araw);
+    const float d_resp = unclamped ? d_alpha * p->density : 0.0f;
+    const float d_dns = unclamped ? d_alpha * c.resp : 0.0f;
+    const float d_g = particle_response_grd(cfg->kernel_degree, c.g, c.resp, d_resp);
+    /* g = |grd x gro|^2 */
+    const v3 gc = cross3(c.grd, c.gro);
+    const v3 gcg = scl3(2.0f * d_g, gc);
+    v3 d_grd = cross3(c.gro, gcg);
+    v3 d_gro = cross3(gcg, c.grd);
+    /* depth = |grds|, grds = scale * grd * dp, dp = dot(grd, -gro) */
+    const float dp = dot3(c.grd, scl3(-1.0f, c.gro));
+    const v3 grds = scl3(dp, mul3(p->scale, c.grd));
+    v3 d_scl = V3(0.0f, 0.0f, 0.0f);
+    if (depth > 0.0f) {
+        const v3 d_grds = scl3(d_depth / depth, grds);
+        d_scl = scl3(dp, mul3(d_grds, c.grd));
+        d_grd = add3(d_grd, scl3(dp, mul3(d_grds, p->scale)));
+        const float d_dp = dot3(d_grds, mul3(p->scale, c.grd));
+        d_grd = sub3(d_grd, scl3(d_dp, c.gro));
+        d_gro = sub3(d_gro, scl3(d_dp, c.grd));
+    }
+    /* cannonicalRay: grd = normalize(giscl * R^T d), gro = giscl * R^T (o - pos) */
+    const v3 d_grdu = safe_normalize_bw(c.grdu, d_grd);
+    const v3 d_rdr = mul3(c.giscl, d_grdu);
+    const v3 d_gposcr = mul3(c.giscl, d_gro);
+    const v3 d_giscl = add3(mul3(c.ray_dir_r, d_grdu), mul3(c.gposcr, d_gro));
+    d_scl = sub3(d_scl, V3(d_giscl.x / (p->scale.x * p->scale.x), d_giscl.y / (p->scale.y * p->scale.y), d_giscl.z / (p->scale.z * p->scale.z)));
+    const v3 d_gposc = V3(d_gposcr.x * rt[0].x + d_gposcr.y * rt[1].x + d_gposcr.z * rt[2].x,
+                          d_gposcr.x * rt[0].y + d_gposcr.y * rt[1].y + d_gposcr.z * rt[2].y,
+                          d_gposcr.x * rt[0].z + d_gposcr.y * rt[1].z + d_gposcr.z * rt[2].z);
+    const v4 q1 = matmul_bw_quat(c.gposc, d_gposcr, p->qw, p->qx, p->qy, p->qz);
+    const v4 q2 = matmul_bw_quat(ray->d, d_rdr, p->qw, p->qx, p->qy, p->qz);
+    const float vals[11] = {-d_gposc.x, -d_gposc.y, -d_gposc.z, d_dns, q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w,
+                            d_scl.x, d_scl.y, d_scl.z};
+    double* dg = density_grad + 12 * pi;
+    for (int k = 0; k < 11; ++k) {
+#pragma omp atomic
+        dg[k] += (double)vals[k];
+    }
+}
+
+ORACLE_API void gut_oracle_render_bwd_kbuffer(const GutConfig* cfg, const GutCamera* cam, uint32_t N, uint32_t W, uint32_t H,
+                                              const float* density12, const float* features,
+                                              const float* ray_ori, const float* ray_dir,
+                                              const uint32_t* tile_ranges, const uint32_t* sorted_idx,
+                                              const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
+                                              double* density_grad /* [N,12] += */, double* feature_grad /* [N,3] += */,
+                                              const uint32_t* tile_list, uint32_t n_tile_list) {
+    (void)N;
+    const frame_consts f = make_frame(cam, W, H);
+    const int K = cfg->k_buffer_size;
+    const float minT = cfg->min_transmittance;
+    const int64_t n_work = tile_list ? (int64_t)n_tile_list : (int64_t)f.gx * f.gy;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t work = 0; work < n_work; ++work) {
+        const int64_t tile = tile_list ? (int64_t)tile_list[work] : work;
+        const uint32_t tx = (uint32_t)(tile % f.gx), ty = (uint32_t)(tile / f.gx);
+        const uint32_t r0 = tile_ranges[2 * tile], r1 = tile_ranges[2 * tile + 1];
+        for (uint32_t py = ty * TILE; py < ty * TILE + TILE && py < H; ++py)
+            for (uint32_t px = tx * TILE; px < tx * TILE + TILE && px < W; ++px) {
+                const size_t idx = (size_t)px + (size_t)W * py;
+                ray_t ray = init_ray(&f, ray_ori, ray_dir, idx);
+                if (!ray.valid) continue;
+                bwd_state st; /* initializeBackwardRay rayPayloadBackward.cuh:46-55 */
+                st.Tb = 1.0f - rgba[4 * idx + 3];
+                st.Tg = -1.0f * rgba_grad[4 * idx + 3];
+                st.Db = dist[idx]; st.Dg = dist_grad[idx];
+                st.Fb = V3(rgba[4 * idx], rgba[4 * idx + 1], rgba[4 * idx + 2]);
+                st.Fg = V3(rgba_grad[4 * idx], rgba_grad[4 * idx + 1], rgba_grad[4 * idx + 2]);
+                float T = 1.0f; int alive = 1;
+                hit_t kb[MAX_K]; int nk = 0;
+                for (int k = 0; k < K; ++k) { kb[k].idx = -1; kb[k].t = -1.0f; kb[k].alpha = 0.0f; }
+#define PROCESS_HIT_BWD(HT)                                                                    \
+    do {                                                                                      \
+        const hit_t* h_ = (HT);                                                               \
+        kbuffer_hit_bwd(cfg, density12, features, &ray, h_, &st, density_grad, feature_grad); \
+        T *= (1.0f - h_->alpha);                                                              \
+        if (T < minT) alive = 0;                                                              \
+    } while (0)
+                for (uint32_t s = r0; alive && s < r1; ++s) {
+                    const uint32_t pi = sorted_idx[s];
+                    if (pi == 0xFFFFFFFFu) break;
+                    const raw_particle* p = (const raw_particle*)(density12 + 12 * (size_t)pi);
+                    v3 rt[3]; particle_rotT(p, rt);
+                    canon_t c;
+                    if (!particle_hit(cfg, p, rt, ray.o, ray.d, &c)) continue;
+                    hit_t h = {(int)pi, canon_distance(p, &c), c.alpha};
+                    if (!(h.t > ray.tmin && h.t < ray.tmax)) continue;
+                    if (K == 0) { PROCESS_HIT_BWD(&h); continue; }
+                    if (nk == K) { hit_t closest = kb[0]; PROCESS_HIT_BWD(&closest); kb[0].t = -1.0f; } else nk++;
+                    for (int i = K - 1; i >= 0; --i)
+                        if (h.t > kb[i].t) { hit_t tmp = kb[i]; kb[i] = h; h = tmp; }
+                }
+                if (K > 0)
+                    for (int i = 0; alive && i < nk; ++i) PROCESS_HIT_BWD(&kb[K - nk + i]);
+#undef PROCESS_HIT_BWD
+            }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
  * K6: GUTProjector::evalBackward gutProjector.cuh:390-430 ; radianceFromSpHBwd gaussianParticles.cuh:120-187
  * sph_grad [N,ncoef,3] += ; the view-direction -> position term is a no-op (gaussianParticles.slang:307-318).
  * ---------------------------------------------------------------------------------------- */

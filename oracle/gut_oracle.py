@@ -140,8 +140,8 @@ def forward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, tile_l
 
 
 def backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, fwd, rgba_grad, dist_grad, tile_list=None):
-    """K5 + K6 (src/gutRenderer.cu:400-497) for k_buffer_size == 0. Returns ([N,12], [N,ncoef*3]) float32."""
-    assert cfg.k_buffer_size == 0, "oracle backward implements the K=0 path (gutKBufferRenderer.cuh:294-386)"
+    """K5 + K6 (src/gutRenderer.cu:400-497). k_buffer_size == 0: evalBackwardNoKBuffer (gutKBufferRenderer.cuh:294-386);
+    k_buffer_size > 0: evalKBuffer<Backward> (:217-292).  Returns ([N,12], [N,ncoef*3], [N,3]) float32."""
     density12 = _f32(density12); sph = _f32(sph)
     N = density12.shape[0]
     ncoef = (cfg.sph_max_degree + 1) ** 2
@@ -153,7 +153,8 @@ def backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, fwd, 
     rgba_grad = _f32(rgba_grad); dist_grad = _f32(dist_grad)
     proj, bins = fwd["proj"], fwd["bins"]
     tl_p, tl_n, _keep = _tiles(tile_list)
-    lib().gut_oracle_render_bwd(C.byref(cfg), C.byref(cam), C.c_uint32(N), C.c_uint32(W), C.c_uint32(H), _p(density12),
+    fn = lib().gut_oracle_render_bwd if cfg.k_buffer_size == 0 else lib().gut_oracle_render_bwd_kbuffer
+    fn(C.byref(cfg), C.byref(cam), C.c_uint32(N), C.c_uint32(W), C.c_uint32(H), _p(density12),
                                 _p(proj["features"]), _p(ray_ori), _p(ray_dir), _p(bins["tile_ranges"]),
                                 _p(bins["sorted_values"]), _p(fwd["rgba"]), _p(rgba_grad), _p(fwd["dist"]), _p(dist_grad),
                                 _p(dg), _p(fg), tl_p, tl_n)

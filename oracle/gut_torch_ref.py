@@ -419,3 +419,159 @@ def forward_backward(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degre
         out["density_grad"] = g12
         out["radiance_grad"] = leaves["sph"].grad.numpy()
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# k_buffer_size > 0 (sorted compositing): gutKBufferRenderer.cuh:28-85 (HitParticleKBuffer), :217-292 (evalKBuffer)
+# ---------------------------------------------------------------------------------------------------
+def _kbuffer_order(K, alpha, tt, acc, min_t):
+    """Order in which one ray processes its accepted list entries: a K-entry buffer sorted by hit distance; when full the
+    closest entry is processed before the new one is inserted; the rest drains closest-first; processing stops when the
+    transmittance falls below min_t.  alpha/tt/acc are 1-D numpy arrays over the tile's list."""
+    buf = []          # (t, list position), ascending t; mirrors m_kbuffer[K - numHits ...]
+    order = []
+    T = 1.0
+    for l in np.nonzero(acc)[0]:
+        if len(buf) == K:
+            t0, l0 = buf.pop(0)
+            order.append(l0)
+            T *= 1.0 - alpha[l0]
+            if T < min_t:
+                return order
+        # insert: bubbles past entries with strictly smaller t (hitParticle.hitT > m_kbuffer[i].hitT)
+        pos = len(buf)
+        while pos > 0 and not (tt[l] > buf[pos - 1][0]):
+            pos -= 1
+        buf.insert(pos, (tt[l], l))
+    for t0, l0 in buf:
+        order.append(l0)
+        T *= 1.0 - alpha[l0]
+        if T < min_t:
+            break
+    return order
+
+
+def forward_backward_kbuffer(cfg, cam, density12, sph, ray_ori, ray_dir, W, H, sph_degree, tile_ranges, sorted_values, tiles_count,
+                             rgba_grad=None, dist_grad=None, dtype=torch.float64):
+    """K4 / K5 / K6 for k_buffer_size > 0.  The forward is composited by torch in the k-buffer's order; the backward applies
+    the reference's per-hit un-blend recurrences (shRadiativeParticles.slang:179-207, gaussianParticles.slang:394-451) to get
+    dL/dalpha and dL/ddepth of every processed hit and lets autograd differentiate alpha and depth wrt the particle
+    parameters -- which is what Slang's bwd_diff does there (true derivatives, clamp masked)."""
+    K = int(cfg.k_buffer_size)
+    d12 = torch.as_tensor(np.asarray(density12), dtype=dtype)
+    pos, dns, quat, scl = d12[:, 0:3].clone(), d12[:, 3].clone(), d12[:, 4:8].clone(), d12[:, 8:11].clone()
+    sphc = torch.as_tensor(np.asarray(sph), dtype=dtype).clone()
+    want_grad = rgba_grad is not None
+    for v in (pos, dns, quat, scl, sphc):
+        v.requires_grad_(want_grad)
+    fc = frame_constants(cam, dtype)
+    feats = features_from_sh(cfg, fc, pos, sphc, sph_degree)
+    feats = feats * torch.as_tensor(np.asarray(tiles_count) > 0, dtype=dtype).unsqueeze(-1)
+    n = d12.shape[0]
+    ro = torch.as_tensor(np.asarray(ray_ori), dtype=dtype).reshape(H, W, 3)
+    rd = torch.as_tensor(np.asarray(ray_dir), dtype=dtype).reshape(H, W, 3)
+    o_w = ro @ fc["R_c2w"].T + fc["t_c2w"]
+    d_w = rd @ fc["R_c2w"].T
+    inv = 1.0 / d_w
+    ta, tb = (-1e6 - o_w) * inv, (1e6 - o_w) * inv
+    tmin = torch.minimum(ta, tb).amax(-1).clamp_min(0)
+    tmax = torch.maximum(ta, tb).amin(-1)
+    valid_ray = tmax > tmin
+    gx = (W + TILE - 1) // TILE
+    Rt = quat_wxyz_to_matrix(quat).transpose(-1, -2)
+    rgba = torch.zeros((H, W, 4), dtype=dtype)
+    dist = torch.full((H, W), 1e6, dtype=dtype)
+    hits = torch.zeros((H, W), dtype=dtype)
+    g12 = np.zeros((n, 12)); fgrad_acc = torch.zeros((n, 3), dtype=dtype)
+    leaves = [pos, dns, quat, scl]
+    leaf_grads = [torch.zeros_like(v) for v in leaves]
+    if want_grad:
+        rg = torch.as_tensor(np.asarray(rgba_grad), dtype=dtype).reshape(H, W, 4)
+        dg = torch.as_tensor(np.asarray(dist_grad), dtype=dtype).reshape(H, W)
+    for t in range(tile_ranges.shape[0]):
+        b0, b1 = int(tile_ranges[t, 0]), int(tile_ranges[t, 1])
+        ty, tx = divmod(t, gx)
+        ys, xs = slice(ty * TILE, min((ty + 1) * TILE, H)), slice(tx * TILE, min((tx + 1) * TILE, W))
+        hh, ww = ys.stop - ys.start, xs.stop - xs.start
+        vr = valid_ray[ys, xs].reshape(-1)
+        npx = hh * ww
+        if b1 <= b0:
+            rgba[ys, xs] = 0.0
+            dist[ys, xs] = torch.where(vr, torch.zeros(npx, dtype=dtype), torch.full((npx,), 1e6, dtype=dtype)).reshape(hh, ww)
+            continue
+        o = o_w[ys, xs].reshape(-1, 3); d = d_w[ys, xs].reshape(-1, 3)
+        idx = torch.as_tensor(sorted_values[b0:b1].astype(np.int64))
+        p, s, rt, dn = pos[idx], scl[idx], Rt[idx], dns[idx]
+        giscl = 1.0 / s
+        gro = giscl.unsqueeze(0) * torch.einsum("lij,plj->pli", rt, o.unsqueeze(1) - p.unsqueeze(0))
+        grdu = giscl.unsqueeze(0) * torch.einsum("lij,pj->pli", rt, d)
+        grd = grdu / grdu.norm(dim=-1, keepdim=True)
+        cr = torch.linalg.cross(grd, gro, dim=-1)
+        g2 = (cr * cr).sum(-1)
+        resp = _response(cfg.kernel_degree, g2)
+        alpha = torch.clamp(resp * dn.unsqueeze(0), max=cfg.max_alpha)
+        grds = s.unsqueeze(0) * grd * (-(grd * gro).sum(-1, keepdim=True))
+        tt = torch.sqrt((grds * grds).sum(-1))
+        with torch.no_grad():
+            acc = (resp > cfg.min_kernel_response) & (alpha > cfg.min_alpha) & (tt > tmin[ys, xs].reshape(-1, 1)) & \
+                  (tt < tmax[ys, xs].reshape(-1, 1)) & vr.unsqueeze(1)
+            a_np, t_np, acc_np = alpha.numpy(), tt.numpy(), acc.numpy()
+            orders = [_kbuffer_order(K, a_np[q], t_np[q], acc_np[q], cfg.min_transmittance) for q in range(npx)]
+            lmax = max(1, max(len(x) for x in orders))
+            sel = torch.zeros((npx, lmax), dtype=torch.long)
+            msk = torch.zeros((npx, lmax), dtype=torch.bool)
+            for q, od in enumerate(orders):
+                sel[q, :len(od)] = torch.as_tensor(od, dtype=torch.long)
+                msk[q, :len(od)] = True
+        mf = msk.to(dtype)
+        a_sel = torch.gather(alpha, 1, sel) * mf
+        t_sel = torch.gather(tt, 1, sel) * mf
+        pidx = idx[sel]                                                    # [P, L] particle of each processed hit
+        f_raw = feats[pidx]                                                # unclamped
+        f_cl = torch.clamp(f_raw, min=0)
+        T_before = torch.cat([torch.ones((npx, 1), dtype=dtype), torch.cumprod(1 - a_sel, dim=1)[:, :-1]], 1)
+        w = a_sel * T_before
+        C = (w.unsqueeze(-1) * f_cl).sum(1)
+        D = (w * t_sel).sum(1)
+        T_fin = torch.prod(1 - a_sel, dim=1)
+        vrf = vr.to(dtype)
+        rgba[ys, xs] = (torch.cat([C, (1 - T_fin).unsqueeze(-1)], -1) * vrf.unsqueeze(-1)).detach().reshape(hh, ww, 4)
+        dist[ys, xs] = torch.where(vr, D, torch.full_like(D, 1e6)).detach().reshape(hh, ww)
+        hits[ys, xs] = ((w > 0) & msk).sum(1).to(dtype).reshape(hh, ww)
+        if not want_grad:
+            continue
+        with torch.no_grad():
+            Tb = T_fin.clone(); Tg = -rg[ys, xs, 3].reshape(-1).clone()
+            Db = D.clone(); Dg = dg[ys, xs].reshape(-1).clone()
+            Fb = C.clone(); Fg = rg[ys, xs, :3].reshape(-1, 3).clone()
+            d_alpha = torch.zeros_like(a_sel); d_depth = torch.zeros_like(a_sel)
+            for kk in range(lmax):
+                a = a_sel[:, kk]; on = (a > 0) & msk[:, kk]
+                onf = on.to(dtype)
+                wgt = 1.0 / (1.0 - a)
+                fr = f_raw[:, kk]
+                Fb_n = (Fb - fr * a.unsqueeze(-1)) * wgt.unsqueeze(-1)
+                Fb = torch.where(on.unsqueeze(-1), Fb_n, Fb)
+                ag = (Fg * (fr - Fb)).sum(-1) * onf
+                fgrad_acc.index_add_(0, pidx[:, kk], Fg * (a * onf).unsqueeze(-1))
+                Fg = Fg * (1 - a * onf).unsqueeze(-1)
+                Tb = torch.where(on, Tb * wgt, Tb)
+                Db = torch.where(on, (Db - t_sel[:, kk] * a) * wgt, Db)
+                d_alpha[:, kk] = (ag + Dg * (t_sel[:, kk] - Db) - Tg * Tb) * onf
+                d_depth[:, kk] = Dg * a * onf
+                Dg = Dg * (1 - a * onf); Tg = Tg * (1 - a * onf)
+        gr = torch.autograd.grad([a_sel, t_sel], leaves, grad_outputs=[d_alpha, d_depth], retain_graph=True, allow_unused=True)
+        for acc_g, g_ in zip(leaf_grads, gr):
+            if g_ is not None:
+                acc_g += g_
+    out = {"rgba": rgba.numpy(), "dist": dist.numpy(), "hits": hits.numpy()}
+    if want_grad:
+        g12[:, 0:3] = leaf_grads[0].numpy(); g12[:, 3] = leaf_grads[1].numpy()
+        g12[:, 4:8] = leaf_grads[2].numpy(); g12[:, 8:11] = leaf_grads[3].numpy()
+        # K6: mask by feature > 0, back through the SH evaluation (no position gradient through the view direction)
+        fg = fgrad_acc * (feats.detach() > 0).to(dtype)
+        sg, = torch.autograd.grad([feats], [sphc], grad_outputs=[fg])
+        out["density_grad"] = g12
+        out["radiance_grad"] = sg.numpy()
+        out["feature_grad"] = fgrad_acc.numpy()
+    return out

@@ -91,6 +91,44 @@ def test_compositing_and_gradients_two_restatements_agree(kind, deg, seed):
     assert rel_l2(gsph, ref["radiance_grad"]) < 2e-4
 
 
+@pytest.mark.parametrize("kind,deg,seed,K", [("init", 3, 5, 16), ("dense", 2, 9, 4), ("init", 1, 11, 1)])
+def test_kbuffer_compositing_and_gradients_two_restatements_agree(kind, deg, seed, K):
+    """k_buffer_size > 0 (gutKBufferRenderer.cuh:28-85, 217-292): the C oracle's hand-derived true-derivative backward against
+    torch autograd of alpha / hit distance driven by the reference's un-blend recurrences."""
+    n, w, h = 900, 48, 32
+    cfg = abi.default_config()
+    cfg.k_buffer_size = K
+    scene, view, cam, d12, sph = _inputs(n, w, h, seed=seed, kind=kind)
+    if kind == "dense":   # some negative colours: the K>0 backward un-blends with the UNclamped feature (reference quirk)
+        sph = sph.copy(); sph[::7, 0:3] -= 2.5
+    ro, rd = view["rays_ori"].numpy(), view["rays_dir"].numpy()
+    fwd = O.forward(cfg, cam, d12, sph, ro, rd, w, h, deg)
+    border = fwd["margin"] < BORDERLINE_MARGIN
+    rng = np.random.default_rng(seed)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    rgba_grad[border] = 0; dist_grad[border] = 0
+    g12, gsph, gfeat = O.backward(cfg, cam, d12, sph, ro, rd, w, h, deg, fwd, rgba_grad, dist_grad)
+    ref = T.forward_backward_kbuffer(cfg, cam, d12, sph, ro, rd, w, h, deg, fwd["bins"]["tile_ranges"], fwd["bins"]["sorted_values"],
+                                     fwd["proj"]["tiles_count"], rgba_grad, dist_grad)
+    clean = ~border
+    assert clean.mean() > 0.97
+    assert np.abs(ref["rgba"] - fwd["rgba"])[clean].max() < 5e-5
+    assert np.abs(ref["dist"] - fwd["dist"])[clean].max() < 5e-5 * max(1.0, float(fwd["dist"].max()))
+    assert np.array_equal(ref["hits"][clean], fwd["hits"][clean])
+    assert fwd["hits"].max() > min(K, 3)
+    if K > 1:   # the sorted path really reorders: it differs from the unsorted K = 0 composite somewhere
+        cfg0 = abi.default_config()
+        unsorted = O.forward(cfg0, cam, d12, sph, ro, rd, w, h, deg)
+        assert np.abs(unsorted["rgba"] - fwd["rgba"]).max() > 1e-4
+    assert rel_l2(gfeat, ref["feature_grad"]) < 2e-4
+    for lo, hi, what in ((0, 3, "position"), (3, 4, "density"), (4, 8, "rotation"), (8, 11, "scale")):
+        e = rel_l2(g12[:, lo:hi], ref["density_grad"][:, lo:hi])
+        assert e < 5e-4, (what, e)
+    assert np.all(g12[:, 11] == 0)
+    assert rel_l2(gsph, ref["radiance_grad"]) < 2e-4
+
+
 def _single_particle(density, scale, pos=(0.0, 0.0, 0.0), w=33, h=33):
     """One isotropic Gaussian at `pos`, camera on the -y axis looking at the origin from distance 4."""
     view = syn.make_view(w, h)
