@@ -253,7 +253,7 @@ int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
     if (!degree_supported(cfg->kernel_degree)) return GUT_ERR_UNSUPPORTED;
     if (cfg->sph_max_degree < 0 || cfg->sph_max_degree > 3) return GUT_ERR_UNSUPPORTED;
     if (cfg->ut_require_all_sigma_points_valid) return GUT_ERR_UNSUPPORTED;  // static_assert in threedgut.cuh:73
-    if (cfg->k_buffer_size != 0) return GUT_ERR_UNSUPPORTED;                 // sorted (K>0) path: SURVEY 8f rank 2, not built yet
+    if (cfg->k_buffer_size != 0 && !gut_kbuffer_size_supported(cfg->k_buffer_size)) return GUT_ERR_UNSUPPORTED;  // K in {0, 4, 8, 16}
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return GUT_ERR_CUDA;
     GutHandle* h = new GutHandle();
@@ -354,8 +354,12 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         {
             StageTimer t(h, ST_RENDER, s);
             const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)d_density, (const float4*)h->features.p};
-            GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
-                                          d_rgba, d_dist, d_hits, nullptr, s));
+            if (h->cfg.k_buffer_size > 0)
+                GUT_CUDA(h, gut_launch_render_kbuffer(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
+                                                      d_rgba, d_dist, d_hits, s));
+            else
+                GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
+                                              d_rgba, d_dist, d_hits, nullptr, s));
             h->launches += 1;
         }
     }
@@ -413,8 +417,12 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
     if (h->fwd_M > 0) {
         StageTimer t(h, ST_BWD_RENDER, s);
         const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)d_density, (const float4*)h->features.p};
-        GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
-                                               (float*)h->raw_grad.p, s));
+        if (h->cfg.k_buffer_size > 0)
+            GUT_CUDA(h, gut_launch_render_kbuffer_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba,
+                                                           d_rgba_grad, d_dist, d_dist_grad, (float*)h->raw_grad.p, s));
+        else
+            GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
+                                                   (float*)h->raw_grad.p, s));
         h->launches += 1;
     }
     {
@@ -511,6 +519,7 @@ int gut_measure_work(GutHandle* h, void* stream_, const float* d_ray_ori, const 
     if (!h->fwd_valid || h->fwd_stream != s) return fail(h, GUT_ERR_NO_FORWARD, "gut_measure_work needs a preceding forward on this stream");
     *tests = 0; *hits = 0;
     if (h->fwd_M == 0) return GUT_OK;
+    if (h->cfg.k_buffer_size > 0) return fail(h, GUT_ERR_UNSUPPORTED, "gut_measure_work counts the k_buffer_size == 0 walk only");
     DeviceGuard guard(h->device);
     GUT_CUDA(h, ensure(h->stats, 16, s));
     GUT_CUDA(h, cudaMemsetAsync(h->stats.p, 0, 16, s));

@@ -92,5 +92,15 @@ cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& fra
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
                                        float* raw_grad /* [N,16] accumulators, see gut_render.cu backward_walk */, cudaStream_t stream);
 
+// k_buffer_size > 0 (sorted compositing, gut_render_kbuffer.cu): same arguments as the two launchers above
+bool gut_kbuffer_size_supported(int k);
+cudaError_t gut_launch_render_kbuffer(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
+                                      const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
+                                      cudaStream_t stream);
+cudaError_t gut_launch_render_kbuffer_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
+                                               GutParticleSource src, const float* ray_ori, const float* ray_dir, const float* rgba,
+                                               const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
+                                               cudaStream_t stream);
+
 cudaError_t gut_launch_fill_outputs(uint32_t num_pixels, float* rgba, float* dist, float* hits, cudaStream_t stream);
 cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream);

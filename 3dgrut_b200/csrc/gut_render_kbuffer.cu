@@ -1,0 +1,348 @@
+// gut_render_kbuffer.cu -- K4 / K5 of the 3DGUT rasteriser for k_buffer_size > 0 (the "sorted" configurations,
+// configs/paper/3dgut/base_sorted.yaml: k_buffer_size = 16).
+//
+// reference: HitParticleKBuffer<K> (include/3dgut/kernels/cuda/renderers/gutKBufferRenderer.cuh:28-85),
+//   GUTKBufferRenderer::evalKBuffer (:217-292) and processHitParticle (:108-171), forward and backward branch;
+//   per-hit backward: particleFeaturesIntegrateBwd (kernels/slang/models/shRadiativeParticles.slang:179-207) and
+//   particleDensityProcessHitBwdToBuffer (kernels/slang/models/gaussianParticles.slang:394-451), i.e. Slang autodiff of
+//   hit (:188-222) + integrateHit<true> (:224-252): true derivatives, alpha clamp masked, tMinMax test also in backward.
+//
+// Design.  A ray keeps its K closest pending hits (distance, alpha, particle) in REGISTERS, sorted by distance; the
+// insertion is a fully unrolled compare-exchange chain over static indices, the drain walks the static indices too, so
+// nothing spills to local memory.  One warp per CTA owns an 8x4 pixel block (eight blocks per 16x16 tile, one ray per
+// lane -- the k-buffer leaves no registers for a second ray) and stages the tile's sorted list through the same
+// warp-private pipeline as the K = 0 kernels (gut_render_common.cuh).  A hit leaves the buffer long after its batch
+// left shared memory, so processing gathers the particle by index: its K1 colour in the forward, its 48-byte
+// parameters too in the backward.
+// Backward: the reference adds 11 + 3 atomics per hit and thread into [N,12] / [N,3].  Here a hit produces the same 15
+// ray-linear canonical-frame values as the K = 0 kernel (gut_render.cu), with the true hit-distance Jacobians and the
+// masked clamp, and adds them to the [N,16] accumulators that K6 turns into parameter gradients -- K6 is shared.
+#include "gut_render_common.cuh"
+
+namespace {
+
+constexpr int KB_BLOCKS_PER_TILE = 8;   // 8x4 pixel blocks (one warp, one ray per lane) of a 16x16 tile
+
+template <int K>
+struct KBuffer {
+    float t[K], a[K];
+    uint32_t p[K];
+    uint32_t n;
+    GUT_D void clear() {
+        n = 0;
+#pragma unroll
+        for (int i = 0; i < K; ++i) { t[i] = -1.0f; a[i] = 0.0f; p[i] = 0xffffffffu; }
+    }
+    GUT_D bool full() const { return n == (uint32_t)K; }
+    // insert (the caller has processed entry 0 if the buffer was full): HitParticleKBuffer::insert, :45-62
+    GUT_D void insert(float ht, float ha, uint32_t hp) {
+        if (full()) t[0] = -1.0f; else n++;
+#pragma unroll
+        for (int i = K - 1; i >= 0; --i) {
+            if (ht > t[i]) {
+                const float tt = t[i], ta = a[i]; const uint32_t tp = p[i];
+                t[i] = ht; a[i] = ha; p[i] = hp;
+                ht = tt; ha = ta; hp = tp;
+            }
+        }
+    }
+};
+
+struct RayK {
+    float3 o, d;
+    float tmin, tmax;
+    bool inside, valid;
+    uint32_t pix;
+};
+GUT_D RayK make_ray_k(const GutFrame& fr, const float* __restrict__ ray_ori, const float* __restrict__ ray_dir, uint32_t tile, uint32_t block) {
+    const uint32_t tx = tile % fr.grid_x, ty = tile / fr.grid_x, l = threadIdx.x & 31;
+    const uint32_t px = tx * GUT_TILE + (block & 1) * 8 + (l & 7), py = ty * GUT_TILE + (block >> 1) * 4 + (l >> 3);
+    RayK r;
+    r.inside = px < fr.width && py < fr.height;
+    r.pix = r.inside ? px + fr.width * py : 0u;
+    r.o = fr.cam_centre; r.d = f3(0.f, 0.f, 1.f); r.tmin = 0.f; r.tmax = 0.f; r.valid = false;
+    if (r.inside) {
+        const Ray q = make_ray(fr, ray_ori, ray_dir, r.pix);
+        r.o = q.o; r.d = q.d; r.tmin = q.tmin; r.tmax = q.tmax; r.valid = q.valid;
+    }
+    return r;
+}
+
+// test of one staged record against one ray; on acceptance also the hit distance (canonicalRayDistance,
+// gaussianParticles.slang:165-171).  dlt = ray origin - frame origin.
+template <int DEG>
+GUT_D bool record_hit(const GutConfig& cfg, const float4* __restrict__ r, const float3 d, const float3 dlt, float tmin, float tmax,
+                      float& alpha, float& t) {
+    const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
+    const float3 go = f3(A.w + A.x * dlt.x + A.y * dlt.y + A.z * dlt.z, B.w + B.x * dlt.x + B.y * dlt.y + B.z * dlt.z,
+                         Cm.w + Cm.x * dlt.x + Cm.y * dlt.y + Cm.z * dlt.z);
+    const float3 u = f3(A.x * d.x + A.y * d.y + A.z * d.z, B.x * d.x + B.y * d.y + B.z * d.z, Cm.x * d.x + Cm.y * d.y + Cm.z * d.z);
+    const float l2 = dot(u, u);
+    const float3 c = cross(u, go);
+    const float il2 = mufu_rcp(l2);
+    const float g2 = dot(c, c) * il2;
+    const float resp = (DEG == 2) ? mufu_ex2(g2 * -0.72134752044448170368f) : kernel_response<DEG>(g2);
+    const float araw = resp * S.w;
+    if (!((resp > cfg.min_kernel_response) && (araw > cfg.min_alpha))) return false;
+    const float3 su = f3(S.x * u.x, S.y * u.y, S.z * u.z);
+    t = fabsf(dot(u, go)) * il2 * mufu_sqrt(dot(su, su));
+    alpha = fminf(cfg.max_alpha, araw);
+    return t > tmin && t < tmax;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K4 forward, K > 0
+// ---------------------------------------------------------------------------------------------------
+struct FwdStateK {
+    float T, D, cr, cg, cb;
+    uint32_t nhits;
+    bool alive;
+};
+// processHitParticle, forward branch (:153-170): integrateHit<false> + integrateRadiance<false>
+GUT_D void process_hit_fwd(const GutConfig& cfg, const float4* __restrict__ features, float t, float alpha, uint32_t p, FwdStateK& st) {
+    const float w = alpha * st.T;
+    st.D = fmaf(t, w, st.D);
+    st.T *= (1.0f - alpha);
+    if (w > 0.0f) {
+        const float4 F = __ldg(features + p);
+        st.cr = fmaf(fmaxf(F.x, 0.0f), w, st.cr); st.cg = fmaf(fmaxf(F.y, 0.0f), w, st.cg); st.cb = fmaf(fmaxf(F.z, 0.0f), w, st.cb);
+        st.nhits++;
+    }
+    if (st.T < cfg.min_transmittance) st.alive = false;
+}
+
+template <int DEG, int K>
+__global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+                                                                            GutParticleSource src, const float* __restrict__ ray_ori,
+                                                                            const float* __restrict__ ray_dir, float4* __restrict__ rgba,
+                                                                            float* __restrict__ dist, float* __restrict__ hits) {
+    __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
+    const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
+    const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
+    const float3 dlt = ray.o - fr.cam_centre;
+
+    const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
+    WarpStager<false> stg;
+    stg.init(smem_raw, src, b0, b1 - b0, fr.cam_centre);
+
+    FwdStateK st;
+    st.T = 1.0f; st.D = 0.0f; st.cr = st.cg = st.cb = 0.0f; st.nhits = 0;
+    st.alive = ray.inside && ray.valid;
+    KBuffer<K> kb;
+    kb.clear();
+    for (uint32_t b = 0; b < stg.nb; ++b) {
+        stg.stage(b);
+        const uint32_t cnt = stg.count(b);
+        for (uint32_t j = 0; j < cnt; ++j) {
+            float alpha, t;
+            if (st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t)) {
+                if (kb.full()) process_hit_fwd(cfg, src.features, kb.t[0], kb.a[0], kb.p[0], st);
+                kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
+            }
+        }
+        if (!__any_sync(0xffffffffu, st.alive)) break;
+        stg.rotate();
+    }
+    stg.drain();
+    // drain the buffer closest first (:282-290): valid entries sit at the top, invalid ones have t = -1
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+        if (st.alive && kb.t[i] >= 0.0f) process_hit_fwd(cfg, src.features, kb.t[i], kb.a[i], kb.p[i], st);
+
+    if (ray.inside && ray.valid) {
+        rgba[ray.pix] = make_float4(st.cr, st.cg, st.cb, 1.0f - st.T);
+        dist[ray.pix] = st.D;
+        if (cfg.enable_hitcounts) hits[ray.pix] = (float)st.nhits;
+    } else if (ray.inside) {
+        rgba[ray.pix] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        dist[ray.pix] = 1e06f;
+        hits[ray.pix] = 0.0f;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K5 backward, K > 0
+// ---------------------------------------------------------------------------------------------------
+struct BwdStateK {
+    float Tb, Tg, Db, Dg;    // transmittance / distance still behind the current hit, and their gradients
+    float3 Fb, Fg;           // colour still behind the current hit, and its gradient
+    float T;
+    bool alive;
+};
+
+// processHitParticle, backward branch (:116-152).  Adds the hit's 15 canonical-frame values (see gut_render.cu,
+// backward_walk) to raw_grad[16 p + .]; K6 turns them into parameter gradients.
+template <int DEG>
+GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 origin, const float3 o, const float3 d,
+                           float t, float alpha, uint32_t p, BwdStateK& st, float* __restrict__ raw_grad) {
+    if (alpha > 0.0f) {
+        const float4 r0 = __ldg(src.density12 + 3 * (size_t)p), q = __ldg(src.density12 + 3 * (size_t)p + 1),
+                     r2 = __ldg(src.density12 + 3 * (size_t)p + 2), F = __ldg(src.features + p);
+        // particleFeaturesIntegrateBwd: un-blend the UNclamped feature, adjoint of lerp(I, f, alpha)
+        const float wgt = mufu_rcp(1.0f - alpha);
+        st.Fb = f3((st.Fb.x - F.x * alpha) * wgt, (st.Fb.y - F.y * alpha) * wgt, (st.Fb.z - F.z * alpha) * wgt);
+        const float alpha_grad = st.Fg.x * (F.x - st.Fb.x) + st.Fg.y * (F.y - st.Fb.y) + st.Fg.z * (F.z - st.Fb.z);
+        const float3 fgrad = st.Fg * alpha;
+        st.Fg = st.Fg * (1.0f - alpha);
+        // particleDensityProcessHitBwdToBuffer: un-blend transmittance and distance, adjoint of integrateHit<true>
+        st.Tb *= wgt;
+        st.Db = (st.Db - t * alpha) * wgt;
+        const float d_alpha = alpha_grad + st.Dg * (t - st.Db) - st.Tg * st.Tb;
+        const float d_depth = st.Dg * alpha;
+        st.Dg *= (1.0f - alpha);
+        st.Tg *= (1.0f - alpha);
+
+        // the particle in its canonical frame (same quantities as the staged record, gut_render_common.cuh)
+        float3 c0, c1, c2;
+        quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);
+        const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
+        const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;
+        const float3 v = o - f3(r0.x, r0.y, r0.z);
+        const float3 go = f3(dot(m0, v), dot(m1, v), dot(m2, v));
+        const float3 u = f3(dot(m0, d), dot(m1, d), dot(m2, d));
+        const float il = mufu_rsq(dot(u, u));
+        const float3 grd = u * il;
+        const float dgo = dot(grd, go);
+        const float3 cr = cross(grd, go);
+        const float g2 = dot(cr, cr);
+        const float resp = (DEG == 2) ? mufu_ex2(g2 * -0.72134752044448170368f) : kernel_response<DEG>(g2);
+        // alpha = min(max_alpha, resp * density): no gradient when clamped
+        const bool unclamped = !(cfg.max_alpha < resp * r0.w);
+        const float dDens = unclamped ? d_alpha * resp : 0.0f;
+        const float g2G = kernel_response_grad<DEG>(g2, resp, unclamped ? d_alpha * r0.w : 0.0f);
+        // depth = |dgo| |sg|, sg = s * grd: true Jacobians wrt go, grd and the explicit scale
+        const float3 sg = f3(r2.x * grd.x, r2.y * grd.y, r2.z * grd.z);
+        const float3 sg2 = sg * sg;
+        const float ssum = sg2.x + sg2.y + sg2.z;
+        const float depth = fabsf(dgo) * mufu_sqrt(ssum);
+        const float kap = depth > 0.0f ? -dgo * d_depth * mufu_rcp(depth) : 0.0f;   // dL/dgrds = kap sg
+        const float kd = kap * dgo;
+        const float3 gcG = cr * (2.0f * g2G);
+        const float3 grdG = cross(go, gcG);
+        const float3 groG = cross(gcG, grd);
+        const float3 Ag = f3(fmaf(-kap * ssum, grd.x, groG.x), fmaf(-kap * ssum, grd.y, groG.y), fmaf(-kap * ssum, grd.z, groG.z));
+        const float3 X = f3(grdG.x - kap * fmaf(dgo * r2.x, sg.x, ssum * go.x), grdG.y - kap * fmaf(dgo * r2.y, sg.y, ssum * go.y),
+                            grdG.z - kap * fmaf(dgo * r2.z, sg.z, ssum * go.z));
+        const float gx = dot(grd, X);
+        const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
+        const float3 dlt = o - origin;
+        float* acc = raw_grad + 16 * (size_t)p;
+        atomicAdd(acc + 0, Ag.x); atomicAdd(acc + 1, Ag.y); atomicAdd(acc + 2, Ag.z);
+        atomicAdd(acc + 3, dDens);
+        atomicAdd(acc + 4, (r2.z * iy) * fmaf(go.z, Ag.y, u.z * Bg.y) - (r2.y * iz) * fmaf(go.y, Ag.z, u.y * Bg.z));
+        atomicAdd(acc + 5, (r2.x * iz) * fmaf(go.x, Ag.z, u.x * Bg.z) - (r2.z * ix) * fmaf(go.z, Ag.x, u.z * Bg.x));
+        atomicAdd(acc + 6, (r2.y * ix) * fmaf(go.y, Ag.x, u.y * Bg.x) - (r2.x * iy) * fmaf(go.x, Ag.y, u.x * Bg.y));
+        atomicAdd(acc + 7, ix * (Bg.x * d.x + Ag.x * dlt.x) + iy * (Bg.y * d.y + Ag.y * dlt.y) + iz * (Bg.z * d.z + Ag.z * dlt.z));
+        atomicAdd(acc + 8, fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x)));
+        atomicAdd(acc + 9, fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y)));
+        atomicAdd(acc + 10, fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z)));
+        atomicAdd(acc + 11, fgrad.x); atomicAdd(acc + 12, fgrad.y); atomicAdd(acc + 13, fgrad.z);
+        atomicAdd(acc + 14, -kd * ssum);
+    }
+    st.T *= (1.0f - alpha);
+    if (st.T < cfg.min_transmittance) st.alive = false;
+}
+
+template <int DEG, int K>
+__global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_kernel(
+    GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
+    const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
+    const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
+    const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
+    __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
+    const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
+    const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
+    const float3 dlt = ray.o - fr.cam_centre;
+
+    BwdStateK st;   // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
+    st.alive = ray.inside && ray.valid;
+    st.T = 1.0f; st.Tb = 1.0f; st.Tg = 0.0f; st.Db = 0.0f; st.Dg = 0.0f;
+    st.Fb = f3(0.f, 0.f, 0.f); st.Fg = f3(0.f, 0.f, 0.f);
+    if (st.alive) {
+        const float4 fd = __ldg(rgba + ray.pix), gd = __ldg(rgba_grad + ray.pix);
+        st.Tb = 1.0f - fd.w; st.Tg = -gd.w;
+        st.Db = __ldg(dist + ray.pix); st.Dg = __ldg(dist_grad + ray.pix);
+        st.Fb = f3(fd.x, fd.y, fd.z); st.Fg = f3(gd.x, gd.y, gd.z);
+    }
+
+    const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
+    WarpStager<false> stg;
+    stg.init(smem_raw, src, b0, b1 - b0, fr.cam_centre);
+    KBuffer<K> kb;
+    kb.clear();
+    for (uint32_t b = 0; b < stg.nb; ++b) {
+        stg.stage(b);
+        const uint32_t cnt = stg.count(b);
+        for (uint32_t j = 0; j < cnt; ++j) {
+            float alpha, t;
+            if (st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t)) {
+                if (kb.full()) process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, kb.t[0], kb.a[0], kb.p[0], st, raw_grad);
+                kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
+            }
+        }
+        if (!__any_sync(0xffffffffu, st.alive)) break;
+        stg.rotate();
+    }
+    stg.drain();
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+        if (st.alive && kb.t[i] >= 0.0f) process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, kb.t[i], kb.a[i], kb.p[i], st, raw_grad);
+}
+
+template <int DEG, int K>
+cudaError_t launch_fwd(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src, const float* ray_ori,
+                       const float* ray_dir, float* rgba, float* dist, float* hits, cudaStream_t stream) {
+    gut_render_kbuffer_kernel<DEG, K><<<frame.num_tiles * KB_BLOCKS_PER_TILE, RENDER_THREADS, 0, stream>>>(
+        cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<float4*>(rgba), dist, hits);
+    return cudaGetLastError();
+}
+template <int DEG, int K>
+cudaError_t launch_bwd(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src, const float* ray_ori,
+                       const float* ray_dir, const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
+                       float* raw_grad, cudaStream_t stream) {
+    gut_render_kbuffer_backward_kernel<DEG, K><<<frame.num_tiles * KB_BLOCKS_PER_TILE, RENDER_THREADS, 0, stream>>>(
+        cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba), reinterpret_cast<const float4*>(rgba_grad),
+        dist, dist_grad, raw_grad);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+bool gut_kbuffer_size_supported(int k) { return k == 4 || k == 8 || k == 16; }
+
+#define GUT_DISPATCH_DEG_K(deg, k, CALL)                                  \
+    switch (deg) {                                                        \
+    case 0: GUT_DISPATCH_K(0, k, CALL)                                    \
+    case 1: GUT_DISPATCH_K(1, k, CALL)                                    \
+    case 2: GUT_DISPATCH_K(2, k, CALL)                                    \
+    case 3: GUT_DISPATCH_K(3, k, CALL)                                    \
+    case 4: GUT_DISPATCH_K(4, k, CALL)                                    \
+    case 5: GUT_DISPATCH_K(5, k, CALL)                                    \
+    case 8: GUT_DISPATCH_K(8, k, CALL)                                    \
+    default: return cudaErrorInvalidValue;                                \
+    }
+#define GUT_DISPATCH_K(D, k, CALL)                                        \
+    switch (k) {                                                          \
+    case 4: return CALL(D, 4);                                            \
+    case 8: return CALL(D, 8);                                            \
+    case 16: return CALL(D, 16);                                          \
+    default: return cudaErrorInvalidValue;                                \
+    }
+
+cudaError_t gut_launch_render_kbuffer(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
+                                      const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
+                                      cudaStream_t stream) {
+#define CALL_FWD(D, KK) launch_fwd<D, KK>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, stream)
+    GUT_DISPATCH_DEG_K(cfg.kernel_degree, cfg.k_buffer_size, CALL_FWD)
+#undef CALL_FWD
+}
+
+cudaError_t gut_launch_render_kbuffer_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
+                                               GutParticleSource src, const float* ray_ori, const float* ray_dir, const float* rgba,
+                                               const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
+                                               cudaStream_t stream) {
+#define CALL_BWD(D, KK) \
+    launch_bwd<D, KK>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, raw_grad, stream)
+    GUT_DISPATCH_DEG_K(cfg.kernel_degree, cfg.k_buffer_size, CALL_BWD)
+#undef CALL_BWD
+}

@@ -106,6 +106,56 @@ def test_backward_gradients(pkg, name, n, w, h, deg, kind, seed):
     assert e <= TOL_GRAD, (name, "sph", e)
 
 
+KB_CASES = [
+    # name, N, W, H, sph_degree, kind, seed, K
+    ("sorted_k16_init", 6000, 150, 70, 3, "init", 5, 16),
+    ("sorted_k4_dense", 3000, 96, 96, 2, "dense", 9, 4),
+    ("sorted_k8_init", 4000, 64, 80, 1, "init", 21, 8),
+]
+
+
+@pytest.mark.parametrize("name,n,w,h,deg,kind,seed,K", KB_CASES)
+def test_kbuffer_forward_and_backward(pkg, name, n, w, h, deg, kind, seed, K):
+    """k_buffer_size > 0 (sorted compositing, gutKBufferRenderer.cuh:28-292): image and gradients against the oracle."""
+    scene = syn.make_scene(n, 3, seed=seed, kind=kind)
+    if kind == "dense":   # negative colours exercise the unclamped un-blend of the K>0 backward
+        scene["features"][::7, 0:3] -= 2.5
+    view = syn.make_view(w, h)
+    cfg = abi.default_config(); cfg.k_buffer_size = K
+    rng = np.random.default_rng(seed)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    ref0 = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg)
+    border = ref0["borderline"]
+    rgba_grad[border] = 0; dist_grad[border] = 0      # a ray that may take another branch is kept out of the gradient comparison
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg, rgba_grad=rgba_grad, dist_grad=dist_grad)
+    raster = _raster(pkg, k_buffer_size=K)
+    (rgba, dist, hits, vis), (d12, sph, cam) = _run_forward(raster, scene, view, deg, stage=False)
+    stats = compare_images(rgba.cpu().numpy(), ref["rgba"], border)
+    assert stats["max_abs_clean"] <= TOL_IMG, (name, stats)
+    assert stats["borderline_fraction"] < 0.08, (name, stats)   # includes rays with two hit distances within 2e-6 (order may flip)
+    assert stats["max_abs_borderline"] < 2e-2, (name, stats)
+    clean = ~border
+    d_err = np.abs(dist.cpu().numpy().reshape(h, w) - ref["dist"])[clean]
+    assert d_err.max() <= TOL_IMG * max(1.0, float(np.abs(ref["dist"]).max())), (name, d_err.max())
+    assert np.array_equal(hits.cpu().numpy().reshape(h, w)[clean], ref["hits"][clean])
+    # the sorted composite differs from the unsorted one (otherwise this test would not exercise the buffer)
+    ref_unsorted = oracle_reference(scene, view, w, h, sph_degree=deg)
+    assert np.abs(ref_unsorted["rgba"] - ref["rgba"]).max() > 1e-4
+    # gradients: feed the ORACLE's forward outputs so that both backward passes un-blend the same image
+    rgba_o = torch.from_numpy(ref["rgba"]).cuda(); dist_o = torch.from_numpy(ref["dist"]).cuda().reshape(h, w, 1)
+    g12, gsph = raster.trace_bwd(0, deg, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba_o, torch.from_numpy(rgba_grad).cuda(), dist_o, torch.from_numpy(dist_grad).cuda().reshape(h, w, 1))
+    torch.cuda.synchronize()
+    g12 = g12.cpu().numpy(); gsph = gsph.cpu().numpy()
+    assert np.all(g12[:, 11] == 0)
+    for lo, hi, what in ((0, 3, "position"), (3, 4, "density"), (4, 8, "rotation"), (8, 11, "scale")):
+        e = rel_l2(g12[:, lo:hi], ref["density_grad"][:, lo:hi])
+        assert e <= TOL_GRAD, (name, what, e)
+    e = rel_l2(gsph, ref["radiance_grad"])
+    assert e <= TOL_GRAD, (name, "sph", e)
+
+
 def test_tracer_autograd_matches_native(pkg):
     """The Tracer.render autograd path returns the same gradients as the raw trace/trace_bwd calls."""
     n, w, h, deg = 3000, 64, 48, 3
