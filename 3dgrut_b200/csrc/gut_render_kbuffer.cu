@@ -170,12 +170,35 @@ struct BwdStateK {
     bool alive;
 };
 
-// processHitParticle, backward branch (:116-152).  Adds the hit's 15 canonical-frame values (see gut_render.cu,
-// backward_walk) to raw_grad[16 p + .]; K6 turns them into parameter gradients.
+// Sum 16 per-lane values over the warp with 16 shuffles (each stage exchanges the half of the values the partner lane
+// will own).  On return lane l holds the warp total of value ((l>>4)&1)*8 + ((l>>3)&1)*4 + ((l>>2)&1)*2 + ((l>>1)&1).
+GUT_D float warp_transpose_reduce16(float (&v)[16], uint32_t lane) {
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 8 >> s;
+        const bool up = lane & (16u >> s);
+#pragma unroll
+        for (int k = 0; k < h; ++k) {
+            const float send = up ? v[k] : v[k + h];
+            const float keep = up ? v[k + h] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16 >> s);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+// processHitParticle, backward branch (:116-152), for the lanes with `need` set (all 32 lanes call).  A hit yields the
+// 15 canonical-frame values of gut_render.cu's backward_walk (true hit-distance Jacobians, masked clamp).  Rays of an
+// 8x4 block mostly leave their buffers with the same particle at the same time, so the values are summed per distinct
+// particle across the warp (leader loop + transpose-reduce) and added to raw_grad[16 p + .] with one RED per value and
+// group instead of one per value and ray (the reference: 14 atomics per hit and thread).
 template <int DEG>
 GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 origin, const float3 o, const float3 d,
-                           float t, float alpha, uint32_t p, BwdStateK& st, float* __restrict__ raw_grad) {
-    if (alpha > 0.0f) {
+                           bool need, float t, float alpha, uint32_t p, BwdStateK& st, uint32_t lane, float* __restrict__ raw_grad) {
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.0f;
+    if (need && alpha > 0.0f) {
         const float4 r0 = __ldg(src.density12 + 3 * (size_t)p), q = __ldg(src.density12 + 3 * (size_t)p + 1),
                      r2 = __ldg(src.density12 + 3 * (size_t)p + 2), F = __ldg(src.features + p);
         // particleFeaturesIntegrateBwd: un-blend the UNclamped feature, adjoint of lerp(I, f, alpha)
@@ -197,8 +220,8 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
         quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);
         const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
         const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;
-        const float3 v = o - f3(r0.x, r0.y, r0.z);
-        const float3 go = f3(dot(m0, v), dot(m1, v), dot(m2, v));
+        const float3 rel = o - f3(r0.x, r0.y, r0.z);
+        const float3 go = f3(dot(m0, rel), dot(m1, rel), dot(m2, rel));
         const float3 u = f3(dot(m0, d), dot(m1, d), dot(m2, d));
         const float il = mufu_rsq(dot(u, u));
         const float3 grd = u * il;
@@ -226,21 +249,35 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
         const float gx = dot(grd, X);
         const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
         const float3 dlt = o - origin;
-        float* acc = raw_grad + 16 * (size_t)p;
-        atomicAdd(acc + 0, Ag.x); atomicAdd(acc + 1, Ag.y); atomicAdd(acc + 2, Ag.z);
-        atomicAdd(acc + 3, dDens);
-        atomicAdd(acc + 4, (r2.z * iy) * fmaf(go.z, Ag.y, u.z * Bg.y) - (r2.y * iz) * fmaf(go.y, Ag.z, u.y * Bg.z));
-        atomicAdd(acc + 5, (r2.x * iz) * fmaf(go.x, Ag.z, u.x * Bg.z) - (r2.z * ix) * fmaf(go.z, Ag.x, u.z * Bg.x));
-        atomicAdd(acc + 6, (r2.y * ix) * fmaf(go.y, Ag.x, u.y * Bg.x) - (r2.x * iy) * fmaf(go.x, Ag.y, u.x * Bg.y));
-        atomicAdd(acc + 7, ix * (Bg.x * d.x + Ag.x * dlt.x) + iy * (Bg.y * d.y + Ag.y * dlt.y) + iz * (Bg.z * d.z + Ag.z * dlt.z));
-        atomicAdd(acc + 8, fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x)));
-        atomicAdd(acc + 9, fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y)));
-        atomicAdd(acc + 10, fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z)));
-        atomicAdd(acc + 11, fgrad.x); atomicAdd(acc + 12, fgrad.y); atomicAdd(acc + 13, fgrad.z);
-        atomicAdd(acc + 14, -kd * ssum);
+        v[0] = Ag.x; v[1] = Ag.y; v[2] = Ag.z;
+        v[3] = dDens;
+        v[4] = (r2.z * iy) * fmaf(go.z, Ag.y, u.z * Bg.y) - (r2.y * iz) * fmaf(go.y, Ag.z, u.y * Bg.z);
+        v[5] = (r2.x * iz) * fmaf(go.x, Ag.z, u.x * Bg.z) - (r2.z * ix) * fmaf(go.z, Ag.x, u.z * Bg.x);
+        v[6] = (r2.y * ix) * fmaf(go.y, Ag.x, u.y * Bg.x) - (r2.x * iy) * fmaf(go.x, Ag.y, u.x * Bg.y);
+        v[7] = ix * (Bg.x * d.x + Ag.x * dlt.x) + iy * (Bg.y * d.y + Ag.y * dlt.y) + iz * (Bg.z * d.z + Ag.z * dlt.z);
+        v[8] = fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x));
+        v[9] = fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y));
+        v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));
+        v[11] = fgrad.x; v[12] = fgrad.y; v[13] = fgrad.z;
+        v[14] = -kd * ssum;
     }
-    st.T *= (1.0f - alpha);
-    if (st.T < cfg.min_transmittance) st.alive = false;
+    if (need) {
+        st.T *= (1.0f - alpha);
+        if (st.T < cfg.min_transmittance) st.alive = false;
+    }
+    // one reduction per distinct particle among the lanes that processed a hit
+    uint32_t remaining = __ballot_sync(0xffffffffu, need);
+    const uint32_t slot = ((lane >> 4) & 1u) * 8u + ((lane >> 3) & 1u) * 4u + ((lane >> 2) & 1u) * 2u + ((lane >> 1) & 1u);
+    while (remaining) {
+        const uint32_t pl = __shfl_sync(0xffffffffu, p, __ffs(remaining) - 1);
+        const bool mine = need && p == pl;
+        float g[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) g[k] = mine ? v[k] : 0.0f;
+        const float total = warp_transpose_reduce16(g, lane);
+        if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)pl + slot, total);
+        remaining &= ~__ballot_sync(0xffffffffu, mine);
+    }
 }
 
 template <int DEG, int K>
@@ -253,6 +290,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
     const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
     const float3 dlt = ray.o - fr.cam_centre;
+    const uint32_t lane = threadIdx.x & 31;
 
     BwdStateK st;   // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
     st.alive = ray.inside && ray.valid;
@@ -275,18 +313,22 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
         const uint32_t cnt = stg.count(b);
         for (uint32_t j = 0; j < cnt; ++j) {
             float alpha, t;
-            if (st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t)) {
-                if (kb.full()) process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, kb.t[0], kb.a[0], kb.p[0], st, raw_grad);
-                kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
-            }
+            const bool hit = st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t);
+            const bool need = hit && kb.full();
+            if (__any_sync(0xffffffffu, need))
+                process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, need, kb.t[0], kb.a[0], kb.p[0], st, lane, raw_grad);
+            if (hit) kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
         }
         if (!__any_sync(0xffffffffu, st.alive)) break;
         stg.rotate();
     }
     stg.drain();
 #pragma unroll
-    for (int i = 0; i < K; ++i)
-        if (st.alive && kb.t[i] >= 0.0f) process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, kb.t[i], kb.a[i], kb.p[i], st, raw_grad);
+    for (int i = 0; i < K; ++i) {
+        const bool need = st.alive && kb.t[i] >= 0.0f;
+        if (__any_sync(0xffffffffu, need))
+            process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, need, kb.t[i], kb.a[i], kb.p[i], st, lane, raw_grad);
+    }
 }
 
 template <int DEG, int K>

@@ -442,6 +442,31 @@ def run_ours(args):
         ms = a0.elapsed_time(a1) / reps
         fwd_1080p = {"fps": 1e3 / ms, "ms_per_frame": ms, "particles": n, "intersections_M": raster.frame_stats()["num_intersections"]}
 
+    # ---- auxiliary: the "sorted" configuration (k_buffer_size = 16, configs/paper/3dgut/base_sorted.yaml; SURVEY 8d's second
+    # config): forward + backward of ONE view of the same workload, device resident ---------------------------------------
+    sorted_k16 = None
+    if rank == 0 and not args.no_aux and views:
+        rk = native.SplatRaster(abi.default_config(enable_kernel_timings=1, k_buffer_size=16), device=dev)
+        v0 = views[0]
+        g_rgba = torch.rand((h, w, 4), device=dev) * 2 - 1
+        g_dist = (torch.rand((h, w, 1), device=dev) * 2 - 1) * 0.01
+
+        def step_k():
+            o = rk.trace(0, SPH_DEGREE, d12, sph, v0["rays_ori"], v0["rays_dir"], None, v0["camera"])
+            rk.trace_bwd(0, SPH_DEGREE, d12, sph, v0["rays_ori"], v0["rays_dir"], None, v0["camera"], 0, 1, None, None,
+                         o[0], g_rgba, o[1], g_dist)
+        step_k()
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 3
+        a0.record()
+        for _ in range(reps):
+            step_k()
+        a1.record()
+        torch.cuda.synchronize()
+        ms = a0.elapsed_time(a1) / reps
+        sorted_k16 = {"mpix_per_s": P / (ms * 1e-3) / 1e6, "ms_per_view": ms, "stage_ms": rk.stage_times()}
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -458,7 +483,7 @@ def run_ours(args):
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P},
-            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p,
+            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
