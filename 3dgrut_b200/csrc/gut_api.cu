@@ -391,10 +391,10 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     return GUT_OK;
 }
 
-int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
-                 const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
-                 const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad, float* d_radiance_grad,
-                 int32_t accumulate) {
+static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                         const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
+                         const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad, float* d_radiance_grad,
+                         float* d_colour_grad, int32_t accumulate) {
     int rc = check_common(h, camera, N, sph_degree, W, H);
     if (rc != GUT_OK) return rc;
     (void)d_radiance;
@@ -403,7 +403,7 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
         return fail(h, GUT_ERR_NO_FORWARD, "cannot render backward: no forward context on this stream (reference: gutRenderer.cu:413-417)");
     if (h->fwd_N != N || h->fwd_W != W || h->fwd_H != H) return fail(h, GUT_ERR_NO_FORWARD, "backward shapes differ from the preceding forward");
     if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_rgba_grad || !d_dist || !d_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null ray/gradient pointer");
-    if (N > 0 && (!d_density || !d_density_grad || !d_radiance_grad)) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    if (N > 0 && (!d_density || !d_density_grad || (!d_radiance_grad && !d_colour_grad))) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
     if (N == 0) return GUT_OK;
     DeviceGuard guard(h->device);
     if (h->cfg.enable_kernel_timings) start_timer(h->timers, 1, s);
@@ -428,10 +428,47 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
     {
         StageTimer t(h, ST_BWD_PROJECT, s);
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
-                                                (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad, accumulate, s));
+                                                (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad,
+                                                d_colour_grad, accumulate, s));
         h->launches += 1;
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
+    return GUT_OK;
+}
+
+int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                 const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
+                 const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad, float* d_radiance_grad,
+                 int32_t accumulate) {
+    if (h && N > 0 && !d_radiance_grad) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    return backward_impl(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist,
+                         d_dist_grad, d_density_grad, d_radiance_grad, nullptr, accumulate);
+}
+
+int gut_backward_colour(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                        const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
+                        const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad,
+                        int32_t accumulate_density, float* d_colour_grad, float* view_centre_out) {
+    if (h && N > 0 && !d_colour_grad) return fail(h, GUT_ERR_BAD_INPUT, "null colour gradient pointer");
+    int rc = backward_impl(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist,
+                           d_dist_grad, d_density_grad, nullptr, d_colour_grad, accumulate_density);
+    if (rc == GUT_OK && view_centre_out) {
+        view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
+    }
+    return rc;
+}
+
+int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degree, const float* d_density, uint32_t n_views,
+                           const float* d_view_centres, const float* d_colour_grads, float* d_radiance_grad, int32_t accumulate) {
+    const float* view_centres = d_view_centres;
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
+    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_gradient_expand is built for 16 SH coefficients");
+    if (N == 0) return GUT_OK;
+    if (!d_density || !d_radiance_grad || (n_views > 0 && (!view_centres || !d_colour_grads))) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_sh_expand(N, sph_degree, d_density, n_views, view_centres, d_colour_grads, d_radiance_grad, accumulate, (cudaStream_t)stream_));
+    h->launches += 1;
     return GUT_OK;
 }
 

@@ -66,7 +66,13 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream);
+                                        float* raw_grad, float* density_grad, float* sph_grad,
+                                        float* colour_out /* non-null: write the view's masked colour gradient [N,4] instead of sph_grad */,
+                                        int accumulate, cudaStream_t stream);
+
+// deferred SH backward of a multi-view step (gut_project.cu, gut_sh_expand_kernel)
+cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
+                                 const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream);
 
 // exclusive scan of tile_hist[T*SUB] -> tile_start[T+1] and absolute sub-bucket cursors tile_cursor[T*SUB]; stats[0]=M, stats[1]=max list
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,

@@ -291,7 +291,8 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
                                                                           const uint32_t* __restrict__ tiles_count,
                                                                           const float4* __restrict__ features,
                                                                           float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
-                                                                          float* __restrict__ sph_grad, int accumulate) {
+                                                                          float* __restrict__ sph_grad, float4* __restrict__ colour_out,
+                                                                          int accumulate) {
     __shared__ float4 s_dg[K6_WARPS][32 * 3];      // parameter-gradient rows of the warp
     __shared__ float s_basis[K6_WARPS][32][17];    // SH basis per row (+1 pad: conflict-free column reads)
     __shared__ float4 s_g[K6_WARPS][32];           // masked colour gradient per row, w = 1 if the row was touched
@@ -373,6 +374,11 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
             }
         }
     }
+    // deferred SH gradient: hand out the masked colour gradient of this view, gut_sh_expand_kernel sums the views later
+    if (colour_out) {
+        if (i < N) colour_out[i] = make_float4(g.x, g.y, g.z, 0.0f);
+        return;
+    }
     // [N,48]
     if (ncoef_all == 16) {
         float4* dst = reinterpret_cast<float4*>(sph_grad) + 12 * (size_t)warp_base;
@@ -435,12 +441,77 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        float* raw_grad, float* density_grad, float* sph_grad, int accumulate, cudaStream_t stream) {
+                                        float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, int accumulate,
+                                        cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     gut_project_backward_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree,
                                                                       reinterpret_cast<const float4*>(density12), tiles_count,
                                                                       features, reinterpret_cast<float4*>(raw_grad),
-                                                                      reinterpret_cast<float4*>(density_grad), sph_grad, accumulate);
+                                                                      reinterpret_cast<float4*>(density_grad), sph_grad,
+                                                                      reinterpret_cast<float4*>(colour_out), accumulate);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Deferred SH backward of a multi-view step: dL/dSH[i] (+)= sum_v basis(normalize(pos_i - centre_v)) (x) colour_grad_v[i].
+// K6 hands out 16 bytes per particle and view instead of read-modify-writing the 192-byte SH gradient row once per
+// view; this kernel expands all views at once (and, across GPUs, the views of all ranks after an all-gather of the
+// colour gradients -- 12 bytes per particle and view on the wire instead of 192 per particle, 3dgrut_b200/dist.py).
+// Phase A: one thread per particle accumulates its 48 values over the views; phase B: the warp writes its 32 rows as
+// contiguous 128-bit accesses.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
+                                                                   uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
+                                                                   const float4* __restrict__ colour_grads /* [n_views][N] */,
+                                                                   float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate) {
+    __shared__ float s_out[K6_WARPS][32][49];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t warp_base = i - lane;
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; ++k) acc[k] = 0.0f;
+    if (i < N) {
+        const float4 r0 = __ldg(density12 + 3 * (size_t)i);
+        for (uint32_t v = 0; v < n_views; ++v) {
+            const float4 g = __ldg(colour_grads + (size_t)v * N + i);
+            if (g.x == 0.0f && g.y == 0.0f && g.z == 0.0f) continue;   // the view did not touch the particle
+            const float3 d = f3(r0.x, r0.y, r0.z) - f3(__ldg(centres + 3 * v), __ldg(centres + 3 * v + 1), __ldg(centres + 3 * v + 2));
+            const float len = sqrtf(dot(d, d));
+            const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(d.x / len, d.y / len, d.z / len);
+            float b[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) b[k] = 0.0f;
+            gut_sh_basis(sph_degree, dir, b);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                acc[3 * k] += b[k] * g.x; acc[3 * k + 1] += b[k] * g.y; acc[3 * k + 2] += b[k] * g.z;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 48; ++k) s_out[wid][lane][k] = acc[k];
+    __syncwarp();
+    const uint32_t rows = warp_base < N ? min(32u, N - warp_base) : 0u;
+    float4* dst = sph_grad + 12 * (size_t)warp_base;
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const uint32_t f = it * 32 + lane;
+        const uint32_t row = f / 12, e0 = (f % 12) * 4;
+        if (row < rows) {
+            float4 val = make_float4(s_out[wid][row][e0], s_out[wid][row][e0 + 1], s_out[wid][row][e0 + 2], s_out[wid][row][e0 + 3]);
+            if (accumulate) { const float4 p = dst[f]; val.x += p.x; val.y += p.y; val.z += p.z; val.w += p.w; }
+            dst[f] = val;
+        }
+    }
+}
+
+cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+                                 const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
+        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, reinterpret_cast<const float4*>(colour_grads),
+        reinterpret_cast<float4*>(sph_grad), accumulate);
     return cudaGetLastError();
 }
 

@@ -4,9 +4,13 @@ The reference is single-GPU, batch size 1 (threedgrut/trainer.py:143-149) and ha
 Here the particle set is replicated on every rank, the views of a step are split over the ranks, every rank
 sums the gradients of its views in place (``accumulate`` mode of gut_backward, no re-zeroing between views)
 and ONE fp32 sum-allreduce of the two per-Gaussian gradient buffers ([N,12] and [N,48]) over NCCL / NVLink
-closes the step.  The [N,12] buffer is final as soon as the last view's compositing backward (K5) has run,
-so its allreduce is issued on a side stream and overlaps the SH backward (K6) of that view; the [N,48]
-allreduce follows K6.  There is no other exchange: images and hit counts stay rank local.
+closes the step.  There is no other exchange: images and hit counts stay rank local.
+
+``training_step_deferred`` is the cheaper formulation of the same step.  The SH gradient of one view is
+basis(view direction) x colour gradient -- 3 numbers per particle and view -- so the ranks all-gather the per-view
+colour gradients ([N,4] each, 16 B per particle and view instead of 192 B per particle), allreduce only the [N,12]
+buffer, and every rank expands all views of the step into [N,48] once (gut_sh_gradient_expand).  The result is the
+same summed gradient on every rank; on one GPU it also replaces V read-modify-writes of the [N,48] buffer by one write.
 """
 import torch
 import torch.distributed as dist
@@ -71,3 +75,61 @@ def training_step(raster, exchange, views, sph_degree, particle_density, particl
         exchange.radiance_grad.zero_()
     exchange.allreduce()
     return outs
+
+
+class DeferredExchange:
+    """Buffers of the deferred-SH step: [N,12] accumulator, per-view colour gradients of this rank and of all ranks."""
+
+    def __init__(self, n_particles, n_sph_floats, views_per_rank, device, world=None):
+        self.world = world if world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
+        self.views_per_rank = views_per_rank
+        self.density_grad = torch.zeros((n_particles, 12), dtype=torch.float32, device=device)
+        self.radiance_grad = torch.zeros((n_particles, n_sph_floats), dtype=torch.float32, device=device)
+        self.colour_all = torch.zeros((self.world * views_per_rank, n_particles, 4), dtype=torch.float32, device=device)
+        self.centres_all = torch.zeros((self.world * views_per_rank, 3), dtype=torch.float32, device=device)
+
+    def local_slot(self, rank, i):
+        return rank * self.views_per_rank + i
+
+    def bytes_per_rank(self):
+        """Bytes this rank contributes to the collectives of a step."""
+        return self.density_grad.numel() * 4 + self.views_per_rank * self.colour_all.shape[1] * 16
+
+
+def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
+    """Same result as ``training_step`` (summed [N,12] and [N,48] gradients on every rank) with the SH expansion deferred.
+    Every rank must hold ``ex.views_per_rank`` views or fewer (missing ones contribute zeros)."""
+    outs = []
+    lo = ex.local_slot(rank, 0)
+    mine = ex.colour_all[lo:lo + ex.views_per_rank]
+    centres = []
+    for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
+        rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
+                                              v["camera"])
+        c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
+                                    rgba, rg, dist_, dg, ex.density_grad, mine[i], accumulate_density=(i > 0))
+        centres.append(c)
+        outs.append((rgba, dist_))
+    if not views:
+        ex.density_grad.zero_()
+    for i in range(len(views), ex.views_per_rank):
+        mine[i].zero_()
+        centres.append([0.0, 0.0, 0.0])
+    my_centres = ex.centres_all[lo:lo + ex.views_per_rank]
+    my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
+    if ex.world > 1:
+        dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM)
+        _all_gather(ex.colour_all, mine)
+        _all_gather(ex.centres_all, my_centres)
+    raster.sh_gradient_expand(sph_degree, particle_density, ex.centres_all, ex.colour_all, ex.radiance_grad, accumulate=False)
+    return outs
+
+
+def _all_gather(out, mine):
+    """All-gather of equal slices along dim 0 (``mine`` may be this rank's slice of ``out``: in-place)."""
+    try:
+        dist.all_gather_into_tensor(out.view(-1), mine.reshape(-1))
+    except (RuntimeError, NotImplementedError):   # backend without the flat variant
+        parts = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
+        dist.all_gather(parts, mine.contiguous())
+        out.copy_(torch.cat(parts, 0))

@@ -62,6 +62,11 @@ def load_library():
     lib.gut_forward.restype = C.c_int
     lib.gut_backward.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, fp, i32]
     lib.gut_backward.restype = C.c_int
+    lib.gut_backward_colour.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, i32, fp,
+                                        C.POINTER(C.c_float)]
+    lib.gut_backward_colour.restype = C.c_int
+    lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
+    lib.gut_sh_gradient_expand.restype = C.c_int
     lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
     lib.gut_forward_host.restype = C.c_int
     lib.gut_backward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, i32]
@@ -251,6 +256,52 @@ class SplatRaster:
         if rc != 0:
             self._raise(rc)
         return out_density_grad, out_radiance_grad
+
+    def trace_bwd_colour(self, num_active_features, particle_density, particle_radiance, ray_origin, ray_direction, sensor: abi.GutCamera,
+                         ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad,
+                         out_density_grad, out_colour_grad, accumulate_density=False):
+        """gut_backward_colour: traceBwd with the SH expansion deferred.  Adds (or writes) the [N,12] gradient into
+        ``out_density_grad``, writes the view's masked colour gradient into ``out_colour_grad`` [N,4] and returns the
+        world-space view centre (3 floats) ``sh_gradient_expand`` needs for this view."""
+        dev = self.device
+        dens = _check_cuda_f32("particle_density", particle_density, dev)
+        rad = _check_cuda_f32("particle_radiance", particle_radiance, dev)
+        ro = _check_cuda_f32("ray_origin", ray_origin, dev)
+        rd = _check_cuda_f32("ray_direction", ray_direction, dev)
+        rgba = _check_cuda_f32("ray_radiance_density", ray_radiance_density, dev)
+        rgba_g = _check_cuda_f32("ray_radiance_density_grad", ray_radiance_density_grad, dev)
+        dist = _check_cuda_f32("ray_hit_distance", ray_hit_distance, dev)
+        dist_g = _check_cuda_f32("ray_hit_distance_grad", ray_hit_distance_grad, dev)
+        n = dens.shape[0]
+        height, width = ro.shape[1], ro.shape[2]
+        if rgba_g.numel() != height * width * 4 or dist_g.numel() != height * width:
+            raise GutError(abi.GutStatus.BAD_INPUT, "gradient shapes do not match the view")
+        if out_density_grad.shape != (n, 12) or out_colour_grad.shape != (n, 4) or not out_colour_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be [N,12], out_colour_grad a contiguous [N,4]")
+        centre = (C.c_float * 3)()
+        rc = self.lib.gut_backward_colour(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
+                                          width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
+                                          _ptr(out_density_grad), 1 if accumulate_density else 0, _ptr(out_colour_grad), centre)
+        if rc != 0:
+            self._raise(rc)
+        return [centre[0], centre[1], centre[2]]
+
+    def sh_gradient_expand(self, num_active_features, particle_density, view_centres, colour_grads, out_radiance_grad, accumulate=False):
+        """gut_sh_gradient_expand: out_radiance_grad [N,48] (+)= sum over views of basis(direction) x colour gradient.
+        ``colour_grads`` is a contiguous [V,N,4] tensor, ``view_centres`` a [V,3] float32 CUDA tensor."""
+        dev = self.device
+        dens = _check_cuda_f32("particle_density", particle_density, dev)
+        cg = _check_cuda_f32("colour_grads", colour_grads, dev)
+        vc = _check_cuda_f32("view_centres", view_centres, dev)
+        n = dens.shape[0]
+        nv = vc.shape[0]
+        if vc.shape != (nv, 3) or cg.shape != (nv, n, 4) or out_radiance_grad.shape != (n, self.n_coeffs * 3) or not out_radiance_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "colour_grads must be [V,N,4] and out_radiance_grad a contiguous [N,48]")
+        rc = self.lib.gut_sh_gradient_expand(self._h, self._stream(), n, int(num_active_features), _ptr(dens), nv, _ptr(vc), _ptr(cg),
+                                             _ptr(out_radiance_grad), 1 if accumulate else 0)
+        if rc != 0:
+            self._raise(rc)
+        return out_radiance_grad
 
     def collect_times(self):
         """reference: SplatRaster::collectTimes (splatRaster.cpp:334-364) -> {tag: mean ms}."""

@@ -47,6 +47,10 @@ def parse_args():
     p.add_argument("--height", type=int, default=H_IMG)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--exchange", choices=("deferred", "allreduce"), default="deferred",
+                   help="gradient exchange of the step: deferred = allreduce [N,12] + all-gather per-view colour gradients, SH expansion "
+                        "once per step (3dgrut_b200/dist.py training_step_deferred); allreduce = per-view [N,48] accumulation + one "
+                        "allreduce of [N,12]+[N,48]")
     p.add_argument("--no-aux", action="store_true", help="skip the auxiliary forward-only 1080p measurement")
     p.add_argument("--cpu-sample-tiles", type=int, default=24)
     return p.parse_args()
@@ -56,7 +60,9 @@ def workload_config(args, world):
     return {
         "workload": f"3DGUT training step: {args.particles} random-init Gaussians (S-init), SH deg {SPH_DEGREE}, batch of {args.views} "
                     f"pinhole views {args.width}x{args.height}, k_buffer_size=0, views sharded over {world} GPU(s), "
-                    f"NCCL allreduce of [N,12]+[N,48] fp32 gradients",
+                    + ("NCCL allreduce of the [N,12] fp32 gradients + all-gather of the per-view colour gradients [N,4], SH gradient "
+                       "[N,48] expanded once per step on every rank" if args.exchange == "deferred" else
+                       "NCCL allreduce of [N,12]+[N,48] fp32 gradients"),
         "particles": args.particles, "views_per_step": args.views, "width": args.width, "height": args.height,
         "sph_degree": SPH_DEGREE, "parallelism": f"view-sharded dp{world}, particles replicated",
         "l2_policy": "inputs larger than L2: every view streams the particle parameters and SH (3M x 240 B = 720 MB), the [N,16] gradient "
@@ -242,7 +248,10 @@ def run_ours(args):
 
     cfg = abi.default_config(enable_kernel_timings=1)
     raster = native.SplatRaster(cfg, device=dev)
-    exchange = gdist.GradientExchange(n, sph.shape[1], dev, world=world)
+    if args.exchange == "deferred":
+        exchange = gdist.DeferredExchange(n, sph.shape[1], (args.views + world - 1) // world, dev, world=world)
+    else:
+        exchange = gdist.GradientExchange(n, sph.shape[1], dev, world=world)
 
     def barrier():
         torch.cuda.synchronize()
@@ -251,6 +260,8 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     def step():
+        if args.exchange == "deferred":
+            return gdist.training_step_deferred(raster, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
         return gdist.training_step(raster, exchange, views, SPH_DEGREE, d12, sph, upstream)
 
     for _ in range(args.warmup):

@@ -34,6 +34,24 @@ class FakeRaster:
         return out_density_grad, out_radiance_grad
 
 
+    # deferred-SH variants (gut_backward_colour / gut_sh_gradient_expand): the stand-in's "SH gradient" of a view is
+    # centre_x * colour gradient broadcast over the 48 columns, so that the expansion needs both gathered inputs
+    def trace_bwd_colour(self, deg, density, radiance, ray_o, ray_d, camera, rgba, rgba_grad, d, d_grad, out_density_grad,
+                         out_colour_grad, accumulate_density=False):
+        g1 = rgba_grad.sum() * density + d_grad.sum()
+        if accumulate_density:
+            out_density_grad += g1
+        else:
+            out_density_grad.copy_(g1)
+        out_colour_grad.copy_(rgba_grad.mean() * radiance[:, :4])
+        return [float(ray_o.flatten()[0]) + 1.0, 0.0, 0.0]
+
+    def sh_gradient_expand(self, deg, density, centres, colour_all, out, accumulate=False):
+        val = (centres[:, 0].reshape(-1, 1, 1) * colour_all[:, :, :3]).sum(0)          # [N,3]
+        out.copy_(val.repeat(1, NSPH // 3))
+        return out
+
+
 def _data():
     g = torch.Generator().manual_seed(0)
     density = torch.randn((N, 12), generator=g); radiance = torch.randn((N, NSPH), generator=g)
@@ -48,6 +66,25 @@ def _step(rank, world):
     ex = gdist.GradientExchange(N, NSPH, "cpu", world=world)
     gdist.training_step(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids])
     return ex.density_grad.clone(), ex.radiance_grad.clone()
+
+
+def _step_deferred(rank, world):
+    density, radiance, views, ups = _data()
+    ids = gdist.shard_views(NVIEWS, rank, world)
+    vpr = (NVIEWS + world - 1) // world
+    ex = gdist.DeferredExchange(N, NSPH, vpr, "cpu", world=world)
+    gdist.training_step_deferred(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids], rank=rank)
+    return ex.density_grad.clone(), ex.radiance_grad.clone()
+
+
+def _worker_deferred(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g1, g2 = _step_deferred(rank, world)
+        q.put((rank, g1.numpy(), g2.numpy()))
+    finally:
+        dist.destroy_process_group()
 
 
 def _worker(rank, world, port, q):
@@ -81,6 +118,25 @@ def test_two_rank_step_equals_single_process():
     for p in procs: p.join(30)
     assert all(p.exitcode == 0 for p in procs)
     for _, g1, g2 in res:   # every rank holds the full sum after the allreduce
+        torch.testing.assert_close(torch.from_numpy(g1), ref1, rtol=1e-5, atol=1e-4)
+        torch.testing.assert_close(torch.from_numpy(g2), ref2, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.timeout(120)
+def test_two_rank_deferred_step_equals_single_process():
+    """all-gather of per-view colour gradients + allreduce of [N,12] + local expansion == the single-process result
+    (ranks hold 3 and 2 of the 5 views: the missing slot of rank 1 must contribute zeros)."""
+    ref1, ref2 = _step_deferred(0, 1)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_deferred, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs: p.start()
+    res = [q.get(timeout=90) for _ in procs]
+    for p in procs: p.join(30)
+    assert all(p.exitcode == 0 for p in procs)
+    for _, g1, g2 in res:
         torch.testing.assert_close(torch.from_numpy(g1), ref1, rtol=1e-5, atol=1e-4)
         torch.testing.assert_close(torch.from_numpy(g2), ref2, rtol=1e-5, atol=1e-5)
 
