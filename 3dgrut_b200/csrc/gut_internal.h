@@ -67,7 +67,7 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad,
-                                        float* colour_out /* non-null: write the view's masked colour gradient [N,4] instead of sph_grad */,
+                                        float* colour_out /* non-null: write the view's masked colour gradient [N,3] instead of sph_grad */,
                                         int accumulate, cudaStream_t stream);
 
 // deferred SH backward of a multi-view step (gut_project.cu, gut_sh_expand_kernel)

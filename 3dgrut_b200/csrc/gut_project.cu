@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
                                                                           const uint32_t* __restrict__ tiles_count,
                                                                           const float4* __restrict__ features,
                                                                           float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
-                                                                          float* __restrict__ sph_grad, float4* __restrict__ colour_out,
+                                                                          float* __restrict__ sph_grad, float* __restrict__ colour_out,
                                                                           int accumulate) {
     __shared__ float4 s_dg[K6_WARPS][32 * 3];      // parameter-gradient rows of the warp
     __shared__ float s_basis[K6_WARPS][32][17];    // SH basis per row (+1 pad: conflict-free column reads)
@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
     }
     // deferred SH gradient: hand out the masked colour gradient of this view, gut_sh_expand_kernel sums the views later
     if (colour_out) {
-        if (i < N) colour_out[i] = make_float4(g.x, g.y, g.z, 0.0f);
+        if (i < N) { colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z; }
         return;
     }
     // [N,48]
@@ -447,14 +447,13 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
     gut_project_backward_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree,
                                                                       reinterpret_cast<const float4*>(density12), tiles_count,
                                                                       features, reinterpret_cast<float4*>(raw_grad),
-                                                                      reinterpret_cast<float4*>(density_grad), sph_grad,
-                                                                      reinterpret_cast<float4*>(colour_out), accumulate);
+                                                                      reinterpret_cast<float4*>(density_grad), sph_grad, colour_out, accumulate);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------------
 // Deferred SH backward of a multi-view step: dL/dSH[i] (+)= sum_v basis(normalize(pos_i - centre_v)) (x) colour_grad_v[i].
-// K6 hands out 16 bytes per particle and view instead of read-modify-writing the 192-byte SH gradient row once per
+// K6 hands out 12 bytes per particle and view instead of read-modify-writing the 192-byte SH gradient row once per
 // view; this kernel expands all views at once (and, across GPUs, the views of all ranks after an all-gather of the
 // colour gradients -- 12 bytes per particle and view on the wire instead of 192 per particle, 3dgrut_b200/dist.py).
 // Phase A: one thread per particle accumulates its 48 values over the views; phase B: the warp writes its 32 rows as
@@ -462,7 +461,7 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                    uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
-                                                                   const float4* __restrict__ colour_grads /* [n_views][N] */,
+                                                                   const float* __restrict__ colour_grads /* [n_views][N][3] */,
                                                                    float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate) {
     __shared__ float s_out[K6_WARPS][32][49];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -474,7 +473,8 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
     if (i < N) {
         const float4 r0 = __ldg(density12 + 3 * (size_t)i);
         for (uint32_t v = 0; v < n_views; ++v) {
-            const float4 g = __ldg(colour_grads + (size_t)v * N + i);
+            const float* gp = colour_grads + 3 * ((size_t)v * N + i);
+            const float3 g = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
             if (g.x == 0.0f && g.y == 0.0f && g.z == 0.0f) continue;   // the view did not touch the particle
             const float3 d = f3(r0.x, r0.y, r0.z) - f3(__ldg(centres + 3 * v), __ldg(centres + 3 * v + 1), __ldg(centres + 3 * v + 2));
             const float len = sqrtf(dot(d, d));
@@ -510,7 +510,7 @@ cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* densit
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
-        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, reinterpret_cast<const float4*>(colour_grads),
+        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, colour_grads,
         reinterpret_cast<float4*>(sph_grad), accumulate);
     return cudaGetLastError();
 }

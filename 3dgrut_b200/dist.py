@@ -8,7 +8,7 @@ closes the step.  There is no other exchange: images and hit counts stay rank lo
 
 ``training_step_deferred`` is the cheaper formulation of the same step.  The SH gradient of one view is
 basis(view direction) x colour gradient -- 3 numbers per particle and view -- so the ranks all-gather the per-view
-colour gradients ([N,4] each, 16 B per particle and view instead of 192 B per particle), allreduce only the [N,12]
+colour gradients ([N,3] each, 12 B per particle and view instead of 192 B per particle), allreduce only the [N,12]
 buffer, and every rank expands all views of the step into [N,48] once (gut_sh_gradient_expand).  The result is the
 same summed gradient on every rank; on one GPU it also replaces V read-modify-writes of the [N,48] buffer by one write.
 """
@@ -85,7 +85,7 @@ class DeferredExchange:
         self.views_per_rank = views_per_rank
         self.density_grad = torch.zeros((n_particles, 12), dtype=torch.float32, device=device)
         self.radiance_grad = torch.zeros((n_particles, n_sph_floats), dtype=torch.float32, device=device)
-        self.colour_all = torch.zeros((self.world * views_per_rank, n_particles, 4), dtype=torch.float32, device=device)
+        self.colour_all = torch.zeros((self.world * views_per_rank, n_particles, 3), dtype=torch.float32, device=device)
         self.centres_all = torch.zeros((self.world * views_per_rank, 3), dtype=torch.float32, device=device)
 
     def local_slot(self, rank, i):
@@ -93,7 +93,7 @@ class DeferredExchange:
 
     def bytes_per_rank(self):
         """Bytes this rank contributes to the collectives of a step."""
-        return self.density_grad.numel() * 4 + self.views_per_rank * self.colour_all.shape[1] * 16
+        return self.density_grad.numel() * 4 + self.views_per_rank * self.colour_all.shape[1] * 12
 
 
 def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
@@ -117,11 +117,15 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         centres.append([0.0, 0.0, 0.0])
     my_centres = ex.centres_all[lo:lo + ex.views_per_rank]
     my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
+    pending = None
     if ex.world > 1:
-        dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM)
         _all_gather(ex.colour_all, mine)
         _all_gather(ex.centres_all, my_centres)
+        # the [N,12] allreduce runs on the collective stream while this stream expands the SH gradient
+        pending = dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)
     raster.sh_gradient_expand(sph_degree, particle_density, ex.centres_all, ex.colour_all, ex.radiance_grad, accumulate=False)
+    if pending is not None:
+        pending.wait()
     return outs
 
 

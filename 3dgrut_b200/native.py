@@ -261,7 +261,7 @@ class SplatRaster:
                          ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad,
                          out_density_grad, out_colour_grad, accumulate_density=False):
         """gut_backward_colour: traceBwd with the SH expansion deferred.  Adds (or writes) the [N,12] gradient into
-        ``out_density_grad``, writes the view's masked colour gradient into ``out_colour_grad`` [N,4] and returns the
+        ``out_density_grad``, writes the view's masked colour gradient into ``out_colour_grad`` [N,3] and returns the
         world-space view centre (3 floats) ``sh_gradient_expand`` needs for this view."""
         dev = self.device
         dens = _check_cuda_f32("particle_density", particle_density, dev)
@@ -276,8 +276,8 @@ class SplatRaster:
         height, width = ro.shape[1], ro.shape[2]
         if rgba_g.numel() != height * width * 4 or dist_g.numel() != height * width:
             raise GutError(abi.GutStatus.BAD_INPUT, "gradient shapes do not match the view")
-        if out_density_grad.shape != (n, 12) or out_colour_grad.shape != (n, 4) or not out_colour_grad.is_contiguous():
-            raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be [N,12], out_colour_grad a contiguous [N,4]")
+        if out_density_grad.shape != (n, 12) or out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be [N,12], out_colour_grad a contiguous [N,3]")
         centre = (C.c_float * 3)()
         rc = self.lib.gut_backward_colour(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
                                           width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
@@ -288,15 +288,15 @@ class SplatRaster:
 
     def sh_gradient_expand(self, num_active_features, particle_density, view_centres, colour_grads, out_radiance_grad, accumulate=False):
         """gut_sh_gradient_expand: out_radiance_grad [N,48] (+)= sum over views of basis(direction) x colour gradient.
-        ``colour_grads`` is a contiguous [V,N,4] tensor, ``view_centres`` a [V,3] float32 CUDA tensor."""
+        ``colour_grads`` is a contiguous [V,N,3] tensor, ``view_centres`` a [V,3] float32 CUDA tensor."""
         dev = self.device
         dens = _check_cuda_f32("particle_density", particle_density, dev)
         cg = _check_cuda_f32("colour_grads", colour_grads, dev)
         vc = _check_cuda_f32("view_centres", view_centres, dev)
         n = dens.shape[0]
         nv = vc.shape[0]
-        if vc.shape != (nv, 3) or cg.shape != (nv, n, 4) or out_radiance_grad.shape != (n, self.n_coeffs * 3) or not out_radiance_grad.is_contiguous():
-            raise GutError(abi.GutStatus.BAD_INPUT, "colour_grads must be [V,N,4] and out_radiance_grad a contiguous [N,48]")
+        if vc.shape != (nv, 3) or cg.shape != (nv, n, 3) or out_radiance_grad.shape != (n, self.n_coeffs * 3) or not out_radiance_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "colour_grads must be [V,N,3] and out_radiance_grad a contiguous [N,48]")
         rc = self.lib.gut_sh_gradient_expand(self._h, self._stream(), n, int(num_active_features), _ptr(dens), nv, _ptr(vc), _ptr(cg),
                                              _ptr(out_radiance_grad), 1 if accumulate else 0)
         if rc != 0:

@@ -60,7 +60,7 @@ def workload_config(args, world):
     return {
         "workload": f"3DGUT training step: {args.particles} random-init Gaussians (S-init), SH deg {SPH_DEGREE}, batch of {args.views} "
                     f"pinhole views {args.width}x{args.height}, k_buffer_size=0, views sharded over {world} GPU(s), "
-                    + ("NCCL allreduce of the [N,12] fp32 gradients + all-gather of the per-view colour gradients [N,4], SH gradient "
+                    + ("NCCL allreduce of the [N,12] fp32 gradients + all-gather of the per-view colour gradients [N,3], SH gradient "
                        "[N,48] expanded once per step on every rank" if args.exchange == "deferred" else
                        "NCCL allreduce of [N,12]+[N,48] fp32 gradients"),
         "particles": args.particles, "views_per_step": args.views, "width": args.width, "height": args.height,

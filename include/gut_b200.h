@@ -192,10 +192,10 @@ GUT_API int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
  * Deferred SH gradient for multi-view steps (this build's extension).
  * dL/dSH of one view is basis(view direction) (x) dL/dcolour (gaussianParticles.cuh:120-187), i.e. 3 numbers per
  * particle and view expanded to 3 x 16.  gut_backward_colour is gut_backward without that expansion: it writes the
- * view's masked colour gradient d_colour_grad[N,4] (xyz, w = 0; zero for particles the view did not touch) and the
+ * view's masked colour gradient d_colour_grad[N,3] (zero for particles the view did not touch) and the
  * world-space view centre it used (host float[3], may be NULL).  gut_sh_gradient_expand then forms
  *   d_particle_radiance_grad[N,48] (+)= sum_v basis(normalize(position - centre_v)) (x) colour_grad_v
- * for all views at once (d_colour_grads is [n_views, N, 4]; d_view_centres is a DEVICE array [n_views, 3], so the
+ * for all views at once (d_colour_grads is [n_views, N, 3]; d_view_centres is a DEVICE array [n_views, 3], so the
  * centres of other ranks' views can arrive by the same all-gather as their colour gradients).
  * One step of V views therefore writes the 192-byte SH gradient row once instead of read-modify-writing it V times,
  * and data-parallel ranks exchange 12 B per particle and view instead of 192 B per particle.

@@ -43,7 +43,7 @@ class FakeRaster:
             out_density_grad += g1
         else:
             out_density_grad.copy_(g1)
-        out_colour_grad.copy_(rgba_grad.mean() * radiance[:, :4])
+        out_colour_grad.copy_(rgba_grad.mean() * radiance[:, :3])
         return [float(ray_o.flatten()[0]) + 1.0, 0.0, 0.0]
 
     def sh_gradient_expand(self, deg, density, centres, colour_all, out, accumulate=False):
