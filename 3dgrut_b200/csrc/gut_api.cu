@@ -49,6 +49,7 @@ struct GutHandle {
 
     // forward context consumed by backward
     bool fwd_valid = false;
+    bool pending_density = false;   // gut_backward_colour left view-summed accumulators for gut_density_gradient_finish
     cudaStream_t fwd_stream = nullptr;
     uint32_t fwd_N = 0, fwd_W = 0, fwd_H = 0;
     uint64_t fwd_M = 0;
@@ -403,7 +404,9 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
         return fail(h, GUT_ERR_NO_FORWARD, "cannot render backward: no forward context on this stream (reference: gutRenderer.cu:413-417)");
     if (h->fwd_N != N || h->fwd_W != W || h->fwd_H != H) return fail(h, GUT_ERR_NO_FORWARD, "backward shapes differ from the preceding forward");
     if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_rgba_grad || !d_dist || !d_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null ray/gradient pointer");
-    if (N > 0 && (!d_density || !d_density_grad || (!d_radiance_grad && !d_colour_grad))) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    if (N > 0 && (!d_density || (!d_density_grad && !d_colour_grad) || (!d_radiance_grad && !d_colour_grad))) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    if (!d_colour_grad && h->pending_density)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_backward after gut_backward_colour: call gut_density_gradient_finish first");
     if (N == 0) return GUT_OK;
     DeviceGuard guard(h->device);
     if (h->cfg.enable_kernel_timings) start_timer(h->timers, 1, s);
@@ -447,15 +450,34 @@ int gut_backward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t 
 
 int gut_backward_colour(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
                         const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
-                        const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad,
-                        int32_t accumulate_density, float* d_colour_grad, float* view_centre_out) {
+                        const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_colour_grad, float* view_centre_out) {
     if (h && N > 0 && !d_colour_grad) return fail(h, GUT_ERR_BAD_INPUT, "null colour gradient pointer");
     int rc = backward_impl(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist,
-                           d_dist_grad, d_density_grad, nullptr, d_colour_grad, accumulate_density);
-    if (rc == GUT_OK && view_centre_out) {
-        view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
+                           d_dist_grad, nullptr, nullptr, d_colour_grad, 0);
+    if (rc == GUT_OK) {
+        h->pending_density = true;
+        if (view_centre_out) {
+            view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
+        }
     }
     return rc;
+}
+
+int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const float* d_density, float* d_density_grad, int32_t accumulate) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (N == 0) { h->pending_density = false; return GUT_OK; }
+    if (!d_density || !d_density_grad) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    if ((size_t)N * 64 > h->raw_grad.cap || !h->raw_grad.p) {   // no gut_backward_colour ran: the sum is zero
+        GUT_CUDA(h, ensure(h->raw_grad, (size_t)N * 64, s));
+        GUT_CUDA(h, cudaMemsetAsync(h->raw_grad.p, 0, h->raw_grad.cap, s));
+    }
+    GUT_CUDA(h, gut_launch_project_backward(h->cfg, h->fwd_frame, N, 0, d_density, nullptr, nullptr, (float*)h->raw_grad.p, d_density_grad,
+                                            nullptr, nullptr, accumulate, s));
+    h->launches += 1;
+    h->pending_density = false;
+    return GUT_OK;
 }
 
 int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degree, const float* d_density, uint32_t n_views,

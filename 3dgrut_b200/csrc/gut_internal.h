@@ -38,7 +38,7 @@ static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
 struct __align__(16) GutRecordBwd {
     float r_yz, r_zy, r_xz, r_zx;   // s_y/s_z, s_z/s_y, s_x/s_z, s_z/s_x
     float r_yx, r_xy, isx, isy;     // s_y/s_x, s_x/s_y, 1/s_x, 1/s_y
-    float isz, pad0, pad1, pad2;    // 1/s_z
+    float isz, wx, wy, wz;          // 1/s_z | (frame origin - position) / scale
 };
 static_assert(sizeof(GutRecordBwd) == 48, "backward record must be 3 float4");
 

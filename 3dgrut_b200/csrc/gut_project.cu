@@ -286,6 +286,11 @@ constexpr int K6_WARPS = K6_THREADS / 32;
 // Phase B: each warp writes its 32 rows of [N,12] (3 float4 per row) and [N,48] (12 float4 per row) as contiguous,
 // fully coalesced 128-bit accesses (12 independent loads in flight per lane when accumulating) instead of every
 // thread walking its own 192-byte row.
+// DENSITY: convert the accumulators into the [N,12] gradient (and reset them); COLOUR: the SH / colour part (and reset
+// its three accumulators).  Both: one backward call of the reference API.  COLOUR only: one view of a deferred step
+// (gut_backward_colour).  DENSITY only: end of a deferred step, over ALL particles (tiles_count == nullptr): the
+// accumulators then hold the sum over the step's views, which is legitimate because they are view-independent.
+template <bool DENSITY, bool COLOUR>
 __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutConfig cfg, GutFrame fr, uint32_t N, int sph_degree,
                                                                           const float4* __restrict__ density12,
                                                                           const uint32_t* __restrict__ tiles_count,
@@ -308,18 +313,19 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
     float b[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) b[k] = 0.0f;
-    if (i < N) touched = tiles_count[i] != 0;
+    if (i < N) touched = tiles_count ? tiles_count[i] != 0 : true;
     if (touched) {
         const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos, density
+        float4* rg = raw_grad + 4 * (size_t)i;
+        float4 g0, g1, g2 = rg[2], g3 = rg[3];
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (DENSITY) { g0 = rg[0]; g1 = rg[1]; rg[0] = z; rg[1] = z; }
+        if (DENSITY && COLOUR) { rg[2] = z; rg[3] = z; }
+        else if (DENSITY) { rg[2] = make_float4(0.0f, 0.0f, 0.0f, g2.w); rg[3] = make_float4(g3.x, g3.y, 0.0f, 0.0f); }
+        else { rg[2] = make_float4(g2.x, g2.y, g2.z, 0.0f); rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w); }
+        if (DENSITY) {
         const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
         const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
-        const float4 ft = __ldg(features + i);
-        float4* rg = raw_grad + 4 * (size_t)i;
-        const float4 g0 = rg[0], g1 = rg[1], g2 = rg[2], g3 = rg[3];
-        {
-            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            rg[0] = z; rg[1] = z; rg[2] = z; rg[3] = z;
-        }
         // ---- (i) parameter gradient ----
         const float3 A = f3(g0.x, g0.y, g0.z);
         const float3 tau = f3(g1.x, g1.y, g1.z);
@@ -334,20 +340,23 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
         o0 = make_float4(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
                          -(c0.z * As.x + c1.z * As.y + c2.z * As.z), g0.w);
         o2 = make_float4(-Z.x * is.x, -Z.y * is.y, -Z.z * is.z, 0.0f);
-        // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = sum Z + W ; trace = tr_dir + sum_i A_i v_i / s_i
-        const float3 vf = fr.cam_centre - f3(r0.x, r0.y, r0.z);
-        const float rho = 2.0f * ((Z.x + Z.y + Z.z + W) - (tr_dir + As.x * vf.x + As.y * vf.y + As.z * vf.z));
+        // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = sum Z + W ; the trace is summed per ray by K5
+        const float rho = 2.0f * ((Z.x + Z.y + Z.z + W) - tr_dir);
         // tangential part: body-frame torque -> 2 q (x) (0, tau)
         const float3 rv = f3(qv.y, qv.z, qv.w);
         const float3 rxt = cross(rv, tau);
         o1 = make_float4(rho * qv.x - 2.0f * dot(rv, tau), rho * rv.x + 2.0f * (qv.x * tau.x + rxt.x),
                          rho * rv.y + 2.0f * (qv.x * tau.y + rxt.y), rho * rv.z + 2.0f * (qv.x * tau.z + rxt.z));
+        }
+        if (COLOUR) {
         // ---- (ii) SH: masked colour gradient and basis of the view direction ----
+        const float4 ft = __ldg(features + i);
         const float3 v = f3(r0.x, r0.y, r0.z) - fr.cam_centre;
         const float len = sqrtf(dot(v, v));
         const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(v.x / len, v.y / len, v.z / len);
         gut_sh_basis(sph_degree, dir, b);
         g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
+        }
     }
     s_dg[wid][3 * lane] = o0; s_dg[wid][3 * lane + 1] = o1; s_dg[wid][3 * lane + 2] = o2;
 #pragma unroll
@@ -357,7 +366,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
 
     const uint32_t rows = warp_base < N ? min(32u, N - warp_base) : 0u;
     // [N,12]: 3 float4 per row, rows*3 contiguous float4
-    {
+    if (DENSITY) {
         float4* dst = density_grad + 3 * (size_t)warp_base;
 #pragma unroll
         for (int it = 0; it < 3; ++it) {
@@ -374,6 +383,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
             }
         }
     }
+    if (!COLOUR) return;
     // deferred SH gradient: hand out the masked colour gradient of this view, gut_sh_expand_kernel sums the views later
     if (colour_out) {
         if (i < N) { colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z; }
@@ -439,15 +449,45 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
     return cudaGetLastError();
 }
 
+// One view of a deferred step (gut_backward_colour): hand out the view's masked colour gradient and reset its three
+// accumulators; everything else waits for the end of the step.  ~100 bytes per particle, no shared memory.
+__global__ void __launch_bounds__(256) gut_colour_gradient_kernel(uint32_t N, const uint32_t* __restrict__ tiles_count,
+                                                                  const float4* __restrict__ features, float4* __restrict__ raw_grad,
+                                                                  float* __restrict__ colour_out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    float3 g = f3(0.f, 0.f, 0.f);
+    if (tiles_count[i] != 0) {
+        float4* rg = raw_grad + 4 * (size_t)i;
+        const float4 g2 = rg[2], g3 = rg[3];
+        const float4 ft = __ldg(features + i);
+        g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
+        rg[2] = make_float4(g2.x, g2.y, g2.z, 0.0f);
+        rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w);
+    }
+    colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z;
+}
+
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, int accumulate,
                                         cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    gut_project_backward_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree,
-                                                                      reinterpret_cast<const float4*>(density12), tiles_count,
-                                                                      features, reinterpret_cast<float4*>(raw_grad),
-                                                                      reinterpret_cast<float4*>(density_grad), sph_grad, colour_out, accumulate);
+    const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
+    const float4* d12 = reinterpret_cast<const float4*>(density12);
+    float4* rg = reinterpret_cast<float4*>(raw_grad);
+    float4* dg = reinterpret_cast<float4*>(density_grad);
+    if (density_grad && (sph_grad || colour_out))
+        gut_project_backward_kernel<true, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
+                                                                               sph_grad, colour_out, accumulate);
+    else if (density_grad)
+        gut_project_backward_kernel<true, false><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
+                                                                                nullptr, nullptr, accumulate);
+    else if (colour_out)
+        gut_colour_gradient_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, tiles_count, features, rg, colour_out);
+    else
+        gut_project_backward_kernel<false, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg,
+                                                                                nullptr, sph_grad, colour_out, accumulate);
     return cudaGetLastError();
 }
 

@@ -312,7 +312,7 @@ struct BwdRay {
 //   [0..2]  A   = dL/d go            (canonical ray origin)        -> dL/dpos   = -ms^T A
 //   [3]     dL/d density
 //   [4..6]  tau = body-frame torque                                 -> dL/dquat  = rho q + 2 q (x) (0, tau)
-//   [7]     tr  = sum_i (dL/dR^T)_ii, direction part                -> rho (radial part of dL/dquat, R(q) is a polynomial)
+//   [7]     tr  = sum_i (dL/dR^T)_ii                                -> rho (radial part of dL/dquat, R(q) is a polynomial)
 //   [8..10] Z_i = go_i A_i + u_i B_i - s_i * (hit-distance term)    -> dL/dscale_i = -Z_i / s_i
 //   [11..13] dL/d colour
 //   [14]    W   = sum_i s_i * (hit-distance scale term)             -> rho
@@ -342,7 +342,8 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
         const float4 F = r[4];
         {
             const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
-            const float isz = recb[3 * j + 2].x;
+            const float4 R2 = recb[3 * j + 2];
+            const float isz = R2.x;
             const F2x3& go = k.go;
             const F2x3& u = k.u;
             const F2 il = mk2(mufu_rsq(h0 ? lo(k.l2) : 1.0f), mufu_rsq(h1 ? hi(k.l2) : 1.0f));   // 1 / |u|
@@ -415,6 +416,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             v[5] = (fma(bc(R0.z), fma(go.x, Ag.z, u.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, u.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
             v[6] = (fma(bc(R1.x), fma(go.y, Ag.x, u.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, u.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
             F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x)));
+            tr = fma(Ag.z, bc(R2.w), fma(Ag.y, bc(R2.z), fma(Ag.x, bc(R2.y), tr)));   // origin part: A . (frame origin - position) / s
             if (!UNIFORM) tr = fma(bc(isz), Ag.z * ray.dlt.z, fma(bc(R1.w), Ag.y * ray.dlt.y, fma(bc(R1.z), Ag.x * ray.dlt.x, tr)));
             v[7] = (tr);
             v[8] = (fma(go.x, Ag.x, fma(u.x, Bg.x, kd * sg2.x)));

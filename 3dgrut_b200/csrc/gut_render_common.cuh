@@ -154,7 +154,7 @@ struct WarpStager {
                 float4* outb = recb + 3 * lane;
                 outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
                 outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
-                outb[2] = make_float4(iz, 0.0f, 0.0f, 0.0f);
+                outb[2] = make_float4(iz, v.x * ix, v.y * iy, v.z * iz);   // 1/s_z | (frame origin - position) / s
             }
         } else if (lane < cnt_pad) {
             out[0] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);

@@ -248,13 +248,12 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
                             grdG.z - kap * fmaf(dgo * r2.z, sg.z, ssum * go.z));
         const float gx = dot(grd, X);
         const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
-        const float3 dlt = o - origin;
         v[0] = Ag.x; v[1] = Ag.y; v[2] = Ag.z;
         v[3] = dDens;
         v[4] = (r2.z * iy) * fmaf(go.z, Ag.y, u.z * Bg.y) - (r2.y * iz) * fmaf(go.y, Ag.z, u.y * Bg.z);
         v[5] = (r2.x * iz) * fmaf(go.x, Ag.z, u.x * Bg.z) - (r2.z * ix) * fmaf(go.z, Ag.x, u.z * Bg.x);
         v[6] = (r2.y * ix) * fmaf(go.y, Ag.x, u.y * Bg.x) - (r2.x * iy) * fmaf(go.x, Ag.y, u.x * Bg.y);
-        v[7] = ix * (Bg.x * d.x + Ag.x * dlt.x) + iy * (Bg.y * d.y + Ag.y * dlt.y) + iz * (Bg.z * d.z + Ag.z * dlt.z);
+        v[7] = ix * (Bg.x * d.x + Ag.x * rel.x) + iy * (Bg.y * d.y + Ag.y * rel.y) + iz * (Bg.z * d.z + Ag.z * rel.z);
         v[8] = fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x));
         v[9] = fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y));
         v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));

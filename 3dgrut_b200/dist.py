@@ -9,8 +9,10 @@ closes the step.  There is no other exchange: images and hit counts stay rank lo
 ``training_step_deferred`` is the cheaper formulation of the same step.  The SH gradient of one view is
 basis(view direction) x colour gradient -- 3 numbers per particle and view -- so the ranks all-gather the per-view
 colour gradients ([N,3] each, 12 B per particle and view instead of 192 B per particle), allreduce only the [N,12]
-buffer, and every rank expands all views of the step into [N,48] once (gut_sh_gradient_expand).  The result is the
-same summed gradient on every rank; on one GPU it also replaces V read-modify-writes of the [N,48] buffer by one write.
+buffer, and every rank expands all views of the step into [N,48] once (gut_sh_gradient_expand).  The [N,12] part is
+deferred too: the backward's per-particle accumulators are view independent, so they sum over the rank's views and are
+converted once (gut_density_gradient_finish).  The result is the same summed gradient on every rank; on one GPU it
+replaces V read-modify-writes of both gradient buffers by one write each.
 """
 import torch
 import torch.distributed as dist
@@ -107,11 +109,10 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
-                                    rgba, rg, dist_, dg, ex.density_grad, mine[i], accumulate_density=(i > 0))
+                                    rgba, rg, dist_, dg, mine[i])
         centres.append(c)
         outs.append((rgba, dist_))
-    if not views:
-        ex.density_grad.zero_()
+    raster.density_gradient_finish(particle_density, ex.density_grad)   # zeros when this rank had no view
     for i in range(len(views), ex.views_per_rank):
         mine[i].zero_()
         centres.append([0.0, 0.0, 0.0])

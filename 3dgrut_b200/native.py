@@ -62,9 +62,11 @@ def load_library():
     lib.gut_forward.restype = C.c_int
     lib.gut_backward.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, fp, i32]
     lib.gut_backward.restype = C.c_int
-    lib.gut_backward_colour.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, i32, fp,
+    lib.gut_backward_colour.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp,
                                         C.POINTER(C.c_float)]
     lib.gut_backward_colour.restype = C.c_int
+    lib.gut_density_gradient_finish.argtypes = [vp, vp, u32, fp, fp, i32]
+    lib.gut_density_gradient_finish.restype = C.c_int
     lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
     lib.gut_sh_gradient_expand.restype = C.c_int
     lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
@@ -258,11 +260,10 @@ class SplatRaster:
         return out_density_grad, out_radiance_grad
 
     def trace_bwd_colour(self, num_active_features, particle_density, particle_radiance, ray_origin, ray_direction, sensor: abi.GutCamera,
-                         ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad,
-                         out_density_grad, out_colour_grad, accumulate_density=False):
-        """gut_backward_colour: traceBwd with the SH expansion deferred.  Adds (or writes) the [N,12] gradient into
-        ``out_density_grad``, writes the view's masked colour gradient into ``out_colour_grad`` [N,3] and returns the
-        world-space view centre (3 floats) ``sh_gradient_expand`` needs for this view."""
+                         ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad, out_colour_grad):
+        """gut_backward_colour: traceBwd of one view of a deferred step.  Writes the view's masked colour gradient into
+        ``out_colour_grad`` [N,3], keeps summing the density-part accumulators inside the handle (``density_gradient_finish``
+        converts them once per step) and returns the world-space view centre (3 floats) ``sh_gradient_expand`` needs."""
         dev = self.device
         dens = _check_cuda_f32("particle_density", particle_density, dev)
         rad = _check_cuda_f32("particle_radiance", particle_radiance, dev)
@@ -276,15 +277,26 @@ class SplatRaster:
         height, width = ro.shape[1], ro.shape[2]
         if rgba_g.numel() != height * width * 4 or dist_g.numel() != height * width:
             raise GutError(abi.GutStatus.BAD_INPUT, "gradient shapes do not match the view")
-        if out_density_grad.shape != (n, 12) or out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
-            raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be [N,12], out_colour_grad a contiguous [N,3]")
+        if out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "out_colour_grad must be a contiguous [N,3]")
         centre = (C.c_float * 3)()
         rc = self.lib.gut_backward_colour(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
                                           width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
-                                          _ptr(out_density_grad), 1 if accumulate_density else 0, _ptr(out_colour_grad), centre)
+                                          _ptr(out_colour_grad), centre)
         if rc != 0:
             self._raise(rc)
         return [centre[0], centre[1], centre[2]]
+
+    def density_gradient_finish(self, particle_density, out_density_grad, accumulate=False):
+        """gut_density_gradient_finish: out_density_grad [N,12] (+)= the gradient of all views since the last finish."""
+        dens = _check_cuda_f32("particle_density", particle_density, self.device)
+        if out_density_grad.shape != (dens.shape[0], 12) or not out_density_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be a contiguous [N,12]")
+        rc = self.lib.gut_density_gradient_finish(self._h, self._stream(), dens.shape[0], _ptr(dens), _ptr(out_density_grad),
+                                                  1 if accumulate else 0)
+        if rc != 0:
+            self._raise(rc)
+        return out_density_grad
 
     def sh_gradient_expand(self, num_active_features, particle_density, view_centres, colour_grads, out_radiance_grad, accumulate=False):
         """gut_sh_gradient_expand: out_radiance_grad [N,48] (+)= sum over views of basis(direction) x colour gradient.

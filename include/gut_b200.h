@@ -189,16 +189,25 @@ GUT_API int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
                  int32_t accumulate);
 
 /*
- * Deferred SH gradient for multi-view steps (this build's extension).
- * dL/dSH of one view is basis(view direction) (x) dL/dcolour (gaussianParticles.cuh:120-187), i.e. 3 numbers per
- * particle and view expanded to 3 x 16.  gut_backward_colour is gut_backward without that expansion: it writes the
- * view's masked colour gradient d_colour_grad[N,3] (zero for particles the view did not touch) and the
- * world-space view centre it used (host float[3], may be NULL).  gut_sh_gradient_expand then forms
- *   d_particle_radiance_grad[N,48] (+)= sum_v basis(normalize(position - centre_v)) (x) colour_grad_v
- * for all views at once (d_colour_grads is [n_views, N, 3]; d_view_centres is a DEVICE array [n_views, 3], so the
- * centres of other ranks' views can arrive by the same all-gather as their colour gradients).
- * One step of V views therefore writes the 192-byte SH gradient row once instead of read-modify-writing it V times,
+ * Deferred gradients for multi-view steps (this build's extension).
+ * The backward of one view leaves two things per particle: 12 ray-summed canonical-frame accumulators that are linear
+ * and VIEW-INDEPENDENT (they become the [N,12] gradient through the particle's own rotation and scale only), and
+ * dL/dcolour, which the reference expands to dL/dSH = basis(view direction) (x) dL/dcolour
+ * (gaussianParticles.cuh:120-187): 3 numbers per particle and view blown up to 3 x 16.  So a step of V views can
+ * defer both conversions to its end:
+ *   gut_backward_colour          per view: compositing backward; writes the view's masked colour gradient
+ *                                d_colour_grad[N,3] (zero for particles the view did not touch) and the world-space
+ *                                view centre it used (host float[3], may be NULL); the density-part accumulators keep
+ *                                summing inside the handle;
+ *   gut_density_gradient_finish  once: d_particle_density_grad[N,12] (+)= conversion of the summed accumulators
+ *                                (which are reset);
+ *   gut_sh_gradient_expand       once: d_particle_radiance_grad[N,48] (+)= sum_v basis(normalize(position - centre_v))
+ *                                (x) colour_grad_v over all views (d_colour_grads is [n_views, N, 3]; d_view_centres
+ *                                is a DEVICE array [n_views, 3], so the centres of other ranks' views can arrive by
+ *                                the same all-gather as their colour gradients).
+ * One step therefore writes the 48-byte and 192-byte gradient rows once instead of read-modify-writing them V times,
  * and data-parallel ranks exchange 12 B per particle and view instead of 192 B per particle.
+ * gut_backward (the reference-shaped call) must not be interleaved between gut_backward_colour and the finish.
  */
 GUT_API int gut_backward_colour(GutHandle* h, void* stream, const GutCamera* camera,
                  uint32_t num_particles, int32_t sph_degree_active,
@@ -207,8 +216,9 @@ GUT_API int gut_backward_colour(GutHandle* h, void* stream, const GutCamera* cam
                  const float* d_ray_origin, const float* d_ray_direction,
                  const float* d_ray_radiance_density, const float* d_ray_radiance_density_grad,
                  const float* d_ray_hit_distance, const float* d_ray_hit_distance_grad,
-                 float* d_particle_density_grad, int32_t accumulate_density,
                  float* d_colour_grad, float* view_centre_out);
+GUT_API int gut_density_gradient_finish(GutHandle* h, void* stream, uint32_t num_particles,
+                 const float* d_particle_density, float* d_particle_density_grad, int32_t accumulate);
 GUT_API int gut_sh_gradient_expand(GutHandle* h, void* stream, uint32_t num_particles, int32_t sph_degree_active,
                  const float* d_particle_density, uint32_t n_views, const float* d_view_centres,
                  const float* d_colour_grads, float* d_particle_radiance_grad, int32_t accumulate);

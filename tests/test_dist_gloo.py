@@ -36,15 +36,15 @@ class FakeRaster:
 
     # deferred-SH variants (gut_backward_colour / gut_sh_gradient_expand): the stand-in's "SH gradient" of a view is
     # centre_x * colour gradient broadcast over the 48 columns, so that the expansion needs both gathered inputs
-    def trace_bwd_colour(self, deg, density, radiance, ray_o, ray_d, camera, rgba, rgba_grad, d, d_grad, out_density_grad,
-                         out_colour_grad, accumulate_density=False):
-        g1 = rgba_grad.sum() * density + d_grad.sum()
-        if accumulate_density:
-            out_density_grad += g1
-        else:
-            out_density_grad.copy_(g1)
+    def trace_bwd_colour(self, deg, density, radiance, ray_o, ray_d, camera, rgba, rgba_grad, d, d_grad, out_colour_grad):
+        self._pending = getattr(self, "_pending", 0) + (rgba_grad.sum() * density + d_grad.sum())
         out_colour_grad.copy_(rgba_grad.mean() * radiance[:, :3])
         return [float(ray_o.flatten()[0]) + 1.0, 0.0, 0.0]
+
+    def density_gradient_finish(self, density, out, accumulate=False):
+        out.copy_(getattr(self, "_pending", 0) + torch.zeros_like(out))
+        self._pending = 0
+        return out
 
     def sh_gradient_expand(self, deg, density, centres, colour_all, out, accumulate=False):
         val = (centres[:, 0].reshape(-1, 1, 1) * colour_all[:, :, :3]).sum(0)          # [N,3]
