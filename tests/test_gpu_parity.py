@@ -106,6 +106,43 @@ def test_backward_gradients(pkg, name, n, w, h, deg, kind, seed):
     assert e <= TOL_GRAD, (name, "sph", e)
 
 
+@pytest.mark.parametrize("K", [0, 8])
+def test_rays_not_starting_at_the_frame_origin(pkg, K):
+    """Ray bundles whose origins differ per pixel (e.g. an orthographic or multi-sensor rig) take the kernels' non-uniform
+    path: the canonical origin is corrected per ray (gut_render.cu particle_test<.., UNIFORM=false>).  Forward and backward
+    against the oracle, for the unsorted and the sorted compositing."""
+    n, w, h, deg, seed = 4000, 80, 56, 2, 33
+    scene = syn.make_scene(n, 3, seed=seed, kind="init")
+    view = syn.make_view(w, h)
+    g = torch.Generator().manual_seed(seed)
+    view["rays_ori"] = view["rays_ori"] + (torch.rand(view["rays_ori"].shape, generator=g) - 0.5) * 0.2   # camera-space offsets
+    cfg = abi.default_config(); cfg.k_buffer_size = K
+    rng = np.random.default_rng(seed)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    ref0 = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg)
+    border = ref0["borderline"]
+    rgba_grad[border] = 0; dist_grad[border] = 0
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg, rgba_grad=rgba_grad, dist_grad=dist_grad)
+    raster = _raster(pkg, k_buffer_size=K)
+    (rgba, dist, hits, vis), (d12, sph, cam) = _run_forward(raster, scene, view, deg, stage=False)
+    stats = compare_images(rgba.cpu().numpy(), ref["rgba"], border)
+    assert stats["max_abs_clean"] <= TOL_IMG, stats
+    assert stats["borderline_fraction"] < 0.08, stats
+    clean = ~border
+    assert np.abs(dist.cpu().numpy().reshape(h, w) - ref["dist"])[clean].max() <= TOL_IMG * max(1.0, float(np.abs(ref["dist"]).max()))
+    assert np.array_equal(hits.cpu().numpy().reshape(h, w)[clean], ref["hits"][clean])
+    rgba_o = torch.from_numpy(ref["rgba"]).cuda(); dist_o = torch.from_numpy(ref["dist"]).cuda().reshape(h, w, 1)
+    g12, gsph = raster.trace_bwd(0, deg, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba_o, torch.from_numpy(rgba_grad).cuda(), dist_o, torch.from_numpy(dist_grad).cuda().reshape(h, w, 1))
+    torch.cuda.synchronize()
+    g12 = g12.cpu().numpy()
+    for lo, hi, what in ((0, 3, "position"), (3, 4, "density"), (4, 8, "rotation"), (8, 11, "scale")):
+        e = rel_l2(g12[:, lo:hi], ref["density_grad"][:, lo:hi])
+        assert e <= TOL_GRAD, (K, what, e)
+    assert rel_l2(gsph.cpu().numpy(), ref["radiance_grad"]) <= TOL_GRAD
+
+
 KB_CASES = [
     # name, N, W, H, sph_degree, kind, seed, K
     ("sorted_k16_init", 6000, 150, 70, 3, "init", 5, 16),
