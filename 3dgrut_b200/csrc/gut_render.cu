@@ -438,7 +438,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(RENDER_THREADS, 16) gut_render_backward_kernel(
+__global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
