@@ -42,13 +42,15 @@ struct GutHandle {
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
-    DevBuf entries, scratch, sorted_idx;
+    DevBuf entries, scratch, sorted_idx, hit_masks;
     // host-buffer mode (gut_*_host)
     DevBuf h_ray_ori, h_ray_dir, h_rgba, h_dist, h_hits, h_rgba_grad, h_dist_grad;
     uint32_t* pinned_stats = nullptr;  // [2] = {M, max tile list}
 
     // forward context consumed by backward
     bool fwd_valid = false;
+    bool training = true;           // forward records the hit masks the backward walks (gut_set_training)
+    bool fwd_masks = false;         // the last forward recorded them
     bool pending_density = false;   // gut_backward_colour left view-summed accumulators for gut_density_gradient_finish
     cudaStream_t fwd_stream = nullptr;
     uint32_t fwd_N = 0, fwd_W = 0, fwd_H = 0;
@@ -272,7 +274,7 @@ void gut_destroy(GutHandle* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->raw_grad, &h->tile_hist,
-                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx,
+                     &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->hit_masks,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
     if (h->pinned_stats) cudaFreeHost(h->pinned_stats);
@@ -359,8 +361,16 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
                 GUT_CUDA(h, gut_launch_render_kbuffer(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
                                                       d_rgba, d_dist, d_hits, s));
             else
+            {
+                uint32_t* masks = nullptr;
+                if (h->training) {
+                    GUT_CUDA(h, ensure(h->hit_masks, gut_hit_mask_words(M, fr.num_tiles) * 4, s));
+                    masks = (uint32_t*)h->hit_masks.p;
+                }
+                h->fwd_masks = masks != nullptr;
                 GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
-                                              d_rgba, d_dist, d_hits, nullptr, s));
+                                              d_rgba, d_dist, d_hits, nullptr, masks, s));
+            }
             h->launches += 1;
         }
     }
@@ -403,6 +413,8 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
     if (!h->fwd_valid || h->fwd_stream != s)
         return fail(h, GUT_ERR_NO_FORWARD, "cannot render backward: no forward context on this stream (reference: gutRenderer.cu:413-417)");
     if (h->fwd_N != N || h->fwd_W != W || h->fwd_H != H) return fail(h, GUT_ERR_NO_FORWARD, "backward shapes differ from the preceding forward");
+    if (h->fwd_M > 0 && h->cfg.k_buffer_size == 0 && !h->fwd_masks)
+        return fail(h, GUT_ERR_NO_FORWARD, "the preceding forward ran in inference mode (gut_set_training(h, 0)): no hit masks for the backward");
     if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_rgba_grad || !d_dist || !d_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null ray/gradient pointer");
     if (N > 0 && (!d_density || (!d_density_grad && !d_colour_grad) || (!d_radiance_grad && !d_colour_grad))) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
     if (!d_colour_grad && h->pending_density)
@@ -425,7 +437,7 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
                                                            d_rgba_grad, d_dist, d_dist_grad, (float*)h->raw_grad.p, s));
         else
             GUT_CUDA(h, gut_launch_render_backward(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist, d_dist_grad,
-                                                   (float*)h->raw_grad.p, s));
+                                                   (float*)h->raw_grad.p, (const uint32_t*)h->hit_masks.p, s));
         h->launches += 1;
     }
     {
@@ -477,6 +489,12 @@ int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const f
                                             nullptr, nullptr, accumulate, s));
     h->launches += 1;
     h->pending_density = false;
+    return GUT_OK;
+}
+
+int gut_set_training(GutHandle* h, int32_t training) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    h->training = training != 0;
     return GUT_OK;
 }
 
@@ -584,7 +602,7 @@ int gut_measure_work(GutHandle* h, void* stream_, const float* d_ray_ori, const 
     GUT_CUDA(h, cudaMemsetAsync(h->stats.p, 0, 16, s));
     const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)h->fwd_density, (const float4*)h->features.p};
     GUT_CUDA(h, gut_launch_render(h->cfg, h->fwd_frame, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
-                                  nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, s));
+                                  nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, nullptr, s));
     unsigned long long host[2] = {0, 0};
     GUT_CUDA(h, cudaMemcpyAsync(host, h->stats.p, 16, cudaMemcpyDeviceToHost, s));
     GUT_CUDA(h, cudaStreamSynchronize(s));

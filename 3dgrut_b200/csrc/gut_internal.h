@@ -91,12 +91,15 @@ cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_s
 
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              unsigned long long* counters /* non-null: count tests/hits instead of rendering */, cudaStream_t stream);
+                              unsigned long long* counters /* non-null: count tests/hits instead of rendering */,
+                              uint32_t* hit_masks /* nullable: per (block, batch) masks of accepted entries for the backward */, cudaStream_t stream);
+size_t gut_hit_mask_words(uint64_t num_intersections, uint32_t num_tiles);
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
                                        GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
-                                       float* raw_grad /* [N,16] accumulators, see gut_render.cu backward_walk */, cudaStream_t stream);
+                                       float* raw_grad /* [N,16] accumulators, see gut_render.cu backward_walk */,
+                                       const uint32_t* hit_masks /* written by the forward */, cudaStream_t stream);
 
 // k_buffer_size > 0 (sorted compositing, gut_render_kbuffer.cu): same arguments as the two launchers above
 bool gut_kbuffer_size_supported(int k);

@@ -156,8 +156,11 @@ struct FwdState {
     bool alive[2];
 };
 
+// Returns, as a bit per record of the batch, which records one of this lane's two rays accepted while alive (before the
+// tMinMax test): the union over the warp is what the backward has to revisit (hit_mask_slot below).
 template <int DEG, bool UNIFORM, bool COUNT>
-GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const RayPair& ray, FwdState& st) {
+GUT_D uint32_t forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const RayPair& ray, FwdState& st) {
+    uint32_t accepted = 0;
     const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
     for (uint32_t j0 = 0; j0 < cnt_pad; j0 += ALIVE_CHECK) {
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
@@ -181,6 +184,7 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
                     if (COUNT && (j + q + p) < cnt) { st.ntests[0] += st.alive[0]; st.ntests[1] += st.alive[1]; }
                     const bool h0 = acc[p][0] && st.alive[0], h1 = acc[p][1] && st.alive[1];
                     if (h0 || h1) {
+                        accepted |= 1u << (j + q + p);
                         // hit distance |s * grd * dot(grd, -go)| with grd = u / |u|  (canonicalRayDistance, gaussianParticles.slang:165-171)
                         F2x3 su;
                         su.x = bc(S[p].x) * k[p].u.x; su.y = bc(S[p].y) * k[p].u.y; su.z = bc(S[p].z) * k[p].u.z;
@@ -205,6 +209,16 @@ GUT_D void forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, ui
             }
         }
     }
+    return accepted;
+}
+
+// The forward leaves one 32-bit mask per (8x8 block, batch of 32 list entries): bit j set = some ray of the block accepted
+// entry j while alive.  The backward walks only those entries (41 % of a block's tests find no hit at the bench
+// workload).  The mask is a superset of what the backward accepts: its rays die no later than the forward's (it
+// composites the forward's hits plus those the forward's tMinMax test dropped), and it re-tests every revisited entry.
+// Slot of batch b of a tile whose list starts at b0: (b0 / 32 + tile + b) is unique across tiles.
+GUT_D size_t hit_mask_slot(uint32_t b0, uint32_t tile, uint32_t b, uint32_t block) {
+    return ((size_t)(b0 >> 5) + tile + b) * BLOCKS_PER_TILE + block;
 }
 
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
@@ -214,7 +228,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_kernel(GutConfi
                                                                      GutParticleSource src,
                                                                      const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                      float4* __restrict__ rgba, float* __restrict__ dist,
-                                                                     float* __restrict__ hits, unsigned long long* __restrict__ counters) {
+                                                                     float* __restrict__ hits, unsigned long long* __restrict__ counters,
+                                                                     uint32_t* __restrict__ hit_masks /* nullable: inference */) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
 
     const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
@@ -232,8 +247,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_kernel(GutConfi
     for (int h = 0; h < 2; ++h) { st.nhits[h] = 0; st.ntests[h] = 0; st.alive[h] = ray.inside[h] && ray.valid[h]; }
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
-        if (uniform) forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
-        else forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
+        const uint32_t accepted = uniform ? forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, st)
+                                          : forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
+        if (!COUNT && hit_masks) {
+            const uint32_t m = __reduce_or_sync(0xffffffffu, accepted);
+            if ((threadIdx.x & 31) == 0) hit_masks[hit_mask_slot(b0, tile, b, block)] = m;
+        }
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;   // the block saturated early
         stg.rotate();
     }
@@ -321,21 +340,20 @@ struct BwdRay {
 // A ray of the lane that does not take the hit runs the same packed instructions with alpha = 0 and a zeroed
 // upstream sum: every one of its 15 values is then exactly 0 and its state is unchanged.
 template <int DEG, bool UNIFORM>
-GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t cnt,
+GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t mask,
                          const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
     const float minT = cfg.min_transmittance;
     const F2 one = bc(1.0f);
-    for (uint32_t j0 = 0; j0 < cnt; j0 += ALIVE_CHECK) {
-      if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
-      const uint32_t je = min(cnt, j0 + ALIVE_CHECK);
-      for (uint32_t j = j0; j < je; ++j) {
+    while (mask) {
+      {
+        const uint32_t j = __ffs(mask) - 1;
+        mask &= mask - 1;
         const float4* r = rec + 5 * j;
         const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
         Canon2 k;
         bool acc0, acc1;
         particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
         const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];  // no tMinMax test here
-        if (!__any_sync(0xffffffffu, h0 || h1)) continue;
 
         // every lane runs the hit math (rays that do not take the hit are masked, see above): no lane-level branch
         F2 v[16];
@@ -442,7 +460,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_backward_kernel
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
-    const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
+    const float* __restrict__ dist_grad, float* __restrict__ raw_grad, const uint32_t* __restrict__ hit_masks) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<true>::TOTAL];
 
     const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
@@ -481,8 +499,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_backward_kernel
 
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
-        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
-        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, stg.count(b), ray, st, lane, raw_grad);
+        const uint32_t mask = __ldg(hit_masks + hit_mask_slot(b0, tile, b, block));   // entries some ray of the block accepted in the forward
+        if (uniform) backward_walk<DEG, true>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad);
+        else backward_walk<DEG, false>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad);
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
         stg.rotate();
     }
@@ -492,14 +511,14 @@ __global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_backward_kernel
 template <int DEG>
 cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              unsigned long long* counters, cudaStream_t stream) {
+                              unsigned long long* counters, uint32_t* hit_masks, cudaStream_t stream) {
     const uint32_t grid = frame.num_tiles * BLOCKS_PER_TILE;
     if (counters)
         gut_render_kernel<DEG, true><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
-                                                                       nullptr, counters);
+                                                                       nullptr, counters, nullptr);
     else
         gut_render_kernel<DEG, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
-                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr);
+                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks);
     return cudaGetLastError();
 }
 
@@ -507,10 +526,10 @@ template <int DEG>
 cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                                   const float* ray_ori, const float* ray_dir, const float* rgba,
                                   const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
-                                  cudaStream_t stream) {
+                                  const uint32_t* hit_masks, cudaStream_t stream) {
     gut_render_backward_kernel<DEG><<<frame.num_tiles * BLOCKS_PER_TILE, RENDER_THREADS, 0, stream>>>(
         cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
-        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad);
+        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
     return cudaGetLastError();
 }
 
@@ -530,8 +549,8 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
 
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              unsigned long long* counters, cudaStream_t stream) {
-#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, counters, stream)
+                              unsigned long long* counters, uint32_t* hit_masks, cudaStream_t stream) {
+#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, counters, hit_masks, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_FWD)
 #undef CALL_FWD
 }
@@ -539,9 +558,13 @@ cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,
                                        GutParticleSource src, const float* ray_ori, const float* ray_dir,
                                        const float* rgba, const float* rgba_grad, const float* dist, const float* dist_grad,
-                                       float* raw_grad, cudaStream_t stream) {
+                                       float* raw_grad, const uint32_t* hit_masks, cudaStream_t stream) {
 #define CALL_BWD(D) \
-    launch_render_bwd_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, raw_grad, stream)
+    launch_render_bwd_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, raw_grad, hit_masks, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_BWD)
 #undef CALL_BWD
+}
+
+size_t gut_hit_mask_words(uint64_t num_intersections, uint32_t num_tiles) {
+    return ((size_t)(num_intersections >> 5) + num_tiles + 2) * BLOCKS_PER_TILE;
 }

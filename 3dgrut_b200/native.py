@@ -65,6 +65,8 @@ def load_library():
     lib.gut_backward_colour.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp,
                                         C.POINTER(C.c_float)]
     lib.gut_backward_colour.restype = C.c_int
+    lib.gut_set_training.argtypes = [vp, i32]
+    lib.gut_set_training.restype = C.c_int
     lib.gut_density_gradient_finish.argtypes = [vp, vp, u32, fp, fp, i32]
     lib.gut_density_gradient_finish.restype = C.c_int
     lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
@@ -314,6 +316,10 @@ class SplatRaster:
         if rc != 0:
             self._raise(rc)
         return out_radiance_grad
+
+    def set_training(self, training: bool):
+        """gut_set_training: training=False skips the hit-mask recording of the forward (inference); no backward may follow."""
+        self.lib.gut_set_training(self._h, 1 if training else 0)
 
     def collect_times(self):
         """reference: SplatRaster::collectTimes (splatRaster.cpp:334-364) -> {tag: mean ms}."""

@@ -118,6 +118,8 @@ class Tracer:
         rays_d = gpu_batch.rays_dir
         sensor = camera_from_batch(gpu_batch)
         num_gaussians = gaussians.num_gaussians
+        # under torch.no_grad() (validation / rendering) no backward can follow: skip the forward's hit-mask recording
+        self.tracer_wrapper.set_training(torch.is_grad_enabled())
         with torch.cuda.nvtx.range(f"model.forward({num_gaussians} gaussians)"):
             pred_rgba, pred_dist, hits_count, mog_visibility = Tracer._Autograd.apply(
                 self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),

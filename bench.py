@@ -440,6 +440,7 @@ def run_ours(args):
     if rank == 0 and not args.no_aux:
         hv = syn.make_view(1920, 1080, k=0, n_views=args.views)
         ro, rd, cam = hv["rays_ori"].to(dev), hv["rays_dir"].to(dev), camera_of(hv)
+        raster.set_training(False)   # inference: no backward follows (Tracer.render does this under torch.no_grad())
         for _ in range(3):
             raster.trace(0, SPH_DEGREE, d12, sph, ro, rd, None, cam)
         torch.cuda.synchronize()
@@ -452,6 +453,7 @@ def run_ours(args):
         torch.cuda.synchronize()
         ms = a0.elapsed_time(a1) / reps
         fwd_1080p = {"fps": 1e3 / ms, "ms_per_frame": ms, "particles": n, "intersections_M": raster.frame_stats()["num_intersections"]}
+        raster.set_training(True)
 
     # ---- auxiliary: the "sorted" configuration (k_buffer_size = 16, configs/paper/3dgut/base_sorted.yaml; SURVEY 8d's second
     # config): forward + backward of ONE view of the same workload, device resident ---------------------------------------

@@ -189,6 +189,14 @@ GUT_API int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
                  int32_t accumulate);
 
 /*
+ * training != 0 (the default): gut_forward also records, per 8x8 pixel block and batch of 32 list entries, which entries
+ * some ray accepted; gut_backward revisits only those (the reference re-tests the whole list).  training == 0 skips the
+ * recording for inference (Tracer.render(train=False)); a gut_backward after such a forward fails with
+ * GUT_ERR_NO_FORWARD.
+ */
+GUT_API int gut_set_training(GutHandle* h, int32_t training);
+
+/*
  * Deferred gradients for multi-view steps (this build's extension).
  * The backward of one view leaves two things per particle: 12 ray-summed canonical-frame accumulators that are linear
  * and VIEW-INDEPENDENT (they become the [N,12] gradient through the particle's own rotation and scale only), and

@@ -270,3 +270,17 @@ def test_empty_and_error_paths(pkg):
                         rgba, torch.ones_like(rgba), dist, torch.ones_like(dist))
     with pytest.raises(native.GutError):
         raster.trace(0, 3, d12[:, :11].contiguous(), sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam)
+    # a forward in inference mode records no hit masks: the backward refuses instead of walking stale ones
+    scene2 = syn.make_scene(500, 3, seed=2)
+    d12b = syn.pack_density(scene2).cuda(); sphb = scene2["features"].cuda()
+    raster.set_training(False)
+    rgba_i, dist_i, _, _ = raster.trace(0, 3, d12b, sphb, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam)
+    assert raster.frame_stats()["num_intersections"] > 0
+    with pytest.raises(native.GutError):
+        raster.trace_bwd(0, 3, d12b, sphb, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                         rgba_i, torch.ones_like(rgba_i), dist_i, torch.ones_like(dist_i))
+    raster.set_training(True)
+    rgba_t, dist_t, _, _ = raster.trace(0, 3, d12b, sphb, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam)
+    assert torch.equal(rgba_t, rgba_i) and torch.equal(dist_t, dist_i)   # recording does not change the image
+    raster.trace_bwd(0, 3, d12b, sphb, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                     rgba_t, torch.ones_like(rgba_t), dist_t, torch.ones_like(dist_t))
