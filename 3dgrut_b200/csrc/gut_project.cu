@@ -313,16 +313,21 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
     float b[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) b[k] = 0.0f;
-    if (i < N) touched = tiles_count ? tiles_count[i] != 0 : true;
-    if (touched) {
+    // All loads are issued before tiles_count is known (an untouched particle has zero accumulators, so computing on it is
+    // harmless): the kernel is bound by the latency of its load -> store chains, and a dependent first load doubles them.
+    if (i < N) {
+        touched = tiles_count ? tiles_count[i] != 0 : true;
         const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos, density
         float4* rg = raw_grad + 4 * (size_t)i;
         float4 g0, g1, g2 = rg[2], g3 = rg[3];
         const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        if (DENSITY) { g0 = rg[0]; g1 = rg[1]; rg[0] = z; rg[1] = z; }
-        if (DENSITY && COLOUR) { rg[2] = z; rg[3] = z; }
-        else if (DENSITY) { rg[2] = make_float4(0.0f, 0.0f, 0.0f, g2.w); rg[3] = make_float4(g3.x, g3.y, 0.0f, 0.0f); }
-        else { rg[2] = make_float4(g2.x, g2.y, g2.z, 0.0f); rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w); }
+        if (DENSITY) { g0 = rg[0]; g1 = rg[1]; }
+        if (touched) {
+            if (DENSITY) { rg[0] = z; rg[1] = z; }
+            if (DENSITY && COLOUR) { rg[2] = z; rg[3] = z; }
+            else if (DENSITY) { rg[2] = make_float4(0.0f, 0.0f, 0.0f, g2.w); rg[3] = make_float4(g3.x, g3.y, 0.0f, 0.0f); }
+            else { rg[2] = make_float4(g2.x, g2.y, g2.z, 0.0f); rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w); }
+        }
         if (DENSITY) {
         const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
         const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
