@@ -94,12 +94,14 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
                                                        uint32_t* __restrict__ tile_cursor, uint2* __restrict__ entries, uint32_t capacity) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
-    if (proj.tiles_count[i] == 0) return;
+    // all loads in flight at once: three dependent rounds (count -> extent -> rest) would triple the memory latency the
+    // kernel sits on before its atomics start
+    const uint32_t count = proj.tiles_count[i];
     const float2 ext = proj.extent[i];
-    if (ext.x <= 1e-06f) return;
     const uint32_t depth_bits = __float_as_uint(proj.depth[i]);
     const float2 centre = proj.proj_pos[i];
     const float4 co = proj.conic_opacity[i];
+    if (count == 0 || ext.x <= 1e-06f) return;
     const float max_power = gut_logf(co.w / cfg.min_alpha);
     const GutTileBox bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, ext);
     // The bucket slot comes back from an L2 atomic (~1 us under contention).  Walking the box EMIT_ILP tiles at a time
