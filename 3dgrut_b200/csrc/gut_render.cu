@@ -224,7 +224,7 @@ GUT_D size_t hit_mask_slot(uint32_t b0, uint32_t tile, uint32_t b, uint32_t bloc
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+__global__ void __launch_bounds__(RENDER_THREADS, 25) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                      GutParticleSource src,
                                                                      const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                      float4* __restrict__ rgba, float* __restrict__ dist,
