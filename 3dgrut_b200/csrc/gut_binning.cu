@@ -209,18 +209,19 @@ __device__ void radix_pass(const uint32_t* src_k, const uint32_t* src_v, uint32_
 }
 
 template <int THREADS, uint32_t CAP>
-__global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uint32_t N, const uint32_t* __restrict__ tile_start,
-                                                                uint2* __restrict__ entries, uint2* __restrict__ scratch,
-                                                                uint32_t n_min, uint32_t n_max,
-                                                                uint32_t* __restrict__ sorted_idx) {
+__global__ void __launch_bounds__(THREADS) gut_tile_radix_sort_kernel(GutFrame fr, const uint32_t* __restrict__ tile_start,
+                                                                      uint2* __restrict__ entries, uint2* __restrict__ scratch,
+                                                                      const uint32_t* __restrict__ tile_flags,
+                                                                      uint32_t* __restrict__ sorted_idx) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ SortShared<THREADS / 32> sh;
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
 
-    const uint32_t tile = blockIdx.x;
+    // persistent: the launch is idle for ordinary frames (no flagged bucket, none above CAP), so it must cost next to nothing
+    for (uint32_t tile = blockIdx.x; tile < fr.num_tiles; tile += gridDim.x) {
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     const uint32_t n = b1 - b0;
-    if (n == 0 || n < n_min || n > n_max) return;   // this launch handles buckets of n_min..n_max entries
-    const uint32_t tid = threadIdx.x, lane = tid & 31;
+    if (n == 0 || !(n > CAP || tile_flags[tile])) continue;   // block-uniform
 
     // shared-memory layout: [key A | val A | key B | val B], CAP entries each; buckets above CAP sort in global memory
     // (keys and values de-interleaved in place over `entries` / `scratch`, which hold 2 x n words each).
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uin
     uint32_t* kb = in_smem ? va + CAP : reinterpret_cast<uint32_t*>(entries + b0);
     uint32_t* vb = kb + (in_smem ? CAP : n);
 
+    __syncthreads();   // previous tile of this CTA is done with the shared buffers
     if (tid == 0) { sh.or_bits = 0; sh.and_bits = 0xffffffffu; sh.ties = 0; }
     __syncthreads();
     {
@@ -274,6 +276,124 @@ __global__ void __launch_bounds__(THREADS) gut_tile_sort_kernel(GutFrame fr, uin
 
     // sorted particle list of the tile (the compositing kernels gather the parameters themselves)
     for (uint32_t i = tid; i < n; i += THREADS) sorted_idx[b0 + i] = va[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Per-tile sort, common path: ONE counting pass instead of 3-4 radix passes.
+//
+// The bucket's depth keys are binned monotonically on their value range, bin = (key - min) >> shift with BINS >= the
+// bucket size, so the typical bin holds zero to a few entries.  Every thread keeps its EPT entries in registers:
+//   load (+ min/max)  ->  bin count with shared atomics (the returned old value is the entry's slot in its bin)
+//   ->  exclusive scan of the bins  ->  scatter into shared memory (bins in order, entries of a bin in arrival order)
+//   ->  every entry ranks itself inside its bin by counting the bin's smaller (depth, particle) pairs and stores its
+//       particle index at bin start + rank of the sorted list in global memory (neighbouring threads write neighbouring
+//       words).
+// (depth, particle) is a strict total order, so the result does not depend on the order the emit atomics filled the
+// bucket in, and equal depths come out in ascending particle order like the reference's stable sort leaves them.
+// Ranking costs sum(bin size^2): a bucket with a bin above BIN_LIMIT (depths piled up on a few values with outliers
+// stretching the range) is flagged and left to the radix kernel below, whose cost does not depend on the distribution.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t BIN_LIMIT = 256;
+
+template <int THREADS, uint32_t CAP, uint32_t LOG_BINS>
+__global__ void __launch_bounds__(THREADS) gut_tile_bin_sort_kernel(const uint32_t* __restrict__ tile_start, const uint2* __restrict__ entries,
+                                                                    uint32_t n_min, uint32_t n_max, uint32_t* __restrict__ sorted_idx,
+                                                                    uint32_t* __restrict__ tile_flags) {
+    constexpr uint32_t BINS = 1u << LOG_BINS;
+    constexpr int EPT = CAP / THREADS;        // entries per thread
+    constexpr int BPT = BINS / THREADS;       // bins per thread in the scan
+    constexpr int WARPS = THREADS / 32;
+    static_assert(CAP % THREADS == 0 && BINS % THREADS == 0 && BPT % 4 == 0, "tiling");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint2* sorted = reinterpret_cast<uint2*>(smem_raw);                    // [CAP]
+    uint32_t* bins = reinterpret_cast<uint32_t*>(sorted + CAP);            // [BINS + 4]: counts, then exclusive starts (+ total)
+    __shared__ uint32_t s_min, s_max, s_big, s_wsum[WARPS];
+
+    const uint32_t tile = blockIdx.x;
+    const uint32_t b0 = tile_start[tile], n = tile_start[tile + 1] - b0;
+    if (n < n_min || n > n_max) return;       // this launch handles buckets of n_min..n_max entries (n_min >= 1)
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+    uint2 ent[EPT];
+    uint32_t kmin = 0xffffffffu, kmax = 0u;
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) {
+        const uint32_t i = tid + e * THREADS;
+        ent[e] = make_uint2(0u, 0u);
+        if (i < n) {
+            ent[e] = __ldg(entries + b0 + i);
+            kmin = min(kmin, ent[e].x); kmax = max(kmax, ent[e].x);
+        }
+    }
+    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_big = 0u; }
+#pragma unroll
+    for (int k = 0; k < BPT / 4; ++k) reinterpret_cast<uint4*>(bins)[tid + k * THREADS] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    kmin = __reduce_min_sync(0xffffffffu, kmin); kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if (lane == 0) { atomicMin(&s_min, kmin); atomicMax(&s_max, kmax); }
+    __syncthreads();
+    kmin = s_min;
+    const uint32_t range_bits = 32u - __clz(s_max - kmin);                 // 0 when every key is the same
+    const uint32_t shift = range_bits > LOG_BINS ? range_bits - LOG_BINS : 0u;
+
+    uint32_t slot[EPT];
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) {
+        slot[e] = 0;
+        if (tid + e * THREADS < n) slot[e] = atomicAdd(&bins[(ent[e].x - kmin) >> shift], 1u);
+    }
+    __syncthreads();
+
+    // exclusive scan of the bin counts, BPT consecutive bins per thread
+    {
+        uint32_t c[BPT], sum = 0, big = 0;
+#pragma unroll
+        for (int k = 0; k < BPT / 4; ++k) {
+            const uint4 q = reinterpret_cast<const uint4*>(bins)[tid * (BPT / 4) + k];
+            c[4 * k] = q.x; c[4 * k + 1] = q.y; c[4 * k + 2] = q.z; c[4 * k + 3] = q.w;
+        }
+#pragma unroll
+        for (int k = 0; k < BPT; ++k) { sum += c[k]; big = max(big, c[k]); }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += v;
+        }
+        if (lane == 31) s_wsum[wid] = incl;
+        if (big > BIN_LIMIT) s_big = 1u;
+        __syncthreads();
+        uint32_t run = incl - sum;
+        for (uint32_t w = 0; w < wid; ++w) run += s_wsum[w];
+#pragma unroll
+        for (int k = 0; k < BPT; ++k) { const uint32_t t = c[k]; c[k] = run; run += t; }
+#pragma unroll
+        for (int k = 0; k < BPT / 4; ++k)
+            reinterpret_cast<uint4*>(bins)[tid * (BPT / 4) + k] = make_uint4(c[4 * k], c[4 * k + 1], c[4 * k + 2], c[4 * k + 3]);
+        if (tid == THREADS - 1) bins[BINS] = run;                          // = n
+    }
+    const bool big = s_big != 0u;
+    if (tid == 0) tile_flags[tile] = big ? 1u : 0u;
+    if (big) return;                                                       // block-uniform: the radix kernel sorts this bucket
+    __syncthreads();
+
+#pragma unroll
+    for (int e = 0; e < EPT; ++e)
+        if (tid + e * THREADS < n) sorted[bins[(ent[e].x - kmin) >> shift] + slot[e]] = ent[e];
+    __syncthreads();
+
+    for (uint32_t i = tid; i < n; i += THREADS) {
+        const uint2 me = sorted[i];
+        const uint32_t b = (me.x - kmin) >> shift;
+        const uint32_t s0 = bins[b], s1 = bins[b + 1];
+        uint32_t rank = 0;
+        for (uint32_t j = s0; j < s1; ++j) {
+            const uint2 o = sorted[j];
+            rank += (o.x < me.x || (o.x == me.x && o.y < me.y)) ? 1u : 0u;
+        }
+        sorted_idx[b0 + s0 + rank] = me.y;
+    }
 }
 
 // reference-shaped debug outputs: sorted u64 keys (tile<<32 | depth bits) and uvec2 tile ranges ((0,0) for empty tiles,
@@ -315,23 +435,37 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 }
 
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries,
-                                 uint2* scratch, uint32_t* sorted_idx, cudaStream_t stream) {
-    // small buckets: 256 threads, 4096-entry shared buffers (64 KB -> 3 CTAs per SM);
-    // large buckets: 512 threads, 12288-entry buffers (192 KB, one CTA per SM); above that the passes run over global memory.
-    constexpr uint32_t CAP_S = 4096, CAP_L = 12288;
-    const size_t smem_s = 4 * CAP_S * sizeof(uint32_t), smem_l = 4 * CAP_L * sizeof(uint32_t);
+                                 uint2* scratch, uint32_t* tile_flags, uint32_t* sorted_idx, cudaStream_t stream) {
+    // buckets up to 4096 entries: 256 threads, 4096 bins (48 KB -> 4 CTAs per SM); up to 12288: 512 threads, 16384 bins (160 KB);
+    // flagged buckets and buckets above 12288 entries: radix passes (in 192 KB of shared memory / over global memory).
+    (void)N;
+    constexpr uint32_t CAP_S = 4096, CAP_L = 12288, LOG_BINS_S = 12, LOG_BINS_L = 14;
+    const size_t smem_s = CAP_S * sizeof(uint2) + ((1u << LOG_BINS_S) + 4) * sizeof(uint32_t);
+    const size_t smem_l = CAP_L * sizeof(uint2) + ((1u << LOG_BINS_L) + 4) * sizeof(uint32_t);
+    const size_t smem_r = 4 * CAP_L * sizeof(uint32_t);
     static bool configured = false;
+    static int radix_grid = 0;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gut_tile_sort_kernel<256, CAP_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
+        cudaError_t e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<256, CAP_S, LOG_BINS_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(gut_tile_sort_kernel<512, CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
+        e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(gut_tile_radix_sort_kernel<512, CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r);
+        if (e != cudaSuccess) return e;
+        int dev = 0, sms = 0;
+        e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        radix_grid = sms;
         configured = true;
     }
-    gut_tile_sort_kernel<256, CAP_S><<<frame.num_tiles, 256, smem_s, stream>>>(frame, N, tile_start, entries, scratch, 1u, CAP_S, sorted_idx);
+    gut_tile_bin_sort_kernel<256, CAP_S, LOG_BINS_S><<<frame.num_tiles, 256, smem_s, stream>>>(tile_start, entries, 1u, CAP_S, sorted_idx, tile_flags);
     if (max_list > CAP_S)
-        gut_tile_sort_kernel<512, CAP_L><<<frame.num_tiles, 512, smem_l, stream>>>(frame, N, tile_start, entries, scratch, CAP_S + 1u, 0xffffffffu,
-                                                                                  sorted_idx);
+        gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L><<<frame.num_tiles, 512, smem_l, stream>>>(tile_start, entries, CAP_S + 1u, CAP_L, sorted_idx,
+                                                                                               tile_flags);
+    const uint32_t grid = frame.num_tiles < (uint32_t)radix_grid ? frame.num_tiles : (uint32_t)radix_grid;
+    gut_tile_radix_sort_kernel<512, CAP_L><<<grid, 512, smem_r, stream>>>(frame, tile_start, entries, scratch, tile_flags, sorted_idx);
     return cudaGetLastError();
 }
 
