@@ -119,3 +119,61 @@ def test_backward_properties(name):
     torch.cuda.synchronize()
     assert rel_l2(acc12.cpu().numpy(), (2.0 * g12).cpu().numpy()) <= 1e-4
     assert rel_l2(accsph.cpu().numpy(), (2.0 * gsph).cpu().numpy()) <= 1e-4
+
+
+def _lexicographic(st):
+    m = int(st["num_intersections"])
+    keys = st["sorted_keys"].view(torch.int64)[:m]
+    idx = st["sorted_particle_idx"].view(torch.int32).long()[:m]
+    up = keys[1:] > keys[:-1]
+    tie = (keys[1:] == keys[:-1]) & (idx[1:] > idx[:-1])
+    return bool((up | tie).all()), m, idx
+
+
+SORT_CASES = {
+    # bucket sizes per 16x16 tile of a 64x64 view: the three code paths of the per-tile sort
+    "buckets_up_to_4096": dict(n=12_000, piled=False),
+    "buckets_up_to_12288": dict(n=50_000, piled=False),
+    "buckets_above_12288": dict(n=400_000, piled=False),
+    # depths piled up on a few neighbouring float values plus outliers: the counting sort hands the bucket to the radix sort
+    "piled_depths": dict(n=30_000, piled=True),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SORT_CASES))
+def test_sort_paths(name):
+    c = SORT_CASES[name]
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = native.SplatRaster(cfg_from_conf(make_conf()))
+    n, w, h = c["n"], 64, 64
+    scene = syn.make_scene(n, 3, seed=77, kind="init")
+    view = syn.make_view(w, h)
+    if c["piled"]:
+        c2w = view["T_to_world"][0]
+        right, down, fwd, eye = c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3]
+        g = torch.Generator().manual_seed(5)
+        z = 3.0 + (torch.arange(n) % 61).float() * 2.4e-7          # a few dozen neighbouring floats -> ties and near ties
+        far = torch.rand(n, generator=g) < 0.02
+        z[far] = 0.5 + 20.0 * torch.rand(int(far.sum()), generator=g)   # outliers stretch the key range
+        a = (torch.rand(n, generator=g) - 0.5) * 0.9 * z
+        b = (torch.rand(n, generator=g) - 0.5) * 0.9 * z
+        scene["positions"] = (eye[None] + z[:, None] * fwd[None] + a[:, None] * right[None] + b[:, None] * down[None]).contiguous()
+        scene["scale"] = torch.full((n, 3), 0.01)
+    d12 = syn.pack_density(scene).cuda()
+    sph = scene["features"].cuda()
+    rgba, dist, hits, vis, st = raster.trace(0, 3, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, camera_of(view),
+                                             stage_outputs=True)
+    torch.cuda.synchronize()
+    ok, m, idx = _lexicographic(st)
+    longest = int(raster.frame_stats()["max_tile_list_length"])
+    assert ok, f"{name}: (tile, depth, particle) order broken (M={m}, longest bucket {longest})"
+    assert bool((torch.bincount(idx, minlength=n) == st["tiles_count"].long()).all())
+    ranges = st["tile_ranges"].view(torch.int32).long().reshape(-1, 2)
+    sizes = ranges[:, 1] - ranges[:, 0]
+    if name == "buckets_up_to_4096":
+        assert int(sizes.max()) <= 4096
+    elif name == "buckets_up_to_12288":
+        assert 4096 < int(sizes.max()) <= 12288
+    elif name == "buckets_above_12288":
+        assert int(sizes.max()) > 12288
+    assert bool(torch.isfinite(rgba).all())
