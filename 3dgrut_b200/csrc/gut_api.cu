@@ -351,8 +351,8 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         {
             StageTimer t(h, ST_SORT, s);
             GUT_CUDA(h, gut_launch_tile_sort(fr, N, max_list, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p,
-                                             (uint32_t*)h->tile_hist.p /* free after the scan: bucket flags */, (uint32_t*)h->sorted_idx.p, s));
-            h->launches += max_list > 4096 ? 3 : 2;
+                                             (uint32_t*)h->tile_hist.p /* free after the scan: bucket flags */, (uint32_t*)h->stats.p + 2, (uint32_t*)h->sorted_idx.p, s));
+            h->launches += max_list > 8192 ? 3 : 2;
         }
         {
             StageTimer t(h, ST_RENDER, s);

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
     }
     atomicMax(&max_s, local_max);
     __syncthreads();
-    if (tid == 0) { start[T] = carry_s; stats[0] = carry_s; stats[1] = max_s; }
+    if (tid == 0) { start[T] = carry_s; stats[0] = carry_s; stats[1] = max_s; stats[2] = 0u; /* buckets handed to the radix sort */ }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -212,10 +212,12 @@ template <int THREADS, uint32_t CAP>
 __global__ void __launch_bounds__(THREADS) gut_tile_radix_sort_kernel(GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                       uint2* __restrict__ entries, uint2* __restrict__ scratch,
                                                                       const uint32_t* __restrict__ tile_flags,
+                                                                      const uint32_t* __restrict__ flagged_count, bool oversize,
                                                                       uint32_t* __restrict__ sorted_idx) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ SortShared<THREADS / 32> sh;
     const uint32_t tid = threadIdx.x, lane = tid & 31;
+    if (!oversize && *flagged_count == 0u) return;   // the ordinary frame: nothing was handed on
 
     // persistent: the launch is idle for ordinary frames (no flagged bucket, none above CAP), so it must cost next to nothing
     for (uint32_t tile = blockIdx.x; tile < fr.num_tiles; tile += gridDim.x) {
@@ -296,15 +298,15 @@ __global__ void __launch_bounds__(THREADS) gut_tile_radix_sort_kernel(GutFrame f
 // ---------------------------------------------------------------------------------------------------
 constexpr uint32_t BIN_LIMIT = 256;
 
-template <int THREADS, uint32_t CAP, uint32_t LOG_BINS>
-__global__ void __launch_bounds__(THREADS) gut_tile_bin_sort_kernel(const uint32_t* __restrict__ tile_start, const uint2* __restrict__ entries,
-                                                                    uint32_t n_min, uint32_t n_max, uint32_t* __restrict__ sorted_idx,
-                                                                    uint32_t* __restrict__ tile_flags) {
+template <int THREADS, uint32_t CAP, uint32_t LOG_BINS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) gut_tile_bin_sort_kernel(const uint32_t* __restrict__ tile_start, const uint2* __restrict__ entries,
+                                                                                uint32_t n_min, uint32_t n_max, uint32_t* __restrict__ sorted_idx,
+                                                                                uint32_t* __restrict__ tile_flags, uint32_t* __restrict__ flagged_count) {
     constexpr uint32_t BINS = 1u << LOG_BINS;
     constexpr int EPT = CAP / THREADS;        // entries per thread
     constexpr int BPT = BINS / THREADS;       // bins per thread in the scan
     constexpr int WARPS = THREADS / 32;
-    static_assert(CAP % THREADS == 0 && BINS % THREADS == 0 && BPT % 4 == 0, "tiling");
+    static_assert(CAP % THREADS == 0 && BINS % THREADS == 0 && BPT % 4 == 0 && EPT % 4 == 0 && BIN_LIMIT <= 256, "tiling");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint2* sorted = reinterpret_cast<uint2*>(smem_raw);                    // [CAP]
     uint32_t* bins = reinterpret_cast<uint32_t*>(sorted + CAP);            // [BINS + 4]: counts, then exclusive starts (+ total)
@@ -337,11 +339,12 @@ __global__ void __launch_bounds__(THREADS) gut_tile_bin_sort_kernel(const uint32
     const uint32_t range_bits = 32u - __clz(s_max - kmin);                 // 0 when every key is the same
     const uint32_t shift = range_bits > LOG_BINS ? range_bits - LOG_BINS : 0u;
 
-    uint32_t slot[EPT];
+    // slot of the entry inside its bin, 8 bits each: a bin that overflows them is above BIN_LIMIT and the bucket is handed on
+    uint32_t slot4[EPT / 4];
 #pragma unroll
     for (int e = 0; e < EPT; ++e) {
-        slot[e] = 0;
-        if (tid + e * THREADS < n) slot[e] = atomicAdd(&bins[(ent[e].x - kmin) >> shift], 1u);
+        if ((e & 3) == 0) slot4[e >> 2] = 0;
+        if (tid + e * THREADS < n) slot4[e >> 2] |= (atomicAdd(&bins[(ent[e].x - kmin) >> shift], 1u) & 0xffu) << (8 * (e & 3));
     }
     __syncthreads();
 
@@ -374,13 +377,16 @@ __global__ void __launch_bounds__(THREADS) gut_tile_bin_sort_kernel(const uint32
         if (tid == THREADS - 1) bins[BINS] = run;                          // = n
     }
     const bool big = s_big != 0u;
-    if (tid == 0) tile_flags[tile] = big ? 1u : 0u;
+    if (tid == 0) {
+        tile_flags[tile] = big ? 1u : 0u;
+        if (big) atomicAdd(flagged_count, 1u);
+    }
     if (big) return;                                                       // block-uniform: the radix kernel sorts this bucket
     __syncthreads();
 
 #pragma unroll
     for (int e = 0; e < EPT; ++e)
-        if (tid + e * THREADS < n) sorted[bins[(ent[e].x - kmin) >> shift] + slot[e]] = ent[e];
+        if (tid + e * THREADS < n) sorted[bins[(ent[e].x - kmin) >> shift] + ((slot4[e >> 2] >> (8 * (e & 3))) & 0xffu)] = ent[e];
     __syncthreads();
 
     for (uint32_t i = tid; i < n; i += THREADS) {
@@ -435,20 +441,20 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 }
 
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries,
-                                 uint2* scratch, uint32_t* tile_flags, uint32_t* sorted_idx, cudaStream_t stream) {
-    // buckets up to 4096 entries: 256 threads, 4096 bins (48 KB -> 4 CTAs per SM); up to 12288: 512 threads, 16384 bins (160 KB);
+                                 uint2* scratch, uint32_t* tile_flags, uint32_t* flagged_count, uint32_t* sorted_idx, cudaStream_t stream) {
+    // buckets up to 8192 entries: 512 threads, 8192 bins (96 KB, two CTAs per SM); up to 12288: 16384 bins (160 KB);
     // flagged buckets and buckets above 12288 entries: radix passes (in 192 KB of shared memory / over global memory).
     (void)N;
-    constexpr uint32_t CAP_S = 4096, CAP_L = 12288, LOG_BINS_S = 12, LOG_BINS_L = 14;
-    const size_t smem_s = CAP_S * sizeof(uint2) + ((1u << LOG_BINS_S) + 4) * sizeof(uint32_t);
+    constexpr uint32_t CAP_M = 8192, CAP_L = 12288, LOG_BINS_M = 13, LOG_BINS_L = 14;
+    const size_t smem_m = CAP_M * sizeof(uint2) + ((1u << LOG_BINS_M) + 4) * sizeof(uint32_t);
     const size_t smem_l = CAP_L * sizeof(uint2) + ((1u << LOG_BINS_L) + 4) * sizeof(uint32_t);
     const size_t smem_r = 4 * CAP_L * sizeof(uint32_t);
     static bool configured = false;
     static int radix_grid = 0;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<256, CAP_S, LOG_BINS_S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
+        cudaError_t e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_M, LOG_BINS_M, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_m);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
+        e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(gut_tile_radix_sort_kernel<512, CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r);
         if (e != cudaSuccess) return e;
@@ -460,12 +466,14 @@ cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max
         radix_grid = sms;
         configured = true;
     }
-    gut_tile_bin_sort_kernel<256, CAP_S, LOG_BINS_S><<<frame.num_tiles, 256, smem_s, stream>>>(tile_start, entries, 1u, CAP_S, sorted_idx, tile_flags);
-    if (max_list > CAP_S)
-        gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L><<<frame.num_tiles, 512, smem_l, stream>>>(tile_start, entries, CAP_S + 1u, CAP_L, sorted_idx,
-                                                                                               tile_flags);
+    gut_tile_bin_sort_kernel<512, CAP_M, LOG_BINS_M, 2><<<frame.num_tiles, 512, smem_m, stream>>>(tile_start, entries, 1u, CAP_M, sorted_idx, tile_flags,
+                                                                                              flagged_count);
+    if (max_list > CAP_M)
+        gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L, 1><<<frame.num_tiles, 512, smem_l, stream>>>(tile_start, entries, CAP_M + 1u, CAP_L, sorted_idx,
+                                                                                                  tile_flags, flagged_count);
     const uint32_t grid = frame.num_tiles < (uint32_t)radix_grid ? frame.num_tiles : (uint32_t)radix_grid;
-    gut_tile_radix_sort_kernel<512, CAP_L><<<grid, 512, smem_r, stream>>>(frame, tile_start, entries, scratch, tile_flags, sorted_idx);
+    gut_tile_radix_sort_kernel<512, CAP_L><<<grid, 512, smem_r, stream>>>(frame, tile_start, entries, scratch, tile_flags, flagged_count,
+                                                                         max_list > CAP_L, sorted_idx);
     return cudaGetLastError();
 }
 

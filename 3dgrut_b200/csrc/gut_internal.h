@@ -84,7 +84,7 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 // per-tile sort of the (depth, idx) buckets -> sorted particle list; scratch = alt buffer for oversize tiles;
 // tile_flags [T] = scratch words (buckets handed from the counting sort to the radix sort)
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries, uint2* scratch,
-                                 uint32_t* tile_flags, uint32_t* sorted_idx, cudaStream_t stream);
+                                 uint32_t* tile_flags, uint32_t* flagged_count /* zeroed by the tile scan */, uint32_t* sorted_idx, cudaStream_t stream);
 
 // debug/parity: rebuild the reference-shaped sorted key array and tile ranges
 cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_start, const uint32_t* sorted_idx, const float* depth,
