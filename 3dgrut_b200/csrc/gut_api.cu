@@ -38,7 +38,7 @@ struct GutHandle {
     uint64_t launches = 0;
 
     // per-particle workspace (K1 outputs) -- grow only, like GutRenderForwardContext (gutRenderer.cu:166-203)
-    DevBuf tiles_count, proj_pos, conic, extent, depth, features, raw_grad;
+    DevBuf tiles_count, proj_pos, conic, extent, depth, features, emit_rec, raw_grad;
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
@@ -273,7 +273,7 @@ void gut_destroy(GutHandle* h) {
     if (!h) return;
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
-    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->raw_grad, &h->tile_hist,
+    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->emit_rec, &h->raw_grad, &h->tile_hist,
                      &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->hit_masks,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
@@ -306,6 +306,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     GUT_CUDA(h, ensure(h->extent, n1 * 8, s));
     GUT_CUDA(h, ensure(h->depth, n1 * 4, s));
     GUT_CUDA(h, ensure(h->features, n1 * 16, s));
+    GUT_CUDA(h, ensure(h->emit_rec, n1 * 16, s));
     GUT_CUDA(h, ensure(h->tile_hist, (size_t)T * GUT_TILE_SUB * 4, s));
     GUT_CUDA(h, ensure(h->tile_start, ((size_t)T + 1) * 4, s));
     GUT_CUDA(h, ensure(h->tile_cursor, (size_t)T * GUT_TILE_SUB * 4, s));
@@ -313,7 +314,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
 
     GutProjBuffers pb;
     pb.tiles_count = (uint32_t*)h->tiles_count.p; pb.proj_pos = (float2*)h->proj_pos.p; pb.conic_opacity = (float4*)h->conic.p;
-    pb.extent = (float2*)h->extent.p; pb.depth = (float*)h->depth.p; pb.features = (float4*)h->features.p;
+    pb.extent = (float2*)h->extent.p; pb.depth = (float*)h->depth.p; pb.features = (float4*)h->features.p; pb.emit_rec = (uint4*)h->emit_rec.p;
 
     {
         StageTimer t(h, ST_PROJECT, s);

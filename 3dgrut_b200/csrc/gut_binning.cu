@@ -87,26 +87,50 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K2: emit.  One thread per particle re-walks its tile box with the same culling test as K1 and appends
-// (depth bits, particle) to each surviving tile's bucket.  reference: GUTProjector::expand, gutProjector.cuh:324-388.
+// K2: emit.  One thread per particle appends (depth bits, particle) to the bucket of every tile that survived K1's culling
+// test.  reference: GUTProjector::expand, gutProjector.cuh:324-388 (which re-walks the box and repeats the tests).
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame fr, uint32_t N, GutProjBuffers proj,
                                                        uint32_t* __restrict__ tile_cursor, uint2* __restrict__ entries, uint32_t capacity) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
-    // all loads in flight at once: three dependent rounds (count -> extent -> rest) would triple the memory latency the
-    // kernel sits on before its atomics start
-    const uint32_t count = proj.tiles_count[i];
+    // K1 left the culled tile box as a bit mask (gut_math.cuh, GUT_EMIT_*): one 16-byte load, no tests to repeat.
+    const uint4 rec = __ldg(proj.emit_rec + i);
+    const uint32_t depth_bits = rec.w;
+    const uint32_t sub = i & (GUT_TILE_SUB - 1);
+    // The bucket slot comes back from an L2 atomic (~1 us under contention): EMIT_ILP independent atomics are kept in
+    // flight per thread instead of one dependent round trip per tile.
+    constexpr int EMIT_ILP = 4;
+    if (!(rec.z & GUT_EMIT_BIG)) {
+        uint64_t mask = ((uint64_t)rec.y << 32) | rec.x;
+        if (mask == 0ull) return;
+        const uint32_t x0 = rec.z & 0xfffu, y0 = (rec.z >> 12) & 0xfffu, bw = (rec.z >> 24) & 0x7fu;
+        const uint32_t inv = 65536u / bw + 1u;   // row = (bit * inv) >> 16, exact for bit < 64, bw <= 64
+        while (mask) {
+            uint32_t t[EMIT_ILP], slot[EMIT_ILP];
+            bool ok[EMIT_ILP];
+#pragma unroll
+            for (int k = 0; k < EMIT_ILP; ++k) {
+                ok[k] = mask != 0ull;
+                const uint32_t bit = ok[k] ? (uint32_t)__ffsll((long long)mask) - 1u : 0u;
+                mask &= mask - 1ull;
+                const uint32_t row = (bit * inv) >> 16;
+                t[k] = (y0 + row) * fr.grid_x + x0 + (bit - row * bw);
+            }
+#pragma unroll
+            for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + sub], 1u) : 0u;
+#pragma unroll
+            for (int k = 0; k < EMIT_ILP; ++k)
+                if (ok[k] && slot[k] < capacity) entries[slot[k]] = make_uint2(depth_bits, i);
+        }
+        return;
+    }
+    // box above 64 tiles: walk it with the same culling test as K1 (reference: GUTProjector::expand, gutProjector.cuh:324-388)
     const float2 ext = proj.extent[i];
-    const uint32_t depth_bits = __float_as_uint(proj.depth[i]);
     const float2 centre = proj.proj_pos[i];
     const float4 co = proj.conic_opacity[i];
-    if (count == 0 || ext.x <= 1e-06f) return;
     const float max_power = gut_logf(co.w / cfg.min_alpha);
     const GutTileBox bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, ext);
-    // The bucket slot comes back from an L2 atomic (~1 us under contention).  Walking the box EMIT_ILP tiles at a time
-    // keeps that many independent atomics in flight per thread instead of one dependent round trip per tile.
-    constexpr int EMIT_ILP = 4;
     const uint32_t bw = bb.x1 - bb.x0;
     const uint32_t total = bw * (bb.y1 - bb.y0);
     uint32_t x = bb.x0, y = bb.y0;
@@ -121,7 +145,7 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
             if (++x == bb.x1) { x = bb.x0; ++y; }
         }
 #pragma unroll
-        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + (i & (GUT_TILE_SUB - 1))], 1u) : 0u;
+        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + sub], 1u) : 0u;
 #pragma unroll
         for (int k = 0; k < EMIT_ILP; ++k) {
             if (ok[k] && slot[k] < capacity) entries[slot[k]] = make_uint2(depth_bits, i);

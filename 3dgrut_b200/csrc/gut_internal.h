@@ -57,6 +57,7 @@ struct GutProjBuffers {
     float2* extent;          // [N]
     float* depth;            // [N]
     float4* features;        // [N] xyz = SH radiance + 0.5 (unclamped), w unused
+    uint4* emit_rec;         // [N] culled tile box of the particle for the emit pass (gut_math.cuh, GUT_EMIT_*)
 };
 
 // ---- launchers implemented in the .cu files (all enqueue on `stream`, return cudaGetLastError()) ----

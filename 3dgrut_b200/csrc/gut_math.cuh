@@ -100,7 +100,9 @@ GUT_HD GutTileBox gut_tile_bbox(uint32_t gx, uint32_t gy, float2 pos, float2 ext
 // reference: tileMinParticlePowerResponse, gutProjector.cuh:49-78.  Written so that every product and
 // sum rounds once, in the reference's evaluation order (the TU is built with --fmad=false), which makes
 // the count pass (K1) and the emit pass (K2) agree with each other and with the oracle exactly.
-GUT_HD float gut_tile_min_power(float tx_, float ty_, float4 co, float2 mean) {
+// rcx, rcy = 1 / (ts^2 co.x), 1 / (ts^2 co.z): per-particle IEEE quotients, passed in so that a caller that tests many
+// tiles of one particle divides once (same bits as dividing per tile).
+GUT_HD float gut_tile_min_power_rc(float tx_, float ty_, float4 co, float2 mean, float rcx, float rcy) {
     const float ts = (float)GUT_TILE;
     const float tminx = ts * tx_, tminy = ts * ty_;
     const float tmaxx = ts + tminx, tmaxy = ts + tminy;
@@ -111,7 +113,6 @@ GUT_HD float gut_tile_min_power(float tx_, float ty_, float4 co, float2 mean) {
         const float px = tmaxx * (1.0f - lax) + tminx * lax, py = tmaxy * (1.0f - lay) + tminy * lay;
         const float dxx = copysignf(ts, mox), dxy = copysignf(ts, moy);
         const float dfx = mean.x - px, dfy = mean.y - py;
-        const float rcx = 1.0f / (ts * ts * co.x), rcy = 1.0f / (ts * ts * co.z);
         float ax = (dxx * co.x * dfx + dxx * co.y * dfy) * rcx;
         float ay = (dxy * co.y * dfx + dxy * co.z * dfy) * rcy;
         ax = ax < 0.0f ? 0.0f : (ax > 1.0f ? 1.0f : ax);  // __saturatef, NaN -> 0 below
@@ -124,6 +125,16 @@ GUT_HD float gut_tile_min_power(float tx_, float ty_, float4 co, float2 mean) {
     }
     return 0.0f;
 }
+GUT_HD float gut_tile_min_power(float tx_, float ty_, float4 co, float2 mean) {
+    const float ts = (float)GUT_TILE;
+    return gut_tile_min_power_rc(tx_, ty_, co, mean, 1.0f / (ts * ts * co.x), 1.0f / (ts * ts * co.z));
+}
+
+// K1 -> emit hand-off (16 B per particle): the culling decisions of a tile box of up to 64 tiles as a bit mask (bit =
+// row-major position inside the box), so the emit pass appends without repeating the tests.
+//   x, y = mask bits 0-31, 32-63;  z = x0 | y0 << 12 | box width << 24 | (box above 64 tiles: emit re-walks it) << 31;  w = depth bits
+#define GUT_EMIT_BIG 0x80000000u
+#define GUT_EMIT_MASK_TILES 64u
 
 // SH basis (degree <= 3), sign convention of the reference: gaussianParticles.cuh:57-96
 GUT_HD void gut_sh_basis(int deg, float3 d, float* b) {

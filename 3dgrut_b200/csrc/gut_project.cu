@@ -161,10 +161,11 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
                                                           GutProjBuffers out, float* __restrict__ visibility,
                                                           uint32_t* __restrict__ tile_hist) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
-    const float4 r0 = __ldg(density12 + 3 * (size_t)i);      // pos.xyz, density
-    const float4 r1 = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
-    const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale.xyz, pad
+    const bool in_range = i < N;                              // out-of-range lanes stay for the warp-cooperative tile walk
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const float4 r0 = in_range ? __ldg(density12 + 3 * (size_t)i) : zero4;      // pos.xyz, density
+    const float4 r1 = in_range ? __ldg(density12 + 3 * (size_t)i + 1) : zero4;  // quat w,x,y,z
+    const float4 r2 = in_range ? __ldg(density12 + 3 * (size_t)i + 2) : zero4;  // scale.xyz, pad
     const float3 pos = f3(r0.x, r0.y, r0.z);
     const float opacity = r0.w;
     const float fw = (float)fr.width, fh = (float)fr.height;
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
     float2 centre = make_float2(0.0f, 0.0f);
     float3 cov = f3(0.0f, 0.0f, 0.0f);
     float3 sensor_ray = f3(0.0f, 0.0f, 0.0f);
-    if (opacity >= cfg.min_alpha && !(view_depth(fr.view, pos) < 0.2f)) {
+    if (in_range && opacity >= cfg.min_alpha && !(view_depth(fr.view, pos) < 0.2f)) {
         float3 c[3];
         quat_to_columns(r1.x, r1.y, r1.z, r1.w, c[0], c[1], c[2]);
         const float sc[3] = {r2.x, r2.y, r2.z};
@@ -216,19 +217,63 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
     float max_power = 0.0f;
     const bool valid_conic = valid_proj && conic_extent(cfg, cov, opacity, extent, co, max_power);
     // reference stores int 1 into float storage (gutProjector.cuh:275); 1.0f has the same truthiness and survives FTZ
-    visibility[i] = valid_conic ? 1.0f : 0.0f;
+    if (in_range) visibility[i] = valid_conic ? 1.0f : 0.0f;
 
-    uint32_t ntiles = 0;
-    if (valid_conic) {
-        const GutTileBox bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, extent);
-        for (uint32_t y = bb.y0; y < bb.y1; ++y)
-            for (uint32_t x = bb.x0; x < bb.x1; ++x) {
-                if (!cfg.tile_based_culling || gut_tile_min_power((float)x, (float)y, co, centre) < max_power) {
-                    ntiles++;
-                    atomicAdd(&tile_hist[(y * fr.grid_x + x) * GUT_TILE_SUB + (i & (GUT_TILE_SUB - 1))], 1u);  // RED: per-tile (sub-)list length for the bucket scan
-                }
-            }
+    // Tile walk (gutProjector.cuh:284-322), warp-cooperative: box sizes differ a lot between neighbouring particles, so the
+    // boxes of the warp's 32 particles are flattened into one list of (particle, tile) items and every lane tests one item
+    // per round, whatever particle it belongs to.  Each lane publishes its box in shared memory; an item finds its owner by
+    // binary search over the warp's exclusive box-size prefix.
+    __shared__ float4 s_box[256 / 32][32][3];     // {conic, max_power} {centre, rcx, rcy} {x0, y0, width, magic}
+    __shared__ uint32_t s_res[256 / 32][32][3];   // tiles kept, mask of kept tiles (boxes of up to 64 tiles)
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    GutTileBox bb{0u, 0u, 0u, 0u};
+    if (valid_conic) bb = gut_tile_bbox(fr.grid_x, fr.grid_y, centre, extent);
+    const uint32_t bw = bb.x1 - bb.x0;
+    const uint32_t total = bw * (bb.y1 - bb.y0);
+    uint32_t incl = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
     }
+    const uint32_t excl = incl - total;
+    const uint32_t warp_total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total) {
+        const float ts = (float)GUT_TILE;
+        s_box[wid][lane][0] = make_float4(co.x, co.y, co.z, max_power);
+        s_box[wid][lane][1] = make_float4(centre.x, centre.y, 1.0f / (ts * ts * co.x), 1.0f / (ts * ts * co.z));
+        // row = umulhi(item, magic) is exact for item * width < 2^32 (width 1: the item is the row)
+        s_box[wid][lane][2] = make_float4(__uint_as_float(bb.x0), __uint_as_float(bb.y0), __uint_as_float(bw),
+                                          __uint_as_float(bw > 1u ? 0xffffffffu / bw + 1u : 0u));
+    }
+    s_res[wid][lane][0] = 0u; s_res[wid][lane][1] = 0u; s_res[wid][lane][2] = 0u;
+    __syncwarp();
+    for (uint32_t q0 = 0; q0 < warp_total; q0 += 32) {
+        const uint32_t q = q0 + lane;
+        uint32_t owner = 0;   // last lane whose prefix is <= q: lanes with empty boxes share their successor's prefix and lose to it
+#pragma unroll
+        for (uint32_t step = 16; step; step >>= 1) {
+            const uint32_t v = __shfl_sync(0xffffffffu, excl, owner + step);
+            if (v <= q) owner += step;
+        }
+        const uint32_t first = __shfl_sync(0xffffffffu, excl, owner);
+        if (q < warp_total) {
+            const float4 b0 = s_box[wid][owner][0], b1 = s_box[wid][owner][1], b2 = s_box[wid][owner][2];
+            const uint32_t item = q - first, w_o = __float_as_uint(b2.z), magic = __float_as_uint(b2.w);
+            const uint32_t row = magic ? __umulhi(item, magic) : item;
+            const uint32_t x = __float_as_uint(b2.x) + (item - row * w_o), y = __float_as_uint(b2.y) + row;
+            if (!cfg.tile_based_culling ||
+                gut_tile_min_power_rc((float)x, (float)y, make_float4(b0.x, b0.y, b0.z, 0.0f), make_float2(b1.x, b1.y), b1.z, b1.w) < b0.w) {
+                atomicAdd(&s_res[wid][owner][0], 1u);
+                if (item < GUT_EMIT_MASK_TILES) atomicOr(&s_res[wid][owner][1 + (item >> 5)], 1u << (item & 31u));
+                // RED: per-tile (sub-)list length for the bucket scan; the owner's particle index has the owner's lane in its low bits
+                atomicAdd(&tile_hist[(y * fr.grid_x + x) * GUT_TILE_SUB + (owner & (GUT_TILE_SUB - 1))], 1u);
+            }
+        }
+    }
+    __syncwarp();
+    if (!in_range) return;
+    const uint32_t ntiles = s_res[wid][lane][0];
     out.tiles_count[i] = ntiles;
     if (ntiles == 0) {
         out.proj_pos[i] = make_float2(0.0f, 0.0f);
@@ -236,8 +281,11 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
         out.extent[i] = make_float2(0.0f, 0.0f);
         out.depth[i] = 0.0f;
         out.features[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        out.emit_rec[i] = make_uint4(0u, 0u, 0u, 0u);
         return;
     }
+    const uint32_t box_word = bb.x0 | (bb.y0 << 12) | ((total > GUT_EMIT_MASK_TILES ? 0u : bw) << 24) | (total > GUT_EMIT_MASK_TILES ? GUT_EMIT_BIG : 0u);
+    const uint32_t mask_lo = s_res[wid][lane][1], mask_hi = s_res[wid][lane][2];
 
     // SH colour seen from the sensor centre, +0.5, unclamped (gutProjector.cuh:304-310, gaussianParticles.cuh:64-96)
     const float dist = sqrtf(dot(sensor_ray, sensor_ray));
@@ -268,7 +316,9 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
     out.proj_pos[i] = centre;
     out.conic_opacity[i] = co;
     out.extent[i] = extent;
-    out.depth[i] = cfg.global_z_order ? view_depth(fr.view, pos) : dist;
+    const float depth = cfg.global_z_order ? view_depth(fr.view, pos) : dist;
+    out.depth[i] = depth;
+    out.emit_rec[i] = make_uint4(mask_lo, mask_hi, box_word, __float_as_uint(depth));
 }
 
 // ---------------------------------------------------------------------------------------------------
