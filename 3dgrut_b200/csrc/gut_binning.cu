@@ -21,13 +21,12 @@ constexpr int SCAN_THREADS = 1024;
 
 // ---------------------------------------------------------------------------------------------------
 // Exclusive scan of the tile histogram (T is a few thousand: one CTA, chunks of 1024 tiles with a carry).
-// hist holds GUT_TILE_SUB sub-counts per tile; start[t] = first slot of tile t's bucket, cursor[t*SUB+k] = first
+// hist holds GUT_TILE_SUB sub-counts per tile; start[t] = first slot of tile t's bucket, cursor[GUT_SUB_SLOT(t,k,T)] = first
 // slot of sub-bucket k (absolute positions: the emit pass appends with one atomicAdd and no further look-up).
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T, const uint32_t* __restrict__ hist,
                                                                     uint32_t* __restrict__ start, uint32_t* __restrict__ cursor,
                                                                     uint32_t* __restrict__ stats) {
-    static_assert(GUT_TILE_SUB == 8, "the scan reads a tile's sub-counts as two uint4");
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
     __shared__ uint32_t max_s;
@@ -41,8 +40,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
 #pragma unroll
         for (int k = 0; k < GUT_TILE_SUB; ++k) c[k] = 0;
         if (i < T) {
-            const uint4 a = reinterpret_cast<const uint4*>(hist)[2 * (size_t)i], b4 = reinterpret_cast<const uint4*>(hist)[2 * (size_t)i + 1];
-            c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b4.x; c[5] = b4.y; c[6] = b4.z; c[7] = b4.w;
+#pragma unroll
+            for (int k = 0; k < GUT_TILE_SUB; ++k) c[k] = hist[GUT_SUB_SLOT(i, k, T)];
         }
         uint32_t v = 0;
 #pragma unroll
@@ -74,8 +73,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
             uint32_t o[GUT_TILE_SUB];
 #pragma unroll
             for (int k = 0; k < GUT_TILE_SUB; ++k) { o[k] = run; run += c[k]; }
-            reinterpret_cast<uint4*>(cursor)[2 * (size_t)i] = make_uint4(o[0], o[1], o[2], o[3]);
-            reinterpret_cast<uint4*>(cursor)[2 * (size_t)i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+#pragma unroll
+            for (int k = 0; k < GUT_TILE_SUB; ++k) cursor[GUT_SUB_SLOT(i, k, T)] = o[k];
         }
         __syncthreads();
         if (tid == SCAN_THREADS - 1) carry_s = carry + warp_sums[31];
@@ -90,7 +89,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) gut_tile_scan_kernel(uint32_t T,
 // K2: emit.  One thread per particle appends (depth bits, particle) to the bucket of every tile that survived K1's culling
 // test.  reference: GUTProjector::expand, gutProjector.cuh:324-388 (which re-walks the box and repeats the tests).
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame fr, uint32_t N, GutProjBuffers proj,
+__global__ void __launch_bounds__(256, 8) gut_emit_kernel(GutConfig cfg, GutFrame fr, uint32_t N, GutProjBuffers proj,
                                                        uint32_t* __restrict__ tile_cursor, uint2* __restrict__ entries, uint32_t capacity) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
@@ -118,7 +117,7 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
                 t[k] = (y0 + row) * fr.grid_x + x0 + (bit - row * bw);
             }
 #pragma unroll
-            for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + sub], 1u) : 0u;
+            for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[GUT_SUB_SLOT(t[k], sub, fr.num_tiles)], 1u) : 0u;
 #pragma unroll
             for (int k = 0; k < EMIT_ILP; ++k)
                 if (ok[k] && slot[k] < capacity) entries[slot[k]] = make_uint2(depth_bits, i);
@@ -145,7 +144,7 @@ __global__ void __launch_bounds__(256) gut_emit_kernel(GutConfig cfg, GutFrame f
             if (++x == bb.x1) { x = bb.x0; ++y; }
         }
 #pragma unroll
-        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[t[k] * GUT_TILE_SUB + sub], 1u) : 0u;
+        for (int k = 0; k < EMIT_ILP; ++k) slot[k] = ok[k] ? atomicAdd(&tile_cursor[GUT_SUB_SLOT(t[k], sub, fr.num_tiles)], 1u) : 0u;
 #pragma unroll
         for (int k = 0; k < EMIT_ILP; ++k) {
             if (ok[k] && slot[k] < capacity) entries[slot[k]] = make_uint2(depth_bits, i);

@@ -15,7 +15,10 @@
 #define GUT_INVALID_PARTICLE 0xFFFFFFFFu
 // Every tile's bucket counter / cursor is split into GUT_TILE_SUB sub-counters selected by the low bits of the particle
 // index: the returning L2 atomics of the emit pass then spread over 8x more addresses (same-address atomics serialise).
-#define GUT_TILE_SUB 8
+#define GUT_TILE_SUB 16
+// sub-counter k of tile t (T tiles): sub-counter major, so that the sub-counters of one hot tile sit in different L2 sectors
+// (atomics to one 32-byte sector serialise just like atomics to one address)
+#define GUT_SUB_SLOT(t, k, T) ((size_t)(k) * (T) + (t))
 
 #define GUT_HD __host__ __device__ __forceinline__
 #define GUT_D __device__ __forceinline__

@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
                 atomicAdd(&s_res[wid][owner][0], 1u);
                 if (item < GUT_EMIT_MASK_TILES) atomicOr(&s_res[wid][owner][1 + (item >> 5)], 1u << (item & 31u));
                 // RED: per-tile (sub-)list length for the bucket scan; the owner's particle index has the owner's lane in its low bits
-                atomicAdd(&tile_hist[(y * fr.grid_x + x) * GUT_TILE_SUB + (owner & (GUT_TILE_SUB - 1))], 1u);
+                atomicAdd(&tile_hist[GUT_SUB_SLOT(y * fr.grid_x + x, owner & (GUT_TILE_SUB - 1), fr.num_tiles)], 1u);
             }
         }
     }
