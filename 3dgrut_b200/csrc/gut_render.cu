@@ -31,6 +31,8 @@
 //    transpose-reduce (not 14 x 5 butterflies) and ONE red.global.add.f32 instruction per (warp, particle) -- and
 //    nothing at all when no ray of the block hit (the reference reduces and does 14 atomics regardless,
 //    shRadiativeGaussianParticles.cuh:409-482 called outside the isAlive branch at gutKBufferRenderer.cuh:379-383).
+#include <stdlib.h>
+
 #include "gut_render_common.cuh"
 
 namespace {
@@ -224,12 +226,12 @@ GUT_D size_t hit_mask_slot(uint32_t b0, uint32_t tile, uint32_t b, uint32_t bloc
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT>
-__global__ void __launch_bounds__(RENDER_THREADS, 25) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+__global__ void __launch_bounds__(RENDER_THREADS, 24) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                      GutParticleSource src,
                                                                      const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                      float4* __restrict__ rgba, float* __restrict__ dist,
                                                                      float* __restrict__ hits, unsigned long long* __restrict__ counters,
-                                                                     uint32_t* __restrict__ hit_masks /* nullable: inference */) {
+                                                                     uint32_t* __restrict__ hit_masks /* nullable: inference */, bool block_culling) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
 
     const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
@@ -245,13 +247,48 @@ __global__ void __launch_bounds__(RENDER_THREADS, 25) gut_render_kernel(GutConfi
     st.T = bc(1.0f); st.D = bc(0.0f); st.cr = st.cg = st.cb = bc(0.0f);
 #pragma unroll
     for (int h = 0; h < 2; ++h) { st.nhits[h] = 0; st.ntests[h] = 0; st.alive[h] = ray.inside[h] && ray.valid[h]; }
+
+    // cone around the block's live rays for block_cull (kept in shared memory: the walk has no registers to spare)
+    __shared__ float4 s_cone;
+    {
+        const uint32_t lane = threadIdx.x & 31;
+        float3 dn[2], sum = f3(0.f, 0.f, 0.f);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float3 d = f3(h ? hi(ray.d.x) : lo(ray.d.x), h ? hi(ray.d.y) : lo(ray.d.y), h ? hi(ray.d.z) : lo(ray.d.z));
+            dn[h] = rsqrtf(dot(d, d)) * d;
+            if (st.alive[h]) sum = sum + dn[h];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sum.x += __shfl_xor_sync(0xffffffffu, sum.x, o); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, o); sum.z += __shfl_xor_sync(0xffffffffu, sum.z, o);
+        }
+        const float n2 = dot(sum, sum);
+        const float3 axis = n2 > 0.0f ? rsqrtf(n2) * sum : f3(0.f, 0.f, 1.f);
+        float cmin = 1.0f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) if (st.alive[h]) cmin = fminf(cmin, dot(axis, dn[h]));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cmin = fminf(cmin, __shfl_xor_sync(0xffffffffu, cmin, o));
+        // tan(half angle), widened; no cull (w < 0) for degenerate bundles, per-ray origins or another kernel degree
+        float tan_h = -1.0f;
+        if (DEG == 2 && block_culling && uniform && cmin > 0.5f) tan_h = sqrtf(fmaxf(1.0f - cmin * cmin, 0.0f)) / cmin * 1.001f + 1e-6f;
+        if (lane == 0) s_cone = make_float4(axis.x, axis.y, axis.z, tan_h);
+        __syncwarp();
+    }
     for (uint32_t b = 0; b < stg.nb; ++b) {
-        stg.stage(b);
-        const uint32_t accepted = uniform ? forward_walk<DEG, true, COUNT>(cfg, stg.rec, stg.count(b), ray, st)
-                                          : forward_walk<DEG, false, COUNT>(cfg, stg.rec, stg.count(b), ray, st);
+        // records no ray of the block can accept are dropped while staging; the walk sees the kept ones, compacted
+        uint32_t keep;
+        const uint32_t kept = stg.stage_culled(b, cfg, s_cone, keep);
+        const uint32_t accepted = uniform ? forward_walk<DEG, true, COUNT>(cfg, stg.rec, kept, ray, st)
+                                          : forward_walk<DEG, false, COUNT>(cfg, stg.rec, kept, ray, st);
         if (!COUNT && hit_masks) {
-            const uint32_t m = __reduce_or_sync(0xffffffffu, accepted);
-            if ((threadIdx.x & 31) == 0) hit_masks[hit_mask_slot(b0, tile, b, block)] = m;
+            // bit k of `accepted` = k-th kept record; the backward indexes the batch by list position
+            const uint32_t lane = threadIdx.x & 31;
+            const uint32_t comp = __reduce_or_sync(0xffffffffu, accepted);
+            const bool mine = ((keep >> lane) & 1u) && ((comp >> __popc(keep & ((1u << lane) - 1u))) & 1u);
+            const uint32_t m = __ballot_sync(0xffffffffu, mine);
+            if (lane == 0) hit_masks[hit_mask_slot(b0, tile, b, block)] = m;
         }
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;   // the block saturated early
         stg.rotate();
@@ -515,12 +552,15 @@ cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters, uint32_t* hit_masks, cudaStream_t stream) {
     const uint32_t grid = frame.num_tiles * BLOCKS_PER_TILE;
+    // test hook: GUT_DEBUG_NO_BLOCK_CULL=1 walks every record, to prove that the cull changes no bit of the outputs
+    const char* dbg = getenv("GUT_DEBUG_NO_BLOCK_CULL");
+    const bool cull = !(dbg && dbg[0] == '1');
     if (counters)
         gut_render_kernel<DEG, true><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
-                                                                       nullptr, counters, nullptr);
+                                                                       nullptr, counters, nullptr, cull);
     else
         gut_render_kernel<DEG, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
-                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks);
+                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks, cull);
     return cudaGetLastError();
 }
 

@@ -167,6 +167,64 @@ struct WarpStager {
         issue_gather(bi + 1, p_next);
         p_after = load_idx(bi + 2);
     }
+    // Forward only: stage + block-level cull.  The lane decides whether ANY ray of the 8x8 block can accept its record,
+    // from a cone that contains the block's ray directions (axis cone.xyz, tan of the half angle cone.w; w < 0: no cull).
+    // A ray accepts when its canonical distance^2 g2 = |go|^2 sin^2(angle(u, go)) is below
+    // g2max = 2 min(ln(1 / min_response), ln(density / min_alpha)) (degree-2 kernel).  Every ray direction of the block is
+    // axis + tan(a) e with a <= half angle and e a unit vector, so u = ms d deviates from uc = ms axis by at most
+    // asin(rho), rho = tan(half angle) |ms|_2 / |uc|, |ms|_2 = 1 / min scale.  The smallest possible g2 is therefore
+    // |go|^2 sin^2(phi_c - asin(rho)); the record is dropped when even that is above g2max (2 % margin on g2 and an
+    // absolute one on the sine, far above the fp32 error of either side).  Conservative: image and hit masks are
+    // bit-identical to walking every record.  Kept records are compacted to the front of the batch in list order, the
+    // rest of the batch becomes padding; `keep` has a bit per list position.  Returns the number of kept records.
+    GUT_D uint32_t stage_culled(uint32_t bi, const GutConfig& cfg, const float4 cone, uint32_t& keep) {
+        static_assert(!BWD, "forward only");
+        cp_async_wait_all();
+        __syncwarp();   // the walk of batch bi-1 is over in every lane: rec may be overwritten
+        const uint32_t cnt = count(bi);
+        float4 o0 = make_float4(1.0f, 0.0f, 0.0f, 0.0f), o1 = make_float4(0.0f, 1.0f, 0.0f, 0.0f), o2 = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+        float4 o3 = make_float4(1.0f, 1.0f, 1.0f, 0.0f), o4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        bool k = false;
+        if (lane < cnt) {
+            const float4 r0 = raw[lane], q = raw[BATCH + lane], r2 = raw[2 * BATCH + lane], ft = raw[3 * BATCH + lane];
+            float3 c0, c1, c2;
+            quat_to_columns(q.x, q.y, q.z, q.w, c0, c1, c2);   // columns of R == rows of R^T
+            const float ix = mufu_rcp(r2.x), iy = mufu_rcp(r2.y), iz = mufu_rcp(r2.z);
+            const float3 m0 = c0 * ix, m1 = c1 * iy, m2 = c2 * iz;   // rows of ms = diag(1/s) R^T
+            const float3 v = origin - f3(r0.x, r0.y, r0.z);          // frame origin - position
+            const float3 go = f3(dot(m0, v), dot(m1, v), dot(m2, v));
+            k = true;
+            if (cone.w >= 0.0f && !(r0.w > cfg.min_alpha)) k = false;   // araw = resp * density never passes min_alpha
+            if (k && cone.w >= 0.0f) {
+                const float3 ax = f3(cone.x, cone.y, cone.z);
+                const float3 uc = f3(dot(m0, ax), dot(m1, ax), dot(m2, ax));
+                const float l2 = dot(uc, uc), gg = dot(go, go), ug = dot(uc, go);
+                const float3 cr = cross(uc, go);
+                const float il = mufu_rsq(l2), inv = il * mufu_rsq(gg);
+                const float sin_c = mufu_sqrt(dot(cr, cr)) * inv, cos_c = fabsf(ug) * inv;
+                const float rho = cone.w * il * fmaxf(ix, fmaxf(iy, iz));
+                // ln(x) = lg2(x) ln 2
+                const float g2max = 1.3862943611f * fminf(__log2f(1.0f / cfg.min_kernel_response), __log2f(r0.w / cfg.min_alpha));
+                const float lhs = sin_c * mufu_sqrt(fmaxf(1.0f - rho * rho, 0.0f)) - cos_c * rho - 4e-6f;
+                if ((rho < 1.0f) && (lhs > 0.0f) && (lhs * lhs * gg > 1.02f * g2max + 1e-3f)) k = false;
+            }
+            if (k) {
+                o0 = make_float4(m0.x, m0.y, m0.z, go.x);
+                o1 = make_float4(m1.x, m1.y, m1.z, go.y);
+                o2 = make_float4(m2.x, m2.y, m2.z, go.z);
+                o3 = make_float4(r2.x, r2.y, r2.z, r0.w);
+                o4 = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_cur));
+            }
+        }
+        keep = __ballot_sync(0xffffffffu, k);
+        const uint32_t kept = __popc(keep), below = (1u << lane) - 1u;
+        float4* out = rec + 5 * (k ? __popc(keep & below) : kept + __popc(~keep & below));
+        out[0] = o0; out[1] = o1; out[2] = o2; out[3] = o3; out[4] = o4;
+        __syncwarp();   // raw is consumed, rec is published
+        issue_gather(bi + 1, p_next);
+        p_after = load_idx(bi + 2);
+        return kept;
+    }
     GUT_D void rotate() { p_cur = p_next; p_next = p_after; }
     // before the warp retires: nothing may still be landing in its shared memory
     GUT_D void drain() { cp_async_wait_all(); }

@@ -177,3 +177,45 @@ def test_sort_paths(name):
     elif name == "buckets_above_12288":
         assert int(sizes.max()) > 12288
     assert bool(torch.isfinite(rgba).all())
+
+
+CULL_CASES = {
+    "c2_isotropic": dict(n=1_000_000, w=1237, h=822, model="pinhole", kind="init", seed=1002),
+    "anisotropic_dense": dict(n=300_000, w=640, h=480, model="pinhole", kind="dense", seed=31),
+    "fisheye": dict(n=300_000, w=640, h=480, model="fisheye", kind="dense", seed=32),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CULL_CASES))
+def test_block_cull_changes_no_bit(name, monkeypatch):
+    """The forward drops, per 8x8 block, list entries that no ray of the block can accept (gut_render.cu, block_cull).
+    The bound is conservative: image, distance, hit counts and the gradients (through the hit masks) are bit-identical /
+    equal to walking every entry."""
+    c = CULL_CASES[name]
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = native.SplatRaster(cfg_from_conf(make_conf()))
+    scene = syn.make_scene(c["n"], 3, seed=c["seed"], kind=c["kind"])
+    view = syn.make_view(c["w"], c["h"], model=c["model"])
+    d12 = syn.pack_density(scene).cuda()
+    sph = scene["features"].cuda()
+    ro, rd, cam = view["rays_ori"].cuda(), view["rays_dir"].cuda(), camera_of(view)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    rg = torch.rand((c["h"], c["w"], 4), device="cuda", generator=g) * 2 - 1
+    dg = (torch.rand((c["h"], c["w"], 1), device="cuda", generator=g) * 2 - 1) * 0.01
+
+    def run():
+        out = raster.trace(0, 3, d12, sph, ro, rd, None, cam)
+        t, hh = raster.measure_work(ro, rd)
+        g12, gsph = raster.trace_bwd(0, 3, d12, sph, ro, rd, None, cam, 0, 1, None, None, out[0], rg, out[1], dg)
+        torch.cuda.synchronize()
+        return [x.clone() for x in out], t, hh, g12.clone(), gsph.clone()
+
+    culled, t_c, h_c, g12_c, gsph_c = run()
+    monkeypatch.setenv("GUT_DEBUG_NO_BLOCK_CULL", "1")
+    full, t_f, h_f, g12_f, gsph_f = run()
+    for a, b in zip(culled, full):
+        assert torch.equal(a, b)
+    assert h_c == h_f and t_c <= t_f
+    assert rel_l2(g12_c.cpu().numpy(), g12_f.cpu().numpy()) <= 1e-5      # same hits; atomics reorder the sums
+    assert rel_l2(gsph_c.cpu().numpy(), gsph_f.cpu().numpy()) <= 1e-5
+    print(f"{name}: tests per ray {t_f} -> {t_c} ({100.0 * (1 - t_c / max(t_f, 1)):.1f} % dropped)")
