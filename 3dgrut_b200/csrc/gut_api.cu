@@ -513,6 +513,31 @@ int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_
     return GUT_OK;
 }
 
+int gut_pack_particles(GutHandle* h, void* stream_, uint32_t N, const float* d_positions, const float* d_density, const float* d_rotation,
+                       const float* d_scale, float* d_particle_density) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (N == 0) return GUT_OK;
+    if (!d_positions || !d_density || !d_rotation || !d_scale || !d_particle_density) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (((uintptr_t)d_rotation | (uintptr_t)d_particle_density) & 15) return fail(h, GUT_ERR_BAD_INPUT, "rotation / packed buffers must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_pack_particles(N, d_positions, d_density, d_rotation, d_scale, d_particle_density, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_unpack_particle_gradient(GutHandle* h, void* stream_, uint32_t N, const float* d_particle_density_grad, float* d_positions_grad,
+                                 float* d_density_grad, float* d_rotation_grad, float* d_scale_grad) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (N == 0) return GUT_OK;
+    if (!d_particle_density_grad || !d_positions_grad || !d_density_grad || !d_rotation_grad || !d_scale_grad) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (((uintptr_t)d_rotation_grad | (uintptr_t)d_particle_density_grad) & 15) return fail(h, GUT_ERR_BAD_INPUT, "rotation / packed buffers must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_unpack_gradient(N, d_particle_density_grad, d_positions_grad, d_density_grad, d_rotation_grad, d_scale_grad,
+                                           (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
 int gut_forward_host(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
                      const float* d_radiance, uint32_t W, uint32_t H, const float* h_ray_ori, const float* h_ray_dir, float* h_rgba,
                      float* h_dist, float* h_hits, float* d_visibility) {

@@ -113,5 +113,10 @@ cudaError_t gut_launch_render_kbuffer_backward(const GutConfig& cfg, const GutFr
                                                const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
                                                cudaStream_t stream);
 
+// [N,3] positions, [N,1] density, [N,4] rotation, [N,3] scale <-> [N,12] (gut_project.cu)
+cudaError_t gut_launch_pack_particles(uint32_t N, const float* pos, const float* dens, const float* rot, const float* scale, float* out12,
+                                      cudaStream_t stream);
+cudaError_t gut_launch_unpack_gradient(uint32_t N, const float* grad12, float* pos, float* dens, float* rot, float* scale, cudaStream_t stream);
+
 cudaError_t gut_launch_fill_outputs(uint32_t num_pixels, float* rgba, float* dist, float* hits, cudaStream_t stream);
 cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream);

@@ -615,3 +615,49 @@ cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float
     gut_copy_features3_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, features4, features3);
     return cudaGetLastError();
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// Packing of the model's parameter tensors into the [N,12] record the kernels read, and the inverse for its gradient
+// (reference: torch.cat in threedgut_tracer/tracer.py:176-178 and the column split autograd derives from it).
+// One thread per particle; a warp's reads of a [N,3] / [N,4] tensor cover one contiguous span.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gut_pack_particles_kernel(uint32_t N, const float* __restrict__ pos, const float* __restrict__ dens,
+                                                                 const float4* __restrict__ rot, const float* __restrict__ scale,
+                                                                 float4* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float px = __ldg(pos + 3 * (size_t)i), py = __ldg(pos + 3 * (size_t)i + 1), pz = __ldg(pos + 3 * (size_t)i + 2);
+    const float d = __ldg(dens + i);
+    const float4 q = __ldg(rot + i);
+    const float sx = __ldg(scale + 3 * (size_t)i), sy = __ldg(scale + 3 * (size_t)i + 1), sz = __ldg(scale + 3 * (size_t)i + 2);
+    out[3 * (size_t)i] = make_float4(px, py, pz, d);
+    out[3 * (size_t)i + 1] = q;
+    out[3 * (size_t)i + 2] = make_float4(sx, sy, sz, 0.0f);
+}
+
+__global__ void __launch_bounds__(256) gut_unpack_gradient_kernel(uint32_t N, const float4* __restrict__ grad12, float* __restrict__ pos,
+                                                                  float* __restrict__ dens, float4* __restrict__ rot, float* __restrict__ scale) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float4 a = __ldg(grad12 + 3 * (size_t)i), q = __ldg(grad12 + 3 * (size_t)i + 1), c = __ldg(grad12 + 3 * (size_t)i + 2);
+    pos[3 * (size_t)i] = a.x; pos[3 * (size_t)i + 1] = a.y; pos[3 * (size_t)i + 2] = a.z;
+    dens[i] = a.w;
+    rot[i] = q;
+    scale[3 * (size_t)i] = c.x; scale[3 * (size_t)i + 1] = c.y; scale[3 * (size_t)i + 2] = c.z;
+}
+
+cudaError_t gut_launch_pack_particles(uint32_t N, const float* pos, const float* dens, const float* rot, const float* scale, float* out12,
+                                      cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_pack_particles_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, pos, dens, reinterpret_cast<const float4*>(rot), scale,
+                                                                  reinterpret_cast<float4*>(out12));
+    return cudaGetLastError();
+}
+
+cudaError_t gut_launch_unpack_gradient(uint32_t N, const float* grad12, float* pos, float* dens, float* rot, float* scale, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    gut_unpack_gradient_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, reinterpret_cast<const float4*>(grad12), pos, dens,
+                                                                   reinterpret_cast<float4*>(rot), scale);
+    return cudaGetLastError();
+}

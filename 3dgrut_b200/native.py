@@ -71,6 +71,10 @@ def load_library():
     lib.gut_density_gradient_finish.restype = C.c_int
     lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
     lib.gut_sh_gradient_expand.restype = C.c_int
+    lib.gut_pack_particles.argtypes = [vp, vp, u32, fp, fp, fp, fp, fp]
+    lib.gut_pack_particles.restype = C.c_int
+    lib.gut_unpack_particle_gradient.argtypes = [vp, vp, u32, fp, fp, fp, fp, fp]
+    lib.gut_unpack_particle_gradient.restype = C.c_int
     lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
     lib.gut_forward_host.restype = C.c_int
     lib.gut_backward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, i32]
@@ -316,6 +320,38 @@ class SplatRaster:
         if rc != 0:
             self._raise(rc)
         return out_radiance_grad
+
+    def pack_particles(self, positions, density, rotation, scale):
+        """gut_pack_particles: [N,3], [N,1], [N,4], [N,3] -> the [N,12] particle_density record (tracer.py:176-178's torch.cat)."""
+        dev = self.device
+        pos = _check_cuda_f32("positions", positions, dev)
+        dns = _check_cuda_f32("density", density, dev)
+        rot = _check_cuda_f32("rotation", rotation, dev)
+        scl = _check_cuda_f32("scale", scale, dev)
+        n = pos.shape[0]
+        if pos.shape != (n, 3) or dns.shape != (n, 1) or rot.shape != (n, 4) or scl.shape != (n, 3):
+            raise GutError(abi.GutStatus.BAD_INPUT, "expected positions [N,3], density [N,1], rotation [N,4], scale [N,3]")
+        out = torch.empty((n, 12), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_pack_particles(self._h, self._stream(), n, _ptr(pos), _ptr(dns), _ptr(rot), _ptr(scl), _ptr(out))
+        if rc != 0:
+            self._raise(rc)
+        return out
+
+    def unpack_particle_gradient(self, density_grad):
+        """gut_unpack_particle_gradient: [N,12] gradient -> (positions [N,3], density [N,1], rotation [N,4], scale [N,3]) gradients."""
+        dev = self.device
+        g = _check_cuda_f32("density_grad", density_grad, dev)
+        n = g.shape[0]
+        if g.shape != (n, 12):
+            raise GutError(abi.GutStatus.BAD_INPUT, "density_grad must be [N,12]")
+        pos = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        dns = torch.empty((n, 1), dtype=torch.float32, device=dev)
+        rot = torch.empty((n, 4), dtype=torch.float32, device=dev)
+        scl = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_unpack_particle_gradient(self._h, self._stream(), n, _ptr(g), _ptr(pos), _ptr(dns), _ptr(rot), _ptr(scl))
+        if rc != 0:
+            self._raise(rc)
+        return pos, dns, rot, scl
 
     def set_training(self, training: bool):
         """gut_set_training: training=False skips the hit-mask recording of the forward (inference); no backward may follow."""

@@ -73,8 +73,8 @@ class Tracer:
         @staticmethod
         def forward(ctx, tracer_wrapper, frame_id, n_active_features, ray_ori, ray_dir, mog_pos, mog_rot, mog_scl, mog_dns, mog_sph,
                     sensor):
-            # [pos, density, rot, scale, 0] -> [N,12]  (tracer.py:176-178)
-            particle_density = torch.cat([mog_pos, mog_dns, mog_rot, mog_scl, torch.zeros_like(mog_dns)], dim=1).contiguous()
+            # [pos, density, rot, scale, 0] -> [N,12]  (tracer.py:176-178's torch.cat, as one packing kernel)
+            particle_density = tracer_wrapper.pack_particles(mog_pos, mog_dns, mog_rot, mog_scl)
             particle_radiance = mog_sph.contiguous()
             rgba, dist, hits, vis = tracer_wrapper.trace(frame_id, n_active_features, particle_density, particle_radiance,
                                                          ray_ori, ray_dir, None, sensor)
@@ -96,9 +96,8 @@ class Tracer:
             density_grad, radiance_grad = ctx.tracer_wrapper.trace_bwd(
                 ctx.frame_id, ctx.n_active_features, particle_density, particle_radiance, ray_ori, ray_dir, None, ctx.sensor,
                 0, 1, None, None, rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous())
-            pos_g, dns_g, rot_g, scl_g, _pad = torch.split(density_grad, [3, 1, 4, 3, 1], dim=1)
-            return (None, None, None, None, None, pos_g.contiguous(), rot_g.contiguous(), scl_g.contiguous(), dns_g.contiguous(),
-                    radiance_grad, None)
+            pos_g, dns_g, rot_g, scl_g = ctx.tracer_wrapper.unpack_particle_gradient(density_grad)
+            return (None, None, None, None, None, pos_g, rot_g, scl_g, dns_g, radiance_grad, None)
 
     def __init__(self, conf):
         self.device = "cuda"

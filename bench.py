@@ -290,12 +290,17 @@ def run_ours(args):
     value = args.views * P * args.steps / (ms_total * 1e-3) / 1e6
 
     # ---- roofline of the dominant kernel (rank 0's views) ----------------------------------------------
-    tests = hits = 0
+    tests = hits = tests_exec = 0
     m_sum = 0
     for v in views:
         raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
+        # algorithmic work = what the reference's walk does: every list entry of the tile for every live ray.  The forward's
+        # conservative block cull (gut_render_common.cuh, stage_culled) skips part of it; the executed count is reported too.
+        os.environ["GUT_DEBUG_NO_BLOCK_CULL"] = "1"
         t_, h_ = raster.measure_work(v["rays_ori"], v["rays_dir"])
-        tests += t_; hits += h_
+        del os.environ["GUT_DEBUG_NO_BLOCK_CULL"]
+        te_, _ = raster.measure_work(v["rays_ori"], v["rays_dir"])
+        tests += t_; hits += h_; tests_exec += te_
         m_sum += raster.frame_stats()["num_intersections"]
     nv = max(1, len(views))
     tests_v, hits_v, m_v = tests / nv, hits / nv, m_sum / nv
@@ -318,16 +323,22 @@ def run_ours(args):
         stages.append({"stage": tag, "bound": bound, "ms_per_launch": ms, "achieved": ach, "peak": peak, "unit": unit,
                        "frac": ach / peak, "algorithmic_work": what})
 
-    add_stage("render::project", "hbm", n * (48 + 56 + 192 * vis_frac), 1e9, hbm_peak, "GB/s", "48+56+192 B/particle")
-    add_stage("render::expand", "hbm", n * 44 + m_v * 8, 1e9, hbm_peak, "GB/s", "44 B/particle + 8 B/intersection")
+    add_stage("render::project", "hbm", n * (48 + 72 + 192 * vis_frac), 1e9, hbm_peak, "GB/s",
+              "48 B parameters + 192 B SH in, 72 B projected record out per particle")
+    add_stage("render::expand", "hbm", n * 16 + m_v * 8, 1e9, hbm_peak, "GB/s", "16 B culled-box record per particle + 8 B per intersection")
     add_stage("render::sort", "hbm", m_v * (8 + 4), 1e9, hbm_peak, "GB/s",
-              "8 B bucket read + 4 B sorted-list write per intersection (the passes run in shared memory)")
+              "8 B bucket read + 4 B sorted-list write per intersection (the counting pass runs in shared memory)")
     add_stage("render::render", "fp32", tests_v * FLOP_FWD_TEST + hits_v * FLOP_FWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "71 FLOP/test + 32 FLOP/hit")
     add_stage("render-backward::render", "fp32", tests_v * FLOP_BWD_TEST + hits_v * FLOP_BWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "100 FLOP/test + 250 FLOP/hit")
-    add_stage("render-backward::project", "hbm", n * (48 + 16 + 64 + 48 + 192), 1e9, hbm_peak, "GB/s",
-              "48 B params + 16 B colour + 64 B accumulators in, 48 + 192 B gradients out per particle (accumulation re-reads not counted)")
+    if args.exchange == "deferred":
+        add_stage("render-backward::project", "hbm", n * (16 + 32 + 12), 1e9, hbm_peak, "GB/s",
+                  "per view: 16 B colour + one 32 B accumulator sector in, 12 B colour gradient out per particle "
+                  "(the [N,12] / [N,48] conversions run once per step, outside the per-view stages)")
+    else:
+        add_stage("render-backward::project", "hbm", n * (48 + 16 + 64 + 48 + 192), 1e9, hbm_peak, "GB/s",
+                  "48 B params + 16 B colour + 64 B accumulators in, 48 + 192 B gradients out per particle (accumulation re-reads not counted)")
     dominant = max(stages, key=lambda s: s["ms_per_launch"]) if stages else None
     roofline = None
     if dominant:
@@ -495,7 +506,8 @@ def run_ours(args):
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
-                              "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P},
+                              "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,
+                              "forward_tests_executed_per_pixel": tests_exec / nv / P},
             "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16,
         }
         print(json.dumps(line), flush=True)

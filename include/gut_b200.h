@@ -232,6 +232,17 @@ GUT_API int gut_sh_gradient_expand(GutHandle* h, void* stream, uint32_t num_part
                  const float* d_colour_grads, float* d_particle_radiance_grad, int32_t accumulate);
 
 /*
+ * Packing of the model's parameter tensors into the [N,12] particle_density record and the inverse for its gradient.
+ * Replaces: torch.cat([positions, density, rotation, scale, zeros], dim=1) in threedgut_tracer/tracer.py:176-178 and the
+ * column split autograd derives from it for the backward (tracer.py:265-286 returns the [N,12] gradient, autograd slices it).
+ *   d_positions [N,3], d_density [N,1], d_rotation [N,4] (w,x,y,z; 16-byte aligned), d_scale [N,3]  <->  [N,12]
+ */
+GUT_API int gut_pack_particles(GutHandle* h, void* stream, uint32_t num_particles, const float* d_positions, const float* d_density,
+                 const float* d_rotation, const float* d_scale, float* d_particle_density);
+GUT_API int gut_unpack_particle_gradient(GutHandle* h, void* stream, uint32_t num_particles, const float* d_particle_density_grad,
+                 float* d_positions_grad, float* d_density_grad, float* d_rotation_grad, float* d_scale_grad);
+
+/*
  * Same two calls with HOST buffers: inputs are copied host->device and results
  * device->host inside the call on `stream` (the end-to-end path bench.py times).
  * Particle parameters stay device resident (they are the model, not a per-view

@@ -53,9 +53,9 @@ print("wrote", f"{out_dir}/launches_{tag}.md", f"{out_dir}/ncu_full_{tag}.md")
 
 # ---- DRAM traffic per launch of each stage's kernel -> profiles/traffic.json (bench.py's roofline.traffic) ----------
 import json
-STAGE_OF = {"gut_project_kernel": "render::project", "gut_emit_kernel": "render::expand", "gut_tile_sort_kernel": "render::sort",
+STAGE_OF = {"gut_project_kernel": "render::project", "gut_emit_kernel": "render::expand", "gut_tile_bin_sort_kernel": "render::sort",
             "gut_render_kernel": "render::render", "gut_render_backward_kernel": "render-backward::render",
-            "gut_project_backward_kernel": "render-backward::project"}
+            "gut_colour_gradient_kernel": "render-backward::project"}
 traffic = {"source": f"profiles/ncu_full_{tag}.md (ncu --set full, one view of the bench workload)", "stages": {}}
 ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -64,6 +64,8 @@ for r in rows[2:]:
     for k, st in STAGE_OF.items():
         if name == k:
             b = float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]]
-            traffic["stages"][st] = {"kernel": k, "dram_bytes_per_launch": b}
+            # a kernel launched per variant (the backward: uniform-origin / per-ray origin): the instance that did the work
+            if st not in traffic["stages"] or b > traffic["stages"][st]["dram_bytes_per_launch"]:
+                traffic["stages"][st] = {"kernel": k, "dram_bytes_per_launch": b}
 json.dump(traffic, open(f"{out_dir}/traffic.json", "w"), indent=1)
 print("wrote", f"{out_dir}/traffic.json")

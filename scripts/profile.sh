@@ -11,6 +11,6 @@ $BENCH > $OUT/plain_${TAG}.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $OUT/launches_${TAG}.csv $BENCH > $OUT/ncu_launches_${TAG}.log 2>&1
 echo "launch list rc=$?"
 $ONE > $OUT/plain_one_${TAG}.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:gut_ -s 21 -c 7 -f -o $OUT/prof_${TAG} $ONE > $OUT/ncu_full_${TAG}.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:gut_ -s 33 -c 11 -f -o $OUT/prof_${TAG} $ONE > $OUT/ncu_full_${TAG}.log 2>&1
 echo "full capture rc=$?"
 ls -la $OUT

@@ -284,3 +284,22 @@ def test_empty_and_error_paths(pkg):
     assert torch.equal(rgba_t, rgba_i) and torch.equal(dist_t, dist_i)   # recording does not change the image
     raster.trace_bwd(0, 3, d12b, sphb, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
                      rgba_t, torch.ones_like(rgba_t), dist_t, torch.ones_like(dist_t))
+
+
+def test_pack_and_unpack_kernels_equal_cat_and_split():
+    """gut_pack_particles / gut_unpack_particle_gradient against the torch.cat / torch.split they replace (tracer.py:176-178)."""
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = native.SplatRaster(cfg_from_conf(make_conf()))
+    for n in (1, 33, 100_003):
+        g = torch.Generator(device="cuda").manual_seed(n)
+        pos, dns = torch.randn((n, 3), device="cuda", generator=g), torch.rand((n, 1), device="cuda", generator=g)
+        rot, scl = torch.randn((n, 4), device="cuda", generator=g), torch.rand((n, 3), device="cuda", generator=g)
+        packed = raster.pack_particles(pos, dns, rot, scl)
+        assert torch.equal(packed, torch.cat([pos, dns, rot, scl, torch.zeros_like(dns)], dim=1))
+        grad = torch.randn((n, 12), device="cuda", generator=g)
+        parts = raster.unpack_particle_gradient(grad)
+        for a, b in zip(parts, torch.split(grad, [3, 1, 4, 3, 1], dim=1)):
+            assert a.is_contiguous() and torch.equal(a, b)
+    with pytest.raises(native.GutError):
+        raster.pack_particles(torch.zeros((4, 3), device="cuda"), torch.zeros((4, 1), device="cuda"), torch.zeros((4, 3), device="cuda"),
+                              torch.zeros((4, 3), device="cuda"))
