@@ -15,6 +15,8 @@ _LAZY = {
     "load_library": ".native",
     "ShutterType": ".abi",
     "default_config": ".abi",
+    "SelectiveAdam": ".optimizers",
+    "update_gradient_buffer": ".optimizers",
 }
 
 

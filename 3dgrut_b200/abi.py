@@ -131,6 +131,28 @@ class GutFrameStats(C.Structure):
     ]
 
 
+class Activation(enum.IntEnum):
+    """GutActivation (include/gut_b200.h): the model's activation table, threedgrut/utils/misc.py:48-53."""
+    NONE = 0
+    EXP = 1
+    SIGMOID = 2
+
+
+GUT_ADAM_MAX_GROUPS = 8
+
+
+class GutAdamGroup(C.Structure):
+    """One parameter group of gut_selective_adam_step: contiguous fp32 [N, width] tensors and its learning rate."""
+    _fields_ = [
+        ("param", C.c_void_p),
+        ("grad", C.c_void_p),
+        ("exp_avg", C.c_void_p),
+        ("exp_avg_sq", C.c_void_p),
+        ("width", C.c_uint32),
+        ("lr", C.c_float),
+    ]
+
+
 def _fill(arr, values, n):
     vals = [float(v) for v in values]
     if len(vals) != n:

@@ -248,6 +248,7 @@ size_t gut_sizeof_config(void) { return sizeof(GutConfig); }
 size_t gut_sizeof_camera(void) { return sizeof(GutCamera); }
 size_t gut_sizeof_stage_outputs(void) { return sizeof(GutStageOutputs); }
 size_t gut_sizeof_frame_stats(void) { return sizeof(GutFrameStats); }
+size_t gut_sizeof_adam_group(void) { return sizeof(GutAdamGroup); }
 
 int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
     if (!cfg || !out) return GUT_ERR_BAD_INPUT;
@@ -534,6 +535,92 @@ int gut_unpack_particle_gradient(GutHandle* h, void* stream_, uint32_t N, const 
     DeviceGuard guard(h->device);
     GUT_CUDA(h, gut_launch_unpack_gradient(N, d_particle_density_grad, d_positions_grad, d_density_grad, d_rotation_grad, d_scale_grad,
                                            (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+static bool valid_activation(int32_t a) { return a == GUT_ACT_NONE || a == GUT_ACT_EXP || a == GUT_ACT_SIGMOID; }
+
+int gut_activate_pack(GutHandle* h, void* stream_, uint32_t N, const float* d_positions, const float* d_rotation_raw, const float* d_scale_raw,
+                      const float* d_density_raw, int32_t scale_activation, int32_t density_activation, float* d_particle_density) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!valid_activation(scale_activation) || !valid_activation(density_activation)) return fail(h, GUT_ERR_BAD_INPUT, "unknown activation");
+    if (N == 0) return GUT_OK;
+    if (!d_positions || !d_rotation_raw || !d_scale_raw || !d_density_raw || !d_particle_density) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (((uintptr_t)d_rotation_raw | (uintptr_t)d_particle_density) & 15) return fail(h, GUT_ERR_BAD_INPUT, "rotation / packed buffers must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_activate_pack(N, d_positions, d_rotation_raw, d_scale_raw, d_density_raw, scale_activation, density_activation,
+                                         d_particle_density, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_activate_pack_backward(GutHandle* h, void* stream_, uint32_t N, const float* d_rotation_raw, const float* d_particle_density,
+                               const float* d_particle_density_grad, int32_t scale_activation, int32_t density_activation,
+                               float* d_positions_grad, float* d_rotation_grad, float* d_scale_grad, float* d_density_grad) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!valid_activation(scale_activation) || !valid_activation(density_activation)) return fail(h, GUT_ERR_BAD_INPUT, "unknown activation");
+    if (N == 0) return GUT_OK;
+    if (!d_rotation_raw || !d_particle_density || !d_particle_density_grad || !d_positions_grad || !d_rotation_grad || !d_scale_grad || !d_density_grad)
+        return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (((uintptr_t)d_rotation_raw | (uintptr_t)d_particle_density | (uintptr_t)d_particle_density_grad | (uintptr_t)d_rotation_grad) & 15)
+        return fail(h, GUT_ERR_BAD_INPUT, "rotation / packed buffers must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_activate_backward(N, d_rotation_raw, d_particle_density, d_particle_density_grad, scale_activation, density_activation,
+                                             d_positions_grad, d_rotation_grad, d_scale_grad, d_density_grad, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_pack_features(GutHandle* h, void* stream_, uint32_t N, const float* d_albedo, const float* d_specular, float* d_particle_radiance) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_pack_features is built for 16 SH coefficients (3 + 45 floats)");
+    if (N == 0) return GUT_OK;
+    if (!d_albedo || !d_specular || !d_particle_radiance) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if ((uintptr_t)d_particle_radiance & 15) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_pack_features(N, d_albedo, d_specular, d_particle_radiance, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_unpack_feature_gradient(GutHandle* h, void* stream_, uint32_t N, const float* d_particle_radiance_grad, float* d_albedo_grad,
+                                float* d_specular_grad) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_unpack_feature_gradient is built for 16 SH coefficients (3 + 45 floats)");
+    if (N == 0) return GUT_OK;
+    if (!d_particle_radiance_grad || !d_albedo_grad || !d_specular_grad) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if ((uintptr_t)d_particle_radiance_grad & 15) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_unpack_features(N, d_particle_radiance_grad, d_albedo_grad, d_specular_grad, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_selective_adam_step(GutHandle* h, void* stream_, uint32_t N, const GutAdamGroup* groups, uint32_t num_groups, const float* d_visibility,
+                            float beta1, float beta2, float eps, int32_t zero_grad) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (num_groups > GUT_ADAM_MAX_GROUPS) return fail(h, GUT_ERR_BAD_INPUT, "at most %d parameter groups per call", GUT_ADAM_MAX_GROUPS);
+    if (N == 0 || num_groups == 0) return GUT_OK;
+    if (!groups) return fail(h, GUT_ERR_BAD_INPUT, "groups is NULL");
+    for (uint32_t i = 0; i < num_groups; ++i) {
+        if (!groups[i].param || !groups[i].grad || !groups[i].exp_avg || !groups[i].exp_avg_sq) return fail(h, GUT_ERR_BAD_INPUT, "null pointer in group %u", i);
+        if (groups[i].width == 0) return fail(h, GUT_ERR_BAD_INPUT, "group %u has width 0", i);
+    }
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_selective_adam(N, groups, num_groups, d_visibility, beta1, beta2, eps, zero_grad, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_densify_stats(GutHandle* h, void* stream_, uint32_t N, const float* d_positions, const float* d_positions_grad, const float* sensor_position,
+                      float* d_accum, float* d_denom) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (N == 0) return GUT_OK;
+    if (!d_positions || !d_positions_grad || !sensor_position || !d_accum || !d_denom) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_densify_stats(N, d_positions, d_positions_grad, make_float3(sensor_position[0], sensor_position[1], sensor_position[2]),
+                                         d_accum, d_denom, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;
 }

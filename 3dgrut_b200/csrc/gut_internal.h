@@ -118,5 +118,17 @@ cudaError_t gut_launch_pack_particles(uint32_t N, const float* pos, const float*
                                       cudaStream_t stream);
 cudaError_t gut_launch_unpack_gradient(uint32_t N, const float* grad12, float* pos, float* dens, float* rot, float* scale, cudaStream_t stream);
 
+// model-side passes (gut_model.cu): fused activations + packing, feature cat / split, SelectiveAdam, densification statistics
+cudaError_t gut_launch_activate_pack(uint32_t N, const float* pos, const float* rot, const float* scale, const float* dens, int scale_act,
+                                     int density_act, float* out12, cudaStream_t stream);
+cudaError_t gut_launch_activate_backward(uint32_t N, const float* rot, const float* packed12, const float* grad12, int scale_act, int density_act,
+                                         float* pos_g, float* rot_g, float* scale_g, float* dens_g, cudaStream_t stream);
+cudaError_t gut_launch_pack_features(uint32_t N, const float* albedo, const float* specular, float* out48, cudaStream_t stream);
+cudaError_t gut_launch_unpack_features(uint32_t N, const float* grad48, float* albedo_g, float* specular_g, cudaStream_t stream);
+cudaError_t gut_launch_selective_adam(uint32_t N, const GutAdamGroup* groups, uint32_t n_groups, const float* visibility, float b1, float b2,
+                                      float eps, int zero_grad, cudaStream_t stream);
+cudaError_t gut_launch_densify_stats(uint32_t N, const float* pos, const float* pos_g, float3 sensor, float* accum, float* denom,
+                                     cudaStream_t stream);
+
 cudaError_t gut_launch_fill_outputs(uint32_t num_pixels, float* rgba, float* dist, float* hits, cudaStream_t stream);
 cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream);

@@ -75,6 +75,18 @@ def load_library():
     lib.gut_pack_particles.restype = C.c_int
     lib.gut_unpack_particle_gradient.argtypes = [vp, vp, u32, fp, fp, fp, fp, fp]
     lib.gut_unpack_particle_gradient.restype = C.c_int
+    lib.gut_activate_pack.argtypes = [vp, vp, u32, fp, fp, fp, fp, i32, i32, fp]
+    lib.gut_activate_pack.restype = C.c_int
+    lib.gut_activate_pack_backward.argtypes = [vp, vp, u32, fp, fp, fp, i32, i32, fp, fp, fp, fp]
+    lib.gut_activate_pack_backward.restype = C.c_int
+    lib.gut_pack_features.argtypes = [vp, vp, u32, fp, fp, fp]
+    lib.gut_pack_features.restype = C.c_int
+    lib.gut_unpack_feature_gradient.argtypes = [vp, vp, u32, fp, fp, fp]
+    lib.gut_unpack_feature_gradient.restype = C.c_int
+    lib.gut_selective_adam_step.argtypes = [vp, vp, u32, C.POINTER(abi.GutAdamGroup), u32, fp, C.c_float, C.c_float, C.c_float, i32]
+    lib.gut_selective_adam_step.restype = C.c_int
+    lib.gut_densify_stats.argtypes = [vp, vp, u32, fp, fp, C.POINTER(C.c_float), fp, fp]
+    lib.gut_densify_stats.restype = C.c_int
     lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
     lib.gut_forward_host.restype = C.c_int
     lib.gut_backward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, i32]
@@ -92,12 +104,15 @@ def load_library():
     lib.gut_measure_work.restype = C.c_int
     lib.gut_last_error.argtypes = [vp]
     lib.gut_last_error.restype = C.c_char_p
-    for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats"):
+    for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats",
+                 "gut_sizeof_adam_group"):
         getattr(lib, name).restype = C.c_size_t
     if lib.gut_abi_version() != abi.GUT_ABI_VERSION:
         raise ImportError(f"libgut_b200 ABI {lib.gut_abi_version()} != python mirror {abi.GUT_ABI_VERSION}")
     if lib.gut_sizeof_config() != C.sizeof(abi.GutConfig) or lib.gut_sizeof_camera() != C.sizeof(abi.GutCamera):
         raise ImportError("libgut_b200 struct layout differs from 3dgrut_b200/abi.py")
+    if lib.gut_sizeof_adam_group() != C.sizeof(abi.GutAdamGroup):
+        raise ImportError("libgut_b200 GutAdamGroup layout differs from 3dgrut_b200/abi.py")
     _lib = lib
     return lib
 
@@ -352,6 +367,122 @@ class SplatRaster:
         if rc != 0:
             self._raise(rc)
         return pos, dns, rot, scl
+
+    # ---- model-side passes ---------------------------------------------------------
+    def activate_pack(self, positions, rotation_raw, scale_raw, density_raw, scale_activation=abi.Activation.EXP,
+                      density_activation=abi.Activation.SIGMOID):
+        """gut_activate_pack: raw parameters -> [N,12] record with normalize / scale / density activations applied
+        (model.py:77-93 + tracer.py:176-178 in one pass)."""
+        dev = self.device
+        pos = _check_cuda_f32("positions", positions, dev)
+        rot = _check_cuda_f32("rotation", rotation_raw, dev)
+        scl = _check_cuda_f32("scale", scale_raw, dev)
+        dns = _check_cuda_f32("density", density_raw, dev)
+        n = pos.shape[0]
+        if pos.shape != (n, 3) or dns.shape != (n, 1) or rot.shape != (n, 4) or scl.shape != (n, 3):
+            raise GutError(abi.GutStatus.BAD_INPUT, "expected positions [N,3], rotation [N,4], scale [N,3], density [N,1]")
+        out = torch.empty((n, 12), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_activate_pack(self._h, self._stream(), n, _ptr(pos), _ptr(rot), _ptr(scl), _ptr(dns), int(scale_activation),
+                                        int(density_activation), _ptr(out))
+        if rc != 0:
+            self._raise(rc)
+        return out
+
+    def activate_pack_backward(self, rotation_raw, particle_density, density_grad, scale_activation=abi.Activation.EXP,
+                               density_activation=abi.Activation.SIGMOID):
+        """gut_activate_pack_backward: [N,12] gradient -> gradients of the RAW (positions, rotation, scale, density)."""
+        dev = self.device
+        rot = _check_cuda_f32("rotation", rotation_raw, dev)
+        pk = _check_cuda_f32("particle_density", particle_density, dev)
+        g = _check_cuda_f32("density_grad", density_grad, dev)
+        n = rot.shape[0]
+        if rot.shape != (n, 4) or pk.shape != (n, 12) or g.shape != (n, 12):
+            raise GutError(abi.GutStatus.BAD_INPUT, "expected rotation [N,4], particle_density [N,12], density_grad [N,12]")
+        pos_g = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        rot_g = torch.empty((n, 4), dtype=torch.float32, device=dev)
+        scl_g = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        dns_g = torch.empty((n, 1), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_activate_pack_backward(self._h, self._stream(), n, _ptr(rot), _ptr(pk), _ptr(g), int(scale_activation),
+                                                 int(density_activation), _ptr(pos_g), _ptr(rot_g), _ptr(scl_g), _ptr(dns_g))
+        if rc != 0:
+            self._raise(rc)
+        return pos_g, rot_g, scl_g, dns_g
+
+    def pack_features(self, features_albedo, features_specular):
+        """gut_pack_features: cat((albedo [N,3], specular [N,45]), dim=1) -> [N,48] (model.py:74-75)."""
+        dev = self.device
+        alb = _check_cuda_f32("features_albedo", features_albedo, dev)
+        spc = _check_cuda_f32("features_specular", features_specular, dev)
+        n = alb.shape[0]
+        if alb.shape != (n, 3) or spc.shape != (n, 45):
+            raise GutError(abi.GutStatus.BAD_INPUT, "expected features_albedo [N,3] and features_specular [N,45]")
+        out = torch.empty((n, 48), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_pack_features(self._h, self._stream(), n, _ptr(alb), _ptr(spc), _ptr(out))
+        if rc != 0:
+            self._raise(rc)
+        return out
+
+    def unpack_feature_gradient(self, radiance_grad):
+        """gut_unpack_feature_gradient: [N,48] gradient -> (albedo [N,3], specular [N,45]) gradients."""
+        dev = self.device
+        g = _check_cuda_f32("radiance_grad", radiance_grad, dev)
+        n = g.shape[0]
+        if g.shape != (n, 48):
+            raise GutError(abi.GutStatus.BAD_INPUT, "radiance_grad must be [N,48]")
+        alb = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        spc = torch.empty((n, 45), dtype=torch.float32, device=dev)
+        rc = self.lib.gut_unpack_feature_gradient(self._h, self._stream(), n, _ptr(g), _ptr(alb), _ptr(spc))
+        if rc != 0:
+            self._raise(rc)
+        return alb, spc
+
+    def selective_adam_step(self, groups, visibility, beta1, beta2, eps, zero_grad=False):
+        """gut_selective_adam_step.  ``groups`` is a list of (param, grad, exp_avg, exp_avg_sq, lr); every tensor a contiguous
+        float32 CUDA [N, ...] tensor, updated in place.  ``visibility`` is the tracer's mog_visibility ([N,1] float) or None."""
+        if len(groups) == 0:
+            return
+        if len(groups) > abi.GUT_ADAM_MAX_GROUPS:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"at most {abi.GUT_ADAM_MAX_GROUPS} parameter groups per call")
+        dev = self.device
+        n = groups[0][0].shape[0]
+        arr = (abi.GutAdamGroup * len(groups))()
+        for i, (p, g, m, v, lr) in enumerate(groups):
+            for name, t in (("param", p), ("grad", g), ("exp_avg", m), ("exp_avg_sq", v)):
+                if not t.is_cuda or t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
+                    raise GutError(abi.GutStatus.BAD_INPUT, f"group {i}: {name} must be a contiguous float32 tensor on {dev}")
+                if t.shape != p.shape:
+                    raise GutError(abi.GutStatus.BAD_INPUT, f"group {i}: {name} has shape {tuple(t.shape)}, param {tuple(p.shape)}")
+            if p.shape[0] != n:
+                raise GutError(abi.GutStatus.BAD_INPUT, f"group {i} has {p.shape[0]} rows, group 0 has {n}")
+            arr[i].param, arr[i].grad, arr[i].exp_avg, arr[i].exp_avg_sq = p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr()
+            arr[i].width = p.numel() // max(n, 1)
+            arr[i].lr = float(lr)
+        vis = None
+        if visibility is not None:
+            vis = visibility.reshape(-1)
+            if vis.dtype != torch.float32:
+                vis = vis.to(torch.float32)
+            vis = _check_cuda_f32("visibility", vis, dev)
+            if vis.shape[0] != n:
+                raise GutError(abi.GutStatus.BAD_INPUT, f"visibility has {vis.shape[0]} rows, parameters {n}")
+        rc = self.lib.gut_selective_adam_step(self._h, self._stream(), n, arr, len(groups), _ptr(vis), float(beta1), float(beta2), float(eps),
+                                              1 if zero_grad else 0)
+        if rc != 0:
+            self._raise(rc)
+
+    def densify_stats(self, positions, positions_grad, sensor_position, grad_norm_accum, grad_norm_denom):
+        """gut_densify_stats: GSStrategy.update_gradient_buffer (strategy/gs.py:104-115), in place on accum / denom [N,1]."""
+        dev = self.device
+        pos = _check_cuda_f32("positions", positions, dev)
+        g = _check_cuda_f32("positions_grad", positions_grad, dev)
+        n = pos.shape[0]
+        for name, t in (("grad_norm_accum", grad_norm_accum), ("grad_norm_denom", grad_norm_denom)):
+            if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != n:
+                raise GutError(abi.GutStatus.BAD_INPUT, f"{name} must be a contiguous float32 CUDA tensor with N elements")
+        sp = (C.c_float * 3)(*[float(x) for x in sensor_position])
+        rc = self.lib.gut_densify_stats(self._h, self._stream(), n, _ptr(pos), _ptr(g), sp, _ptr(grad_norm_accum), _ptr(grad_norm_denom))
+        if rc != 0:
+            self._raise(rc)
 
     def set_training(self, training: bool):
         """gut_set_training: training=False skips the hit-mask recording of the forward (inference); no backward may follow."""

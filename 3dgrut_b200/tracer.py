@@ -66,6 +66,29 @@ def config_from_conf(conf) -> abi.GutConfig:
     return d
 
 
+_KNOWN_ACTIVATIONS = {torch.exp: abi.Activation.EXP, torch.sigmoid: abi.Activation.SIGMOID}
+
+
+def _raw_parameters(gaussians):
+    """(scale_activation, density_activation) when ``gaussians`` exposes the reference model's raw parameters and its
+    activations are ones libgut_b200 implements (MixtureOfGaussians: model.py:163-167, 480-485; table utils/misc.py:48-53);
+    None otherwise, in which case render() calls get_rotation() / get_scale() / get_density() / get_features() as the
+    reference does."""
+    for name in ("rotation", "scale", "density", "features_albedo", "features_specular"):
+        if not torch.is_tensor(getattr(gaussians, name, None)):
+            return None
+    if getattr(gaussians, "rotation_activation", None) is not torch.nn.functional.normalize:
+        return None
+    scale_act = _KNOWN_ACTIVATIONS.get(getattr(gaussians, "scale_activation", None))
+    density_act = _KNOWN_ACTIVATIONS.get(getattr(gaussians, "density_activation", None))
+    if scale_act is None or density_act is None:
+        return None
+    n = gaussians.positions.shape[0]
+    if gaussians.features_albedo.shape != (n, 3) or gaussians.features_specular.shape != (n, 45):
+        return None
+    return int(scale_act), int(density_act)
+
+
 class Tracer:
     class _Autograd(torch.autograd.Function):
         """reference: Tracer._Autograd (tracer.py:159-286)."""
@@ -99,9 +122,46 @@ class Tracer:
             pos_g, dns_g, rot_g, scl_g = ctx.tracer_wrapper.unpack_particle_gradient(density_grad)
             return (None, None, None, None, None, pos_g, rot_g, scl_g, dns_g, radiance_grad, None)
 
+    class _AutogradRaw(torch.autograd.Function):
+        """The same call with the model's RAW parameters: the activations of model.py:77-93, the feature
+        cat of model.py:74-75 and the [N,12] packing of tracer.py:176-178 are one kernel each way instead of ~10 torch
+        kernels and their autograd mirror images.  Gradients come back for the raw nn.Parameters."""
+
+        @staticmethod
+        def forward(ctx, tracer_wrapper, frame_id, n_active_features, ray_ori, ray_dir, mog_pos, rot_raw, scl_raw, dns_raw, albedo, specular,
+                    sensor, scale_act, density_act):
+            particle_density = tracer_wrapper.activate_pack(mog_pos, rot_raw, scl_raw, dns_raw, scale_act, density_act)
+            particle_radiance = tracer_wrapper.pack_features(albedo, specular)
+            rgba, dist, hits, vis = tracer_wrapper.trace(frame_id, n_active_features, particle_density, particle_radiance,
+                                                         ray_ori, ray_dir, None, sensor)
+            ctx.save_for_backward(ray_ori, ray_dir, rgba, dist, particle_density, particle_radiance, rot_raw)
+            ctx.frame_id = frame_id
+            ctx.n_active_features = n_active_features
+            ctx.sensor = sensor
+            ctx.tracer_wrapper = tracer_wrapper
+            ctx.activations = (scale_act, density_act)
+            ctx.mark_non_differentiable(hits, vis)
+            return rgba, dist, hits, vis
+
+        @staticmethod
+        def backward(ctx, rgba_grad, dist_grad, _hits_grad_unused, _vis_grad_unused):
+            ray_ori, ray_dir, rgba, dist, particle_density, particle_radiance, rot_raw = ctx.saved_tensors
+            if rgba_grad is None:
+                rgba_grad = torch.zeros_like(rgba)
+            if dist_grad is None:
+                dist_grad = torch.zeros_like(dist)
+            density_grad, radiance_grad = ctx.tracer_wrapper.trace_bwd(
+                ctx.frame_id, ctx.n_active_features, particle_density, particle_radiance, ray_ori, ray_dir, None, ctx.sensor,
+                0, 1, None, None, rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous())
+            pos_g, rot_g, scl_g, dns_g = ctx.tracer_wrapper.activate_pack_backward(rot_raw, particle_density, density_grad, *ctx.activations)
+            alb_g, spc_g = ctx.tracer_wrapper.unpack_feature_gradient(radiance_grad)
+            return (None, None, None, None, None, pos_g, rot_g, scl_g, dns_g, alb_g, spc_g, None, None, None)
+
     def __init__(self, conf):
         self.device = "cuda"
         self.conf = conf
+        # render.fused_activations (not a reference key; default on): take the model's raw parameters when it exposes them
+        self.fused_activations = bool(_get(conf, "render.fused_activations", True))
         torch.zeros(1, device=self.device)  # force CUDA context creation, as the reference does (tracer.py:292)
         self.tracer_wrapper = SplatRaster(config_from_conf(conf))
 
@@ -119,11 +179,20 @@ class Tracer:
         num_gaussians = gaussians.num_gaussians
         # under torch.no_grad() (validation / rendering) no backward can follow: skip the forward's hit-mask recording
         self.tracer_wrapper.set_training(torch.is_grad_enabled())
+        raw = _raw_parameters(gaussians) if self.fused_activations else None
         with torch.cuda.nvtx.range(f"model.forward({num_gaussians} gaussians)"):
-            pred_rgba, pred_dist, hits_count, mog_visibility = Tracer._Autograd.apply(
-                self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),
-                gaussians.positions.contiguous(), gaussians.get_rotation().contiguous(), gaussians.get_scale().contiguous(),
-                gaussians.get_density().contiguous(), gaussians.get_features().contiguous(), sensor)
+            if raw is not None:
+                scale_act, density_act = raw
+                pred_rgba, pred_dist, hits_count, mog_visibility = Tracer._AutogradRaw.apply(
+                    self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),
+                    gaussians.positions.contiguous(), gaussians.rotation.contiguous(), gaussians.scale.contiguous(),
+                    gaussians.density.contiguous(), gaussians.features_albedo.contiguous(), gaussians.features_specular.contiguous(),
+                    sensor, scale_act, density_act)
+            else:
+                pred_rgba, pred_dist, hits_count, mog_visibility = Tracer._Autograd.apply(
+                    self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),
+                    gaussians.positions.contiguous(), gaussians.get_rotation().contiguous(), gaussians.get_scale().contiguous(),
+                    gaussians.get_density().contiguous(), gaussians.get_features().contiguous(), sensor)
             pred_rgb = pred_rgba[..., :3].unsqueeze(0).contiguous()
             pred_opacity = pred_rgba[..., 3:].unsqueeze(0).contiguous()
             pred_dist = pred_dist.unsqueeze(0).contiguous()

@@ -243,6 +243,55 @@ GUT_API int gut_unpack_particle_gradient(GutHandle* h, void* stream, uint32_t nu
                  float* d_positions_grad, float* d_density_grad, float* d_rotation_grad, float* d_scale_grad);
 
 /*
+ * Activation + packing fused at the Tracer boundary: raw model parameters in, packed records out.
+ * Replaces, in one pass each way: rotation_activation = torch.nn.functional.normalize, scale_activation (exp),
+ * density_activation (sigmoid) of threedgrut/model/model.py:77-93 (table threedgrut/utils/misc.py:48-53), the
+ * torch.cat of threedgut_tracer/tracer.py:176-178, get_features() = torch.cat((albedo, specular), dim=1) of
+ * model.py:74-75, and the autograd mirror image of all of them.
+ *   d_positions [N,3], d_rotation_raw [N,4] (16-byte aligned), d_scale_raw [N,3], d_density_raw [N,1]  ->  [N,12]
+ *   d_features_albedo [N,3], d_features_specular [N,45]  <->  [N,48]
+ * gut_activate_pack_backward takes the packed record the forward produced (activated scale / density are read from
+ * it) and the [N,12] gradient gut_backward wrote; it writes the gradients of the RAW parameters.
+ */
+enum GutActivation { GUT_ACT_NONE = 0, GUT_ACT_EXP = 1, GUT_ACT_SIGMOID = 2 };
+GUT_API int gut_activate_pack(GutHandle* h, void* stream, uint32_t num_particles, const float* d_positions, const float* d_rotation_raw,
+                 const float* d_scale_raw, const float* d_density_raw, int32_t scale_activation, int32_t density_activation,
+                 float* d_particle_density);
+GUT_API int gut_activate_pack_backward(GutHandle* h, void* stream, uint32_t num_particles, const float* d_rotation_raw,
+                 const float* d_particle_density, const float* d_particle_density_grad, int32_t scale_activation,
+                 int32_t density_activation, float* d_positions_grad, float* d_rotation_grad, float* d_scale_grad,
+                 float* d_density_grad);
+GUT_API int gut_pack_features(GutHandle* h, void* stream, uint32_t num_particles, const float* d_features_albedo,
+                 const float* d_features_specular, float* d_particle_radiance);
+GUT_API int gut_unpack_feature_gradient(GutHandle* h, void* stream, uint32_t num_particles, const float* d_particle_radiance_grad,
+                 float* d_features_albedo_grad, float* d_features_specular_grad);
+
+/*
+ * The optimiser step after the gradient exchange.
+ * gut_selective_adam_step replaces SelectiveAdam.step (threedgrut/optimizers/__init__.py:88-133) and its kernel
+ * selective_adam_update_kernel (threedgrut/optimizers/optimizers.cu:47-84), for every parameter group in ONE launch:
+ *     m = b1 m + (1 - b1) g ;  v = b2 v + (1 - b2) g g ;  param += -lr m / (sqrt(v) + eps)        (no bias correction)
+ * applied to the rows whose d_visibility entry is non-zero (the tracer's mog_visibility [N,1]; NULL = every row).
+ * Invisible rows keep param, exp_avg and exp_avg_sq.  zero_grad != 0 also clears every gradient (optimizer.zero_grad(),
+ * threedgrut/trainer.py:751).  Each group is a contiguous fp32 [N, width] tensor with its own learning rate.
+ * gut_densify_stats replaces GSStrategy.update_gradient_buffer (threedgrut/strategy/gs.py:104-115): for particles whose
+ * position gradient is non-zero, accum += |grad * |position - sensor_position|| / 2 and denom += 1.
+ */
+#define GUT_ADAM_MAX_GROUPS 8
+typedef struct GutAdamGroup {
+    float*       param;       /* [N, width] */
+    const float* grad;        /* [N, width]; written (zeroed) when zero_grad != 0 */
+    float*       exp_avg;     /* [N, width] */
+    float*       exp_avg_sq;  /* [N, width] */
+    uint32_t     width;
+    float        lr;
+} GutAdamGroup;
+GUT_API int gut_selective_adam_step(GutHandle* h, void* stream, uint32_t num_particles, const GutAdamGroup* groups, uint32_t num_groups,
+                 const float* d_visibility, float beta1, float beta2, float eps, int32_t zero_grad);
+GUT_API int gut_densify_stats(GutHandle* h, void* stream, uint32_t num_particles, const float* d_positions, const float* d_positions_grad,
+                 const float* sensor_position /* host [3] */, float* d_grad_norm_accum, float* d_grad_norm_denom);
+
+/*
  * Same two calls with HOST buffers: inputs are copied host->device and results
  * device->host inside the call on `stream` (the end-to-end path bench.py times).
  * Particle parameters stay device resident (they are the model, not a per-view
@@ -301,6 +350,7 @@ GUT_API size_t      gut_sizeof_config(void);
 GUT_API size_t      gut_sizeof_camera(void);
 GUT_API size_t      gut_sizeof_stage_outputs(void);
 GUT_API size_t      gut_sizeof_frame_stats(void);
+GUT_API size_t      gut_sizeof_adam_group(void);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,248 @@
+"""GPU parity of the model-side kernels through the C ABI, against oracle/model_oracle.py and
+against the torch functions / literal reference code they replace."""
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as mo
+from tests.helpers import SyntheticGaussians, cfg_from_conf, make_batch, make_conf, rel_l2, syn
+
+pytestmark = pytest.mark.gpu
+
+TOL_ACT = 2e-6     # fp32 activations: CUDA expf vs libm / torch (relative)
+
+
+@pytest.fixture(scope="module")
+def native():
+    return importlib.import_module("3dgrut_b200.native")
+
+
+@pytest.fixture(scope="module")
+def raster(native):
+    return native.SplatRaster(cfg_from_conf(make_conf()))
+
+
+def _raw(n, seed, device="cuda"):
+    g = torch.Generator().manual_seed(seed)
+    raw = {
+        "positions": torch.randn(n, 3, generator=g),
+        "rotation": torch.rand(n, 4, generator=g) + 0.05,
+        "scale": torch.randn(n, 3, generator=g) * 0.7 - 3.0,
+        "density": torch.randn(n, 1, generator=g) * 2.0,
+        "albedo": torch.rand(n, 3, generator=g),
+        "specular": torch.randn(n, 45, generator=g) * 0.05,
+    }
+    return {k: v.to(device) for k, v in raw.items()}
+
+
+@pytest.mark.parametrize("n", [1, 31, 100_003])
+def test_activate_pack_forward_and_backward(raster, n):
+    raw = _raw(n, n)
+    cpu = {k: v.cpu().numpy() for k, v in raw.items()}
+    packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
+    want = mo.activate_pack(cpu["positions"], cpu["rotation"], cpu["scale"], cpu["density"])
+    np.testing.assert_allclose(packed.cpu().numpy(), want, rtol=TOL_ACT, atol=1e-7)
+    assert torch.equal(packed[:, 0:3], raw["positions"]) and (packed[:, 11] == 0).all()
+    # the torch chain of the reference (model.py:77-93, tracer.py:176-178)
+    dns = torch.sigmoid(raw["density"])
+    ref = torch.cat([raw["positions"], dns, torch.nn.functional.normalize(raw["rotation"]), torch.exp(raw["scale"]), torch.zeros_like(dns)], dim=1)
+    np.testing.assert_allclose(packed.cpu().numpy(), ref.cpu().numpy(), rtol=TOL_ACT, atol=1e-7)
+
+    g12 = torch.randn((n, 12), device="cuda", generator=torch.Generator(device="cuda").manual_seed(n + 1))
+    got = raster.activate_pack_backward(raw["rotation"], packed, g12)
+    exp = mo.activate_pack_backward(cpu["rotation"], packed.cpu().numpy(), g12.cpu().numpy())
+    for name, a, b in zip(("positions", "rotation", "scale", "density"), got, exp):
+        assert a.is_contiguous()
+        assert rel_l2(a.cpu().numpy(), b) <= TOL_ACT, name
+    # and against autograd of the torch chain
+    leaves = {k: raw[k].clone().requires_grad_(True) for k in ("positions", "rotation", "scale", "density")}
+    d2 = torch.sigmoid(leaves["density"])
+    chain = torch.cat([leaves["positions"], d2, torch.nn.functional.normalize(leaves["rotation"]), torch.exp(leaves["scale"]),
+                       torch.zeros_like(d2)], dim=1)
+    (chain * g12).sum().backward()
+    for name, a in zip(("positions", "rotation", "scale", "density"), got):
+        assert rel_l2(a.cpu().numpy(), leaves[name].grad.cpu().numpy()) <= 1e-5, name
+
+
+def test_activation_kinds_and_degenerate_quaternion(raster, native):
+    raw = _raw(257, 4)
+    raw["rotation"][0] = 0.0          # |q| below the normalize eps: torch clamps the norm
+    packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"], mo.ACT_NONE, mo.ACT_NONE)
+    assert torch.equal(packed[:, 8:11], raw["scale"]) and torch.equal(packed[:, 3:4], raw["density"])
+    assert (packed[0, 4:8] == 0).all()
+    g12 = torch.ones((257, 12), device="cuda")
+    _, rot_g, scl_g, dns_g = raster.activate_pack_backward(raw["rotation"], packed, g12, mo.ACT_NONE, mo.ACT_NONE)
+    assert torch.equal(scl_g, g12[:, 8:11]) and torch.equal(dns_g, g12[:, 3:4])
+    assert torch.allclose(rot_g[0], torch.full((4,), 1e12, device="cuda"), rtol=1e-6)
+    with pytest.raises(native.GutError):
+        raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"], 7, mo.ACT_SIGMOID)
+    with pytest.raises(native.GutError):
+        raster.activate_pack(raw["positions"], raw["rotation"][:, :3], raw["scale"], raw["density"])
+
+
+@pytest.mark.parametrize("n", [1, 5, 65_537])
+def test_feature_cat_and_split_are_exact(raster, n):
+    raw = _raw(n, 11 + n)
+    feats = raster.pack_features(raw["albedo"], raw["specular"])
+    assert torch.equal(feats, torch.cat((raw["albedo"], raw["specular"]), dim=1))
+    g48 = torch.randn((n, 48), device="cuda", generator=torch.Generator(device="cuda").manual_seed(n))
+    alb_g, spc_g = raster.unpack_feature_gradient(g48)
+    assert alb_g.is_contiguous() and spc_g.is_contiguous()
+    assert torch.equal(alb_g, g48[:, :3]) and torch.equal(spc_g, g48[:, 3:])
+
+
+class RawGaussians:
+    """The raw-parameter attributes of MixtureOfGaussians (model.py:163-167, 480-485) plus its activated getters."""
+
+    def __init__(self, raw, n_active_features=3):
+        for k in ("positions", "rotation", "scale", "density"):
+            setattr(self, k, raw[k].clone().requires_grad_(True))
+        self.features_albedo = raw["albedo"].clone().requires_grad_(True)
+        self.features_specular = raw["specular"].clone().requires_grad_(True)
+        self.scale_activation, self.density_activation = torch.exp, torch.sigmoid
+        self.rotation_activation = torch.nn.functional.normalize
+        self.n_active_features = n_active_features
+        self.num_gaussians = self.positions.shape[0]
+
+    def get_rotation(self):
+        return self.rotation_activation(self.rotation)
+
+    def get_scale(self):
+        return self.scale_activation(self.scale)
+
+    def get_density(self):
+        return self.density_activation(self.density)
+
+    def get_features(self):
+        return torch.cat((self.features_albedo, self.features_specular), dim=1)
+
+    def background(self, T_to_world, rays_d, rgb, opacity, train):
+        return rgb, opacity
+
+    def parameters(self):
+        return [self.positions, self.rotation, self.scale, self.density, self.features_albedo, self.features_specular]
+
+
+def _raw_from_scene(scene):
+    """Invert the activations of a synthetic (post-activation) scene: what a MixtureOfGaussians would hold."""
+    raw = {
+        "positions": scene["positions"],
+        "rotation": scene["rotation"] * 1.7,                       # any positive multiple normalises to the same quaternion
+        "scale": torch.log(scene["scale"]),
+        "density": torch.log(scene["density"] / (1 - scene["density"])),
+        "albedo": scene["features"][:, :3].contiguous(),
+        "specular": scene["features"][:, 3:].contiguous(),
+    }
+    return {k: v.cuda() for k, v in raw.items()}
+
+
+def test_tracer_fused_raw_path_equals_torch_activation_path():
+    """Tracer.render with raw parameters (one activation kernel each way) against the reference-shaped path where torch
+    applies the activations and autograd differentiates them."""
+    pkg = importlib.import_module("3dgrut_b200")
+    n, w, h = 3000, 64, 48
+    scene = syn.make_scene(n, 3, seed=21, kind="dense")
+    view = syn.make_view(w, h)
+    raw = _raw_from_scene(scene)
+    outs, grads = [], []
+    for fused in (True, False):
+        conf = make_conf()
+        conf["render"]["fused_activations"] = fused
+        tracer = pkg.Tracer(conf)
+        g = RawGaussians(raw)
+        out = tracer.render(g, make_batch(view, "cuda"), train=True)
+        gen = torch.Generator(device="cuda").manual_seed(1)
+        loss = (out["pred_rgb"] * torch.rand(out["pred_rgb"].shape, device="cuda", generator=gen)).sum() + \
+            (out["pred_opacity"] * torch.rand(out["pred_opacity"].shape, device="cuda", generator=gen)).sum() + \
+            0.01 * (out["pred_dist"] * torch.rand(out["pred_dist"].shape, device="cuda", generator=gen)).sum()
+        loss.backward()
+        outs.append(out)
+        grads.append([p.grad.clone() for p in g.parameters()])
+    assert (outs[0]["pred_rgb"] - outs[1]["pred_rgb"]).abs().max() <= 1e-5
+    assert (outs[0]["pred_opacity"] - outs[1]["pred_opacity"]).abs().max() <= 1e-5
+    for name, a, b in zip(("positions", "rotation", "scale", "density", "albedo", "specular"), grads[0], grads[1]):
+        assert a.shape == b.shape
+        assert rel_l2(a.cpu().numpy(), b.cpu().numpy()) <= 1e-4, name
+
+
+def _adam_groups(n, seed, widths=(3, 4, 3, 1, 3, 45)):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    groups = []
+    for i, w in enumerate(widths):
+        p = torch.randn((n, w), device="cuda", generator=g)
+        m = torch.randn((n, w), device="cuda", generator=g) * 0.01
+        v = torch.rand((n, w), device="cuda", generator=g) * 1e-4
+        groups.append([p, torch.randn((n, w), device="cuda", generator=g), m, v, 10.0 ** (-2 - 0.5 * i)])
+    return groups
+
+
+@pytest.mark.parametrize("n", [1, 7, 10_001])
+@pytest.mark.parametrize("masked", [False, True])
+def test_selective_adam_step_is_bit_exact(raster, n, masked):
+    """One launch over six parameter groups (N x {3,4,3,1,3,45}: aligned and unaligned rows) against the oracle's fp32
+    restatement of selective_adam_update_kernel -- integer-exact comparison of the float bit patterns."""
+    groups = _adam_groups(n, 100 + n)
+    vis = None
+    if masked:
+        vis = (torch.rand((n, 1), device="cuda", generator=torch.Generator(device="cuda").manual_seed(n)) < 0.6).float()
+    b1, b2, eps = 0.9, 0.999, 1e-15
+    want = [mo.selective_adam_update(p.cpu().numpy(), g.cpu().numpy(), m.cpu().numpy(), v.cpu().numpy(),
+                                     None if vis is None else vis.cpu().numpy(), lr, b1, b2, eps) for p, g, m, v, lr in groups]
+    grads_before = [g.clone() for _, g, _, _, _ in groups]
+    raster.selective_adam_step([tuple(x) for x in groups], vis, b1, b2, eps)
+    for (p, g, m, v, _), (pw, mw, vw), g0 in zip(groups, want, grads_before):
+        assert np.array_equal(p.cpu().numpy().view(np.uint32), pw.view(np.uint32))
+        assert np.array_equal(m.cpu().numpy().view(np.uint32), mw.view(np.uint32))
+        assert np.array_equal(v.cpu().numpy().view(np.uint32), vw.view(np.uint32))
+        assert torch.equal(g, g0)   # gradients untouched without zero_grad
+    raster.selective_adam_step([tuple(x) for x in groups], vis, b1, b2, eps, zero_grad=True)
+    for _, g, _, _, _ in groups:
+        assert (g == 0).all()
+
+
+def test_selective_adam_class_mirrors_reference_api():
+    """3dgrut_b200.SelectiveAdam: the reference's constructor / step(visibility) / state keys (optimizers/__init__.py:45-133)."""
+    pkg = importlib.import_module("3dgrut_b200")
+    n = 5000
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    params = {name: torch.nn.Parameter(torch.randn((n, w), device="cuda", generator=gen)) for name, w in (("positions", 3), ("density", 1), ("features_specular", 45))}
+    opt = pkg.SelectiveAdam([{"params": [p], "name": k, "lr": lr} for (k, p), lr in zip(params.items(), (1e-3, 5e-2, 2e-4))], lr=1e-3, eps=1e-15)
+    state = {k: (p.detach().cpu().numpy().copy(), np.zeros((n, p.shape[1]), np.float32), np.zeros((n, p.shape[1]), np.float32)) for k, p in params.items()}
+    for step in range(3):
+        vis = (torch.rand((n, 1), device="cuda", generator=gen) < 0.5).float()
+        for p in params.values():
+            p.grad = torch.randn(p.shape, device="cuda", generator=gen)
+        for (k, p), lr in zip(params.items(), (1e-3, 5e-2, 2e-4)):
+            state[k] = mo.selective_adam_update(state[k][0], p.grad.cpu().numpy(), state[k][1], state[k][2], vis.cpu().numpy(), lr, 0.9, 0.999, 1e-15)
+        opt.step(vis)
+    for k, p in params.items():
+        assert np.array_equal(p.detach().cpu().numpy(), state[k][0]), k
+        st = opt.state[p]
+        assert set(st) == {"step", "exp_avg", "exp_avg_sq"}
+        assert np.array_equal(st["exp_avg"].cpu().numpy(), state[k][1]) and np.array_equal(st["exp_avg_sq"].cpu().numpy(), state[k][2])
+
+
+def test_densify_stats_equal_literal_reference_code(raster):
+    pkg = importlib.import_module("3dgrut_b200")
+    n = 20_011
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    pos = torch.nn.Parameter(torch.randn((n, 3), device="cuda", generator=gen))
+    pos.grad = torch.randn((n, 3), device="cuda", generator=gen) * 1e-3
+    pos.grad[::3] = 0.0
+    sensor = torch.tensor([0.3, -4.0, 1.5], device="cuda")
+    accum = torch.rand((n, 1), device="cuda", generator=gen)
+    denom = torch.randint(0, 5, (n, 1), device="cuda", generator=gen).float()
+    a_o, d_o = mo.update_gradient_buffer(pos.detach().cpu().numpy(), pos.grad.cpu().numpy(), sensor.cpu().numpy(), accum.cpu().numpy(),
+                                         denom.cpu().numpy())
+    # strategy/gs.py:104-115, literally, on clones
+    a_t, d_t = accum.clone(), denom.clone()
+    mask = (pos.grad != 0).max(dim=1)[0]
+    dist = (pos.detach()[mask] - sensor).norm(dim=1, keepdim=True)
+    a_t[mask] += torch.norm(pos.grad[mask] * dist, dim=-1, keepdim=True) / 2
+    d_t[mask] += 1
+    pkg.update_gradient_buffer(pos, accum, denom, sensor)
+    np.testing.assert_allclose(accum.cpu().numpy(), a_o, rtol=1e-6)
+    np.testing.assert_allclose(accum.cpu().numpy(), a_t.cpu().numpy(), rtol=1e-6)
+    assert np.array_equal(denom.cpu().numpy(), d_o) and torch.equal(denom, d_t)
