@@ -38,6 +38,9 @@
 namespace {
 
 constexpr int BLOCKS_PER_TILE = 4;    // 8x8 pixel blocks (one warp, two rays per lane) of a 16x16 tile
+#ifndef GUT_BWD_MIN_BLOCKS
+#define GUT_BWD_MIN_BLOCKS 20         // resident one-warp CTAs per SM the backward kernel is compiled for (96 registers);
+#endif                                // measured: 24 (80 regs, spills) 4.76 ms, 20 4.05 ms, 18 (112 regs) 4.21 ms per view
 
 // ---- packed FP32 (sm_100a FFMA2 / FMUL2 / FADD2: two fp32 lanes per instruction, one issue slot) -----------
 // Both compositing kernels are issue bound, and a packed instruction does the work of two scalar ones for the same
@@ -496,7 +499,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 // once per variant and a block leaves at once when its rays are of the other kind.  Keeping the per-ray origin offsets
 // out of the common variant's live set is worth 0.27 ms per view at the 96-register cap; the idle launch costs ~10 us.
 template <int DEG, bool UNIFORM>
-__global__ void __launch_bounds__(RENDER_THREADS, 20) gut_render_backward_kernel(
+__global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,

@@ -18,7 +18,8 @@ import torch
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgut_b200.so")
+# GUT_B200_LIBRARY: developer hook to A/B a differently tuned build of the same library (scripts/ab_build.sh)
+LIB_PATH = os.environ.get("GUT_B200_LIBRARY") or os.path.join(_HERE, "libgut_b200.so")
 _lib = None
 
 

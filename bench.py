@@ -491,6 +491,59 @@ def run_ours(args):
         ms = a0.elapsed_time(a1) / reps
         sorted_k16 = {"mpix_per_s": P / (ms * 1e-3) / 1e6, "ms_per_view": ms, "stage_ms": rk.stage_times()}
 
+    # ---- auxiliary: the model-side passes either side of the path at the workload's N: each is one
+    # HBM-bound pass; algorithmic bytes per particle / measured time against the measured copy bandwidth -------------------
+    model_side = None
+    if rank == 0 and not args.no_aux:
+        gen = torch.Generator(device=dev).manual_seed(5)
+        raw = {"positions": d12[:, 0:3].contiguous(), "rotation": (d12[:, 4:8] * 1.7).contiguous(), "scale": torch.log(d12[:, 8:11]).contiguous(),
+               "density": torch.logit(d12[:, 3:4]).contiguous(), "albedo": sph[:, :3].contiguous(), "specular": sph[:, 3:].contiguous()}
+        g12 = torch.randn((n, 12), device=dev, generator=gen)
+        g48 = torch.randn((n, 48), device=dev, generator=gen)
+        packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
+        groups = []
+        for k_, lr_ in (("positions", 1.6e-4), ("rotation", 1e-3), ("scale", 5e-3), ("density", 5e-2), ("albedo", 2.5e-3), ("specular", 1.25e-4)):
+            p_ = raw[k_].clone()
+            groups.append((p_, torch.randn(p_.shape, device=dev, generator=gen) * 1e-3, torch.zeros_like(p_), torch.zeros_like(p_), lr_))
+        vis_all = torch.ones((n, 1), device=dev)
+        stat_a, stat_d = torch.zeros((n, 1), device=dev), torch.zeros((n, 1), device=dev)
+
+        def torch_chain():   # what the reference runs per forward+backward: model.py:74-93, tracer.py:176-178 and autograd of it
+            leaves = {k_: v_.detach().requires_grad_(True) for k_, v_ in raw.items()}
+            dn = torch.sigmoid(leaves["density"])
+            pk = torch.cat([leaves["positions"], dn, torch.nn.functional.normalize(leaves["rotation"]), torch.exp(leaves["scale"]),
+                            torch.zeros_like(dn)], dim=1)
+            ft = torch.cat((leaves["albedo"], leaves["specular"]), dim=1)
+            torch.autograd.backward([pk, ft], [g12, g48])
+
+        def timed(fn, reps=5):
+            fn()
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(reps):
+                fn()
+            a1.record()
+            torch.cuda.synchronize()
+            return a0.elapsed_time(a1) / reps
+
+        passes = {
+            "activate_pack": (lambda: raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"]), 44 + 48),
+            "activate_pack_backward": (lambda: raster.activate_pack_backward(raw["rotation"], packed, g12), 48 + 32 + 16 + 44),
+            "pack_features": (lambda: raster.pack_features(raw["albedo"], raw["specular"]), 192 + 192),
+            "unpack_feature_gradient": (lambda: raster.unpack_feature_gradient(g48), 192 + 192),
+            "selective_adam_step(6 groups, all visible)": (lambda: raster.selective_adam_step(groups, vis_all, 0.9, 0.999, 1e-15), 59 * 28),
+            "densify_stats": (lambda: raster.densify_stats(groups[0][0], groups[0][1], (0.0, 0.0, 4.0), stat_a, stat_d), 24 + 16),
+        }
+        model_side = {"particles": n, "hbm_peak_gbs": hbm_peak, "passes": {}}
+        for name_, (fn_, bytes_) in passes.items():
+            ms_ = timed(fn_)
+            model_side["passes"][name_] = {"ms": ms_, "bytes_per_particle": bytes_, "gbs": n * bytes_ / (ms_ * 1e-3) / 1e9,
+                                           "frac": n * bytes_ / (ms_ * 1e-3) / 1e9 / hbm_peak}
+        fused_ms = sum(model_side["passes"][k_]["ms"] for k_ in ("activate_pack", "activate_pack_backward", "pack_features", "unpack_feature_gradient"))
+        model_side["activations_fwd_bwd_ms"] = {"fused_kernels": fused_ms, "torch_chain_of_the_reference": timed(torch_chain)}
+        del groups, g12, g48, packed, raw
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -508,7 +561,7 @@ def run_ours(args):
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,
                               "forward_tests_executed_per_pixel": tests_exec / nv / P},
-            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16,
+            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16, "model_side": model_side,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
