@@ -7,44 +7,67 @@
 //   particleDensityProcessHitBwdToBuffer (kernels/slang/models/gaussianParticles.slang:394-451), i.e. Slang autodiff of
 //   hit (:188-222) + integrateHit<true> (:224-252): true derivatives, alpha clamp masked, tMinMax test also in backward.
 //
-// Design.  A ray keeps its K closest pending hits (distance, alpha, particle) in REGISTERS, sorted by distance; the
-// insertion is a fully unrolled compare-exchange chain over static indices, the drain walks the static indices too, so
-// nothing spills to local memory.  One warp per CTA owns an 8x4 pixel block (eight blocks per 16x16 tile, one ray per
-// lane -- the k-buffer leaves no registers for a second ray) and stages the tile's sorted list through the same
+// Design.  A ray keeps the ORDER of its K closest pending hits in K registers -- one 32-bit key per hit, the distance bits
+// with the payload slot number in the low 4 mantissa bits -- and their exact (distance, alpha, particle) in a
+// conflict-free shared-memory column; insertion is a fully unrolled integer min/max chain over static indices, the
+// drain walks the static indices too, so nothing spills to local memory.  One warp per CTA owns an 8x4 pixel block (eight blocks per 16x16 tile, one ray per
+// lane) and stages the tile's sorted list through the same
 // warp-private pipeline as the K = 0 kernels (gut_render_common.cuh).  A hit leaves the buffer long after its batch
 // left shared memory, so processing gathers the particle by index: its K1 colour in the forward, its 48-byte
 // parameters too in the backward.
-// Backward: the reference adds 11 + 3 atomics per hit and thread into [N,12] / [N,3].  Here a hit produces the same 15
-// ray-linear canonical-frame values as the K = 0 kernel (gut_render.cu), with the true hit-distance Jacobians and the
-// masked clamp, and adds them to the [N,16] accumulators that K6 turns into parameter gradients -- K6 is shared.
+// Backward: the reference adds 11 + 3 scalar atomics per hit and thread into [N,12] / [N,3].  Here a hit produces the same
+// 15 ray-linear canonical-frame values as the K = 0 kernel (gut_render.cu), with the true hit-distance Jacobians and the
+// masked clamp, and adds them to the [N,16] accumulators with four red.global.add.v4.f32 -- K6 is shared.
 #include "gut_render_common.cuh"
 
 namespace {
 
 constexpr int KB_BLOCKS_PER_TILE = 8;   // 8x4 pixel blocks (one warp, one ray per lane) of a 16x16 tile
 
+// The ordering state of a ray's buffer is ONE 32-bit key per entry: the hit distance's bit pattern (positive floats order
+// like unsigned integers) with its low 4 mantissa bits replaced by the number of the payload slot that holds the hit's
+// exact (distance, alpha, particle) in shared memory.  Insertion is then a min/max chain -- two integer instructions per
+// level instead of a compare and six selects on three 32-bit fields -- and the buffer costs K registers, not 3K.
+// Two hits whose distances agree in all but the last 4 mantissa bits (relative 1.9e-6) are ordered by slot number;
+// the oracle marks rays with such near ties as borderline (another fp32 implementation may order them either way).
+constexpr uint32_t KB_SLOT_MASK = 15u;
 template <int K>
 struct KBuffer {
-    float t[K], a[K];
-    uint32_t p[K];
+    static_assert(K <= 16, "payload slot number is 4 bits");
+    uint32_t key[K];     // ascending; 0 = empty (empties sit at the bottom, like t = -1 in HitParticleKBuffer)
     uint32_t n;
     GUT_D void clear() {
         n = 0;
 #pragma unroll
-        for (int i = 0; i < K; ++i) { t[i] = -1.0f; a[i] = 0.0f; p[i] = 0xffffffffu; }
+        for (int i = 0; i < K; ++i) key[i] = 0u;
     }
     GUT_D bool full() const { return n == (uint32_t)K; }
-    // insert (the caller has processed entry 0 if the buffer was full): HitParticleKBuffer::insert, :45-62
-    GUT_D void insert(float ht, float ha, uint32_t hp) {
-        if (full()) t[0] = -1.0f; else n++;
+    GUT_D uint32_t front_slot() const { return key[0] & KB_SLOT_MASK; }
+    // insert (the caller has processed entry 0 if the buffer was full): HitParticleKBuffer::insert, :45-62.
+    // Returns the payload slot the caller writes the new hit to (the popped entry's slot when the buffer was full).
+    GUT_D uint32_t insert(float ht) {
+        uint32_t slot;
+        if (full()) { slot = front_slot(); key[0] = 0u; } else slot = n++;
+        uint32_t carry = (__float_as_uint(ht) & ~KB_SLOT_MASK) | slot;
 #pragma unroll
         for (int i = K - 1; i >= 0; --i) {
-            if (ht > t[i]) {
-                const float tt = t[i], ta = a[i]; const uint32_t tp = p[i];
-                t[i] = ht; a[i] = ha; p[i] = hp;
-                ht = tt; ha = ta; hp = tp;
-            }
+            const uint32_t small = min(key[i], carry);
+            key[i] = max(key[i], carry);
+            carry = small;
         }
+        return slot;
+    }
+};
+
+// exact payload of the buffered hits: [field][slot][lane] in shared memory, a lane only ever touches its own column
+// (bank = lane: conflict free, no synchronisation)
+template <int K>
+struct KPayload {
+    float* t; float* a; uint32_t* p;
+    GUT_D void init(float* base) { t = base; a = base + K * 32; p = reinterpret_cast<uint32_t*>(base + 2 * K * 32); }
+    GUT_D void put(uint32_t slot, uint32_t lane, float ht, float ha, uint32_t hp) {
+        const uint32_t o = slot * 32u + lane;
+        t[o] = ht; a[o] = ha; p[o] = hp;
     }
 };
 
@@ -117,6 +140,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_kernel(GutC
                                                                             const float* __restrict__ ray_dir, float4* __restrict__ rgba,
                                                                             float* __restrict__ dist, float* __restrict__ hits) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
+    __shared__ float kb_payload[3 * K * 32];
     const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
     const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
     const float3 dlt = ray.o - fr.cam_centre;
@@ -128,26 +152,36 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_kernel(GutC
     FwdStateK st;
     st.T = 1.0f; st.D = 0.0f; st.cr = st.cg = st.cb = 0.0f; st.nhits = 0;
     st.alive = ray.inside && ray.valid;
+    const uint32_t lane = threadIdx.x & 31;
     KBuffer<K> kb;
     kb.clear();
+    KPayload<K> pay;
+    pay.init(kb_payload);
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
         const uint32_t cnt = stg.count(b);
         for (uint32_t j = 0; j < cnt; ++j) {
             float alpha, t;
             if (st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t)) {
-                if (kb.full()) process_hit_fwd(cfg, src.features, kb.t[0], kb.a[0], kb.p[0], st);
-                kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
+                if (kb.full()) {
+                    const uint32_t o = kb.front_slot() * 32u + lane;
+                    process_hit_fwd(cfg, src.features, pay.t[o], pay.a[o], pay.p[o], st);
+                }
+                const uint32_t slot = kb.insert(t);
+                pay.put(slot, lane, t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
             }
         }
         if (!__any_sync(0xffffffffu, st.alive)) break;
         stg.rotate();
     }
     stg.drain();
-    // drain the buffer closest first (:282-290): valid entries sit at the top, invalid ones have t = -1
+    // drain the buffer closest first (:282-290): valid entries sit at the top, empty ones have key 0
 #pragma unroll
     for (int i = 0; i < K; ++i)
-        if (st.alive && kb.t[i] >= 0.0f) process_hit_fwd(cfg, src.features, kb.t[i], kb.a[i], kb.p[i], st);
+        if (st.alive && kb.key[i] != 0u) {
+            const uint32_t o = (kb.key[i] & KB_SLOT_MASK) * 32u + lane;
+            process_hit_fwd(cfg, src.features, pay.t[o], pay.a[o], pay.p[o], st);
+        }
 
     if (ray.inside && ray.valid) {
         rgba[ray.pix] = make_float4(st.cr, st.cg, st.cb, 1.0f - st.T);
@@ -170,35 +204,17 @@ struct BwdStateK {
     bool alive;
 };
 
-// Sum 16 per-lane values over the warp with 16 shuffles (each stage exchanges the half of the values the partner lane
-// will own).  On return lane l holds the warp total of value ((l>>4)&1)*8 + ((l>>3)&1)*4 + ((l>>2)&1)*2 + ((l>>1)&1).
-GUT_D float warp_transpose_reduce16(float (&v)[16], uint32_t lane) {
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-        const int h = 8 >> s;
-        const bool up = lane & (16u >> s);
-#pragma unroll
-        for (int k = 0; k < h; ++k) {
-            const float send = up ? v[k] : v[k + h];
-            const float keep = up ? v[k + h] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16 >> s);
-        }
-    }
-    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
-}
-
-// processHitParticle, backward branch (:116-152), for the lanes with `need` set (all 32 lanes call).  A hit yields the
-// 15 canonical-frame values of gut_render.cu's backward_walk (true hit-distance Jacobians, masked clamp).  Rays of an
-// 8x4 block mostly leave their buffers with the same particle at the same time, so the values are summed per distinct
-// particle across the warp (leader loop + transpose-reduce) and added to raw_grad[16 p + .] with one RED per value and
-// group instead of one per value and ray (the reference: 14 atomics per hit and thread).
+// processHitParticle, backward branch (:116-152), for ONE ray (called by the lanes whose buffer releases a hit).  A hit
+// yields the 15 canonical-frame values of gut_render.cu's backward_walk (true hit-distance Jacobians, masked clamp),
+// added to raw_grad[16 p + .] -- which K6 turns into parameter gradients, as for K = 0 -- with four 128-bit vector
+// reductions per ray (the reference: 14 scalar atomics per hit and thread).  No warp reduction: the rays of a block
+// leave their buffers with different particles most of the time (5.7 distinct particles per pop event of a warp at
+// the bench workload), and one reduction per distinct particle was 44 % of this kernel's instructions.
 template <int DEG>
-GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 origin, const float3 o, const float3 d,
-                           bool need, float t, float alpha, uint32_t p, BwdStateK& st, uint32_t lane, float* __restrict__ raw_grad) {
-    float v[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) v[k] = 0.0f;
-    if (need && alpha > 0.0f) {
+GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 o, const float3 d,
+                           float t, float alpha, uint32_t p, BwdStateK& st, float* __restrict__ raw_grad) {
+    if (alpha > 0.0f) {
+        float v[15];
         const float4 r0 = __ldg(src.density12 + 3 * (size_t)p), q = __ldg(src.density12 + 3 * (size_t)p + 1),
                      r2 = __ldg(src.density12 + 3 * (size_t)p + 2), F = __ldg(src.features + p);
         // particleFeaturesIntegrateBwd: un-blend the UNclamped feature, adjoint of lerp(I, f, alpha)
@@ -259,22 +275,18 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
         v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));
         v[11] = fgrad.x; v[12] = fgrad.y; v[13] = fgrad.z;
         v[14] = -kd * ssum;
-    }
-    if (need) {
-        st.T *= (1.0f - alpha);
-        if (st.T < cfg.min_transmittance) st.alive = false;
-    }
     // Rays of a block leave their buffers with DIFFERENT particles most of the time (measured: 5.7 distinct particles per
     // pop event of a warp at the bench workload), so a warp reduction per distinct particle costs more than it saves
     // (it was 44 % of the kernel's instructions).  Each lane adds its 15 values itself with four 128-bit vector
     // reductions (red.global.add.v4.f32, sm_90+): 4 instructions per pop event instead of ~90 per distinct particle.
-    if (need && alpha > 0.0f) {
         float4* dst = reinterpret_cast<float4*>(raw_grad + 16 * (size_t)p);
         atomicAdd(dst, make_float4(v[0], v[1], v[2], v[3]));
         atomicAdd(dst + 1, make_float4(v[4], v[5], v[6], v[7]));
         atomicAdd(dst + 2, make_float4(v[8], v[9], v[10], v[11]));
         atomicAdd(dst + 3, make_float4(v[12], v[13], v[14], 0.0f));
     }
+    st.T *= (1.0f - alpha);
+    if (st.T < cfg.min_transmittance) st.alive = false;
 }
 
 template <int DEG, int K>
@@ -284,6 +296,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
+    __shared__ float kb_payload[3 * K * 32];
     const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
     const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
     const float3 dlt = ray.o - fr.cam_centre;
@@ -305,6 +318,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     stg.init(smem_raw, src, b0, b1 - b0, fr.cam_centre);
     KBuffer<K> kb;
     kb.clear();
+    KPayload<K> pay;
+    pay.init(kb_payload);
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
         const uint32_t cnt = stg.count(b);
@@ -312,9 +327,14 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
             float alpha, t;
             const bool hit = st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t);
             const bool need = hit && kb.full();
-            if (__any_sync(0xffffffffu, need))
-                process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, need, kb.t[0], kb.a[0], kb.p[0], st, lane, raw_grad);
-            if (hit) kb.insert(t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
+            if (need) {
+                const uint32_t o = kb.front_slot() * 32u + lane;
+                process_hit_bwd<DEG>(cfg, src, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
+            }
+            if (hit) {
+                const uint32_t slot = kb.insert(t);
+                pay.put(slot, lane, t, alpha, __float_as_uint(stg.rec[5 * j + 4].w));
+            }
         }
         if (!__any_sync(0xffffffffu, st.alive)) break;
         stg.rotate();
@@ -322,9 +342,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     stg.drain();
 #pragma unroll
     for (int i = 0; i < K; ++i) {
-        const bool need = st.alive && kb.t[i] >= 0.0f;
-        if (__any_sync(0xffffffffu, need))
-            process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, need, kb.t[i], kb.a[i], kb.p[i], st, lane, raw_grad);
+        if (st.alive && kb.key[i] != 0u) {
+            const uint32_t o = (kb.key[i] & KB_SLOT_MASK) * 32u + lane;
+            process_hit_bwd<DEG>(cfg, src, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
+        }
     }
 }
 

@@ -814,9 +814,10 @@ ORACLE_API void gut_oracle_render(const GutConfig* cfg, const GutCamera* cam, ui
                     if (!(h.t > ray.tmin && h.t < ray.tmax)) continue;
                     if (K == 0) { PROCESS_HIT(&h); continue; }
                     if (nk == K) { hit_t closest = kb[0]; PROCESS_HIT(&closest); kb[0].t = -1.0f; } else nk++;
-                    /* a near tie in hit distance may be ordered the other way by another fp32 implementation */
+                    /* a near tie in hit distance may be ordered the other way by another fp32 implementation: distances agree to
+                       ~1e-6, and libgut_b200 orders buffered hits on the distance bits without the low 4 mantissa bits (1.9e-6) */
                     for (int i = 0; i < K; ++i)
-                        if (kb[i].t >= 0.0f) mrg = fminf(mrg, 10.0f * fabsf(h.t - kb[i].t) / fmaxf(fabsf(h.t), 1e-30f)); /* distances agree to ~1e-6 */
+                        if (kb[i].t >= 0.0f) mrg = fminf(mrg, 5.0f * fabsf(h.t - kb[i].t) / fmaxf(fabsf(h.t), 1e-30f)); /* flags |dt|/t < 4e-6 */
                     for (int i = K - 1; i >= 0; --i)
                         if (h.t > kb[i].t) { hit_t tmp = kb[i]; kb[i] = h; h = tmp; }
                 }
