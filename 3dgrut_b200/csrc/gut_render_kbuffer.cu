@@ -22,6 +22,9 @@
 
 namespace {
 
+#ifndef GUT_KB_MIN_BLOCKS
+#define GUT_KB_MIN_BLOCKS 20   // resident one-warp CTAs per SM the forward is compiled for (96 registers: 4.59 -> 4.38 ms; the backward is better uncapped, 8.72 vs 8.86 ms)
+#endif
 constexpr int KB_BLOCKS_PER_TILE = 8;   // 8x4 pixel blocks (one warp, one ray per lane) of a 16x16 tile
 
 // The ordering state of a ray's buffer is ONE 32-bit key per entry: the hit distance's bit pattern (positive floats order
@@ -91,6 +94,29 @@ GUT_D RayK make_ray_k(const GutFrame& fr, const float* __restrict__ ray_ori, con
     return r;
 }
 
+// Cone (axis, tan of the half angle) around the live rays of the warp's block for WarpStager::stage_culled; w < 0 = no
+// cull (per-ray origins, degenerate bundles, or a kernel degree the bound is not derived for).  Same construction as in
+// gut_render_kernel (gut_render.cu); an 8x4 block gives a narrower cone than the 8x8 block of the K = 0 kernels.
+template <int DEG>
+GUT_D float4 block_cone(const RayK& ray, const float3 dlt, bool alive) {
+    const bool at_origin = !ray.inside || (dlt.x == 0.0f && dlt.y == 0.0f && dlt.z == 0.0f);
+    const bool uniform = __all_sync(0xffffffffu, at_origin);
+    const float3 dn = rsqrtf(dot(ray.d, ray.d)) * ray.d;
+    float3 sum = alive ? dn : f3(0.f, 0.f, 0.f);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum.x += __shfl_xor_sync(0xffffffffu, sum.x, o); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, o); sum.z += __shfl_xor_sync(0xffffffffu, sum.z, o);
+    }
+    const float n2 = dot(sum, sum);
+    const float3 axis = n2 > 0.0f ? rsqrtf(n2) * sum : f3(0.f, 0.f, 1.f);
+    float cmin = alive ? dot(axis, dn) : 1.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cmin = fminf(cmin, __shfl_xor_sync(0xffffffffu, cmin, o));
+    float tan_h = -1.0f;
+    if (DEG == 2 && uniform && cmin > 0.5f) tan_h = sqrtf(fmaxf(1.0f - cmin * cmin, 0.0f)) / cmin * 1.001f + 1e-6f;
+    return make_float4(axis.x, axis.y, axis.z, tan_h);
+}
+
 // test of one staged record against one ray; on acceptance also the hit distance (canonicalRayDistance,
 // gaussianParticles.slang:165-171).  dlt = ray origin - frame origin.
 template <int DEG>
@@ -135,7 +161,7 @@ GUT_D void process_hit_fwd(const GutConfig& cfg, const float4* __restrict__ feat
 }
 
 template <int DEG, int K>
-__global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+__global__ void __launch_bounds__(RENDER_THREADS, GUT_KB_MIN_BLOCKS) gut_render_kbuffer_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                             GutParticleSource src, const float* __restrict__ ray_ori,
                                                                             const float* __restrict__ ray_dir, float4* __restrict__ rgba,
                                                                             float* __restrict__ dist, float* __restrict__ hits) {
@@ -157,9 +183,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_kernel(GutC
     kb.clear();
     KPayload<K> pay;
     pay.init(kb_payload);
+    const float4 cone = block_cone<DEG>(ray, dlt, st.alive);
     for (uint32_t b = 0; b < stg.nb; ++b) {
-        stg.stage(b);
-        const uint32_t cnt = stg.count(b);
+        uint32_t keep;
+        const uint32_t cnt = stg.stage_culled(b, cfg, cone, keep);   // records no ray of the block can accept are dropped while staging
         for (uint32_t j = 0; j < cnt; ++j) {
             float alpha, t;
             if (st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t)) {
@@ -320,9 +347,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     kb.clear();
     KPayload<K> pay;
     pay.init(kb_payload);
+    const float4 cone = block_cone<DEG>(ray, dlt, st.alive);
     for (uint32_t b = 0; b < stg.nb; ++b) {
-        stg.stage(b);
-        const uint32_t cnt = stg.count(b);
+        uint32_t keep;
+        const uint32_t cnt = stg.stage_culled(b, cfg, cone, keep);
         for (uint32_t j = 0; j < cnt; ++j) {
             float alpha, t;
             const bool hit = st.alive && record_hit<DEG>(cfg, stg.rec + 5 * j, ray.d, dlt, ray.tmin, ray.tmax, alpha, t);
