@@ -162,12 +162,22 @@ class Tracer:
         self.conf = conf
         # render.fused_activations (not a reference key; default on): take the model's raw parameters when it exposes them
         self.fused_activations = bool(_get(conf, "render.fused_activations", True))
+        self._normals, self._normals_key = None, None
         torch.zeros(1, device=self.device)  # force CUDA context creation, as the reference does (tracer.py:292)
         self.tracer_wrapper = SplatRaster(config_from_conf(conf))
 
     @property
     def timings(self):
         return self.tracer_wrapper.collect_times()
+
+    def _constant_normals(self, like):
+        """The reference returns normalize(ones_like(pred_rgb)) -- the constant 1/sqrt(3) -- every frame (tracer.py:347), five
+        full-image torch kernels.  The constant is built once per image shape and handed out as a read-only expanded view."""
+        key = (tuple(like.shape), like.device)
+        if self._normals_key != key:
+            self._normals = torch.nn.functional.normalize(torch.ones((1, 1, 1, like.shape[3]), dtype=like.dtype, device=like.device), dim=3)
+            self._normals_key = key
+        return self._normals.expand(like.shape)
 
     def build_acc(self, gaussians, rebuild=True):
         pass  # 3DGUT has no acceleration structure (tracer.py:301-302)
@@ -203,7 +213,7 @@ class Tracer:
             "pred_rgb": pred_rgb,
             "pred_opacity": pred_opacity,
             "pred_dist": pred_dist,
-            "pred_normals": torch.nn.functional.normalize(torch.ones_like(pred_rgb), dim=3),
+            "pred_normals": self._constant_normals(pred_rgb),
             "hits_count": hits_count,
             "frame_time_ms": timings["forward_render"] if "forward_render" in timings else 0.0,
             "mog_visibility": mog_visibility,

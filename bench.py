@@ -370,6 +370,7 @@ def run_ours(args):
                    "dg": torch.empty((h, w, 1), device=dev)} for _ in range(nbuf)]
         rgba_dev = [torch.empty((h, w, 4), device=dev) for _ in range(nbuf)]
         free_ev = [None] * nbuf   # recorded on the compute stream when a buffer set may be overwritten
+        prefetched = []
 
         def stage(vi):
             nonlocal h2d
@@ -378,7 +379,7 @@ def run_ours(args):
             with torch.cuda.stream(copy_stream):
                 if free_ev[bi] is not None:
                     copy_stream.wait_event(free_ev[bi])
-                for kk in ("rays_ori", "rays_dir", "T_to_world"):
+                for kk in ("rays_ori", "rays_dir"):
                     dev_in[bi][kk].copy_(pv[kk], non_blocking=True)
                     h2d += pv[kk].numel() * 4
                 dev_in[bi]["rg"].copy_(rg_h, non_blocking=True)
@@ -395,23 +396,28 @@ def run_ours(args):
                 p.grad = None
             checksum = None
             cur = torch.cuda.current_stream()
-            ready = stage(0) if pinned else None
+            # the inputs of this step's first view were put in flight at the end of the previous step (a data loader's prefetch)
+            ready = prefetched.pop() if prefetched else (stage(0) if pinned else None)
             for vi in range(len(pinned)):
                 bi = vi % nbuf
                 cur.wait_event(ready)
                 if vi + 1 < len(pinned):
                     ready = stage(vi + 1)
+                # the pose stays a host tensor: the rasteriser consumes it on the host (kernel parameters), and a device copy
+                # would be read straight back with a stream-wide synchronisation (the reference does that, tracer.py:376)
                 dv = dict(pinned[vi])
-                for kk in ("rays_ori", "rays_dir", "T_to_world"):
+                for kk in ("rays_ori", "rays_dir"):
                     dv[kk] = dev_in[bi][kk]
                 rg, dg = dev_in[bi]["rg"], dev_in[bi]["dg"]
-                o = tracer.render(gauss, make_batch(dv, dev), train=True)
+                o = tracer.render(gauss, make_batch(dv, dev, pose_device="cpu"), train=True)
                 loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
                 loss.backward()
                 torch.cat([o["pred_rgb"][0].detach(), o["pred_opacity"][0].detach()], dim=-1, out=rgba_dev[bi])
                 done = torch.cuda.Event()
                 done.record(cur)
                 free_ev[bi] = done
+                if vi + 1 == len(pinned):
+                    prefetched.append(stage(0))   # next step's first view; waits for its buffer set's free event like any stage()
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(done)
                     out_host.copy_(rgba_dev[bi], non_blocking=True)
@@ -420,19 +426,28 @@ def run_ours(args):
             if world > 1:
                 for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
                     dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
-            cur.wait_stream(copy_stream)
+            # the read-back of the last view's image may still be in flight (it is ordered before the next step's read-backs on the
+            # copy stream); the timed region ends with cur.wait_stream(copy_stream) below
             if checksum is not None:
                 float(checksum.item())  # device->host read of the step's scalar result
                 d2h += 4
 
         for _ in range(min(args.warmup, 3)):
             e2e_step()
+        if os.environ.get("GUT_BENCH_E2E_TRACE") and rank == 0:   # developer hook: kernel table of one end-to-end step
+            from torch.profiler import ProfilerActivity, profile
+            with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+                e2e_step()
+                torch.cuda.synchronize()
+            with open(os.environ["GUT_BENCH_E2E_TRACE"], "w") as fh:
+                fh.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=60, max_name_column_width=90))
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
         k_e2e = args.steps
         for _ in range(k_e2e):
             e2e_step()
+        torch.cuda.current_stream().wait_stream(copy_stream)   # every copy of the timed steps has landed
         f1.record()
         barrier()
         ms = f0.elapsed_time(f1)
@@ -441,8 +456,8 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.views * P * k_e2e / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h),
-               "path": "Tracer.render + autograd backward per view; rays, pose and upstream gradients copied from pinned host memory "
-                       "(copy stream, one view ahead), rendered RGBA of every view and the scalar loss read back every step; particles stay "
+               "path": "Tracer.render + autograd backward per view; rays and upstream gradients copied from pinned host memory "
+                       "(copy stream, one view ahead), the 4x4 pose handed over as a host tensor (it becomes kernel parameters), rendered RGBA of every view and the scalar loss read back every step; particles stay "
                        "device resident (they are the model)"}
 
     # ---- auxiliary: forward-only frame time at 1920x1080 (second half of BASELINE.json's metric; reference convention:

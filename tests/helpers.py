@@ -77,13 +77,16 @@ class SyntheticGaussians:
         return rgb, opacity  # black background (threedgrut/model/background.py:81-95)
 
 
-def make_batch(view, device):
+def make_batch(view, device, pose_device=None):
+    """``pose_device="cpu"`` keeps T_to_world a host tensor: the tracer consumes the pose on the host, and a device copy is read
+    straight back with a stream-wide synchronisation (what the reference does, tracer.py:376)."""
+    pose_device = device if pose_device is None else pose_device
     kw = {k: view[k] for k in ("intrinsics", "intrinsics_OpenCVPinholeCameraModelParameters",
                                "intrinsics_OpenCVFisheyeCameraModelParameters") if k in view}
     end = view.get("T_to_world_end")
     return protocols.Batch(rays_ori=view["rays_ori"].to(device), rays_dir=view["rays_dir"].to(device),
-                           T_to_world=view["T_to_world"].to(device),
-                           T_to_world_end=None if end is None else end.to(device), **kw)
+                           T_to_world=view["T_to_world"].to(pose_device),
+                           T_to_world_end=None if end is None else end.to(pose_device), **kw)
 
 
 def camera_of(view):

@@ -204,6 +204,8 @@ def test_tracer_autograd_matches_native(pkg):
     assert out["pred_rgb"].shape == (1, h, w, 3) and out["pred_opacity"].shape == (1, h, w, 1)
     assert out["pred_dist"].shape == (1, h, w, 1) and out["hits_count"].shape == (1, h, w, 1)
     assert out["mog_visibility"].shape == (n, 1)
+    assert out["pred_normals"].shape == (1, h, w, 3)     # normalize(ones_like(pred_rgb)), tracer.py:347
+    assert torch.allclose(out["pred_normals"], torch.full((1, h, w, 3), 3.0 ** -0.5, device="cuda"))
     rng = np.random.default_rng(0)
     rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
     dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
