@@ -17,6 +17,11 @@ _LAZY = {
     "default_config": ".abi",
     "SelectiveAdam": ".optimizers",
     "update_gradient_buffer": ".optimizers",
+    "read_ply": ".scene_io",
+    "write_ply": ".scene_io",
+    "read_colmap_cameras": ".scene_io",
+    "read_colmap_images": ".scene_io",
+    "colmap_views": ".scene_io",
 }
 
 
