@@ -412,7 +412,6 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             sg.x = bc(S.x) * grd.x; sg.y = bc(S.y) * grd.y; sg.z = bc(S.z) * grd.z;
             sg2.x = sg.x * sg.x; sg2.y = sg.y * sg.y; sg2.z = sg.z * sg.z;
             const F2 ssum = sg2.x + sg2.y + sg2.z;
-            const F2 gsq = dgo * dgo * ssum;
             const F2 gdist = mk2(h0 ? fabsf(lo(dgo)) * mufu_sqrt(lo(ssum)) : 0.0f, h1 ? fabsf(hi(dgo)) * mufu_sqrt(hi(ssum)) : 0.0f);
             const F2 alpha = mk2(h0 ? fminf(cfg.max_alpha, lo(k.araw)) : 0.0f, h1 ? fminf(cfg.max_alpha, hi(k.araw)) : 0.0f);
             const F2 T = st.T;
@@ -426,9 +425,10 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             st.Drem = fma(-w, gdist, st.Drem);
             const F2 rD = st.Drem * invT;
             const F2 resD = mk2(fmaxf(lo(rD), 0.0f), fmaxf(hi(rD), 0.0f));
-            const F2 aHit = (gdist - resD) * T * st.dD;
+            const F2 dHit = gdist - resD;              // hit-distance part of the alpha gradient: T * dHit * dD, folded into Sall
             const F2 wd = w * st.dD;
-            const F2 hs = mk2(h0 && lo(gsq) > 0.0f ? lo(wd) * mufu_rcp(lo(gdist)) : 0.0f, h1 && hi(gsq) > 0.0f ? hi(wd) * mufu_rcp(hi(gdist)) : 0.0f);
+            // gdist is 0 for a ray that does not take the hit, so "> 0" also is the hit test (the reference tests gdist^2 > 0)
+            const F2 hs = mk2(lo(gdist) > 0.0f ? lo(wd) * mufu_rcp(lo(gdist)) : 0.0f, hi(gdist) > 0.0f ? hi(wd) * mufu_rcp(hi(gdist)) : 0.0f);
             const F2 nkap = dgo * hs;                  // -kap
             const F2 kd = -(nkap * dgo);               // s_i * sclHit_i = -kd * sg2_i
             // grdHit_i = -kap (sg2_i go_i + dgo s_i sg_i) ; groHit_i = -kap sg2_i grd_i
@@ -447,39 +447,41 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             const F2 resCy = mk2(fmaxf(lo(ry), 0.0f), fmaxf(hi(ry), 0.0f));
             const F2 resCz = mk2(fmaxf(lo(rz), 0.0f), fmaxf(hi(rz), 0.0f));
             const F2 cs = fma(bc(F.z) - resCz, st.dC.z, fma(bc(F.y) - resCy, st.dC.y, (bc(F.x) - resCx) * st.dC.x));
-            const F2 Sall = fma(T, cs, aHit + aDns);
+            const F2 Sall = fma(T, fma(dHit, st.dD, cs), aDns);
             const F2 Ssum = mk2(h0 ? lo(Sall) : 0.0f, h1 ? hi(Sall) : 0.0f);
             const F2 dDens = k.resp * Ssum;
             const F2 respG = bc(S.w) * Ssum;
-            F2 g2G;
-            if (DEG == 2) g2G = bc(-0.5f) * k.resp * respG;
-            else g2G = mk2(kernel_response_grad<DEG>(lo(k.g2), lo(k.resp), lo(respG)), kernel_response_grad<DEG>(hi(k.g2), hi(k.resp), hi(respG)));
-
-            // g2 = |grd x go|^2 : adjoint of the cross product (:671-689); grd x go = c / |u|
-            const F2x3 gcG = k.c * (bc(2.0f) * g2G * il);
+            // g2 = |grd x go|^2 : adjoint of the cross product (:671-689); grd x go = c / |u|, so dL/d(grd x go) = c (2 g2G / |u|).
+            // Degree 2: g2G = -resp respG / 2, the factors 2 and -1/2 cancel
+            F2 gscale;
+            if (DEG == 2) gscale = -(k.resp * respG) * il;
+            else gscale = bc(2.0f) * mk2(kernel_response_grad<DEG>(lo(k.g2), lo(k.resp), lo(respG)), kernel_response_grad<DEG>(hi(k.g2), hi(k.resp), hi(respG))) * il;
+            const F2x3 gcG = k.c * gscale;
             const F2x3 grdG = cross(go, gcG);
             const F2x3 groG = cross(gcG, grd);
             // A = dL/dgo (total), X = dL/dgrd (total)
             F2x3 Ag, X, Bg;
             Ag.x = fma(nkap, sg2.x * grd.x, groG.x); Ag.y = fma(nkap, sg2.y * grd.y, groG.y); Ag.z = fma(nkap, sg2.z * grd.z, groG.z);
             X.x = fma(nkap, tH.x, grdG.x); X.y = fma(nkap, tH.y, grdG.y); X.z = fma(nkap, tH.z, grdG.z);
-            // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): B = dL/du = (X - grd (grd . X)) / |u|
+            // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): B = dL/du = Y / |u| with Y = X - grd (grd . X).
+            // Every use of B below but one is a product u_i B_j = grd_i Y_j, so Y is used directly and only the trace term
+            // is divided by |u|.
             const F2 gx = dot(grd, X);
-            Bg.x = il * fma(-grd.x, gx, X.x); Bg.y = il * fma(-grd.y, gx, X.y); Bg.z = il * fma(-grd.z, gx, X.z);
+            Bg.x = fma(-grd.x, gx, X.x); Bg.y = fma(-grd.y, gx, X.y); Bg.z = fma(-grd.z, gx, X.z);   // = Y
 
             // P_ij = go_i A_j + u_i B_j : diagonal -> scale, off-diagonal -> body-frame torque
             v[0] = (Ag.x); v[1] = (Ag.y); v[2] = (Ag.z);
             v[3] = (dDens);
-            v[4] = (fma(bc(R0.y), fma(go.z, Ag.y, u.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, u.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
-            v[5] = (fma(bc(R0.z), fma(go.x, Ag.z, u.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, u.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
-            v[6] = (fma(bc(R1.x), fma(go.y, Ag.x, u.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, u.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
-            F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x)));
+            v[4] = (fma(bc(R0.y), fma(go.z, Ag.y, grd.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, grd.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
+            v[5] = (fma(bc(R0.z), fma(go.x, Ag.z, grd.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, grd.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
+            v[6] = (fma(bc(R1.x), fma(go.y, Ag.x, grd.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, grd.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
+            F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x))) * il;   // sum_i B_i d_i / s_i
             tr = fma(Ag.z, bc(R2.w), fma(Ag.y, bc(R2.z), fma(Ag.x, bc(R2.y), tr)));   // origin part: A . (frame origin - position) / s
             if (!UNIFORM) tr = fma(bc(isz), Ag.z * ray.dlt.z, fma(bc(R1.w), Ag.y * ray.dlt.y, fma(bc(R1.z), Ag.x * ray.dlt.x, tr)));
             v[7] = (tr);
-            v[8] = (fma(go.x, Ag.x, fma(u.x, Bg.x, kd * sg2.x)));
-            v[9] = (fma(go.y, Ag.y, fma(u.y, Bg.y, kd * sg2.y)));
-            v[10] = (fma(go.z, Ag.z, fma(u.z, Bg.z, kd * sg2.z)));
+            v[8] = (fma(go.x, Ag.x, fma(grd.x, Bg.x, kd * sg2.x)));
+            v[9] = (fma(go.y, Ag.y, fma(grd.y, Bg.y, kd * sg2.y)));
+            v[10] = (fma(go.z, Ag.z, fma(grd.z, Bg.z, kd * sg2.z)));
             v[11] = (w * st.dC.x); v[12] = (w * st.dC.y); v[13] = (w * st.dC.z);
             v[14] = -(kd * ssum);
             v[15] = bc(0.0f);
