@@ -356,6 +356,40 @@ GUT_D float warp_transpose_reduce(const F2 (&V)[16], uint32_t lane) {
     return x;
 }
 
+// Same sum through a warp-private shared-memory tile (-DGUT_BWD_SMEM_REDUCE): 42 instructions instead of 71 at the same
+// FMA-pipe cycles -- and measured SLOWER (3.955 vs 3.91 ms per view): store -> __syncwarp -> load is a longer dependent
+// chain than five shuffle rounds and the kernel runs ~4.5 warps per scheduler.  Kept as a build option for the record.
+//  stage 0: the two rays of a lane are added and the lane stores its row of 16 floats with four 128-bit stores (row
+//           pitch 20 floats, so the stores of a quarter warp cover all 32 banks exactly once);
+//  stage 1: lane l owns the value pair p = l & 7 and the row group g = l >> 3 (8 rows): eight 64-bit loads (odd groups
+//           start 4 rows in, which moves their banks by 16: conflict free within a half warp) summed with packed adds;
+//  stage 2: the four row groups are combined with two 64-bit shuffle rounds (xor 8, xor 16).
+// On return every lane holds the warp totals of values 2p (low) and 2p + 1 (high).  V[15] is padding and not read.
+constexpr uint32_t REDUCE_PITCH = 20;                           // floats per row
+constexpr uint32_t REDUCE_TILE_BYTES = 32 * REDUCE_PITCH * 4;
+GUT_D F2 warp_smem_reduce(const F2 (&V)[16], uint32_t lane, float* __restrict__ tile) {
+    float4* row = reinterpret_cast<float4*>(tile + lane * REDUCE_PITCH);
+    __syncwarp();   // every lane has read the previous visit's tile
+    row[0] = make_float4(lo(V[0]) + hi(V[0]), lo(V[1]) + hi(V[1]), lo(V[2]) + hi(V[2]), lo(V[3]) + hi(V[3]));
+    row[1] = make_float4(lo(V[4]) + hi(V[4]), lo(V[5]) + hi(V[5]), lo(V[6]) + hi(V[6]), lo(V[7]) + hi(V[7]));
+    row[2] = make_float4(lo(V[8]) + hi(V[8]), lo(V[9]) + hi(V[9]), lo(V[10]) + hi(V[10]), lo(V[11]) + hi(V[11]));
+    row[3] = make_float4(lo(V[12]) + hi(V[12]), lo(V[13]) + hi(V[13]), lo(V[14]) + hi(V[14]), 0.0f);
+    __syncwarp();
+    const uint32_t g = lane >> 3, rot = (g & 1u) * 4u;
+    const float* col = tile + g * 8 * REDUCE_PITCH + 2 * (lane & 7u);
+    F2 acc[2];
+#pragma unroll
+    for (uint32_t i = 0; i < 8; ++i) {
+        F2 x;
+        x.v = *reinterpret_cast<const u64*>(col + ((i + rot) & 7u) * REDUCE_PITCH);
+        acc[i & 1] = i < 2 ? x : acc[i & 1] + x;
+    }
+    F2 t = acc[0] + acc[1];
+    t = t + shfl2(t, 8);
+    t = t + shfl2(t, 16);
+    return t;
+}
+
 struct BwdRay {
     F2 T_f, dA, dD;          // final transmittance of the forward pass, upstream gradients
     F2x3 dC;
@@ -381,7 +415,7 @@ struct BwdRay {
 // upstream sum: every one of its 15 values is then exactly 0 and its state is unchanged.
 template <int DEG, bool UNIFORM>
 GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t mask,
-                         const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad) {
+                         const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad, float* __restrict__ tile) {
     const float minT = cfg.min_transmittance;
     const F2 one = bc(1.0f);
     while (mask) {
@@ -490,9 +524,18 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             if (lo(nextT) < minT) st.alive[0] = false;
             if (hi(nextT) < minT) st.alive[1] = false;
         }
+#ifndef GUT_BWD_SMEM_REDUCE
         const float total = warp_transpose_reduce(v, lane);
         const uint32_t slot = reduce_slot(lane);
         if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
+#else
+        const F2 total = warp_smem_reduce(v, lane, tile);
+        if (lane < 8u) {   // lane p adds values 2p and 2p + 1: one 64-bit vector reduction (value 15 is padding)
+            float* dst = raw_grad + 16 * (size_t)__float_as_uint(F.w) + 2 * lane;
+            if (lane < 7u) atomicAdd(reinterpret_cast<float2*>(dst), make_float2(lo(total), hi(total)));
+            else atomicAdd(dst, lo(total));
+        }
+#endif
       }
     }
 }
@@ -507,6 +550,11 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ raw_grad, const uint32_t* __restrict__ hit_masks) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<true>::TOTAL];
+#ifdef GUT_BWD_SMEM_REDUCE
+    __shared__ __align__(16) float reduce_tile[REDUCE_TILE_BYTES / 4];
+#else
+    float* const reduce_tile = nullptr;
+#endif
 
     const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
     const uint32_t lane = threadIdx.x & 31;
@@ -545,7 +593,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
         const uint32_t mask = __ldg(hit_masks + hit_mask_slot(b0, tile, b, block));   // entries some ray of the block accepted in the forward
-        backward_walk<DEG, UNIFORM>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad);
+        backward_walk<DEG, UNIFORM>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad, reduce_tile);
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
         stg.rotate();
     }
