@@ -89,6 +89,9 @@ class DeferredExchange:
         self.radiance_grad = torch.zeros((n_particles, n_sph_floats), dtype=torch.float32, device=device)
         self.colour_all = torch.zeros((self.world * views_per_rank, n_particles, 3), dtype=torch.float32, device=device)
         self.centres_all = torch.zeros((self.world * views_per_rank, 3), dtype=torch.float32, device=device)
+        # union over all views of the step of the tracer's mog_visibility: what SelectiveAdam masks its update with
+        # (trainer.py:747-749 passes the visibility of the step's single view; with V views it is their union)
+        self.visibility = torch.zeros((n_particles, 1), dtype=torch.float32, device=device)
 
     def local_slot(self, rank, i):
         return rank * self.views_per_rank + i
@@ -105,9 +108,11 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
     lo = ex.local_slot(rank, 0)
     mine = ex.colour_all[lo:lo + ex.views_per_rank]
     centres = []
+    ex.visibility.zero_()
     for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
+        torch.maximum(ex.visibility, vis, out=ex.visibility)
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
                                     rgba, rg, dist_, dg, mine[i])
         centres.append(c)
@@ -123,11 +128,34 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         _all_gather(ex.colour_all, mine)
         _all_gather(ex.centres_all, my_centres)
         # the [N,12] allreduce runs on the collective stream while this stream expands the SH gradient
-        pending = dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)
+        pending = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True),
+                   dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True)]   # union of the ranks' visibilities, 4 B/particle
     raster.sh_gradient_expand(sph_degree, particle_density, ex.centres_all, ex.colour_all, ex.radiance_grad, accumulate=False)
     if pending is not None:
-        pending.wait()
+        for work in pending:
+            work.wait()
     return outs
+
+
+PARAMETER_GROUPS = ("positions", "rotation", "scale", "density", "features_albedo", "features_specular")
+
+
+def optimizer_step(raster, ex, raw, particle_density, state, lrs, betas=(0.9, 0.999), eps=1e-15, scale_activation=1,
+                   density_activation=2):
+    """The step after the exchange, identical on every rank: the summed [N,12] / [N,48] gradients of
+    ``ex`` are taken back to the model's RAW parameters (activation adjoints, gut_activate_pack_backward; feature split)
+    and SelectiveAdam updates all six groups in ONE launch, masked by the step's visibility union.
+
+    raw / state / lrs: dicts keyed by PARAMETER_GROUPS -- raw parameter tensors (updated in place), (exp_avg, exp_avg_sq)
+    pairs, learning rates.  ``particle_density`` is the packed record the step rendered with (gut_activate_pack).
+    Returns the raw-parameter gradients (dict)."""
+    pos_g, rot_g, scl_g, dns_g = raster.activate_pack_backward(raw["rotation"], particle_density, ex.density_grad, scale_activation,
+                                                               density_activation)
+    alb_g, spc_g = raster.unpack_feature_gradient(ex.radiance_grad)
+    grads = dict(zip(PARAMETER_GROUPS, (pos_g, rot_g, scl_g, dns_g, alb_g, spc_g)))
+    groups = [(raw[k], grads[k], state[k][0], state[k][1], lrs[k]) for k in PARAMETER_GROUPS]
+    raster.selective_adam_step(groups, ex.visibility, betas[0], betas[1], eps)
+    return grads
 
 
 def _all_gather(out, mine):

@@ -21,7 +21,9 @@ class FakeRaster:
 
     def trace(self, frame, deg, density, radiance, ray_o, ray_d, ray_t, camera):
         rgba = ray_o.sum() * torch.ones((H, W, 4)); d = torch.ones((H, W, 1))
-        return rgba, d, torch.zeros((H, W, 1)), torch.zeros((density.shape[0], 1))
+        vis = torch.zeros((density.shape[0], 1))
+        vis[int(ray_o.flatten()[0])::NVIEWS + 2] = 1.0      # view k sees particles k, k + 7, k + 14, ...
+        return rgba, d, torch.zeros((H, W, 1)), vis
 
     def trace_bwd(self, frame, deg, density, radiance, ray_o, ray_d, ray_t, camera, ts0, ts1, p0, p1, rgba, rgba_grad, d, d_grad,
                   out_density_grad=None, out_radiance_grad=None, accumulate=False):
@@ -74,6 +76,11 @@ def _step_deferred(rank, world):
     vpr = (NVIEWS + world - 1) // world
     ex = gdist.DeferredExchange(N, NSPH, vpr, "cpu", world=world)
     gdist.training_step_deferred(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids], rank=rank)
+    # the visibility SelectiveAdam masks with is the union over ALL views of the step, on every rank
+    want = torch.zeros((N, 1))
+    for k in range(NVIEWS):
+        want[k::NVIEWS + 2] = 1.0
+    assert torch.equal(ex.visibility, want), "visibility union"
     return ex.density_grad.clone(), ex.radiance_grad.clone()
 
 

@@ -266,3 +266,35 @@ def test_ply_scene_renders_identically(tmp_path):
         b = tracer.render(RawGaussians(raw2), make_batch(view, "cuda"))
     assert torch.equal(a["pred_rgb"], b["pred_rgb"]) and torch.equal(a["pred_dist"], b["pred_dist"])
     assert a["pred_opacity"].max() > 0.1
+
+
+def test_dist_optimizer_step_chains_activation_adjoint_and_adam(raster):
+    """dist.optimizer_step: summed [N,12] / [N,48] gradients -> raw-parameter gradients -> one SelectiveAdam launch masked by
+    the step's visibility union, against the oracle's restatement of the same chain."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    n = 4099
+    raw_t = _raw(n, 77)
+    raw = {"positions": raw_t["positions"], "rotation": raw_t["rotation"], "scale": raw_t["scale"], "density": raw_t["density"],
+           "features_albedo": raw_t["albedo"], "features_specular": raw_t["specular"]}
+    before = {k: v.cpu().numpy().copy() for k, v in raw.items()}
+    packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
+    ex = gdist.DeferredExchange(n, 48, 1, "cuda", world=1)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    ex.density_grad.copy_(torch.randn((n, 12), device="cuda", generator=gen))
+    ex.radiance_grad.copy_(torch.randn((n, 48), device="cuda", generator=gen))
+    ex.visibility.copy_((torch.rand((n, 1), device="cuda", generator=gen) < 0.7).float())
+    state = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in raw.items()}
+    lrs = {k: 10.0 ** (-2 - i) for i, k in enumerate(gdist.PARAMETER_GROUPS)}
+    grads = gdist.optimizer_step(raster, ex, raw, packed, state, lrs)
+    g = mo.activate_pack_backward(before["rotation"], packed.cpu().numpy(), ex.density_grad.cpu().numpy())
+    ga, gs = mo.unpack_feature_gradient(ex.radiance_grad.cpu().numpy())
+    want_g = dict(zip(gdist.PARAMETER_GROUPS, (g[0], g[1], g[2], g[3], ga, gs)))
+    vis = ex.visibility.cpu().numpy()
+    for k in gdist.PARAMETER_GROUPS:
+        assert rel_l2(grads[k].cpu().numpy(), want_g[k]) <= TOL_ACT, k
+        # Adam from the kernel's own gradient (the update itself is bit-exact, the activation adjoint is not)
+        p, m, v = mo.selective_adam_update(before[k], grads[k].cpu().numpy(), np.zeros_like(before[k]), np.zeros_like(before[k]), vis,
+                                           lrs[k], 0.9, 0.999, 1e-15)
+        assert np.array_equal(raw[k].cpu().numpy(), p), k
+        assert np.array_equal(state[k][0].cpu().numpy(), m) and np.array_equal(state[k][1].cpu().numpy(), v), k
+        assert np.array_equal(raw[k].cpu().numpy()[vis[:, 0] == 0], before[k][vis[:, 0] == 0]), k
