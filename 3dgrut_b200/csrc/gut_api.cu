@@ -514,6 +514,70 @@ int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_
     return GUT_OK;
 }
 
+int gut_sh_gradient_expand_gather(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degree, const float* d_density, uint32_t n_views,
+                                  const float* d_view_centres, const float* const* colour_grad_ptrs, float* d_radiance_grad, int32_t accumulate) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
+    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_gradient_expand_gather is built for 16 SH coefficients");
+    if (N == 0) return GUT_OK;
+    if (!d_density || !d_radiance_grad || (n_views > 0 && (!d_view_centres || !colour_grad_ptrs))) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    for (uint32_t v = 0; v < n_views; ++v)
+        if (!colour_grad_ptrs[v]) return fail(h, GUT_ERR_BAD_INPUT, "colour gradient pointer of view %u is NULL", v);
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_sh_expand_ptrs(N, sph_degree, d_density, n_views, d_view_centres, colour_grad_ptrs, d_radiance_grad, accumulate,
+                                          (cudaStream_t)stream_));
+    h->launches += n_views == 0 ? 1 : (n_views + GUT_EXPAND_MAX_VIEWS - 1) / GUT_EXPAND_MAX_VIEWS;
+    return GUT_OK;
+}
+
+static_assert(sizeof(cudaIpcMemHandle_t) == GUT_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+
+int gut_peer_buffer_create(GutHandle* h, size_t bytes, void** d_ptr_out, unsigned char* ipc_handle_out) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!d_ptr_out || !ipc_handle_out || bytes == 0) return fail(h, GUT_ERR_BAD_INPUT, "null pointer or empty buffer");
+    DeviceGuard guard(h->device);
+    void* p = nullptr;
+    GUT_CUDA(h, cudaMalloc(&p, bytes));      // a plain allocation: stream-ordered (pool) memory cannot be exported through CUDA IPC
+    cudaIpcMemHandle_t hd;
+    cudaError_t e = cudaMemset(p, 0, bytes);
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hd, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return fail(h, GUT_ERR_CUDA, "exporting the peer buffer failed: %s", cudaGetErrorString(e));
+    }
+    memcpy(ipc_handle_out, &hd, sizeof(hd));
+    *d_ptr_out = p;
+    return GUT_OK;
+}
+
+int gut_peer_buffer_destroy(GutHandle* h, void* d_ptr) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!d_ptr) return GUT_OK;
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, cudaFree(d_ptr));
+    return GUT_OK;
+}
+
+int gut_peer_buffer_open(GutHandle* h, const unsigned char* ipc_handle, void** d_ptr_out) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!ipc_handle || !d_ptr_out) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    DeviceGuard guard(h->device);
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, ipc_handle, sizeof(hd));
+    void* p = nullptr;
+    GUT_CUDA(h, cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+    *d_ptr_out = p;
+    return GUT_OK;
+}
+
+int gut_peer_buffer_close(GutHandle* h, void* d_ptr) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (!d_ptr) return GUT_OK;
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, cudaIpcCloseMemHandle(d_ptr));
+    return GUT_OK;
+}
+
 int gut_pack_particles(GutHandle* h, void* stream_, uint32_t N, const float* d_positions, const float* d_density, const float* d_rotation,
                        const float* d_scale, float* d_particle_density) {
     if (!h) return GUT_ERR_BAD_INPUT;

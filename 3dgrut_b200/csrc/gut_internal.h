@@ -76,6 +76,9 @@ cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* densit
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream);
 
 // exclusive scan of tile_hist[T*SUB] -> tile_start[T+1] and absolute sub-bucket cursors tile_cursor[T*SUB]; stats[0]=M, stats[1]=max list
+cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
+                                      const float* const* colour_ptrs /* host array of device pointers */, float* sph_grad, int accumulate,
+                                      cudaStream_t stream);
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
                                  uint32_t* stats, cudaStream_t stream);
 

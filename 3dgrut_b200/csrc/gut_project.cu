@@ -554,9 +554,17 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
 // Phase A: one thread per particle accumulates its 48 values over the views; phase B: the warp writes its 32 rows as
 // contiguous 128-bit accesses.
 // ---------------------------------------------------------------------------------------------------
+// The colour gradient of view v is read through views.colour[v]: a slice of a local buffer, or -- across GPUs -- a buffer
+// of a PEER GPU mapped into this process (gut_peer_buffer_open), so that the expansion reads the other ranks' gradients
+// straight over NVLink while it computes and no all-gather pass exists (3dgrut_b200/dist.py, training_step_peer).  All
+// loads of a chunk of views are issued before the first is used: one NVLink round trip per chunk, not per view.
+struct ExpandViews {
+    const float* colour[GUT_EXPAND_MAX_VIEWS];   // [N][3] each
+};
+constexpr int EXPAND_CHUNK = 8;
 __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                    uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
-                                                                   const float* __restrict__ colour_grads /* [n_views][N][3] */,
+                                                                   ExpandViews views,
                                                                    float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate) {
     __shared__ float s_out[K6_WARPS][32][49];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -567,20 +575,34 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
     for (int k = 0; k < 48; ++k) acc[k] = 0.0f;
     if (i < N) {
         const float4 r0 = __ldg(density12 + 3 * (size_t)i);
-        for (uint32_t v = 0; v < n_views; ++v) {
-            const float* gp = colour_grads + 3 * ((size_t)v * N + i);
-            const float3 g = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
-            if (g.x == 0.0f && g.y == 0.0f && g.z == 0.0f) continue;   // the view did not touch the particle
-            const float3 d = f3(r0.x, r0.y, r0.z) - f3(__ldg(centres + 3 * v), __ldg(centres + 3 * v + 1), __ldg(centres + 3 * v + 2));
-            const float len = sqrtf(dot(d, d));
-            const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(d.x / len, d.y / len, d.z / len);
-            float b[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) b[k] = 0.0f;
-            gut_sh_basis(sph_degree, dir, b);
+        for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {   // static indices into the pointer table
+            if (v0 >= n_views) break;
+            float3 gq[EXPAND_CHUNK];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                acc[3 * k] += b[k] * g.x; acc[3 * k + 1] += b[k] * g.y; acc[3 * k + 2] += b[k] * g.z;
+            for (int q = 0; q < EXPAND_CHUNK; ++q) {
+                gq[q] = f3(0.f, 0.f, 0.f);
+                if (v0 + q < n_views) {
+                    const float* gp = views.colour[v0 + q] + 3 * (size_t)i;
+                    gq[q] = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q) {
+                const float3 g = gq[q];
+                if (g.x == 0.0f && g.y == 0.0f && g.z == 0.0f) continue;   // the view did not touch the particle
+                const uint32_t v = v0 + q;
+                const float3 d = f3(r0.x, r0.y, r0.z) - f3(__ldg(centres + 3 * v), __ldg(centres + 3 * v + 1), __ldg(centres + 3 * v + 2));
+                const float len = sqrtf(dot(d, d));
+                const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(d.x / len, d.y / len, d.z / len);
+                float b[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) b[k] = 0.0f;
+                gut_sh_basis(sph_degree, dir, b);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    acc[3 * k] += b[k] * g.x; acc[3 * k + 1] += b[k] * g.y; acc[3 * k + 2] += b[k] * g.z;
+                }
             }
         }
     }
@@ -601,13 +623,38 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
     }
 }
 
+// colour_ptrs: HOST array of n_views device pointers.  More than GUT_EXPAND_MAX_VIEWS views are expanded in several
+// launches, the later ones accumulating.
+cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+                                      const float* const* colour_ptrs, float* sph_grad, int accumulate, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    uint32_t done = 0;
+    do {
+        const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
+        ExpandViews views = {};
+        for (uint32_t v = 0; v < nv; ++v) views.colour[v] = colour_ptrs[done + v];
+        gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
+            N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
+            reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0);
+        done += nv;
+    } while (done < n_views);
+    return cudaGetLastError();
+}
+
 cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
-        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, colour_grads,
-        reinterpret_cast<float4*>(sph_grad), accumulate);
-    return cudaGetLastError();
+    if (n_views == 0) return gut_launch_sh_expand_ptrs(N, sph_degree, density12, 0, centres, nullptr, sph_grad, accumulate, stream);
+    uint32_t done = 0;
+    cudaError_t e = cudaSuccess;
+    while (done < n_views && e == cudaSuccess) {   // contiguous [n_views][N][3] buffer -> pointer table, one chunk per launch
+        const float* ptrs[GUT_EXPAND_MAX_VIEWS];
+        const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
+        for (uint32_t v = 0; v < nv; ++v) ptrs[v] = colour_grads + 3 * (size_t)(done + v) * N;
+        e = gut_launch_sh_expand_ptrs(N, sph_degree, density12, nv, centres + 3 * (size_t)done, ptrs, sph_grad, (accumulate || done > 0) ? 1 : 0, stream);
+        done += nv;
+    }
+    return e;
 }
 
 cudaError_t gut_launch_copy_features3(uint32_t N, const float4* features4, float* features3, cudaStream_t stream) {

@@ -82,12 +82,14 @@ def training_step(raster, exchange, views, sph_degree, particle_density, particl
 class DeferredExchange:
     """Buffers of the deferred-SH step: [N,12] accumulator, per-view colour gradients of this rank and of all ranks."""
 
-    def __init__(self, n_particles, n_sph_floats, views_per_rank, device, world=None):
+    def __init__(self, n_particles, n_sph_floats, views_per_rank, device, world=None, track_visibility=False, gather_buffer=True):
         self.world = world if world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
         self.views_per_rank = views_per_rank
+        self.track_visibility = track_visibility   # needed by SelectiveAdam only: one more (small) collective per step
         self.density_grad = torch.zeros((n_particles, 12), dtype=torch.float32, device=device)
         self.radiance_grad = torch.zeros((n_particles, n_sph_floats), dtype=torch.float32, device=device)
-        self.colour_all = torch.zeros((self.world * views_per_rank, n_particles, 3), dtype=torch.float32, device=device)
+        self.colour_all = (torch.zeros((self.world * views_per_rank, n_particles, 3), dtype=torch.float32, device=device)
+                           if gather_buffer else None)
         self.centres_all = torch.zeros((self.world * views_per_rank, 3), dtype=torch.float32, device=device)
         # union over all views of the step of the tracer's mog_visibility: what SelectiveAdam masks its update with
         # (trainer.py:747-749 passes the visibility of the step's single view; with V views it is their union)
@@ -108,11 +110,13 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
     lo = ex.local_slot(rank, 0)
     mine = ex.colour_all[lo:lo + ex.views_per_rank]
     centres = []
-    ex.visibility.zero_()
+    if ex.track_visibility:
+        ex.visibility.zero_()
     for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
-        torch.maximum(ex.visibility, vis, out=ex.visibility)
+        if ex.track_visibility:
+            torch.maximum(ex.visibility, vis, out=ex.visibility)
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
                                     rgba, rg, dist_, dg, mine[i])
         centres.append(c)
@@ -128,12 +132,106 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         _all_gather(ex.colour_all, mine)
         _all_gather(ex.centres_all, my_centres)
         # the [N,12] allreduce runs on the collective stream while this stream expands the SH gradient
-        pending = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True),
-                   dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True)]   # union of the ranks' visibilities, 4 B/particle
+        pending = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
+        if ex.track_visibility:   # union of the ranks' visibilities, 4 B/particle
+            pending.append(dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True))
     raster.sh_gradient_expand(sph_degree, particle_density, ex.centres_all, ex.colour_all, ex.radiance_grad, accumulate=False)
     if pending is not None:
         for work in pending:
             work.wait()
+    return outs
+
+
+class _DeviceArray:
+    """A raw device allocation as something torch.as_tensor can wrap without copying (__cuda_array_interface__)."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class PeerExchange(DeferredExchange):
+    """DeferredExchange whose per-view colour gradients live in device buffers every rank of the node has mapped (CUDA IPC over
+    NVLink / NVSwitch): the SH expansion reads the other ranks' slices directly (gut_sh_gradient_expand_gather) and the
+    all-gather pass disappears.  Two buffer sets alternate between steps, so a rank may write step s+1 while a slower peer
+    still reads step s; the all-gather of the view centres (a few bytes) is the step's cross-rank ordering point.
+
+    One process per GPU, all on one node; ``raster`` provides the native handle.  Call ``close()`` before the process group
+    is destroyed."""
+
+    SETS = 2
+
+    def __init__(self, raster, n_particles, n_sph_floats, views_per_rank, device, rank, world=None):
+        super().__init__(n_particles, n_sph_floats, views_per_rank, device, world=world, gather_buffer=False)   # peer buffers instead
+        self.raster, self.rank = raster, rank
+        self.slot_floats = (3 * n_particles + 3) // 4 * 4       # 16-byte aligned slots
+        floats = self.SETS * views_per_rank * self.slot_floats
+        self.my_ptr, handle = raster.peer_buffer_create(floats * 4)
+        handles = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, handle)
+        else:
+            handles[0] = handle
+        self.ptrs = [self.my_ptr if r == rank else raster.peer_buffer_open(handles[r]) for r in range(self.world)]
+        self.mine = torch.as_tensor(_DeviceArray(self.my_ptr, floats), device=device).view(self.SETS, views_per_rank, self.slot_floats)
+        self.n_particles = n_particles
+        self.my_centres = torch.zeros((views_per_rank, 3), dtype=torch.float32, device=device)
+        self.step = 0
+        if self.world > 1:
+            dist.barrier()       # every rank has mapped every buffer before anyone writes
+
+    def slot_tensor(self, s, i):
+        """[N,3] view of this rank's slot i of buffer set s."""
+        return self.mine[s, i, :3 * self.n_particles].view(self.n_particles, 3)
+
+    def slot_ptr(self, r, s, i):
+        return self.ptrs[r] + 4 * ((s * self.views_per_rank + i) * self.slot_floats)
+
+    def bytes_per_rank(self):
+        return self.density_grad.numel() * 4 + self.views_per_rank * self.n_particles * 12
+
+    def close(self):
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()       # nobody still reads a buffer that is about to be unmapped
+        for r, p in enumerate(self.ptrs):
+            if r != self.rank:
+                self.raster.peer_buffer_close(p)
+        self.mine = None
+        self.raster.peer_buffer_destroy(self.my_ptr)
+        self.ptrs = []
+
+
+def training_step_peer(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
+    """``training_step_deferred`` with the colour-gradient all-gather folded into the expansion kernel (peer-memory loads).
+    Same summed [N,12] and [N,48] gradients on every rank."""
+    outs, centres = [], []
+    s = ex.step % ex.SETS
+    ex.step += 1
+    for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
+        rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
+                                              v["camera"])
+        c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
+                                    rgba, rg, dist_, dg, ex.slot_tensor(s, i))
+        centres.append(c)
+        outs.append((rgba, dist_))
+    for i in range(len(views), ex.views_per_rank):
+        ex.slot_tensor(s, i).zero_()
+        centres.append([0.0, 0.0, 0.0])
+    ex.my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
+    gathered, reduced = None, None
+    if ex.world > 1:
+        # ordering point of the step: this all-gather completes on a rank only after every rank's colour gradients are written
+        gathered = dist.all_gather_into_tensor(ex.centres_all.view(-1), ex.my_centres.view(-1), async_op=True)
+    else:
+        ex.centres_all.copy_(ex.my_centres)
+    raster.density_gradient_finish(particle_density, ex.density_grad)       # overlaps the ordering point
+    if ex.world > 1:
+        reduced = dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)
+        gathered.wait()
+    ptrs = [ex.slot_ptr(r, s, i) for r in range(ex.world) for i in range(ex.views_per_rank)]
+    raster.sh_gradient_expand_gather(sph_degree, particle_density, ex.centres_all, ptrs, ex.radiance_grad, accumulate=False)
+    if reduced is not None:
+        reduced.wait()
     return outs
 
 

@@ -72,6 +72,16 @@ def load_library():
     lib.gut_density_gradient_finish.restype = C.c_int
     lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
     lib.gut_sh_gradient_expand.restype = C.c_int
+    lib.gut_sh_gradient_expand_gather.argtypes = [vp, vp, u32, i32, fp, u32, fp, C.POINTER(C.c_void_p), fp, i32]
+    lib.gut_sh_gradient_expand_gather.restype = C.c_int
+    lib.gut_peer_buffer_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]
+    lib.gut_peer_buffer_create.restype = C.c_int
+    lib.gut_peer_buffer_destroy.argtypes = [vp, vp]
+    lib.gut_peer_buffer_destroy.restype = C.c_int
+    lib.gut_peer_buffer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    lib.gut_peer_buffer_open.restype = C.c_int
+    lib.gut_peer_buffer_close.argtypes = [vp, vp]
+    lib.gut_peer_buffer_close.restype = C.c_int
     lib.gut_pack_particles.argtypes = [vp, vp, u32, fp, fp, fp, fp, fp]
     lib.gut_pack_particles.restype = C.c_int
     lib.gut_unpack_particle_gradient.argtypes = [vp, vp, u32, fp, fp, fp, fp, fp]
@@ -336,6 +346,44 @@ class SplatRaster:
         if rc != 0:
             self._raise(rc)
         return out_radiance_grad
+
+    def sh_gradient_expand_gather(self, num_active_features, particle_density, view_centres, colour_ptrs, out_radiance_grad, accumulate=False):
+        """gut_sh_gradient_expand_gather: like sh_gradient_expand, with one device pointer per view (int addresses; local slices or
+        buffers of peer GPUs opened with peer_buffer_open).  ``view_centres`` is a [V,3] float32 CUDA tensor."""
+        dev = self.device
+        dens = _check_cuda_f32("particle_density", particle_density, dev)
+        vc = _check_cuda_f32("view_centres", view_centres, dev)
+        n, nv = dens.shape[0], len(colour_ptrs)
+        if vc.shape != (nv, 3) or out_radiance_grad.shape != (n, self.n_coeffs * 3) or not out_radiance_grad.is_contiguous():
+            raise GutError(abi.GutStatus.BAD_INPUT, "view_centres must be [V,3] with one pointer per view, out_radiance_grad a contiguous [N,48]")
+        table = (C.c_void_p * max(nv, 1))(*[int(x) for x in colour_ptrs])
+        rc = self.lib.gut_sh_gradient_expand_gather(self._h, self._stream(), n, int(num_active_features), _ptr(dens), nv, _ptr(vc), table,
+                                                    _ptr(out_radiance_grad), 1 if accumulate else 0)
+        if rc != 0:
+            self._raise(rc)
+        return out_radiance_grad
+
+    def peer_buffer_create(self, nbytes):
+        """gut_peer_buffer_create -> (device address, 64-byte CUDA IPC handle) of a zeroed device allocation peers can map."""
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        rc = self.lib.gut_peer_buffer_create(self._h, int(nbytes), C.byref(ptr), handle)
+        if rc != 0:
+            self._raise(rc)
+        return int(ptr.value), handle.raw
+
+    def peer_buffer_open(self, handle):
+        ptr = C.c_void_p()
+        rc = self.lib.gut_peer_buffer_open(self._h, bytes(handle), C.byref(ptr))
+        if rc != 0:
+            self._raise(rc)
+        return int(ptr.value)
+
+    def peer_buffer_close(self, ptr):
+        self.lib.gut_peer_buffer_close(self._h, C.c_void_p(int(ptr)))
+
+    def peer_buffer_destroy(self, ptr):
+        self.lib.gut_peer_buffer_destroy(self._h, C.c_void_p(int(ptr)))
 
     def pack_particles(self, positions, density, rotation, scale):
         """gut_pack_particles: [N,3], [N,1], [N,4], [N,3] -> the [N,12] particle_density record (tracer.py:176-178's torch.cat)."""

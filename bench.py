@@ -47,22 +47,26 @@ def parse_args():
     p.add_argument("--height", type=int, default=H_IMG)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    p.add_argument("--exchange", choices=("deferred", "allreduce"), default="deferred",
+    p.add_argument("--exchange", choices=("auto", "peer", "deferred", "allreduce"), default="auto",
                    help="gradient exchange of the step: deferred = allreduce [N,12] + all-gather per-view colour gradients, SH expansion "
-                        "once per step (3dgrut_b200/dist.py training_step_deferred); allreduce = per-view [N,48] accumulation + one "
-                        "allreduce of [N,12]+[N,48]")
+                        "once per step (3dgrut_b200/dist.py training_step_deferred); peer = the same with the all-gather folded into the "
+                        "expansion kernel (loads from the other ranks' buffers over NVLink, training_step_peer); allreduce = per-view "
+                        "[N,48] accumulation + one allreduce of [N,12]+[N,48]; auto = peer on more than one GPU, deferred on one")
     p.add_argument("--no-aux", action="store_true", help="skip the auxiliary forward-only 1080p measurement")
     p.add_argument("--cpu-sample-tiles", type=int, default=24)
     return p.parse_args()
 
 
 def workload_config(args, world):
+    exchange = ("peer" if world > 1 else "deferred") if args.exchange == "auto" else args.exchange
     return {
         "workload": f"3DGUT training step: {args.particles} random-init Gaussians (S-init), SH deg {SPH_DEGREE}, batch of {args.views} "
                     f"pinhole views {args.width}x{args.height}, k_buffer_size=0, views sharded over {world} GPU(s), "
                     + ("NCCL allreduce of the [N,12] fp32 gradients + all-gather of the per-view colour gradients [N,3], SH gradient "
-                       "[N,48] expanded once per step on every rank" if args.exchange == "deferred" else
-                       "NCCL allreduce of [N,12]+[N,48] fp32 gradients"),
+                       "[N,48] expanded once per step on every rank" if exchange == "deferred" else
+                       "NCCL allreduce of the [N,12] fp32 gradients; per-view colour gradients [N,3] read from the other ranks' buffers over "
+                       "NVLink inside the kernel that expands the SH gradient [N,48] (peer memory, no all-gather pass)"
+                       if exchange == "peer" else "NCCL allreduce of [N,12]+[N,48] fp32 gradients"),
         "particles": args.particles, "views_per_step": args.views, "width": args.width, "height": args.height,
         "sph_degree": SPH_DEGREE, "parallelism": f"view-sharded dp{world}, particles replicated",
         "l2_policy": "inputs larger than L2: every view streams the particle parameters and SH (3M x 240 B = 720 MB), the [N,16] gradient "
@@ -248,9 +252,26 @@ def run_ours(args):
 
     cfg = abi.default_config(enable_kernel_timings=1)
     raster = native.SplatRaster(cfg, device=dev)
+    if args.exchange == "auto":
+        args.exchange = "peer" if world > 1 else "deferred"
+    if args.exchange == "peer":
+        try:
+            exchange = gdist.PeerExchange(raster, n, sph.shape[1], (args.views + world - 1) // world, dev, rank, world=world)
+            ok = 1
+        except Exception as e:   # CUDA IPC unavailable on this box: every rank falls back together
+            print(f"[bench] rank {rank}: peer buffers unavailable ({e!r})", file=sys.stderr, flush=True)
+            exchange, ok = None, 0
+        if world > 1:
+            flag = torch.tensor([ok], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = int(flag.item())
+        if not ok:
+            if exchange is not None:
+                exchange.close()
+            args.exchange = "deferred"
     if args.exchange == "deferred":
         exchange = gdist.DeferredExchange(n, sph.shape[1], (args.views + world - 1) // world, dev, world=world)
-    else:
+    elif args.exchange == "allreduce":
         exchange = gdist.GradientExchange(n, sph.shape[1], dev, world=world)
 
     def barrier():
@@ -260,6 +281,8 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     def step():
+        if args.exchange == "peer":
+            return gdist.training_step_peer(raster, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
         if args.exchange == "deferred":
             return gdist.training_step_deferred(raster, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
         return gdist.training_step(raster, exchange, views, SPH_DEGREE, d12, sph, upstream)
@@ -332,7 +355,7 @@ def run_ours(args):
               "71 FLOP/test + 32 FLOP/hit")
     add_stage("render-backward::render", "fp32", tests_v * FLOP_BWD_TEST + hits_v * FLOP_BWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "100 FLOP/test + 250 FLOP/hit")
-    if args.exchange == "deferred":
+    if args.exchange in ("deferred", "peer"):
         add_stage("render-backward::project", "hbm", n * (16 + 32 + 12), 1e9, hbm_peak, "GB/s",
                   "per view: 16 B colour + one 32 B accumulator sector in, 12 B colour gradient out per particle "
                   "(the [N,12] / [N,48] conversions run once per step, outside the per-view stages)")
@@ -579,6 +602,8 @@ def run_ours(args):
             "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16, "model_side": model_side,
         }
         print(json.dumps(line), flush=True)
+    if args.exchange == "peer":
+        exchange.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -232,6 +232,25 @@ GUT_API int gut_sh_gradient_expand(GutHandle* h, void* stream, uint32_t num_part
                  const float* d_colour_grads, float* d_particle_radiance_grad, int32_t accumulate);
 
 /*
+ * The same expansion with one pointer per view (a HOST array of n_views device pointers, each [N,3]), so that a view's colour
+ * gradient may live in a buffer of a PEER GPU: gut_peer_buffer_create makes a device allocation that other processes of the
+ * node map with gut_peer_buffer_open (CUDA IPC over NVLink / NVSwitch), and the expansion kernel then reads the other ranks'
+ * per-view colour gradients directly while it computes -- the all-gather of the data-parallel step becomes loads inside
+ * the kernel that consumes it.  The caller orders the step across ranks (every rank's colour gradients are complete
+ * before any rank expands; 3dgrut_b200/dist.py does it with the small all-gather of the view centres).
+ * No reference counterpart (the reference is single-GPU); n_views == 0 writes zeros.
+ */
+#define GUT_EXPAND_MAX_VIEWS 16      /* views per launch; more are expanded in several launches */
+#define GUT_IPC_HANDLE_BYTES 64
+GUT_API int gut_sh_gradient_expand_gather(GutHandle* h, void* stream, uint32_t num_particles, int32_t sph_degree_active,
+                 const float* d_particle_density, uint32_t n_views, const float* d_view_centres,
+                 const float* const* colour_grad_ptrs, float* d_particle_radiance_grad, int32_t accumulate);
+GUT_API int gut_peer_buffer_create(GutHandle* h, size_t bytes, void** d_ptr_out, unsigned char* ipc_handle_out /* [64] */);
+GUT_API int gut_peer_buffer_destroy(GutHandle* h, void* d_ptr);
+GUT_API int gut_peer_buffer_open(GutHandle* h, const unsigned char* ipc_handle /* [64] */, void** d_ptr_out);
+GUT_API int gut_peer_buffer_close(GutHandle* h, void* d_ptr);
+
+/*
  * Packing of the model's parameter tensors into the [N,12] particle_density record and the inverse for its gradient.
  * Replaces: torch.cat([positions, density, rotation, scale, zeros], dim=1) in threedgut_tracer/tracer.py:176-178 and the
  * column split autograd derives from it for the backward (tracer.py:265-286 returns the [N,12] gradient, autograd slices it).

@@ -74,7 +74,7 @@ def _step_deferred(rank, world):
     density, radiance, views, ups = _data()
     ids = gdist.shard_views(NVIEWS, rank, world)
     vpr = (NVIEWS + world - 1) // world
-    ex = gdist.DeferredExchange(N, NSPH, vpr, "cpu", world=world)
+    ex = gdist.DeferredExchange(N, NSPH, vpr, "cpu", world=world, track_visibility=True)
     gdist.training_step_deferred(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids], rank=rank)
     # the visibility SelectiveAdam masks with is the union over ALL views of the step, on every rank
     want = torch.zeros((N, 1))

@@ -278,7 +278,7 @@ def test_dist_optimizer_step_chains_activation_adjoint_and_adam(raster):
            "features_albedo": raw_t["albedo"], "features_specular": raw_t["specular"]}
     before = {k: v.cpu().numpy().copy() for k, v in raw.items()}
     packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
-    ex = gdist.DeferredExchange(n, 48, 1, "cuda", world=1)
+    ex = gdist.DeferredExchange(n, 48, 1, "cuda", world=1, track_visibility=True)
     gen = torch.Generator(device="cuda").manual_seed(3)
     ex.density_grad.copy_(torch.randn((n, 12), device="cuda", generator=gen))
     ex.radiance_grad.copy_(torch.randn((n, 48), device="cuda", generator=gen))
