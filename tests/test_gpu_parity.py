@@ -248,6 +248,53 @@ def test_deferred_sh_gradient_equals_per_view_accumulation(pkg):
     assert rel_l2(dx.radiance_grad.cpu().numpy(), ex.radiance_grad.cpu().numpy()) <= 1e-5
 
 
+def test_expand_gather_with_peer_buffer_equals_contiguous_expand(pkg):
+    """gut_sh_gradient_expand_gather (one pointer per view) over slots of a gut_peer_buffer_create allocation == gut_sh_gradient_expand
+    over a contiguous [V,N,3] buffer; 19 views exercise the chunking (16 per launch) and the accumulate flag.  Single process: the
+    cross-rank mapping (gut_peer_buffer_open) is covered by scripts/multi_gpu_peer_check.py on 2+ GPUs."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = _raster(pkg)
+    n, nv = 3001, 19
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    d12 = syn.pack_density(syn.make_scene(n, 3, seed=2)).cuda()
+    colour = torch.randn((nv, n, 3), device="cuda", generator=gen)
+    colour[:, ::4] = 0.0                                   # untouched particles
+    centres = torch.randn((nv, 3), device="cuda", generator=gen) * 4
+    want = torch.empty((n, 48), device="cuda")
+    raster.sh_gradient_expand(3, d12, centres, colour, want)
+    ex = gdist.PeerExchange(raster, n, 48, nv, "cuda", rank=0, world=1)
+    for i in range(nv):
+        ex.slot_tensor(1, i).copy_(colour[i])
+    ptrs = [ex.slot_ptr(0, 1, i) for i in range(nv)]
+    assert all(p % 16 == 0 for p in ptrs)
+    got = torch.full((n, 48), 7.0, device="cuda")
+    raster.sh_gradient_expand_gather(3, d12, centres, ptrs, got)
+    assert torch.equal(got, want)
+    raster.sh_gradient_expand_gather(3, d12, centres, ptrs, got, accumulate=True)
+    assert rel_l2(got.cpu().numpy(), 2 * want.cpu().numpy()) <= 1e-6     # (want + chunk 1) + chunk 2: another summation order
+    raster.sh_gradient_expand_gather(3, d12, centres[:0], [], got)      # no views: zeros
+    assert not got.any()
+    with pytest.raises(native.GutError):
+        raster.sh_gradient_expand_gather(3, d12, centres[:2], [ptrs[0], 0], got)
+    # one-rank step through the peer formulation == the deferred formulation
+    w, h = 64, 48
+    hv = syn.make_view(w, h)
+    views = [{"rays_ori": hv["rays_ori"].cuda(), "rays_dir": hv["rays_dir"].cuda(), "camera": camera_of(hv)}]
+    ups = [(torch.rand((h, w, 4), device="cuda", generator=gen) * 2 - 1, torch.rand((h, w, 1), device="cuda", generator=gen) * 0.01)]
+    sph = syn.make_scene(n, 3, seed=2)["features"].cuda()
+    px = gdist.PeerExchange(raster, n, 48, 1, "cuda", rank=0, world=1)
+    dx = gdist.DeferredExchange(n, 48, 1, "cuda", world=1)
+    for _ in range(2):   # both buffer sets
+        gdist.training_step_peer(raster, px, views, 3, d12, sph, ups)
+        gdist.training_step_deferred(raster, dx, views, 3, d12, sph, ups)
+        torch.cuda.synchronize()
+        assert float(dx.radiance_grad.abs().max()) > 0
+        assert rel_l2(px.radiance_grad.cpu().numpy(), dx.radiance_grad.cpu().numpy()) <= 1e-5
+        assert rel_l2(px.density_grad.cpu().numpy(), dx.density_grad.cpu().numpy()) <= 1e-5
+    px.close(); ex.close()
+
+
 def test_empty_and_error_paths(pkg):
     native = importlib.import_module("3dgrut_b200.native")
     raster = _raster(pkg)
