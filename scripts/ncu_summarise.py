@@ -49,6 +49,28 @@ with open(f"{out_dir}/ncu_full_{tag}.md", "w") as f:
             if w in hdr:
                 i = hdr.index(w)
                 f.write(f"| {w} | {r[i]} | {units[i]} |\n")
+    # auxiliary captures (k-buffer kernels of the K = 16 configuration, model-side passes): first launch of each kernel
+    for extra, what in (("kbuffer", "the K = 16 forward + backward of the auxiliary `sorted_k16` measurement"),
+                        ("model", "the model-side passes of the auxiliary `model_side` measurement (N = 3M)")):
+        rep2 = f"gpurun_out/prof_{tag}_{extra}.ncu-rep"
+        if not os.path.exists(rep2):
+            continue
+        raw2 = subprocess.run(["ncu", "-i", rep2, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows2 = list(csv.reader(io.StringIO(raw2)))
+        if len(rows2) < 3:
+            continue
+        hdr2, units2, seen = rows2[0], rows2[1], set()
+        f.write(f"\n# auxiliary capture: {what}\n")
+        for r in rows2[2:]:
+            name = r[hdr2.index("Kernel Name")].split("(")[0]
+            if name in seen:
+                continue
+            seen.add(name)
+            f.write(f"\n## `{name}`\n\n| metric | value | unit |\n|---|---|---|\n")
+            for w in want:
+                if w in hdr2:
+                    i = hdr2.index(w)
+                    f.write(f"| {w} | {r[i]} | {units2[i]} |\n")
 print("wrote", f"{out_dir}/launches_{tag}.md", f"{out_dir}/ncu_full_{tag}.md")
 
 # ---- DRAM traffic per launch of each stage's kernel -> profiles/traffic.json (bench.py's roofline.traffic) ----------
