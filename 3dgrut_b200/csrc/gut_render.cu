@@ -116,13 +116,26 @@ GUT_D RayPair make_ray_pair(const GutFrame& fr, const float* __restrict__ ray_or
 }
 
 
+// The four compositing thresholds are -D defines in the reference (setup_3dgut.py:47-70) and run-time fields of GutConfig
+// here.  STD = true instantiates the kernels with the reference's default values as immediates (no constant-bank loads,
+// no registers); gut_launch_render* picks it when the handle's configuration holds exactly those values.
+constexpr float STD_MIN_RESPONSE = 0.0113f, STD_MIN_ALPHA = (float)(1.0 / 255.0), STD_MAX_ALPHA = 0.99f, STD_MIN_T = 0.0001f;
+template <bool STD> GUT_D float thr_min_response(const GutConfig& c) { return STD ? STD_MIN_RESPONSE : c.min_kernel_response; }
+template <bool STD> GUT_D float thr_min_alpha(const GutConfig& c) { return STD ? STD_MIN_ALPHA : c.min_alpha; }
+template <bool STD> GUT_D float thr_max_alpha(const GutConfig& c) { return STD ? STD_MAX_ALPHA : c.max_alpha; }
+template <bool STD> GUT_D float thr_min_T(const GutConfig& c) { return STD ? STD_MIN_T : c.min_transmittance; }
+inline bool thresholds_are_standard(const GutConfig& c) {
+    return c.min_kernel_response == STD_MIN_RESPONSE && c.min_alpha == STD_MIN_ALPHA && c.max_alpha == STD_MAX_ALPHA &&
+           c.min_transmittance == STD_MIN_T;
+}
+
 // canonical-frame test shared by forward and backward, for the two rays of a lane.  u = ms d (unnormalised canonical
 // direction), go = canonical origin, c = u x go.
 struct Canon2 {
     F2x3 go, u, c;
     F2 l2, il2, g2, resp, araw;
 };
-template <int DEG, bool UNIFORM>
+template <int DEG, bool UNIFORM, bool STD>
 GUT_D void particle_test(const GutConfig& cfg, const float4 A, const float4 B, const float4 Cm, const float density, const RayPair& ray,
                          Canon2& k, bool& accept0, bool& accept1) {
     k.go.x = bc(A.w); k.go.y = bc(B.w); k.go.z = bc(Cm.w);
@@ -148,8 +161,8 @@ GUT_D void particle_test(const GutConfig& cfg, const float4 A, const float4 B, c
     k.resp = mk2(r0, r1);
     k.araw = k.resp * bc(density);
     // alpha = min(max_alpha, araw) > min_alpha  <=>  araw > min_alpha  (max_alpha > min_alpha is checked at gut_create)
-    accept0 = (r0 > cfg.min_kernel_response) && (lo(k.araw) > cfg.min_alpha);
-    accept1 = (r1 > cfg.min_kernel_response) && (hi(k.araw) > cfg.min_alpha);
+    accept0 = (r0 > thr_min_response<STD>(cfg)) && (lo(k.araw) > thr_min_alpha<STD>(cfg));
+    accept1 = (r1 > thr_min_response<STD>(cfg)) && (hi(k.araw) > thr_min_alpha<STD>(cfg));
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -163,7 +176,7 @@ struct FwdState {
 
 // Returns, as a bit per record of the batch, which records one of this lane's two rays accepted while alive (before the
 // tMinMax test): the union over the warp is what the backward has to revisit (hit_mask_slot below).
-template <int DEG, bool UNIFORM, bool COUNT>
+template <int DEG, bool UNIFORM, bool COUNT, bool STD>
 GUT_D uint32_t forward_walk(const GutConfig& cfg, const float4* __restrict__ rec, uint32_t cnt, const RayPair& ray, FwdState& st) {
     uint32_t accepted = 0;
     const uint32_t cnt_pad = (cnt + WALK_UNROLL - 1) & ~(WALK_UNROLL - 1);
@@ -182,7 +195,7 @@ GUT_D uint32_t forward_walk(const GutConfig& cfg, const float4* __restrict__ rec
                 for (int p = 0; p < 2; ++p) {
                     const float4 A = r[5 * p], B = r[5 * p + 1], Cm = r[5 * p + 2];
                     S[p] = r[5 * p + 3];
-                    particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S[p].w, ray, k[p], acc[p][0], acc[p][1]);
+                    particle_test<DEG, UNIFORM, STD>(cfg, A, B, Cm, S[p].w, ray, k[p], acc[p][0], acc[p][1]);
                 }
 #pragma unroll
                 for (int p = 0; p < 2; ++p) {
@@ -199,7 +212,7 @@ GUT_D uint32_t forward_walk(const GutConfig& cfg, const float4* __restrict__ rec
                         const bool in0 = h0 && t0 > ray.tmin[0] && t0 < ray.tmax[0];
                         const bool in1 = h1 && t1 > ray.tmin[1] && t1 < ray.tmax[1];
                         // a ray that does not take the hit composites alpha = 0: its state is left unchanged
-                        const F2 alpha = mk2(in0 ? fminf(cfg.max_alpha, lo(k[p].araw)) : 0.0f, in1 ? fminf(cfg.max_alpha, hi(k[p].araw)) : 0.0f);
+                        const F2 alpha = mk2(in0 ? fminf(thr_max_alpha<STD>(cfg), lo(k[p].araw)) : 0.0f, in1 ? fminf(thr_max_alpha<STD>(cfg), hi(k[p].araw)) : 0.0f);
                         const float4 F = r[5 * p + 4];
                         const F2 w = alpha * st.T;
                         st.D = fma(mk2(in0 ? t0 : 0.0f, in1 ? t1 : 0.0f), w, st.D);
@@ -207,8 +220,8 @@ GUT_D uint32_t forward_walk(const GutConfig& cfg, const float4* __restrict__ rec
                         st.cr = fma(bc(F.x), w, st.cr); st.cg = fma(bc(F.y), w, st.cg); st.cb = fma(bc(F.z), w, st.cb);
                         if (lo(w) > 0.0f) st.nhits[0]++;
                         if (hi(w) > 0.0f) st.nhits[1]++;
-                        if (lo(st.T) < cfg.min_transmittance) st.alive[0] = false;
-                        if (hi(st.T) < cfg.min_transmittance) st.alive[1] = false;
+                        if (lo(st.T) < thr_min_T<STD>(cfg)) st.alive[0] = false;
+                        if (hi(st.T) < thr_min_T<STD>(cfg)) st.alive[1] = false;
                     }
                 }
             }
@@ -228,7 +241,7 @@ GUT_D size_t hit_mask_slot(uint32_t b0, uint32_t tile, uint32_t b, uint32_t bloc
 
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
-template <int DEG, bool COUNT>
+template <int DEG, bool COUNT, bool STD>
 __global__ void __launch_bounds__(RENDER_THREADS, 24) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                      GutParticleSource src,
                                                                      const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
@@ -283,8 +296,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, 24) gut_render_kernel(GutConfi
         // records no ray of the block can accept are dropped while staging; the walk sees the kept ones, compacted
         uint32_t keep;
         const uint32_t kept = stg.stage_culled(b, cfg, s_cone, keep);
-        const uint32_t accepted = uniform ? forward_walk<DEG, true, COUNT>(cfg, stg.rec, kept, ray, st)
-                                          : forward_walk<DEG, false, COUNT>(cfg, stg.rec, kept, ray, st);
+        const uint32_t accepted = uniform ? forward_walk<DEG, true, COUNT, STD>(cfg, stg.rec, kept, ray, st)
+                                          : forward_walk<DEG, false, COUNT, STD>(cfg, stg.rec, kept, ray, st);
         if (!COUNT && hit_masks) {
             // bit k of `accepted` = k-th kept record; the backward indexes the batch by list position
             const uint32_t lane = threadIdx.x & 31;
@@ -413,10 +426,10 @@ struct BwdRay {
 // quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.
 // A ray of the lane that does not take the hit runs the same packed instructions with alpha = 0 and a zeroed
 // upstream sum: every one of its 15 values is then exactly 0 and its state is unchanged.
-template <int DEG, bool UNIFORM>
+template <int DEG, bool UNIFORM, bool STD>
 GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, const float4* __restrict__ recb, uint32_t mask,
                          const RayPair& ray, BwdRay& st, uint32_t lane, float* __restrict__ raw_grad, float* __restrict__ tile) {
-    const float minT = cfg.min_transmittance;
+    const float minT = thr_min_T<STD>(cfg);
     const F2 one = bc(1.0f);
     while (mask) {
       {
@@ -426,7 +439,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
         const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
         Canon2 k;
         bool acc0, acc1;
-        particle_test<DEG, UNIFORM>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
+        particle_test<DEG, UNIFORM, STD>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
         const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];  // no tMinMax test here
 
         // every lane runs the hit math (rays that do not take the hit are masked, see above): no lane-level branch
@@ -447,7 +460,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             sg2.x = sg.x * sg.x; sg2.y = sg.y * sg.y; sg2.z = sg.z * sg.z;
             const F2 ssum = sg2.x + sg2.y + sg2.z;
             const F2 gdist = mk2(h0 ? fabsf(lo(dgo)) * mufu_sqrt(lo(ssum)) : 0.0f, h1 ? fabsf(hi(dgo)) * mufu_sqrt(hi(ssum)) : 0.0f);
-            const F2 alpha = mk2(h0 ? fminf(cfg.max_alpha, lo(k.araw)) : 0.0f, h1 ? fminf(cfg.max_alpha, hi(k.araw)) : 0.0f);
+            const F2 alpha = mk2(h0 ? fminf(thr_max_alpha<STD>(cfg), lo(k.araw)) : 0.0f, h1 ? fminf(thr_max_alpha<STD>(cfg), hi(k.araw)) : 0.0f);
             const F2 T = st.T;
             const F2 w = alpha * T;
             const F2 om = one - alpha;
@@ -543,7 +556,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 // UNIFORM (every ray of the block starts at the frame origin) is a launch-level template parameter: the kernel is launched
 // once per variant and a block leaves at once when its rays are of the other kind.  Keeping the per-ray origin offsets
 // out of the common variant's live set is worth 0.27 ms per view at the 96-register cap; the idle launch costs ~10 us.
-template <int DEG, bool UNIFORM>
+template <int DEG, bool UNIFORM, bool STD>
 __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render_backward_kernel(
     GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start, GutParticleSource src,
     const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
@@ -593,7 +606,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     for (uint32_t b = 0; b < stg.nb; ++b) {
         stg.stage(b);
         const uint32_t mask = __ldg(hit_masks + hit_mask_slot(b0, tile, b, block));   // entries some ray of the block accepted in the forward
-        backward_walk<DEG, UNIFORM>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad, reduce_tile);
+        backward_walk<DEG, UNIFORM, STD>(cfg, stg.rec, stg.recb, mask, ray, st, lane, raw_grad, reduce_tile);
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
         stg.rotate();
     }
@@ -609,11 +622,14 @@ cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const
     const char* dbg = getenv("GUT_DEBUG_NO_BLOCK_CULL");
     const bool cull = !(dbg && dbg[0] == '1');
     if (counters)
-        gut_render_kernel<DEG, true><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
-                                                                       nullptr, counters, nullptr, cull);
+        gut_render_kernel<DEG, true, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
+                                                                              nullptr, counters, nullptr, cull);
+    else if (DEG == 2 && thresholds_are_standard(cfg))   // the reference's defaults as immediates (default kernel degree only)
+        gut_render_kernel<DEG, false, DEG == 2><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
+                                                                                  reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks, cull);
     else
-        gut_render_kernel<DEG, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
-                                                                        reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks, cull);
+        gut_render_kernel<DEG, false, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir,
+                                                                               reinterpret_cast<float4*>(rgba), dist, hits, nullptr, hit_masks, cull);
     return cudaGetLastError();
 }
 
@@ -623,12 +639,21 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
                                   const float* rgba_grad, const float* dist, const float* dist_grad, float* raw_grad,
                                   const uint32_t* hit_masks, cudaStream_t stream) {
     const uint32_t grid = frame.num_tiles * BLOCKS_PER_TILE;
-    gut_render_backward_kernel<DEG, true><<<grid, RENDER_THREADS, 0, stream>>>(
-        cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
-        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
-    gut_render_backward_kernel<DEG, false><<<grid, RENDER_THREADS, 0, stream>>>(
-        cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
-        reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
+    if (DEG == 2 && thresholds_are_standard(cfg)) {
+        gut_render_backward_kernel<DEG, true, DEG == 2><<<grid, RENDER_THREADS, 0, stream>>>(
+            cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+            reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
+        gut_render_backward_kernel<DEG, false, DEG == 2><<<grid, RENDER_THREADS, 0, stream>>>(
+            cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+            reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
+    } else {
+        gut_render_backward_kernel<DEG, true, false><<<grid, RENDER_THREADS, 0, stream>>>(
+            cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+            reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
+        gut_render_backward_kernel<DEG, false, false><<<grid, RENDER_THREADS, 0, stream>>>(
+            cfg, frame, tile_start, src, ray_ori, ray_dir, reinterpret_cast<const float4*>(rgba),
+            reinterpret_cast<const float4*>(rgba_grad), dist, dist_grad, raw_grad, hit_masks);
+    }
     return cudaGetLastError();
 }
 

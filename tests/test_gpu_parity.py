@@ -106,6 +106,36 @@ def test_backward_gradients(pkg, name, n, w, h, deg, kind, seed):
     assert e <= TOL_GRAD, (name, "sph", e)
 
 
+def test_non_default_thresholds_take_the_run_time_path(pkg):
+    """The reference's default thresholds are immediates in the degree-2 kernels (gut_render.cu, STD = true); any other value
+    of particle_kernel_min_response / min_alpha / max_alpha / min_transmittance runs the instantiation that reads GutConfig."""
+    n, w, h, deg = 3000, 80, 64, 2
+    scene = syn.make_scene(n, 3, seed=31, kind="dense")
+    view = syn.make_view(w, h)
+    over = dict(particle_kernel_min_response=0.05, particle_kernel_min_alpha=0.01, particle_kernel_max_alpha=0.9, min_transmittance=0.02)
+    cfg = cfg_from_conf(make_conf(**over))
+    assert abs(cfg.max_alpha - 0.9) < 1e-6 and abs(cfg.min_transmittance - 0.02) < 1e-6
+    rng = np.random.default_rng(31)
+    rgba_grad = rng.uniform(-1, 1, (h, w, 4)).astype(np.float32)
+    dist_grad = rng.uniform(-0.01, 0.01, (h, w)).astype(np.float32)
+    ref0 = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg)
+    border = ref0["borderline"]
+    rgba_grad[border] = 0; dist_grad[border] = 0
+    ref = oracle_reference(scene, view, w, h, sph_degree=deg, cfg=cfg, rgba_grad=rgba_grad, dist_grad=dist_grad)
+    ref_std = oracle_reference(scene, view, w, h, sph_degree=deg)
+    assert np.abs(ref["rgba"] - ref_std["rgba"]).max() > 1e-3       # the thresholds matter on this scene
+    raster = _raster(pkg, **over)
+    (rgba, dist, hits, vis), (d12, sph, cam) = _run_forward(raster, scene, view, deg, stage=False)
+    stats = compare_images(rgba.cpu().numpy(), ref["rgba"], border)
+    assert stats["max_abs_clean"] <= TOL_IMG, stats
+    rgba_o = torch.from_numpy(ref["rgba"]).cuda(); dist_o = torch.from_numpy(ref["dist"]).cuda().reshape(h, w, 1)
+    g12, gsph = raster.trace_bwd(0, deg, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba_o, torch.from_numpy(rgba_grad).cuda(), dist_o, torch.from_numpy(dist_grad).cuda().reshape(h, w, 1))
+    torch.cuda.synchronize()
+    assert rel_l2(g12.cpu().numpy(), ref["density_grad"]) <= TOL_GRAD
+    assert rel_l2(gsph.cpu().numpy(), ref["radiance_grad"]) <= TOL_GRAD
+
+
 @pytest.mark.parametrize("K", [0, 8])
 def test_rays_not_starting_at_the_frame_origin(pkg, K):
     """Ray bundles whose origins differ per pixel (e.g. an orthographic or multi-sensor rig) take the kernels' non-uniform
