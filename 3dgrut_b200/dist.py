@@ -165,13 +165,40 @@ class PeerExchange(DeferredExchange):
         self.raster, self.rank = raster, rank
         self.slot_floats = (3 * n_particles + 3) // 4 * 4       # 16-byte aligned slots
         floats = self.SETS * views_per_rank * self.slot_floats
-        self.my_ptr, handle = raster.peer_buffer_create(floats * 4)
+        # Set-up either succeeds on every rank or raises on every rank: a rank that cannot export or map a buffer still
+        # takes part in both exchanges below, so nobody is left waiting in a collective.
+        self.my_ptr, handle, problem = None, None, None
+        try:
+            self.my_ptr, handle = raster.peer_buffer_create(floats * 4)
+        except Exception as e:   # noqa: BLE001 -- reported to all ranks below
+            problem = f"rank {rank}: {e}"
         handles = [None] * self.world
         if self.world > 1:
             dist.all_gather_object(handles, handle)
         else:
             handles[0] = handle
-        self.ptrs = [self.my_ptr if r == rank else raster.peer_buffer_open(handles[r]) for r in range(self.world)]
+        self.ptrs = [None] * self.world
+        if problem is None and all(h is not None for h in handles):
+            try:
+                for r in range(self.world):
+                    self.ptrs[r] = self.my_ptr if r == rank else raster.peer_buffer_open(handles[r])
+            except Exception as e:   # noqa: BLE001
+                problem = f"rank {rank}: {e}"
+        elif problem is None:
+            problem = f"rank {rank}: a peer could not export its buffer"
+        problems = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(problems, problem)
+        else:
+            problems[0] = problem
+        if any(problems):
+            for r, q in enumerate(self.ptrs):
+                if q is not None and r != rank:
+                    raster.peer_buffer_close(q)
+            if self.my_ptr is not None:
+                raster.peer_buffer_destroy(self.my_ptr)
+            self.ptrs = []
+            raise RuntimeError("peer-memory exchange unavailable: " + "; ".join(q for q in problems if q))
         self.mine = torch.as_tensor(_DeviceArray(self.my_ptr, floats), device=device).view(self.SETS, views_per_rank, self.slot_floats)
         self.n_particles = n_particles
         self.my_centres = torch.zeros((views_per_rank, 3), dtype=torch.float32, device=device)

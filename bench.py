@@ -258,16 +258,10 @@ def run_ours(args):
         try:
             exchange = gdist.PeerExchange(raster, n, sph.shape[1], (args.views + world - 1) // world, dev, rank, world=world)
             ok = 1
-        except Exception as e:   # CUDA IPC unavailable on this box: every rank falls back together
+        except RuntimeError as e:   # CUDA IPC unavailable on this box: the constructor raises on every rank together
             print(f"[bench] rank {rank}: peer buffers unavailable ({e!r})", file=sys.stderr, flush=True)
             exchange, ok = None, 0
-        if world > 1:
-            flag = torch.tensor([ok], device=dev)
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            ok = int(flag.item())
-        if not ok:
-            if exchange is not None:
-                exchange.close()
+        if not ok:   # PeerExchange fails on every rank or on none
             args.exchange = "deferred"
     if args.exchange == "deferred":
         exchange = gdist.DeferredExchange(n, sph.shape[1], (args.views + world - 1) // world, dev, world=world)
