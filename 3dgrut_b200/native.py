@@ -151,6 +151,10 @@ class SplatRaster:
         if not torch.cuda.is_available():
             raise RuntimeError("3dgrut_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError(f"3dgrut_b200 runs on CUDA devices only (got {self.device})")
+        if self.device.index is None:   # "cuda" without an index: the current device
+            self.device = torch.device("cuda", torch.cuda.current_device())
         major, _minor = torch.cuda.get_device_capability(self.device)
         if major != 10:
             raise RuntimeError(f"libgut_b200 is built for sm_100a only; device capability is {major}.{_minor}")
