@@ -38,6 +38,9 @@
 namespace {
 
 constexpr int BLOCKS_PER_TILE = 4;    // 8x8 pixel blocks (one warp, two rays per lane) of a 16x16 tile
+#ifndef GUT_FWD_MIN_BLOCKS
+#define GUT_FWD_MIN_BLOCKS 24         // resident one-warp CTAs per SM the forward is compiled for (80 registers); measured 20: 1.282, 24: 1.286, 28: 1.311 ms
+#endif
 #ifndef GUT_BWD_MIN_BLOCKS
 #define GUT_BWD_MIN_BLOCKS 20         // resident one-warp CTAs per SM the backward kernel is compiled for (96 registers);
 #endif                                // measured: 24 (80 regs, spills) 4.76 ms, 20 4.05 ms, 18 (112 regs) 4.21 ms per view
@@ -242,7 +245,7 @@ GUT_D size_t hit_mask_slot(uint32_t b0, uint32_t tile, uint32_t b, uint32_t bloc
 // COUNT = true is the instrumented variant used by gut_measure_work(): it writes no image, it counts the ray x particle
 // tests and accepted hits the frame performs (the units the FP32 roofline of K4/K5 is expressed in).
 template <int DEG, bool COUNT, bool STD>
-__global__ void __launch_bounds__(RENDER_THREADS, 24) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
+__global__ void __launch_bounds__(RENDER_THREADS, GUT_FWD_MIN_BLOCKS) gut_render_kernel(GutConfig cfg, GutFrame fr, const uint32_t* __restrict__ tile_start,
                                                                      GutParticleSource src,
                                                                      const float* __restrict__ ray_ori, const float* __restrict__ ray_dir,
                                                                      float4* __restrict__ rgba, float* __restrict__ dist,
