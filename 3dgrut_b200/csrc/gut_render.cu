@@ -410,8 +410,7 @@ struct BwdRay {
     F2 T_f, dA, dD;          // final transmittance of the forward pass, upstream gradients
     F2x3 dC;
     F2 T;                    // running transmittance of the re-walk
-    F2 Drem;                 // forward distance / colour still to be composited behind the current hit
-    F2x3 Crem;
+    F2x3 Crem;               // forward colour still to be composited behind the current hit
     bool alive[2];
 };
 
@@ -472,10 +471,12 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
 
             // hit-distance terms (gaussianParticles.cuh:536-567; the Jacobians of grds wrt grd / gro are the reference's
             // element-wise ones).  grds = -dgo sg;  dL/dgrds = grds hs = kap sg  with  kap = -dgo hs
-            st.Drem = fma(-w, gdist, st.Drem);
-            const F2 rD = st.Drem * invT;
-            const F2 resD = mk2(fmaxf(lo(rD), 0.0f), fmaxf(hi(rD), 0.0f));
-            const F2 dHit = gdist - resD;              // hit-distance part of the alpha gradient: T * dHit * dD, folded into Sall
+            // The alpha gradient's hit-distance part is T * gdist * dD: the reference's residual distance is identically 0.
+            // Its wrapper hands processHitBwd (hitT, hitTBackward, hitTGradient) where the callee declares (integratedDepth,
+            // depth&, depthGrad) (shRadiativeGaussianParticles.cuh:369-406, gaussianParticles.cuh:499-501), so the residual is
+            // max((0 - (D_f + w gdist)) / nextT, 0) = 0 for the forward's non-negative D_f.  Pinned on the reference's own
+            // kernels by tests/test_gpu_reference.py.
+            const F2 dHit = gdist;
             const F2 wd = w * st.dD;
             // gdist is 0 for a ray that does not take the hit, so "> 0" also is the hit test (the reference tests gdist^2 > 0)
             const F2 hs = mk2(lo(gdist) > 0.0f ? lo(wd) * mufu_rcp(lo(gdist)) : 0.0f, hi(gdist) > 0.0f ? hi(wd) * mufu_rcp(hi(gdist)) : 0.0f);
@@ -580,24 +581,23 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
 
     // initializeBackwardRay (rayPayloadBackward.cuh:46-55)
     BwdRay st;
-    float Tf[2], Df[2], dA[2], dD[2];
+    float Tf[2], dA[2], dD[2];
     float3 Cf[2], dC[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         st.alive[h] = ray.inside[h] && ray.valid[h];
-        Tf[h] = 1.0f; Df[h] = 0.0f; dA[h] = 0.0f; dD[h] = 0.0f;
+        Tf[h] = 1.0f; dA[h] = 0.0f; dD[h] = 0.0f;
         Cf[h] = f3(0.f, 0.f, 0.f); dC[h] = f3(0.f, 0.f, 0.f);
         if (st.alive[h]) {
             const float4 fd = __ldg(rgba + ray.pix[h]), gd = __ldg(rgba_grad + ray.pix[h]);
             Tf[h] = 1.0f - fd.w;       // transmittanceBackward
             dA[h] = gd.w;              // transmittanceGradient = -dA; used as residualTrm * -(-dA)
-            Df[h] = __ldg(dist + ray.pix[h]);
             dD[h] = __ldg(dist_grad + ray.pix[h]);
             Cf[h] = f3(fd.x, fd.y, fd.z);
             dC[h] = f3(gd.x, gd.y, gd.z);
         }
     }
-    st.T_f = mk2(Tf[0], Tf[1]); st.Drem = mk2(Df[0], Df[1]); st.dA = mk2(dA[0], dA[1]); st.dD = mk2(dD[0], dD[1]);
+    st.T_f = mk2(Tf[0], Tf[1]); st.dA = mk2(dA[0], dA[1]); st.dD = mk2(dD[0], dD[1]);
     st.Crem.x = mk2(Cf[0].x, Cf[1].x); st.Crem.y = mk2(Cf[0].y, Cf[1].y); st.Crem.z = mk2(Cf[0].z, Cf[1].z);
     st.dC.x = mk2(dC[0].x, dC[1].x); st.dC.y = mk2(dC[0].y, dC[1].y); st.dC.z = mk2(dC[0].z, dC[1].z);
     st.T = bc(1.0f);

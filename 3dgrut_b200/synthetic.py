@@ -112,10 +112,49 @@ def fisheye_rays(w, h, fx, fy, cx, cy, k):
     return torch.zeros((1, h, w, 3)), torch.from_numpy(d[None].astype(np.float32)).contiguous()
 
 
-def make_view(w, h, k=0, n_views=1, model="pinhole", rolling=False):
-    """One synthetic view: dict(rays_ori, rays_dir, T_to_world [1,4,4], intrinsics kwargs for Batch, T_to_world_end)."""
+# distortion set of the "opencv_pinhole" synthetic camera: rational k1..k6, tangential p1/p2, thin-prism s1..s4, all
+# non-zero and large enough that image corners leave the 0.8 < icD < 1.2 trust region of the reference's projection
+# (cameraProjections.cuh:57-103)
+OPENCV_PINHOLE_DISTORTION = {
+    "radial_coeffs": (-0.28, 0.07, -0.008, 0.02, -0.01, 0.002),
+    "tangential_coeffs": (0.0015, -0.0011),
+    "thin_prism_coeffs": (0.0009, -0.0004, -0.0007, 0.0003),
+}
+
+
+def _opencv_distort(u, v, rc, tc, pc):
+    """Normalised image point -> distorted normalised point (the forward model of cameraProjections.cuh:66-90)."""
+    r2 = u * u + v * v
+    icd = (1 + r2 * (rc[0] + r2 * (rc[1] + r2 * rc[2]))) / (1 + r2 * (rc[3] + r2 * (rc[4] + r2 * rc[5])))
+    dx = 2 * tc[0] * u * v + tc[1] * (r2 + 2 * u * u) + r2 * (pc[0] + r2 * pc[1])
+    dy = tc[0] * (r2 + 2 * v * v) + 2 * tc[1] * u * v + r2 * (pc[2] + r2 * pc[3])
+    return u * icd + dx, v * icd + dy
+
+
+def opencv_pinhole_rays(w, h, fx, fy, cx, cy, rc, tc, pc, iters=30):
+    """Unit rays of a distorted OpenCV pinhole camera through pixel centres: fixed-point inversion of the distortion
+    (as image_points_to_camera_rays does, threedgrut/datasets/camera_models.py:156-236)."""
+    xd = (np.arange(w, dtype=np.float64) + 0.5 - cx) / fx
+    yd = (np.arange(h, dtype=np.float64) + 0.5 - cy) / fy
+    gxd, gyd = np.meshgrid(xd, yd)
+    u, v = gxd.copy(), gyd.copy()
+    for _ in range(iters):
+        du, dv = _opencv_distort(u, v, rc, tc, pc)
+        u = u - 0.7 * (du - gxd)
+        v = v - 0.7 * (dv - gyd)
+    d = np.stack((u, v, np.ones_like(u)), axis=-1)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    return torch.zeros((1, h, w, 3)), torch.from_numpy(d[None].astype(np.float32)).contiguous()
+
+
+def make_view(w, h, k=0, n_views=1, model="pinhole", rolling=False, shutter=None):
+    """One synthetic view: dict(rays_ori, rays_dir, T_to_world [1,4,4], intrinsics kwargs for Batch, T_to_world_end).
+    ``shutter``: a ShutterType name for the OpenCV models; default ROLLING_TOP_TO_BOTTOM when ``rolling`` else GLOBAL."""
     c2w = orbit_c2w(k, n_views)
     out = {"T_to_world": torch.from_numpy(c2w[None].copy())}
+    if shutter is None:
+        shutter = "ROLLING_TOP_TO_BOTTOM" if rolling else "GLOBAL"
+    rolling = shutter != "GLOBAL"
     if model == "pinhole":
         fx = fy = 1.0 * w
         out["rays_ori"], out["rays_dir"] = pinhole_rays(w, h, fx, fy)
@@ -127,11 +166,26 @@ def make_view(w, h, k=0, n_views=1, model="pinhole", rolling=False):
         out["rays_ori"], out["rays_dir"] = fisheye_rays(w, h, fx, fy, cx, cy, kk)
         out["intrinsics_OpenCVFisheyeCameraModelParameters"] = {
             "resolution": np.array([w, h], dtype=np.int64),
-            "shutter_type": "ROLLING_TOP_TO_BOTTOM" if rolling else "GLOBAL",
+            "shutter_type": shutter,
             "principal_point": np.array([cx, cy], dtype=np.float32),
             "focal_length": np.array([fx, fy], dtype=np.float32),
             "radial_coeffs": np.array(kk, dtype=np.float32),
             "max_angle": fisheye_max_angle(w, h, fx, fy, cx, cy, kk),
+        }
+    elif model == "opencv_pinhole":
+        fx, fy = 0.62 * w, 0.60 * w          # wide enough that r^2 reaches ~1 in the corners
+        cx, cy = 0.49 * w, 0.52 * h          # principal point off the image centre
+        dd = OPENCV_PINHOLE_DISTORTION
+        out["rays_ori"], out["rays_dir"] = opencv_pinhole_rays(w, h, fx, fy, cx, cy, dd["radial_coeffs"], dd["tangential_coeffs"],
+                                                               dd["thin_prism_coeffs"])
+        out["intrinsics_OpenCVPinholeCameraModelParameters"] = {
+            "resolution": np.array([w, h], dtype=np.int64),
+            "shutter_type": shutter,
+            "principal_point": np.array([cx, cy], dtype=np.float32),
+            "focal_length": np.array([fx, fy], dtype=np.float32),
+            "radial_coeffs": np.array(dd["radial_coeffs"], dtype=np.float32),
+            "tangential_coeffs": np.array(dd["tangential_coeffs"], dtype=np.float32),
+            "thin_prism_coeffs": np.array(dd["thin_prism_coeffs"], dtype=np.float32),
         }
     else:
         raise ValueError(model)

@@ -917,8 +917,19 @@ ORACLE_API void gut_oracle_render_bwd(const GutConfig* cfg, const GutCamera* cam
                     const float weight = galpha * T;
                     const float nextT = (1 - galpha) * T;
 
-                    D += weight * gdist;
-                    const float resD = fmaxf((nextT <= minT ? 0 : (D_f - D) / nextT), 0);
+                    /* CALL-SITE QUIRK (found by the reference + shim build, tests/test_gpu_reference.py): the wrapper
+                     * shRadiativeGaussianParticles.cuh:369-406 hands processHitBwd its last three arguments as
+                     * (hitT, hitTBackward, hitTGradient) where the callee (gaussianParticles.cuh:499-501) declares
+                     * (integratedDepth, depth&, depthGrad): `integratedDepth` is the ray's RUNNING distance ray.hitT -- 0 from
+                     * initializeRay (rayPayload.cuh:88) and never updated, because `depth&` binds to the wrapper's by-value
+                     * copy of the forward's final distance.  So per call: depth = D_f + weight * gdist (discarded afterwards),
+                     * integratedDepth = 0, and the residual is max(-(D_f + w gdist) / nextT, 0) = 0 for every non-negative
+                     * forward distance.  The hit-distance part of the alpha gradient is therefore gdist * T * dD. */
+                    const float integratedDepth = 0.0f;          /* ray.hitT */
+                    float depth_local = D_f;                       /* by-value copy of ray.hitTBackward */
+                    depth_local += weight * gdist;                 /* :542 */
+                    D += weight * gdist;                           /* what the callee's author meant; kept for reference only */
+                    const float resD = fmaxf((nextT <= minT ? 0 : (integratedDepth - depth_local) / nextT), 0);   /* :543-545 */
                     const float galphaRayHitGrd = (gdist - resD) * T * D_grad;
                     const v3 grdsRayHitGrd = gsqdist > 0.0f
                         ? scl3(D_grad, V3((2 * grds.x * weight) / (2 * gdist), (2 * grds.y * weight) / (2 * gdist), (2 * grds.z * weight) / (2 * gdist)))

@@ -375,7 +375,11 @@ def composite(cfg, cam, pos, dns, quat, scl, feats, ray_ori, ray_dir, W, H, tile
         T_before = torch.cat([torch.ones((npx, 1), dtype=dtype), torch.cumprod(om, dim=1)[:, :-1]], 1)
         w = alpha * T_before * accf
         C = (w.unsqueeze(-1) * torch.clamp(ft, min=0).unsqueeze(0)).sum(1)
-        D = (w * tt).sum(1)
+        # Distance: the reference's K = 0 backward takes d dist / d alpha_i = T_i * t_i only -- its residual-distance term is
+        # identically 0 because of swapped arguments at the call site of processHitBwd (shRadiativeGaussianParticles.cuh:
+        # 369-406 vs gaussianParticles.cuh:499-501; see oracle/gut_oracle.c, gut_oracle_render_bwd) -- i.e. the transmittance
+        # in front of a hit carries no distance gradient back to the closer particles: detached here.
+        D = (alpha * T_before.detach() * accf * tt).sum(1)
         T_final = torch.prod(om, dim=1)
         n_hits = (acc & (w > 0)).sum(1).to(dtype)
         px_rgba = torch.cat([C, (1 - T_final).unsqueeze(-1)], -1) * vr.unsqueeze(-1).to(dtype)
