@@ -134,10 +134,13 @@ struct AdamGroups {
     uint32_t vec_ok;     // bit i: group i's four pointers are 16-byte aligned and its element count is a multiple of 4
 };
 
+// The rounding is that of the reference's compiled kernel (default nvcc flags: the moment updates contract into one FMA
+// each, IEEE sqrt / division; SASS of oracle/_ref/optimizers_cu.o), spelled out because this translation unit is built
+// with --fmad=false: bit-identical parameters, exp_avg and exp_avg_sq (tests/test_gpu_model.py, against that kernel).
 GUT_D void adam_scalar(float& p, float g, float& m, float& v, float lr, float b1, float b2, float eps) {
-    m = b1 * m + (1.0f - b1) * g;
-    v = b2 * v + (1.0f - b2) * g * g;
-    p += -lr * m / (sqrtf(v) + eps);
+    m = fmaf(g, 1.0f - b1, b1 * m);
+    v = fmaf(g, g * (1.0f - b2), b2 * v);
+    p = p - (lr * m) / (sqrtf(v) + eps);
 }
 
 __global__ void __launch_bounds__(MODEL_THREADS) gut_selective_adam_kernel(AdamGroups groups, uint32_t N, const float* __restrict__ visibility,

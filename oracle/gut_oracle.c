@@ -1186,3 +1186,30 @@ ORACLE_API void gut_oracle_project_bwd(const GutConfig* cfg, const GutCamera* ca
         for (int k = 0; k < nact; ++k) { out[3 * k] += b[k] * g.x; out[3 * k + 1] += b[k] * g.y; out[3 * k + 2] += b[k] * g.z; }
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * SelectiveAdam: selective_adam_update_kernel, threedgrut/optimizers/optimizers.cu:47-84, one scalar per
+ * thread.  PINNED on the reference's own kernel: the rounding below is that of the reference's COMPILED kernel (default
+ * nvcc flags, setup_optimizers.py:27-44: FMA contraction on, IEEE sqrt and division), read from its SASS
+ * (oracle/_ref/optimizers_cu.o):   FMUL t = m * b1 ; FADD c = 1 - b1 ; FFMA m' = g * c + t
+ *                                  FMUL u = v * b2 ; FMUL w = g * (1 - b2) ; FFMA v' = g * w + u
+ *                                  FMUL s = m' * lr ; sqrt_rn ; FADD d = sqrt + eps ; div_rn ; FADD param - s / d
+ * and tests/test_gpu_model.py compares it bit for bit with that kernel on the GPU box; tests/golden/reference_adam.npz is
+ * the same comparison frozen for the CPU suite. */
+ORACLE_API void gut_oracle_selective_adam(uint64_t n_rows, uint32_t width, float* param, const float* grad, float* exp_avg,
+                                          float* exp_avg_sq, const uint8_t* visibility /* per row, may be NULL */,
+                                          float lr, float b1, float b2, float eps) {
+    for (uint64_t r = 0; r < n_rows; ++r) {
+        if (visibility && !visibility[r]) continue;
+        for (uint32_t c = 0; c < width; ++c) {
+            const uint64_t i = r * width + c;
+            const float g = grad[i];
+            const float m = fmaf(g, 1.0f - b1, b1 * exp_avg[i]);
+            const float v = fmaf(g, g * (1.0f - b2), b2 * exp_avg_sq[i]);
+            const float step = (lr * m) / (sqrtf(v) + eps);
+            param[i] = param[i] - step;
+            exp_avg[i] = m;
+            exp_avg_sq[i] = v;
+        }
+    }
+}

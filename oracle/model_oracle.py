@@ -3,9 +3,10 @@ activation + packing at the Tracer boundary, SelectiveAdam and the densification
 
 Pinning: the activations ARE torch functions in the reference (threedgrut/utils/misc.py:48-53: torch.sigmoid, torch.exp,
 torch.nn.functional.normalize), so tests/test_model_oracle.py checks this restatement -- forward and backward -- against
-those torch functions and their autograd on CPU: pinned.  SelectiveAdam lives in a CUDA kernel that cannot run here
-(threedgrut/optimizers/optimizers.cu:47-84); it is restated operation by operation and checked on closed-form first
-steps and against an independent float64 evaluation: parity unpinned for that kernel (no reference-produced vector).
+those torch functions and their autograd on CPU: pinned.  SelectiveAdam (threedgrut/optimizers/optimizers.cu:47-84) is
+restated with the rounding of the reference's compiled kernel and pinned on that kernel: oracle/ref_build builds
+optimizers.cu / optimizers.cpp unchanged (oracle/_ref/lib_optimizers_cc.so), tests/test_gpu_model.py compares bit for bit on
+the GPU box, and tests/golden/reference_adam.npz holds vectors that kernel produced for the CPU suite.
 """
 import numpy as np
 
@@ -76,17 +77,24 @@ def selective_adam_update(param, grad, exp_avg, exp_avg_sq, visibility, lr, b1, 
     """selective_adam_update_kernel (optimizers.cu:47-84), one scalar per thread, all float32:
         if (!visibility[g_idx]) return;
         m = b1 * m + (1 - b1) * g;  v = b2 * v + (1 - b2) * g * g;  param += -lr * m / (sqrt(v) + eps)
-    No bias correction.  Returns new (param, exp_avg, exp_avg_sq); rows with visibility == 0 are unchanged."""
-    lr, b1, b2, eps = F32(lr), F32(b1), F32(b2), F32(eps)
-    p, g, m, v = (a.astype(F32) for a in (param, grad, exp_avg, exp_avg_sq))
+    No bias correction.  Returns new (param, exp_avg, exp_avg_sq); rows with visibility == 0 are unchanged.
+    The arithmetic runs in oracle/gut_oracle.c (gut_oracle_selective_adam): the reference's compiled kernel contracts
+    the two moment updates into FMAs, and a single-rounding fmaf is not expressible in numpy."""
+    import ctypes as C
+
+    from oracle import gut_oracle as O
+
+    p, g, m, v = (np.ascontiguousarray(a, dtype=F32).copy() for a in (param, grad, exp_avg, exp_avg_sq))
     n = p.shape[0]
-    vis = np.ones(n, dtype=bool) if visibility is None else (np.asarray(visibility).reshape(n) != 0)
-    mask = vis.reshape((n,) + (1,) * (p.ndim - 1))
-    m_new = (b1 * m + (F32(1) - b1) * g).astype(F32)
-    v_new = (b2 * v + ((F32(1) - b2) * g) * g).astype(F32)
-    step = ((-lr * m_new) / (np.sqrt(v_new) + eps)).astype(F32)
-    p_new = (p + step).astype(F32)
-    return np.where(mask, p_new, p), np.where(mask, m_new, m), np.where(mask, v_new, v)
+    width = int(p.size // max(n, 1))
+    vis_p = C.c_void_p(0)
+    if visibility is not None:
+        vis = np.ascontiguousarray((np.asarray(visibility).reshape(n) != 0).astype(np.uint8))   # visibility.bool(), __init__.py:126
+        vis_p = vis.ctypes.data_as(C.c_void_p)
+    fp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    O.lib().gut_oracle_selective_adam(C.c_uint64(n), C.c_uint32(width), fp(p), fp(g), fp(m), fp(v), vis_p,
+                                      C.c_float(lr), C.c_float(b1), C.c_float(b2), C.c_float(eps))
+    return p, m, v
 
 
 def update_gradient_buffer(positions, positions_grad, sensor_position, accum, denom):

@@ -137,3 +137,14 @@ def probe_backward(cam, sph_degree, d12, sph, ray_ori, ray_dir, w, h, rgba, rgba
                              _ptr(gsph))
     assert rc == 0, rc
     return g12, gsph
+
+
+def optimizers_available():
+    return os.path.exists(os.path.join(REF_DIR, "lib_optimizers_cc.so"))
+
+
+def optimizers_module():
+    """threedgrut/optimizers/optimizers.{cu,cpp} built unchanged (plain CUDA + torch, no Slang): ``selective_adam_update``."""
+    if REF_DIR not in sys.path:
+        sys.path.insert(0, REF_DIR)
+    return importlib.import_module("lib_optimizers_cc")

@@ -202,6 +202,40 @@ def test_selective_adam_step_is_bit_exact(raster, n, masked):
         assert (g == 0).all()
 
 
+@pytest.mark.parametrize("n,masked", [(10_001, True), (100_000, False), (5, True)])
+def test_selective_adam_bit_exact_against_the_reference_kernel(raster, n, masked):
+    """gut_selective_adam_step (one launch, six groups) against the reference's own compiled selective_adam_update_kernel
+    (threedgrut/optimizers/optimizers.cu, built unchanged by oracle/ref_build into oracle/_ref/lib_optimizers_cc.so), called the
+    way SelectiveAdam.step calls it (optimizers/__init__.py:119-133), three steps in a row: every bit of param, exp_avg and
+    exp_avg_sq.  The numpy/C oracle is compared with both."""
+    from tests import refshim
+
+    if not refshim.optimizers_available():
+        pytest.skip("oracle/_ref/lib_optimizers_cc.so not built")
+    ref = refshim.optimizers_module()
+    ours = _adam_groups(n, 300 + n)
+    theirs = [[t.clone() if torch.is_tensor(t) else t for t in g] for g in ours]
+    orc = [[t.cpu().numpy().copy() if torch.is_tensor(t) else t for t in g] for g in ours]
+    gen = torch.Generator(device="cuda").manual_seed(n)
+    b1, b2, eps = 0.9, 0.999, 1e-15
+    for step in range(3):
+        vis = (torch.rand((n, 1), device="cuda", generator=gen) < 0.6).float() if masked else torch.ones((n, 1), device="cuda")
+        for go, gt, gc in zip(ours, theirs, orc):
+            grad = torch.randn(go[0].shape, device="cuda", generator=gen) * 10.0 ** (-step)
+            go[1].copy_(grad); gt[1].copy_(grad); gc[1] = grad.cpu().numpy()
+        for p, g, m, v, lr in theirs:
+            ref.selective_adam_update(p, g, m, v, vis.bool().squeeze(1), lr, b1, b2, eps)
+        raster.selective_adam_step([tuple(x) for x in ours], vis, b1, b2, eps)
+        for gc in orc:
+            gc[0], gc[2], gc[3] = mo.selective_adam_update(gc[0], gc[1], gc[2], gc[3], vis.cpu().numpy(), gc[4], b1, b2, eps)
+        torch.cuda.synchronize()
+        for i, (go, gt, gc) in enumerate(zip(ours, theirs, orc)):
+            for k, what in ((0, "param"), (2, "exp_avg"), (3, "exp_avg_sq")):
+                a, b = go[k].cpu().numpy().view(np.uint32), gt[k].cpu().numpy().view(np.uint32)
+                assert np.array_equal(a, b), (step, i, what, int((a != b).sum()))
+                assert np.array_equal(gc[k].view(np.uint32), b), ("oracle", step, i, what)
+
+
 def test_selective_adam_class_mirrors_reference_api():
     """3dgrut_b200.SelectiveAdam: the reference's constructor / step(visibility) / state keys (optimizers/__init__.py:45-133)."""
     pkg = importlib.import_module("3dgrut_b200")
