@@ -4,11 +4,13 @@ Mirrors ``Tracer.__create_camera_parameters`` and ``SensorPose3DModel`` of the
 reference (threedgut_tracer/tracer.py:54-151, 362-431): a ``Batch`` carries a
 camera-to-world matrix and one of three intrinsics descriptions; the native
 layer wants a ``GutCamera`` (intrinsics + two world->sensor ``[t, q_xyzw]``
-poses).  Pure numpy, no CUDA, so it is testable on a CPU box.
+poses).  Host-side numpy (+ one CPU torch call), no CUDA, so it is testable on a CPU box; pinned on the reference's own
+Python by tests/test_camera_golden.py.
 """
 import math
 
 import numpy as np
+import torch
 
 from .abi import GutCamera, ShutterType, fisheye_camera, pinhole_camera, set_poses
 
@@ -38,7 +40,10 @@ def so3_to_quat_xyzw(R: np.ndarray) -> np.ndarray:
         q[1] = R[0, 2] - R[2, 0]
         q[2] = R[1, 0] - R[0, 1]
         q[3] = np.float32(1) + trace
-    return (q / np.float32(np.linalg.norm(q))).astype(np.float32)
+    # the reference normalises with torch (`quat / torch.norm(quat, dim=1)[:, None]`, tracer.py:131); torch's fp32 norm and
+    # numpy's differ in the last bit for some inputs, and the pose must come out bit-identical (tests/test_camera_golden.py)
+    qt = torch.from_numpy(q.reshape(1, 4))
+    return (qt / torch.norm(qt, dim=1)[:, None]).reshape(4).numpy().astype(np.float32)
 
 
 def c2w_to_sensor_pose(T_to_world: np.ndarray) -> np.ndarray:
