@@ -52,6 +52,9 @@ struct GutHandle {
     bool training = true;           // forward records the hit masks the backward walks (gut_set_training)
     bool fwd_masks = false;         // the last forward recorded them
     bool pending_density = false;   // gut_backward_colour left view-summed accumulators for gut_density_gradient_finish
+    uint32_t pending_N = 0;         // particle count of that pending accumulation
+    bool block_cull = true;         // conservative per-block cull of the K = 0 forward (gut_set_block_cull: test control)
+    int sm_count = 0;               // SMs of the handle's device (grid of the persistent radix-sort kernel)
     cudaStream_t fwd_stream = nullptr;
     uint32_t fwd_N = 0, fwd_W = 0, fwd_H = 0;
     uint64_t fwd_M = 0;
@@ -178,7 +181,8 @@ bool degree_supported(int d) { return d == 0 || d == 1 || d == 2 || d == 3 || d 
 void start_timer(std::deque<EventPair>& q, int tag, cudaStream_t s) {
     EventPair ep;
     ep.tag = tag;
-    if (cudaEventCreate(&ep.a) != cudaSuccess || cudaEventCreate(&ep.b) != cudaSuccess) return;
+    if (cudaEventCreate(&ep.a) != cudaSuccess) return;
+    if (cudaEventCreate(&ep.b) != cudaSuccess) { cudaEventDestroy(ep.a); return; }
     cudaEventRecord(ep.a, s);
     q.push_back(ep);
     while (q.size() > 256) {
@@ -266,6 +270,13 @@ int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
     for (int i = 0; i < ST_COUNT; ++i) h->last_stage_ms[i] = -1.0f;
     DeviceGuard g(device);
     if (cudaMallocHost(&h->pinned_stats, 2 * sizeof(uint32_t)) != cudaSuccess) { delete h; return GUT_ERR_CUDA; }
+    // kernel attributes are per device: set them for THIS handle's device (a second handle on another GPU needs them too)
+    if (gut_configure_tile_sort(&h->sm_count) != cudaSuccess || h->sm_count <= 0) {
+        cudaGetLastError();
+        cudaFreeHost(h->pinned_stats);
+        delete h;
+        return GUT_ERR_CUDA;
+    }
     *out = h;
     return GUT_OK;
 }
@@ -353,7 +364,8 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
         {
             StageTimer t(h, ST_SORT, s);
             GUT_CUDA(h, gut_launch_tile_sort(fr, N, max_list, (const uint32_t*)h->tile_start.p, (uint2*)h->entries.p, (uint2*)h->scratch.p,
-                                             (uint32_t*)h->tile_hist.p /* free after the scan: bucket flags */, (uint32_t*)h->stats.p + 2, (uint32_t*)h->sorted_idx.p, s));
+                                             (uint32_t*)h->tile_hist.p /* free after the scan: bucket flags */, (uint32_t*)h->stats.p + 2, (uint32_t*)h->sorted_idx.p,
+                                             h->sm_count, s));
             h->launches += max_list > 8192 ? 3 : 2;
         }
         {
@@ -371,7 +383,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
                 }
                 h->fwd_masks = masks != nullptr;
                 GUT_CUDA(h, gut_launch_render(h->cfg, fr, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
-                                              d_rgba, d_dist, d_hits, nullptr, masks, s));
+                                              d_rgba, d_dist, d_hits, nullptr, masks, h->block_cull, s));
             }
             h->launches += 1;
         }
@@ -420,7 +432,10 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
     if (!d_ray_ori || !d_ray_dir || !d_rgba || !d_rgba_grad || !d_dist || !d_dist_grad) return fail(h, GUT_ERR_BAD_INPUT, "null ray/gradient pointer");
     if (N > 0 && (!d_density || (!d_density_grad && !d_colour_grad) || (!d_radiance_grad && !d_colour_grad))) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
     if (!d_colour_grad && h->pending_density)
-        return fail(h, GUT_ERR_BAD_INPUT, "gut_backward after gut_backward_colour: call gut_density_gradient_finish first");
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_backward after gut_backward_colour: call gut_density_gradient_finish (or gut_reset_gradients) first");
+    if (d_colour_grad && h->pending_density && h->pending_N != N)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_backward_colour: %u particles, but the pending accumulation of this step holds %u "
+                                          "(particle set changed mid-step: call gut_reset_gradients)", N, h->pending_N);
     if (N == 0) return GUT_OK;
     DeviceGuard guard(h->device);
     if (h->cfg.enable_kernel_timings) start_timer(h->timers, 1, s);
@@ -470,6 +485,7 @@ int gut_backward_colour(GutHandle* h, void* stream_, const GutCamera* camera, ui
                            d_dist_grad, nullptr, nullptr, d_colour_grad, 0);
     if (rc == GUT_OK) {
         h->pending_density = true;
+        h->pending_N = N;
         if (view_centre_out) {
             view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
         }
@@ -481,6 +497,9 @@ int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const f
     if (!h) return GUT_ERR_BAD_INPUT;
     if (N == 0) { h->pending_density = false; return GUT_OK; }
     if (!d_density || !d_density_grad) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (h->pending_density && h->pending_N != N)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_density_gradient_finish: %u particles, but the pending accumulation holds %u "
+                                          "(call gut_reset_gradients after changing the particle set)", N, h->pending_N);
     cudaStream_t s = (cudaStream_t)stream_;
     DeviceGuard guard(h->device);
     if ((size_t)N * 64 > h->raw_grad.cap || !h->raw_grad.p) {   // no gut_backward_colour ran: the sum is zero
@@ -497,6 +516,22 @@ int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const f
 int gut_set_training(GutHandle* h, int32_t training) {
     if (!h) return GUT_ERR_BAD_INPUT;
     h->training = training != 0;
+    return GUT_OK;
+}
+
+int gut_set_block_cull(GutHandle* h, int32_t enabled) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    h->block_cull = enabled != 0;
+    return GUT_OK;
+}
+
+int gut_reset_gradients(GutHandle* h, void* stream_) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    if (h->raw_grad.p) GUT_CUDA(h, cudaMemsetAsync(h->raw_grad.p, 0, h->raw_grad.cap, s));
+    h->pending_density = false;
+    h->pending_N = 0;
     return GUT_OK;
 }
 
@@ -779,7 +814,7 @@ int gut_measure_work(GutHandle* h, void* stream_, const float* d_ray_ori, const 
     GUT_CUDA(h, cudaMemsetAsync(h->stats.p, 0, 16, s));
     const GutParticleSource src{(const uint32_t*)h->sorted_idx.p, (const float4*)h->fwd_density, (const float4*)h->features.p};
     GUT_CUDA(h, gut_launch_render(h->cfg, h->fwd_frame, (const uint32_t*)h->tile_start.p, src, d_ray_ori, d_ray_dir,
-                                  nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, nullptr, s));
+                                  nullptr, nullptr, nullptr, (unsigned long long*)h->stats.p, nullptr, h->block_cull, s));
     unsigned long long host[2] = {0, 0};
     GUT_CUDA(h, cudaMemcpyAsync(host, h->stats.p, 16, cudaMemcpyDeviceToHost, s));
     GUT_CUDA(h, cudaStreamSynchronize(s));

@@ -463,40 +463,42 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
     return cudaGetLastError();
 }
 
+namespace {
+constexpr uint32_t SORT_CAP_M = 8192, SORT_CAP_L = 12288, SORT_LOG_BINS_M = 13, SORT_LOG_BINS_L = 14;
+constexpr size_t SORT_SMEM_M = SORT_CAP_M * sizeof(uint2) + ((1u << SORT_LOG_BINS_M) + 4) * sizeof(uint32_t);
+constexpr size_t SORT_SMEM_L = SORT_CAP_L * sizeof(uint2) + ((1u << SORT_LOG_BINS_L) + 4) * sizeof(uint32_t);
+constexpr size_t SORT_SMEM_R = 4 * SORT_CAP_L * sizeof(uint32_t);
+}  // namespace
+
+// Function attributes belong to the device (its primary context): gut_create calls this under its DeviceGuard for every
+// handle, so a second handle on another GPU of the same process gets the dynamic shared-memory opt-in too.
+cudaError_t gut_configure_tile_sort(int* sm_count) {
+    cudaError_t e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, SORT_CAP_M, SORT_LOG_BINS_M, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM_M);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, SORT_CAP_L, SORT_LOG_BINS_L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM_L);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(gut_tile_radix_sort_kernel<512, SORT_CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM_R);
+    if (e != cudaSuccess) return e;
+    int dev = 0;
+    e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    return cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, dev);
+}
+
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries,
-                                 uint2* scratch, uint32_t* tile_flags, uint32_t* flagged_count, uint32_t* sorted_idx, cudaStream_t stream) {
+                                 uint2* scratch, uint32_t* tile_flags, uint32_t* flagged_count, uint32_t* sorted_idx, int sm_count,
+                                 cudaStream_t stream) {
     // buckets up to 8192 entries: 512 threads, 8192 bins (96 KB, two CTAs per SM); up to 12288: 16384 bins (160 KB);
     // flagged buckets and buckets above 12288 entries: radix passes (in 192 KB of shared memory / over global memory).
     (void)N;
-    constexpr uint32_t CAP_M = 8192, CAP_L = 12288, LOG_BINS_M = 13, LOG_BINS_L = 14;
-    const size_t smem_m = CAP_M * sizeof(uint2) + ((1u << LOG_BINS_M) + 4) * sizeof(uint32_t);
-    const size_t smem_l = CAP_L * sizeof(uint2) + ((1u << LOG_BINS_L) + 4) * sizeof(uint32_t);
-    const size_t smem_r = 4 * CAP_L * sizeof(uint32_t);
-    static bool configured = false;
-    static int radix_grid = 0;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_M, LOG_BINS_M, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_m);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(gut_tile_radix_sort_kernel<512, CAP_L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r);
-        if (e != cudaSuccess) return e;
-        int dev = 0, sms = 0;
-        e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return e;
-        radix_grid = sms;
-        configured = true;
-    }
-    gut_tile_bin_sort_kernel<512, CAP_M, LOG_BINS_M, 2><<<frame.num_tiles, 512, smem_m, stream>>>(tile_start, entries, 1u, CAP_M, sorted_idx, tile_flags,
-                                                                                              flagged_count);
-    if (max_list > CAP_M)
-        gut_tile_bin_sort_kernel<512, CAP_L, LOG_BINS_L, 1><<<frame.num_tiles, 512, smem_l, stream>>>(tile_start, entries, CAP_M + 1u, CAP_L, sorted_idx,
-                                                                                                  tile_flags, flagged_count);
-    const uint32_t grid = frame.num_tiles < (uint32_t)radix_grid ? frame.num_tiles : (uint32_t)radix_grid;
-    gut_tile_radix_sort_kernel<512, CAP_L><<<grid, 512, smem_r, stream>>>(frame, tile_start, entries, scratch, tile_flags, flagged_count,
-                                                                         max_list > CAP_L, sorted_idx);
+    gut_tile_bin_sort_kernel<512, SORT_CAP_M, SORT_LOG_BINS_M, 2><<<frame.num_tiles, 512, SORT_SMEM_M, stream>>>(
+        tile_start, entries, 1u, SORT_CAP_M, sorted_idx, tile_flags, flagged_count);
+    if (max_list > SORT_CAP_M)
+        gut_tile_bin_sort_kernel<512, SORT_CAP_L, SORT_LOG_BINS_L, 1><<<frame.num_tiles, 512, SORT_SMEM_L, stream>>>(
+            tile_start, entries, SORT_CAP_M + 1u, SORT_CAP_L, sorted_idx, tile_flags, flagged_count);
+    const uint32_t grid = frame.num_tiles < (uint32_t)sm_count ? frame.num_tiles : (uint32_t)sm_count;
+    gut_tile_radix_sort_kernel<512, SORT_CAP_L><<<grid, 512, SORT_SMEM_R, stream>>>(frame, tile_start, entries, scratch, tile_flags, flagged_count,
+                                                                                max_list > SORT_CAP_L, sorted_idx);
     return cudaGetLastError();
 }
 

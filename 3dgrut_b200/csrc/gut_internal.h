@@ -88,7 +88,10 @@ cudaError_t gut_launch_emit(const GutConfig& cfg, const GutFrame& frame, uint32_
 // per-tile sort of the (depth, idx) buckets -> sorted particle list; scratch = alt buffer for oversize tiles;
 // tile_flags [T] = scratch words (buckets handed from the counting sort to the radix sort)
 cudaError_t gut_launch_tile_sort(const GutFrame& frame, uint32_t N, uint32_t max_list, const uint32_t* tile_start, uint2* entries, uint2* scratch,
-                                 uint32_t* tile_flags, uint32_t* flagged_count /* zeroed by the tile scan */, uint32_t* sorted_idx, cudaStream_t stream);
+                                 uint32_t* tile_flags, uint32_t* flagged_count /* zeroed by the tile scan */, uint32_t* sorted_idx,
+                                 int sm_count /* of the handle's device */, cudaStream_t stream);
+// per-device kernel attributes (dynamic shared memory opt-in) + SM count of the CURRENT device; called by gut_create
+cudaError_t gut_configure_tile_sort(int* sm_count);
 
 // debug/parity: rebuild the reference-shaped sorted key array and tile ranges
 cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_start, const uint32_t* sorted_idx, const float* depth,
@@ -97,7 +100,8 @@ cudaError_t gut_launch_export_keys(const GutFrame& frame, const uint32_t* tile_s
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
                               unsigned long long* counters /* non-null: count tests/hits instead of rendering */,
-                              uint32_t* hit_masks /* nullable: per (block, batch) masks of accepted entries for the backward */, cudaStream_t stream);
+                              uint32_t* hit_masks /* nullable: per (block, batch) masks of accepted entries for the backward */,
+                              bool block_cull /* conservative per-block cone cull while staging (gut_set_block_cull) */, cudaStream_t stream);
 size_t gut_hit_mask_words(uint64_t num_intersections, uint32_t num_tiles);
 
 cudaError_t gut_launch_render_backward(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start,

@@ -619,11 +619,10 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
 template <int DEG>
 cudaError_t launch_render_deg(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              unsigned long long* counters, uint32_t* hit_masks, cudaStream_t stream) {
+                              unsigned long long* counters, uint32_t* hit_masks, bool cull, cudaStream_t stream) {
     const uint32_t grid = frame.num_tiles * BLOCKS_PER_TILE;
-    // test hook: GUT_DEBUG_NO_BLOCK_CULL=1 walks every record, to prove that the cull changes no bit of the outputs
-    const char* dbg = getenv("GUT_DEBUG_NO_BLOCK_CULL");
-    const bool cull = !(dbg && dbg[0] == '1');
+    // cull == false (gut_set_block_cull(h, 0), a test control) walks every record: proves that the cull changes no output bit.
+    // The kernel applies the cone bound only for DEG == 2 (block_cull's g2max is the degree-2 response bound).
     if (counters)
         gut_render_kernel<DEG, true, false><<<grid, RENDER_THREADS, 0, stream>>>(cfg, frame, tile_start, src, ray_ori, ray_dir, nullptr, nullptr,
                                                                               nullptr, counters, nullptr, cull);
@@ -676,8 +675,8 @@ cudaError_t launch_render_bwd_deg(const GutConfig& cfg, const GutFrame& frame, c
 
 cudaError_t gut_launch_render(const GutConfig& cfg, const GutFrame& frame, const uint32_t* tile_start, GutParticleSource src,
                               const float* ray_ori, const float* ray_dir, float* rgba, float* dist, float* hits,
-                              unsigned long long* counters, uint32_t* hit_masks, cudaStream_t stream) {
-#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, counters, hit_masks, stream)
+                              unsigned long long* counters, uint32_t* hit_masks, bool block_cull, cudaStream_t stream) {
+#define CALL_FWD(D) launch_render_deg<D>(cfg, frame, tile_start, src, ray_ori, ray_dir, rgba, dist, hits, counters, hit_masks, block_cull, stream)
     GUT_DISPATCH_DEGREE(cfg.kernel_degree, CALL_FWD)
 #undef CALL_FWD
 }

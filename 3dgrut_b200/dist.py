@@ -160,8 +160,9 @@ class PeerExchange(DeferredExchange):
 
     SETS = 2
 
-    def __init__(self, raster, n_particles, n_sph_floats, views_per_rank, device, rank, world=None):
-        super().__init__(n_particles, n_sph_floats, views_per_rank, device, world=world, gather_buffer=False)   # peer buffers instead
+    def __init__(self, raster, n_particles, n_sph_floats, views_per_rank, device, rank, world=None, track_visibility=False):
+        super().__init__(n_particles, n_sph_floats, views_per_rank, device, world=world, track_visibility=track_visibility,
+                         gather_buffer=False)   # peer buffers instead
         self.raster, self.rank = raster, rank
         self.slot_floats = (3 * n_particles + 3) // 4 * 4       # 16-byte aligned slots
         floats = self.SETS * views_per_rank * self.slot_floats
@@ -234,9 +235,13 @@ def training_step_peer(raster, ex, views, sph_degree, particle_density, particle
     outs, centres = [], []
     s = ex.step % ex.SETS
     ex.step += 1
+    if ex.track_visibility:
+        ex.visibility.zero_()
     for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
+        if ex.track_visibility:
+            torch.maximum(ex.visibility, vis, out=ex.visibility)
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
                                     rgba, rg, dist_, dg, ex.slot_tensor(s, i))
         centres.append(c)
@@ -253,12 +258,15 @@ def training_step_peer(raster, ex, views, sph_degree, particle_density, particle
         ex.centres_all.copy_(ex.my_centres)
     raster.density_gradient_finish(particle_density, ex.density_grad)       # overlaps the ordering point
     if ex.world > 1:
-        reduced = dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)
+        reduced = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
+        if ex.track_visibility:   # union of the ranks' visibilities, 4 B/particle
+            reduced.append(dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True))
         gathered.wait()
     ptrs = [ex.slot_ptr(r, s, i) for r in range(ex.world) for i in range(ex.views_per_rank)]
     raster.sh_gradient_expand_gather(sph_degree, particle_density, ex.centres_all, ptrs, ex.radiance_grad, accumulate=False)
     if reduced is not None:
-        reduced.wait()
+        for work in reduced:
+            work.wait()
     return outs
 
 
@@ -273,7 +281,13 @@ def optimizer_step(raster, ex, raw, particle_density, state, lrs, betas=(0.9, 0.
 
     raw / state / lrs: dicts keyed by PARAMETER_GROUPS -- raw parameter tensors (updated in place), (exp_avg, exp_avg_sq)
     pairs, learning rates.  ``particle_density`` is the packed record the step rendered with (gut_activate_pack).
-    Returns the raw-parameter gradients (dict)."""
+    Returns the raw-parameter gradients (dict).
+
+    The exchange must have been built with ``track_visibility=True`` (its ``visibility`` buffer is what masks the update;
+    an untracked buffer is all zeros and SelectiveAdam would silently update nothing): anything else raises."""
+    if not getattr(ex, "track_visibility", False):
+        raise ValueError("optimizer_step needs an exchange built with track_visibility=True: SelectiveAdam is masked by the "
+                         "visibility union of the step's views, which this exchange did not record")
     pos_g, rot_g, scl_g, dns_g = raster.activate_pack_backward(raw["rotation"], particle_density, ex.density_grad, scale_activation,
                                                                density_activation)
     alb_g, spc_g = raster.unpack_feature_gradient(ex.radiance_grad)

@@ -68,6 +68,10 @@ def load_library():
     lib.gut_backward_colour.restype = C.c_int
     lib.gut_set_training.argtypes = [vp, i32]
     lib.gut_set_training.restype = C.c_int
+    lib.gut_set_block_cull.argtypes = [vp, i32]
+    lib.gut_set_block_cull.restype = C.c_int
+    lib.gut_reset_gradients.argtypes = [vp, vp]
+    lib.gut_reset_gradients.restype = C.c_int
     lib.gut_density_gradient_finish.argtypes = [vp, vp, u32, fp, fp, i32]
     lib.gut_density_gradient_finish.restype = C.c_int
     lib.gut_sh_gradient_expand.argtypes = [vp, vp, u32, i32, fp, u32, fp, fp, fp, i32]
@@ -540,6 +544,16 @@ class SplatRaster:
     def set_training(self, training: bool):
         """gut_set_training: training=False skips the hit-mask recording of the forward (inference); no backward may follow."""
         self.lib.gut_set_training(self._h, 1 if training else 0)
+
+    def set_block_cull(self, enabled: bool):
+        """gut_set_block_cull: test control, see include/gut_b200.h (outputs are bit-identical either way)."""
+        self.lib.gut_set_block_cull(self._h, 1 if enabled else 0)
+
+    def reset_gradients(self):
+        """gut_reset_gradients: forget the pending sums of an abandoned multi-view step."""
+        rc = self.lib.gut_reset_gradients(self._h, self._stream())
+        if rc != 0:
+            self._raise(rc)
 
     def collect_times(self):
         """reference: SplatRaster::collectTimes (splatRaster.cpp:334-364) -> {tag: mean ms}."""

@@ -313,9 +313,9 @@ def run_ours(args):
         raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
         # algorithmic work = what the reference's walk does: every list entry of the tile for every live ray.  The forward's
         # conservative block cull (gut_render_common.cuh, stage_culled) skips part of it; the executed count is reported too.
-        os.environ["GUT_DEBUG_NO_BLOCK_CULL"] = "1"
+        raster.set_block_cull(False)
         t_, h_ = raster.measure_work(v["rays_ori"], v["rays_dir"])
-        del os.environ["GUT_DEBUG_NO_BLOCK_CULL"]
+        raster.set_block_cull(True)
         te_, _ = raster.measure_work(v["rays_ori"], v["rays_dir"])
         tests += t_; hits += h_; tests_exec += te_
         m_sum += raster.frame_stats()["num_intersections"]

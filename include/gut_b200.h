@@ -197,6 +197,21 @@ GUT_API int gut_backward(GutHandle* h, void* stream, const GutCamera* camera,
 GUT_API int gut_set_training(GutHandle* h, int32_t training);
 
 /*
+ * Test control: enabled == 0 makes the k_buffer_size == 0 forward walk every list entry instead of dropping, per 8x8 block,
+ * the entries whose response cannot reach the threshold for any ray of the block (a conservative cone bound).  Outputs are
+ * bit-identical either way (tests/test_gpu_fullsize.py); gut_measure_work uses it to count the reference's walk.
+ */
+GUT_API int gut_set_block_cull(GutHandle* h, int32_t enabled);
+
+/*
+ * Drops the gradient state a multi-view step keeps inside the handle: zeroes the [N,16] accumulators and forgets a pending
+ * gut_backward_colour sum.  Call it when a step is abandoned (an exception between gut_backward_colour and
+ * gut_density_gradient_finish) or when the particle set changes mid-step (densification); gut_backward_colour and
+ * gut_density_gradient_finish reject a particle count that differs from the pending accumulation's.
+ */
+GUT_API int gut_reset_gradients(GutHandle* h, void* stream);
+
+/*
  * Deferred gradients for multi-view steps (this build's extension).
  * The backward of one view leaves two things per particle: 12 ray-summed canonical-frame accumulators that are linear
  * and VIEW-INDEPENDENT (they become the [N,12] gradient through the particle's own rotation and scale only), and

@@ -187,7 +187,7 @@ CULL_CASES = {
 
 
 @pytest.mark.parametrize("name", sorted(CULL_CASES))
-def test_block_cull_changes_no_bit(name, monkeypatch):
+def test_block_cull_changes_no_bit(name):
     """The forward drops, per 8x8 block, list entries that no ray of the block can accept (gut_render.cu, block_cull).
     The bound is conservative: image, distance, hit counts and the gradients (through the hit masks) are bit-identical /
     equal to walking every entry."""
@@ -211,8 +211,9 @@ def test_block_cull_changes_no_bit(name, monkeypatch):
         return [x.clone() for x in out], t, hh, g12.clone(), gsph.clone()
 
     culled, t_c, h_c, g12_c, gsph_c = run()
-    monkeypatch.setenv("GUT_DEBUG_NO_BLOCK_CULL", "1")
+    raster.set_block_cull(False)
     full, t_f, h_f, g12_f, gsph_f = run()
+    raster.set_block_cull(True)
     for a, b in zip(culled, full):
         assert torch.equal(a, b)
     assert h_c == h_f and t_c <= t_f

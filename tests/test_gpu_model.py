@@ -332,3 +332,68 @@ def test_dist_optimizer_step_chains_activation_adjoint_and_adam(raster):
         assert np.array_equal(raw[k].cpu().numpy(), p), k
         assert np.array_equal(state[k][0].cpu().numpy(), m) and np.array_equal(state[k][1].cpu().numpy(), v), k
         assert np.array_equal(raw[k].cpu().numpy()[vis[:, 0] == 0], before[k][vis[:, 0] == 0]), k
+
+
+def test_optimizer_step_refuses_an_exchange_without_visibility(raster):
+    """An exchange that did not track visibility holds an all-zero mask: SelectiveAdam would update nothing, silently."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    ex = gdist.DeferredExchange(16, 48, 1, "cuda", world=1)
+    with pytest.raises(ValueError, match="track_visibility"):
+        gdist.optimizer_step(raster, ex, {}, None, {}, {})
+
+
+def test_peer_step_then_optimizer_step_changes_the_parameters(raster):
+    """training_step_peer (the bench default on more than one GPU; world 1 here) records the visibility union when asked,
+    so the optimiser step behind it really moves the visible particles."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    from tests.helpers import camera_of
+
+    n, w, h = 5000, 96, 64
+    raw_t = _raw(n, 21)
+    raw_t["positions"] = (torch.rand((n, 3), device="cuda") * 3 - 1.5)
+    raw_t["scale"] = torch.full((n, 3), -2.5, device="cuda")
+    raw = {"positions": raw_t["positions"], "rotation": raw_t["rotation"], "scale": raw_t["scale"], "density": raw_t["density"],
+           "features_albedo": raw_t["albedo"], "features_specular": raw_t["specular"]}
+    before = {k: v.clone() for k, v in raw.items()}
+    packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
+    sph = raster.pack_features(raw["features_albedo"], raw["features_specular"])
+    view = syn.make_view(w, h)
+    views = [{"rays_ori": view["rays_ori"].cuda(), "rays_dir": view["rays_dir"].cuda(), "camera": camera_of(view)}]
+    up = [(torch.rand((h, w, 4), device="cuda"), torch.rand((h, w, 1), device="cuda") * 0.01)]
+    try:
+        ex = gdist.PeerExchange(raster, n, 48, 1, "cuda", 0, world=1, track_visibility=True)
+    except RuntimeError as e:
+        pytest.skip(f"CUDA IPC unavailable: {e}")
+    try:
+        gdist.training_step_peer(raster, ex, views, 3, packed, sph, up, rank=0)
+        vis = ex.visibility.clone()
+        assert 0 < vis.sum() < n
+        state = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in raw.items()}
+        lrs = {k: 1e-2 for k in gdist.PARAMETER_GROUPS}
+        gdist.optimizer_step(raster, ex, raw, packed, state, lrs)
+        torch.cuda.synchronize()
+        moved = (raw["positions"] != before["positions"]).any(dim=1)
+        assert moved.any() and not moved[vis[:, 0] == 0].any()
+    finally:
+        ex.close()
+
+
+def test_two_handles_on_two_devices_in_one_process():
+    """Kernel attributes (dynamic shared memory opt-in of the per-tile sort) are per device: a second handle on another GPU
+    of the same process must render too."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    native = importlib.import_module("3dgrut_b200.native")
+    from tests.helpers import camera_of
+
+    scene = syn.make_scene(20000, 3, seed=3)
+    view = syn.make_view(160, 96)
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        r = native.SplatRaster(cfg_from_conf(make_conf()), device=dev)
+        with torch.cuda.device(dev):
+            out = r.trace(0, 3, syn.pack_density(scene).to(dev), scene["features"].to(dev), view["rays_ori"].to(dev),
+                          view["rays_dir"].to(dev), None, camera_of(view))
+            torch.cuda.synchronize()
+        outs.append(out[0].cpu())
+    assert torch.equal(outs[0], outs[1]) and outs[0].abs().max() > 0

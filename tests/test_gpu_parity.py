@@ -382,3 +382,34 @@ def test_pack_and_unpack_kernels_equal_cat_and_split():
     with pytest.raises(native.GutError):
         raster.pack_particles(torch.zeros((4, 3), device="cuda"), torch.zeros((4, 1), device="cuda"), torch.zeros((4, 3), device="cuda"),
                               torch.zeros((4, 3), device="cuda"))
+
+
+def test_host_buffer_entry_points_equal_the_device_pointer_calls(pkg):
+    """gut_forward_host / gut_backward_host (include/gut_b200.h): rays and upstream gradients in pinned HOST memory, image /
+    distance / hit counts back to host memory, copies enqueued on the call's stream -- same bits as gut_forward / gut_backward
+    on device tensors (the backward's float atomics land in another order: gradients to 1e-6)."""
+    n, w, h, deg = 6000, 150, 70, 3
+    scene = syn.make_scene(n, 3, seed=5)
+    view = syn.make_view(w, h)
+    raster = _raster(pkg)
+    (rgba, dist, hits, vis), (d12, sph, cam) = _run_forward(raster, scene, view, deg, stage=False)
+    rng = np.random.default_rng(5)
+    rg = torch.from_numpy(rng.uniform(-1, 1, (h, w, 4)).astype(np.float32))
+    dg = torch.from_numpy(rng.uniform(-0.01, 0.01, (h, w, 1)).astype(np.float32))
+    g12, gsph = raster.trace_bwd(0, deg, d12, sph, view["rays_ori"].cuda(), view["rays_dir"].cuda(), None, cam, 0, 1, None, None,
+                                 rgba, rg.cuda(), dist, dg.cuda())
+    torch.cuda.synchronize()
+    h_ro, h_rd = view["rays_ori"].pin_memory(), view["rays_dir"].pin_memory()
+    h_rgba = torch.empty((h, w, 4)).pin_memory(); h_dist = torch.empty((h, w, 1)).pin_memory(); h_hits = torch.empty((h, w, 1)).pin_memory()
+    vis2 = torch.empty((n, 1), device="cuda")
+    raster.trace_host(deg, d12, sph, h_ro, h_rd, cam, h_rgba, h_dist, h_hits, vis2)
+    g12h = torch.empty((n, 12), device="cuda"); gsphh = torch.empty((n, 48), device="cuda")
+    raster.trace_bwd_host(deg, d12, sph, w, h, cam, rg.pin_memory(), dg.pin_memory(), g12h, gsphh)
+    torch.cuda.synchronize()
+    assert torch.equal(h_rgba, rgba.cpu()) and torch.equal(h_dist, dist.cpu()) and torch.equal(h_hits, hits.cpu())
+    assert torch.equal(vis2, vis)
+    assert rel_l2(g12h.cpu().numpy(), g12.cpu().numpy()) <= 1e-5 and rel_l2(gsphh.cpu().numpy(), gsph.cpu().numpy()) <= 1e-5
+    # a backward without its host forward is refused
+    other = _raster(pkg)
+    with pytest.raises(Exception):
+        other.trace_bwd_host(deg, d12, sph, w, h, cam, rg.pin_memory(), dg.pin_memory(), g12h, gsphh)
