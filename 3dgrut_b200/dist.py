@@ -102,43 +102,65 @@ class DeferredExchange:
         """Bytes this rank contributes to the collectives of a step."""
         return self.density_grad.numel() * 4 + self.views_per_rank * self.colour_all.shape[1] * 12
 
+    # ---- step protocol shared with PeerExchange (used by training_step_* below and by Tracer.begin_step) --------------
+    def begin_step(self, rank=0):
+        """Start a step: returns nothing; ``slot(i)`` is where view i's colour gradient goes."""
+        self._rank = rank
+        self._centres = []
+        if self.track_visibility:
+            self.visibility.zero_()
+
+    def slot(self, i):
+        """[N,3] buffer that receives the masked colour gradient of this rank's view i (gut_backward_colour)."""
+        return self.colour_all[self.local_slot(self._rank, i)]
+
+    def add_view(self, centre, visibility=None):
+        """Record a finished view: the world-space view centre its backward used and (optionally) its mog_visibility."""
+        self._centres.append([float(c) for c in centre])
+        if self.track_visibility and visibility is not None:
+            torch.maximum(self.visibility, visibility.reshape(self.visibility.shape), out=self.visibility)
+
+    def finish_step(self, raster, sph_degree, particle_density):
+        """Close the step: [N,12] conversion of the view-summed accumulators, exchange with the other ranks, [N,48] expansion
+        over all views of the step.  Leaves the summed gradients in ``density_grad`` / ``radiance_grad`` on every rank."""
+        lo = self.local_slot(self._rank, 0)
+        mine = self.colour_all[lo:lo + self.views_per_rank]
+        centres = list(self._centres)
+        raster.density_gradient_finish(particle_density, self.density_grad)   # zeros when this rank had no view
+        for i in range(len(centres), self.views_per_rank):
+            mine[i].zero_()
+            centres.append([0.0, 0.0, 0.0])
+        my_centres = self.centres_all[lo:lo + self.views_per_rank]
+        my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
+        pending = None
+        if self.world > 1:
+            _all_gather(self.colour_all, mine)
+            _all_gather(self.centres_all, my_centres)
+            # the [N,12] allreduce runs on the collective stream while this stream expands the SH gradient
+            pending = [dist.all_reduce(self.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
+            if self.track_visibility:   # union of the ranks' visibilities, 4 B/particle
+                pending.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
+        raster.sh_gradient_expand(sph_degree, particle_density, self.centres_all, self.colour_all, self.radiance_grad, accumulate=False)
+        if pending is not None:
+            for work in pending:
+                work.wait()
+        return self.density_grad, self.radiance_grad
+
 
 def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
     """Same result as ``training_step`` (summed [N,12] and [N,48] gradients on every rank) with the SH expansion deferred.
-    Every rank must hold ``ex.views_per_rank`` views or fewer (missing ones contribute zeros)."""
+    Every rank must hold ``ex.views_per_rank`` views or fewer (missing ones contribute zeros).  Works with a
+    ``DeferredExchange`` (NCCL all-gather of the colour gradients) and with a ``PeerExchange`` (peer-memory loads)."""
     outs = []
-    lo = ex.local_slot(rank, 0)
-    mine = ex.colour_all[lo:lo + ex.views_per_rank]
-    centres = []
-    if ex.track_visibility:
-        ex.visibility.zero_()
+    ex.begin_step(rank)
     for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
-        if ex.track_visibility:
-            torch.maximum(ex.visibility, vis, out=ex.visibility)
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
-                                    rgba, rg, dist_, dg, mine[i])
-        centres.append(c)
+                                    rgba, rg, dist_, dg, ex.slot(i))
+        ex.add_view(c, vis)
         outs.append((rgba, dist_))
-    raster.density_gradient_finish(particle_density, ex.density_grad)   # zeros when this rank had no view
-    for i in range(len(views), ex.views_per_rank):
-        mine[i].zero_()
-        centres.append([0.0, 0.0, 0.0])
-    my_centres = ex.centres_all[lo:lo + ex.views_per_rank]
-    my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
-    pending = None
-    if ex.world > 1:
-        _all_gather(ex.colour_all, mine)
-        _all_gather(ex.centres_all, my_centres)
-        # the [N,12] allreduce runs on the collective stream while this stream expands the SH gradient
-        pending = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
-        if ex.track_visibility:   # union of the ranks' visibilities, 4 B/particle
-            pending.append(dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True))
-    raster.sh_gradient_expand(sph_degree, particle_density, ex.centres_all, ex.colour_all, ex.radiance_grad, accumulate=False)
-    if pending is not None:
-        for work in pending:
-            work.wait()
+    ex.finish_step(raster, sph_degree, particle_density)
     return outs
 
 
@@ -217,6 +239,40 @@ class PeerExchange(DeferredExchange):
     def bytes_per_rank(self):
         return self.density_grad.numel() * 4 + self.views_per_rank * self.n_particles * 12
 
+    def begin_step(self, rank=None):
+        super().begin_step(self.rank if rank is None else rank)
+        self._set = self.step % self.SETS
+        self.step += 1
+
+    def slot(self, i):
+        return self.slot_tensor(self._set, i)
+
+    def finish_step(self, raster, sph_degree, particle_density):
+        s = self._set
+        centres = list(self._centres)
+        for i in range(len(centres), self.views_per_rank):
+            self.slot_tensor(s, i).zero_()
+            centres.append([0.0, 0.0, 0.0])
+        self.my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
+        gathered, reduced = None, None
+        if self.world > 1:
+            # ordering point of the step: this all-gather completes on a rank only after every rank's colour gradients are written
+            gathered = dist.all_gather_into_tensor(self.centres_all.view(-1), self.my_centres.view(-1), async_op=True)
+        else:
+            self.centres_all.copy_(self.my_centres)
+        raster.density_gradient_finish(particle_density, self.density_grad)       # overlaps the ordering point
+        if self.world > 1:
+            reduced = [dist.all_reduce(self.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
+            if self.track_visibility:   # union of the ranks' visibilities, 4 B/particle
+                reduced.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
+            gathered.wait()
+        ptrs = [self.slot_ptr(r, s, i) for r in range(self.world) for i in range(self.views_per_rank)]
+        raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, ptrs, self.radiance_grad, accumulate=False)
+        if reduced is not None:
+            for work in reduced:
+                work.wait()
+        return self.density_grad, self.radiance_grad
+
     def close(self):
         torch.cuda.synchronize()
         if self.world > 1:
@@ -230,44 +286,9 @@ class PeerExchange(DeferredExchange):
 
 
 def training_step_peer(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
-    """``training_step_deferred`` with the colour-gradient all-gather folded into the expansion kernel (peer-memory loads).
-    Same summed [N,12] and [N,48] gradients on every rank."""
-    outs, centres = [], []
-    s = ex.step % ex.SETS
-    ex.step += 1
-    if ex.track_visibility:
-        ex.visibility.zero_()
-    for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
-        rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
-                                              v["camera"])
-        if ex.track_visibility:
-            torch.maximum(ex.visibility, vis, out=ex.visibility)
-        c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
-                                    rgba, rg, dist_, dg, ex.slot_tensor(s, i))
-        centres.append(c)
-        outs.append((rgba, dist_))
-    for i in range(len(views), ex.views_per_rank):
-        ex.slot_tensor(s, i).zero_()
-        centres.append([0.0, 0.0, 0.0])
-    ex.my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
-    gathered, reduced = None, None
-    if ex.world > 1:
-        # ordering point of the step: this all-gather completes on a rank only after every rank's colour gradients are written
-        gathered = dist.all_gather_into_tensor(ex.centres_all.view(-1), ex.my_centres.view(-1), async_op=True)
-    else:
-        ex.centres_all.copy_(ex.my_centres)
-    raster.density_gradient_finish(particle_density, ex.density_grad)       # overlaps the ordering point
-    if ex.world > 1:
-        reduced = [dist.all_reduce(ex.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
-        if ex.track_visibility:   # union of the ranks' visibilities, 4 B/particle
-            reduced.append(dist.all_reduce(ex.visibility, op=dist.ReduceOp.MAX, async_op=True))
-        gathered.wait()
-    ptrs = [ex.slot_ptr(r, s, i) for r in range(ex.world) for i in range(ex.views_per_rank)]
-    raster.sh_gradient_expand_gather(sph_degree, particle_density, ex.centres_all, ptrs, ex.radiance_grad, accumulate=False)
-    if reduced is not None:
-        for work in reduced:
-            work.wait()
-    return outs
+    """``training_step_deferred`` with the colour-gradient all-gather folded into the expansion kernel (peer-memory loads):
+    the same loop over a ``PeerExchange``.  Same summed [N,12] and [N,48] gradients on every rank."""
+    return training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=rank)
 
 
 PARAMETER_GROUPS = ("positions", "rotation", "scale", "density", "features_albedo", "features_specular")

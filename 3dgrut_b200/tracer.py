@@ -157,6 +157,29 @@ class Tracer:
             alb_g, spc_g = ctx.tracer_wrapper.unpack_feature_gradient(radiance_grad)
             return (None, None, None, None, None, pos_g, rot_g, scl_g, dns_g, alb_g, spc_g, None, None, None)
 
+    class _AutogradView(torch.autograd.Function):
+        """One view of a multi-view step (Tracer.begin_step): the forward renders from the step's packed parameters, the
+        backward is gut_backward_colour -- it leaves the view's colour gradient in the step's slot and keeps summing the
+        density-part accumulators inside the handle; the parameter gradients are formed once, by TracerStep.finish()."""
+
+        @staticmethod
+        def forward(ctx, step, view_index, anchor, ray_ori, ray_dir, sensor):
+            w = step.tracer.tracer_wrapper
+            rgba, dist, hits, vis = w.trace(view_index, step.n_active_features, step.particle_density, step.particle_radiance,
+                                            ray_ori, ray_dir, None, sensor)
+            ctx.save_for_backward(ray_ori, ray_dir, rgba, dist)
+            ctx.step, ctx.view_index, ctx.sensor, ctx.vis = step, view_index, sensor, vis
+            ctx.mark_non_differentiable(hits, vis)
+            return rgba, dist, hits, vis
+
+        @staticmethod
+        def backward(ctx, rgba_grad, dist_grad, _hits_grad_unused, _vis_grad_unused):
+            ray_ori, ray_dir, rgba, dist = ctx.saved_tensors
+            step = ctx.step
+            step._view_backward(ctx.view_index, ctx.sensor, ray_ori, ray_dir, rgba, torch.zeros_like(rgba) if rgba_grad is None else rgba_grad,
+                                dist, torch.zeros_like(dist) if dist_grad is None else dist_grad, ctx.vis)
+            return (None, None, torch.zeros_like(step.anchor), None, None, None)
+
     def __init__(self, conf):
         self.device = "cuda"
         self.conf = conf
@@ -181,6 +204,22 @@ class Tracer:
 
     def build_acc(self, gaussians, rebuild=True):
         pass  # 3DGUT has no acceleration structure (tracer.py:301-302)
+
+    def begin_step(self, gaussians, exchange=None, views_per_rank=None, rank=0):
+        """Multi-view training step (this build's extension; the reference renders one view per step, trainer.py:143-149):
+
+            step = tracer.begin_step(gaussians, exchange)      # parameters activated + packed ONCE for all views
+            for batch in batches:
+                out = step.render(batch)                        # same dict as Tracer.render
+                loss_fn(out).backward()                         # per view, BEFORE the next step.render
+            step.finish()                                       # gradients of all views summed into the parameters' .grad
+
+        The views' backward passes leave 12 B per particle and view (dL/dcolour) plus view-independent accumulators inside the
+        rasteriser; finish() turns them into [N,12] / [N,48] once (gut_density_gradient_finish, gut_sh_gradient_expand), runs the
+        data-parallel exchange when ``exchange`` spans several ranks (3dgrut_b200.dist.DeferredExchange / PeerExchange), applies
+        the activation adjoints and accumulates into ``.grad`` like autograd would.  Without ``exchange`` a single-rank one is
+        created for ``views_per_rank`` views (default 8) and reused across steps."""
+        return TracerStep(self, gaussians, exchange, views_per_rank, rank)
 
     def render(self, gaussians, gpu_batch, train=False, frame_id=0):
         rays_o = gpu_batch.rays_ori
@@ -218,3 +257,110 @@ class Tracer:
             "frame_time_ms": timings["forward_render"] if "forward_render" in timings else 0.0,
             "mog_visibility": mog_visibility,
         }
+
+
+class TracerStep:
+    """One multi-view step in flight (see Tracer.begin_step)."""
+
+    def __init__(self, tracer, gaussians, exchange, views_per_rank, rank):
+        from . import dist as gdist
+
+        self.tracer, self.gaussians, self.rank = tracer, gaussians, rank
+        w = tracer.tracer_wrapper
+        w.set_training(True)
+        self.n_active_features = gaussians.n_active_features
+        self.raw = _raw_parameters(gaussians) if tracer.fused_activations else None
+        if self.raw is not None:
+            self.leaves = (gaussians.positions, gaussians.rotation, gaussians.scale, gaussians.density, gaussians.features_albedo,
+                           gaussians.features_specular)
+        else:
+            # activated tensors, possibly non-leaf (the model's torch activations, evaluated WITH autograd recording): finish()
+            # hands them their gradients and autograd carries on to the raw parameters
+            self.leaves = (gaussians.positions, gaussians.get_rotation(), gaussians.get_scale(), gaussians.get_density(),
+                           gaussians.get_features())
+        with torch.no_grad():
+            if self.raw is not None:
+                self.particle_density = w.activate_pack(gaussians.positions, gaussians.rotation, gaussians.scale, gaussians.density, *self.raw)
+                self.particle_radiance = w.pack_features(gaussians.features_albedo, gaussians.features_specular)
+            else:
+                pos, rot, scl, dns, feat = self.leaves
+                self.particle_density = w.pack_particles(pos.contiguous(), dns.contiguous(), rot.contiguous(), scl.contiguous())
+                self.particle_radiance = feat.detach().contiguous()
+        n, n_sph = self.particle_density.shape[0], self.particle_radiance.shape[1]
+        if exchange is None:
+            vpr = views_per_rank or 8
+            cached = getattr(tracer, "_step_exchange", None)
+            if cached is None or cached.density_grad.shape[0] != n or cached.views_per_rank < vpr or cached.radiance_grad.shape[1] != n_sph:
+                cached = gdist.DeferredExchange(n, n_sph, vpr, self.particle_density.device, world=1, track_visibility=True)
+                tracer._step_exchange = cached
+            exchange = cached
+        self.exchange = exchange
+        self.anchor = torch.zeros(1, device=self.particle_density.device, requires_grad=True)
+        self.n_views = 0          # forwards issued
+        self.n_backward = 0       # backwards done
+        self._open = None         # view whose forward context the rasteriser currently holds
+        self.finished = False
+        w.reset_gradients()       # nothing pending from an abandoned step
+        exchange.begin_step(rank)
+
+    def render(self, gpu_batch, train=True):
+        if self.finished:
+            raise RuntimeError("TracerStep.render after finish()")
+        if self.n_views >= self.exchange.views_per_rank:
+            raise RuntimeError(f"the step's exchange holds {self.exchange.views_per_rank} views per rank")
+        if self._open is not None:
+            raise RuntimeError("TracerStep.render: the previous view's backward has not run; the rasteriser holds ONE forward "
+                               "context (as the reference, gutRenderer.cu:413-417), so call backward() per view before the next render")
+        t = self.tracer
+        sensor = camera_from_batch(gpu_batch)
+        i = self.n_views
+        self.n_views += 1
+        self._open = i
+        rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, gpu_batch.rays_ori.contiguous(),
+                                                           gpu_batch.rays_dir.contiguous(), sensor)
+        pred_rgb = rgba[..., :3].unsqueeze(0).contiguous()
+        pred_opacity = rgba[..., 3:].unsqueeze(0).contiguous()
+        pred_rgb, pred_opacity = self.gaussians.background(gpu_batch.T_to_world.contiguous(), gpu_batch.rays_dir, pred_rgb, pred_opacity, train)
+        timings = t.tracer_wrapper.collect_times()
+        return {"pred_rgb": pred_rgb, "pred_opacity": pred_opacity, "pred_dist": dist.unsqueeze(0).contiguous(),
+                "pred_normals": t._constant_normals(pred_rgb), "hits_count": hits.unsqueeze(0).contiguous(),
+                "frame_time_ms": timings["forward_render"] if "forward_render" in timings else 0.0, "mog_visibility": vis}
+
+    def _view_backward(self, i, sensor, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, vis):
+        if self._open != i:
+            raise RuntimeError(f"backward of view {i} after another view was rendered: its forward context is gone")
+        w = self.tracer.tracer_wrapper
+        c = w.trace_bwd_colour(self.n_active_features, self.particle_density, self.particle_radiance, ray_ori, ray_dir, sensor,
+                               rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous(), self.exchange.slot(i))
+        self.exchange.add_view(c, vis)
+        self.n_backward += 1
+        self._open = None
+
+    def finish(self):
+        """Sum the views' gradients into the parameters' ``.grad`` (all ranks of the exchange must call it).  Returns the
+        step's visibility union [N,1] (what SelectiveAdam masks with) when the exchange tracks it."""
+        if self.finished:
+            raise RuntimeError("TracerStep.finish called twice")
+        if self._open is not None:     # a view rendered without a backward contributes nothing: drop its slot
+            self.exchange.slot(self._open).zero_()
+            self.exchange.add_view([0.0, 0.0, 0.0], None)
+            self._open = None
+        self.finished = True
+        w = self.tracer.tracer_wrapper
+        g12, g48 = self.exchange.finish_step(w, self.n_active_features, self.particle_density)
+        if self.raw is not None:
+            pos, rot, scl, dns, alb, spc = self.leaves
+            pos_g, rot_g, scl_g, dns_g = w.activate_pack_backward(rot, self.particle_density, g12, *self.raw)
+            alb_g, spc_g = w.unpack_feature_gradient(g48)
+            pairs = zip(self.leaves, (pos_g, rot_g, scl_g, dns_g, alb_g, spc_g))
+        else:
+            pos_g, dns_g, rot_g, scl_g = w.unpack_particle_gradient(g12)
+            pairs = zip(self.leaves, (pos_g, rot_g, scl_g, dns_g, g48.clone()))
+        tensors, grads = [], []
+        for t, g in pairs:
+            if t.requires_grad:
+                tensors.append(t)
+                grads.append(g.reshape(t.shape))
+        if tensors:
+            torch.autograd.backward(tensors, grads)
+        return self.exchange.visibility if getattr(self.exchange, "track_visibility", False) else None

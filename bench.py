@@ -52,7 +52,8 @@ def parse_args():
                         "once per step (3dgrut_b200/dist.py training_step_deferred); peer = the same with the all-gather folded into the "
                         "expansion kernel (loads from the other ranks' buffers over NVLink, training_step_peer); allreduce = per-view "
                         "[N,48] accumulation + one allreduce of [N,12]+[N,48]; auto = peer on more than one GPU, deferred on one")
-    p.add_argument("--no-aux", action="store_true", help="skip the auxiliary forward-only 1080p measurement")
+    p.add_argument("--no-aux", action="store_true", help="skip the auxiliary measurements (sorted K=16, model-side passes, reference + shim)")
+    p.add_argument("--no-sweep", action="store_true", help="skip the C5 forward-only 1080p sweep over 0.5M-6M particles")
     p.add_argument("--cpu-sample-tiles", type=int, default=24)
     return p.parse_args()
 
@@ -147,6 +148,10 @@ def cpu_oracle_sample(args, n_tiles_sample, repeats=1):
 
     import ctypes as C
 
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: set the thread count explicitly and report what the library got
+    want = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    O.set_threads(want)
+    threads = O.threads_used()
     cfg = abi.default_config()
     w, h, n = args.width, args.height, args.particles
     scene = syn.make_scene(n, 3, seed=1003)
@@ -179,10 +184,12 @@ def cpu_oracle_sample(args, n_tiles_sample, repeats=1):
         rec = {"mpix_s": est, "t_whole_frame_stages_s": whole, "t_composite_sample_s": comp, "tests": out["tests"], "M": bins["M"]}
         if best is None or rec["mpix_s"] > best["mpix_s"]:
             best = rec
-    cores = os.cpu_count() or 1
-    best["cores"] = cores
+    best["cores"] = threads
+    best["host_cpus"] = os.cpu_count()
     best["sample"] = (f"one {w}x{h} view of the workload: projection+binning+SH-backward over all {n} particles, compositing fwd+bwd on "
-                      f"{len(tiles)} random tiles ({sample_pixels} px) with OpenMP on {cores} host threads; extrapolated per pixel")
+                      f"{len(tiles)} random tiles ({sample_pixels} px) with OpenMP on {threads} host threads (counted inside the library); "
+                      f"extrapolated per pixel: sample_px / (t_composite_sample + t_whole_frame_stages * sample_px / frame_px)")
+    best["sample_pixels"] = sample_pixels
     return best
 
 
@@ -205,12 +212,70 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"],
+                         "t_whole_frame_stages_s": last["t_whole_frame_stages_s"], "t_composite_sample_s": last["t_composite_sample_s"],
+                         "sample_pixels": last["sample_pixels"], "host_cpus": last["host_cpus"]},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-        "note": "the reference ships no CPU implementation of this path (SURVEY.md 8c); this arm times the C oracle port of it",
+        "note": "the reference ships no CPU implementation of this path (SURVEY.md 8c); this arm times the C oracle port of it "
+                "(pinned on the reference's own kernels: tests/test_reference_golden.py, tests/test_gpu_reference.py)",
     }
+    if not args.no_aux:
+        try:
+            line["reference_shim_gpu"] = reference_shim_gpu(args)
+        except Exception as e:   # no GPU in this process / oracle/_ref not built: the line stands without it
+            line["reference_shim_gpu"] = {"unavailable": repr(e)[:300]}
     print(json.dumps(line), flush=True)
+
+
+def reference_shim_gpu(args):
+    """Context figure for the reference arm only (never loaded by the GPU arm of this file): the reference's OWN CUDA tracer --
+    its unchanged sources built against the hand-written threedgutSlang.cuh of oracle/ref_build ("reference + shim",
+    oracle/_ref/lib3dgut_cc_k0.so, through the reference's pybind API) -- forward + backward of ONE view of the workload on
+    cuda:0, timed with CUDA events after warm-up."""
+    import torch
+
+    from tests import refshim
+    from tests.helpers import camera_of, syn
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device")
+    if not refshim.available(0):
+        raise RuntimeError("oracle/_ref/lib3dgut_cc_k0.so not built")
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    w, h, n = args.width, args.height, args.particles
+    scene = syn.make_scene(n, 3, seed=1003)
+    view = syn.make_view(w, h, k=0, n_views=args.views)
+    cam = camera_of(view)
+    d12 = syn.pack_density(scene).to(dev); sph = scene["features"].to(dev)
+    ro, rd = view["rays_ori"].to(dev), view["rays_dir"].to(dev)
+    g = torch.Generator().manual_seed(2000)
+    rg = (torch.rand((h, w, 4), generator=g) * 2 - 1).to(dev)
+    dg = ((torch.rand((h, w, 1), generator=g) * 2 - 1) * 0.01).to(dev)
+    ref = refshim.ReferenceRaster(0, enable_kernel_timings=True)
+
+    def one():
+        rgba, dist, hits, vis = ref.trace(SPH_DEGREE, d12, sph, ro, rd, cam)
+        ref.trace_bwd(SPH_DEGREE, d12, sph, ro, rd, cam, rgba, rg, dist, dg)
+
+    for _ in range(2):
+        one()
+    torch.cuda.synchronize()
+    ref.collect_times()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    t = ref.collect_times()
+    return {"label": "reference + shim (the reference's CUDA sources unchanged, Slang-generated header hand-written; K=0)",
+            "ms_per_view_fwd_bwd": ms, "mpix_per_s": w * h / (ms * 1e-3) / 1e6, "forward_render_ms": t.get("forward_render"),
+            "backward_render_ms": t.get("backward_render"), "particles": n, "width": w, "height": h,
+            "includes": "torch.zeros of the outputs and of the [N,12]+[N,48] gradients per call, as SplatRaster::trace / traceBwd do"}
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -408,12 +473,18 @@ def run_ours(args):
                 ev.record(copy_stream)
             return ev
 
+        # the step's gradient exchange is the one the device-resident loop above used (peer memory / NCCL), now driven by
+        # Tracer.begin_step ... finish(); a plain per-tensor allreduce has no step protocol, so that mode takes the deferred one
+        e2e_exchange = exchange if args.exchange in ("peer", "deferred") else gdist.DeferredExchange(
+            n, sph.shape[1], (args.views + world - 1) // world, dev, world=world)
+
         def e2e_step():
             nonlocal h2d, d2h
             h2d = d2h = 0
             for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
                 p.grad = None
             checksum = None
+            tstep = tracer.begin_step(gauss, exchange=e2e_exchange, rank=rank)
             cur = torch.cuda.current_stream()
             # the inputs of this step's first view were put in flight at the end of the previous step (a data loader's prefetch)
             ready = prefetched.pop() if prefetched else (stage(0) if pinned else None)
@@ -428,7 +499,7 @@ def run_ours(args):
                 for kk in ("rays_ori", "rays_dir"):
                     dv[kk] = dev_in[bi][kk]
                 rg, dg = dev_in[bi]["rg"], dev_in[bi]["dg"]
-                o = tracer.render(gauss, make_batch(dv, dev, pose_device="cpu"), train=True)
+                o = tstep.render(make_batch(dv, dev, pose_device="cpu"))
                 loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
                 loss.backward()
                 torch.cat([o["pred_rgb"][0].detach(), o["pred_opacity"][0].detach()], dim=-1, out=rgba_dev[bi])
@@ -442,9 +513,9 @@ def run_ours(args):
                     out_host.copy_(rgba_dev[bi], non_blocking=True)
                 d2h += out_host.numel() * 4
                 checksum = loss.detach() if checksum is None else checksum + loss.detach()
-            if world > 1:
-                for p in (gauss.positions, gauss._rotation, gauss._scale, gauss._density, gauss._features):
-                    dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
+            # gradients of all views (and of all ranks) -> .grad of the parameters: one [N,12] conversion, the exchange, one [N,48]
+            # expansion per step
+            tstep.finish()
             # the read-back of the last view's image may still be in flight (it is ordered before the next step's read-backs on the
             # copy stream); the timed region ends with cur.wait_stream(copy_stream) below
             if checksum is not None:
@@ -486,7 +557,8 @@ def run_ours(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.views * P * k_e2e / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h),
-               "path": "Tracer.render + autograd backward per view; rays and upstream gradients copied from pinned host memory "
+               "path": "Tracer.begin_step / step.render + autograd backward per view / step.finish (the multi-view entry of the plugin: "
+                       "gradient conversions and the data-parallel exchange once per step); rays and upstream gradients copied from pinned host memory "
                        "(copy stream, one view ahead), the 4x4 pose handed over as a host tensor (it becomes kernel parameters), rendered RGBA of every view and the scalar loss read back every step (the loss through pinned memory, consumed one step later); particles stay "
                        "device resident (they are the model)"}
 
@@ -510,6 +582,53 @@ def run_ours(args):
         ms = a0.elapsed_time(a1) / reps
         fwd_1080p = {"fps": 1e3 / ms, "ms_per_frame": ms, "particles": n, "intersections_M": raster.frame_stats()["num_intersections"]}
         raster.set_training(True)
+
+    # ---- C5 (BASELINE.json configs[4], metric "fwd-only FPS @1080p"): forward-only render sweep 0.5M-6M Gaussians, 1080p views
+    # dealt round-robin to the ranks, no collective (render.py eval throughput).  Reference timing convention: CUDA events around
+    # the forward only (splatRaster.cpp:208-241, threedgrut/render.py:231-259), frames per second over the whole job = views /
+    # (max over ranks of the time a rank needs for its views). ---------------------------------------------------------------
+    fwd_sweep = None
+    if not args.no_sweep:
+        fwd_sweep = {"width": 1920, "height": 1080, "views": args.views, "sph_degree": SPH_DEGREE, "n_gpus": world,
+                     "convention": "CUDA events around gut_forward only, inference mode (no hit-mask recording), inputs device resident",
+                     "by_particles": {}}
+        sweep_views = []
+        for k in my_view_ids:
+            hv = syn.make_view(1920, 1080, k=k, n_views=args.views)
+            sweep_views.append((hv["rays_ori"].to(dev), hv["rays_dir"].to(dev), camera_of(hv)))
+        raster.set_training(False)
+        for n_s in (500_000, 1_000_000, 2_000_000, 3_000_000, 6_000_000):
+            if n_s == n:
+                d12_s, sph_s = d12, sph
+            else:
+                sc = syn.make_scene(n_s, 3, seed=1003)
+                d12_s, sph_s = syn.pack_density(sc).to(dev), sc["features"].to(dev)
+                del sc
+            for ro_, rd_, cam_ in sweep_views:      # warm-up: grows the workspace to this size
+                raster.trace(0, SPH_DEGREE, d12_s, sph_s, ro_, rd_, None, cam_)
+            barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 3
+            a0.record()
+            m_tot = 0
+            for _ in range(reps):
+                for ro_, rd_, cam_ in sweep_views:
+                    raster.trace(0, SPH_DEGREE, d12_s, sph_s, ro_, rd_, None, cam_)
+                    m_tot += raster.frame_stats()["num_intersections"]
+            a1.record()
+            barrier()
+            ms_rank = a0.elapsed_time(a1) / reps
+            tt = torch.tensor([ms_rank], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms_job = float(tt.item())
+            fwd_sweep["by_particles"][str(n_s)] = {
+                "fps": args.views / (ms_job * 1e-3) if ms_job > 0 else None, "ms_per_frame_on_a_gpu": ms_rank / max(1, len(sweep_views)),
+                "intersections_M_per_frame": m_tot / max(1, reps * len(sweep_views)) / 1e6}
+            if n_s != n:
+                del d12_s, sph_s
+        raster.set_training(True)
+        del sweep_views
 
     # ---- auxiliary: the "sorted" configuration (k_buffer_size = 16, configs/paper/3dgut/base_sorted.yaml; SURVEY 8d's second
     # config): forward + backward of ONE view of the same workload, device resident ---------------------------------------
@@ -590,10 +709,12 @@ def run_ours(args):
         del groups, g12, g48, packed, raw
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and not args.no_cpu_baseline:
         try:
-            c = cpu_oracle_sample(args, args.cpu_sample_tiles)
-            cpu_baseline = {"value": c["mpix_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"]}
+            c = cpu_oracle_sample(args, args.cpu_sample_tiles if world == 1 else max(8, args.cpu_sample_tiles // 2))
+            cpu_baseline = {"value": c["mpix_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"],
+                            "t_whole_frame_stages_s": c["t_whole_frame_stages_s"], "t_composite_sample_s": c["t_composite_sample_s"],
+                            "sample_pixels": c["sample_pixels"], "host_cpus": c["host_cpus"]}
         except Exception as e:
             cpu_baseline = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e!r}"}
 
@@ -606,7 +727,7 @@ def run_ours(args):
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,
                               "forward_tests_executed_per_pixel": tests_exec / nv / P},
-            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "sorted_k16": sorted_k16, "model_side": model_side,
+            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "fwd_sweep": fwd_sweep, "sorted_k16": sorted_k16, "model_side": model_side,
         }
         print(json.dumps(line), flush=True)
     if args.exchange == "peer":

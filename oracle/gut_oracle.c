@@ -20,6 +20,9 @@
  * Build: see oracle/Makefile  (gcc -O2 -ffp-contract=off -fopenmp).
  */
 #include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -1212,4 +1215,26 @@ ORACLE_API void gut_oracle_selective_adam(uint64_t n_rows, uint32_t width, float
             exp_avg_sq[i] = v;
         }
     }
+}
+
+/* Host threads the OpenMP loops of this library use.  torchrun exports OMP_NUM_THREADS=1 to its workers, so bench.py's
+ * reference arm sets the count explicitly and reports what the library really used (gut_oracle_threads_used runs a
+ * parallel region and counts). */
+ORACLE_API void gut_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+ORACLE_API int gut_oracle_threads_used(void) {
+    int n = 1;
+#ifdef _OPENMP
+#pragma omp parallel
+    {
+#pragma omp single
+        n = omp_get_num_threads();
+    }
+#endif
+    return n;
 }

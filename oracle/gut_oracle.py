@@ -48,6 +48,17 @@ def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
+def set_threads(n):
+    """OpenMP threads of the oracle's loops (overrides OMP_NUM_THREADS, which torchrun sets to 1)."""
+    lib().gut_oracle_set_threads(C.c_int(int(n)))
+
+
+def threads_used():
+    """Threads a parallel region of the oracle really gets (counted inside the library)."""
+    lib().gut_oracle_threads_used.restype = C.c_int
+    return int(lib().gut_oracle_threads_used())
+
+
 def higher_msb(n):
     return int(lib().gut_oracle_higher_msb(int(n)))
 

@@ -397,3 +397,63 @@ def test_two_handles_on_two_devices_in_one_process():
             torch.cuda.synchronize()
         outs.append(out[0].cpu())
     assert torch.equal(outs[0], outs[1]) and outs[0].abs().max() > 0
+
+
+def _loss(out, seed):
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    return (out["pred_rgb"] * torch.rand(out["pred_rgb"].shape, device="cuda", generator=gen)).sum() + \
+        (out["pred_opacity"] * torch.rand(out["pred_opacity"].shape, device="cuda", generator=gen)).sum() + \
+        0.01 * (out["pred_dist"] * torch.rand(out["pred_dist"].shape, device="cuda", generator=gen)).sum()
+
+
+@pytest.mark.parametrize("fused,nonleaf", [(True, False), (False, False), (False, True)])
+def test_multi_view_step_equals_per_view_render(fused, nonleaf):
+    """Tracer.begin_step / step.render / step.finish (deferred gradient conversions, one per step) against the reference-shaped
+    loop Tracer.render + backward per view: same images, same summed gradients on the parameters -- raw parameters through
+    the fused activation kernels, activated leaf tensors, and activated NON-leaf tensors (the model's own torch activations:
+    gradients must continue through autograd to the raw parameters)."""
+    pkg = importlib.import_module("3dgrut_b200")
+    n, w, h, nv = 6000, 112, 80, 3
+    scene = syn.make_scene(n, 3, seed=44)
+    views = [syn.make_view(w, h, k=k, n_views=nv) for k in range(nv)]
+    conf = make_conf()
+    conf["render"]["fused_activations"] = fused
+    tracer = pkg.Tracer(conf)
+
+    def model():
+        if fused or nonleaf:
+            return RawGaussians(_raw_from_scene({k: v.cuda() for k, v in scene.items()}))
+        return SyntheticGaussians(scene, "cuda", n_active_features=3, requires_grad=True)
+
+    def params(g):
+        return g.parameters() if hasattr(g, "parameters") else [g.positions, g._rotation, g._scale, g._density, g._features]
+
+    ga = model()
+    imgs_a = []
+    for k, v in enumerate(views):
+        out = tracer.render(ga, make_batch(v, "cuda"), train=True)
+        _loss(out, k).backward()
+        imgs_a.append(out["pred_rgb"].detach().clone())
+    gb = model()
+    step = tracer.begin_step(gb, views_per_rank=nv)
+    imgs_b = []
+    for k, v in enumerate(views):
+        out = step.render(make_batch(v, "cuda"))
+        _loss(out, k).backward()
+        imgs_b.append(out["pred_rgb"].detach().clone())
+    vis = step.finish()
+    torch.cuda.synchronize()
+    for a, b in zip(imgs_a, imgs_b):
+        assert torch.equal(a, b)
+    for pa, pb in zip(params(ga), params(gb)):
+        assert pb.grad is not None and pa.grad.shape == pb.grad.shape
+        assert rel_l2(pb.grad.cpu().numpy(), pa.grad.cpu().numpy()) <= 2e-5
+    assert vis is not None and 0 < float(vis.sum()) <= n
+    # protocol errors: a second render before the backward, render after finish
+    step2 = tracer.begin_step(model(), views_per_rank=nv)
+    step2.render(make_batch(views[0], "cuda"))
+    with pytest.raises(RuntimeError, match="backward"):
+        step2.render(make_batch(views[1], "cuda"))
+    step2.finish()
+    with pytest.raises(RuntimeError):
+        step2.render(make_batch(views[1], "cuda"))
