@@ -320,7 +320,7 @@ int gut_forward(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N
     GUT_CUDA(h, ensure(h->features, n1 * 16, s));
     GUT_CUDA(h, ensure(h->emit_rec, n1 * 16, s));
     GUT_CUDA(h, ensure(h->tile_hist, (size_t)T * GUT_TILE_SUB * 4, s));
-    GUT_CUDA(h, ensure(h->tile_start, ((size_t)T + 1) * 4, s));
+    GUT_CUDA(h, ensure(h->tile_start, (2 * (size_t)T + 1) * 4, s));   // bucket offsets [T+1] + heavy-first tile order [T]
     GUT_CUDA(h, ensure(h->tile_cursor, (size_t)T * GUT_TILE_SUB * 4, s));
     GUT_CUDA(h, ensure(h->stats, 16, s));
 

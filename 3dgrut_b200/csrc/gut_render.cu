@@ -253,7 +253,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_FWD_MIN_BLOCKS) gut_render
                                                                      uint32_t* __restrict__ hit_masks /* nullable: inference */, bool block_culling) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
 
-    const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
+    // CTAs are dispatched in blockIdx order: tiles longest list first (gut_tile_scan_kernel leaves the order behind tile_start)
+    const uint32_t tile = __ldg(tile_start + fr.num_tiles + 1 + blockIdx.x / BLOCKS_PER_TILE), block = blockIdx.x % BLOCKS_PER_TILE;
     bool at_origin;
     const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, block, at_origin);
     const bool uniform = __all_sync(0xffffffffu, at_origin);
@@ -573,7 +574,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     float* const reduce_tile = nullptr;
 #endif
 
-    const uint32_t tile = blockIdx.x / BLOCKS_PER_TILE, block = blockIdx.x % BLOCKS_PER_TILE;
+    // CTAs are dispatched in blockIdx order: tiles longest list first (gut_tile_scan_kernel leaves the order behind tile_start)
+    const uint32_t tile = __ldg(tile_start + fr.num_tiles + 1 + blockIdx.x / BLOCKS_PER_TILE), block = blockIdx.x % BLOCKS_PER_TILE;
     const uint32_t lane = threadIdx.x & 31;
     bool at_origin;
     const RayPair ray = make_ray_pair(fr, ray_ori, ray_dir, tile, block, at_origin);

@@ -167,7 +167,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_KB_MIN_BLOCKS) gut_render_
                                                                             float* __restrict__ dist, float* __restrict__ hits) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
     __shared__ float kb_payload[3 * K * 32];
-    const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
+    // CTAs are dispatched in blockIdx order: tiles longest list first (gut_tile_scan_kernel leaves the order behind tile_start)
+    const uint32_t tile = __ldg(tile_start + fr.num_tiles + 1 + blockIdx.x / KB_BLOCKS_PER_TILE), block = blockIdx.x % KB_BLOCKS_PER_TILE;
     const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
     const float3 dlt = ray.o - fr.cam_centre;
 
@@ -324,7 +325,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     const float* __restrict__ dist_grad, float* __restrict__ raw_grad) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<false>::TOTAL];
     __shared__ float kb_payload[3 * K * 32];
-    const uint32_t tile = blockIdx.x / KB_BLOCKS_PER_TILE, block = blockIdx.x % KB_BLOCKS_PER_TILE;
+    // CTAs are dispatched in blockIdx order: tiles longest list first (gut_tile_scan_kernel leaves the order behind tile_start)
+    const uint32_t tile = __ldg(tile_start + fr.num_tiles + 1 + blockIdx.x / KB_BLOCKS_PER_TILE), block = blockIdx.x % KB_BLOCKS_PER_TILE;
     const RayK ray = make_ray_k(fr, ray_ori, ray_dir, tile, block);
     const float3 dlt = ray.o - fr.cam_centre;
     const uint32_t lane = threadIdx.x & 31;
