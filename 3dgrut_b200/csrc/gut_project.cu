@@ -37,11 +37,17 @@ GUT_D Quat slerp(Quat a, Quat b, float t) {
     return r;
 }
 
-GUT_D float3 to_sensor(Quat q, float3 t, float3 p) {
-    float3 c0, c1, c2;
-    quat_to_columns(q.w, q.x, q.y, q.z, c0, c1, c2);
-    return rotate_cols(c0, c1, c2, p) + t;
+// world -> sensor as a matrix: the shutter-start pose is the same for every sigma point of every particle, so a thread
+// forms it once instead of once per projected point
+struct PoseMat { float3 c0, c1, c2, t; };
+GUT_D PoseMat pose_matrix(Quat q, float3 t) {
+    PoseMat m;
+    quat_to_columns(q.w, q.x, q.y, q.z, m.c0, m.c1, m.c2);
+    m.t = t;
+    return m;
 }
+GUT_D float3 to_sensor(const PoseMat& m, float3 p) { return rotate_cols(m.c0, m.c1, m.c2, p) + m.t; }
+GUT_D float3 to_sensor(Quat q, float3 t, float3 p) { return to_sensor(pose_matrix(q, t), p); }
 
 GUT_D bool within_resolution(float rx, float ry, float tol, float2 p) {
     const float mx = rx * tol, my = ry * tol;
@@ -49,11 +55,18 @@ GUT_D bool within_resolution(float rx, float ry, float tol, float2 p) {
 }
 
 // OpenCV pinhole with rational radial, tangential and thin-prism terms (cameraProjections.cuh:57-103)
-GUT_D bool project_pinhole(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out) {
+// `ideal`: every distortion coefficient is zero (frame-uniform).  Then num = den = icd = 1 and dx = dy = 0 exactly for any
+// finite r2, and (1 * u + 0) * f + c rounds like u * f + c: the short path below returns the same bits.
+GUT_D bool project_pinhole(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out, bool ideal) {
     if (pos.z <= 0.0f) { out = make_float2(0.0f, 0.0f); return false; }
     const float ux = pos.x / pos.z, uy = pos.y / pos.z;
     const float sx = ux * ux, sy = uy * uy;
     const float r2 = sx + sy;
+    if (ideal && r2 <= 1e18f) {   // r2^3 stays finite
+        out.x = (ux + 0.0f) * cam.focal_length[0] + cam.principal_point[0];   // + 0: -0 -> +0 as the long path does
+        out.y = (uy + 0.0f) * cam.focal_length[1] + cam.principal_point[1];
+        return within_resolution(fw, fh, tol, out);
+    }
     const float a1 = 2.0f * ux * uy, a2 = r2 + 2.0f * sx, a3 = r2 + 2.0f * sy;
     const float* k = cam.radial_coeffs; const float* p = cam.tangential_coeffs; const float* s = cam.thin_prism_coeffs;
     const float num = 1.0f + r2 * (k[0] + r2 * (k[1] + r2 * k[2]));
@@ -89,8 +102,19 @@ GUT_D bool project_fisheye(const GutCamera& cam, float fw, float fh, float3 pos,
     return (theta < cam.max_angle) && within_resolution(fw, fh, tol, out);
 }
 
-GUT_D bool project_point(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out) {
-    if (cam.model == GUT_CAMERA_OPENCV_PINHOLE) return project_pinhole(cam, fw, fh, pos, tol, out);
+GUT_D bool pinhole_is_ideal(const GutCamera& cam) {
+    bool z = cam.model == GUT_CAMERA_OPENCV_PINHOLE;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) z = z && cam.radial_coeffs[k] == 0.0f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) z = z && cam.tangential_coeffs[k] == 0.0f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) z = z && cam.thin_prism_coeffs[k] == 0.0f;
+    return z;
+}
+
+GUT_D bool project_point(const GutCamera& cam, float fw, float fh, float3 pos, float tol, float2& out, bool ideal) {
+    if (cam.model == GUT_CAMERA_OPENCV_PINHOLE) return project_pinhole(cam, fw, fh, pos, tol, out, ideal);
     if (cam.model == GUT_CAMERA_OPENCV_FISHEYE) return project_fisheye(cam, fw, fh, pos, tol, out);
     out = make_float2(0.0f, 0.0f);
     return false;
@@ -108,21 +132,22 @@ GUT_D float shutter_time(const GutCamera& cam, float fw, float fh, float2 p) {
 
 // Project with the start pose; under a rolling shutter refine the capture time of the point by fixed-point
 // iteration on its own image row/column (cameraProjections.cuh:146-185).
-GUT_D bool project_with_shutter(const GutCamera& cam, float fw, float fh, int n_iter, float3 pos, float tol, float2& out) {
+GUT_D bool project_with_shutter(const GutCamera& cam, float fw, float fh, int n_iter, float3 pos, float tol, float2& out,
+                                const PoseMat& m0, bool ideal) {
+    bool ok = project_point(cam, fw, fh, to_sensor(m0, pos), tol, out, ideal);
+    if (cam.shutter == GUT_SHUTTER_GLOBAL) return ok;
     const Quat q0 = pose_quat(cam.start_pose);
     const float3 t0 = pose_t(cam.start_pose);
-    bool ok = project_point(cam, fw, fh, to_sensor(q0, t0, pos), tol, out);
-    if (cam.shutter == GUT_SHUTTER_GLOBAL) return ok;
     const Quat q1 = pose_quat(cam.end_pose);
     const float3 t1 = pose_t(cam.end_pose);
     if (!ok) {
-        ok = project_point(cam, fw, fh, to_sensor(q1, t1, pos), tol, out);
+        ok = project_point(cam, fw, fh, to_sensor(q1, t1, pos), tol, out, ideal);
         if (!ok) return false;
     }
     for (int i = 0; i < n_iter; ++i) {
         const float a = shutter_time(cam, fw, fh, out);
         const float3 t = f3(mixf(t0.x, t1.x, a), mixf(t0.y, t1.y, a), mixf(t0.z, t1.z, a));
-        ok = project_point(cam, fw, fh, to_sensor(slerp(q0, q1, a), t, pos), tol, out);
+        ok = project_point(cam, fw, fh, to_sensor(slerp(q0, q1, a), t, pos), tol, out, ideal);
     }
     return ok;
 }
@@ -156,7 +181,10 @@ GUT_D bool conic_extent(const GutConfig& cfg, float3 cov, float opacity, float2&
 // ---------------------------------------------------------------------------------------------------
 // K1.  One thread per particle.  The 48-byte parameter record is fetched as three 128-bit loads.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCamera cam, GutFrame fr, uint32_t N, int sph_degree,
+#ifndef GUT_K1_MIN_BLOCKS
+#define GUT_K1_MIN_BLOCKS 3   // 64 registers, no spills; 4 spills the sigma-point array
+#endif
+__global__ void __launch_bounds__(256, GUT_K1_MIN_BLOCKS) gut_project_kernel(GutConfig cfg, GutCamera cam, GutFrame fr, uint32_t N, int sph_degree,
                                                           const float4* __restrict__ density12, const float* __restrict__ sph,
                                                           GutProjBuffers out, float* __restrict__ visibility,
                                                           uint32_t* __restrict__ tile_hist) {
@@ -189,14 +217,16 @@ __global__ void __launch_bounds__(256) gut_project_kernel(GutConfig cfg, GutCame
         const float sc[3] = {r2.x, r2.y, r2.z};
         sensor_ray = pos - fr.cam_centre;
         float2 sp[7];
-        int nvalid = project_with_shutter(cam, fw, fh, n_iter, pos, tol, sp[0]) ? 1 : 0;
+        const PoseMat m0 = pose_matrix(pose_quat(cam.start_pose), pose_t(cam.start_pose));
+        const bool ideal = pinhole_is_ideal(cam);
+        int nvalid = project_with_shutter(cam, fw, fh, n_iter, pos, tol, sp[0], m0, ideal) ? 1 : 0;
         centre.x = sp[0].x * w0_mean; centre.y = sp[0].y * w0_mean;
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
             const float3 d = (fr.ut_delta * sc[a]) * c[a];
-            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos + d, tol, sp[a + 1]) ? 1 : 0;
+            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos + d, tol, sp[a + 1], m0, ideal) ? 1 : 0;
             centre.x += wi * sp[a + 1].x; centre.y += wi * sp[a + 1].y;
-            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos - d, tol, sp[a + 4]) ? 1 : 0;
+            nvalid += project_with_shutter(cam, fw, fh, n_iter, pos - d, tol, sp[a + 4], m0, ideal) ? 1 : 0;
             centre.x += wi * sp[a + 4].x; centre.y += wi * sp[a + 4].y;
         }
         const bool reject = cfg.ut_require_all_sigma_points_valid ? (nvalid < 7) : (nvalid == 0);
