@@ -8,6 +8,7 @@
 #include <string.h>
 
 #include <deque>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -832,3 +833,144 @@ int gut_frame_stats(GutHandle* h, GutFrameStats* out) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// gut_project_noalloc (include/gut_b200.h): the projection stage with its scratch in a file-scope device array.
+// No counterpart in the reference.  Nothing above this line knows about it.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t NA_N = GUT_NOALLOC_MAX_PARTICLES, NA_T = GUT_NOALLOC_MAX_TILES;
+// byte offsets of the sections (all multiples of 256)
+constexpr size_t NA_OFF_COUNT = 0;                          // u32  [NA_N]      tiles touched per particle
+constexpr size_t NA_OFF_POS = NA_OFF_COUNT + NA_N * 4;      // f32  [NA_N,2]
+constexpr size_t NA_OFF_CONIC = NA_OFF_POS + NA_N * 8;      // f32  [NA_N,4]
+constexpr size_t NA_OFF_EXTENT = NA_OFF_CONIC + NA_N * 16;  // f32  [NA_N,2]
+constexpr size_t NA_OFF_DEPTH = NA_OFF_EXTENT + NA_N * 8;   // f32  [NA_N]
+constexpr size_t NA_OFF_FEAT = NA_OFF_DEPTH + NA_N * 4;     // f32  [NA_N,4]
+constexpr size_t NA_OFF_EMIT = NA_OFF_FEAT + NA_N * 16;     // u32  [NA_N,4]    (K1 writes it; unused here)
+constexpr size_t NA_OFF_HIST = NA_OFF_EMIT + NA_N * 16;     // u32  [GUT_TILE_SUB][T] per-tile sub-counters: MUST START AT ZERO
+constexpr size_t NA_BYTES = NA_OFF_HIST + NA_T * GUT_TILE_SUB * 4;
+static_assert(NA_BYTES == GUT_NOALLOC_SCRATCH_BYTES, "header constant out of date");
+static_assert(NA_OFF_HIST % 256 == 0 && NA_OFF_EMIT % 256 == 0, "sections stay 256-byte aligned");
+
+// The scratch.  In HOST code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: host code gets
+// the address from cudaGetSymbolAddress (noalloc_scratch_of below); device code names the array directly.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// Tile ranges from the sub-counters: one CTA scans the T per-tile totals (T <= 8192).  Reads the array by name.
+constexpr int NA_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(NA_SCAN_THREADS) gut_noalloc_ranges_kernel(uint32_t T, uint32_t* __restrict__ ranges) {
+    const uint32_t* hist = reinterpret_cast<const uint32_t*>(g_noalloc_scratch + NA_OFF_HIST);
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry_s;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < T; base += NA_SCAN_THREADS) {
+        const uint32_t t = base + tid;
+        uint32_t v = 0;
+        if (t < T) {
+#pragma unroll
+            for (int k = 0; k < GUT_TILE_SUB; ++k) v += hist[GUT_SUB_SLOT(t, k, T)];
+        }
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += n;
+        }
+        if (lane == 31) warp_sums[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t ws = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t n = __shfl_up_sync(0xffffffffu, ws, o);
+                if (lane >= (uint32_t)o) ws += n;
+            }
+            warp_sums[lane] = ws;
+        }
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        const uint32_t first = carry + (wid ? warp_sums[wid - 1] : 0u) + incl - v;
+        if (t < T) {   // (0,0) for an empty tile, as gut_forward's stage outputs have it
+            ranges[2 * t] = v ? first : 0u;
+            ranges[2 * t + 1] = v ? first + v : 0u;
+        }
+        __syncthreads();
+        if (tid == NA_SCAN_THREADS - 1) carry_s = carry + warp_sums[31];
+        __syncthreads();
+    }
+}
+
+// Device address of the array on the CURRENT device, looked up once per device (every device that loads the module has
+// its own copy of the array).
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[NA_MAX_DEVICES] = {};
+std::mutex g_noalloc_mutex;
+
+cudaError_t noalloc_scratch_of(int device, unsigned char** out) {
+    if (device < 0 || device >= NA_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);   // the caller made `device` current
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" int gut_project_noalloc(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree,
+                                   const float* d_density, const float* d_radiance, uint32_t W, uint32_t H, float* d_visibility,
+                                   GutStageOutputs* so) {
+    int rc = check_common(h, camera, N, sph_degree, W, H);
+    if (rc != GUT_OK) return rc;
+    if (N > GUT_NOALLOC_MAX_PARTICLES)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_project_noalloc: %u particles exceed GUT_NOALLOC_MAX_PARTICLES = %u (fixed scratch; use gut_forward)",
+                    N, GUT_NOALLOC_MAX_PARTICLES);
+    const uint64_t tiles = (uint64_t)((W + GUT_TILE - 1) / GUT_TILE) * (uint64_t)((H + GUT_TILE - 1) / GUT_TILE);
+    if (tiles > GUT_NOALLOC_MAX_TILES)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_project_noalloc: %ux%u has %llu tiles, more than GUT_NOALLOC_MAX_TILES = %u (fixed scratch; use gut_forward)",
+                    W, H, (unsigned long long)tiles, GUT_NOALLOC_MAX_TILES);
+    if (N > 0 && (!d_density || !d_radiance || !d_visibility)) return fail(h, GUT_ERR_BAD_INPUT, "null particle pointer");
+    if (so && (so->d_sorted_keys || so->d_sorted_particle_idx))
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_project_noalloc does not sort: d_sorted_keys / d_sorted_particle_idx must be NULL");
+    cudaStream_t s = (cudaStream_t)stream_;
+    DeviceGuard guard(h->device);
+    unsigned char* base = nullptr;
+    {
+        const cudaError_t e = noalloc_scratch_of(h->device, &base);
+        if (e != cudaSuccess) return fail(h, GUT_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", h->device, cudaGetErrorString(e));
+    }
+    const GutFrame fr = make_frame(h->cfg, *camera, W, H);
+    const uint32_t T = fr.num_tiles;
+    GutProjBuffers pb;
+    pb.tiles_count = (uint32_t*)(base + NA_OFF_COUNT); pb.proj_pos = (float2*)(base + NA_OFF_POS);
+    pb.conic_opacity = (float4*)(base + NA_OFF_CONIC); pb.extent = (float2*)(base + NA_OFF_EXTENT);
+    pb.depth = (float*)(base + NA_OFF_DEPTH); pb.features = (float4*)(base + NA_OFF_FEAT); pb.emit_rec = (uint4*)(base + NA_OFF_EMIT);
+    uint32_t* hist = (uint32_t*)(base + NA_OFF_HIST);
+    // the array keeps the last call's contents: the counters are the one section that must start at zero
+    GUT_CUDA(h, cudaMemsetAsync(hist, 0, (size_t)T * GUT_TILE_SUB * 4, s));
+    GUT_CUDA(h, gut_launch_project(h->cfg, *camera, fr, N, sph_degree, d_density, d_radiance, pb, d_visibility, hist, s));
+    h->launches += N ? 1 : 0;
+    if (so) {
+        if (so->d_tiles_count) GUT_CUDA(h, cudaMemcpyAsync(so->d_tiles_count, pb.tiles_count, (size_t)N * 4, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_position) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_position, pb.proj_pos, (size_t)N * 8, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_conic_opacity) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_conic_opacity, pb.conic_opacity, (size_t)N * 16, cudaMemcpyDeviceToDevice, s));
+        if (so->d_proj_extent) GUT_CUDA(h, cudaMemcpyAsync(so->d_proj_extent, pb.extent, (size_t)N * 8, cudaMemcpyDeviceToDevice, s));
+        if (so->d_global_depth) GUT_CUDA(h, cudaMemcpyAsync(so->d_global_depth, pb.depth, (size_t)N * 4, cudaMemcpyDeviceToDevice, s));
+        if (so->d_features) { GUT_CUDA(h, gut_launch_copy_features3(N, pb.features, (float*)so->d_features, s)); h->launches += N ? 1 : 0; }
+        if (so->d_tile_ranges) {
+            gut_noalloc_ranges_kernel<<<1, NA_SCAN_THREADS, 0, s>>>(T, (uint32_t*)so->d_tile_ranges);
+            GUT_CUDA(h, cudaGetLastError());
+            h->launches += 1;
+        }
+    }
+    return GUT_OK;
+}

@@ -117,6 +117,8 @@ def load_library():
     lib.gut_frame_stats.restype = C.c_int
     lib.gut_measure_work.argtypes = [vp, vp, fp, fp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.gut_measure_work.restype = C.c_int
+    lib.gut_project_noalloc.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, C.POINTER(abi.GutStageOutputs)]
+    lib.gut_project_noalloc.restype = C.c_int
     lib.gut_last_error.argtypes = [vp]
     lib.gut_last_error.restype = C.c_char_p
     for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats",

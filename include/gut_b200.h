@@ -377,6 +377,35 @@ GUT_API int gut_frame_stats(GutHandle* h, GutFrameStats* out);
 GUT_API int gut_measure_work(GutHandle* h, void* stream, const float* d_ray_origin, const float* d_ray_direction,
                              uint64_t* num_tests, uint64_t* num_hits);
 
+/*
+ * gut_project_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers that
+ * cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * The projection stage alone (K1 of gut_forward: unscented projection, conic / extent, SH colour, per-tile culling and
+ * counting) for a small particle set, with ALL of its scratch -- the per-particle projected records and the per-tile
+ * sub-counters -- in one file-scope `static __device__` array of the library (GUT_NOALLOC_SCRATCH_BYTES = 5 MiB, held by
+ * every GPU that loads the library until the process exits).  The call allocates nothing: no cudaMalloc / cudaMallocAsync /
+ * cudaFree, no allocating library routine; it clears the tile counters, launches the kernels and copies the requested
+ * results into the caller's buffers on `stream`, without synchronising.
+ *   inputs : as gut_forward (no rays).  num_particles <= GUT_NOALLOC_MAX_PARTICLES and
+ *            ceil(width/16) * ceil(height/16) <= GUT_NOALLOC_MAX_TILES, else GUT_ERR_BAD_INPUT with a message naming the limit.
+ *   outputs: d_particle_visibility [N] (required); the K1 fields of `outputs` (d_tiles_count, d_proj_position,
+ *            d_proj_conic_opacity, d_proj_extent, d_global_depth, d_features; any may be NULL) with the same values, bit
+ *            for bit, as gut_forward's stage outputs; d_tile_ranges [T,2] = first / one-past-last slot of every tile's list
+ *            in the sorted order gut_forward would build ((0,0) for empty tiles).  d_sorted_keys / d_sorted_particle_idx
+ *            are not produced (they must be NULL) and num_intersections is not written (no device->host read-back).
+ * Every call on a device shares the one array, which keeps the previous call's contents (the call clears what must start
+ * at zero): two calls that overlap on the GPU -- different streams, or different handles on one device -- RACE.
+ * The forward context of `h` is not touched: a gut_backward still refers to the last gut_forward.
+ */
+#define GUT_NOALLOC_MAX_PARTICLES 65536u
+#define GUT_NOALLOC_MAX_TILES     8192u       /* 1920 x 1080 has 8160 tiles of 16 x 16 */
+#define GUT_NOALLOC_SCRATCH_BYTES (GUT_NOALLOC_MAX_PARTICLES * 72u + GUT_NOALLOC_MAX_TILES * 64u)
+GUT_API int gut_project_noalloc(GutHandle* h, void* stream, const GutCamera* camera,
+                 uint32_t num_particles, int32_t sph_degree_active,
+                 const float* d_particle_density, const float* d_particle_radiance,
+                 uint32_t width, uint32_t height,
+                 float* d_particle_visibility, GutStageOutputs* outputs);
+
 GUT_API const char* gut_last_error(GutHandle* h);
 GUT_API int         gut_abi_version(void);
 /* struct sizes as compiled into the library, so a foreign-language binding can verify its mirror of the structs */
