@@ -38,7 +38,15 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__thread_inst_executed_per_inst_executed.ratio", "launch__grid_size", "launch__block_size",
         "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
-        "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
+        "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum",
+        # issue / pipe utilisation and the warp-state mix (what a statement like "the FMA pipe is N % busy" rests on)
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.per_cycle_active",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__inst_executed_pipe_uniform.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.per_cycle_active",
+        "smsp__warps_active.avg.per_cycle_active", "smsp__average_warps_active_per_inst_executed.ratio",
+        "smsp__cycles_active.avg", "sm__cycles_elapsed.max", "smsp__thread_inst_executed.sum"]
+want += [h for h in hdr if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
+want += [h for h in hdr if h.startswith("smsp__sass_thread_inst_executed_op_f") and h.endswith(".sum") and h not in want]
 with open(f"{out_dir}/ncu_full_{tag}.md", "w") as f:
     f.write(f"# ncu --set full, {tag}\n\n`ncu --set full --clock-control none --import-source on -k regex:gut_` over one view of "
             "`python bench.py --steps 1 --warmup 3 --views 1 --no-e2e --no-cpu-baseline` (3M Gaussians, 1237x822).\n")
