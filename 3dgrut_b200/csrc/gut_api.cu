@@ -40,6 +40,7 @@ struct GutHandle {
 
     // per-particle workspace (K1 outputs) -- grow only, like GutRenderForwardContext (gutRenderer.cu:166-203)
     DevBuf tiles_count, proj_pos, conic, extent, depth, features, emit_rec, raw_grad;
+    DevBuf a_sum;   // [N,4] sum over the views of a deferred step of K5's A accumulator (gut_project.cu, origin fold)
     // per-tile
     DevBuf tile_hist, tile_start, tile_cursor, stats;
     // per-intersection
@@ -286,7 +287,7 @@ void gut_destroy(GutHandle* h) {
     if (!h) return;
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
-    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->emit_rec, &h->raw_grad, &h->tile_hist,
+    DevBuf* all[] = {&h->tiles_count, &h->proj_pos, &h->conic, &h->extent, &h->depth, &h->features, &h->emit_rec, &h->raw_grad, &h->a_sum, &h->tile_hist,
                      &h->tile_start, &h->tile_cursor, &h->stats, &h->entries, &h->scratch, &h->sorted_idx, &h->hit_masks,
                      &h->h_ray_ori, &h->h_ray_dir, &h->h_rgba, &h->h_dist, &h->h_hits, &h->h_rgba_grad, &h->h_dist_grad};
     for (DevBuf* b : all) release(*b);
@@ -458,11 +459,15 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
                                                    (float*)h->raw_grad.p, (const uint32_t*)h->hit_masks.p, s));
         h->launches += 1;
     }
+    if (d_colour_grad && ((size_t)N * 16 > h->a_sum.cap || !h->a_sum.p)) {
+        GUT_CUDA(h, ensure(h->a_sum, (size_t)N * 16, s));
+        GUT_CUDA(h, cudaMemsetAsync(h->a_sum.p, 0, h->a_sum.cap, s));
+    }
     {
         StageTimer t(h, ST_BWD_PROJECT, s);
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
                                                 (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad,
-                                                d_colour_grad, accumulate, s));
+                                                d_colour_grad, d_colour_grad ? (float*)h->a_sum.p : nullptr, accumulate, s));
         h->launches += 1;
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
@@ -507,8 +512,12 @@ int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const f
         GUT_CUDA(h, ensure(h->raw_grad, (size_t)N * 64, s));
         GUT_CUDA(h, cudaMemsetAsync(h->raw_grad.p, 0, h->raw_grad.cap, s));
     }
+    if ((size_t)N * 16 > h->a_sum.cap || !h->a_sum.p) {
+        GUT_CUDA(h, ensure(h->a_sum, (size_t)N * 16, s));
+        GUT_CUDA(h, cudaMemsetAsync(h->a_sum.p, 0, h->a_sum.cap, s));
+    }
     GUT_CUDA(h, gut_launch_project_backward(h->cfg, h->fwd_frame, N, 0, d_density, nullptr, nullptr, (float*)h->raw_grad.p, d_density_grad,
-                                            nullptr, nullptr, accumulate, s));
+                                            nullptr, nullptr, (float*)h->a_sum.p, accumulate, s));
     h->launches += 1;
     h->pending_density = false;
     return GUT_OK;
@@ -531,6 +540,7 @@ int gut_reset_gradients(GutHandle* h, void* stream_) {
     cudaStream_t s = (cudaStream_t)stream_;
     DeviceGuard guard(h->device);
     if (h->raw_grad.p) GUT_CUDA(h, cudaMemsetAsync(h->raw_grad.p, 0, h->raw_grad.cap, s));
+    if (h->a_sum.p) GUT_CUDA(h, cudaMemsetAsync(h->a_sum.p, 0, h->a_sum.cap, s));
     h->pending_density = false;
     h->pending_N = 0;
     return GUT_OK;

@@ -25,7 +25,7 @@ struct GutFrame {
 //     (unit-Gaussian) frame; go = ms * (frame origin - position) is the canonical ray origin of every ray that
 //     starts at the frame origin (GutFrame::cam_centre) -- all of them for pinhole / fisheye ray bundles -- so a
 //     ray/particle test needs ONE mat-vec (the direction), not two;
-//   GutRecordBwd (48 B, backward only): the six scale ratios s_i / s_j of the body-frame torque and 1 / scale.
+//   GutRecordBwd (32 B, backward only): 1 / scale and scale^2.
 struct __align__(16) GutRecord {
     float ms0x, ms0y, ms0z, gox;    // row 0 of ms | go.x
     float ms1x, ms1y, ms1z, goy;    // row 1       | go.y
@@ -36,11 +36,10 @@ struct __align__(16) GutRecord {
 };
 static_assert(sizeof(GutRecord) == 80, "record must be 5 float4");
 struct __align__(16) GutRecordBwd {
-    float r_yz, r_zy, r_xz, r_zx;   // s_y/s_z, s_z/s_y, s_x/s_z, s_z/s_x
-    float r_yx, r_xy, isx, isy;     // s_y/s_x, s_x/s_y, 1/s_x, 1/s_y
-    float isz, wx, wy, wz;          // 1/s_z | (frame origin - position) / scale
+    float isx, isy, isz, pad0;      // 1 / scale
+    float s2x, s2y, s2z, pad1;      // scale^2
 };
-static_assert(sizeof(GutRecordBwd) == 48, "backward record must be 3 float4");
+static_assert(sizeof(GutRecordBwd) == 32, "backward record must be 2 float4");
 
 // Global-memory sources of the per-intersection data.
 struct GutParticleSource {
@@ -69,6 +68,7 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad,
                                         float* colour_out /* non-null: write the view's masked colour gradient [N,3] instead of sph_grad */,
+                                        float* a_sum /* [N,4] sum of A over the views of a deferred step; NULL for the one-view backward */,
                                         int accumulate, cudaStream_t stream);
 
 // deferred SH backward of a multi-view step (gut_project.cu, gut_sh_expand_kernel)

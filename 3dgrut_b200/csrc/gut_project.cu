@@ -362,6 +362,20 @@ __global__ void __launch_bounds__(256, GUT_K1_MIN_BLOCKS) gut_project_kernel(Gut
 constexpr int K6_THREADS = 128;
 constexpr int K6_WARPS = K6_THREADS / 32;
 
+// The "origin fold": K5 leaves out the go (x) A halves of the torque, the trace and the scale terms when go is the same
+// for every ray of the view (gut_render.cu, backward_walk).  With A summed over the view's rays they are
+//   tau' += A x (s^2 go) = A x (s * R^T v),   tr += sum_i A_i v_i / s_i,   Z_i += go_i A_i,      v = view centre - position,
+// go = diag(1/s) R^T v.  c0..c2 are the columns of R, is = 1 / s.
+GUT_D void origin_fold(const float3 A, const float3 v, const float3 c0, const float3 c1, const float3 c2, const float3 sc,
+                       const float3 is, float3& tq, float& tr, float3& Z) {
+    const float3 rv = f3(dot(c0, v), dot(c1, v), dot(c2, v));
+    const float3 go = rv * is;
+    const float3 G = sc * rv;
+    tq = tq + cross(A, G);
+    tr = tr + (A.x * (v.x * is.x) + A.y * (v.y * is.y) + A.z * (v.z * is.z));
+    Z = Z + go * A;
+}
+
 // Phase A: one thread per particle computes the [N,12] gradient row and the masked colour gradient + SH basis.
 // Phase B: each warp writes its 32 rows of [N,12] (3 float4 per row) and [N,48] (12 float4 per row) as contiguous,
 // fully coalesced 128-bit accesses (12 independent loads in flight per lane when accumulating) instead of every
@@ -377,7 +391,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
                                                                           const float4* __restrict__ features,
                                                                           float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
                                                                           float* __restrict__ sph_grad, float* __restrict__ colour_out,
-                                                                          int accumulate) {
+                                                                          float4* __restrict__ a_sum, int accumulate) {
     __shared__ float4 s_dg[K6_WARPS][32 * 3];      // parameter-gradient rows of the warp
     __shared__ float s_basis[K6_WARPS][32][17];    // SH basis per row (+1 pad: conflict-free column reads)
     __shared__ float4 s_g[K6_WARPS][32];           // masked colour gradient per row, w = 1 if the row was touched
@@ -412,14 +426,22 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
         const float4 qv = __ldg(density12 + 3 * (size_t)i + 1);  // quat w,x,y,z
         const float4 r2 = __ldg(density12 + 3 * (size_t)i + 2);  // scale
         // ---- (i) parameter gradient ----
-        const float3 A = f3(g0.x, g0.y, g0.z);
-        const float3 tau = f3(g1.x, g1.y, g1.z);
-        const float tr_dir = g1.w;
-        const float3 Z = f3(g2.x, g2.y, g2.z);
+        float3 A = f3(g0.x, g0.y, g0.z);
+        float3 tq = f3(g1.x, g1.y, g1.z);
+        float tr_dir = g1.w;
+        float3 Z = f3(g2.x, g2.y, g2.z);
         const float W = g3.z;
         const float3 is = f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z);
         float3 c0, c1, c2;
         quat_to_columns(qv.x, qv.y, qv.z, qv.w, c0, c1, c2);
+        if (a_sum) {   // end of a deferred step: every view folded its own origin (gut_view_fold_kernel) and moved its A here
+            const float4 as = a_sum[i];
+            A = f3(as.x, as.y, as.z);
+            if (as.x != 0.0f || as.y != 0.0f || as.z != 0.0f) a_sum[i] = z;
+        } else {
+            origin_fold(A, fr.cam_centre - f3(r0.x, r0.y, r0.z), c0, c1, c2, f3(r2.x, r2.y, r2.z), is, tq, tr_dir, Z);
+        }
+        const float3 tau = f3(tq.x * (is.y * is.z), tq.y * (is.x * is.z), tq.z * (is.x * is.y));
         const float3 As = A * is;
         // dL/dpos = -R (A / s)
         o0 = make_float4(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
@@ -535,44 +557,65 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 }
 
 // One view of a deferred step (gut_backward_colour): hand out the view's masked colour gradient and reset its three
-// accumulators; everything else waits for the end of the step.  ~100 bytes per particle, no shared memory.
-__global__ void __launch_bounds__(256) gut_colour_gradient_kernel(uint32_t N, const uint32_t* __restrict__ tiles_count,
-                                                                  const float4* __restrict__ features, float4* __restrict__ raw_grad,
-                                                                  float* __restrict__ colour_out) {
+// accumulators; fold the view's origin into the torque / trace / scale accumulators (origin_fold above: it needs the
+// A of THIS view alone and this view's centre) and move A to the step's sum `a_sum`, leaving [0..2] zero for the next
+// view.  Everything else waits for the end of the step.
+__global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 centre, const float4* __restrict__ density12,
+                                                            const float4* __restrict__ features, float4* __restrict__ raw_grad,
+                                                            float4* __restrict__ a_sum, float* __restrict__ colour_out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     // no test of tiles_count: the accumulators of an untouched particle are zero, and skipping the dependent load matters
     // more than the bytes (the kernel is bound by the latency of its load -> store chain, not by bandwidth)
-    (void)tiles_count;
     float4* rg = raw_grad + 4 * (size_t)i;
-    const float4 g2 = rg[2], g3 = rg[3];
+    const float4 a = rg[0], g2 = rg[2], g3 = rg[3];
     const float4 ft = __ldg(features + i);
     const float3 g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
-    if (g2.w != 0.0f) rg[2] = make_float4(g2.x, g2.y, g2.z, 0.0f);
+    float3 Z = f3(g2.x, g2.y, g2.z);
+    const bool moved = a.x != 0.0f || a.y != 0.0f || a.z != 0.0f;
+    if (moved) {   // second round trip for the particles the view's rays pushed on
+        const float4 r0 = __ldg(density12 + 3 * (size_t)i), qv = __ldg(density12 + 3 * (size_t)i + 1), r2 = __ldg(density12 + 3 * (size_t)i + 2);
+        const float4 g1 = rg[1], as = a_sum[i];
+        float3 c0, c1, c2;
+        quat_to_columns(qv.x, qv.y, qv.z, qv.w, c0, c1, c2);
+        float3 tq = f3(g1.x, g1.y, g1.z);
+        float tr = g1.w;
+        origin_fold(f3(a.x, a.y, a.z), centre - f3(r0.x, r0.y, r0.z), c0, c1, c2, f3(r2.x, r2.y, r2.z),
+                    f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z), tq, tr, Z);
+        rg[1] = make_float4(tq.x, tq.y, tq.z, tr);
+        a_sum[i] = make_float4(as.x + a.x, as.y + a.y, as.z + a.z, 0.0f);
+        rg[0] = make_float4(0.0f, 0.0f, 0.0f, a.w);
+    }
+    if (moved || g2.w != 0.0f) rg[2] = make_float4(Z.x, Z.y, Z.z, 0.0f);
     if (g3.x != 0.0f || g3.y != 0.0f) rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w);
     colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z;
 }
 
+// a_sum [N,4]: the deferred step's sum of A over its views.  Required with colour_out (one view of a deferred step) and
+// with density_grad alone (end of the step); NULL for the one-view backward, which folds its own origin.
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, int accumulate,
-                                        cudaStream_t stream) {
+                                        float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, float* a_sum,
+                                        int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
     const float4* d12 = reinterpret_cast<const float4*>(density12);
     float4* rg = reinterpret_cast<float4*>(raw_grad);
     float4* dg = reinterpret_cast<float4*>(density_grad);
+    float4* as = reinterpret_cast<float4*>(a_sum);
     if (density_grad && (sph_grad || colour_out))
         gut_project_backward_kernel<true, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
-                                                                               sph_grad, colour_out, accumulate);
-    else if (density_grad)
+                                                                               sph_grad, colour_out, nullptr, accumulate);
+    else if (density_grad) {
+        if (!a_sum) return cudaErrorInvalidValue;
         gut_project_backward_kernel<true, false><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
-                                                                                nullptr, nullptr, accumulate);
-    else if (colour_out)
-        gut_colour_gradient_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, tiles_count, features, rg, colour_out);
-    else
+                                                                                nullptr, nullptr, as, accumulate);
+    } else if (colour_out) {
+        if (!a_sum) return cudaErrorInvalidValue;
+        gut_view_fold_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, frame.cam_centre, d12, features, rg, as, colour_out);
+    } else
         gut_project_backward_kernel<false, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg,
-                                                                                nullptr, sph_grad, colour_out, accumulate);
+                                                                                nullptr, sph_grad, colour_out, nullptr, accumulate);
     return cudaGetLastError();
 }
 

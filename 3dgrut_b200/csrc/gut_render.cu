@@ -373,38 +373,48 @@ GUT_D float warp_transpose_reduce(const F2 (&V)[16], uint32_t lane) {
     return x;
 }
 
-// Same sum through a warp-private shared-memory tile (-DGUT_BWD_SMEM_REDUCE): 42 instructions instead of 71 at the same
-// FMA-pipe cycles -- and measured SLOWER (3.955 vs 3.91 ms per view): store -> __syncwarp -> load is a longer dependent
-// chain than five shuffle rounds and the kernel runs ~4.5 warps per scheduler.  Kept as a build option for the record.
-//  stage 0: the two rays of a lane are added and the lane stores its row of 16 floats with four 128-bit stores (row
-//           pitch 20 floats, so the stores of a quarter warp cover all 32 banks exactly once);
-//  stage 1: lane l owns the value pair p = l & 7 and the row group g = l >> 3 (8 rows): eight 64-bit loads (odd groups
-//           start 4 rows in, which moves their banks by 16: conflict free within a half warp) summed with packed adds;
-//  stage 2: the four row groups are combined with two 64-bit shuffle rounds (xor 8, xor 16).
-// On return every lane holds the warp totals of values 2p (low) and 2p + 1 (high).  V[15] is padding and not read.
 constexpr uint32_t REDUCE_PITCH = 20;                           // floats per row
 constexpr uint32_t REDUCE_TILE_BYTES = 32 * REDUCE_PITCH * 4;
-GUT_D F2 warp_smem_reduce(const F2 (&V)[16], uint32_t lane, float* __restrict__ tile) {
+
+// The same sum through a warp-private shared-memory tile, software-pipelined (the default; -DGUT_BWD_SHUFFLE_REDUCE selects
+// the shuffle version above): a hit's rows are stored at the end of its iteration and summed during the NEXT hit's
+// arithmetic, so that the store -> load -> add -> shuffle chain of one hit overlaps the FMA chain of the next instead of
+// following its own -- the walk is bound by the length of its dependent chains at ~4.6 warps per scheduler.  44
+// instructions instead of 71, and off the critical path: 3.27 -> 3.12 ms per view.  (Not pipelined, the tile version was
+// SLOWER than the shuffles, 3.955 vs 3.91 ms at the time: store -> __syncwarp -> load is the longer chain.)
+//  reduce_store : the two rays of a lane are added and the lane stores its row of 16 floats with four 128-bit stores (row
+//                 pitch 20 floats, so the stores of a quarter warp cover all 32 banks exactly once);
+//  reduce_load  : lane l owns the value pair p = l & 7 and the row group g = l >> 3 (8 rows): eight 64-bit loads (odd groups
+//                 start 4 rows in, which moves their banks by 16: conflict free within a half warp);
+//  reduce_finish: packed adds, then the four row groups are combined with two 64-bit shuffle rounds (xor 8, xor 16): every
+//                 lane holds the warp totals of values 2p (low) and 2p + 1 (high).  Value 15 is padding.
+GUT_D void reduce_store(const F2 (&V)[16], uint32_t lane, float* __restrict__ tile) {
     float4* row = reinterpret_cast<float4*>(tile + lane * REDUCE_PITCH);
-    __syncwarp();   // every lane has read the previous visit's tile
     row[0] = make_float4(lo(V[0]) + hi(V[0]), lo(V[1]) + hi(V[1]), lo(V[2]) + hi(V[2]), lo(V[3]) + hi(V[3]));
     row[1] = make_float4(lo(V[4]) + hi(V[4]), lo(V[5]) + hi(V[5]), lo(V[6]) + hi(V[6]), lo(V[7]) + hi(V[7]));
     row[2] = make_float4(lo(V[8]) + hi(V[8]), lo(V[9]) + hi(V[9]), lo(V[10]) + hi(V[10]), lo(V[11]) + hi(V[11]));
     row[3] = make_float4(lo(V[12]) + hi(V[12]), lo(V[13]) + hi(V[13]), lo(V[14]) + hi(V[14]), 0.0f);
-    __syncwarp();
+}
+GUT_D F2 reduce_load(uint32_t lane, const float* __restrict__ tile) {   // sum over the lane's 8 rows of its value pair
     const uint32_t g = lane >> 3, rot = (g & 1u) * 4u;
     const float* col = tile + g * 8 * REDUCE_PITCH + 2 * (lane & 7u);
-    F2 acc[2];
+    F2 x[8];
 #pragma unroll
-    for (uint32_t i = 0; i < 8; ++i) {
-        F2 x;
-        x.v = *reinterpret_cast<const u64*>(col + ((i + rot) & 7u) * REDUCE_PITCH);
-        acc[i & 1] = i < 2 ? x : acc[i & 1] + x;
-    }
-    F2 t = acc[0] + acc[1];
+    for (uint32_t i = 0; i < 8; ++i) x[i].v = *reinterpret_cast<const u64*>(col + ((i + rot) & 7u) * REDUCE_PITCH);
+    return ((x[0] + x[1]) + (x[2] + x[3])) + ((x[4] + x[5]) + (x[6] + x[7]));
+}
+GUT_D F2 reduce_finish(F2 t) {
     t = t + shfl2(t, 8);
     t = t + shfl2(t, 16);
     return t;
+}
+// lane p < 8 adds values 2p and 2p + 1 of particle `idx`: one 64-bit vector reduction (value 15 is padding)
+GUT_D void reduce_commit(F2 total, uint32_t lane, uint32_t idx, float* __restrict__ raw_grad) {
+    if (lane < 8u) {
+        float* dst = raw_grad + 16 * (size_t)idx + 2 * lane;
+        if (lane < 7u) atomicAdd(reinterpret_cast<float2*>(dst), make_float2(lo(total), hi(total)));
+        else atomicAdd(dst, lo(total));
+    }
 }
 
 struct BwdRay {
@@ -413,6 +423,8 @@ struct BwdRay {
     F2 T;                    // running transmittance of the re-walk
     F2x3 Crem;               // forward colour still to be composited behind the current hit
     bool alive[2];
+    bool pending;            // the reduce tile holds the rows of a hit that is not summed yet ...
+    uint32_t pending_idx;    // ... of this particle (warp-uniform)
 };
 
 // Per accepted hit a ray produces 15 values that are LINEAR in the ray, so they can be summed over rays first (the two
@@ -420,13 +432,16 @@ struct BwdRay {
 // 16 floats per particle) and turned into parameter gradients once per particle by K6 (gut_project.cu):
 //   [0..2]  A   = dL/d go            (canonical ray origin)        -> dL/dpos   = -ms^T A
 //   [3]     dL/d density
-//   [4..6]  tau = body-frame torque                                 -> dL/dquat  = rho q + 2 q (x) (0, tau)
-//   [7]     tr  = sum_i (dL/dR^T)_ii                                -> rho (radial part of dL/dquat, R(q) is a polynomial)
-//   [8..10] Z_i = go_i A_i + u_i B_i - s_i * (hit-distance term)    -> dL/dscale_i = -Z_i / s_i
+//   [4..6]  tau' = body-frame torque x (s_j s_k), direction half     -> dL/dquat  = rho q + 2 q (x) (0, tau)
+//   [7]     tr  = sum_i (dL/dR^T)_ii, direction half                -> rho (radial part of dL/dquat, R(q) is a polynomial)
+//   [8..10] Z_i = u_i B_i - s_i * (hit-distance term)  [+ go_i A_i]  -> dL/dscale_i = -Z_i / s_i
 //   [11..13] dL/d colour
 //   [14]    W   = sum_i s_i * (hit-distance scale term)             -> rho
 // with B = dL/d u.  This is the chain rule of processHitBwd (gaussianParticles.cuh:635-738) with the per-ray
-// quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.
+// quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.  tau, tr and Z each have a
+// half that is go (x) A: with all rays starting at the frame origin go is a per-particle constant, so that half is
+// go_frame (x) sum_rays(A) and K6 adds it from [0..2] (the "origin fold", gut_project.cu) -- 12 packed FP32 instructions
+// per hit that the 64 rays of a block do not execute.  Only the per-ray remainder of go (non-UNIFORM rays) is added here.
 // A ray of the lane that does not take the hit runs the same packed instructions with alpha = 0 and a zeroed
 // upstream sum: every one of its 15 values is then exactly 0 and its state is unchanged.
 template <int DEG, bool UNIFORM, bool STD>
@@ -438,29 +453,35 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
       {
         const uint32_t j = __ffs(mask) - 1;
         mask &= mask - 1;
+#ifndef GUT_BWD_SHUFFLE_REDUCE
+        // rows of the previous hit (stored before the last __syncwarp): summed while this hit's arithmetic runs.  Two
+        // registers stay live, and the two shuffle rounds are placed further down between independent stretches of it.
+        F2 prev = reduce_load(lane, tile);
+#endif
         const float4* r = rec + 5 * j;
         const float4 A = r[0], B = r[1], Cm = r[2], S = r[3];
         Canon2 k;
         bool acc0, acc1;
         particle_test<DEG, UNIFORM, STD>(cfg, A, B, Cm, S.w, ray, k, acc0, acc1);
         const bool h0 = acc0 && st.alive[0], h1 = acc1 && st.alive[1];  // no tMinMax test here
+#ifndef GUT_BWD_SHUFFLE_REDUCE
+        prev = prev + shfl2(prev, 8);
+#endif
 
         // every lane runs the hit math (rays that do not take the hit are masked, see above): no lane-level branch
         F2 v[16];
         const float4 F = r[4];
         {
-            const float4 R0 = recb[3 * j], R1 = recb[3 * j + 1];
-            const float4 R2 = recb[3 * j + 2];
-            const float isz = R2.x;
+            const float4 IS = recb[2 * j], S2 = recb[2 * j + 1];   // 1 / scale, scale^2
             const F2x3& go = k.go;
             const F2x3& u = k.u;
             const F2 il = mk2(mufu_rsq(h0 ? lo(k.l2) : 1.0f), mufu_rsq(h1 ? hi(k.l2) : 1.0f));   // 1 / |u|
             const F2x3 grd = u * il;                   // normalised canonical direction
             const F2 dgo = dot(grd, go);
-            // hit distance gdist = |s * grd * dot(grd, -go)| = |dgo| * |sg|, sg = s * grd
-            F2x3 sg, sg2;
-            sg.x = bc(S.x) * grd.x; sg.y = bc(S.y) * grd.y; sg.z = bc(S.z) * grd.z;
-            sg2.x = sg.x * sg.x; sg2.y = sg.y * sg.y; sg2.z = sg.z * sg.z;
+            // hit distance gdist = |s * grd * dot(grd, -go)| = |dgo| * |sg|, sg = s * grd.  hv = s^2 grd, sg2 = sg^2 = hv grd
+            F2x3 hv, sg2;
+            hv.x = bc(S2.x) * grd.x; hv.y = bc(S2.y) * grd.y; hv.z = bc(S2.z) * grd.z;
+            sg2.x = hv.x * grd.x; sg2.y = hv.y * grd.y; sg2.z = hv.z * grd.z;
             const F2 ssum = sg2.x + sg2.y + sg2.z;
             const F2 gdist = mk2(h0 ? fabsf(lo(dgo)) * mufu_sqrt(lo(ssum)) : 0.0f, h1 ? fabsf(hi(dgo)) * mufu_sqrt(hi(ssum)) : 0.0f);
             const F2 alpha = mk2(h0 ? fminf(thr_max_alpha<STD>(cfg), lo(k.araw)) : 0.0f, h1 ? fminf(thr_max_alpha<STD>(cfg), hi(k.araw)) : 0.0f);
@@ -477,82 +498,99 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             // depth&, depthGrad) (shRadiativeGaussianParticles.cuh:369-406, gaussianParticles.cuh:499-501), so the residual is
             // max((0 - (D_f + w gdist)) / nextT, 0) = 0 for the forward's non-negative D_f.  Pinned on the reference's own
             // kernels by tests/test_gpu_reference.py.
-            const F2 dHit = gdist;
             const F2 wd = w * st.dD;
             // gdist is 0 for a ray that does not take the hit, so "> 0" also is the hit test (the reference tests gdist^2 > 0)
             const F2 hs = mk2(lo(gdist) > 0.0f ? lo(wd) * mufu_rcp(lo(gdist)) : 0.0f, hi(gdist) > 0.0f ? hi(wd) * mufu_rcp(hi(gdist)) : 0.0f);
             const F2 nkap = dgo * hs;                  // -kap
-            const F2 kd = -(nkap * dgo);               // s_i * sclHit_i = -kd * sg2_i
-            // grdHit_i = -kap (sg2_i go_i + dgo s_i sg_i) ; groHit_i = -kap sg2_i grd_i
-            F2x3 tH;
-            tH.x = fma(sg2.x, go.x, dgo * bc(S.x) * sg.x);
-            tH.y = fma(sg2.y, go.y, dgo * bc(S.y) * sg.y);
-            tH.z = fma(sg2.z, go.z, dgo * bc(S.z) * sg.z);
+            const F2 nd = nkap * dgo;                  // -kd, with s_i * sclHit_i = -kd * sg2_i
+            // groHit_i = -kap sg2_i grd_i ; grdHit_i = -kap (sg2_i go_i + dgo hv_i)
+            F2x3 mk;
+            mk.x = nkap * sg2.x; mk.y = nkap * sg2.y; mk.z = nkap * sg2.z;
 
             // opacity and colour terms (:569-633)
             const F2 resT = mk2(lo(alpha) < 0.999999f ? lo(st.T_f) * mufu_rcp(lo(om)) : lo(T),
                                 hi(alpha) < 0.999999f ? hi(st.T_f) * mufu_rcp(hi(om)) : hi(T));
             const F2 aDns = resT * st.dA;
             st.Crem.x = fma(-w, bc(F.x), st.Crem.x); st.Crem.y = fma(-w, bc(F.y), st.Crem.y); st.Crem.z = fma(-w, bc(F.z), st.Crem.z);
-            const F2 rx = st.Crem.x * invT, ry = st.Crem.y * invT, rz = st.Crem.z * invT;
-            const F2 resCx = mk2(fmaxf(lo(rx), 0.0f), fmaxf(hi(rx), 0.0f));
-            const F2 resCy = mk2(fmaxf(lo(ry), 0.0f), fmaxf(hi(ry), 0.0f));
-            const F2 resCz = mk2(fmaxf(lo(rz), 0.0f), fmaxf(hi(rz), 0.0f));
-            const F2 cs = fma(bc(F.z) - resCz, st.dC.z, fma(bc(F.y) - resCy, st.dC.y, (bc(F.x) - resCx) * st.dC.x));
-            const F2 Sall = fma(T, fma(dHit, st.dD, cs), aDns);
+            // residual colour max(Crem / nextT, 0) = invT max(Crem, 0) (invT >= 0):  sum_c (F_c - resC_c) dC_c = F.dC - invT (max(Crem, 0).dC)
+            const F2 mcx = mk2(fmaxf(lo(st.Crem.x), 0.0f), fmaxf(hi(st.Crem.x), 0.0f));
+            const F2 mcy = mk2(fmaxf(lo(st.Crem.y), 0.0f), fmaxf(hi(st.Crem.y), 0.0f));
+            const F2 mcz = mk2(fmaxf(lo(st.Crem.z), 0.0f), fmaxf(hi(st.Crem.z), 0.0f));
+            const F2 fdc = fma(bc(F.z), st.dC.z, fma(bc(F.y), st.dC.y, bc(F.x) * st.dC.x));
+            const F2 mdc = fma(mcz, st.dC.z, fma(mcy, st.dC.y, mcx * st.dC.x));
+            const F2 cs = fma(-invT, mdc, fdc);
+#ifndef GUT_BWD_SHUFFLE_REDUCE
+            prev = prev + shfl2(prev, 16);
+#endif
+            const F2 Sall = fma(T, fma(gdist, st.dD, cs), aDns);
             const F2 Ssum = mk2(h0 ? lo(Sall) : 0.0f, h1 ? hi(Sall) : 0.0f);
             const F2 dDens = k.resp * Ssum;
-            const F2 respG = bc(S.w) * Ssum;
             // g2 = |grd x go|^2 : adjoint of the cross product (:671-689); grd x go = c / |u|, so dL/d(grd x go) = c (2 g2G / |u|).
-            // Degree 2: g2G = -resp respG / 2, the factors 2 and -1/2 cancel
+            // Degree 2: g2G = -resp respG / 2 with respG = density Ssum: the factors 2 and -1/2 cancel and resp Ssum is dDens
             F2 gscale;
-            if (DEG == 2) gscale = -(k.resp * respG) * il;
-            else gscale = bc(2.0f) * mk2(kernel_response_grad<DEG>(lo(k.g2), lo(k.resp), lo(respG)), kernel_response_grad<DEG>(hi(k.g2), hi(k.resp), hi(respG))) * il;
+            if (DEG == 2) gscale = -(bc(S.w) * dDens) * il;
+            else {
+                const F2 respG = bc(S.w) * Ssum;
+                gscale = bc(2.0f) * mk2(kernel_response_grad<DEG>(lo(k.g2), lo(k.resp), lo(respG)), kernel_response_grad<DEG>(hi(k.g2), hi(k.resp), hi(respG))) * il;
+            }
             const F2x3 gcG = k.c * gscale;
             const F2x3 grdG = cross(go, gcG);
             const F2x3 groG = cross(gcG, grd);
             // A = dL/dgo (total), X = dL/dgrd (total)
             F2x3 Ag, X, Bg;
-            Ag.x = fma(nkap, sg2.x * grd.x, groG.x); Ag.y = fma(nkap, sg2.y * grd.y, groG.y); Ag.z = fma(nkap, sg2.z * grd.z, groG.z);
-            X.x = fma(nkap, tH.x, grdG.x); X.y = fma(nkap, tH.y, grdG.y); X.z = fma(nkap, tH.z, grdG.z);
+            Ag.x = fma(mk.x, grd.x, groG.x); Ag.y = fma(mk.y, grd.y, groG.y); Ag.z = fma(mk.z, grd.z, groG.z);
+            X.x = fma(mk.x, go.x, fma(nd, hv.x, grdG.x)); X.y = fma(mk.y, go.y, fma(nd, hv.y, grdG.y)); X.z = fma(mk.z, go.z, fma(nd, hv.z, grdG.z));
             // normalisation adjoint (safe_normalize_bw, mathUtils.cuh:420-430): B = dL/du = Y / |u| with Y = X - grd (grd . X).
             // Every use of B below but one is a product u_i B_j = grd_i Y_j, so Y is used directly and only the trace term
             // is divided by |u|.
             const F2 gx = dot(grd, X);
             Bg.x = fma(-grd.x, gx, X.x); Bg.y = fma(-grd.y, gx, X.y); Bg.z = fma(-grd.z, gx, X.z);   // = Y
 
-            // P_ij = go_i A_j + u_i B_j : diagonal -> scale, off-diagonal -> body-frame torque
+            // P_ij = go_i A_j + u_i B_j = go_i A_j + grd_i Y_j : diagonal -> scale, off-diagonal -> body-frame torque,
+            // tau_x = (s_z/s_y) P_zy - (s_y/s_z) P_yz = [(Y x hv)_x + (A x s^2 go)_x] / (s_y s_z), and cyclic.
+            // The go (x) A half is linear in A with a per-PARTICLE factor when every ray starts at the frame origin, and A is
+            // summed over the rays anyway (v[0..2]): K6 adds go_frame (x) sum(A) once per particle (gut_project.cu), and so
+            // for the trace and the scale terms; here only the part of go that differs per ray (dl = ms (ray origin - frame
+            // origin), non-UNIFORM rays) is left.  K6 also applies the 1 / (s_j s_k) of the torque.
+            const F2x3 tq = cross(Bg, hv);
             v[0] = (Ag.x); v[1] = (Ag.y); v[2] = (Ag.z);
             v[3] = (dDens);
-            v[4] = (fma(bc(R0.y), fma(go.z, Ag.y, grd.z * Bg.y), -(bc(R0.x) * fma(go.y, Ag.z, grd.y * Bg.z))));   // rho_zy P_zy - rho_yz P_yz
-            v[5] = (fma(bc(R0.z), fma(go.x, Ag.z, grd.x * Bg.z), -(bc(R0.w) * fma(go.z, Ag.x, grd.z * Bg.x))));   // rho_xz P_xz - rho_zx P_zx
-            v[6] = (fma(bc(R1.x), fma(go.y, Ag.x, grd.y * Bg.x), -(bc(R1.y) * fma(go.x, Ag.y, grd.x * Bg.y))));   // rho_yx P_yx - rho_xy P_xy
-            F2 tr = fma(bc(isz), Bg.z * ray.d.z, fma(bc(R1.w), Bg.y * ray.d.y, bc(R1.z) * (Bg.x * ray.d.x))) * il;   // sum_i B_i d_i / s_i
-            tr = fma(Ag.z, bc(R2.w), fma(Ag.y, bc(R2.z), fma(Ag.x, bc(R2.y), tr)));   // origin part: A . (frame origin - position) / s
-            if (!UNIFORM) tr = fma(bc(isz), Ag.z * ray.dlt.z, fma(bc(R1.w), Ag.y * ray.dlt.y, fma(bc(R1.z), Ag.x * ray.dlt.x, tr)));
+            v[4] = tq.x; v[5] = tq.y; v[6] = tq.z;
+            F2 tr = fma(bc(IS.z) * ray.d.z, Bg.z, fma(bc(IS.y) * ray.d.y, Bg.y, (bc(IS.x) * ray.d.x) * Bg.x)) * il;   // sum_i B_i d_i / s_i
+            const F2 kd = -nd;
+            v[8] = fma(kd, sg2.x, grd.x * Bg.x);
+            v[9] = fma(kd, sg2.y, grd.y * Bg.y);
+            v[10] = fma(kd, sg2.z, grd.z * Bg.z);
+            if (!UNIFORM) {
+                // dl = ms (ray origin - frame origin) = go - go_frame (the rounding of the difference is that of go itself)
+                F2x3 dl, gd;
+                dl.x = go.x - bc(A.w); dl.y = go.y - bc(B.w); dl.z = go.z - bc(Cm.w);
+                gd.x = bc(S2.x) * dl.x; gd.y = bc(S2.y) * dl.y; gd.z = bc(S2.z) * dl.z;
+                const F2x3 ta = cross(Ag, gd);
+                v[4] = v[4] + ta.x; v[5] = v[5] + ta.y; v[6] = v[6] + ta.z;
+                tr = fma(bc(IS.z), Ag.z * ray.dlt.z, fma(bc(IS.y), Ag.y * ray.dlt.y, fma(bc(IS.x), Ag.x * ray.dlt.x, tr)));
+                v[8] = fma(dl.x, Ag.x, v[8]); v[9] = fma(dl.y, Ag.y, v[9]); v[10] = fma(dl.z, Ag.z, v[10]);
+            }
             v[7] = (tr);
-            v[8] = (fma(go.x, Ag.x, fma(grd.x, Bg.x, kd * sg2.x)));
-            v[9] = (fma(go.y, Ag.y, fma(grd.y, Bg.y, kd * sg2.y)));
-            v[10] = (fma(go.z, Ag.z, fma(grd.z, Bg.z, kd * sg2.z)));
             v[11] = (w * st.dC.x); v[12] = (w * st.dC.y); v[13] = (w * st.dC.z);
-            v[14] = -(kd * ssum);
+            v[14] = nd * ssum;
             v[15] = bc(0.0f);
 
             st.T = nextT;
             if (lo(nextT) < minT) st.alive[0] = false;
             if (hi(nextT) < minT) st.alive[1] = false;
         }
-#ifndef GUT_BWD_SMEM_REDUCE
+#ifndef GUT_BWD_SHUFFLE_REDUCE
+        if (st.pending) reduce_commit(prev, lane, st.pending_idx, raw_grad);
+        __syncwarp();   // every lane has read the previous hit's rows
+        reduce_store(v, lane, tile);
+        __syncwarp();   // this hit's rows are visible to the next iteration's loads
+        st.pending = true;
+        st.pending_idx = __float_as_uint(F.w);
+#else
         const float total = warp_transpose_reduce(v, lane);
         const uint32_t slot = reduce_slot(lane);
         if ((lane & 1u) == 0u && slot < 15u) atomicAdd(raw_grad + 16 * (size_t)__float_as_uint(F.w) + slot, total);
-#else
-        const F2 total = warp_smem_reduce(v, lane, tile);
-        if (lane < 8u) {   // lane p adds values 2p and 2p + 1: one 64-bit vector reduction (value 15 is padding)
-            float* dst = raw_grad + 16 * (size_t)__float_as_uint(F.w) + 2 * lane;
-            if (lane < 7u) atomicAdd(reinterpret_cast<float2*>(dst), make_float2(lo(total), hi(total)));
-            else atomicAdd(dst, lo(total));
-        }
 #endif
       }
     }
@@ -568,7 +606,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     const float4* __restrict__ rgba, const float4* __restrict__ rgba_grad, const float* __restrict__ dist,
     const float* __restrict__ dist_grad, float* __restrict__ raw_grad, const uint32_t* __restrict__ hit_masks) {
     __shared__ __align__(16) unsigned char smem_raw[StageLayout<true>::TOTAL];
-#ifdef GUT_BWD_SMEM_REDUCE
+#ifndef GUT_BWD_SHUFFLE_REDUCE
     __shared__ __align__(16) float reduce_tile[REDUCE_TILE_BYTES / 4];
 #else
     float* const reduce_tile = nullptr;
@@ -603,6 +641,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
     st.Crem.x = mk2(Cf[0].x, Cf[1].x); st.Crem.y = mk2(Cf[0].y, Cf[1].y); st.Crem.z = mk2(Cf[0].z, Cf[1].z);
     st.dC.x = mk2(dC[0].x, dC[1].x); st.dC.y = mk2(dC[0].y, dC[1].y); st.dC.z = mk2(dC[0].z, dC[1].z);
     st.T = bc(1.0f);
+    st.pending = false; st.pending_idx = 0u;
 
     const uint32_t b0 = tile_start[tile], b1 = tile_start[tile + 1];
     WarpStager<true> stg;
@@ -615,6 +654,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
         if (!__any_sync(0xffffffffu, st.alive[0] || st.alive[1])) break;
         stg.rotate();
     }
+#ifndef GUT_BWD_SHUFFLE_REDUCE
+    if (st.pending) reduce_commit(reduce_finish(reduce_load(lane, reduce_tile)), lane, st.pending_idx, raw_grad);   // the last hit
+#endif
     stg.drain();
 }
 

@@ -150,11 +150,10 @@ struct WarpStager {
             out[2] = make_float4(m2.x, m2.y, m2.z, dot(m2, v));
             out[3] = make_float4(r2.x, r2.y, r2.z, r0.w);
             out[4] = make_float4(fmaxf(ft.x, 0.0f), fmaxf(ft.y, 0.0f), fmaxf(ft.z, 0.0f), __uint_as_float(p_cur));
-            if (BWD) {   // scale ratios s_i / s_j of the body-frame torque, and 1 / s
-                float4* outb = recb + 3 * lane;
-                outb[0] = make_float4(r2.y * iz, r2.z * iy, r2.x * iz, r2.z * ix);
-                outb[1] = make_float4(r2.y * ix, r2.x * iy, ix, iy);
-                outb[2] = make_float4(iz, v.x * ix, v.y * iy, v.z * iz);   // 1/s_z | (frame origin - position) / s
+            if (BWD) {   // 1 / s and s^2
+                float4* outb = recb + 2 * lane;
+                outb[0] = make_float4(ix, iy, iz, 0.0f);
+                outb[1] = make_float4(r2.x * r2.x, r2.y * r2.y, r2.z * r2.z, 0.0f);
             }
         } else if (lane < cnt_pad) {
             out[0] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);

@@ -239,7 +239,7 @@ struct BwdStateK {
 // leave their buffers with different particles most of the time (5.7 distinct particles per pop event of a warp at
 // the bench workload), and one reduction per distinct particle was 44 % of this kernel's instructions.
 template <int DEG>
-GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 o, const float3 d,
+GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, const float3 centre, const float3 o, const float3 d,
                            float t, float alpha, uint32_t p, BwdStateK& st, float* __restrict__ raw_grad) {
     if (alpha > 0.0f) {
         float v[15];
@@ -291,16 +291,22 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
         const float3 X = f3(grdG.x - kap * fmaf(dgo * r2.x, sg.x, ssum * go.x), grdG.y - kap * fmaf(dgo * r2.y, sg.y, ssum * go.y),
                             grdG.z - kap * fmaf(dgo * r2.z, sg.z, ssum * go.z));
         const float gx = dot(grd, X);
-        const float3 Bg = f3(il * (X.x - grd.x * gx), il * (X.y - grd.y * gx), il * (X.z - grd.z * gx));
+        const float3 Y = f3(X.x - grd.x * gx, X.y - grd.y * gx, X.z - grd.z * gx);   // |u| dL/du
+        // The accumulators follow gut_render.cu's backward_walk: K6 adds the halves of the torque, the trace and the scale
+        // terms that are go_frame (x) sum(A) (origin fold, gut_project.cu) and scales the torque by 1 / (s_j s_k); a ray adds
+        // the direction halves and what its own origin contributes beyond the frame origin (dl = ms (o - frame origin)).
+        const float3 dlt = o - centre;
+        const float3 dl = f3(dot(m0, dlt), dot(m1, dlt), dot(m2, dlt));
+        const float3 hv = f3(r2.x * sg.x, r2.y * sg.y, r2.z * sg.z);                       // s^2 grd
+        const float3 gd = f3(r2.x * r2.x * dl.x, r2.y * r2.y * dl.y, r2.z * r2.z * dl.z);  // s^2 dl
+        const float3 tq = cross(Y, hv) + cross(Ag, gd);
         v[0] = Ag.x; v[1] = Ag.y; v[2] = Ag.z;
         v[3] = dDens;
-        v[4] = (r2.z * iy) * fmaf(go.z, Ag.y, u.z * Bg.y) - (r2.y * iz) * fmaf(go.y, Ag.z, u.y * Bg.z);
-        v[5] = (r2.x * iz) * fmaf(go.x, Ag.z, u.x * Bg.z) - (r2.z * ix) * fmaf(go.z, Ag.x, u.z * Bg.x);
-        v[6] = (r2.y * ix) * fmaf(go.y, Ag.x, u.y * Bg.x) - (r2.x * iy) * fmaf(go.x, Ag.y, u.x * Bg.y);
-        v[7] = ix * (Bg.x * d.x + Ag.x * rel.x) + iy * (Bg.y * d.y + Ag.y * rel.y) + iz * (Bg.z * d.z + Ag.z * rel.z);
-        v[8] = fmaf(go.x, Ag.x, fmaf(u.x, Bg.x, kd * sg2.x));
-        v[9] = fmaf(go.y, Ag.y, fmaf(u.y, Bg.y, kd * sg2.y));
-        v[10] = fmaf(go.z, Ag.z, fmaf(u.z, Bg.z, kd * sg2.z));
+        v[4] = tq.x; v[5] = tq.y; v[6] = tq.z;
+        v[7] = il * (ix * (Y.x * d.x) + iy * (Y.y * d.y) + iz * (Y.z * d.z)) + (ix * (Ag.x * dlt.x) + iy * (Ag.y * dlt.y) + iz * (Ag.z * dlt.z));
+        v[8] = fmaf(dl.x, Ag.x, fmaf(grd.x, Y.x, kd * sg2.x));
+        v[9] = fmaf(dl.y, Ag.y, fmaf(grd.y, Y.y, kd * sg2.y));
+        v[10] = fmaf(dl.z, Ag.z, fmaf(grd.z, Y.z, kd * sg2.z));
         v[11] = fgrad.x; v[12] = fgrad.y; v[13] = fgrad.z;
         v[14] = -kd * ssum;
     // Rays of a block leave their buffers with DIFFERENT particles most of the time (measured: 5.7 distinct particles per
@@ -359,7 +365,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
             const bool need = hit && kb.full();
             if (need) {
                 const uint32_t o = kb.front_slot() * 32u + lane;
-                process_hit_bwd<DEG>(cfg, src, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
+                process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
             }
             if (hit) {
                 const uint32_t slot = kb.insert(t);
@@ -374,7 +380,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) gut_render_kbuffer_backward_ke
     for (int i = 0; i < K; ++i) {
         if (st.alive && kb.key[i] != 0u) {
             const uint32_t o = (kb.key[i] & KB_SLOT_MASK) * 32u + lane;
-            process_hit_bwd<DEG>(cfg, src, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
+            process_hit_bwd<DEG>(cfg, src, fr.cam_centre, ray.o, ray.d, pay.t[o], pay.a[o], pay.p[o], st, raw_grad);
         }
     }
 }

@@ -447,7 +447,9 @@ def test_multi_view_step_equals_per_view_render(fused, nonleaf):
         assert torch.equal(a, b)
     for pa, pb in zip(params(ga), params(gb)):
         assert pb.grad is not None and pa.grad.shape == pb.grad.shape
-        assert rel_l2(pb.grad.cpu().numpy(), pa.grad.cpu().numpy()) <= 2e-5
+        # two summation orders of the same fp32 terms.  The rotation gradient is the difference of two large halves (origin
+        # fold, gut_project.cu) that are summed over the views separately in one order and per view in the other: 1e-4
+        assert rel_l2(pb.grad.cpu().numpy(), pa.grad.cpu().numpy()) <= 1e-4
     assert vis is not None and 0 < float(vis.sum()) <= n
     # protocol errors: a second render before the backward, render after finish
     step2 = tracer.begin_step(model(), views_per_rank=nv)
