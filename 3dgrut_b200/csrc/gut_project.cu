@@ -364,16 +364,17 @@ constexpr int K6_WARPS = K6_THREADS / 32;
 
 // The "origin fold": K5 leaves out the go (x) A halves of the torque, the trace and the scale terms when go is the same
 // for every ray of the view (gut_render.cu, backward_walk).  With A summed over the view's rays they are
-//   tau' += A x (s^2 go) = A x (s * R^T v),   tr += sum_i A_i v_i / s_i,   Z_i += go_i A_i,      v = view centre - position,
+//   tau' += A x (s^2 go) = A x (s * R^T v),   tr += sum_i A_i v_i / s_i,   Z_i += go_i A_i,   W += go . A,      v = view centre - position,
 // go = diag(1/s) R^T v.  c0..c2 are the columns of R, is = 1 / s.
 GUT_D void origin_fold(const float3 A, const float3 v, const float3 c0, const float3 c1, const float3 c2, const float3 sc,
-                       const float3 is, float3& tq, float& tr, float3& Z) {
+                       const float3 is, float3& tq, float& tr, float3& Z, float& W) {
     const float3 rv = f3(dot(c0, v), dot(c1, v), dot(c2, v));
     const float3 go = rv * is;
     const float3 G = sc * rv;
     tq = tq + cross(A, G);
     tr = tr + (A.x * (v.x * is.x) + A.y * (v.y * is.y) + A.z * (v.z * is.z));
     Z = Z + go * A;
+    W = W + dot(go, A);
 }
 
 // Phase A: one thread per particle computes the [N,12] gradient row and the masked colour gradient + SH basis.
@@ -430,7 +431,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
         float3 tq = f3(g1.x, g1.y, g1.z);
         float tr_dir = g1.w;
         float3 Z = f3(g2.x, g2.y, g2.z);
-        const float W = g3.z;
+        float W = g3.z;   // sum_i P_ii (the trace of dL/dR^T R^T)
         const float3 is = f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z);
         float3 c0, c1, c2;
         quat_to_columns(qv.x, qv.y, qv.z, qv.w, c0, c1, c2);
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
             A = f3(as.x, as.y, as.z);
             if (as.x != 0.0f || as.y != 0.0f || as.z != 0.0f) a_sum[i] = z;
         } else {
-            origin_fold(A, fr.cam_centre - f3(r0.x, r0.y, r0.z), c0, c1, c2, f3(r2.x, r2.y, r2.z), is, tq, tr_dir, Z);
+            origin_fold(A, fr.cam_centre - f3(r0.x, r0.y, r0.z), c0, c1, c2, f3(r2.x, r2.y, r2.z), is, tq, tr_dir, Z, W);
         }
         const float3 tau = f3(tq.x * (is.y * is.z), tq.y * (is.x * is.z), tq.z * (is.x * is.y));
         const float3 As = A * is;
@@ -447,8 +448,9 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
         o0 = make_float4(-(c0.x * As.x + c1.x * As.y + c2.x * As.z), -(c0.y * As.x + c1.y * As.y + c2.y * As.z),
                          -(c0.z * As.x + c1.z * As.y + c2.z * As.z), g0.w);
         o2 = make_float4(-Z.x * is.x, -Z.y * is.y, -Z.z * is.z, 0.0f);
-        // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = sum Z + W ; the trace is summed per ray by K5
-        const float rho = 2.0f * ((Z.x + Z.y + Z.z + W) - tr_dir);
+        // radial part: q . dL/dq = 2 <dL/dR^T, R^T - I> ; <dL/dR^T, R^T> = sum_i P_ii = go . A (W: origin fold, the direction
+        // half u . B vanishes) ; <dL/dR^T, I> = tr (direction half summed per ray by K5, origin half from the fold)
+        const float rho = 2.0f * (W - tr_dir);
         // tangential part: body-frame torque -> 2 q (x) (0, tau)
         const float3 rv = f3(qv.y, qv.z, qv.w);
         const float3 rxt = cross(rv, tau);
@@ -572,6 +574,7 @@ __global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 c
     const float4 ft = __ldg(features + i);
     const float3 g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
     float3 Z = f3(g2.x, g2.y, g2.z);
+    float W = g3.z;
     const bool moved = a.x != 0.0f || a.y != 0.0f || a.z != 0.0f;
     if (moved) {   // second round trip for the particles the view's rays pushed on
         const float4 r0 = __ldg(density12 + 3 * (size_t)i), qv = __ldg(density12 + 3 * (size_t)i + 1), r2 = __ldg(density12 + 3 * (size_t)i + 2);
@@ -581,13 +584,13 @@ __global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 c
         float3 tq = f3(g1.x, g1.y, g1.z);
         float tr = g1.w;
         origin_fold(f3(a.x, a.y, a.z), centre - f3(r0.x, r0.y, r0.z), c0, c1, c2, f3(r2.x, r2.y, r2.z),
-                    f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z), tq, tr, Z);
+                    f3(1.0f / r2.x, 1.0f / r2.y, 1.0f / r2.z), tq, tr, Z, W);
         rg[1] = make_float4(tq.x, tq.y, tq.z, tr);
         a_sum[i] = make_float4(as.x + a.x, as.y + a.y, as.z + a.z, 0.0f);
         rg[0] = make_float4(0.0f, 0.0f, 0.0f, a.w);
     }
     if (moved || g2.w != 0.0f) rg[2] = make_float4(Z.x, Z.y, Z.z, 0.0f);
-    if (g3.x != 0.0f || g3.y != 0.0f) rg[3] = make_float4(0.0f, 0.0f, g3.z, g3.w);
+    if (moved || g3.x != 0.0f || g3.y != 0.0f) rg[3] = make_float4(0.0f, 0.0f, W, g3.w);
     colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z;
 }
 

@@ -409,11 +409,12 @@ GUT_D F2 reduce_finish(F2 t) {
     return t;
 }
 // lane p < 8 adds values 2p and 2p + 1 of particle `idx`: one 64-bit vector reduction (value 15 is padding)
-GUT_D void reduce_commit(F2 total, uint32_t lane, uint32_t idx, float* __restrict__ raw_grad) {
+// (value 14 is zero when every ray starts at the frame origin: with14 = false skips its reduction)
+GUT_D void reduce_commit(F2 total, uint32_t lane, uint32_t idx, float* __restrict__ raw_grad, bool with14) {
     if (lane < 8u) {
         float* dst = raw_grad + 16 * (size_t)idx + 2 * lane;
         if (lane < 7u) atomicAdd(reinterpret_cast<float2*>(dst), make_float2(lo(total), hi(total)));
-        else atomicAdd(dst, lo(total));
+        else if (with14) atomicAdd(dst, lo(total));
     }
 }
 
@@ -436,7 +437,7 @@ struct BwdRay {
 //   [7]     tr  = sum_i (dL/dR^T)_ii, direction half                -> rho (radial part of dL/dquat, R(q) is a polynomial)
 //   [8..10] Z_i = u_i B_i - s_i * (hit-distance term)  [+ go_i A_i]  -> dL/dscale_i = -Z_i / s_i
 //   [11..13] dL/d colour
-//   [14]    W   = sum_i s_i * (hit-distance scale term)             -> rho
+//   [14]    sum_i P_ii = go . A  (the direction half u . B vanishes)  -> rho
 // with B = dL/d u.  This is the chain rule of processHitBwd (gaussianParticles.cuh:635-738) with the per-ray
 // quaternion / matrix products (matmul_bw_quat, matmul_bw_vec) factored out of the ray loop.  tau, tr and Z each have a
 // half that is go (x) A: with all rays starting at the frame origin go is a per-particle constant, so that half is
@@ -561,6 +562,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             v[8] = fma(kd, sg2.x, grd.x * Bg.x);
             v[9] = fma(kd, sg2.y, grd.y * Bg.y);
             v[10] = fma(kd, sg2.z, grd.z * Bg.z);
+            F2 v14 = bc(0.0f);
             if (!UNIFORM) {
                 // dl = ms (ray origin - frame origin) = go - go_frame (the rounding of the difference is that of go itself)
                 F2x3 dl, gd;
@@ -570,10 +572,13 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
                 v[4] = v[4] + ta.x; v[5] = v[5] + ta.y; v[6] = v[6] + ta.z;
                 tr = fma(bc(IS.z), Ag.z * ray.dlt.z, fma(bc(IS.y), Ag.y * ray.dlt.y, fma(bc(IS.x), Ag.x * ray.dlt.x, tr)));
                 v[8] = fma(dl.x, Ag.x, v[8]); v[9] = fma(dl.y, Ag.y, v[9]); v[10] = fma(dl.z, Ag.z, v[10]);
+                v14 = dot(dl, Ag);
             }
             v[7] = (tr);
             v[11] = (w * st.dC.x); v[12] = (w * st.dC.y); v[13] = (w * st.dC.z);
-            v[14] = nd * ssum;
+            // [14]: sum_i P_ii = go . A + grd . Y, and grd . Y = 0 (Y is X minus its component along the unit vector grd): only
+            // the part of go . A that differs per ray is left; K6's origin fold adds go_frame . sum(A)
+            v[14] = UNIFORM ? bc(0.0f) : v14;
             v[15] = bc(0.0f);
 
             st.T = nextT;
@@ -581,7 +586,7 @@ GUT_D void backward_walk(const GutConfig& cfg, const float4* __restrict__ rec, c
             if (hi(nextT) < minT) st.alive[1] = false;
         }
 #ifndef GUT_BWD_SHUFFLE_REDUCE
-        if (st.pending) reduce_commit(prev, lane, st.pending_idx, raw_grad);
+        if (st.pending) reduce_commit(prev, lane, st.pending_idx, raw_grad, !UNIFORM);
         __syncwarp();   // every lane has read the previous hit's rows
         reduce_store(v, lane, tile);
         __syncwarp();   // this hit's rows are visible to the next iteration's loads
@@ -655,7 +660,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GUT_BWD_MIN_BLOCKS) gut_render
         stg.rotate();
     }
 #ifndef GUT_BWD_SHUFFLE_REDUCE
-    if (st.pending) reduce_commit(reduce_finish(reduce_load(lane, reduce_tile)), lane, st.pending_idx, raw_grad);   // the last hit
+    if (st.pending) reduce_commit(reduce_finish(reduce_load(lane, reduce_tile)), lane, st.pending_idx, raw_grad, !UNIFORM);   // the last hit
 #endif
     stg.drain();
 }

@@ -308,7 +308,7 @@ GUT_D void process_hit_bwd(const GutConfig& cfg, const GutParticleSource& src, c
         v[9] = fmaf(dl.y, Ag.y, fmaf(grd.y, Y.y, kd * sg2.y));
         v[10] = fmaf(dl.z, Ag.z, fmaf(grd.z, Y.z, kd * sg2.z));
         v[11] = fgrad.x; v[12] = fgrad.y; v[13] = fgrad.z;
-        v[14] = -kd * ssum;
+        v[14] = dot(dl, Ag);   // per-ray part of go . A; the direction half of the trace vanishes (gut_render.cu)
     // Rays of a block leave their buffers with DIFFERENT particles most of the time (measured: 5.7 distinct particles per
     // pop event of a warp at the bench workload), so a warp reduction per distinct particle costs more than it saves
     // (it was 44 % of the kernel's instructions).  Each lane adds its 15 values itself with four 128-bit vector
