@@ -166,6 +166,9 @@ GutFrame make_frame(const GutConfig& cfg, const GutCamera& cam, uint32_t W, uint
     const float3 tm = f3(p0[0] * (1.0f - 0.5f) + p1[0] * 0.5f, p0[1] * (1.0f - 0.5f) + p1[1] * 0.5f, p0[2] * (1.0f - 0.5f) + p1[2] * 0.5f);
     quat_cols(qm, f.view.c[0], f.view.c[1], f.view.c[2]);
     f.view.c[3] = tm;
+    // shutter-start pose as a matrix (the same quat_to_columns the kernel would run, in the same IEEE arithmetic)
+    quat_cols(HQuat{p0[6], p0[3], p0[4], p0[5]}, f.start.c[0], f.start.c[1], f.start.c[2]);
+    f.start.c[3] = f3(p0[0], p0[1], p0[2]);
     // inverse pose: transpose -> quaternion -> matrix round trip, exactly as sensorPoseInverse + sensorPoseToMat do
     const float3 r0 = f.view.c[0], r1 = f.view.c[1], r2 = f.view.c[2];
     const float3 i0 = f3(r0.x, r1.x, r2.x), i1 = f3(r0.y, r1.y, r2.y), i2 = f3(r0.z, r1.z, r2.z);

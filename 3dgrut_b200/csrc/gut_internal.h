@@ -14,6 +14,7 @@ struct GutFrame {
     uint32_t num_tiles;
     GutMat4x3 view;             // world -> sensor at the mid-shutter pose (depth ordering, z cull)
     GutMat4x3 c2w;              // sensor -> world at the mid-shutter pose (ray set-up)
+    GutMat4x3 start;            // world -> sensor at the shutter-START pose: what every sigma point of K1 is projected with first
     float3 cam_centre;          // sensor position in world space (SH view direction)
     float ut_delta;             // sqrt(alpha^2 (3 + kappa)), narrowed from double (setup_3dgut.py:45)
 };

@@ -22,7 +22,16 @@ base = int(body[0][0], 16)
 per_addr = {int(r[0], 16) - base: (int(r[iex]), int(r[ismp] or 0), r[isrc]) for r in body}
 
 # nvdisasm -g: "//## File "path", line N" comments precede the instructions they belong to; functions start at ".text.<name>:"
-dis = subprocess.run(["nvdisasm", "-g", "-c", obj], capture_output=True, text=True).stdout
+# a host object holds the cubin as a fat-binary member: extract it first
+import glob, os, tempfile
+cubin = obj
+if not obj.endswith(".cubin"):
+    tmp = tempfile.mkdtemp(prefix="ncu_by_line_")
+    subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, capture_output=True)
+    found = glob.glob(os.path.join(tmp, "*.cubin"))
+    assert found, f"no cubin inside {obj}"
+    cubin = found[0]
+dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout
 line_of, cur, infn = {}, None, False
 fn_re = re.compile(r"^\s*\.text\.(\S+):")
 for l in dis.splitlines():
