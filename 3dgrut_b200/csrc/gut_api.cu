@@ -462,7 +462,8 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
                                                    (float*)h->raw_grad.p, (const uint32_t*)h->hit_masks.p, s));
         h->launches += 1;
     }
-    if (d_colour_grad && ((size_t)N * 16 > h->a_sum.cap || !h->a_sum.p)) {
+    const bool deferred_view = d_colour_grad && !d_density_grad;
+    if (deferred_view && ((size_t)N * 16 > h->a_sum.cap || !h->a_sum.p)) {
         GUT_CUDA(h, ensure(h->a_sum, (size_t)N * 16, s));
         GUT_CUDA(h, cudaMemsetAsync(h->a_sum.p, 0, h->a_sum.cap, s));
     }
@@ -470,7 +471,7 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
         StageTimer t(h, ST_BWD_PROJECT, s);
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
                                                 (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad,
-                                                d_colour_grad, d_colour_grad ? (float*)h->a_sum.p : nullptr, accumulate, s));
+                                                d_colour_grad, deferred_view ? (float*)h->a_sum.p : nullptr, accumulate, s));
         h->launches += 1;
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
@@ -498,6 +499,21 @@ int gut_backward_colour(GutHandle* h, void* stream_, const GutCamera* camera, ui
         if (view_centre_out) {
             view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
         }
+    }
+    return rc;
+}
+
+int gut_backward_colour_density(GutHandle* h, void* stream_, const GutCamera* camera, uint32_t N, int32_t sph_degree, const float* d_density,
+                                const float* d_radiance, uint32_t W, uint32_t H, const float* d_ray_ori, const float* d_ray_dir, const float* d_rgba,
+                                const float* d_rgba_grad, const float* d_dist, const float* d_dist_grad, float* d_density_grad,
+                                float* d_colour_grad, float* view_centre_out, int32_t accumulate) {
+    if (h && N > 0 && (!d_colour_grad || !d_density_grad)) return fail(h, GUT_ERR_BAD_INPUT, "null gradient pointer");
+    if (h && h->pending_density)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_backward_colour_density after gut_backward_colour: call gut_density_gradient_finish (or gut_reset_gradients) first");
+    int rc = backward_impl(h, stream_, camera, N, sph_degree, d_density, d_radiance, W, H, d_ray_ori, d_ray_dir, d_rgba, d_rgba_grad, d_dist,
+                           d_dist_grad, d_density_grad, nullptr, d_colour_grad, accumulate);
+    if (rc == GUT_OK && view_centre_out) {
+        view_centre_out[0] = h->fwd_frame.cam_centre.x; view_centre_out[1] = h->fwd_frame.cam_centre.y; view_centre_out[2] = h->fwd_frame.cam_centre.z;
     }
     return rc;
 }

@@ -277,6 +277,14 @@ __global__ void __launch_bounds__(256, ROLLING ? GUT_K1_MIN_BLOCKS : GUT_K1_MIN_
     const bool valid_conic = valid_proj && conic_extent(cfg, cov, opacity, extent, co, max_power);
     // reference stores int 1 into float storage (gutProjector.cuh:275); 1.0f has the same truthiness and survives FTZ
     if (in_range) visibility[i] = valid_conic ? 1.0f : 0.0f;
+#ifndef GUT_K1_NO_SH_PREFETCH
+    // the SH row (192 B) is read after the tile walk, by the particles that kept a tile: start it towards L2 now
+    if (valid_conic) {
+        const char* row = reinterpret_cast<const char*>(sph + (size_t)i * ((cfg.sph_max_degree + 1) * (cfg.sph_max_degree + 1)) * 3);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 128));
+    }
+#endif
 
     // Tile walk (gutProjector.cuh:284-322), warp-cooperative: box sizes differ a lot between neighbouring particles, so the
     // boxes of the warp's 32 particles are flattened into one list of (particle, tile) items and every lane tests one item

@@ -114,6 +114,12 @@ class DeferredExchange:
         """[N,3] buffer that receives the masked colour gradient of this rank's view i (gut_backward_colour)."""
         return self.colour_all[self.local_slot(self._rank, i)]
 
+    def density_out(self, i):
+        """[N,12] buffer the backward of view i may write its gradient into directly (gut_backward_colour_density), or None.
+        A rank that renders ONE view per step has nothing to sum over views: its backward converts the accumulators itself
+        and the step needs neither the per-view fold pass nor gut_density_gradient_finish."""
+        return self.density_grad if self.views_per_rank == 1 else None
+
     def add_view(self, centre, visibility=None):
         """Record a finished view: the world-space view centre its backward used and (optionally) its mog_visibility."""
         self._centres.append([float(c) for c in centre])
@@ -126,7 +132,10 @@ class DeferredExchange:
         lo = self.local_slot(self._rank, 0)
         mine = self.colour_all[lo:lo + self.views_per_rank]
         centres = list(self._centres)
-        raster.density_gradient_finish(particle_density, self.density_grad)   # zeros when this rank had no view
+        if self.views_per_rank > 1:
+            raster.density_gradient_finish(particle_density, self.density_grad)   # zeros when this rank had no view
+        elif not centres:
+            self.density_grad.zero_()   # one view per rank and none for this rank in this step
         for i in range(len(centres), self.views_per_rank):
             mine[i].zero_()
             centres.append([0.0, 0.0, 0.0])
@@ -157,7 +166,7 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
                                               v["camera"])
         c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
-                                    rgba, rg, dist_, dg, ex.slot(i))
+                                    rgba, rg, dist_, dg, ex.slot(i), out_density_grad=ex.density_out(i))
         ex.add_view(c, vis)
         outs.append((rgba, dist_))
     ex.finish_step(raster, sph_degree, particle_density)
@@ -226,6 +235,7 @@ class PeerExchange(DeferredExchange):
         self.n_particles = n_particles
         self.my_centres = torch.zeros((views_per_rank, 3), dtype=torch.float32, device=device)
         self.step = 0
+        self.profile, self._marks = None, []
         if self.world > 1:
             dist.barrier()       # every rank has mapped every buffer before anyone writes
 
@@ -247,8 +257,34 @@ class PeerExchange(DeferredExchange):
     def slot(self, i):
         return self.slot_tensor(self._set, i)
 
+    def _mark(self, name):
+        """Optional phase timing of finish_step (``self.profile = {}`` switches it on): CUDA events on the compute stream."""
+        if self.profile is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._marks.append((name, ev))
+
+    def phase_times(self):
+        """Mean milliseconds per phase of finish_step since the last call (needs ``profile``); synchronises."""
+        torch.cuda.synchronize()
+        self._fold_marks()
+        out = {k: sum(v) / len(v) for k, v in (self.profile or {}).items() if v}
+        if self.profile is not None:
+            self.profile.clear()
+        return out
+
+    def _fold_marks(self):
+        if self.profile is not None:
+            for (_n0, e0), (n1, e1) in zip(self._marks[:-1], self._marks[1:]):
+                self.profile.setdefault(n1, []).append(e0.elapsed_time(e1))
+        self._marks = []
+
     def finish_step(self, raster, sph_degree, particle_density):
         s = self._set
+        if self.profile is not None and self._marks:     # fold the previous step's events into the sums
+            torch.cuda.synchronize()
+            self._fold_marks()
+        self._mark("start")
         centres = list(self._centres)
         for i in range(len(centres), self.views_per_rank):
             self.slot_tensor(s, i).zero_()
@@ -260,17 +296,24 @@ class PeerExchange(DeferredExchange):
             gathered = dist.all_gather_into_tensor(self.centres_all.view(-1), self.my_centres.view(-1), async_op=True)
         else:
             self.centres_all.copy_(self.my_centres)
-        raster.density_gradient_finish(particle_density, self.density_grad)       # overlaps the ordering point
+        if self.views_per_rank > 1:
+            raster.density_gradient_finish(particle_density, self.density_grad)   # overlaps the ordering point
+        elif not self._centres:
+            self.density_grad.zero_()   # one view per rank and none for this rank in this step
+        self._mark("density_finish")
         if self.world > 1:
             reduced = [dist.all_reduce(self.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
             if self.track_visibility:   # union of the ranks' visibilities, 4 B/particle
                 reduced.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
             gathered.wait()
+        self._mark("wait_for_all_ranks")
         ptrs = [self.slot_ptr(r, s, i) for r in range(self.world) for i in range(self.views_per_rank)]
         raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, ptrs, self.radiance_grad, accumulate=False)
+        self._mark("sh_expand_gather")
         if reduced is not None:
             for work in reduced:
                 work.wait()
+        self._mark("allreduce_remainder")
         return self.density_grad, self.radiance_grad
 
     def close(self):

@@ -66,6 +66,9 @@ def load_library():
     lib.gut_backward_colour.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp,
                                         C.POINTER(C.c_float)]
     lib.gut_backward_colour.restype = C.c_int
+    lib.gut_backward_colour_density.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp, fp, fp,
+                                                C.POINTER(C.c_float), i32]
+    lib.gut_backward_colour_density.restype = C.c_int
     lib.gut_set_training.argtypes = [vp, i32]
     lib.gut_set_training.restype = C.c_int
     lib.gut_set_block_cull.argtypes = [vp, i32]
@@ -302,10 +305,13 @@ class SplatRaster:
         return out_density_grad, out_radiance_grad
 
     def trace_bwd_colour(self, num_active_features, particle_density, particle_radiance, ray_origin, ray_direction, sensor: abi.GutCamera,
-                         ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad, out_colour_grad):
+                         ray_radiance_density, ray_radiance_density_grad, ray_hit_distance, ray_hit_distance_grad, out_colour_grad,
+                         out_density_grad=None, accumulate=False):
         """gut_backward_colour: traceBwd of one view of a deferred step.  Writes the view's masked colour gradient into
         ``out_colour_grad`` [N,3], keeps summing the density-part accumulators inside the handle (``density_gradient_finish``
-        converts them once per step) and returns the world-space view centre (3 floats) ``sh_gradient_expand`` needs."""
+        converts them once per step) and returns the world-space view centre (3 floats) ``sh_gradient_expand`` needs.
+        With ``out_density_grad`` [N,12] (gut_backward_colour_density: the handle's only view of the step) the view's [N,12]
+        gradient is written at once and nothing is left pending."""
         dev = self.device
         dens = _check_cuda_f32("particle_density", particle_density, dev)
         rad = _check_cuda_f32("particle_radiance", particle_radiance, dev)
@@ -322,9 +328,17 @@ class SplatRaster:
         if out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
             raise GutError(abi.GutStatus.BAD_INPUT, "out_colour_grad must be a contiguous [N,3]")
         centre = (C.c_float * 3)()
-        rc = self.lib.gut_backward_colour(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
-                                          width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
-                                          _ptr(out_colour_grad), centre)
+        if out_density_grad is not None:
+            if out_density_grad.shape != (n, 12) or not out_density_grad.is_contiguous():
+                raise GutError(abi.GutStatus.BAD_INPUT, "out_density_grad must be a contiguous [N,12]")
+            rc = self.lib.gut_backward_colour_density(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens),
+                                                      _ptr(rad), width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist),
+                                                      _ptr(dist_g), _ptr(out_density_grad), _ptr(out_colour_grad), centre,
+                                                      1 if accumulate else 0)
+        else:
+            rc = self.lib.gut_backward_colour(self._h, self._stream(), C.byref(sensor), n, int(num_active_features), _ptr(dens), _ptr(rad),
+                                              width, height, _ptr(ro), _ptr(rd), _ptr(rgba), _ptr(rgba_g), _ptr(dist), _ptr(dist_g),
+                                              _ptr(out_colour_grad), centre)
         if rc != 0:
             self._raise(rc)
         return [centre[0], centre[1], centre[2]]

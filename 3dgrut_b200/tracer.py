@@ -331,7 +331,8 @@ class TracerStep:
             raise RuntimeError(f"backward of view {i} after another view was rendered: its forward context is gone")
         w = self.tracer.tracer_wrapper
         c = w.trace_bwd_colour(self.n_active_features, self.particle_density, self.particle_radiance, ray_ori, ray_dir, sensor,
-                               rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous(), self.exchange.slot(i))
+                               rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous(), self.exchange.slot(i),
+                               out_density_grad=self.exchange.density_out(i))
         self.exchange.add_view(c, vis)
         self.n_backward += 1
         self._open = None
@@ -343,6 +344,9 @@ class TracerStep:
             raise RuntimeError("TracerStep.finish called twice")
         if self._open is not None:     # a view rendered without a backward contributes nothing: drop its slot
             self.exchange.slot(self._open).zero_()
+            direct = self.exchange.density_out(self._open)
+            if direct is not None:     # one view per rank: no backward wrote the step's [N,12] gradient
+                direct.zero_()
             self.exchange.add_view([0.0, 0.0, 0.0], None)
             self._open = None
         self.finished = True

@@ -368,6 +368,24 @@ def run_ours(args):
     ms_total = float(t.item())
     launches = raster.frame_stats()["kernel_launches"] - launches0
     stage_ms = raster.stage_times()
+    # what a step spends outside its views' kernels (gradient conversion, exchange, waiting for the slowest rank): the step time
+    # minus this rank's per-view stage times; and, untimed, three more steps with CUDA events between the phases of the exchange
+    step_tail_ms = ms_total / args.steps - len(views) * sum(stage_ms.values())
+    exchange_phases = None
+    if hasattr(exchange, "phase_times"):
+        exchange.profile = {}
+        for _ in range(3):
+            step()
+        exchange_phases = exchange.phase_times()
+        exchange.profile = None
+        raster.stage_times()
+    if world > 1:
+        tails = [None] * world
+        dist.all_gather_object(tails, {"rank": rank, "views": len(views), "views_ms": len(views) * sum(stage_ms.values()),
+                                       "tail_ms": step_tail_ms, "exchange_phases_ms": exchange_phases})
+    else:
+        tails = [{"rank": 0, "views": len(views), "views_ms": len(views) * sum(stage_ms.values()), "tail_ms": step_tail_ms,
+                  "exchange_phases_ms": exchange_phases}]
     stats = raster.frame_stats()
     value = args.views * P * args.steps / (ms_total * 1e-3) / 1e6
 
@@ -722,7 +740,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "step_breakdown": tails,
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,

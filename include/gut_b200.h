@@ -240,6 +240,17 @@ GUT_API int gut_backward_colour(GutHandle* h, void* stream, const GutCamera* cam
                  const float* d_ray_radiance_density, const float* d_ray_radiance_density_grad,
                  const float* d_ray_hit_distance, const float* d_ray_hit_distance_grad,
                  float* d_colour_grad, float* view_centre_out);
+/* A step in which this handle renders ONE view: the view's [N,12] gradient is written at once (as gut_backward does, into
+ * d_particle_density_grad, added when accumulate != 0) together with its colour gradient -- no accumulation is left pending
+ * and no gut_density_gradient_finish pass is needed; only the SH expansion waits for the other ranks' views. */
+GUT_API int gut_backward_colour_density(GutHandle* h, void* stream, const GutCamera* camera,
+                 uint32_t num_particles, int32_t sph_degree_active,
+                 const float* d_particle_density, const float* d_particle_radiance,
+                 uint32_t width, uint32_t height,
+                 const float* d_ray_origin, const float* d_ray_direction,
+                 const float* d_ray_radiance_density, const float* d_ray_radiance_density_grad,
+                 const float* d_ray_hit_distance, const float* d_ray_hit_distance_grad,
+                 float* d_particle_density_grad, float* d_colour_grad, float* view_centre_out, int32_t accumulate);
 GUT_API int gut_density_gradient_finish(GutHandle* h, void* stream, uint32_t num_particles,
                  const float* d_particle_density, float* d_particle_density_grad, int32_t accumulate);
 GUT_API int gut_sh_gradient_expand(GutHandle* h, void* stream, uint32_t num_particles, int32_t sph_degree_active,

@@ -6,6 +6,7 @@ import importlib
 import os
 import socket
 
+import numpy as np
 import pytest
 import torch
 import torch.distributed as dist
@@ -38,8 +39,12 @@ class FakeRaster:
 
     # deferred-SH variants (gut_backward_colour / gut_sh_gradient_expand): the stand-in's "SH gradient" of a view is
     # centre_x * colour gradient broadcast over the 48 columns, so that the expansion needs both gathered inputs
-    def trace_bwd_colour(self, deg, density, radiance, ray_o, ray_d, camera, rgba, rgba_grad, d, d_grad, out_colour_grad):
-        self._pending = getattr(self, "_pending", 0) + (rgba_grad.sum() * density + d_grad.sum())
+    def trace_bwd_colour(self, deg, density, radiance, ray_o, ray_d, camera, rgba, rgba_grad, d, d_grad, out_colour_grad,
+                         out_density_grad=None):
+        if out_density_grad is not None:    # one view per rank: the view's gradient is written directly, nothing pending
+            out_density_grad.copy_(rgba_grad.sum() * density + d_grad.sum())
+        else:
+            self._pending = getattr(self, "_pending", 0) + (rgba_grad.sum() * density + d_grad.sum())
         out_colour_grad.copy_(rgba_grad.mean() * radiance[:, :3])
         return [float(ray_o.flatten()[0]) + 1.0, 0.0, 0.0]
 
@@ -54,11 +59,12 @@ class FakeRaster:
         return out
 
 
-def _data():
+def _data(nviews=None):
+    nviews = NVIEWS if nviews is None else nviews
     g = torch.Generator().manual_seed(0)
     density = torch.randn((N, 12), generator=g); radiance = torch.randn((N, NSPH), generator=g)
-    views = [{"rays_ori": torch.full((1, H, W, 3), float(k)), "rays_dir": torch.ones((1, H, W, 3)), "camera": None} for k in range(NVIEWS)]
-    ups = [(torch.randn((H, W, 4), generator=g), torch.randn((H, W, 1), generator=g)) for _ in range(NVIEWS)]
+    views = [{"rays_ori": torch.full((1, H, W, 3), float(k)), "rays_dir": torch.ones((1, H, W, 3)), "camera": None} for k in range(nviews)]
+    ups = [(torch.randn((H, W, 4), generator=g), torch.randn((H, W, 1), generator=g)) for _ in range(nviews)]
     return density, radiance, views, ups
 
 
@@ -70,25 +76,27 @@ def _step(rank, world):
     return ex.density_grad.clone(), ex.radiance_grad.clone()
 
 
-def _step_deferred(rank, world):
-    density, radiance, views, ups = _data()
-    ids = gdist.shard_views(NVIEWS, rank, world)
-    vpr = (NVIEWS + world - 1) // world
+def _step_deferred(rank, world, nviews=None):
+    nviews = NVIEWS if nviews is None else nviews
+    density, radiance, views, ups = _data(nviews)
+    ids = gdist.shard_views(nviews, rank, world)
+    vpr = (nviews + world - 1) // world
     ex = gdist.DeferredExchange(N, NSPH, vpr, "cpu", world=world, track_visibility=True)
+    ex.density_grad.fill_(123.0)     # stale content a step must not keep
     gdist.training_step_deferred(FakeRaster(), ex, [views[i] for i in ids], 3, density, radiance, [ups[i] for i in ids], rank=rank)
     # the visibility SelectiveAdam masks with is the union over ALL views of the step, on every rank
     want = torch.zeros((N, 1))
-    for k in range(NVIEWS):
+    for k in range(nviews):
         want[k::NVIEWS + 2] = 1.0
     assert torch.equal(ex.visibility, want), "visibility union"
     return ex.density_grad.clone(), ex.radiance_grad.clone()
 
 
-def _worker_deferred(rank, world, port, q):
+def _worker_deferred(rank, world, port, q, nviews=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        g1, g2 = _step_deferred(rank, world)
+        g1, g2 = _step_deferred(rank, world, nviews)
         q.put((rank, g1.numpy(), g2.numpy()))
     finally:
         dist.destroy_process_group()
@@ -155,3 +163,23 @@ def test_rank_without_views_contributes_zero():
     ex.density_grad.fill_(3.0); ex.radiance_grad.fill_(4.0)
     gdist.training_step(FakeRaster(), ex, [], 3, density, radiance, [])
     assert float(ex.density_grad.abs().max()) == 0.0 and float(ex.radiance_grad.abs().max()) == 0.0
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("nviews", [2, 1])
+def test_two_rank_step_with_one_view_per_rank(nviews):
+    """views_per_rank == 1: every rank's backward writes its [N,12] gradient directly (DeferredExchange.density_out) and no
+    finish pass runs; with ONE view for two ranks the rank without a view contributes zeros, not its buffer's old content."""
+    ref1, ref2 = _step_deferred(0, 1, nviews)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_deferred, args=(r, 2, port, q, nviews)) for r in range(2)]
+    for p in procs: p.start()
+    res = [q.get(timeout=90) for _ in procs]
+    for p in procs: p.join(30)
+    assert all(p.exitcode == 0 for p in procs)
+    for _rank, g1, g2 in res:
+        assert np.allclose(g1, ref1.numpy(), rtol=1e-5, atol=1e-5)
+        assert np.allclose(g2, ref2.numpy(), rtol=1e-5, atol=1e-5)

@@ -278,6 +278,40 @@ def test_deferred_sh_gradient_equals_per_view_accumulation(pkg):
     assert rel_l2(dx.radiance_grad.cpu().numpy(), ex.radiance_grad.cpu().numpy()) <= 1e-5
 
 
+def test_one_view_per_rank_step_writes_the_density_gradient_directly(pkg):
+    """views_per_rank == 1 (what a rank of an 8-GPU step holds): the view's backward converts its accumulators itself
+    (gut_backward_colour_density) -- same [N,12] and [N,48] as gut_backward, no pass left pending, and a step in which the
+    rank has no view leaves zeros, not the previous step's gradient."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    n, w, h, deg = 5000, 96, 64, 3
+    scene = syn.make_scene(n, 3, seed=18)
+    d12 = syn.pack_density(scene).cuda(); sph = scene["features"].cuda()
+    hv = syn.make_view(w, h, k=1, n_views=3)
+    views = [{"rays_ori": hv["rays_ori"].cuda(), "rays_dir": hv["rays_dir"].cuda(), "camera": camera_of(hv)}]
+    g = torch.Generator().manual_seed(5)
+    ups = [((torch.rand((h, w, 4), generator=g) * 2 - 1).cuda(), ((torch.rand((h, w, 1), generator=g) * 2 - 1) * 0.01).cuda())]
+    raster = _raster(pkg)
+    ex = gdist.GradientExchange(n, 48, "cuda", world=1)
+    gdist.training_step(raster, ex, views, deg, d12, sph, ups)
+    dx = gdist.DeferredExchange(n, 48, 1, "cuda", world=1)
+    assert dx.density_out(0) is dx.density_grad
+    for _ in range(2):
+        gdist.training_step_deferred(raster, dx, views, deg, d12, sph, ups)
+        torch.cuda.synchronize()
+        assert float(ex.density_grad.abs().max()) > 0
+        assert rel_l2(dx.density_grad.cpu().numpy(), ex.density_grad.cpu().numpy()) <= 1e-5
+        assert rel_l2(dx.radiance_grad.cpu().numpy(), ex.radiance_grad.cpu().numpy()) <= 1e-5
+    # nothing pending: the reference-shaped backward is accepted right away
+    out = raster.trace(0, deg, d12, sph, views[0]["rays_ori"], views[0]["rays_dir"], None, views[0]["camera"])
+    raster.trace_bwd(0, deg, d12, sph, views[0]["rays_ori"], views[0]["rays_dir"], None, views[0]["camera"], 0, 1, None, None,
+                     out[0], ups[0][0], out[1], ups[0][1])
+    # a step without a view for this rank
+    gdist.training_step_deferred(raster, dx, [], deg, d12, sph, [])
+    torch.cuda.synchronize()
+    assert not dx.density_grad.any() and not dx.radiance_grad.any()
+    assert gdist.DeferredExchange(n, 48, 2, "cuda", world=1).density_out(0) is None
+
+
 def test_expand_gather_with_peer_buffer_equals_contiguous_expand(pkg):
     """gut_sh_gradient_expand_gather (one pointer per view) over slots of a gut_peer_buffer_create allocation == gut_sh_gradient_expand
     over a contiguous [V,N,3] buffer; 19 views exercise the chunking (16 per launch) and the accumulate flag.  Single process: the
