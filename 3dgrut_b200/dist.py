@@ -126,9 +126,11 @@ class DeferredExchange:
         if self.track_visibility and visibility is not None:
             torch.maximum(self.visibility, visibility.reshape(self.visibility.shape), out=self.visibility)
 
-    def finish_step(self, raster, sph_degree, particle_density):
+    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None):
         """Close the step: [N,12] conversion of the view-summed accumulators, exchange with the other ranks, [N,48] expansion
-        over all views of the step.  Leaves the summed gradients in ``density_grad`` / ``radiance_grad`` on every rank."""
+        over all views of the step.  Leaves the summed gradients in ``density_grad`` / ``radiance_grad`` on every rank
+        (``radiance_out``: write the [N,48] gradient there instead of into the exchange's own buffer)."""
+        radiance = self.radiance_grad if radiance_out is None else radiance_out
         lo = self.local_slot(self._rank, 0)
         mine = self.colour_all[lo:lo + self.views_per_rank]
         centres = list(self._centres)
@@ -149,11 +151,11 @@ class DeferredExchange:
             pending = [dist.all_reduce(self.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
             if self.track_visibility:   # union of the ranks' visibilities, 4 B/particle
                 pending.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
-        raster.sh_gradient_expand(sph_degree, particle_density, self.centres_all, self.colour_all, self.radiance_grad, accumulate=False)
+        raster.sh_gradient_expand(sph_degree, particle_density, self.centres_all, self.colour_all, radiance, accumulate=False)
         if pending is not None:
             for work in pending:
                 work.wait()
-        return self.density_grad, self.radiance_grad
+        return self.density_grad, radiance
 
 
 def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
@@ -279,7 +281,8 @@ class PeerExchange(DeferredExchange):
                 self.profile.setdefault(n1, []).append(e0.elapsed_time(e1))
         self._marks = []
 
-    def finish_step(self, raster, sph_degree, particle_density):
+    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None):
+        radiance = self.radiance_grad if radiance_out is None else radiance_out
         s = self._set
         if self.profile is not None and self._marks:     # fold the previous step's events into the sums
             torch.cuda.synchronize()
@@ -308,13 +311,13 @@ class PeerExchange(DeferredExchange):
             gathered.wait()
         self._mark("wait_for_all_ranks")
         ptrs = [self.slot_ptr(r, s, i) for r in range(self.world) for i in range(self.views_per_rank)]
-        raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, ptrs, self.radiance_grad, accumulate=False)
+        raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, ptrs, radiance, accumulate=False)
         self._mark("sh_expand_gather")
         if reduced is not None:
             for work in reduced:
                 work.wait()
         self._mark("allreduce_remainder")
-        return self.density_grad, self.radiance_grad
+        return self.density_grad, radiance
 
     def close(self):
         torch.cuda.synchronize()

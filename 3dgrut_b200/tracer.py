@@ -351,7 +351,12 @@ class TracerStep:
             self._open = None
         self.finished = True
         w = self.tracer.tracer_wrapper
-        g12, g48 = self.exchange.finish_step(w, self.n_active_features, self.particle_density)
+        # activated leaves take the [N,48] gradient as it is: the expansion writes into a fresh tensor that becomes the
+        # parameter's .grad (the exchange's own buffer is reused by the next step, a copy out of it was 576 MB per step)
+        fresh = None
+        if self.raw is None and self.leaves[4].requires_grad:
+            fresh = torch.empty_like(self.particle_radiance)
+        g12, g48 = self.exchange.finish_step(w, self.n_active_features, self.particle_density, radiance_out=fresh)
         if self.raw is not None:
             pos, rot, scl, dns, alb, spc = self.leaves
             pos_g, rot_g, scl_g, dns_g = w.activate_pack_backward(rot, self.particle_density, g12, *self.raw)
@@ -359,12 +364,20 @@ class TracerStep:
             pairs = zip(self.leaves, (pos_g, rot_g, scl_g, dns_g, alb_g, spc_g))
         else:
             pos_g, dns_g, rot_g, scl_g = w.unpack_particle_gradient(g12)
-            pairs = zip(self.leaves, (pos_g, rot_g, scl_g, dns_g, g48.clone()))
+            pairs = zip(self.leaves, (pos_g, rot_g, scl_g, dns_g, g48 if fresh is not None else g48.clone()))
         tensors, grads = [], []
         for t, g in pairs:
-            if t.requires_grad:
+            if not t.requires_grad:
+                continue
+            g = g.reshape(t.shape)
+            if t.is_leaf:      # what AccumulateGrad does, without its defensive copy of a gradient it cannot prove unshared
+                if t.grad is None:
+                    t.grad = g
+                else:
+                    t.grad.add_(g)
+            else:
                 tensors.append(t)
-                grads.append(g.reshape(t.shape))
+                grads.append(g)
         if tensors:
             torch.autograd.backward(tensors, grads)
         return self.exchange.visibility if getattr(self.exchange, "track_visibility", False) else None

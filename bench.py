@@ -463,20 +463,26 @@ def run_ours(args):
         h2d = d2h = 0
         # Inputs of view k+1 are copied host->device on a copy stream while view k computes (two device buffer sets);
         # the rendered RGBA goes back as ONE contiguous device->host copy per view.  All copies are inside the timed region.
-        copy_stream = torch.cuda.Stream(device=dev)
+        copy_stream = torch.cuda.Stream(device=dev)     # host -> device
+        back_stream = torch.cuda.Stream(device=dev)     # device -> host: its own stream, the two directions have their own engines
         nbuf = 2
         dev_in = [{"rays_ori": torch.empty((1, h, w, 3), device=dev), "rays_dir": torch.empty((1, h, w, 3), device=dev),
                    "T_to_world": torch.empty((1, 4, 4), device=dev), "rg": torch.empty((h, w, 4), device=dev),
                    "dg": torch.empty((h, w, 1), device=dev)} for _ in range(nbuf)]
         rgba_dev = [torch.empty((h, w, 4), device=dev) for _ in range(nbuf)]
         free_ev = [None] * nbuf   # recorded on the compute stream when a buffer set may be overwritten
+        back_ev = [None] * nbuf   # recorded on the read-back stream when an image buffer has been copied out
         prefetched = []
         loss_slots = [{"host": torch.zeros(1, dtype=torch.float32).pin_memory(), "event": None} for _ in range(2)]
         loss_turn = [0]
 
+        seq = [0]   # views staged so far, over all steps: the buffer sets alternate along this sequence, so that the inputs of
+                    # the NEXT view -- of this step or, for its last view, of the next step -- travel while the current one renders
+
         def stage(vi):
             nonlocal h2d
-            bi = vi % nbuf
+            bi = seq[0] % nbuf
+            seq[0] += 1
             pv, (rg_h, dg_h) = pinned[vi], host_up[vi]
             with torch.cuda.stream(copy_stream):
                 if free_ev[bi] is not None:
@@ -489,7 +495,7 @@ def run_ours(args):
                 h2d += (rg_h.numel() + dg_h.numel()) * 4
                 ev = torch.cuda.Event()
                 ev.record(copy_stream)
-            return ev
+            return ev, bi
 
         # the step's gradient exchange is the one the device-resident loop above used (peer memory / NCCL), now driven by
         # Tracer.begin_step ... finish(); a plain per-tensor allreduce has no step protocol, so that mode takes the deferred one
@@ -507,10 +513,14 @@ def run_ours(args):
             # the inputs of this step's first view were put in flight at the end of the previous step (a data loader's prefetch)
             ready = prefetched.pop() if prefetched else (stage(0) if pinned else None)
             for vi in range(len(pinned)):
-                bi = vi % nbuf
-                cur.wait_event(ready)
+                ready_ev, bi = ready
+                cur.wait_event(ready_ev)
+                # next view in flight now: the following view of this step, or the first view of the next step (a data loader's
+                # prefetch); stage() waits for its buffer set's free event
                 if vi + 1 < len(pinned):
                     ready = stage(vi + 1)
+                else:
+                    prefetched.append(stage(0))
                 # the pose stays a host tensor: the rasteriser consumes it on the host (kernel parameters), and a device copy
                 # would be read straight back with a stream-wide synchronisation (the reference does that, tracer.py:376)
                 dv = dict(pinned[vi])
@@ -520,15 +530,17 @@ def run_ours(args):
                 o = tstep.render(make_batch(dv, dev, pose_device="cpu"))
                 loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
                 loss.backward()
+                if back_ev[bi] is not None:
+                    cur.wait_event(back_ev[bi])       # the read-back that last used this image buffer has ended
                 torch.cat([o["pred_rgb"][0].detach(), o["pred_opacity"][0].detach()], dim=-1, out=rgba_dev[bi])
                 done = torch.cuda.Event()
                 done.record(cur)
                 free_ev[bi] = done
-                if vi + 1 == len(pinned):
-                    prefetched.append(stage(0))   # next step's first view; waits for its buffer set's free event like any stage()
-                with torch.cuda.stream(copy_stream):
-                    copy_stream.wait_event(done)
+                with torch.cuda.stream(back_stream):
+                    back_stream.wait_event(done)
                     out_host.copy_(rgba_dev[bi], non_blocking=True)
+                    back_ev[bi] = torch.cuda.Event()
+                    back_ev[bi].record(back_stream)
                 d2h += out_host.numel() * 4
                 checksum = loss.detach() if checksum is None else checksum + loss.detach()
             # gradients of all views (and of all ranks) -> .grad of the parameters: one [N,12] conversion, the exchange, one [N,48]
@@ -564,7 +576,8 @@ def run_ours(args):
         k_e2e = args.steps
         for _ in range(k_e2e):
             e2e_step()
-        torch.cuda.current_stream().wait_stream(copy_stream)   # every copy of the timed steps has landed
+        torch.cuda.current_stream().wait_stream(back_stream)   # every read-back of the timed steps has landed (the host->device
+        torch.cuda.current_stream().wait_stream(copy_stream)   # copies too: one view of a step after the timed ones is in flight)
         f1.record()
         barrier()
         for slot in loss_slots:                                 # the last steps' results (their copies ended before f1)
@@ -577,7 +590,7 @@ def run_ours(args):
                "d2h_bytes_per_step": int(d2h),
                "path": "Tracer.begin_step / step.render + autograd backward per view / step.finish (the multi-view entry of the plugin: "
                        "gradient conversions and the data-parallel exchange once per step); rays and upstream gradients copied from pinned host memory "
-                       "(copy stream, one view ahead), the 4x4 pose handed over as a host tensor (it becomes kernel parameters), rendered RGBA of every view and the scalar loss read back every step (the loss through pinned memory, consumed one step later); particles stay "
+                       "(copy stream, one view ahead -- across step boundaries too, like a data loader's prefetch; read-backs on a second stream), the 4x4 pose handed over as a host tensor (it becomes kernel parameters), rendered RGBA of every view and the scalar loss read back every step (the loss through pinned memory, consumed one step later); particles stay "
                        "device resident (they are the model)"}
 
     # ---- auxiliary: forward-only frame time at 1920x1080 (second half of BASELINE.json's metric; reference convention:
