@@ -153,6 +153,17 @@ class GutAdamGroup(C.Structure):
     ]
 
 
+class GutAdamTensors(C.Structure):
+    """One parameter of the fused optimiser epilogue (gut_density_adam / gut_sh_expand_adam): raw parameter and its two
+    moments, contiguous fp32, updated in place, and the learning rate."""
+    _fields_ = [
+        ("param", C.c_void_p),
+        ("exp_avg", C.c_void_p),
+        ("exp_avg_sq", C.c_void_p),
+        ("lr", C.c_float),
+    ]
+
+
 def _fill(arr, values, n):
     vals = [float(v) for v in values]
     if len(vals) != n:

@@ -258,6 +258,7 @@ size_t gut_sizeof_camera(void) { return sizeof(GutCamera); }
 size_t gut_sizeof_stage_outputs(void) { return sizeof(GutStageOutputs); }
 size_t gut_sizeof_frame_stats(void) { return sizeof(GutFrameStats); }
 size_t gut_sizeof_adam_group(void) { return sizeof(GutAdamGroup); }
+size_t gut_sizeof_adam_tensors(void) { return sizeof(GutAdamTensors); }
 
 int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
     if (!cfg || !out) return GUT_ERR_BAD_INPUT;
@@ -738,6 +739,50 @@ int gut_selective_adam_step(GutHandle* h, void* stream_, uint32_t N, const GutAd
     }
     DeviceGuard guard(h->device);
     GUT_CUDA(h, gut_launch_selective_adam(N, groups, num_groups, d_visibility, beta1, beta2, eps, zero_grad, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+static bool adam_tensors_ok(const GutAdamTensors* t) { return t && t->param && t->exp_avg && t->exp_avg_sq; }
+
+int gut_density_adam(GutHandle* h, void* stream_, uint32_t N, const float* d_density, const float* d_density_grad, const GutAdamTensors* positions,
+                     const GutAdamTensors* rotation, const GutAdamTensors* scale, const GutAdamTensors* density, int32_t scale_act,
+                     int32_t density_act, const float* d_visibility, float b1, float b2, float eps, const float* sensor_position,
+                     float* d_accum, float* d_denom) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (N == 0) return GUT_OK;
+    if (!d_density || !d_density_grad || !adam_tensors_ok(positions) || !adam_tensors_ok(rotation) || !adam_tensors_ok(scale) ||
+        !adam_tensors_ok(density))
+        return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (((uintptr_t)rotation->param | (uintptr_t)rotation->exp_avg | (uintptr_t)rotation->exp_avg_sq) & 15u)
+        return fail(h, GUT_ERR_BAD_INPUT, "rotation tensors must be 16-byte aligned");
+    if (scale_act < GUT_ACT_NONE || scale_act > GUT_ACT_SIGMOID || density_act < GUT_ACT_NONE || density_act > GUT_ACT_SIGMOID)
+        return fail(h, GUT_ERR_BAD_INPUT, "unknown activation");
+    if ((sensor_position != nullptr) != (d_accum != nullptr && d_denom != nullptr) || ((d_accum != nullptr) != (d_denom != nullptr)))
+        return fail(h, GUT_ERR_BAD_INPUT, "densification statistics need sensor_position, d_grad_norm_accum and d_grad_norm_denom together");
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_density_adam(N, d_density, d_density_grad, *positions, *rotation, *scale, *density, scale_act, density_act,
+                                        d_visibility, b1, b2, eps, sensor_position, d_accum, d_denom, (cudaStream_t)stream_));
+    h->launches += 1;
+    return GUT_OK;
+}
+
+int gut_sh_expand_adam(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degree, const float* d_density, uint32_t n_views,
+                       const float* d_view_centres, const float* const* colour_grad_ptrs, const GutAdamTensors* albedo,
+                       const GutAdamTensors* specular, const float* d_visibility, float b1, float b2, float eps) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
+    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_expand_adam is built for 16 SH coefficients");
+    if (n_views > GUT_EXPAND_MAX_VIEWS)
+        return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_expand_adam takes at most %d views (the update is applied once, in one launch)", GUT_EXPAND_MAX_VIEWS);
+    if (N == 0) return GUT_OK;
+    if (!d_density || !adam_tensors_ok(albedo) || !adam_tensors_ok(specular) || (n_views > 0 && (!d_view_centres || !colour_grad_ptrs)))
+        return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    for (uint32_t v = 0; v < n_views; ++v)
+        if (!colour_grad_ptrs[v]) return fail(h, GUT_ERR_BAD_INPUT, "colour gradient pointer of view %u is NULL", v);
+    DeviceGuard guard(h->device);
+    GUT_CUDA(h, gut_launch_sh_expand_adam(N, sph_degree, d_density, n_views, d_view_centres, colour_grad_ptrs, *albedo, *specular,
+                                          d_visibility, b1, b2, eps, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;
 }

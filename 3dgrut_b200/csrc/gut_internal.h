@@ -135,6 +135,13 @@ cudaError_t gut_launch_pack_features(uint32_t N, const float* albedo, const floa
 cudaError_t gut_launch_unpack_features(uint32_t N, const float* grad48, float* albedo_g, float* specular_g, cudaStream_t stream);
 cudaError_t gut_launch_selective_adam(uint32_t N, const GutAdamGroup* groups, uint32_t n_groups, const float* visibility, float b1, float b2,
                                       float eps, int zero_grad, cudaStream_t stream);
+cudaError_t gut_launch_density_adam(uint32_t N, const float* packed12, const float* grad12, const GutAdamTensors& pos, const GutAdamTensors& rot,
+                                    const GutAdamTensors& scale, const GutAdamTensors& dens, int scale_act, int density_act,
+                                    const float* visibility, float b1, float b2, float eps, const float* sensor /* host [3] or null */,
+                                    float* accum, float* denom, cudaStream_t stream);
+cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+                                      const float* const* colour_ptrs, const GutAdamTensors& albedo, const GutAdamTensors& specular,
+                                      const float* visibility, float b1, float b2, float eps, cudaStream_t stream);
 cudaError_t gut_launch_densify_stats(uint32_t N, const float* pos, const float* pos_g, float3 sensor, float* accum, float* denom,
                                      cudaStream_t stream);
 

@@ -165,3 +165,13 @@ GUT_HD void gut_sh_basis(int deg, float3 d, float* b) {
         }
     }
 }
+
+// SelectiveAdam's scalar update (threedgrut/optimizers/optimizers.cu:47-84; no bias correction).  The rounding is that of
+// the reference's compiled kernel (default nvcc flags: the moment updates contract into one FMA each, IEEE sqrt /
+// division; SASS of oracle/_ref/optimizers_cu.o), spelled out because the translation units that use it are built with
+// --fmad=false: bit-identical parameters, exp_avg and exp_avg_sq (tests/test_gpu_model.py, against that kernel).
+GUT_D void adam_scalar(float& p, float g, float& m, float& v, float lr, float b1, float b2, float eps) {
+    m = fmaf(g, 1.0f - b1, b1 * m);
+    v = fmaf(g, g * (1.0f - b2), b2 * v);
+    p = p - (lr * m) / (sqrtf(v) + eps);
+}

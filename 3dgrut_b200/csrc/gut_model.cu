@@ -134,15 +134,7 @@ struct AdamGroups {
     uint32_t vec_ok;     // bit i: group i's four pointers are 16-byte aligned and its element count is a multiple of 4
 };
 
-// The rounding is that of the reference's compiled kernel (default nvcc flags: the moment updates contract into one FMA
-// each, IEEE sqrt / division; SASS of oracle/_ref/optimizers_cu.o), spelled out because this translation unit is built
-// with --fmad=false: bit-identical parameters, exp_avg and exp_avg_sq (tests/test_gpu_model.py, against that kernel).
-GUT_D void adam_scalar(float& p, float g, float& m, float& v, float lr, float b1, float b2, float eps) {
-    m = fmaf(g, 1.0f - b1, b1 * m);
-    v = fmaf(g, g * (1.0f - b2), b2 * v);
-    p = p - (lr * m) / (sqrtf(v) + eps);
-}
-
+// adam_scalar: gut_math.cuh (shared with the fused SH expansion + Adam kernel of gut_project.cu)
 __global__ void __launch_bounds__(MODEL_THREADS) gut_selective_adam_kernel(AdamGroups groups, uint32_t N, const float* __restrict__ visibility,
                                                                           float b1, float b2, float eps, int zero_grad) {
     uint32_t gi = 0;
@@ -208,6 +200,94 @@ __global__ void __launch_bounds__(MODEL_THREADS) gut_densify_stats_kernel(uint32
     denom[i] += 1.0f;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// The [N,12] half of the optimiser step as the EPILOGUE of the gradient exchange: the summed [N,12]
+// gradient goes through the activation adjoints (gut_activate_backward_kernel's arithmetic) straight into SelectiveAdam for
+// positions, rotation, scale and density (adam_scalar: the reference kernel's rounding), and the densification statistics
+// of GSStrategy.update_gradient_buffer are taken from the position gradient on the way -- one pass, no raw-gradient tensors.
+// Bit-identical to gut_activate_pack_backward -> gut_selective_adam_step -> gut_densify_stats on the same inputs.
+// ---------------------------------------------------------------------------------------------------
+struct DensityAdam {
+    GutAdamTensors pos, rot, scale, dens;
+};
+__global__ void __launch_bounds__(MODEL_THREADS) gut_density_adam_kernel(uint32_t N, const float4* __restrict__ packed,
+                                                                        const float4* __restrict__ grad12, DensityAdam t, int scale_act,
+                                                                        int density_act, const float* __restrict__ visibility, float b1,
+                                                                        float b2, float eps, int stats, float3 sensor,
+                                                                        float* __restrict__ accum, float* __restrict__ denom) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const size_t i3 = 3 * (size_t)i;
+    const float4 ga = __ldg(grad12 + i3);
+    float px = 0.f, py = 0.f, pz = 0.f;
+    bool have_pos = false;
+    if (stats && !(ga.x == 0.0f && ga.y == 0.0f && ga.z == 0.0f)) {   // positions BEFORE the update, as post_backward sees them
+        px = t.pos.param[i3]; py = t.pos.param[i3 + 1]; pz = t.pos.param[i3 + 2];
+        have_pos = true;
+        const float dx = px - sensor.x, dy = py - sensor.y, dz = pz - sensor.z;
+        const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+        const float ax = ga.x * dist, ay = ga.y * dist, az = ga.z * dist;
+        accum[i] += sqrtf(ax * ax + ay * ay + az * az) / 2.0f;
+        denom[i] += 1.0f;
+    }
+    if (visibility && __ldg(visibility + i) == 0.0f) return;   // invisible rows keep param, exp_avg, exp_avg_sq
+    const float4 gq = __ldg(grad12 + i3 + 1), gs = __ldg(grad12 + i3 + 2);
+    const float4 pa = __ldg(packed + i3), ps = __ldg(packed + i3 + 2);
+    // positions
+    {
+        if (!have_pos) { px = t.pos.param[i3]; py = t.pos.param[i3 + 1]; pz = t.pos.param[i3 + 2]; }
+        float m0 = t.pos.exp_avg[i3], m1 = t.pos.exp_avg[i3 + 1], m2 = t.pos.exp_avg[i3 + 2];
+        float v0 = t.pos.exp_avg_sq[i3], v1 = t.pos.exp_avg_sq[i3 + 1], v2 = t.pos.exp_avg_sq[i3 + 2];
+        adam_scalar(px, ga.x, m0, v0, t.pos.lr, b1, b2, eps);
+        adam_scalar(py, ga.y, m1, v1, t.pos.lr, b1, b2, eps);
+        adam_scalar(pz, ga.z, m2, v2, t.pos.lr, b1, b2, eps);
+        t.pos.param[i3] = px; t.pos.param[i3 + 1] = py; t.pos.param[i3 + 2] = pz;
+        t.pos.exp_avg[i3] = m0; t.pos.exp_avg[i3 + 1] = m1; t.pos.exp_avg[i3 + 2] = m2;
+        t.pos.exp_avg_sq[i3] = v0; t.pos.exp_avg_sq[i3 + 1] = v1; t.pos.exp_avg_sq[i3 + 2] = v2;
+    }
+    // density
+    {
+        float p = t.dens.param[i], m = t.dens.exp_avg[i], v = t.dens.exp_avg_sq[i];
+        adam_scalar(p, activate_grad(density_act, pa.w, ga.w), m, v, t.dens.lr, b1, b2, eps);
+        t.dens.param[i] = p; t.dens.exp_avg[i] = m; t.dens.exp_avg_sq[i] = v;
+    }
+    // scale
+    {
+        const float g0 = activate_grad(scale_act, ps.x, gs.x), g1 = activate_grad(scale_act, ps.y, gs.y), g2 = activate_grad(scale_act, ps.z, gs.z);
+        float p0 = t.scale.param[i3], p1 = t.scale.param[i3 + 1], p2 = t.scale.param[i3 + 2];
+        float m0 = t.scale.exp_avg[i3], m1 = t.scale.exp_avg[i3 + 1], m2 = t.scale.exp_avg[i3 + 2];
+        float v0 = t.scale.exp_avg_sq[i3], v1 = t.scale.exp_avg_sq[i3 + 1], v2 = t.scale.exp_avg_sq[i3 + 2];
+        adam_scalar(p0, g0, m0, v0, t.scale.lr, b1, b2, eps);
+        adam_scalar(p1, g1, m1, v1, t.scale.lr, b1, b2, eps);
+        adam_scalar(p2, g2, m2, v2, t.scale.lr, b1, b2, eps);
+        t.scale.param[i3] = p0; t.scale.param[i3 + 1] = p1; t.scale.param[i3 + 2] = p2;
+        t.scale.exp_avg[i3] = m0; t.scale.exp_avg[i3 + 1] = m1; t.scale.exp_avg[i3 + 2] = m2;
+        t.scale.exp_avg_sq[i3] = v0; t.scale.exp_avg_sq[i3 + 1] = v1; t.scale.exp_avg_sq[i3 + 2] = v2;
+    }
+    // rotation: adjoint of y = x / max(|x|, eps) (gut_activate_backward_kernel), then Adam on the raw quaternion
+    {
+        float4 q = *reinterpret_cast<const float4*>(t.rot.param + 4 * (size_t)i);
+        const float nn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        float4 r;
+        if (nn > NORMALIZE_EPS) {
+            const float inv = 1.0f / nn;
+            const float yx = q.x * inv, yy = q.y * inv, yz = q.z * inv, yw = q.w * inv;
+            const float dt = yx * gq.x + yy * gq.y + yz * gq.z + yw * gq.w;
+            r = make_float4((gq.x - yx * dt) * inv, (gq.y - yy * dt) * inv, (gq.z - yz * dt) * inv, (gq.w - yw * dt) * inv);
+        } else {
+            r = make_float4(gq.x / NORMALIZE_EPS, gq.y / NORMALIZE_EPS, gq.z / NORMALIZE_EPS, gq.w / NORMALIZE_EPS);
+        }
+        float4 m = *reinterpret_cast<float4*>(t.rot.exp_avg + 4 * (size_t)i), v = *reinterpret_cast<float4*>(t.rot.exp_avg_sq + 4 * (size_t)i);
+        adam_scalar(q.x, r.x, m.x, v.x, t.rot.lr, b1, b2, eps);
+        adam_scalar(q.y, r.y, m.y, v.y, t.rot.lr, b1, b2, eps);
+        adam_scalar(q.z, r.z, m.z, v.z, t.rot.lr, b1, b2, eps);
+        adam_scalar(q.w, r.w, m.w, v.w, t.rot.lr, b1, b2, eps);
+        *reinterpret_cast<float4*>(t.rot.param + 4 * (size_t)i) = q;
+        *reinterpret_cast<float4*>(t.rot.exp_avg + 4 * (size_t)i) = m;
+        *reinterpret_cast<float4*>(t.rot.exp_avg_sq + 4 * (size_t)i) = v;
+    }
+}
+
 inline uint32_t blocks_for(uint64_t n) { return (uint32_t)((n + MODEL_THREADS - 1) / MODEL_THREADS); }
 
 }  // namespace
@@ -266,5 +346,19 @@ cudaError_t gut_launch_densify_stats(uint32_t N, const float* pos, const float* 
                                      cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     gut_densify_stats_kernel<<<blocks_for(N), MODEL_THREADS, 0, stream>>>(N, pos, pos_g, sensor, accum, denom);
+    return cudaGetLastError();
+}
+
+cudaError_t gut_launch_density_adam(uint32_t N, const float* packed12, const float* grad12, const GutAdamTensors& pos, const GutAdamTensors& rot,
+                                    const GutAdamTensors& scale, const GutAdamTensors& dens, int scale_act, int density_act,
+                                    const float* visibility, float b1, float b2, float eps, const float* sensor, float* accum, float* denom,
+                                    cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    DensityAdam t{pos, rot, scale, dens};
+    const int stats = (sensor && accum && denom) ? 1 : 0;
+    const float3 sp = stats ? make_float3(sensor[0], sensor[1], sensor[2]) : make_float3(0.f, 0.f, 0.f);
+    gut_density_adam_kernel<<<blocks_for(N), MODEL_THREADS, 0, stream>>>(N, reinterpret_cast<const float4*>(packed12),
+                                                                       reinterpret_cast<const float4*>(grad12), t, scale_act, density_act,
+                                                                       visibility, b1, b2, eps, stats, sp, accum, denom);
     return cudaGetLastError();
 }

@@ -9,6 +9,8 @@
 //            GUTProjector::evalBackward (gutProjector.cuh:390-430).
 #include <float.h>
 
+#include <type_traits>
+
 #include "gut_internal.h"
 
 namespace {
@@ -738,6 +740,128 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
             dst[f] = val;
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SH expansion with SelectiveAdam as its epilogue (gut_sh_expand_adam).  Phase A is gut_sh_expand_kernel's
+// (same arithmetic in the same order: the 48 values are the bits the expansion would have written), phase B applies them:
+// the warp walks its 32 rows of features_albedo (96 contiguous floats) and features_specular (1440 contiguous floats) one
+// float per lane and round, parameter / exp_avg / exp_avg_sq read and written coalesced, rows of invisible particles left alone.
+// ---------------------------------------------------------------------------------------------------
+#ifndef GUT_SHADAM_MIN_BLOCKS
+#define GUT_SHADAM_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(K6_THREADS, GUT_SHADAM_MIN_BLOCKS) gut_sh_expand_adam_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
+                                                                        uint32_t n_views, const float* __restrict__ centres, ExpandViews views,
+                                                                        GutAdamTensors albedo, GutAdamTensors specular,
+                                                                        const float* __restrict__ visibility, float b1, float b2, float eps,
+                                                                        uint32_t vec_mask /* bit 0 / 1: albedo / specular tensors 16-byte aligned */) {
+    __shared__ float s_out[K6_WARPS][32][49];
+    __shared__ float s_vis[K6_WARPS][32];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t warp_base = i - lane;
+    const bool vis = i < N && (visibility ? __ldg(visibility + i) != 0.0f : true);
+    if (!__any_sync(0xffffffffu, vis)) return;   // warp-uniform: none of the 32 rows is updated
+    // the 48 sums live in the lane's row of the shared tile, not in registers: the Adam phase below is what the kernel spends
+    // its time in (IEEE sqrt and division per element), and it runs at twice the occupancy without 48 accumulators in the register
+    // budget: 116 -> 64 registers, 4 -> 8 CTAs per SM, 1.34 -> 1.05 ms at 3M particles and 8 views (the unfused chain: 1.27 ms)
+    float* const acc = &s_out[wid][lane][0];
+#pragma unroll
+    for (int k = 0; k < 48; ++k) acc[k] = 0.0f;
+    if (vis) {
+        const float4 r0 = __ldg(density12 + 3 * (size_t)i);
+#pragma unroll
+        for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {
+            if (v0 >= n_views) break;
+            float3 gq[EXPAND_CHUNK];
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q) {
+                gq[q] = f3(0.f, 0.f, 0.f);
+                if (v0 + q < n_views) {
+                    const float* gp = views.colour[v0 + q] + 3 * (size_t)i;
+                    gq[q] = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q) {
+                const float3 g = gq[q];
+                if (g.x == 0.0f && g.y == 0.0f && g.z == 0.0f) continue;
+                const uint32_t v = v0 + q;
+                const float3 d = f3(r0.x, r0.y, r0.z) - f3(__ldg(centres + 3 * v), __ldg(centres + 3 * v + 1), __ldg(centres + 3 * v + 2));
+                const float len = sqrtf(dot(d, d));
+                const float3 dir = len <= 0.0f ? f3(1.0f, 0.0f, 0.0f) : f3(d.x / len, d.y / len, d.z / len);
+                float b[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) b[k] = 0.0f;
+                gut_sh_basis(sph_degree, dir, b);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    acc[3 * k] += b[k] * g.x; acc[3 * k + 1] += b[k] * g.y; acc[3 * k + 2] += b[k] * g.z;
+                }
+            }
+        }
+    }
+    s_vis[wid][lane] = vis ? 1.0f : 0.0f;
+    __syncwarp();
+    const uint32_t rows = warp_base < N ? min(32u, N - warp_base) : 0u;
+    // The warp's rows are ONE contiguous span of each tensor (32 x 3 and 32 x 45 floats, starting 16-byte aligned when the
+    // tensors are): walked as 128-bit vectors, four consecutive floats per lane and round -- a vector may straddle two rows,
+    // so row, column and visibility are looked up per component.
+    auto update_span = [&](const GutAdamTensors& t, auto width_c, const uint32_t col0, const bool vec_ok) {
+        constexpr uint32_t width = decltype(width_c)::value;
+        const uint32_t total = rows * width;
+        float* p = t.param + (size_t)width * warp_base; float* m = t.exp_avg + (size_t)width * warp_base;
+        float* v = t.exp_avg_sq + (size_t)width * warp_base;
+        constexpr uint32_t rounds = (32 * width / 4 + 31) / 32;
+#pragma unroll
+        for (uint32_t it = 0; it < rounds; ++it) {   // unrolled: all of a lane's loads are in flight before the first update
+            const uint32_t e0 = 4 * (it * 32 + lane);
+            if (e0 >= total) continue;
+            if (vec_ok && e0 + 3 < total) {
+                float gk[4]; bool on[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t e = e0 + c, row = e / width, col = e - row * width;
+                    on[c] = s_vis[wid][row] != 0.0f;
+                    gk[c] = s_out[wid][row][col0 + col];
+                }
+                if (on[0] || on[1] || on[2] || on[3]) {
+                    float4 pp = *reinterpret_cast<float4*>(p + e0), mm = *reinterpret_cast<float4*>(m + e0), vv = *reinterpret_cast<float4*>(v + e0);
+                    if (on[0]) adam_scalar(pp.x, gk[0], mm.x, vv.x, t.lr, b1, b2, eps);
+                    if (on[1]) adam_scalar(pp.y, gk[1], mm.y, vv.y, t.lr, b1, b2, eps);
+                    if (on[2]) adam_scalar(pp.z, gk[2], mm.z, vv.z, t.lr, b1, b2, eps);
+                    if (on[3]) adam_scalar(pp.w, gk[3], mm.w, vv.w, t.lr, b1, b2, eps);
+                    *reinterpret_cast<float4*>(p + e0) = pp; *reinterpret_cast<float4*>(m + e0) = mm; *reinterpret_cast<float4*>(v + e0) = vv;
+                }
+            } else {
+                for (uint32_t e = e0; e < min(e0 + 4u, total); ++e) {
+                    const uint32_t row = e / width, col = e - row * width;
+                    if (s_vis[wid][row] != 0.0f) {
+                        float pp = p[e], mm = m[e], vv = v[e];
+                        adam_scalar(pp, s_out[wid][row][col0 + col], mm, vv, t.lr, b1, b2, eps);
+                        p[e] = pp; m[e] = mm; v[e] = vv;
+                    }
+                }
+            }
+        }
+    };
+    update_span(albedo, std::integral_constant<uint32_t, 3u>{}, 0u, (vec_mask & 1u) != 0u);
+    update_span(specular, std::integral_constant<uint32_t, 45u>{}, 3u, (vec_mask & 2u) != 0u);
+}
+
+cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+                                      const float* const* colour_ptrs, const GutAdamTensors& albedo, const GutAdamTensors& specular,
+                                      const float* visibility, float b1, float b2, float eps, cudaStream_t stream) {
+    if (N == 0) return cudaSuccess;
+    if (n_views > GUT_EXPAND_MAX_VIEWS) return cudaErrorInvalidValue;
+    ExpandViews views = {};
+    for (uint32_t v = 0; v < n_views; ++v) views.colour[v] = colour_ptrs[v];
+    auto aligned = [](const GutAdamTensors& t) { return (((uintptr_t)t.param | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15u) == 0; };
+    const uint32_t vec_mask = (aligned(albedo) ? 1u : 0u) | (aligned(specular) ? 2u : 0u);   // a warp's span starts at 32 x width floats
+    gut_sh_expand_adam_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
+        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, views, albedo, specular, visibility, b1, b2, eps, vec_mask);
+    return cudaGetLastError();
 }
 
 // colour_ptrs: HOST array of n_views device pointers.  More than GUT_EXPAND_MAX_VIEWS views are expanded in several

@@ -126,10 +126,16 @@ class DeferredExchange:
         if self.track_visibility and visibility is not None:
             torch.maximum(self.visibility, visibility.reshape(self.visibility.shape), out=self.visibility)
 
-    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None):
+    def colour_ptrs(self):
+        """One device pointer per view slot of the step (all ranks), what gut_sh_gradient_expand_gather / gut_sh_expand_adam take."""
+        return [self.colour_all[v].data_ptr() for v in range(self.colour_all.shape[0])]
+
+    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None, expand=True):
         """Close the step: [N,12] conversion of the view-summed accumulators, exchange with the other ranks, [N,48] expansion
         over all views of the step.  Leaves the summed gradients in ``density_grad`` / ``radiance_grad`` on every rank
-        (``radiance_out``: write the [N,48] gradient there instead of into the exchange's own buffer)."""
+        (``radiance_out``: write the [N,48] gradient there instead of into the exchange's own buffer).
+        ``expand=False`` stops before the expansion -- every rank's colour gradients and centres are in place and the [N,12]
+        all-reduce has completed -- for ``optimizer_epilogue``, which expands inside the optimiser kernel."""
         radiance = self.radiance_grad if radiance_out is None else radiance_out
         lo = self.local_slot(self._rank, 0)
         mine = self.colour_all[lo:lo + self.views_per_rank]
@@ -151,11 +157,12 @@ class DeferredExchange:
             pending = [dist.all_reduce(self.density_grad, op=dist.ReduceOp.SUM, async_op=True)]
             if self.track_visibility:   # union of the ranks' visibilities, 4 B/particle
                 pending.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
-        raster.sh_gradient_expand(sph_degree, particle_density, self.centres_all, self.colour_all, radiance, accumulate=False)
+        if expand:
+            raster.sh_gradient_expand(sph_degree, particle_density, self.centres_all, self.colour_all, radiance, accumulate=False)
         if pending is not None:
             for work in pending:
                 work.wait()
-        return self.density_grad, radiance
+        return self.density_grad, (radiance if expand else None)
 
 
 def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
@@ -281,7 +288,10 @@ class PeerExchange(DeferredExchange):
                 self.profile.setdefault(n1, []).append(e0.elapsed_time(e1))
         self._marks = []
 
-    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None):
+    def colour_ptrs(self):
+        return [self.slot_ptr(r, self._set, i) for r in range(self.world) for i in range(self.views_per_rank)]
+
+    def finish_step(self, raster, sph_degree, particle_density, radiance_out=None, expand=True):
         radiance = self.radiance_grad if radiance_out is None else radiance_out
         s = self._set
         if self.profile is not None and self._marks:     # fold the previous step's events into the sums
@@ -310,14 +320,14 @@ class PeerExchange(DeferredExchange):
                 reduced.append(dist.all_reduce(self.visibility, op=dist.ReduceOp.MAX, async_op=True))
             gathered.wait()
         self._mark("wait_for_all_ranks")
-        ptrs = [self.slot_ptr(r, s, i) for r in range(self.world) for i in range(self.views_per_rank)]
-        raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, ptrs, radiance, accumulate=False)
+        if expand:
+            raster.sh_gradient_expand_gather(sph_degree, particle_density, self.centres_all, self.colour_ptrs(), radiance, accumulate=False)
         self._mark("sh_expand_gather")
         if reduced is not None:
             for work in reduced:
                 work.wait()
         self._mark("allreduce_remainder")
-        return self.density_grad, radiance
+        return self.density_grad, (radiance if expand else None)
 
     def close(self):
         torch.cuda.synchronize()
@@ -362,6 +372,29 @@ def optimizer_step(raster, ex, raw, particle_density, state, lrs, betas=(0.9, 0.
     groups = [(raw[k], grads[k], state[k][0], state[k][1], lrs[k]) for k in PARAMETER_GROUPS]
     raster.selective_adam_step(groups, ex.visibility, betas[0], betas[1], eps)
     return grads
+
+
+def optimizer_epilogue(raster, ex, raw, particle_density, state, lrs, sph_degree, betas=(0.9, 0.999), eps=1e-15, scale_activation=1,
+                       density_activation=2, sensor_position=None, grad_norm_accum=None, grad_norm_denom=None):
+    """``optimizer_step`` as the EPILOGUE of the step's gradient kernels, after ``ex.finish_step(..., expand=False)``:
+    two launches, no gradient tensors in between.
+      * gut_density_adam: the all-reduced [N,12] gradient -> activation adjoints -> SelectiveAdam on positions / rotation / scale /
+        density, and GSStrategy.update_gradient_buffer on the way when ``sensor_position`` and the two statistics buffers are given;
+      * gut_sh_expand_adam: the views' colour gradients (local or peer memory) are expanded per particle in registers and applied
+        to features_albedo / features_specular -- the [N,48] gradient is never written.
+    Same arguments and the same resulting bits as ``optimizer_step`` (+ ``densify_stats``)."""
+    if not getattr(ex, "track_visibility", False):
+        raise ValueError("optimizer_epilogue needs an exchange built with track_visibility=True (see optimizer_step)")
+    n_slots = ex.world * ex.views_per_rank
+    if n_slots > 16:
+        raise ValueError(f"optimizer_epilogue expands at most 16 views in its one launch, the step holds {n_slots} slots: use optimizer_step")
+    triple = lambda k: (raw[k], state[k][0], state[k][1])
+    raster.density_adam(particle_density, ex.density_grad, triple("positions"), triple("rotation"), triple("scale"), triple("density"),
+                        [lrs[k] for k in ("positions", "rotation", "scale", "density")], ex.visibility, betas[0], betas[1], eps,
+                        scale_activation, density_activation, sensor_position, grad_norm_accum, grad_norm_denom)
+    raster.sh_expand_adam(sph_degree, particle_density, ex.centres_all, ex.colour_ptrs(), triple("features_albedo"),
+                          triple("features_specular"), (lrs["features_albedo"], lrs["features_specular"]), ex.visibility, betas[0],
+                          betas[1], eps)
 
 
 def _all_gather(out, mine):

@@ -103,6 +103,12 @@ def load_library():
     lib.gut_unpack_feature_gradient.restype = C.c_int
     lib.gut_selective_adam_step.argtypes = [vp, vp, u32, C.POINTER(abi.GutAdamGroup), u32, fp, C.c_float, C.c_float, C.c_float, i32]
     lib.gut_selective_adam_step.restype = C.c_int
+    at = C.POINTER(abi.GutAdamTensors)
+    lib.gut_density_adam.argtypes = [vp, vp, u32, fp, fp, at, at, at, at, i32, i32, fp, C.c_float, C.c_float, C.c_float,
+                                     C.POINTER(C.c_float), fp, fp]
+    lib.gut_density_adam.restype = C.c_int
+    lib.gut_sh_expand_adam.argtypes = [vp, vp, u32, i32, fp, u32, fp, C.POINTER(C.c_void_p), at, at, fp, C.c_float, C.c_float, C.c_float]
+    lib.gut_sh_expand_adam.restype = C.c_int
     lib.gut_densify_stats.argtypes = [vp, vp, u32, fp, fp, C.POINTER(C.c_float), fp, fp]
     lib.gut_densify_stats.restype = C.c_int
     lib.gut_forward_host.argtypes = [vp, vp, C.POINTER(abi.GutCamera), u32, i32, fp, fp, u32, u32, fp, fp, fp, fp, fp, fp]
@@ -125,7 +131,7 @@ def load_library():
     lib.gut_last_error.argtypes = [vp]
     lib.gut_last_error.restype = C.c_char_p
     for name in ("gut_sizeof_config", "gut_sizeof_camera", "gut_sizeof_stage_outputs", "gut_sizeof_frame_stats",
-                 "gut_sizeof_adam_group"):
+                 "gut_sizeof_adam_group", "gut_sizeof_adam_tensors"):
         getattr(lib, name).restype = C.c_size_t
     if lib.gut_abi_version() != abi.GUT_ABI_VERSION:
         raise ImportError(f"libgut_b200 ABI {lib.gut_abi_version()} != python mirror {abi.GUT_ABI_VERSION}")
@@ -133,6 +139,8 @@ def load_library():
         raise ImportError("libgut_b200 struct layout differs from 3dgrut_b200/abi.py")
     if lib.gut_sizeof_adam_group() != C.sizeof(abi.GutAdamGroup):
         raise ImportError("libgut_b200 GutAdamGroup layout differs from 3dgrut_b200/abi.py")
+    if lib.gut_sizeof_adam_tensors() != C.sizeof(abi.GutAdamTensors):
+        raise ImportError("libgut_b200 GutAdamTensors layout differs from 3dgrut_b200/abi.py")
     _lib = lib
     return lib
 
@@ -540,6 +548,72 @@ class SplatRaster:
                 raise GutError(abi.GutStatus.BAD_INPUT, f"visibility has {vis.shape[0]} rows, parameters {n}")
         rc = self.lib.gut_selective_adam_step(self._h, self._stream(), n, arr, len(groups), _ptr(vis), float(beta1), float(beta2), float(eps),
                                               1 if zero_grad else 0)
+        if rc != 0:
+            self._raise(rc)
+
+    def _adam_tensors(self, name, triple, lr, n):
+        p, m, v = triple
+        for what, t in (("param", p), ("exp_avg", m), ("exp_avg_sq", v)):
+            if not t.is_cuda or t.dtype != torch.float32 or t.device != self.device or not t.is_contiguous() or t.shape != p.shape:
+                raise GutError(abi.GutStatus.BAD_INPUT, f"{name}: {what} must be a contiguous float32 tensor on {self.device} shaped like the parameter")
+        if p.shape[0] != n:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"{name} has {p.shape[0]} rows, expected {n}")
+        return abi.GutAdamTensors(param=p.data_ptr(), exp_avg=m.data_ptr(), exp_avg_sq=v.data_ptr(), lr=float(lr))
+
+    def _vis(self, visibility, n):
+        if visibility is None:
+            return None
+        vis = visibility.reshape(-1)
+        if vis.dtype != torch.float32:
+            vis = vis.to(torch.float32)
+        vis = _check_cuda_f32("visibility", vis, self.device)
+        if vis.shape[0] != n:
+            raise GutError(abi.GutStatus.BAD_INPUT, f"visibility has {vis.shape[0]} rows, parameters {n}")
+        return vis
+
+    def density_adam(self, particle_density, density_grad, positions, rotation, scale, density, lrs, visibility, beta1, beta2, eps,
+                     scale_activation=abi.Activation.EXP, density_activation=abi.Activation.SIGMOID, sensor_position=None,
+                     grad_norm_accum=None, grad_norm_denom=None):
+        """gut_density_adam: the summed [N,12] gradient -> activation adjoints -> SelectiveAdam on the four raw parameters
+        (each a (param, exp_avg, exp_avg_sq) triple, ``lrs`` their four learning rates) in one pass; with ``sensor_position`` and
+        the two statistics buffers also GSStrategy.update_gradient_buffer."""
+        dens = _check_cuda_f32("particle_density", particle_density, self.device)
+        g = _check_cuda_f32("density_grad", density_grad, self.device)
+        n = dens.shape[0]
+        if dens.shape != (n, 12) or g.shape != (n, 12):
+            raise GutError(abi.GutStatus.BAD_INPUT, "particle_density and density_grad must be [N,12]")
+        ts = [self._adam_tensors(k, t, lr, n) for k, t, lr in zip(("positions", "rotation", "scale", "density"),
+                                                                   (positions, rotation, scale, density), lrs)]
+        vis = self._vis(visibility, n)
+        sensor = None
+        if sensor_position is not None:
+            sensor = (C.c_float * 3)(*[float(x) for x in sensor_position])
+            for t in (grad_norm_accum, grad_norm_denom):
+                if t is None or t.numel() != n or not t.is_contiguous() or t.dtype != torch.float32:
+                    raise GutError(abi.GutStatus.BAD_INPUT, "grad_norm_accum / grad_norm_denom must be contiguous float32 [N,1]")
+        rc = self.lib.gut_density_adam(self._h, self._stream(), n, _ptr(dens), _ptr(g), C.byref(ts[0]), C.byref(ts[1]), C.byref(ts[2]),
+                                       C.byref(ts[3]), int(scale_activation), int(density_activation), _ptr(vis), float(beta1), float(beta2),
+                                       float(eps), sensor, _ptr(grad_norm_accum) if sensor is not None else None,
+                                       _ptr(grad_norm_denom) if sensor is not None else None)
+        if rc != 0:
+            self._raise(rc)
+
+    def sh_expand_adam(self, num_active_features, particle_density, view_centres, colour_ptrs, features_albedo, features_specular, lrs,
+                       visibility, beta1, beta2, eps):
+        """gut_sh_expand_adam: expansion of the step's per-view colour gradients (one device pointer per view, as
+        sh_gradient_expand_gather) with SelectiveAdam on features_albedo / features_specular as its epilogue."""
+        dens = _check_cuda_f32("particle_density", particle_density, self.device)
+        cen = _check_cuda_f32("view_centres", view_centres, self.device)
+        n, nv = dens.shape[0], len(colour_ptrs)
+        if cen.numel() < 3 * nv:
+            raise GutError(abi.GutStatus.BAD_INPUT, "view_centres holds fewer rows than there are colour pointers")
+        alb = self._adam_tensors("features_albedo", features_albedo, lrs[0], n)
+        spc = self._adam_tensors("features_specular", features_specular, lrs[1], n)
+        if features_albedo[0].numel() != 3 * n or features_specular[0].numel() != 45 * n:
+            raise GutError(abi.GutStatus.BAD_INPUT, "features_albedo must be [N,3] and features_specular [N,45]")
+        arr = (C.c_void_p * max(nv, 1))(*[int(p) for p in colour_ptrs])
+        rc = self.lib.gut_sh_expand_adam(self._h, self._stream(), n, int(num_active_features), _ptr(dens), nv, _ptr(cen), arr,
+                                         C.byref(alb), C.byref(spc), _ptr(self._vis(visibility, n)), float(beta1), float(beta2), float(eps))
         if rc != 0:
             self._raise(rc)
 

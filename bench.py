@@ -661,6 +661,76 @@ def run_ours(args):
         raster.set_training(True)
         del sweep_views
 
+    # ---- auxiliary: the WHOLE training step -- raw parameters -> activation + packing -> the views' forward and
+    # backward -> gradient exchange -> SelectiveAdam on all six groups + densification statistics -- with the optimiser as separate
+    # kernels behind the exchange (dist.optimizer_step) and as the epilogue of the gradient kernels (dist.optimizer_epilogue).
+    # Every rank takes part (the step holds collectives). ----------------------------------------------------------------
+    train_step = None
+    if not args.no_aux and (args.views + world - 1) // world * world <= 16:
+        sc = {k: v.to(dev) for k, v in scene.items()}   # the raw parameters a MixtureOfGaussians would hold for this scene
+        rawd = {"positions": sc["positions"].clone(), "rotation": (sc["rotation"] * 1.7).contiguous(), "scale": torch.log(sc["scale"]),
+                "density": torch.log(sc["density"] / (1 - sc["density"])), "features_albedo": sc["features"][:, :3].contiguous(),
+                "features_specular": sc["features"][:, 3:].contiguous()}
+        state = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in rawd.items()}
+        # learning rates 0: the update runs in full (moments change, parameters are read and written) but the scene stays the one
+        # the gradient-only figure was measured on, so the three step times are comparable
+        lrs = {k_: 0.0 for k_ in gdist.PARAMETER_GROUPS}
+        accum, denom = torch.zeros((n, 1), device=dev), torch.zeros((n, 1), device=dev)
+        vpr = (args.views + world - 1) // world
+        ex2 = None
+        try:
+            if args.exchange == "peer":
+                ex2 = gdist.PeerExchange(raster, n, sph.shape[1], vpr, dev, rank, world=world, track_visibility=True)
+            else:
+                ex2 = gdist.DeferredExchange(n, sph.shape[1], vpr, dev, world=world, track_visibility=True)
+        except RuntimeError as e:
+            print(f"[bench] rank {rank}: train_step measurement skipped ({e!r})", file=sys.stderr, flush=True)
+        if ex2 is not None:
+            sensor = [0.0, 0.0, 4.0]
+
+            def whole_step(fused):
+                packed = raster.activate_pack(rawd["positions"], rawd["rotation"], rawd["scale"], rawd["density"])
+                sphp = raster.pack_features(rawd["features_albedo"], rawd["features_specular"])
+                ex2.begin_step(rank)
+                for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
+                    rgba_, dist_, _hits, vis_ = raster.trace(0, SPH_DEGREE, packed, sphp, v["rays_ori"], v["rays_dir"], None, v["camera"])
+                    c_ = raster.trace_bwd_colour(SPH_DEGREE, packed, sphp, v["rays_ori"], v["rays_dir"], v["camera"], rgba_, rg, dist_, dg,
+                                                 ex2.slot(i), out_density_grad=ex2.density_out(i))
+                    ex2.add_view(c_, vis_)
+                if fused:
+                    ex2.finish_step(raster, SPH_DEGREE, packed, expand=False)
+                    gdist.optimizer_epilogue(raster, ex2, rawd, packed, state, lrs, SPH_DEGREE, sensor_position=sensor,
+                                             grad_norm_accum=accum, grad_norm_denom=denom)
+                else:
+                    ex2.finish_step(raster, SPH_DEGREE, packed)
+                    gr = gdist.optimizer_step(raster, ex2, rawd, packed, state, lrs)
+                    raster.densify_stats(rawd["positions"], gr["positions"], sensor, accum, denom)
+
+            def time_steps(fused, reps=5):
+                for _ in range(2):
+                    whole_step(fused)
+                barrier()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                for _ in range(reps):
+                    whole_step(fused)
+                t1.record()
+                barrier()
+                tt_ = torch.tensor([t0.elapsed_time(t1) / reps], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+                return float(tt_.item())
+
+            ms_unfused, ms_fused = time_steps(False), time_steps(True)
+            train_step = {"what": "raw parameters -> activation + packing -> 8 views forward + backward -> exchange -> SelectiveAdam (6 groups, "
+                                  "visibility-masked, learning rates 0 so that the scene stays the measured one) + densification statistics; device-resident inputs",
+                          "ms_per_step_optimizer_as_separate_kernels": ms_unfused, "ms_per_step_optimizer_as_epilogue": ms_fused,
+                          "mpix_per_s_optimizer_as_epilogue": args.views * P / (ms_fused * 1e-3) / 1e6,
+                          "ms_per_step_gradients_only": ms_total / args.steps}
+            if hasattr(ex2, "close"):
+                ex2.close()
+            raster.stage_times()
+
     # ---- auxiliary: the "sorted" configuration (k_buffer_size = 16, configs/paper/3dgut/base_sorted.yaml; SURVEY 8d's second
     # config): forward + backward of ONE view of the same workload, device resident ---------------------------------------
     sorted_k16 = None
@@ -758,7 +828,7 @@ def run_ours(args):
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,
                               "forward_tests_executed_per_pixel": tests_exec / nv / P},
-            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "fwd_sweep": fwd_sweep, "sorted_k16": sorted_k16, "model_side": model_side,
+            "stage_ms": stage_ms, "fwd_only_1080p": fwd_1080p, "fwd_sweep": fwd_sweep, "sorted_k16": sorted_k16, "model_side": model_side, "train_step": train_step,
         }
         print(json.dumps(line), flush=True)
     if args.exchange == "peer":

@@ -337,6 +337,38 @@ GUT_API int gut_densify_stats(GutHandle* h, void* stream, uint32_t num_particles
                  const float* sensor_position /* host [3] */, float* d_grad_norm_accum, float* d_grad_norm_denom);
 
 /*
+ * The optimiser step as the EPILOGUE of a step's gradient kernels (no reference counterpart as a fusion:
+ * the reference runs autograd's activation adjoints, the feature split and SelectiveAdam as separate kernels per group).
+ *   gut_density_adam    the summed [N,12] gradient (after the data-parallel all-reduce) -> activation adjoints -> SelectiveAdam
+ *                       on positions / rotation / scale / density in one pass, plus -- when sensor_position and both
+ *                       statistics buffers are given -- GSStrategy.update_gradient_buffer on the position gradient and the
+ *                       positions BEFORE the update (gs.py:104-115 runs in post_backward, before optimizer.step);
+ *   gut_sh_expand_adam  the per-view colour gradients of ALL views of the step (one device pointer per view, local or
+ *                       peer memory, as gut_sh_gradient_expand_gather; n_views <= GUT_EXPAND_MAX_VIEWS) are expanded per
+ *                       particle into the 48 SH gradients in registers and applied to features_albedo [N,3] /
+ *                       features_specular [N,45] at once: the [N,48] gradient (192 B per particle written, read by the
+ *                       feature split, written again, read by Adam) never exists.
+ * Both are masked by d_visibility [N] (NULL = all rows) like SelectiveAdam.step, and leave bit for bit what
+ * gut_activate_pack_backward / gut_sh_gradient_expand_gather + gut_unpack_feature_gradient -> gut_selective_adam_step ->
+ * gut_densify_stats leave on the same inputs.
+ */
+typedef struct GutAdamTensors {
+    float* param;        /* raw parameter, updated in place */
+    float* exp_avg;
+    float* exp_avg_sq;
+    float  lr;
+} GutAdamTensors;
+GUT_API int gut_density_adam(GutHandle* h, void* stream, uint32_t num_particles, const float* d_particle_density,
+                 const float* d_particle_density_grad, const GutAdamTensors* positions, const GutAdamTensors* rotation,
+                 const GutAdamTensors* scale, const GutAdamTensors* density, int32_t scale_activation, int32_t density_activation,
+                 const float* d_visibility, float beta1, float beta2, float eps,
+                 const float* sensor_position /* host [3] or NULL */, float* d_grad_norm_accum, float* d_grad_norm_denom);
+GUT_API int gut_sh_expand_adam(GutHandle* h, void* stream, uint32_t num_particles, int32_t sph_degree_active,
+                 const float* d_particle_density, uint32_t n_views, const float* d_view_centres,
+                 const float* const* colour_grad_ptrs, const GutAdamTensors* features_albedo,
+                 const GutAdamTensors* features_specular, const float* d_visibility, float beta1, float beta2, float eps);
+
+/*
  * Same two calls with HOST buffers: inputs are copied host->device and results
  * device->host inside the call on `stream` (the end-to-end path bench.py times).
  * Particle parameters stay device resident (they are the model, not a per-view
@@ -425,6 +457,7 @@ GUT_API size_t      gut_sizeof_camera(void);
 GUT_API size_t      gut_sizeof_stage_outputs(void);
 GUT_API size_t      gut_sizeof_frame_stats(void);
 GUT_API size_t      gut_sizeof_adam_group(void);
+GUT_API size_t      gut_sizeof_adam_tensors(void);
 
 #ifdef __cplusplus
 }

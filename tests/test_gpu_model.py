@@ -378,6 +378,81 @@ def test_peer_step_then_optimizer_step_changes_the_parameters(raster):
         ex.close()
 
 
+@pytest.mark.parametrize("kind", ["deferred", "peer"])
+def test_optimizer_epilogue_leaves_the_bits_of_the_unfused_chain(raster, kind):
+    """dist.optimizer_epilogue (gut_density_adam + gut_sh_expand_adam: activation adjoints, SH expansion, SelectiveAdam and the
+    densification statistics as the epilogue of the step's gradient kernels, no gradient tensors in between) against the
+    unfused chain optimizer_step + densify_stats on the same three-view step, two steps in a row: parameters, both moments of all
+    six groups and the statistics BIT for bit; invisible rows untouched."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    from tests.helpers import camera_of
+
+    n, w, h, nv, deg = 6000, 112, 80, 3, 3
+    raw_t = _raw(n, 23)
+    raw_t["positions"] = (torch.rand((n, 3), device="cuda") * 3 - 1.5)
+    raw_t["scale"] = torch.full((n, 3), -2.5, device="cuda") + 0.3 * torch.rand((n, 3), device="cuda")
+    names = {"positions": "positions", "rotation": "rotation", "scale": "scale", "density": "density", "features_albedo": "albedo",
+             "features_specular": "specular"}
+    views, ups = [], []
+    g = torch.Generator().manual_seed(6)
+    for k in range(nv):
+        hv = syn.make_view(w, h, k=k, n_views=nv)
+        views.append({"rays_ori": hv["rays_ori"].cuda(), "rays_dir": hv["rays_dir"].cuda(), "camera": camera_of(hv)})
+        ups.append(((torch.rand((h, w, 4), generator=g) * 2 - 1).cuda(), ((torch.rand((h, w, 1), generator=g) * 2 - 1) * 0.01).cuda()))
+    sensor = [0.3, -0.2, 4.0]
+    lrs = {"positions": 1.6e-4, "rotation": 1e-3, "scale": 5e-3, "density": 5e-2, "features_albedo": 2.5e-3, "features_specular": 1.25e-4}
+
+    raw = {k: raw_t[v].clone() for k, v in names.items()}
+    state = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in raw.items()}
+    accum, denom = torch.zeros((n, 1), device="cuda"), torch.zeros((n, 1), device="cuda")
+    if kind == "peer":
+        try:
+            ex = gdist.PeerExchange(raster, n, 48, nv, "cuda", 0, world=1, track_visibility=True)
+        except RuntimeError as e:
+            pytest.skip(f"CUDA IPC unavailable: {e}")
+    else:
+        ex = gdist.DeferredExchange(n, 48, nv, "cuda", world=1, track_visibility=True)
+    try:
+        for _step in range(2):
+            packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
+            sph = raster.pack_features(raw["features_albedo"], raw["features_specular"])
+            ex.begin_step(0)
+            for i, (v, (rg, dg)) in enumerate(zip(views, ups)):
+                rgba, dist_, hits, vis = raster.trace(0, deg, packed, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
+                c = raster.trace_bwd_colour(deg, packed, sph, v["rays_ori"], v["rays_dir"], v["camera"], rgba, rg, dist_, dg, ex.slot(i))
+                ex.add_view(c, vis)
+            # the step's gradients, once (two backward passes never agree to the bit: both arms read THESE buffers)
+            _, none = ex.finish_step(raster, deg, packed, expand=False)
+            assert none is None
+            torch.cuda.synchronize()
+            vis_union = ex.visibility.clone()
+            assert 0 < float(vis_union.sum()) < n
+            # arm B: the epilogue, on copies
+            raw_b = {k: v.clone() for k, v in raw.items()}
+            state_b = {k: (m.clone(), v.clone()) for k, (m, v) in state.items()}
+            accum_b, denom_b = accum.clone(), denom.clone()
+            gdist.optimizer_epilogue(raster, ex, raw_b, packed, state_b, lrs, deg, sensor_position=sensor, grad_norm_accum=accum_b,
+                                     grad_norm_denom=denom_b)
+            # arm A: expansion into [N,48], activation adjoints, feature split, SelectiveAdam, statistics (from the positions
+            # BEFORE the update: post_backward runs before optimizer.step in the reference)
+            raster.sh_gradient_expand_gather(deg, packed, ex.centres_all, ex.colour_ptrs(), ex.radiance_grad)
+            pos_before = raw["positions"].clone()
+            before = {k: v.clone() for k, v in raw.items()}
+            grads = gdist.optimizer_step(raster, ex, raw, packed, state, lrs)
+            raster.densify_stats(pos_before, grads["positions"], sensor, accum, denom)
+            torch.cuda.synchronize()
+            inv = vis_union[:, 0] == 0
+            for k in names:
+                assert torch.equal(raw[k], raw_b[k]), (k, _step)
+                assert torch.equal(state[k][0], state_b[k][0]) and torch.equal(state[k][1], state_b[k][1]), (k, _step)
+                assert not torch.equal(raw[k], before[k]), k                      # the step moved something
+                assert torch.equal(raw_b[k][inv], before[k][inv]), k              # invisible rows untouched
+            assert torch.equal(accum, accum_b) and torch.equal(denom, denom_b) and float(denom.sum()) > 0
+    finally:
+        if kind == "peer":
+            ex.close()
+
+
 def test_two_handles_on_two_devices_in_one_process():
     """Kernel attributes (dynamic shared memory opt-in of the per-tile sort) are per device: a second handle on another GPU
     of the same process must render too."""
