@@ -267,7 +267,7 @@ int gut_create(const GutConfig* cfg, int device, GutHandle** out) {
     if (!degree_supported(cfg->kernel_degree)) return GUT_ERR_UNSUPPORTED;
     if (cfg->sph_max_degree < 0 || cfg->sph_max_degree > 3) return GUT_ERR_UNSUPPORTED;
     if (cfg->ut_require_all_sigma_points_valid) return GUT_ERR_UNSUPPORTED;  // static_assert in threedgut.cuh:73
-    if (cfg->k_buffer_size != 0 && !gut_kbuffer_size_supported(cfg->k_buffer_size)) return GUT_ERR_UNSUPPORTED;  // K in {0, 4, 8, 16}
+    if (cfg->k_buffer_size != 0 && !gut_kbuffer_size_supported(cfg->k_buffer_size)) return GUT_ERR_UNSUPPORTED;  // K in {0, 1, 2, 4, 8, 12, 16}
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return GUT_ERR_CUDA;
     GutHandle* h = new GutHandle();
@@ -571,11 +571,10 @@ int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_
     const float* view_centres = d_view_centres;
     if (!h) return GUT_ERR_BAD_INPUT;
     if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
-    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_gradient_expand is built for 16 SH coefficients");
     if (N == 0) return GUT_OK;
     if (!d_density || !d_radiance_grad || (n_views > 0 && (!view_centres || !d_colour_grads))) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_sh_expand(N, sph_degree, d_density, n_views, view_centres, d_colour_grads, d_radiance_grad, accumulate, (cudaStream_t)stream_));
+    GUT_CUDA(h, gut_launch_sh_expand(N, sph_degree, (h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1), d_density, n_views, view_centres, d_colour_grads, d_radiance_grad, accumulate, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;
 }
@@ -584,13 +583,12 @@ int gut_sh_gradient_expand_gather(GutHandle* h, void* stream_, uint32_t N, int32
                                   const float* d_view_centres, const float* const* colour_grad_ptrs, float* d_radiance_grad, int32_t accumulate) {
     if (!h) return GUT_ERR_BAD_INPUT;
     if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
-    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_sh_gradient_expand_gather is built for 16 SH coefficients");
     if (N == 0) return GUT_OK;
     if (!d_density || !d_radiance_grad || (n_views > 0 && (!d_view_centres || !colour_grad_ptrs))) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
     for (uint32_t v = 0; v < n_views; ++v)
         if (!colour_grad_ptrs[v]) return fail(h, GUT_ERR_BAD_INPUT, "colour gradient pointer of view %u is NULL", v);
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_sh_expand_ptrs(N, sph_degree, d_density, n_views, d_view_centres, colour_grad_ptrs, d_radiance_grad, accumulate,
+    GUT_CUDA(h, gut_launch_sh_expand_ptrs(N, sph_degree, (h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1), d_density, n_views, d_view_centres, colour_grad_ptrs, d_radiance_grad, accumulate,
                                           (cudaStream_t)stream_));
     h->launches += n_views == 0 ? 1 : (n_views + GUT_EXPAND_MAX_VIEWS - 1) / GUT_EXPAND_MAX_VIEWS;
     return GUT_OK;
@@ -704,12 +702,12 @@ int gut_activate_pack_backward(GutHandle* h, void* stream_, uint32_t N, const fl
 
 int gut_pack_features(GutHandle* h, void* stream_, uint32_t N, const float* d_albedo, const float* d_specular, float* d_particle_radiance) {
     if (!h) return GUT_ERR_BAD_INPUT;
-    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_pack_features is built for 16 SH coefficients (3 + 45 floats)");
+    const uint32_t ncoef = (uint32_t)((h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1));
     if (N == 0) return GUT_OK;
-    if (!d_albedo || !d_specular || !d_particle_radiance) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
-    if ((uintptr_t)d_particle_radiance & 15) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
+    if (!d_albedo || (!d_specular && ncoef > 1) || !d_particle_radiance) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (ncoef == 16 && ((uintptr_t)d_particle_radiance & 15)) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_pack_features(N, d_albedo, d_specular, d_particle_radiance, (cudaStream_t)stream_));
+    GUT_CUDA(h, gut_launch_pack_features(N, ncoef, d_albedo, d_specular, d_particle_radiance, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;
 }
@@ -717,12 +715,12 @@ int gut_pack_features(GutHandle* h, void* stream_, uint32_t N, const float* d_al
 int gut_unpack_feature_gradient(GutHandle* h, void* stream_, uint32_t N, const float* d_particle_radiance_grad, float* d_albedo_grad,
                                 float* d_specular_grad) {
     if (!h) return GUT_ERR_BAD_INPUT;
-    if (h->cfg.sph_max_degree != 3) return fail(h, GUT_ERR_UNSUPPORTED, "gut_unpack_feature_gradient is built for 16 SH coefficients (3 + 45 floats)");
+    const uint32_t ncoef = (uint32_t)((h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1));
     if (N == 0) return GUT_OK;
-    if (!d_particle_radiance_grad || !d_albedo_grad || !d_specular_grad) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
-    if ((uintptr_t)d_particle_radiance_grad & 15) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
+    if (!d_particle_radiance_grad || !d_albedo_grad || (!d_specular_grad && ncoef > 1)) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (ncoef == 16 && ((uintptr_t)d_particle_radiance_grad & 15)) return fail(h, GUT_ERR_BAD_INPUT, "[N,48] buffer must be 16-byte aligned");
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_unpack_features(N, d_particle_radiance_grad, d_albedo_grad, d_specular_grad, (cudaStream_t)stream_));
+    GUT_CUDA(h, gut_launch_unpack_features(N, ncoef, d_particle_radiance_grad, d_albedo_grad, d_specular_grad, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;
 }

@@ -73,11 +73,11 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
                                         int accumulate, cudaStream_t stream);
 
 // deferred SH backward of a multi-view step (gut_project.cu, gut_sh_expand_kernel)
-cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
+cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream);
 
 // exclusive scan of tile_hist[T*SUB] -> tile_start[T+1] and absolute sub-bucket cursors tile_cursor[T*SUB]; stats[0]=M, stats[1]=max list
-cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
+cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
                                       const float* const* colour_ptrs /* host array of device pointers */, float* sph_grad, int accumulate,
                                       cudaStream_t stream);
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
@@ -131,8 +131,8 @@ cudaError_t gut_launch_activate_pack(uint32_t N, const float* pos, const float* 
                                      int density_act, float* out12, cudaStream_t stream);
 cudaError_t gut_launch_activate_backward(uint32_t N, const float* rot, const float* packed12, const float* grad12, int scale_act, int density_act,
                                          float* pos_g, float* rot_g, float* scale_g, float* dens_g, cudaStream_t stream);
-cudaError_t gut_launch_pack_features(uint32_t N, const float* albedo, const float* specular, float* out48, cudaStream_t stream);
-cudaError_t gut_launch_unpack_features(uint32_t N, const float* grad48, float* albedo_g, float* specular_g, cudaStream_t stream);
+cudaError_t gut_launch_pack_features(uint32_t N, uint32_t ncoef, const float* albedo, const float* specular, float* out, cudaStream_t stream);
+cudaError_t gut_launch_unpack_features(uint32_t N, uint32_t ncoef, const float* grad, float* albedo_g, float* specular_g, cudaStream_t stream);
 cudaError_t gut_launch_selective_adam(uint32_t N, const GutAdamGroup* groups, uint32_t n_groups, const float* visibility, float b1, float b2,
                                       float eps, int zero_grad, cudaStream_t stream);
 cudaError_t gut_launch_density_adam(uint32_t N, const float* packed12, const float* grad12, const GutAdamTensors& pos, const GutAdamTensors& rot,

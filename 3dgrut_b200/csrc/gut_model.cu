@@ -118,6 +118,20 @@ __global__ void __launch_bounds__(MODEL_THREADS) gut_unpack_features_kernel(uint
     }
 }
 
+// Any coefficient count (sph_max_degree 0..2: 1, 4, 9 coefficients): one thread per float of the [N, 3 ncoef] side, both sides
+// read / written as contiguous spans.  PACK = true: cat; false: the split of the gradient.
+template <bool PACK>
+__global__ void __launch_bounds__(MODEL_THREADS) gut_features_generic_kernel(uint64_t total, uint32_t width, float* __restrict__ albedo,
+                                                                            float* __restrict__ specular, float* __restrict__ packed) {
+    const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    const uint64_t row = e / width;
+    const uint32_t c = (uint32_t)(e - row * width);
+    float* side = c < 3 ? albedo + 3 * row + c : specular + (uint64_t)(width - 3) * row + (c - 3);
+    if (PACK) packed[e] = *side;
+    else *side = packed[e];
+}
+
 // ---------------------------------------------------------------------------------------------------
 // SelectiveAdam for every parameter group in one launch.
 // reference: selective_adam_update_kernel (threedgrut/optimizers/optimizers.cu:47-84) is launched once per group with
@@ -309,17 +323,29 @@ cudaError_t gut_launch_activate_backward(uint32_t N, const float* rot, const flo
     return cudaGetLastError();
 }
 
-cudaError_t gut_launch_pack_features(uint32_t N, const float* albedo, const float* specular, float* out48, cudaStream_t stream) {
+cudaError_t gut_launch_pack_features(uint32_t N, uint32_t ncoef, const float* albedo, const float* specular, float* out, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    const uint64_t n_vec = 12ull * N;
-    gut_pack_features_kernel<<<blocks_for(n_vec), MODEL_THREADS, 0, stream>>>(n_vec, albedo, specular, reinterpret_cast<float4*>(out48));
+    if (ncoef == 16) {
+        const uint64_t n_vec = 12ull * N;
+        gut_pack_features_kernel<<<blocks_for(n_vec), MODEL_THREADS, 0, stream>>>(n_vec, albedo, specular, reinterpret_cast<float4*>(out));
+    } else {
+        const uint64_t total = 3ull * ncoef * N;
+        gut_features_generic_kernel<true><<<blocks_for(total), MODEL_THREADS, 0, stream>>>(total, 3 * ncoef, const_cast<float*>(albedo),
+                                                                                          const_cast<float*>(specular), out);
+    }
     return cudaGetLastError();
 }
 
-cudaError_t gut_launch_unpack_features(uint32_t N, const float* grad48, float* albedo_g, float* specular_g, cudaStream_t stream) {
+cudaError_t gut_launch_unpack_features(uint32_t N, uint32_t ncoef, const float* grad, float* albedo_g, float* specular_g, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    const uint64_t n_vec = 12ull * N;
-    gut_unpack_features_kernel<<<blocks_for(n_vec), MODEL_THREADS, 0, stream>>>(n_vec, reinterpret_cast<const float4*>(grad48), albedo_g, specular_g);
+    if (ncoef == 16) {
+        const uint64_t n_vec = 12ull * N;
+        gut_unpack_features_kernel<<<blocks_for(n_vec), MODEL_THREADS, 0, stream>>>(n_vec, reinterpret_cast<const float4*>(grad), albedo_g, specular_g);
+    } else {
+        const uint64_t total = 3ull * ncoef * N;
+        gut_features_generic_kernel<false><<<blocks_for(total), MODEL_THREADS, 0, stream>>>(total, 3 * ncoef, albedo_g, specular_g,
+                                                                                           const_cast<float*>(grad));
+    }
     return cudaGetLastError();
 }
 

@@ -684,7 +684,8 @@ constexpr int EXPAND_CHUNK = 8;
 __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                    uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
                                                                    ExpandViews views,
-                                                                   float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate) {
+                                                                   float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate,
+                                                                   int ncoef_all /* (sph_max_degree + 1)^2: the row holds 3 ncoef_all floats */) {
     __shared__ float s_out[K6_WARPS][32][49];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -724,6 +725,15 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
                 }
             }
         }
+    }
+    if (ncoef_all != 16) {   // sph_max_degree 0..2: per-thread rows of 3, 12 or 27 floats (coefficients beyond the active degree are zero)
+        if (i < N) {
+            float* row = reinterpret_cast<float*>(sph_grad) + (size_t)i * ncoef_all * 3;
+#pragma unroll
+            for (int k = 0; k < 27; ++k)
+                if (k < 3 * ncoef_all) row[k] = accumulate ? row[k] + acc[k] : acc[k];
+        }
+        return;
     }
 #pragma unroll
     for (int k = 0; k < 48; ++k) s_out[wid][lane][k] = acc[k];
@@ -866,7 +876,7 @@ cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* d
 
 // colour_ptrs: HOST array of n_views device pointers.  More than GUT_EXPAND_MAX_VIEWS views are expanded in several
 // launches, the later ones accumulating.
-cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres,
                                       const float* const* colour_ptrs, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     uint32_t done = 0;
@@ -876,23 +886,23 @@ cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, const float* d
         for (uint32_t v = 0; v < nv; ++v) views.colour[v] = colour_ptrs[done + v];
         gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
             N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
-            reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0);
+            reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0, ncoef_all);
         done += nv;
     } while (done < n_views);
     return cudaGetLastError();
 }
 
-cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
+cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres,
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    if (n_views == 0) return gut_launch_sh_expand_ptrs(N, sph_degree, density12, 0, centres, nullptr, sph_grad, accumulate, stream);
+    if (n_views == 0) return gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, 0, centres, nullptr, sph_grad, accumulate, stream);
     uint32_t done = 0;
     cudaError_t e = cudaSuccess;
     while (done < n_views && e == cudaSuccess) {   // contiguous [n_views][N][3] buffer -> pointer table, one chunk per launch
         const float* ptrs[GUT_EXPAND_MAX_VIEWS];
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         for (uint32_t v = 0; v < nv; ++v) ptrs[v] = colour_grads + 3 * (size_t)(done + v) * N;
-        e = gut_launch_sh_expand_ptrs(N, sph_degree, density12, nv, centres + 3 * (size_t)done, ptrs, sph_grad, (accumulate || done > 0) ? 1 : 0, stream);
+        e = gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, nv, centres + 3 * (size_t)done, ptrs, sph_grad, (accumulate || done > 0) ? 1 : 0, stream);
         done += nv;
     }
     return e;

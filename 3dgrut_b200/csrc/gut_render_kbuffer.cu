@@ -404,7 +404,8 @@ cudaError_t launch_bwd(const GutConfig& cfg, const GutFrame& frame, const uint32
 
 }  // namespace
 
-bool gut_kbuffer_size_supported(int k) { return k == 4 || k == 8 || k == 16; }
+// every K the 4-bit payload slot allows that is a power of two, plus 12 (the reference: any compile-time K, setup_3dgut.py:57)
+bool gut_kbuffer_size_supported(int k) { return k == 1 || k == 2 || k == 4 || k == 8 || k == 12 || k == 16; }
 
 #define GUT_DISPATCH_DEG_K(deg, k, CALL)                                  \
     switch (deg) {                                                        \
@@ -419,8 +420,11 @@ bool gut_kbuffer_size_supported(int k) { return k == 4 || k == 8 || k == 16; }
     }
 #define GUT_DISPATCH_K(D, k, CALL)                                        \
     switch (k) {                                                          \
+    case 1: return CALL(D, 1);                                            \
+    case 2: return CALL(D, 2);                                            \
     case 4: return CALL(D, 4);                                            \
     case 8: return CALL(D, 8);                                            \
+    case 12: return CALL(D, 12);                                          \
     case 16: return CALL(D, 16);                                          \
     default: return cudaErrorInvalidValue;                                \
     }

@@ -495,9 +495,10 @@ class SplatRaster:
         alb = _check_cuda_f32("features_albedo", features_albedo, dev)
         spc = _check_cuda_f32("features_specular", features_specular, dev)
         n = alb.shape[0]
-        if alb.shape != (n, 3) or spc.shape != (n, 45):
-            raise GutError(abi.GutStatus.BAD_INPUT, "expected features_albedo [N,3] and features_specular [N,45]")
-        out = torch.empty((n, 48), dtype=torch.float32, device=dev)
+        ns = 3 * (self.n_coeffs - 1)
+        if alb.shape != (n, 3) or spc.shape != (n, ns):
+            raise GutError(abi.GutStatus.BAD_INPUT, f"expected features_albedo [N,3] and features_specular [N,{ns}]")
+        out = torch.empty((n, 3 * self.n_coeffs), dtype=torch.float32, device=dev)
         rc = self.lib.gut_pack_features(self._h, self._stream(), n, _ptr(alb), _ptr(spc), _ptr(out))
         if rc != 0:
             self._raise(rc)
@@ -508,10 +509,10 @@ class SplatRaster:
         dev = self.device
         g = _check_cuda_f32("radiance_grad", radiance_grad, dev)
         n = g.shape[0]
-        if g.shape != (n, 48):
-            raise GutError(abi.GutStatus.BAD_INPUT, "radiance_grad must be [N,48]")
+        if g.shape != (n, 3 * self.n_coeffs):
+            raise GutError(abi.GutStatus.BAD_INPUT, f"radiance_grad must be [N,{3 * self.n_coeffs}]")
         alb = torch.empty((n, 3), dtype=torch.float32, device=dev)
-        spc = torch.empty((n, 45), dtype=torch.float32, device=dev)
+        spc = torch.empty((n, 3 * (self.n_coeffs - 1)), dtype=torch.float32, device=dev)
         rc = self.lib.gut_unpack_feature_gradient(self._h, self._stream(), n, _ptr(g), _ptr(alb), _ptr(spc))
         if rc != 0:
             self._raise(rc)

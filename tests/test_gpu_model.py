@@ -378,6 +378,21 @@ def test_peer_step_then_optimizer_step_changes_the_parameters(raster):
         ex.close()
 
 
+@pytest.mark.parametrize("max_deg", [0, 1, 2])
+def test_feature_packing_for_every_sh_degree(max_deg):
+    """gut_pack_features / gut_unpack_feature_gradient with particle_radiance_sph_degree 0..2 (1, 4, 9 coefficients):
+    torch.cat((albedo, specular), dim=1) and its split, bit for bit."""
+    native = importlib.import_module("3dgrut_b200.native")
+    r = native.SplatRaster(cfg_from_conf(make_conf(particle_radiance_sph_degree=max_deg)))
+    n, ns = 10_007, 3 * ((max_deg + 1) ** 2 - 1)
+    g = torch.Generator(device="cuda").manual_seed(max_deg)
+    alb = torch.randn((n, 3), device="cuda", generator=g); spc = torch.randn((n, ns), device="cuda", generator=g)
+    packed = r.pack_features(alb, spc)
+    assert torch.equal(packed, torch.cat((alb, spc), dim=1))
+    a2, s2 = r.unpack_feature_gradient(packed)
+    assert torch.equal(a2, alb) and torch.equal(s2, spc)
+
+
 @pytest.mark.parametrize("kind", ["deferred", "peer"])
 def test_optimizer_epilogue_leaves_the_bits_of_the_unfused_chain(raster, kind):
     """dist.optimizer_epilogue (gut_density_adam + gut_sh_expand_adam: activation adjoints, SH expansion, SelectiveAdam and the
