@@ -140,8 +140,11 @@ class DeferredExchange:
         lo = self.local_slot(self._rank, 0)
         mine = self.colour_all[lo:lo + self.views_per_rank]
         centres = list(self._centres)
+        rasters = list(raster) if isinstance(raster, (list, tuple)) else [raster]
+        raster = rasters[0]
         if self.views_per_rank > 1:
-            raster.density_gradient_finish(particle_density, self.density_grad)   # zeros when this rank had no view
+            for j, r in enumerate(rasters):      # every lane's view-summed accumulators; zeros when this rank had no view
+                r.density_gradient_finish(particle_density, self.density_grad, accumulate=j > 0)
         elif not centres:
             self.density_grad.zero_()   # one view per rank and none for this rank in this step
         for i in range(len(centres), self.views_per_rank):
@@ -165,20 +168,58 @@ class DeferredExchange:
         return self.density_grad, (radiance if expand else None)
 
 
+def _lanes(raster):
+    """``raster`` may be ONE SplatRaster or a list of them ("lanes"): the views of a step are then dealt round-robin to the
+    lanes, each on a CUDA stream of its own, so that the short latency-bound kernels of one view (projection, scan, emit, sort,
+    per-view fold) run under the compositing kernels of another and fill the ends of their grids.  Every lane sums its views'
+    accumulators in its own handle; ``finish_step`` converts them one after the other into the same [N,12] buffer."""
+    lanes = list(raster) if isinstance(raster, (list, tuple)) else [raster]
+    if len(lanes) > 1:
+        for r in lanes:
+            if getattr(r, "_lane_stream", None) is None:
+                r._lane_stream = torch.cuda.Stream(device=r.device)
+    return lanes
+
+
 def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
     """Same result as ``training_step`` (summed [N,12] and [N,48] gradients on every rank) with the SH expansion deferred.
     Every rank must hold ``ex.views_per_rank`` views or fewer (missing ones contribute zeros).  Works with a
-    ``DeferredExchange`` (NCCL all-gather of the colour gradients) and with a ``PeerExchange`` (peer-memory loads)."""
+    ``DeferredExchange`` (NCCL all-gather of the colour gradients) and with a ``PeerExchange`` (peer-memory loads).
+    ``raster``: one SplatRaster, or a list of them to overlap consecutive views on separate streams (``_lanes``)."""
     outs = []
     ex.begin_step(rank)
+    lanes = _lanes(raster)
+    if len(lanes) == 1 or len(views) < 2:
+        r = lanes[0]
+        for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
+            rgba, dist_, hits, vis = r.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
+                                             v["camera"])
+            c = r.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
+                                   rgba, rg, dist_, dg, ex.slot(i), out_density_grad=ex.density_out(i))
+            ex.add_view(c, vis)
+            outs.append((rgba, dist_))
+        ex.finish_step(r, sph_degree, particle_density)
+        return outs
+    cur = torch.cuda.current_stream()
+    for r in lanes:
+        r._lane_stream.wait_stream(cur)      # the step's inputs are ready
+    seen = []
     for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
-        rgba, dist_, hits, vis = raster.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
-                                              v["camera"])
-        c = raster.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
-                                    rgba, rg, dist_, dg, ex.slot(i), out_density_grad=ex.density_out(i))
-        ex.add_view(c, vis)
+        r = lanes[i % len(lanes)]
+        with torch.cuda.stream(r._lane_stream):
+            rgba, dist_, hits, vis = r.trace(0, sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], None,
+                                             v["camera"])
+            c = r.trace_bwd_colour(sph_degree, particle_density, particle_radiance, v["rays_ori"], v["rays_dir"], v["camera"],
+                                   rgba, rg, dist_, dg, ex.slot(i))
+            for t in (rgba, dist_, vis):
+                t.record_stream(cur)
+        seen.append((c, vis))
         outs.append((rgba, dist_))
-    ex.finish_step(raster, sph_degree, particle_density)
+    for r in lanes:
+        cur.wait_stream(r._lane_stream)
+    for c, vis in seen:
+        ex.add_view(c, vis)
+    ex.finish_step(lanes, sph_degree, particle_density)
     return outs
 
 
@@ -309,8 +350,11 @@ class PeerExchange(DeferredExchange):
             gathered = dist.all_gather_into_tensor(self.centres_all.view(-1), self.my_centres.view(-1), async_op=True)
         else:
             self.centres_all.copy_(self.my_centres)
+        rasters = list(raster) if isinstance(raster, (list, tuple)) else [raster]
+        raster = rasters[0]
         if self.views_per_rank > 1:
-            raster.density_gradient_finish(particle_density, self.density_grad)   # overlaps the ordering point
+            for j, r in enumerate(rasters):      # every lane's view-summed accumulators; overlaps the ordering point
+                r.density_gradient_finish(particle_density, self.density_grad, accumulate=j > 0)
         elif not self._centres:
             self.density_grad.zero_()   # one view per rank and none for this rank in this step
         self._mark("density_finish")

@@ -164,7 +164,7 @@ class Tracer:
 
         @staticmethod
         def forward(ctx, step, view_index, anchor, ray_ori, ray_dir, sensor):
-            w = step.tracer.tracer_wrapper
+            w = step.lane(view_index)
             rgba, dist, hits, vis = w.trace(view_index, step.n_active_features, step.particle_density, step.particle_radiance,
                                             ray_ori, ray_dir, None, sensor)
             ctx.save_for_backward(ray_ori, ray_dir, rgba, dist)
@@ -188,6 +188,7 @@ class Tracer:
         self._normals, self._normals_key = None, None
         torch.zeros(1, device=self.device)  # force CUDA context creation, as the reference does (tracer.py:292)
         self.tracer_wrapper = SplatRaster(config_from_conf(conf))
+        self._lane_wrappers = [self.tracer_wrapper]
 
     @property
     def timings(self):
@@ -205,21 +206,33 @@ class Tracer:
     def build_acc(self, gaussians, rebuild=True):
         pass  # 3DGUT has no acceleration structure (tracer.py:301-302)
 
-    def begin_step(self, gaussians, exchange=None, views_per_rank=None, rank=0):
+    def _step_lanes(self, n):
+        """The step's rasteriser handles ("lanes", 3dgrut_b200.dist._lanes): the plugin's own plus n - 1 more, created on first use."""
+        gdist = __import__("importlib").import_module(__package__ + ".dist")
+        while len(self._lane_wrappers) < n:
+            self._lane_wrappers.append(SplatRaster(config_from_conf(self.conf)))
+        return gdist._lanes(self._lane_wrappers[:n])
+
+    def begin_step(self, gaussians, exchange=None, views_per_rank=None, rank=0, lanes=None):
         """Multi-view training step (this build's extension; the reference renders one view per step, trainer.py:143-149):
 
             step = tracer.begin_step(gaussians, exchange)      # parameters activated + packed ONCE for all views
             for batch in batches:
                 out = step.render(batch)                        # same dict as Tracer.render
-                loss_fn(out).backward()                         # per view, BEFORE the next step.render
+                step.backward(loss_fn(out))                     # per view, BEFORE the next step.render (= loss.backward() that
+                                                                # does not hold the caller's stream back, see TracerStep.backward)
             step.finish()                                       # gradients of all views summed into the parameters' .grad
 
         The views' backward passes leave 12 B per particle and view (dL/dcolour) plus view-independent accumulators inside the
         rasteriser; finish() turns them into [N,12] / [N,48] once (gut_density_gradient_finish, gut_sh_gradient_expand), runs the
         data-parallel exchange when ``exchange`` spans several ranks (3dgrut_b200.dist.DeferredExchange / PeerExchange), applies
         the activation adjoints and accumulates into ``.grad`` like autograd would.  Without ``exchange`` a single-rank one is
-        created for ``views_per_rank`` views (default 8) and reused across steps."""
-        return TracerStep(self, gaussians, exchange, views_per_rank, rank)
+        created for ``views_per_rank`` views (default 8) and reused across steps.
+        ``lanes`` (default ``conf.render.step_lanes``, 2): consecutive views go to that many rasteriser handles on CUDA streams of
+        their own, so the projection / binning kernels of a view run under the backward of the previous one; 1 = one stream."""
+        if lanes is None:
+            lanes = int(_get(self.conf, "render.step_lanes", 2))
+        return TracerStep(self, gaussians, exchange, views_per_rank, rank, max(1, lanes))
 
     def render(self, gaussians, gpu_batch, train=False, frame_id=0):
         rays_o = gpu_batch.rays_ori
@@ -262,12 +275,13 @@ class Tracer:
 class TracerStep:
     """One multi-view step in flight (see Tracer.begin_step)."""
 
-    def __init__(self, tracer, gaussians, exchange, views_per_rank, rank):
+    def __init__(self, tracer, gaussians, exchange, views_per_rank, rank, lanes=1):
         from . import dist as gdist
 
         self.tracer, self.gaussians, self.rank = tracer, gaussians, rank
         w = tracer.tracer_wrapper
         w.set_training(True)
+        self._n_lanes = lanes
         self.n_active_features = gaussians.n_active_features
         self.raw = _raw_parameters(gaussians) if tracer.fused_activations else None
         if self.raw is not None:
@@ -295,13 +309,22 @@ class TracerStep:
                 tracer._step_exchange = cached
             exchange = cached
         self.exchange = exchange
+        # one view per rank has nothing to overlap (and its backward writes [N,12] directly)
+        self.lanes = tracer._step_lanes(self._n_lanes if exchange.views_per_rank > 1 else 1)
+        for r in self.lanes[1:]:
+            r.set_training(True)
         self.anchor = torch.zeros(1, device=self.particle_density.device, requires_grad=True)
+        self._seen = []           # (view centre, visibility) of the views whose backward has run, in order
         self.n_views = 0          # forwards issued
         self.n_backward = 0       # backwards done
         self._open = None         # view whose forward context the rasteriser currently holds
         self.finished = False
-        w.reset_gradients()       # nothing pending from an abandoned step
+        for r in self.lanes:
+            r.reset_gradients()   # nothing pending from an abandoned step
         exchange.begin_step(rank)
+
+    def lane(self, view_index):
+        return self.lanes[view_index % len(self.lanes)]
 
     def render(self, gpu_batch, train=True):
         if self.finished:
@@ -316,8 +339,20 @@ class TracerStep:
         i = self.n_views
         self.n_views += 1
         self._open = i
-        rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, gpu_batch.rays_ori.contiguous(),
-                                                           gpu_batch.rays_dir.contiguous(), sensor)
+        ray_ori, ray_dir = gpu_batch.rays_ori.contiguous(), gpu_batch.rays_dir.contiguous()
+        if len(self.lanes) > 1:
+            # the view runs on its lane's stream: it starts once the caller's stream has produced its inputs and the caller's
+            # stream continues once the view's forward is done.  Autograd runs the view's backward on the lane's stream too, so
+            # the NEXT view's forward (other lane) is not queued behind it.
+            cur, side = torch.cuda.current_stream(), self.lane(i)._lane_stream
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, ray_ori, ray_dir, sensor)
+            cur.wait_stream(side)
+            for t_ in (rgba, dist, hits, vis):
+                t_.record_stream(cur)
+        else:
+            rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, ray_ori, ray_dir, sensor)
         pred_rgb = rgba[..., :3].unsqueeze(0).contiguous()
         pred_opacity = rgba[..., 3:].unsqueeze(0).contiguous()
         pred_rgb, pred_opacity = self.gaussians.background(gpu_batch.T_to_world.contiguous(), gpu_batch.rays_dir, pred_rgb, pred_opacity, train)
@@ -326,14 +361,39 @@ class TracerStep:
                 "pred_normals": t._constant_normals(pred_rgb), "hits_count": hits.unsqueeze(0).contiguous(),
                 "frame_time_ms": timings["forward_render"] if "forward_render" in timings else 0.0, "mog_visibility": vis}
 
+    def backward(self, loss, **kwargs):
+        """``loss.backward()`` for the view rendered last, with the view's lane as the ambient stream.  torch makes the stream
+        that is current when ``backward()`` is called wait for every stream its graph ran on; called on the caller's stream
+        that wait would put the next view's forward behind this view's backward kernels and undo the lanes' overlap.  With one
+        lane it is plain ``loss.backward()``.
+        Returns a CUDA event recorded behind the view's backward kernels: the view's input tensors (rays, upstream gradients
+        the caller built) may be overwritten once it has fired -- the caller's stream alone no longer tells."""
+        done = torch.cuda.Event()
+        if len(self.lanes) > 1 and self.n_views > 0:
+            side = self.lane(self.n_views - 1)._lane_stream
+            with torch.cuda.stream(side):
+                loss.backward(**kwargs)
+                done.record(side)
+        else:
+            loss.backward(**kwargs)
+            done.record(torch.cuda.current_stream())
+        return done
+
     def _view_backward(self, i, sensor, ray_ori, ray_dir, rgba, rgba_grad, dist, dist_grad, vis):
         if self._open != i:
             raise RuntimeError(f"backward of view {i} after another view was rendered: its forward context is gone")
-        w = self.tracer.tracer_wrapper
+        w = self.lane(i)
+        if len(self.lanes) > 1:
+            # the kernels below run on the lane's stream; tensors that were allocated on another one (the upstream gradients
+            # autograd built on the caller's stream, the rays) must not return to that stream's pool while they are read
+            side = w._lane_stream
+            rgba_grad, dist_grad = rgba_grad.contiguous(), dist_grad.contiguous()
+            for t_ in (ray_ori, ray_dir, rgba, dist, rgba_grad, dist_grad):
+                t_.record_stream(side)
         c = w.trace_bwd_colour(self.n_active_features, self.particle_density, self.particle_radiance, ray_ori, ray_dir, sensor,
                                rgba, rgba_grad.contiguous(), dist, dist_grad.contiguous(), self.exchange.slot(i),
                                out_density_grad=self.exchange.density_out(i))
-        self.exchange.add_view(c, vis)
+        self._seen.append((c, vis))      # handed to the exchange by finish(): the lanes' streams must not race on its buffers
         self.n_backward += 1
         self._open = None
 
@@ -347,16 +407,22 @@ class TracerStep:
             direct = self.exchange.density_out(self._open)
             if direct is not None:     # one view per rank: no backward wrote the step's [N,12] gradient
                 direct.zero_()
-            self.exchange.add_view([0.0, 0.0, 0.0], None)
+            self._seen.append(([0.0, 0.0, 0.0], None))
             self._open = None
         self.finished = True
         w = self.tracer.tracer_wrapper
+        if len(self.lanes) > 1:
+            cur = torch.cuda.current_stream()
+            for r in self.lanes:
+                cur.wait_stream(r._lane_stream)      # every view's backward has been queued on its lane: wait for them here
+        for c, vis in self._seen:
+            self.exchange.add_view(c, vis)
         # activated leaves take the [N,48] gradient as it is: the expansion writes into a fresh tensor that becomes the
         # parameter's .grad (the exchange's own buffer is reused by the next step, a copy out of it was 576 MB per step)
         fresh = None
         if self.raw is None and self.leaves[4].requires_grad:
             fresh = torch.empty_like(self.particle_radiance)
-        g12, g48 = self.exchange.finish_step(w, self.n_active_features, self.particle_density, radiance_out=fresh)
+        g12, g48 = self.exchange.finish_step(self.lanes, self.n_active_features, self.particle_density, radiance_out=fresh)
         if self.raw is not None:
             pos, rot, scl, dns, alb, spc = self.leaves
             pos_g, rot_g, scl_g, dns_g = w.activate_pack_backward(rot, self.particle_density, g12, *self.raw)

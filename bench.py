@@ -47,6 +47,7 @@ def parse_args():
     p.add_argument("--height", type=int, default=H_IMG)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--lanes", type=int, default=2, help="handles / CUDA streams a rank deals its views to (1 = one stream)")
     p.add_argument("--exchange", choices=("auto", "peer", "deferred", "allreduce"), default="auto",
                    help="gradient exchange of the step: deferred = allreduce [N,12] + all-gather per-view colour gradients, SH expansion "
                         "once per step (3dgrut_b200/dist.py training_step_deferred); peer = the same with the all-gather folded into the "
@@ -317,6 +318,10 @@ def run_ours(args):
 
     cfg = abi.default_config(enable_kernel_timings=1)
     raster = native.SplatRaster(cfg, device=dev)
+    # a second handle ("lane", 3dgrut_b200/dist.py _lanes): consecutive views of a rank's share run on two streams, so that the
+    # latency-bound kernels of one view sit under the compositing kernels of the other.  Nothing to overlap with one view per rank.
+    n_my_views = len(my_view_ids)
+    lanes = [raster] + ([native.SplatRaster(cfg, device=dev)] if (args.lanes > 1 and n_my_views > 1) else [])
     if args.exchange == "auto":
         args.exchange = "peer" if world > 1 else "deferred"
     if args.exchange == "peer":
@@ -339,18 +344,19 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def step():
+    def step(use=None):
+        use = lanes if use is None else use
         if args.exchange == "peer":
-            return gdist.training_step_peer(raster, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
+            return gdist.training_step_peer(use, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
         if args.exchange == "deferred":
-            return gdist.training_step_deferred(raster, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
+            return gdist.training_step_deferred(use, exchange, views, SPH_DEGREE, d12, sph, upstream, rank=rank)
         return gdist.training_step(raster, exchange, views, SPH_DEGREE, d12, sph, upstream)
 
     for _ in range(args.warmup):
         step()
     barrier()
     raster.stage_times()  # drop warm-up timings
-    launches0 = raster.frame_stats()["kernel_launches"]
+    launches0 = sum(r.frame_stats()["kernel_launches"] for r in lanes)
     sampler = ClockSampler(physical_gpu_index(local_rank))
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -366,11 +372,31 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total = float(t.item())
-    launches = raster.frame_stats()["kernel_launches"] - launches0
+    launches = sum(r.frame_stats()["kernel_launches"] for r in lanes) - launches0
     stage_ms = raster.stage_times()
+    ms_one_lane = None
+    if len(lanes) > 1:
+        # With two lanes kernels of different views overlap and a kernel's CUDA events measure the contention too: the per-stage
+        # times (roofline, stage_ms) come from the same steps run on ONE lane right here, and that step time is reported beside
+        # the timed one.
+        for _ in range(2):
+            step([raster])
+        barrier()
+        raster.stage_times()
+        o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        o0.record()
+        for _ in range(args.steps):
+            step([raster])
+        o1.record()
+        barrier()
+        to = torch.tensor([o0.elapsed_time(o1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(to, op=dist.ReduceOp.MAX)
+        ms_one_lane = float(to.item()) / args.steps
+        stage_ms = raster.stage_times()
     # what a step spends outside its views' kernels (gradient conversion, exchange, waiting for the slowest rank): the step time
     # minus this rank's per-view stage times; and, untimed, three more steps with CUDA events between the phases of the exchange
-    step_tail_ms = ms_total / args.steps - len(views) * sum(stage_ms.values())
+    step_tail_ms = (ms_one_lane if ms_one_lane is not None else ms_total / args.steps) - len(views) * sum(stage_ms.values())
     exchange_phases = None
     if hasattr(exchange, "phase_times"):
         exchange.profile = {}
@@ -465,7 +491,7 @@ def run_ours(args):
         # the rendered RGBA goes back as ONE contiguous device->host copy per view.  All copies are inside the timed region.
         copy_stream = torch.cuda.Stream(device=dev)     # host -> device
         back_stream = torch.cuda.Stream(device=dev)     # device -> host: its own stream, the two directions have their own engines
-        nbuf = 2
+        nbuf = 3   # a set is free again only when its view's BACKWARD has run (two views later with two lanes)
         dev_in = [{"rays_ori": torch.empty((1, h, w, 3), device=dev), "rays_dir": torch.empty((1, h, w, 3), device=dev),
                    "T_to_world": torch.empty((1, 4, 4), device=dev), "rg": torch.empty((h, w, 4), device=dev),
                    "dg": torch.empty((h, w, 1), device=dev)} for _ in range(nbuf)]
@@ -529,13 +555,14 @@ def run_ours(args):
                 rg, dg = dev_in[bi]["rg"], dev_in[bi]["dg"]
                 o = tstep.render(make_batch(dv, dev, pose_device="cpu"))
                 loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
-                loss.backward()
+                # loss.backward() with the view's lane as ambient stream (TracerStep.backward); the event fires behind the view's
+                # backward kernels: only then may this buffer set (rays, upstream gradients) be overwritten
+                free_ev[bi] = tstep.backward(loss)
                 if back_ev[bi] is not None:
                     cur.wait_event(back_ev[bi])       # the read-back that last used this image buffer has ended
                 torch.cat([o["pred_rgb"][0].detach(), o["pred_opacity"][0].detach()], dim=-1, out=rgba_dev[bi])
                 done = torch.cuda.Event()
                 done.record(cur)
-                free_ev[bi] = done
                 with torch.cuda.stream(back_stream):
                     back_stream.wait_event(done)
                     out_host.copy_(rgba_dev[bi], non_blocking=True)
@@ -823,7 +850,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "step_breakdown": tails,
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "lanes": len(lanes), "ms_per_step_one_lane": ms_one_lane, "step_breakdown": tails,
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,

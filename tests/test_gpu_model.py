@@ -496,8 +496,8 @@ def _loss(out, seed):
         0.01 * (out["pred_dist"] * torch.rand(out["pred_dist"].shape, device="cuda", generator=gen)).sum()
 
 
-@pytest.mark.parametrize("fused,nonleaf", [(True, False), (False, False), (False, True)])
-def test_multi_view_step_equals_per_view_render(fused, nonleaf):
+@pytest.mark.parametrize("fused,nonleaf,lanes", [(True, False, 2), (False, False, 2), (False, True, 2), (True, False, 1), (False, False, 3)])
+def test_multi_view_step_equals_per_view_render(fused, nonleaf, lanes):
     """Tracer.begin_step / step.render / step.finish (deferred gradient conversions, one per step) against the reference-shaped
     loop Tracer.render + backward per view: same images, same summed gradients on the parameters -- raw parameters through
     the fused activation kernels, activated leaf tensors, and activated NON-leaf tensors (the model's own torch activations:
@@ -525,11 +525,15 @@ def test_multi_view_step_equals_per_view_render(fused, nonleaf):
         _loss(out, k).backward()
         imgs_a.append(out["pred_rgb"].detach().clone())
     gb = model()
-    step = tracer.begin_step(gb, views_per_rank=nv)
+    step = tracer.begin_step(gb, views_per_rank=nv, lanes=lanes)     # views dealt to `lanes` handles on streams of their own
+    assert len(step.lanes) == lanes
     imgs_b = []
     for k, v in enumerate(views):
         out = step.render(make_batch(v, "cuda"))
-        _loss(out, k).backward()
+        if k % 2:
+            _loss(out, k).backward()          # plain autograd call ...
+        else:
+            step.backward(_loss(out, k))      # ... and the one that keeps the caller's stream free of the view's backward
         imgs_b.append(out["pred_rgb"].detach().clone())
     vis = step.finish()
     torch.cuda.synchronize()

@@ -286,6 +286,35 @@ def test_deferred_sh_gradient_equals_per_view_accumulation(pkg, max_deg):
     assert rel_l2(dx.radiance_grad.cpu().numpy(), ex.radiance_grad.cpu().numpy()) <= 1e-5
 
 
+def test_two_lane_step_equals_one_lane_step(pkg):
+    """dist.training_step_deferred with TWO handles ("lanes": consecutive views on two CUDA streams, each lane summing its own
+    accumulators, converted one after the other into the same [N,12] buffer) == the one-lane step; five views, so the lanes hold
+    three and two; twice in a row."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    n, w, h, deg, nv = 5000, 96, 64, 3, 5
+    scene = syn.make_scene(n, 3, seed=19)
+    d12 = syn.pack_density(scene).cuda(); sph = scene["features"].cuda()
+    views, ups = [], []
+    g = torch.Generator().manual_seed(7)
+    for k in range(nv):
+        hv = syn.make_view(w, h, k=k, n_views=nv)
+        views.append({"rays_ori": hv["rays_ori"].cuda(), "rays_dir": hv["rays_dir"].cuda(), "camera": camera_of(hv)})
+        ups.append(((torch.rand((h, w, 4), generator=g) * 2 - 1).cuda(), ((torch.rand((h, w, 1), generator=g) * 2 - 1) * 0.01).cuda()))
+    one = gdist.DeferredExchange(n, 48, nv, "cuda", world=1, track_visibility=True)
+    outs1 = gdist.training_step_deferred(_raster(pkg), one, views, deg, d12, sph, ups)
+    two = gdist.DeferredExchange(n, 48, nv, "cuda", world=1, track_visibility=True)
+    lanes = [_raster(pkg), _raster(pkg)]
+    for _ in range(2):
+        outs2 = gdist.training_step_deferred(lanes, two, views, deg, d12, sph, ups)
+        torch.cuda.synchronize()
+        for (a, b), (c, d) in zip(outs1, outs2):
+            assert torch.equal(a, c) and torch.equal(b, d)                      # the images are the same bits
+        assert float(one.radiance_grad.abs().max()) > 0
+        assert rel_l2(two.density_grad.cpu().numpy(), one.density_grad.cpu().numpy()) <= 1e-5
+        assert rel_l2(two.radiance_grad.cpu().numpy(), one.radiance_grad.cpu().numpy()) <= 1e-5
+        assert torch.equal(two.visibility, one.visibility)
+
+
 def test_one_view_per_rank_step_writes_the_density_gradient_directly(pkg):
     """views_per_rank == 1 (what a rank of an 8-GPU step holds): the view's backward converts its accumulators itself
     (gut_backward_colour_density) -- same [N,12] and [N,48] as gut_backward, no pass left pending, and a step in which the
