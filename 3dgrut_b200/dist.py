@@ -181,11 +181,12 @@ def _lanes(raster):
     return lanes
 
 
-def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0):
+def training_step_deferred(raster, ex, views, sph_degree, particle_density, particle_radiance, upstream, rank=0, finish=True):
     """Same result as ``training_step`` (summed [N,12] and [N,48] gradients on every rank) with the SH expansion deferred.
     Every rank must hold ``ex.views_per_rank`` views or fewer (missing ones contribute zeros).  Works with a
     ``DeferredExchange`` (NCCL all-gather of the colour gradients) and with a ``PeerExchange`` (peer-memory loads).
-    ``raster``: one SplatRaster, or a list of them to overlap consecutive views on separate streams (``_lanes``)."""
+    ``raster``: one SplatRaster, or a list of them to overlap consecutive views on separate streams (``_lanes``).
+    ``finish=False`` leaves ``ex.finish_step(raster, ...)`` to the caller (e.g. with ``expand=False`` before ``optimizer_epilogue``)."""
     outs = []
     ex.begin_step(rank)
     lanes = _lanes(raster)
@@ -198,7 +199,8 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
                                    rgba, rg, dist_, dg, ex.slot(i), out_density_grad=ex.density_out(i))
             ex.add_view(c, vis)
             outs.append((rgba, dist_))
-        ex.finish_step(r, sph_degree, particle_density)
+        if finish:
+            ex.finish_step(r, sph_degree, particle_density)
         return outs
     cur = torch.cuda.current_stream()
     for r in lanes:
@@ -219,7 +221,8 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
         cur.wait_stream(r._lane_stream)
     for c, vis in seen:
         ex.add_view(c, vis)
-    ex.finish_step(lanes, sph_degree, particle_density)
+    if finish:
+        ex.finish_step(lanes, sph_degree, particle_density)
     return outs
 
 

@@ -178,7 +178,7 @@ class Tracer:
             step = ctx.step
             step._view_backward(ctx.view_index, ctx.sensor, ray_ori, ray_dir, rgba, torch.zeros_like(rgba) if rgba_grad is None else rgba_grad,
                                 dist, torch.zeros_like(dist) if dist_grad is None else dist_grad, ctx.vis)
-            return (None, None, torch.zeros_like(step.anchor), None, None, None)
+            return (None, None, torch.zeros(1, device=rgba.device), None, None, None)
 
     def __init__(self, conf):
         self.device = "cuda"
@@ -315,6 +315,7 @@ class TracerStep:
             r.set_training(True)
         self.anchor = torch.zeros(1, device=self.particle_density.device, requires_grad=True)
         self._seen = []           # (view centre, visibility) of the views whose backward has run, in order
+        self._anchors = {}        # per lane: the leaf that makes autograd call the view's backward
         self.n_views = 0          # forwards issued
         self.n_backward = 0       # backwards done
         self._open = None         # view whose forward context the rasteriser currently holds
@@ -347,7 +348,10 @@ class TracerStep:
             cur, side = torch.cuda.current_stream(), self.lane(i)._lane_stream
             side.wait_stream(cur)
             with torch.cuda.stream(side):
-                rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, ray_ori, ray_dir, sensor)
+                lane_id = i % len(self.lanes)
+                if lane_id not in self._anchors:   # a leaf of the lane's own stream: its gradient accumulation runs there too
+                    self._anchors[lane_id] = torch.zeros(1, device=self.particle_density.device, requires_grad=True)
+                rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self._anchors[lane_id], ray_ori, ray_dir, sensor)
             cur.wait_stream(side)
             for t_ in (rgba, dist, hits, vis):
                 t_.record_stream(cur)
