@@ -605,13 +605,16 @@ def run_ours(args):
 
         for _ in range(min(args.warmup, 3)):
             e2e_step()
-        if os.environ.get("GUT_BENCH_E2E_TRACE") and rank == 0:   # developer hook: kernel table of one end-to-end step
+        if os.environ.get("GUT_BENCH_E2E_TRACE"):   # developer hook: kernel table of one end-to-end step (rank 0 writes it)
             from torch.profiler import ProfilerActivity, profile
-            with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-                e2e_step()
-                torch.cuda.synchronize()
-            with open(os.environ["GUT_BENCH_E2E_TRACE"], "w") as fh:
-                fh.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=60, max_name_column_width=90))
+            if rank == 0:
+                with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+                    e2e_step()
+                    torch.cuda.synchronize()
+                with open(os.environ["GUT_BENCH_E2E_TRACE"], "w") as fh:
+                    fh.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=60, max_name_column_width=90))
+            else:
+                e2e_step()   # the step holds collectives: every rank runs it
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
