@@ -465,21 +465,21 @@ def run_ours(args):
     else:
         add_stage("render-backward::project", "hbm", n * (48 + 16 + 64 + 48 + 192), 1e9, hbm_peak, "GB/s",
                   "48 B params + 16 B colour + 64 B accumulators in, 48 + 192 B gradients out per particle (accumulation re-reads not counted)")
-    # The unit that actually binds each kernel, with ncu's own percent-of-peak for it (profiles/ncu_full_r02c.md, one view of this
+    # The unit that actually binds each kernel, with ncu's own percent-of-peak for it (profiles/ncu_full_r02d.md, one view of this
     # workload).  Static annotations of a committed capture, not measured in this run: for K1, K2 and the sort
     # the HBM roofline above is the contract's yardstick, not their limiter.
     limiters = {
-        "render::project": ("instruction issue (IEEE --fmad=false arithmetic for bit-exact tile counts)", "smsp__issue_active", 73.6),
-        "render::expand": ("L2 request rate: one returning atomic + one scattered 8 B store per intersection", "lts__throughput", 63.7),
-        "render::sort": ("shared memory: random-bin atomics and scatter of the per-tile counting sort", "l1tex__throughput", 67.6),
+        "render::project": ("instruction issue (IEEE --fmad=false arithmetic for bit-exact tile counts)", "smsp__issue_active", 78.7),
+        "render::expand": ("L2 request rate: one returning atomic + one scattered 8 B store per intersection", "lts__throughput", 63.5),
+        "render::sort": ("shared memory: random-bin atomics and scatter of the per-tile counting sort", "l1tex__throughput", 67.8),
         "render::render": ("instruction issue", "smsp__issue_active", 75.5),
         "render-backward::render": ("FMA pipe (packed FP32 occupies it two cycles per instruction)", "sm__pipe_fma_cycles_active", 66.9),
-        "render-backward::project": ("DRAM (per-view fold kernel)", "gpu__dram_throughput", 71.1),
+        "render-backward::project": ("DRAM (per-view fold kernel; ncu r02c)", "gpu__dram_throughput", 71.1),
     }
     for st_ in stages:
         lim = limiters.get(st_["stage"])
         if lim:
-            st_["limiter"] = {"unit": lim[0], "ncu_metric": lim[1], "pct_of_peak": lim[2], "source": "profiles/ncu_full_r02c.md"}
+            st_["limiter"] = {"unit": lim[0], "ncu_metric": lim[1], "pct_of_peak": lim[2], "source": "profiles/ncu_full_r02d.md"}
     dominant = max(stages, key=lambda s: s["ms_per_launch"]) if stages else None
     roofline = None
     if dominant:

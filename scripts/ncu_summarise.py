@@ -24,6 +24,24 @@ with open(f"{out_dir}/launches_{tag}.md", "w") as f:
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         f.write(f"| `{k}` | {v[0]} | {v[1]:.1f} | {v[1]/v[0]:.1f} | {v[1]/tot:.3f} |\n")
 
+# ---- the step-only launch list (no auxiliary measurements), when present --------------------------------------------
+step_csv = f"gpurun_out/launches_{tag}_step.csv"
+if os.path.exists(step_csv):
+    lines2 = [l for l in open(step_csv) if l.startswith('"')]
+    agg2 = collections.OrderedDict()
+    for x in csv.DictReader(io.StringIO("".join(lines2))):
+        v = float(x["Metric Value"].replace(",", ""))
+        u = x["Metric Unit"]
+        v = v / 1e3 if u == "ns" else (v * 1e3 if u == "ms" else v)
+        a = agg2.setdefault(x["Kernel Name"].split("(")[0], [0, 0.0])
+        a[0] += 1; a[1] += v
+    tot2 = sum(v[1] for v in agg2.values())
+    with open(f"{out_dir}/launches_{tag}.md", "a") as f:
+        f.write(f"\n## The timed steps only (`--no-aux --no-sweep`: no forward sweeps, k-buffer, model-side or whole-step measurements)\n\n"
+                "| kernel | launches | total us | avg us | share |\n|---|---|---|---|---|\n")
+        for k, v in sorted(agg2.items(), key=lambda kv: -kv[1][1]):
+            f.write(f"| `{k}` | {v[0]} | {v[1]:.1f} | {v[1]/v[0]:.1f} | {v[1]/tot2:.3f} |\n")
+
 # ---- full capture -> selected raw metrics per kernel ---------------------------------------------------
 rep = f"gpurun_out/prof_{tag}.ncu-rep"
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

@@ -11,6 +11,12 @@ ONE="python bench.py --steps 1 --warmup 3 --views 1 --no-e2e --no-cpu-baseline"
 $BENCH > $OUT/plain_${TAG}.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $OUT/launches_${TAG}.csv $BENCH > $OUT/ncu_launches_${TAG}.log 2>&1
 echo "launch list rc=$?"
+# the same without the auxiliary measurements (forward sweeps, k-buffer, model-side passes, whole training step): the launches of
+# the timed steps and their warm-up only, so that a kernel's share here is its share of a step
+STEP="$BENCH --no-aux --no-sweep"
+$STEP > $OUT/plain_step_${TAG}.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $OUT/launches_${TAG}_step.csv $STEP > $OUT/ncu_launches_step_${TAG}.log 2>&1
+echo "step launch list rc=$?"
 $ONE --no-aux > $OUT/plain_one_${TAG}.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:gut_ -s 33 -c 11 -f -o $OUT/prof_${TAG} $ONE --no-aux > $OUT/ncu_full_${TAG}.log 2>&1
 echo "full capture rc=$?"
