@@ -418,8 +418,9 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (rank 0's views) ----------------------------------------------
     tests = hits = tests_exec = 0
     m_sum = 0
+    touched = 0.0   # particles a view keeps (mog_visibility): the rows the per-view fold kernel has to move
     for v in views:
-        raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
+        touched += float(raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])[3].sum())
         # algorithmic work = what the reference's walk does: every list entry of the tile for every live ray.  The forward's
         # conservative block cull (gut_render_common.cuh, stage_culled) skips part of it; the executed count is reported too.
         raster.set_block_cull(False)
@@ -459,9 +460,21 @@ def run_ours(args):
     add_stage("render-backward::render", "fp32", tests_v * FLOP_BWD_TEST + hits_v * FLOP_BWD_HIT, 1e12, fp32_peak, "TFLOP/s",
               "100 FLOP/test + 250 FLOP/hit")
     if args.exchange in ("deferred", "peer"):
-        add_stage("render-backward::project", "hbm", n * (16 + 32 + 12), 1e9, hbm_peak, "GB/s",
-                  "per view: 16 B colour + one 32 B accumulator sector in, 12 B colour gradient out per particle "
-                  "(the [N,12] / [N,48] conversions run once per step, outside the per-view stages)")
+        # rows the view's rays pushed on: those with a colour gradient in the view's slot of the exchange (left by the timed steps)
+        moved = 0.0
+        for i_ in range(len(views)):
+            moved += float((exchange.slot(i_) != 0).any(dim=1).sum())
+        moved_v = moved / nv
+        if exchange.views_per_rank == 1:
+            add_stage("render-backward::project", "hbm", n * (48 + 4 + 16 + 64 + 48 + 12) + moved_v * 64, 1e9, hbm_peak, "GB/s",
+                      "one view per rank (gut_project_backward_kernel<density, colour>): 48 B parameters + 4 B tile count + 16 B colour + 64 B "
+                      "accumulators in, 48 B [N,12] gradient + 12 B colour gradient out per particle; 64 B of accumulators reset per particle "
+                      "the view's rays pushed on")
+        else:
+            add_stage("render-backward::project", "hbm", n * (16 + 48 + 12) + moved_v * (80 + 80), 1e9, hbm_peak, "GB/s",
+                      "per view (gut_view_fold_kernel): 16 B colour + three 16 B accumulator vectors in, 12 B colour gradient out per particle; "
+                      "per particle the view's rays pushed on: + 48 B parameters, 16 B accumulators, 16 B A sum in and 80 B of accumulators / "
+                      "A sum out (the [N,12] / [N,48] conversions run once per step, outside the per-view stages)")
     else:
         add_stage("render-backward::project", "hbm", n * (48 + 16 + 64 + 48 + 192), 1e9, hbm_peak, "GB/s",
                   "48 B params + 16 B colour + 64 B accumulators in, 48 + 192 B gradients out per particle (accumulation re-reads not counted)")

@@ -103,7 +103,7 @@ print("wrote", f"{out_dir}/launches_{tag}.md", f"{out_dir}/ncu_full_{tag}.md")
 import json
 STAGE_OF = {"gut_project_kernel": "render::project", "gut_emit_kernel": "render::expand", "gut_tile_bin_sort_kernel": "render::sort",
             "gut_render_kernel": "render::render", "gut_render_backward_kernel": "render-backward::render",
-            "gut_colour_gradient_kernel": "render-backward::project"}
+            "gut_view_fold_kernel": "render-backward::project", "gut_project_backward_kernel": "render-backward::project"}
 traffic = {"source": f"profiles/ncu_full_{tag}.md (ncu --set full, one view of the bench workload)", "stages": {}}
 ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
