@@ -418,9 +418,8 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (rank 0's views) ----------------------------------------------
     tests = hits = tests_exec = 0
     m_sum = 0
-    touched = 0.0   # particles a view keeps (mog_visibility): the rows the per-view fold kernel has to move
     for v in views:
-        touched += float(raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])[3].sum())
+        raster.trace(0, SPH_DEGREE, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
         # algorithmic work = what the reference's walk does: every list entry of the tile for every live ray.  The forward's
         # conservative block cull (gut_render_common.cuh, stage_culled) skips part of it; the executed count is reported too.
         raster.set_block_cull(False)
