@@ -157,6 +157,24 @@ class Tracer:
             alb_g, spc_g = ctx.tracer_wrapper.unpack_feature_gradient(radiance_grad)
             return (None, None, None, None, None, pos_g, rot_g, scl_g, dns_g, alb_g, spc_g, None, None, None)
 
+    class _SplitRGBA(torch.autograd.Function):
+        """[H,W,4] -> pred_rgb [1,H,W,3], pred_opacity [1,H,W,1] (tracer.py:332-333 slices + contiguous()).  As plain torch ops the
+        adjoint is two zero-filled [H,W,4] images, two strided copies and an add per view; here it is one concatenation."""
+
+        @staticmethod
+        def forward(ctx, rgba):
+            return rgba[..., :3].unsqueeze(0).contiguous(), rgba[..., 3:].unsqueeze(0).contiguous()
+
+        @staticmethod
+        def backward(ctx, rgb_grad, opacity_grad):
+            if rgb_grad is None and opacity_grad is None:
+                return None
+            if rgb_grad is None:
+                rgb_grad = opacity_grad.new_zeros(opacity_grad.shape[:-1] + (3,))
+            if opacity_grad is None:
+                opacity_grad = rgb_grad.new_zeros(rgb_grad.shape[:-1] + (1,))
+            return torch.cat([rgb_grad[0], opacity_grad[0]], dim=-1)
+
     class _AutogradView(torch.autograd.Function):
         """One view of a multi-view step (Tracer.begin_step): the forward renders from the step's packed parameters, the
         backward is gut_backward_colour -- it leaves the view's colour gradient in the step's slot and keeps summing the
@@ -255,8 +273,7 @@ class Tracer:
                     self.tracer_wrapper, frame_id, gaussians.n_active_features, rays_o.contiguous(), rays_d.contiguous(),
                     gaussians.positions.contiguous(), gaussians.get_rotation().contiguous(), gaussians.get_scale().contiguous(),
                     gaussians.get_density().contiguous(), gaussians.get_features().contiguous(), sensor)
-            pred_rgb = pred_rgba[..., :3].unsqueeze(0).contiguous()
-            pred_opacity = pred_rgba[..., 3:].unsqueeze(0).contiguous()
+            pred_rgb, pred_opacity = Tracer._SplitRGBA.apply(pred_rgba)
             pred_dist = pred_dist.unsqueeze(0).contiguous()
             hits_count = hits_count.unsqueeze(0).contiguous()
             pred_rgb, pred_opacity = gaussians.background(gpu_batch.T_to_world.contiguous(), rays_d, pred_rgb, pred_opacity, train)
@@ -357,8 +374,7 @@ class TracerStep:
                 t_.record_stream(cur)
         else:
             rgba, dist, hits, vis = Tracer._AutogradView.apply(self, i, self.anchor, ray_ori, ray_dir, sensor)
-        pred_rgb = rgba[..., :3].unsqueeze(0).contiguous()
-        pred_opacity = rgba[..., 3:].unsqueeze(0).contiguous()
+        pred_rgb, pred_opacity = Tracer._SplitRGBA.apply(rgba)
         pred_rgb, pred_opacity = self.gaussians.background(gpu_batch.T_to_world.contiguous(), gpu_batch.rays_dir, pred_rgb, pred_opacity, train)
         timings = t.tracer_wrapper.collect_times()
         return {"pred_rgb": pred_rgb, "pred_opacity": pred_opacity, "pred_dist": dist.unsqueeze(0).contiguous(),

@@ -581,7 +581,8 @@ def run_ours(args):
                     dv[kk] = dev_in[bi][kk]
                 rg, dg = dev_in[bi]["rg"], dev_in[bi]["dg"]
                 o = tstep.render(make_batch(dv, dev, pose_device="cpu"))
-                loss = (o["pred_rgb"][0] * rg[..., :3]).sum() + (o["pred_opacity"][0] * rg[..., 3:]).sum() + (o["pred_dist"][0] * dg).sum()
+                # (batch axis kept: indexing it away costs a zero-filled image and a copy per output in the adjoint)
+                loss = (o["pred_rgb"] * rg[None, ..., :3]).sum() + (o["pred_opacity"] * rg[None, ..., 3:]).sum() + (o["pred_dist"] * dg[None]).sum()
                 # loss.backward() with the view's lane as ambient stream (TracerStep.backward); the event fires behind the view's
                 # backward kernels: only then may this buffer set (rays, upstream gradients) be overwritten
                 free_ev[bi] = tstep.backward(loss)
