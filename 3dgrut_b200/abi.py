@@ -7,6 +7,7 @@ import ctypes as C
 import enum
 
 GUT_ABI_VERSION = 1
+GUT_COLOUR_DENSE, GUT_COLOUR_COMPACT = 0, 1     # gut_set_colour_layout
 
 
 class GutStatus(enum.IntEnum):

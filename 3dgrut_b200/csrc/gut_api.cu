@@ -55,6 +55,7 @@ struct GutHandle {
     bool fwd_masks = false;         // the last forward recorded them
     bool pending_density = false;   // gut_backward_colour left view-summed accumulators for gut_density_gradient_finish
     uint32_t pending_N = 0;         // particle count of that pending accumulation
+    int colour_compact = 0;         // layout of the colour-gradient slots this handle writes and reads (gut_set_colour_layout)
     bool block_cull = true;         // conservative per-block cull of the K = 0 forward (gut_set_block_cull: test control)
     int sm_count = 0;               // SMs of the handle's device (grid of the persistent radix-sort kernel)
     cudaStream_t fwd_stream = nullptr;
@@ -470,9 +471,10 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
     }
     {
         StageTimer t(h, ST_BWD_PROJECT, s);
+        if (d_colour_grad && h->colour_compact) GUT_CUDA(h, cudaMemsetAsync(d_colour_grad, 0, 16, s));   // the slot's row cursor
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
                                                 (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad,
-                                                d_colour_grad, deferred_view ? (float*)h->a_sum.p : nullptr, accumulate, s));
+                                                d_colour_grad, h->colour_compact, deferred_view ? (float*)h->a_sum.p : nullptr, accumulate, s));
         h->launches += 1;
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
@@ -537,7 +539,7 @@ int gut_density_gradient_finish(GutHandle* h, void* stream_, uint32_t N, const f
         GUT_CUDA(h, cudaMemsetAsync(h->a_sum.p, 0, h->a_sum.cap, s));
     }
     GUT_CUDA(h, gut_launch_project_backward(h->cfg, h->fwd_frame, N, 0, d_density, nullptr, nullptr, (float*)h->raw_grad.p, d_density_grad,
-                                            nullptr, nullptr, (float*)h->a_sum.p, accumulate, s));
+                                            nullptr, nullptr, 0, (float*)h->a_sum.p, accumulate, s));
     h->launches += 1;
     h->pending_density = false;
     return GUT_OK;
@@ -566,6 +568,20 @@ int gut_reset_gradients(GutHandle* h, void* stream_) {
     return GUT_OK;
 }
 
+int gut_set_colour_layout(GutHandle* h, int32_t layout) {
+    if (!h) return GUT_ERR_BAD_INPUT;
+    if (layout != GUT_COLOUR_DENSE && layout != GUT_COLOUR_COMPACT) return fail(h, GUT_ERR_BAD_INPUT, "unknown colour-gradient layout %d", layout);
+    if (h->pending_density && h->colour_compact != (layout == GUT_COLOUR_COMPACT))
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_set_colour_layout in the middle of a step (views pending): finish or reset it first");
+    h->colour_compact = layout == GUT_COLOUR_COMPACT ? 1 : 0;
+    return GUT_OK;
+}
+
+uint64_t gut_colour_slot_floats(uint32_t N, int32_t layout) {
+    const uint64_t rows = ((uint64_t)3 * N + 3u) & ~(uint64_t)3u;
+    return layout == GUT_COLOUR_COMPACT ? 4u + (uint64_t)gut_colour_table_words(N) + rows : rows;
+}
+
 int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degree, const float* d_density, uint32_t n_views,
                            const float* d_view_centres, const float* d_colour_grads, float* d_radiance_grad, int32_t accumulate) {
     const float* view_centres = d_view_centres;
@@ -573,6 +589,9 @@ int gut_sh_gradient_expand(GutHandle* h, void* stream_, uint32_t N, int32_t sph_
     if (sph_degree < 0 || sph_degree > h->cfg.sph_max_degree) return fail(h, GUT_ERR_BAD_INPUT, "sph_degree_active out of range");
     if (N == 0) return GUT_OK;
     if (!d_density || !d_radiance_grad || (n_views > 0 && (!view_centres || !d_colour_grads))) return fail(h, GUT_ERR_BAD_INPUT, "null pointer");
+    if (h->colour_compact && n_views > 0)
+        return fail(h, GUT_ERR_BAD_INPUT, "gut_sh_gradient_expand takes one dense [n_views,N,3] buffer; with the compact colour layout "
+                                          "(gut_set_colour_layout) pass one slot pointer per view to gut_sh_gradient_expand_gather");
     DeviceGuard guard(h->device);
     GUT_CUDA(h, gut_launch_sh_expand(N, sph_degree, (h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1), d_density, n_views, view_centres, d_colour_grads, d_radiance_grad, accumulate, (cudaStream_t)stream_));
     h->launches += 1;
@@ -588,7 +607,7 @@ int gut_sh_gradient_expand_gather(GutHandle* h, void* stream_, uint32_t N, int32
     for (uint32_t v = 0; v < n_views; ++v)
         if (!colour_grad_ptrs[v]) return fail(h, GUT_ERR_BAD_INPUT, "colour gradient pointer of view %u is NULL", v);
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_sh_expand_ptrs(N, sph_degree, (h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1), d_density, n_views, d_view_centres, colour_grad_ptrs, d_radiance_grad, accumulate,
+    GUT_CUDA(h, gut_launch_sh_expand_ptrs(N, sph_degree, (h->cfg.sph_max_degree + 1) * (h->cfg.sph_max_degree + 1), d_density, n_views, d_view_centres, colour_grad_ptrs, h->colour_compact, d_radiance_grad, accumulate,
                                           (cudaStream_t)stream_));
     h->launches += n_views == 0 ? 1 : (n_views + GUT_EXPAND_MAX_VIEWS - 1) / GUT_EXPAND_MAX_VIEWS;
     return GUT_OK;
@@ -779,7 +798,7 @@ int gut_sh_expand_adam(GutHandle* h, void* stream_, uint32_t N, int32_t sph_degr
     for (uint32_t v = 0; v < n_views; ++v)
         if (!colour_grad_ptrs[v]) return fail(h, GUT_ERR_BAD_INPUT, "colour gradient pointer of view %u is NULL", v);
     DeviceGuard guard(h->device);
-    GUT_CUDA(h, gut_launch_sh_expand_adam(N, sph_degree, d_density, n_views, d_view_centres, colour_grad_ptrs, *albedo, *specular,
+    GUT_CUDA(h, gut_launch_sh_expand_adam(N, sph_degree, d_density, n_views, d_view_centres, colour_grad_ptrs, h->colour_compact, *albedo, *specular,
                                           d_visibility, b1, b2, eps, (cudaStream_t)stream_));
     h->launches += 1;
     return GUT_OK;

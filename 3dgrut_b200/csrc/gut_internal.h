@@ -68,7 +68,8 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
                                         float* raw_grad, float* density_grad, float* sph_grad,
-                                        float* colour_out /* non-null: write the view's masked colour gradient [N,3] instead of sph_grad */,
+                                        float* colour_out /* non-null: write the view's masked colour gradient instead of sph_grad */,
+                                        int colour_compact /* layout of colour_out: 0 = [N,3], 1 = compact slot (gut_project.cu, colour_store) */,
                                         float* a_sum /* [N,4] sum of A over the views of a deferred step; NULL for the one-view backward */,
                                         int accumulate, cudaStream_t stream);
 
@@ -78,7 +79,7 @@ cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, int ncoef_all, cons
 
 // exclusive scan of tile_hist[T*SUB] -> tile_start[T+1] and absolute sub-bucket cursors tile_cursor[T*SUB]; stats[0]=M, stats[1]=max list
 cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres /* device [n_views,3] */,
-                                      const float* const* colour_ptrs /* host array of device pointers */, float* sph_grad, int accumulate,
+                                      const float* const* colour_ptrs /* host array of device pointers */, int colour_compact, float* sph_grad, int accumulate,
                                       cudaStream_t stream);
 cudaError_t gut_launch_tile_scan(uint32_t T, const uint32_t* tile_hist, uint32_t* tile_start, uint32_t* tile_cursor,
                                  uint32_t* stats, cudaStream_t stream);
@@ -140,7 +141,7 @@ cudaError_t gut_launch_density_adam(uint32_t N, const float* packed12, const flo
                                     const float* visibility, float b1, float b2, float eps, const float* sensor /* host [3] or null */,
                                     float* accum, float* denom, cudaStream_t stream);
 cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
-                                      const float* const* colour_ptrs, const GutAdamTensors& albedo, const GutAdamTensors& specular,
+                                      const float* const* colour_ptrs, int colour_compact, const GutAdamTensors& albedo, const GutAdamTensors& specular,
                                       const float* visibility, float b1, float b2, float eps, cudaStream_t stream);
 cudaError_t gut_launch_densify_stats(uint32_t N, const float* pos, const float* pos_g, float3 sensor, float* accum, float* denom,
                                      cudaStream_t stream);

@@ -27,6 +27,8 @@ struct GutMat4x3 {  // column-major: c[0..2] rotation columns, c[3] translation 
     float3 c[4];
 };
 
+// compact colour-gradient slot (gut_project.cu, colour_store): words of the (mask, first row) table, a multiple of four
+GUT_HD uint32_t gut_colour_table_words(uint32_t N) { return (2u * ((N + 31u) >> 5) + 3u) & ~3u; }
 GUT_HD float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 GUT_HD float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
 GUT_HD float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }

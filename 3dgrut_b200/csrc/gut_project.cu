@@ -401,6 +401,59 @@ __global__ void __launch_bounds__(256, ROLLING ? GUT_K1_MIN_BLOCKS : GUT_K1_MIN_
 constexpr int K6_THREADS = 128;
 constexpr int K6_WARPS = K6_THREADS / 32;
 
+// ---------------------------------------------------------------------------------------------------
+// Colour-gradient slot of one view (what K6 / the fold pass hand to the step's SH expansion), in one of two layouts:
+//   dense    [N][3] floats, zero rows for the particles the view did not touch;
+//   compact  (gut_set_colour_layout(h, GUT_COLOUR_COMPACT)) only the rows the view's rays pushed on, 12 B each, in the order the
+//            warps of the writing kernel claimed them, behind a table with one (mask, first row) pair per 32 particles:
+//            word 0 = rows handed out (the writers' cursor, zeroed by the host before the pass), words 4 .. 4 + table_words the
+//            table, rows behind it.  A view touches about a sixth of the particles at the bench workload: a reader on another
+//            GPU pulls ~3 B per particle over NVLink instead of 12.
+// ---------------------------------------------------------------------------------------------------
+template <int WARPS>
+GUT_D void colour_store(float* __restrict__ slot, uint32_t N, uint32_t i, const float3 g, const bool compact) {
+    if (!compact) {
+        if (i < N) { slot[3 * (size_t)i] = g.x; slot[3 * (size_t)i + 1] = g.y; slot[3 * (size_t)i + 2] = g.z; }
+        return;
+    }
+    // (every thread of the CTA gets here exactly once: the callers guard their per-particle work with `i < N`, they do not
+    // return early.)  One claim per CTA: the cursor is one address, and same-address atomics retire about one per clock.
+    __shared__ uint32_t s_rows[WARPS + 1];
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const bool moved = i < N && (g.x != 0.0f || g.y != 0.0f || g.z != 0.0f);
+    const uint32_t m = __ballot_sync(0xffffffffu, moved);
+    if (lane == 0) s_rows[wid] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) { const uint32_t c = s_rows[w]; s_rows[w] = total; total += c; }
+        s_rows[WARPS] = total ? atomicAdd(reinterpret_cast<uint32_t*>(slot), total) : 0u;
+    }
+    __syncthreads();
+    const uint32_t base = s_rows[WARPS] + s_rows[wid];
+    if (lane == 0 && i < N) reinterpret_cast<uint2*>(slot + 4)[i >> 5] = make_uint2(m, base);
+    if (moved) {
+        float* row = slot + 4 + gut_colour_table_words(N) + 3 * (size_t)(base + __popc(m & ((1u << lane) - 1u)));
+        row[0] = g.x; row[1] = g.y; row[2] = g.z;
+    }
+}
+// Reading a slot, in two steps so that a caller can put the table loads of several views in flight before the first row load
+// (the second round trip depends on the first; across NVLink each is a few microseconds).
+GUT_D uint2 colour_table_load(const float* __restrict__ slot, uint32_t i, const bool compact) {
+    return compact ? __ldg(reinterpret_cast<const uint2*>(slot + 4) + (i >> 5)) : make_uint2(0u, 0u);   // one 8-byte request per warp
+}
+GUT_D float3 colour_load(const float* __restrict__ slot, uint32_t N, uint32_t i, const uint2 t, const bool compact) {
+    if (!compact) {
+        const float* gp = slot + 3 * (size_t)i;
+        return f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+    }
+    const uint32_t lane = i & 31u;
+    if (!((t.x >> lane) & 1u)) return f3(0.0f, 0.0f, 0.0f);
+    const float* gp = slot + 4 + gut_colour_table_words(N) + 3 * (size_t)(t.y + __popc(t.x & ((1u << lane) - 1u)));
+    return f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+}
+
 // The "origin fold": K5 leaves out the go (x) A halves of the torque, the trace and the scale terms when go is the same
 // for every ray of the view (gut_render.cu, backward_walk).  With A summed over the view's rays they are
 //   tau' += A x (s^2 go) = A x (s * R^T v),   tr += sum_i A_i v_i / s_i,   Z_i += go_i A_i,   W += go . A,      v = view centre - position,
@@ -431,7 +484,8 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
                                                                           const float4* __restrict__ features,
                                                                           float4* __restrict__ raw_grad, float4* __restrict__ density_grad,
                                                                           float* __restrict__ sph_grad, float* __restrict__ colour_out,
-                                                                          float4* __restrict__ a_sum, int accumulate) {
+                                                                          float4* __restrict__ a_sum, int accumulate,
+                                                                          int colour_compact /* layout of colour_out, colour_store above */) {
     __shared__ float4 s_dg[K6_WARPS][32 * 3];      // parameter-gradient rows of the warp
     __shared__ float s_basis[K6_WARPS][32][17];    // SH basis per row (+1 pad: conflict-free column reads)
     __shared__ float4 s_g[K6_WARPS][32];           // masked colour gradient per row, w = 1 if the row was touched
@@ -534,7 +588,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_project_backward_kernel(GutCon
     if (!COLOUR) return;
     // deferred SH gradient: hand out the masked colour gradient of this view, gut_sh_expand_kernel sums the views later
     if (colour_out) {
-        if (i < N) { colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z; }
+        colour_store<K6_WARPS>(colour_out, N, i, g, colour_compact != 0);
         return;
     }
     // [N,48]
@@ -605,17 +659,21 @@ cudaError_t gut_launch_project(const GutConfig& cfg, const GutCamera& cam, const
 // accumulators; fold the view's origin into the torque / trace / scale accumulators (origin_fold above: it needs the
 // A of THIS view alone and this view's centre) and move A to the step's sum `a_sum`, leaving [0..2] zero for the next
 // view.  Everything else waits for the end of the step.
+template <bool COMPACT>
 __global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 centre, const float4* __restrict__ density12,
                                                             const float4* __restrict__ features, float4* __restrict__ raw_grad,
                                                             float4* __restrict__ a_sum, float* __restrict__ colour_out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
+    float3 g = f3(0.0f, 0.0f, 0.0f);
+    // (no early return: in the compact layout the CTA's row claim below is a barrier and a ballot every thread takes part in,
+    // from this one call site)
+    if (i < N) {
     // no test of tiles_count: the accumulators of an untouched particle are zero, and skipping the dependent load matters
     // more than the bytes (the kernel is bound by the latency of its load -> store chain, not by bandwidth)
     float4* rg = raw_grad + 4 * (size_t)i;
     const float4 a = rg[0], g2 = rg[2], g3 = rg[3];
     const float4 ft = __ldg(features + i);
-    const float3 g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
+    g = f3(g2.w * (ft.x > 0.0f ? 1.0f : 0.0f), g3.x * (ft.y > 0.0f ? 1.0f : 0.0f), g3.y * (ft.z > 0.0f ? 1.0f : 0.0f));
     float3 Z = f3(g2.x, g2.y, g2.z);
     float W = g3.z;
     const bool moved = a.x != 0.0f || a.y != 0.0f || a.z != 0.0f;
@@ -634,15 +692,16 @@ __global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 c
     }
     if (moved || g2.w != 0.0f) rg[2] = make_float4(Z.x, Z.y, Z.z, 0.0f);
     if (moved || g3.x != 0.0f || g3.y != 0.0f) rg[3] = make_float4(0.0f, 0.0f, W, g3.w);
-    colour_out[3 * (size_t)i] = g.x; colour_out[3 * (size_t)i + 1] = g.y; colour_out[3 * (size_t)i + 2] = g.z;
+    }
+    colour_store<8>(colour_out, N, i, g, COMPACT);
 }
 
 // a_sum [N,4]: the deferred step's sum of A over its views.  Required with colour_out (one view of a deferred step) and
 // with density_grad alone (end of the step); NULL for the one-view backward, which folds its own origin.
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
                                         const float* density12, const uint32_t* tiles_count, const float4* features,
-                                        float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, float* a_sum,
-                                        int accumulate, cudaStream_t stream) {
+                                        float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, int colour_compact,
+                                        float* a_sum, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
     const float4* d12 = reinterpret_cast<const float4*>(density12);
@@ -651,17 +710,20 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
     float4* as = reinterpret_cast<float4*>(a_sum);
     if (density_grad && (sph_grad || colour_out))
         gut_project_backward_kernel<true, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
-                                                                               sph_grad, colour_out, nullptr, accumulate);
+                                                                               sph_grad, colour_out, nullptr, accumulate, colour_compact);
     else if (density_grad) {
         if (!a_sum) return cudaErrorInvalidValue;
         gut_project_backward_kernel<true, false><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg, dg,
-                                                                                nullptr, nullptr, as, accumulate);
+                                                                                nullptr, nullptr, as, accumulate, 0);
     } else if (colour_out) {
         if (!a_sum) return cudaErrorInvalidValue;
-        gut_view_fold_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, frame.cam_centre, d12, features, rg, as, colour_out);
+        if (colour_compact)
+            gut_view_fold_kernel<true><<<(N + 255) / 256, 256, 0, stream>>>(N, frame.cam_centre, d12, features, rg, as, colour_out);
+        else
+            gut_view_fold_kernel<false><<<(N + 255) / 256, 256, 0, stream>>>(N, frame.cam_centre, d12, features, rg, as, colour_out);
     } else
         gut_project_backward_kernel<false, true><<<grid, K6_THREADS, 0, stream>>>(cfg, frame, N, sph_degree, d12, tiles_count, features, rg,
-                                                                                nullptr, sph_grad, colour_out, nullptr, accumulate);
+                                                                                nullptr, sph_grad, colour_out, nullptr, accumulate, colour_compact);
     return cudaGetLastError();
 }
 
@@ -678,7 +740,8 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
 // straight over NVLink while it computes and no all-gather pass exists (3dgrut_b200/dist.py, training_step_peer).  All
 // loads of a chunk of views are issued before the first is used: one NVLink round trip per chunk, not per view.
 struct ExpandViews {
-    const float* colour[GUT_EXPAND_MAX_VIEWS];   // [N][3] each
+    const float* colour[GUT_EXPAND_MAX_VIEWS];   // one slot each: [N][3], or the compact layout (colour_store / colour_load above)
+    int compact;
 };
 constexpr int EXPAND_CHUNK = 8;
 __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
@@ -699,13 +762,14 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
         for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {   // static indices into the pointer table
             if (v0 >= n_views) break;
             float3 gq[EXPAND_CHUNK];
+            uint2 tq[EXPAND_CHUNK];
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q)
+                tq[q] = (v0 + q < n_views) ? colour_table_load(views.colour[v0 + q], i, views.compact != 0) : make_uint2(0u, 0u);
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
                 gq[q] = f3(0.f, 0.f, 0.f);
-                if (v0 + q < n_views) {
-                    const float* gp = views.colour[v0 + q] + 3 * (size_t)i;
-                    gq[q] = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
-                }
+                if (v0 + q < n_views) gq[q] = colour_load(views.colour[v0 + q], N, i, tq[q], views.compact != 0);
             }
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
@@ -785,13 +849,14 @@ __global__ void __launch_bounds__(K6_THREADS, GUT_SHADAM_MIN_BLOCKS) gut_sh_expa
         for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {
             if (v0 >= n_views) break;
             float3 gq[EXPAND_CHUNK];
+            uint2 tq[EXPAND_CHUNK];
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q)
+                tq[q] = (v0 + q < n_views) ? colour_table_load(views.colour[v0 + q], i, views.compact != 0) : make_uint2(0u, 0u);
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
                 gq[q] = f3(0.f, 0.f, 0.f);
-                if (v0 + q < n_views) {
-                    const float* gp = views.colour[v0 + q] + 3 * (size_t)i;
-                    gq[q] = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
-                }
+                if (v0 + q < n_views) gq[q] = colour_load(views.colour[v0 + q], N, i, tq[q], views.compact != 0);
             }
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
@@ -861,11 +926,12 @@ __global__ void __launch_bounds__(K6_THREADS, GUT_SHADAM_MIN_BLOCKS) gut_sh_expa
 }
 
 cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* density12, uint32_t n_views, const float* centres,
-                                      const float* const* colour_ptrs, const GutAdamTensors& albedo, const GutAdamTensors& specular,
+                                      const float* const* colour_ptrs, int colour_compact, const GutAdamTensors& albedo, const GutAdamTensors& specular,
                                       const float* visibility, float b1, float b2, float eps, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     if (n_views > GUT_EXPAND_MAX_VIEWS) return cudaErrorInvalidValue;
     ExpandViews views = {};
+    views.compact = colour_compact;
     for (uint32_t v = 0; v < n_views; ++v) views.colour[v] = colour_ptrs[v];
     auto aligned = [](const GutAdamTensors& t) { return (((uintptr_t)t.param | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15u) == 0; };
     const uint32_t vec_mask = (aligned(albedo) ? 1u : 0u) | (aligned(specular) ? 2u : 0u);   // a warp's span starts at 32 x width floats
@@ -877,12 +943,13 @@ cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* d
 // colour_ptrs: HOST array of n_views device pointers.  More than GUT_EXPAND_MAX_VIEWS views are expanded in several
 // launches, the later ones accumulating.
 cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres,
-                                      const float* const* colour_ptrs, float* sph_grad, int accumulate, cudaStream_t stream) {
+                                      const float* const* colour_ptrs, int colour_compact, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
     uint32_t done = 0;
     do {
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         ExpandViews views = {};
+        views.compact = colour_compact;
         for (uint32_t v = 0; v < nv; ++v) views.colour[v] = colour_ptrs[done + v];
         gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
             N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
@@ -895,14 +962,14 @@ cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all,
 cudaError_t gut_launch_sh_expand(uint32_t N, int sph_degree, int ncoef_all, const float* density12, uint32_t n_views, const float* centres,
                                  const float* colour_grads, float* sph_grad, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
-    if (n_views == 0) return gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, 0, centres, nullptr, sph_grad, accumulate, stream);
+    if (n_views == 0) return gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, 0, centres, nullptr, 0, sph_grad, accumulate, stream);
     uint32_t done = 0;
     cudaError_t e = cudaSuccess;
     while (done < n_views && e == cudaSuccess) {   // contiguous [n_views][N][3] buffer -> pointer table, one chunk per launch
         const float* ptrs[GUT_EXPAND_MAX_VIEWS];
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         for (uint32_t v = 0; v < nv; ++v) ptrs[v] = colour_grads + 3 * (size_t)(done + v) * N;
-        e = gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, nv, centres + 3 * (size_t)done, ptrs, sph_grad, (accumulate || done > 0) ? 1 : 0, stream);
+        e = gut_launch_sh_expand_ptrs(N, sph_degree, ncoef_all, density12, nv, centres + 3 * (size_t)done, ptrs, 0, sph_grad, (accumulate || done > 0) ? 1 : 0, stream);
         done += nv;
     }
     return e;

@@ -114,6 +114,22 @@ class DeferredExchange:
         """[N,3] buffer that receives the masked colour gradient of this rank's view i (gut_backward_colour)."""
         return self.colour_all[self.local_slot(self._rank, i)]
 
+    colour_layout = 0     # GUT_COLOUR_DENSE: every slot is an [N,3] tensor (PeerExchange may hold compact slots instead)
+
+    def use(self, rasters):
+        """Give the rasteriser handles that write or read this exchange's slots its slot layout (gut_set_colour_layout)."""
+        for r in (rasters if isinstance(rasters, (list, tuple)) else [rasters]):
+            if hasattr(r, "set_colour_layout"):
+                r.set_colour_layout(self.colour_layout)
+
+    def clear_slot(self, i):
+        """Make this rank's view slot i of the current step contribute nothing (a view without a backward)."""
+        self.slot(i).zero_()
+
+    def moved_rows(self, i):
+        """Particles with a colour gradient in this rank's view slot i (synchronises; bench / diagnostics)."""
+        return int((self.slot(i) != 0).any(dim=1).sum())
+
     def density_out(self, i):
         """[N,12] buffer the backward of view i may write its gradient into directly (gut_backward_colour_density), or None.
         A rank that renders ONE view per step has nothing to sum over views: its backward converts the accumulators itself
@@ -190,6 +206,7 @@ def training_step_deferred(raster, ex, views, sph_degree, particle_density, part
     outs = []
     ex.begin_step(rank)
     lanes = _lanes(raster)
+    ex.use(lanes)
     if len(lanes) == 1 or len(views) < 2:
         r = lanes[0]
         for i, (v, (rg, dg)) in enumerate(zip(views, upstream)):
@@ -244,11 +261,16 @@ class PeerExchange(DeferredExchange):
 
     SETS = 2
 
-    def __init__(self, raster, n_particles, n_sph_floats, views_per_rank, device, rank, world=None, track_visibility=False):
+    def __init__(self, raster, n_particles, n_sph_floats, views_per_rank, device, rank, world=None, track_visibility=False, compact=None):
         super().__init__(n_particles, n_sph_floats, views_per_rank, device, world=world, track_visibility=track_visibility,
                          gather_buffer=False)   # peer buffers instead
         self.raster, self.rank = raster, rank
-        self.slot_floats = (3 * n_particles + 3) // 4 * 4       # 16-byte aligned slots
+        # compact slots (include/gut_b200.h, GUT_COLOUR_COMPACT): only the rows a view touched cross NVLink.  Default: on when
+        # there is a peer to read them; every rank must choose the same.
+        self.compact = (self.world > 1) if compact is None else bool(compact)
+        self.colour_layout = 1 if self.compact else 0
+        self.slot_floats = raster.colour_slot_floats(n_particles, self.colour_layout)       # 16-byte aligned slots
+        self.slot_header_floats = self.slot_floats - (3 * n_particles + 3) // 4 * 4          # compact: row cursor + table
         floats = self.SETS * views_per_rank * self.slot_floats
         # Set-up either succeeds on every rank or raises on every rank: a rank that cannot export or map a buffer still
         # takes part in both exchanges below, so nobody is left waiting in a collective.
@@ -293,8 +315,22 @@ class PeerExchange(DeferredExchange):
             dist.barrier()       # every rank has mapped every buffer before anyone writes
 
     def slot_tensor(self, s, i):
-        """[N,3] view of this rank's slot i of buffer set s."""
+        """This rank's slot i of buffer set s: an [N,3] view, or the whole slot (flat) in the compact layout."""
+        if self.compact:
+            return self.mine[s, i]
         return self.mine[s, i, :3 * self.n_particles].view(self.n_particles, 3)
+
+    def clear_slot(self, i, s=None):
+        s = self._set if s is None else s
+        if self.compact:
+            self.mine[s, i, :self.slot_header_floats].zero_()   # no row in use, every mask empty
+        else:
+            self.slot_tensor(s, i).zero_()
+
+    def moved_rows(self, i):
+        if self.compact:
+            return int(self.mine[self._set, i, :1].view(torch.int32)[0])
+        return super().moved_rows(i)
 
     def slot_ptr(self, r, s, i):
         return self.ptrs[r] + 4 * ((s * self.views_per_rank + i) * self.slot_floats)
@@ -344,7 +380,7 @@ class PeerExchange(DeferredExchange):
         self._mark("start")
         centres = list(self._centres)
         for i in range(len(centres), self.views_per_rank):
-            self.slot_tensor(s, i).zero_()
+            self.clear_slot(i, s)
             centres.append([0.0, 0.0, 0.0])
         self.my_centres.copy_(torch.tensor(centres, dtype=torch.float32), non_blocking=True)
         gathered, reduced = None, None
@@ -355,6 +391,7 @@ class PeerExchange(DeferredExchange):
             self.centres_all.copy_(self.my_centres)
         rasters = list(raster) if isinstance(raster, (list, tuple)) else [raster]
         raster = rasters[0]
+        self.use(raster)
         if self.views_per_rank > 1:
             for j, r in enumerate(rasters):      # every lane's view-summed accumulators; overlaps the ordering point
                 r.density_gradient_finish(particle_density, self.density_grad, accumulate=j > 0)
@@ -439,6 +476,7 @@ def optimizer_epilogue(raster, ex, raw, particle_density, state, lrs, sph_degree
     raster.density_adam(particle_density, ex.density_grad, triple("positions"), triple("rotation"), triple("scale"), triple("density"),
                         [lrs[k] for k in ("positions", "rotation", "scale", "density")], ex.visibility, betas[0], betas[1], eps,
                         scale_activation, density_activation, sensor_position, grad_norm_accum, grad_norm_denom)
+    ex.use(raster)
     raster.sh_expand_adam(sph_degree, particle_density, ex.centres_all, ex.colour_ptrs(), triple("features_albedo"),
                           triple("features_specular"), (lrs["features_albedo"], lrs["features_specular"]), ex.visibility, betas[0],
                           betas[1], eps)

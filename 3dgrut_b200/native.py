@@ -71,6 +71,10 @@ def load_library():
     lib.gut_backward_colour_density.restype = C.c_int
     lib.gut_set_training.argtypes = [vp, i32]
     lib.gut_set_training.restype = C.c_int
+    lib.gut_set_colour_layout.argtypes = [vp, i32]
+    lib.gut_set_colour_layout.restype = C.c_int
+    lib.gut_colour_slot_floats.argtypes = [u32, i32]
+    lib.gut_colour_slot_floats.restype = C.c_uint64
     lib.gut_set_block_cull.argtypes = [vp, i32]
     lib.gut_set_block_cull.restype = C.c_int
     lib.gut_reset_gradients.argtypes = [vp, vp]
@@ -181,6 +185,7 @@ class SplatRaster:
         if rc != 0:
             raise GutError(rc, "gut_create failed (unsupported configuration?)")
         self._h = h
+        self.colour_layout = abi.GUT_COLOUR_DENSE
         self.n_coeffs = (config.sph_max_degree + 1) ** 2
 
     def __del__(self):
@@ -333,7 +338,11 @@ class SplatRaster:
         height, width = ro.shape[1], ro.shape[2]
         if rgba_g.numel() != height * width * 4 or dist_g.numel() != height * width:
             raise GutError(abi.GutStatus.BAD_INPUT, "gradient shapes do not match the view")
-        if out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
+        if self.colour_layout == abi.GUT_COLOUR_COMPACT:
+            if out_colour_grad.numel() != self.colour_slot_floats(n) or not out_colour_grad.is_contiguous() or out_colour_grad.data_ptr() % 16:
+                raise GutError(abi.GutStatus.BAD_INPUT, "out_colour_grad must be a 16-byte aligned contiguous slot of "
+                                                        "colour_slot_floats(N) floats (compact colour layout)")
+        elif out_colour_grad.shape != (n, 3) or not out_colour_grad.is_contiguous():
             raise GutError(abi.GutStatus.BAD_INPUT, "out_colour_grad must be a contiguous [N,3]")
         centre = (C.c_float * 3)()
         if out_density_grad is not None:
@@ -635,6 +644,20 @@ class SplatRaster:
     def set_training(self, training: bool):
         """gut_set_training: training=False skips the hit-mask recording of the forward (inference); no backward may follow."""
         self.lib.gut_set_training(self._h, 1 if training else 0)
+
+    def set_colour_layout(self, layout: int):
+        """gut_set_colour_layout: GUT_COLOUR_DENSE ([N,3] per view) or GUT_COLOUR_COMPACT (touched rows behind a table) for the
+        colour-gradient slots this handle writes (trace_bwd_colour) and reads (sh_gradient_expand_gather, sh_expand_adam)."""
+        if int(layout) == self.colour_layout:
+            return
+        rc = self.lib.gut_set_colour_layout(self._h, int(layout))
+        if rc != 0:
+            self._raise(rc)
+        self.colour_layout = int(layout)
+
+    def colour_slot_floats(self, n_particles, layout=None):
+        """gut_colour_slot_floats: floats one view's colour-gradient slot takes for n_particles in the given (default: current) layout."""
+        return int(self.lib.gut_colour_slot_floats(int(n_particles), self.colour_layout if layout is None else int(layout)))
 
     def set_block_cull(self, enabled: bool):
         """gut_set_block_cull: test control, see include/gut_b200.h (outputs are bit-identical either way)."""

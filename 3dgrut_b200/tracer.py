@@ -339,6 +339,8 @@ class TracerStep:
         self.finished = False
         for r in self.lanes:
             r.reset_gradients()   # nothing pending from an abandoned step
+        if hasattr(exchange, "use"):
+            exchange.use(self.lanes)   # slot layout of the exchange (dense [N,3] or compact, 3dgrut_b200.dist.PeerExchange)
         exchange.begin_step(rank)
 
     def lane(self, view_index):
@@ -423,7 +425,7 @@ class TracerStep:
         if self.finished:
             raise RuntimeError("TracerStep.finish called twice")
         if self._open is not None:     # a view rendered without a backward contributes nothing: drop its slot
-            self.exchange.slot(self._open).zero_()
+            self.exchange.clear_slot(self._open)
             direct = self.exchange.density_out(self._open)
             if direct is not None:     # one view per rank: no backward wrote the step's [N,12] gradient
                 direct.zero_()

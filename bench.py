@@ -47,6 +47,8 @@ def parse_args():
     p.add_argument("--height", type=int, default=H_IMG)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--colour-slots", choices=("auto", "dense", "compact"), default="auto",
+                   help="layout of the peer exchange's per-view colour-gradient slots (auto: compact when n_gpus > 1)")
     p.add_argument("--lanes", type=int, default=2, help="handles / CUDA streams a rank deals its views to (1 = one stream)")
     p.add_argument("--exchange", choices=("auto", "peer", "deferred", "allreduce"), default="auto",
                    help="gradient exchange of the step: deferred = allreduce [N,12] + all-gather per-view colour gradients, SH expansion "
@@ -324,9 +326,12 @@ def run_ours(args):
     lanes = [raster] + ([native.SplatRaster(cfg, device=dev)] if (args.lanes > 1 and n_my_views > 1) else [])
     if args.exchange == "auto":
         args.exchange = "peer" if world > 1 else "deferred"
+    # colour-gradient slots of the peer exchange: compact (touched rows only) when there is a peer to read them
+    compact_slots = {"auto": None, "dense": False, "compact": True}[args.colour_slots]
     if args.exchange == "peer":
         try:
-            exchange = gdist.PeerExchange(raster, n, sph.shape[1], (args.views + world - 1) // world, dev, rank, world=world)
+            exchange = gdist.PeerExchange(raster, n, sph.shape[1], (args.views + world - 1) // world, dev, rank, world=world,
+                                          compact=compact_slots)
             ok = 1
         except RuntimeError as e:   # CUDA IPC unavailable on this box: the constructor raises on every rank together
             print(f"[bench] rank {rank}: peer buffers unavailable ({e!r})", file=sys.stderr, flush=True)
@@ -462,7 +467,7 @@ def run_ours(args):
         # rows the view's rays pushed on: those with a colour gradient in the view's slot of the exchange (left by the timed steps)
         moved = 0.0
         for i_ in range(len(views)):
-            moved += float((exchange.slot(i_) != 0).any(dim=1).sum())
+            moved += float(exchange.moved_rows(i_))
         moved_v = moved / nv
         if exchange.views_per_rank == 1:
             add_stage("render-backward::project", "hbm", n * (48 + 4 + 16 + 64 + 48 + 12) + moved_v * 64, 1e9, hbm_peak, "GB/s",
@@ -738,7 +743,7 @@ def run_ours(args):
         ex2 = None
         try:
             if args.exchange == "peer":
-                ex2 = gdist.PeerExchange(raster, n, sph.shape[1], vpr, dev, rank, world=world, track_visibility=True)
+                ex2 = gdist.PeerExchange(raster, n, sph.shape[1], vpr, dev, rank, world=world, track_visibility=True, compact=compact_slots)
             else:
                 ex2 = gdist.DeferredExchange(n, sph.shape[1], vpr, dev, world=world, track_visibility=True)
         except RuntimeError as e:
@@ -875,7 +880,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "lanes": len(lanes), "ms_per_step_one_lane": ms_one_lane, "step_breakdown": tails,
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "lanes": len(lanes), "colour_slots": "compact" if getattr(exchange, "compact", False) else "dense", "ms_per_step_one_lane": ms_one_lane, "step_breakdown": tails,
             "roofline": roofline, "roofline_stages": stages, "cpu_baseline": cpu_baseline,
             "work_per_view": {"intersections_M": m_v, "tiles": stats["num_tiles"], "mean_tile_list": m_v / max(1, stats["num_tiles"]),
                               "max_tile_list": stats["max_tile_list_length"], "tests_per_pixel": tests_v / P, "hits_per_pixel": hits_v / P,

@@ -271,6 +271,23 @@ GUT_API int gut_sh_gradient_expand(GutHandle* h, void* stream, uint32_t num_part
 GUT_API int gut_sh_gradient_expand_gather(GutHandle* h, void* stream, uint32_t num_particles, int32_t sph_degree_active,
                  const float* d_particle_density, uint32_t n_views, const float* d_view_centres,
                  const float* const* colour_grad_ptrs, float* d_particle_radiance_grad, int32_t accumulate);
+/*
+ * Layout of the per-view colour-gradient slots (d_colour_grad of gut_backward_colour / gut_backward_colour_density, the
+ * entries of colour_grad_ptrs of gut_sh_gradient_expand_gather / gut_sh_expand_adam).  No reference counterpart.
+ *   GUT_COLOUR_DENSE    [N,3] floats, zero rows for untouched particles (the default);
+ *   GUT_COLOUR_COMPACT  only the rows the view's rays pushed on (about a sixth of the particles at the bench workload), 12 B
+ *                       each, behind a table of one (mask, first row) pair per 32 particles: float 0 = rows in use, floats
+ *                       4 .. 4 + table the table, rows behind it.  A slot holds gut_colour_slot_floats(N, layout) floats and is
+ *                       16-byte aligned.  The expansion on another GPU then pulls ~3 B per particle and view over NVLink
+ *                       instead of 12.  Writers and readers of a slot must agree: every handle that takes part in a step is
+ *                       given the same layout (3dgrut_b200/dist.py, PeerExchange(compact=True)); gut_sh_gradient_expand (one
+ *                       dense buffer for all views) refuses a handle in compact mode.
+ * The layout cannot change while a step is pending (between gut_backward_colour and gut_density_gradient_finish).
+ */
+#define GUT_COLOUR_DENSE 0
+#define GUT_COLOUR_COMPACT 1
+GUT_API int gut_set_colour_layout(GutHandle* h, int32_t layout);
+GUT_API uint64_t gut_colour_slot_floats(uint32_t num_particles, int32_t layout);
 GUT_API int gut_peer_buffer_create(GutHandle* h, size_t bytes, void** d_ptr_out, unsigned char* ipc_handle_out /* [64] */);
 GUT_API int gut_peer_buffer_destroy(GutHandle* h, void* d_ptr);
 GUT_API int gut_peer_buffer_open(GutHandle* h, const unsigned char* ipc_handle /* [64] */, void** d_ptr_out);

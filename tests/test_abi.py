@@ -51,3 +51,15 @@ def test_stage_names_follow_reference_tags():
     for tag in ("render::project", "render::prepare-expand", "render::expand", "render::sort", "render::render",
                 "render-backward::render", "render-backward::project"):
         assert tag in names
+
+
+def test_colour_slot_sizes():
+    """gut_colour_slot_floats (host arithmetic, no GPU): dense = [N,3] padded to 16 bytes; compact = 4 header floats + one
+    (mask, first row) pair per 32 particles (padded to 16 bytes) + room for every row."""
+    native = importlib.import_module("3dgrut_b200.native")
+    lib = native.load_library()
+    for n in (0, 1, 31, 32, 33, 3001, 3_000_000):
+        rows = (3 * n + 3) // 4 * 4
+        assert lib.gut_colour_slot_floats(n, abi.GUT_COLOUR_DENSE) == rows
+        assert lib.gut_colour_slot_floats(n, abi.GUT_COLOUR_COMPACT) == 4 + (2 * ((n + 31) // 32) + 3) // 4 * 4 + rows
+        assert lib.gut_colour_slot_floats(n, abi.GUT_COLOUR_COMPACT) % 4 == 0

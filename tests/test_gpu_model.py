@@ -393,7 +393,7 @@ def test_feature_packing_for_every_sh_degree(max_deg):
     assert torch.equal(a2, alb) and torch.equal(s2, spc)
 
 
-@pytest.mark.parametrize("kind", ["deferred", "peer"])
+@pytest.mark.parametrize("kind", ["deferred", "peer", "peer-compact"])
 def test_optimizer_epilogue_leaves_the_bits_of_the_unfused_chain(raster, kind):
     """dist.optimizer_epilogue (gut_density_adam + gut_sh_expand_adam: activation adjoints, SH expansion, SelectiveAdam and the
     densification statistics as the epilogue of the step's gradient kernels, no gradient tensors in between) against the
@@ -420,14 +420,15 @@ def test_optimizer_epilogue_leaves_the_bits_of_the_unfused_chain(raster, kind):
     raw = {k: raw_t[v].clone() for k, v in names.items()}
     state = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in raw.items()}
     accum, denom = torch.zeros((n, 1), device="cuda"), torch.zeros((n, 1), device="cuda")
-    if kind == "peer":
+    if kind.startswith("peer"):
         try:
-            ex = gdist.PeerExchange(raster, n, 48, nv, "cuda", 0, world=1, track_visibility=True)
+            ex = gdist.PeerExchange(raster, n, 48, nv, "cuda", 0, world=1, track_visibility=True, compact=kind == "peer-compact")
         except RuntimeError as e:
             pytest.skip(f"CUDA IPC unavailable: {e}")
     else:
         ex = gdist.DeferredExchange(n, 48, nv, "cuda", world=1, track_visibility=True)
     try:
+        ex.use(raster)        # the slot layout the handle writes and reads (dense, or the compact one)
         for _step in range(2):
             packed = raster.activate_pack(raw["positions"], raw["rotation"], raw["scale"], raw["density"])
             sph = raster.pack_features(raw["features_albedo"], raw["features_specular"])
@@ -464,7 +465,8 @@ def test_optimizer_epilogue_leaves_the_bits_of_the_unfused_chain(raster, kind):
                 assert torch.equal(raw_b[k][inv], before[k][inv]), k              # invisible rows untouched
             assert torch.equal(accum, accum_b) and torch.equal(denom, denom_b) and float(denom.sum()) > 0
     finally:
-        if kind == "peer":
+        raster.set_colour_layout(0)
+        if kind.startswith("peer"):
             ex.close()
 
 

@@ -396,6 +396,86 @@ def test_expand_gather_with_peer_buffer_equals_contiguous_expand(pkg):
     px.close(); ex.close()
 
 
+def _decode_compact_slot(flat, n):
+    """A compact colour-gradient slot (include/gut_b200.h, GUT_COLOUR_COMPACT) as the dense [N,3] it stands for, plus its structure."""
+    words = flat.view(torch.int32)
+    count, groups = int(words[0]), (n + 31) // 32
+    table = words[4:4 + 2 * groups].view(groups, 2)
+    header = 4 + (2 * groups + 3) // 4 * 4
+    bits = ((table[:, :1] >> torch.arange(32, device=flat.device, dtype=torch.int32)) & 1).bool()       # [groups, 32]
+    row = table[:, 1:].long() + torch.cumsum(bits, dim=1) - bits.long()
+    rows = flat[header:header + 3 * count].view(count, 3)
+    dense = torch.zeros((groups * 32, 3), device=flat.device)
+    dense[bits.reshape(-1)] = rows[row[bits]]
+    return dense[:n].contiguous(), count, bits, row[bits]
+
+
+def test_compact_colour_slots(pkg):
+    """GUT_COLOUR_COMPACT: a view hands out only the rows it touched.  The slot decodes to a dense [N,3] with consistent structure
+    (every claimed row used once), the expansion reads it to the bit like the dense one it stands for, stale memory behind the
+    rows and in unused slots is never read, and the step's gradients are those of the dense layout."""
+    gdist = importlib.import_module("3dgrut_b200.dist")
+    native = importlib.import_module("3dgrut_b200.native")
+    raster = _raster(pkg)
+    n, w, h, nv = 30011, 96, 64, 3
+    scene = syn.make_scene(n, 3, seed=4)
+    d12, sph = syn.pack_density(scene).cuda(), scene["features"].cuda()
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    views, ups = [], []
+    for k in range(nv):
+        hv = syn.make_view(w, h, k=k, n_views=nv)
+        views.append({"rays_ori": hv["rays_ori"].cuda(), "rays_dir": hv["rays_dir"].cuda(), "camera": camera_of(hv)})
+        ups.append((torch.rand((h, w, 4), device="cuda", generator=gen) * 2 - 1, torch.rand((h, w, 1), device="cuda", generator=gen) * 0.01))
+    assert raster.colour_slot_floats(n, 0) == (3 * n + 3) // 4 * 4
+    assert raster.colour_slot_floats(n, 1) == 4 + (2 * ((n + 31) // 32) + 3) // 4 * 4 + (3 * n + 3) // 4 * 4
+    cx = gdist.PeerExchange(raster, n, 48, nv + 1, "cuda", rank=0, world=1, compact=True)     # one slot more than views: stays empty
+    dx = gdist.PeerExchange(raster, n, 48, nv + 1, "cuda", rank=0, world=1, compact=False)
+    try:
+        for lanes in (1, 2, 1):    # both buffer sets; one step with two handles writing slots
+            rasters = [raster, _raster(pkg)] if lanes == 2 else raster
+            cx.mine.fill_(float("nan"))                                      # nothing but what this step writes may be read
+            gdist.training_step_deferred(rasters, cx, views, 3, d12, sph, ups)
+            torch.cuda.synchronize()
+            assert raster.colour_layout == 1
+            dense = []
+            for i in range(nv):
+                dn, count, bits, rows_used = _decode_compact_slot(cx.slot(i), n)
+                assert count == int(bits.sum()) == cx.moved_rows(i) and 0 < count < n
+                assert torch.equal(torch.sort(rows_used)[0], torch.arange(count, device="cuda"))   # every claimed row, once
+                assert bool(torch.isfinite(dn).all()) and bool((dn != 0).any(dim=1).sum() == count)
+                dense.append(dn)
+            assert cx.moved_rows(nv) == 0
+            got = cx.radiance_grad.clone()
+            assert bool(torch.isfinite(got).all()) and bool(torch.isfinite(cx.density_grad).all())
+            # the same expansion from the decoded dense slots (plus an all-zero one for the unused slot): identical bits
+            raster.set_colour_layout(0)
+            dense.append(torch.zeros((n, 3), device="cuda"))
+            want = torch.empty((n, 48), device="cuda")
+            raster.sh_gradient_expand_gather(3, d12, cx.centres_all, [t.data_ptr() for t in dense], want)
+            assert torch.equal(got, want)
+            # and the step in the dense layout (another backward pass: equal up to the order of its atomics)
+            gdist.training_step_deferred(rasters, dx, views, 3, d12, sph, ups)
+            torch.cuda.synchronize()
+            assert raster.colour_layout == 0
+            for i in range(nv):
+                assert rel_l2(dense[i].cpu().numpy(), dx.slot(i).cpu().numpy()) <= 1e-5
+            assert rel_l2(got.cpu().numpy(), dx.radiance_grad.cpu().numpy()) <= 1e-5
+            assert rel_l2(cx.density_grad.cpu().numpy(), dx.density_grad.cpu().numpy()) <= 1e-5
+        # a handle in compact mode refuses dense arguments
+        raster.set_colour_layout(1)
+        with pytest.raises(native.GutError):
+            raster.sh_gradient_expand(3, d12, cx.centres_all[:nv], torch.zeros((nv, n, 3), device="cuda"), torch.empty((n, 48), device="cuda"))
+        v, (rg, dg) = views[0], ups[0]
+        rgba, dist_, _hits, _vis = raster.trace(0, 3, d12, sph, v["rays_ori"], v["rays_dir"], None, v["camera"])
+        with pytest.raises(native.GutError):
+            raster.trace_bwd_colour(3, d12, sph, v["rays_ori"], v["rays_dir"], v["camera"], rgba, rg, dist_, dg, torch.zeros((n, 3), device="cuda"))
+        with pytest.raises(native.GutError):
+            raster.set_colour_layout(7)
+    finally:
+        raster.set_colour_layout(0)
+        cx.close(); dx.close()
+
+
 def test_empty_and_error_paths(pkg):
     native = importlib.import_module("3dgrut_b200.native")
     raster = _raster(pkg)
