@@ -471,11 +471,10 @@ static int backward_impl(GutHandle* h, void* stream_, const GutCamera* camera, u
     }
     {
         StageTimer t(h, ST_BWD_PROJECT, s);
-        if (d_colour_grad && h->colour_compact) GUT_CUDA(h, cudaMemsetAsync(d_colour_grad, 0, 16, s));   // the slot's row cursor
         GUT_CUDA(h, gut_launch_project_backward(h->cfg, fr, N, sph_degree, d_density, (const uint32_t*)h->tiles_count.p,
                                                 (const float4*)h->features.p, (float*)h->raw_grad.p, d_density_grad, d_radiance_grad,
                                                 d_colour_grad, h->colour_compact, deferred_view ? (float*)h->a_sum.p : nullptr, accumulate, s));
-        h->launches += 1;
+        h->launches += (d_colour_grad && h->colour_compact) ? 2 : 1;   // + the slot's cursor reset
     }
     if (h->cfg.enable_kernel_timings) stop_timer(h->timers, s);
     return GUT_OK;

@@ -696,6 +696,11 @@ __global__ void __launch_bounds__(256) gut_view_fold_kernel(uint32_t N, float3 c
     colour_store<8>(colour_out, N, i, g, COMPACT);
 }
 
+// Row cursor of a compact slot back to zero.  A kernel, not cudaMemsetAsync: the slot may live in memory that peers have mapped
+// (gut_peer_buffer_create), and a memset there does not stay confined to its stream -- it cost 2 ms per view with two handles
+// on two streams.
+__global__ void gut_colour_cursor_reset_kernel(uint4* __restrict__ slot) { *slot = make_uint4(0u, 0u, 0u, 0u); }
+
 // a_sum [N,4]: the deferred step's sum of A over its views.  Required with colour_out (one view of a deferred step) and
 // with density_grad alone (end of the step); NULL for the one-view backward, which folds its own origin.
 cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& frame, uint32_t N, int sph_degree,
@@ -703,6 +708,7 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
                                         float* raw_grad, float* density_grad, float* sph_grad, float* colour_out, int colour_compact,
                                         float* a_sum, int accumulate, cudaStream_t stream) {
     if (N == 0) return cudaSuccess;
+    if (colour_out && colour_compact) gut_colour_cursor_reset_kernel<<<1, 1, 0, stream>>>(reinterpret_cast<uint4*>(colour_out));
     const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
     const float4* d12 = reinterpret_cast<const float4*>(density12);
     float4* rg = reinterpret_cast<float4*>(raw_grad);
@@ -741,9 +747,35 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
 // loads of a chunk of views are issued before the first is used: one NVLink round trip per chunk, not per view.
 struct ExpandViews {
     const float* colour[GUT_EXPAND_MAX_VIEWS];   // one slot each: [N][3], or the compact layout (colour_store / colour_load above)
-    int compact;
 };
 constexpr int EXPAND_CHUNK = 8;
+// The colour gradients of views v0 .. v0 + EXPAND_CHUNK of particle i, all loads in flight together.  The layout is a template
+// parameter of the two expansion kernels: the dense instantiation is the code it was before the compact layout existed (a
+// run-time flag cost it 0.14 ms per step at 3M particles and 8 views).
+template <bool COMPACT>
+GUT_D void load_colour_chunk(const ExpandViews& views, uint32_t v0, uint32_t n_views, uint32_t N, uint32_t i, float3 (&gq)[EXPAND_CHUNK]) {
+    if (!COMPACT) {
+#pragma unroll
+        for (int q = 0; q < EXPAND_CHUNK; ++q) {
+            gq[q] = f3(0.f, 0.f, 0.f);
+            if (v0 + q < n_views) {
+                const float* gp = views.colour[v0 + q] + 3 * (size_t)i;
+                gq[q] = f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+            }
+        }
+    } else {
+        uint2 tq[EXPAND_CHUNK];
+#pragma unroll
+        for (int q = 0; q < EXPAND_CHUNK; ++q)
+            tq[q] = (v0 + q < n_views) ? colour_table_load(views.colour[v0 + q], i, true) : make_uint2(0u, 0u);
+#pragma unroll
+        for (int q = 0; q < EXPAND_CHUNK; ++q) {
+            gq[q] = f3(0.f, 0.f, 0.f);
+            if (v0 + q < n_views) gq[q] = colour_load(views.colour[v0 + q], N, i, tq[q], true);
+        }
+    }
+}
+template <bool COMPACT>
 __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                    uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
                                                                    ExpandViews views,
@@ -762,15 +794,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
         for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {   // static indices into the pointer table
             if (v0 >= n_views) break;
             float3 gq[EXPAND_CHUNK];
-            uint2 tq[EXPAND_CHUNK];
-#pragma unroll
-            for (int q = 0; q < EXPAND_CHUNK; ++q)
-                tq[q] = (v0 + q < n_views) ? colour_table_load(views.colour[v0 + q], i, views.compact != 0) : make_uint2(0u, 0u);
-#pragma unroll
-            for (int q = 0; q < EXPAND_CHUNK; ++q) {
-                gq[q] = f3(0.f, 0.f, 0.f);
-                if (v0 + q < n_views) gq[q] = colour_load(views.colour[v0 + q], N, i, tq[q], views.compact != 0);
-            }
+            load_colour_chunk<COMPACT>(views, v0, n_views, N, i, gq);
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
                 const float3 g = gq[q];
@@ -825,6 +849,7 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
 #ifndef GUT_SHADAM_MIN_BLOCKS
 #define GUT_SHADAM_MIN_BLOCKS 8
 #endif
+template <bool COMPACT>
 __global__ void __launch_bounds__(K6_THREADS, GUT_SHADAM_MIN_BLOCKS) gut_sh_expand_adam_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                         uint32_t n_views, const float* __restrict__ centres, ExpandViews views,
                                                                         GutAdamTensors albedo, GutAdamTensors specular,
@@ -849,15 +874,7 @@ __global__ void __launch_bounds__(K6_THREADS, GUT_SHADAM_MIN_BLOCKS) gut_sh_expa
         for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {
             if (v0 >= n_views) break;
             float3 gq[EXPAND_CHUNK];
-            uint2 tq[EXPAND_CHUNK];
-#pragma unroll
-            for (int q = 0; q < EXPAND_CHUNK; ++q)
-                tq[q] = (v0 + q < n_views) ? colour_table_load(views.colour[v0 + q], i, views.compact != 0) : make_uint2(0u, 0u);
-#pragma unroll
-            for (int q = 0; q < EXPAND_CHUNK; ++q) {
-                gq[q] = f3(0.f, 0.f, 0.f);
-                if (v0 + q < n_views) gq[q] = colour_load(views.colour[v0 + q], N, i, tq[q], views.compact != 0);
-            }
+            load_colour_chunk<COMPACT>(views, v0, n_views, N, i, gq);
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
                 const float3 g = gq[q];
@@ -931,12 +948,16 @@ cudaError_t gut_launch_sh_expand_adam(uint32_t N, int sph_degree, const float* d
     if (N == 0) return cudaSuccess;
     if (n_views > GUT_EXPAND_MAX_VIEWS) return cudaErrorInvalidValue;
     ExpandViews views = {};
-    views.compact = colour_compact;
     for (uint32_t v = 0; v < n_views; ++v) views.colour[v] = colour_ptrs[v];
     auto aligned = [](const GutAdamTensors& t) { return (((uintptr_t)t.param | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15u) == 0; };
     const uint32_t vec_mask = (aligned(albedo) ? 1u : 0u) | (aligned(specular) ? 2u : 0u);   // a warp's span starts at 32 x width floats
-    gut_sh_expand_adam_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
-        N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, views, albedo, specular, visibility, b1, b2, eps, vec_mask);
+    const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
+    if (colour_compact)
+        gut_sh_expand_adam_kernel<true><<<grid, K6_THREADS, 0, stream>>>(
+            N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, views, albedo, specular, visibility, b1, b2, eps, vec_mask);
+    else
+        gut_sh_expand_adam_kernel<false><<<grid, K6_THREADS, 0, stream>>>(
+            N, sph_degree, reinterpret_cast<const float4*>(density12), n_views, centres, views, albedo, specular, visibility, b1, b2, eps, vec_mask);
     return cudaGetLastError();
 }
 
@@ -949,11 +970,16 @@ cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all,
     do {
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         ExpandViews views = {};
-        views.compact = colour_compact;
         for (uint32_t v = 0; v < nv; ++v) views.colour[v] = colour_ptrs[done + v];
-        gut_sh_expand_kernel<<<(N + K6_THREADS - 1) / K6_THREADS, K6_THREADS, 0, stream>>>(
-            N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
-            reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0, ncoef_all);
+        const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
+        if (colour_compact)
+            gut_sh_expand_kernel<true><<<grid, K6_THREADS, 0, stream>>>(
+                N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
+                reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0, ncoef_all);
+        else
+            gut_sh_expand_kernel<false><<<grid, K6_THREADS, 0, stream>>>(
+                N, sph_degree, reinterpret_cast<const float4*>(density12), nv, centres + 3 * (size_t)done, views,
+                reinterpret_cast<float4*>(sph_grad), (accumulate || done > 0) ? 1 : 0, ncoef_all);
         done += nv;
     } while (done < n_views);
     return cudaGetLastError();

@@ -265,9 +265,11 @@ class PeerExchange(DeferredExchange):
         super().__init__(n_particles, n_sph_floats, views_per_rank, device, world=world, track_visibility=track_visibility,
                          gather_buffer=False)   # peer buffers instead
         self.raster, self.rank = raster, rank
-        # compact slots (include/gut_b200.h, GUT_COLOUR_COMPACT): only the rows a view touched cross NVLink.  Default: on when
-        # there is a peer to read them; every rank must choose the same.
-        self.compact = (self.world > 1) if compact is None else bool(compact)
+        # compact slots (include/gut_b200.h, GUT_COLOUR_COMPACT): only the rows a view touched cross NVLink, at the price of a
+        # second, dependent load in the expansion.  Off by default: measured equal to the dense layout at 1 and 2 GPUs (3M
+        # particles, 8 views), not yet measured where the expansion is bound by NVLink ingress (8 GPUs).  Every rank must choose
+        # the same.
+        self.compact = bool(compact)
         self.colour_layout = 1 if self.compact else 0
         self.slot_floats = raster.colour_slot_floats(n_particles, self.colour_layout)       # 16-byte aligned slots
         self.slot_header_floats = self.slot_floats - (3 * n_particles + 3) // 4 * 4          # compact: row cursor + table

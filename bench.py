@@ -48,7 +48,7 @@ def parse_args():
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--colour-slots", choices=("auto", "dense", "compact"), default="auto",
-                   help="layout of the peer exchange's per-view colour-gradient slots (auto: compact when n_gpus > 1)")
+                   help="layout of the peer exchange's per-view colour-gradient slots (auto = the exchange's default: dense)")
     p.add_argument("--lanes", type=int, default=2, help="handles / CUDA streams a rank deals its views to (1 = one stream)")
     p.add_argument("--exchange", choices=("auto", "peer", "deferred", "allreduce"), default="auto",
                    help="gradient exchange of the step: deferred = allreduce [N,12] + all-gather per-view colour gradients, SH expansion "
@@ -326,7 +326,7 @@ def run_ours(args):
     lanes = [raster] + ([native.SplatRaster(cfg, device=dev)] if (args.lanes > 1 and n_my_views > 1) else [])
     if args.exchange == "auto":
         args.exchange = "peer" if world > 1 else "deferred"
-    # colour-gradient slots of the peer exchange: compact (touched rows only) when there is a peer to read them
+    # colour-gradient slots of the peer exchange: dense [N,3], or compact (touched rows only: less NVLink traffic, one more dependent load)
     compact_slots = {"auto": None, "dense": False, "compact": True}[args.colour_slots]
     if args.exchange == "peer":
         try:

@@ -279,7 +279,8 @@ GUT_API int gut_sh_gradient_expand_gather(GutHandle* h, void* stream, uint32_t n
  *                       each, behind a table of one (mask, first row) pair per 32 particles: float 0 = rows in use, floats
  *                       4 .. 4 + table the table, rows behind it.  A slot holds gut_colour_slot_floats(N, layout) floats and is
  *                       16-byte aligned.  The expansion on another GPU then pulls ~3 B per particle and view over NVLink
- *                       instead of 12.  Writers and readers of a slot must agree: every handle that takes part in a step is
+ *                       instead of 12, through two dependent loads instead of one (measured equal to the dense layout at 1 and
+ *                       2 GPUs; an option for steps bound by NVLink ingress).  Writers and readers of a slot must agree: every handle that takes part in a step is
  *                       given the same layout (3dgrut_b200/dist.py, PeerExchange(compact=True)); gut_sh_gradient_expand (one
  *                       dense buffer for all views) refuses a handle in compact mode.
  * The layout cannot change while a step is pending (between gut_backward_colour and gut_density_gradient_finish).
