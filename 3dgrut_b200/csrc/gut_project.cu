@@ -775,8 +775,14 @@ GUT_D void load_colour_chunk(const ExpandViews& views, uint32_t v0, uint32_t n_v
         }
     }
 }
+// -DGUT_EXPAND_SMEM_ACC=1 keeps the 48 sums in the lane's row of the shared tile instead of registers (117 -> 64 registers, 4 -> 8
+// CTAs per SM; same bits).  Measured on one GPU (3M particles, 8 local views): 0.35 -> 0.40 ms, so it is off; whether twice the
+// loads in flight shorten the NVLink-latency-bound expansion at 8 GPUs is not measured yet.
+#ifndef GUT_EXPAND_SMEM_ACC
+#define GUT_EXPAND_SMEM_ACC 0
+#endif
 template <bool COMPACT>
-__global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
+__global__ void __launch_bounds__(K6_THREADS, GUT_EXPAND_SMEM_ACC ? 8 : 1) gut_sh_expand_kernel(uint32_t N, int sph_degree, const float4* __restrict__ density12,
                                                                    uint32_t n_views, const float* __restrict__ centres /* [n_views][3] */,
                                                                    ExpandViews views,
                                                                    float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate,
@@ -785,7 +791,11 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t warp_base = i - lane;
+#if GUT_EXPAND_SMEM_ACC
+    float* const acc = &s_out[wid][lane][0];
+#else
     float acc[48];
+#endif
 #pragma unroll
     for (int k = 0; k < 48; ++k) acc[k] = 0.0f;
     if (i < N) {
@@ -823,8 +833,10 @@ __global__ void __launch_bounds__(K6_THREADS) gut_sh_expand_kernel(uint32_t N, i
         }
         return;
     }
+#if !GUT_EXPAND_SMEM_ACC
 #pragma unroll
     for (int k = 0; k < 48; ++k) s_out[wid][lane][k] = acc[k];
+#endif
     __syncwarp();
     const uint32_t rows = warp_base < N ? min(32u, N - warp_base) : 0u;
     float4* dst = sph_grad + 12 * (size_t)warp_base;
