@@ -747,7 +747,12 @@ cudaError_t gut_launch_project_backward(const GutConfig& cfg, const GutFrame& fr
 // loads of a chunk of views are issued before the first is used: one NVLink round trip per chunk, not per view.
 struct ExpandViews {
     const float* colour[GUT_EXPAND_MAX_VIEWS];   // one slot each: [N][3], or the compact layout (colour_store / colour_load above)
+    int wide;                                    // dense slots, all 16-byte aligned: a warp may fetch its 32 rows as 24 x 16 bytes
 };
+GUT_D void copy16_async(void* sdst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory");
+}
+GUT_D void copy_async_wait() { asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory"); }
 constexpr int EXPAND_CHUNK = 8;
 // The colour gradients of views v0 .. v0 + EXPAND_CHUNK of particle i, all loads in flight together.  The layout is a template
 // parameter of the two expansion kernels: the dense instantiation is the code it was before the compact layout existed (a
@@ -787,24 +792,43 @@ __global__ void __launch_bounds__(K6_THREADS, GUT_EXPAND_SMEM_ACC ? 8 : 1) gut_s
                                                                    ExpandViews views,
                                                                    float4* __restrict__ sph_grad /* [N][12] float4 */, int accumulate,
                                                                    int ncoef_all /* (sph_max_degree + 1)^2: the row holds 3 ncoef_all floats */) {
-    __shared__ float s_out[K6_WARPS][32][49];
+    __shared__ __align__(16) float s_out[K6_WARPS][32][49];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t warp_base = i - lane;
 #if GUT_EXPAND_SMEM_ACC
     float* const acc = &s_out[wid][lane][0];
+    const bool wide = false;
 #else
     float acc[48];
+    // A full warp's 32 dense rows of one view are 384 contiguous bytes: 24 lanes copy 16 bytes each straight into the warp's part
+    // of the (not yet used) output tile -- 8 asynchronous wide requests per chunk of views instead of 24 four-byte loads per lane,
+    // which is what a peer's memory across NVLink wants -- and every lane then picks its row out of shared memory.
+    const bool wide = !COMPACT && views.wide != 0 && warp_base + 32u <= N;   // warp-uniform
 #endif
 #pragma unroll
     for (int k = 0; k < 48; ++k) acc[k] = 0.0f;
-    if (i < N) {
-        const float4 r0 = __ldg(density12 + 3 * (size_t)i);
+    float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < N) r0 = __ldg(density12 + 3 * (size_t)i);
 #pragma unroll
-        for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {   // static indices into the pointer table
-            if (v0 >= n_views) break;
-            float3 gq[EXPAND_CHUNK];
+    for (uint32_t v0 = 0; v0 < GUT_EXPAND_MAX_VIEWS; v0 += EXPAND_CHUNK) {   // static indices into the pointer table
+        if (v0 >= n_views) break;
+        float3 gq[EXPAND_CHUNK];
+        if (wide) {
+            float* const st = &s_out[wid][0][0];   // 96 floats per view of the chunk
+            __syncwarp();                          // the previous chunk has been read
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q)
+                if (v0 + q < n_views && lane < 24u) copy16_async(st + 96 * q + 4 * lane, views.colour[v0 + q] + 3 * (size_t)warp_base + 4 * lane);
+            copy_async_wait();
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < EXPAND_CHUNK; ++q)
+                gq[q] = (v0 + q < n_views) ? f3(st[96 * q + 3 * lane], st[96 * q + 3 * lane + 1], st[96 * q + 3 * lane + 2]) : f3(0.f, 0.f, 0.f);
+        } else if (i < N) {
             load_colour_chunk<COMPACT>(views, v0, n_views, N, i, gq);
+        }
+        if (i < N) {
 #pragma unroll
             for (int q = 0; q < EXPAND_CHUNK; ++q) {
                 const float3 g = gq[q];
@@ -834,6 +858,7 @@ __global__ void __launch_bounds__(K6_THREADS, GUT_EXPAND_SMEM_ACC ? 8 : 1) gut_s
         return;
     }
 #if !GUT_EXPAND_SMEM_ACC
+    __syncwarp();   // (wide: the staged rows have been read by every lane before the tile takes the sums)
 #pragma unroll
     for (int k = 0; k < 48; ++k) s_out[wid][lane][k] = acc[k];
 #endif
@@ -982,7 +1007,11 @@ cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all,
     do {
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         ExpandViews views = {};
-        for (uint32_t v = 0; v < nv; ++v) views.colour[v] = colour_ptrs[done + v];
+        views.wide = colour_compact ? 0 : 1;
+        for (uint32_t v = 0; v < nv; ++v) {
+            views.colour[v] = colour_ptrs[done + v];
+            if ((uintptr_t)colour_ptrs[done + v] & 15u) views.wide = 0;
+        }
         const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
         if (colour_compact)
             gut_sh_expand_kernel<true><<<grid, K6_THREADS, 0, stream>>>(
