@@ -1007,10 +1007,20 @@ cudaError_t gut_launch_sh_expand_ptrs(uint32_t N, int sph_degree, int ncoef_all,
     do {
         const uint32_t nv = n_views - done < GUT_EXPAND_MAX_VIEWS ? n_views - done : GUT_EXPAND_MAX_VIEWS;
         ExpandViews views = {};
+        // the wide fetch (cp.async into the output tile) is used for 16-byte aligned slots in THIS device's memory: it is measured
+        // there (0.35 -> 0.33 ms); a peer's slots keep the per-lane loads the multi-GPU figures were taken with until the wide form
+        // has been timed across NVLink
         views.wide = colour_compact ? 0 : 1;
+        int here = 0;
+        if (cudaGetDevice(&here) != cudaSuccess) views.wide = 0;
         for (uint32_t v = 0; v < nv; ++v) {
             views.colour[v] = colour_ptrs[done + v];
             if ((uintptr_t)colour_ptrs[done + v] & 15u) views.wide = 0;
+            if (views.wide) {
+                cudaPointerAttributes at;
+                if (cudaPointerGetAttributes(&at, colour_ptrs[done + v]) != cudaSuccess) { (void)cudaGetLastError(); views.wide = 0; }
+                else if (at.type != cudaMemoryTypeDevice || at.device != here) views.wide = 0;
+            }
         }
         const dim3 grid((N + K6_THREADS - 1) / K6_THREADS);
         if (colour_compact)
