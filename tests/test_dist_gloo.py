@@ -183,3 +183,28 @@ def test_two_rank_step_with_one_view_per_rank(nviews):
     for _rank, g1, g2 in res:
         assert np.allclose(g1, ref1.numpy(), rtol=1e-5, atol=1e-5)
         assert np.allclose(g2, ref2.numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_exchange_slot_helpers_on_cpu():
+    """Slot bookkeeping shared by the exchanges: clear_slot / moved_rows on the dense layout, and use() handing the exchange's
+    slot layout to handles that know about layouts (stand-ins without the call are left alone)."""
+    ex = gdist.DeferredExchange(N, NSPH, 2, "cpu", world=1)
+    ex.begin_step(0)
+    assert ex.colour_layout == 0 and ex.moved_rows(0) == 0
+    ex.slot(0)[3] = torch.tensor([0.0, 2.0, 0.0])
+    ex.slot(0)[9] = torch.tensor([1.0, 0.0, -1.0])
+    ex.slot(1)[0, 0] = 5.0
+    assert ex.moved_rows(0) == 2 and ex.moved_rows(1) == 1
+    ex.clear_slot(0)
+    assert ex.moved_rows(0) == 0 and ex.moved_rows(1) == 1
+
+    class Layouted:
+        seen = None
+
+        def set_colour_layout(self, layout):
+            self.seen = layout
+
+    a, b = Layouted(), Layouted()
+    ex.use([a, FakeRaster(), b])
+    ex.use(FakeRaster())
+    assert a.seen == 0 and b.seen == 0
